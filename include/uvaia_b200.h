@@ -1,0 +1,149 @@
+/* uvaia_b200.h -- C ABI of the B200-native n-best database search (drop-in for the scoring/heap seam of the
+ * reference program `uvaia`, src/nearest.c).  Plain C: pointers and sizes only, no torch / C++ types.
+ *
+ * The reference has no plugin or FFI interface: `uvaia` is a monolith whose main() calls
+ *     queue_distance_to_consensus (query_t, queue_t, int ir)            src/nearest.c:428-433
+ *     queue_update_min_heaps     (query_t, int iq, queue_t, int ir)    src/nearest.c:442-510
+ *     heap_insert (heap_t, q_item) / heap_finalise_heap_qsort          src/min_heap.c:93-117, 149-158
+ *     quick_count_sequence_non_N (char*, size_t)                       src/fastaseq.c:642-648
+ *     create_query_indices (query_t)                                   src/fastaseq.c:732-777
+ * inside two OpenMP loops (src/nearest.c:293-299).  The entry points below are what a C host bound to this
+ * library calls INSTEAD of those functions; INTEGRATION.md shows the binding in nearest.c.
+ *
+ * Conventions: every function returns 0 on success, a negative UVG_E* code otherwise; uvg_last_error() gives the
+ * message (the reference's biomcmc_error() prints and exits, lowlevel.c:39-52 -- the host decides here).
+ * One host thread drives one context; a context owns one CUDA device and its streams.
+ * There is NO CPU fallback: without a usable CUDA device uvg_create() fails with UVG_ENODEV.
+ */
+#ifndef UVAIA_B200_H
+#define UVAIA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UVG_ABI_VERSION 1
+
+enum { UVG_OK = 0, UVG_EINVAL = -1, UVG_ENODEV = -2, UVG_ENOMEM = -3, UVG_ECUDA = -4, UVG_ESTATE = -5, UVG_ENCCL = -6 };
+
+typedef struct uvg_ctx uvg_ctx;
+
+/* One kept neighbour = the reference's q_item (src/min_heap.h:14-18) with the strdup'ed name replaced by the
+ * ordinal of the reference sequence among the ACCEPTED references, in file order (the host keeps the names). */
+typedef struct uvg_item {
+    int32_t score[6];   /* default: acgt, text, partial, valid, acgt_unique, valid_ref_sites  (nearest.c:499-501)
+                           --acgt : match, valid, match_unique, valid_ref_sites, dist_consensus, dist_unique (:466-470) */
+    int64_t ref;        /* global ordinal of the accepted reference */
+} uvg_item;
+
+typedef struct uvg_params {
+    int32_t abi_version;    /* UVG_ABI_VERSION */
+    int32_t nchar;          /* alignment columns (query->aln->nchar) */
+    int32_t trim;           /* --trim, clamped by the library like fastaseq.c:708-712 */
+    int32_t nbest;          /* --nbest; heap capacity is max(2, nbest) (min_heap.c:58) */
+    int32_t acgt_mode;      /* --acgt */
+    int32_t pool;           /* --pool: only used to detect hazard H1 (pool-dependent truncation) */
+    int32_t device;         /* CUDA ordinal */
+    int32_t first_round;    /* references in the first scoring round per rank (0 = default 1024) */
+    int32_t max_round;      /* largest round per rank (0 = default 65536) */
+    int32_t early_abort;    /* 1 = warp-granular abort of pairs that cannot beat the k-th best (exact, perf only) */
+    int32_t rank, world;    /* row sharding: this context holds tile `rank` of every round (world<=1: single GPU) */
+    int64_t max_survivors;  /* capacity of the survivor buffer in records of 32 B (0 = default) */
+    int64_t db_capacity;    /* references to reserve HBM for (0 = grow on demand) */
+} uvg_params;
+
+typedef struct uvg_query_info {
+    int32_t n_query, nchar, trim;           /* trim after clamping */
+    int32_t n_idx, n_idx_m, n_idx_c;        /* sizes of the three site sets (stderr line fastaseq.c:774) */
+} uvg_query_info;
+
+typedef struct uvg_stats {
+    int64_t n_refs;             /* references scored so far */
+    int64_t n_rounds;
+    int64_t n_survivors;        /* records emitted by the pair-count kernel */
+    int64_t n_admitted;         /* successful heap insertions */
+    int64_t n_h1_flags;         /* admissions that MAY depend on --pool in the reference (hazard H1) */
+    int64_t n_overflow_splits;  /* rounds that had to be split because the survivor buffer filled */
+    int64_t pair_kernel_launches, other_kernel_launches;
+    double  pair_kernel_ms;     /* CUDA-event time of the pair-count launches of the last uvg_search */
+    double  replay_ms;          /* ... of bucket+replay */
+    double  search_ms;          /* ... whole uvg_search */
+    double  encode_ms;          /* ... of the encoder launches of the last uvg_push_refs* */
+    int64_t max_mismatch;       /* "Highest number of ACGT mismatches" (nearest.c:324): max over queries of max_incompatible-1 */
+} uvg_stats;
+
+/* ---- life cycle ---- */
+int  uvg_create(const uvg_params* p, uvg_ctx** out);
+void uvg_destroy(uvg_ctx* ctx);
+const char* uvg_last_error(const uvg_ctx* ctx);        /* ctx may be NULL: error of the last failed uvg_create */
+int  uvg_abi_version(void);
+
+/* ---- queries: replaces create_query_indices + the per-query strings read by queue_update_min_heaps ----
+ * text = n_query rows of nchar bytes, ALREADY filtered (utils.c:10-48) and ordered (fastaseq.c:779-795) by the
+ * host; case-insensitive.  Builds consensus / idx / idx_m / idx_c, the trimmed bit-planes of every query and the
+ * consensus pseudo-query on the device, and empties all heaps (max_incompatible = nchar, nearest.c:375,387). */
+int uvg_set_queries(uvg_ctx* ctx, const uint8_t* text, int32_t n_query, uvg_query_info* info);
+
+/* ---- references: replaces quick_count_sequence_non_N + the ref filter (nearest.c:263-270) + the char2bit lookups.
+ * text = n rows of nchar bytes (host memory; pinned memory makes the copy asynchronous).  Each row gets
+ * non_n_out[i] = #bytes not in "NnXx-?Oo." over the whole row and accepted_out[i] = (non_n >= min_non_n);
+ * accepted rows are appended, in order, to the device-resident packed database (4-bit IUPAC sets as four
+ * bit-planes, 32 references interleaved per 16-byte column word).  Either output pointer may be NULL.
+ * *n_accepted (may be NULL) receives the number appended. */
+int uvg_push_refs(uvg_ctx* ctx, const uint8_t* text, int64_t n, int32_t min_non_n,
+                  int32_t* non_n_out, uint8_t* accepted_out, int64_t* n_accepted);
+/* Same, with text already in device memory (bench "inputs resident in HBM"; outputs stay host pointers). */
+int uvg_push_refs_device(uvg_ctx* ctx, const uint8_t* d_text, int64_t n, int32_t min_non_n,
+                         int32_t* non_n_out, uint8_t* accepted_out, int64_t* n_accepted);
+/* Forget the packed references scored so far but keep heaps and ordinals (streaming hosts: push, search, drop). */
+int uvg_drop_refs(uvg_ctx* ctx);
+int64_t uvg_db_count(const uvg_ctx* ctx);              /* accepted references resident on this rank */
+
+/* ---- search: replaces the two OpenMP loops nearest.c:293-299 (consensus stage, per-query heap updates) ----
+ * Scores every resident reference not scored yet against every query, in file order, in rounds.  Bit-exact with
+ * the reference's sequential admission (order-dependent max_incompatible rule and first-come tie-break). */
+int uvg_search(uvg_ctx* ctx);
+/* Empty all heaps and mark every resident reference as not scored (repeat a search over the same database). */
+int uvg_reset_search(uvg_ctx* ctx);
+
+/* ---- results: replaces heap_finalise_heap_qsort + the reads in save_distance_table (nearest.c:513-547) ----
+ * out must hold max(2,nbest) items; rows come in the reference's output order (heap array after the slot0<->slot n
+ * swap, then libc qsort with compare_q_item); *n = rows (hazard H2: never the NULL-name rows). */
+int uvg_get_heap(uvg_ctx* ctx, int32_t iq, uvg_item* out, int32_t* n);
+/* flags[i] = 1 if accepted reference ordinal first+i ever entered any heap (is_best, nearest.c:303-314). */
+int uvg_get_ever_best(uvg_ctx* ctx, int64_t first, int64_t n, uint8_t* flags);
+int uvg_get_stats(uvg_ctx* ctx, uvg_stats* out);
+
+/* ---- row sharding over several GPUs (one context per GPU / process) ----
+ * Round j covers global ordinals [S_j, S_j + world*T_j) and rank g holds [S_j + g*T_j, S_j + (g+1)*T_j), with
+ * T_1 = first_round, T_{j+1} = min(4*T_j, max_round).  uvg_shard_of maps a global ordinal to (rank, local index). */
+int uvg_shard_of(int64_t ordinal, int32_t world, int32_t first_round, int32_t max_round, int32_t* rank, int64_t* local);
+int uvg_nccl_unique_id(void* out128);                          /* 128 bytes, made by rank 0, sent to all by the host */
+int uvg_nccl_init(uvg_ctx* ctx, const void* id128);            /* collective over all `world` contexts */
+/* In sharded mode every rank declares how many accepted references exist in total before uvg_search. */
+int uvg_set_global_count(uvg_ctx* ctx, int64_t n_total);
+
+/* ---- bench / test utilities (not part of the reference seam) ---- */
+/* Device generator of SARS-CoV-2-shaped alignment rows (same model as uvaia_b200/synth.py; counter-based RNG keyed
+ * by (seed, ordinal)).  clades = n_clades rows of nchar bytes (host).  Writes n rows for ordinals first.. into d_text. */
+int uvg_synth_rows_device(uvg_ctx* ctx, const uint8_t* clades, int32_t n_clades, uint64_t seed, int64_t first,
+                          int64_t n, double n_frac_mean, double ambiguous_frac, uint8_t* d_text);
+void* uvg_device_alloc(uvg_ctx* ctx, size_t bytes);
+void  uvg_device_free(uvg_ctx* ctx, void* p);
+int   uvg_memcpy_d2h(uvg_ctx* ctx, void* dst, const void* d_src, size_t bytes);
+int   uvg_memcpy_h2d(uvg_ctx* ctx, void* d_dst, const void* src, size_t bytes);
+void* uvg_host_alloc_pinned(size_t bytes);
+void  uvg_host_free_pinned(void* p);
+/* Raw per-pair counts of queries x resident references [first, first+n): out[(iq*n + i)*4 + k], k = the four
+ * counters of the mode (default: acgt,text,partial,valid; --acgt: match,valid,mism_idx,0).  Unit-test hook. */
+int uvg_debug_pair_counts(uvg_ctx* ctx, int64_t first, int64_t n, int32_t* out);
+/* Unpack resident reference `local` back to its 4-bit codes (nchar bytes, values 0..15).  Unit-test hook. */
+int uvg_debug_unpack_ref(uvg_ctx* ctx, int64_t local, uint8_t* codes_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UVAIA_B200_H */

@@ -1,0 +1,74 @@
+// Shared layout definitions of the B200 n-best search engine (kernels + host).  See DESIGN.md sections 3-5.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace uvg {
+
+// ---- packed database layout -------------------------------------------------------------------------------
+// A site is a 4-bit IUPAC set (A=1,C=2,G=4,T=8; 0 = invalid: N,O,X,?,- and unknown bytes; biomcmc alignment.c:906-931
+// with the skip rule of :870).  32 consecutive sites of ONE reference form a "column word" of four bit-planes
+// (uint4: x=A, y=C, z=G, w=T; bit i = site 32*w+i).  32 consecutive references form a GROUP; the database is
+//     uint4 db[group][Wp][32]      (lane = reference within group)
+// so a warp reading column word w of its group issues one fully coalesced 512-byte request of 128-bit loads.
+constexpr int GROUP = 32;
+constexpr int WC = 16;            // column words per staged query chunk
+constexpr int QTILE = 64;         // queries per thread block (8 warps x QPW)
+constexpr int QPW = 8;            // queries per warp (register tile)
+constexpr int PAIR_THREADS = 256;
+constexpr int STAGES = 3;
+
+// One staged chunk of a query tile: WC column words of 64 queries.  Contiguous in global memory so that one
+// cp.async.bulk (TMA 1-D bulk copy) moves it into shared memory.
+struct __align__(16) QChunk {
+    uint4    acgt[WC][QTILE];     // query bit-planes (zero outside the trimmed range / beyond nchar)
+    uint2    vo[WC][QTILE];       // x = valid plane (a|c|g|t); y = default mode: one-hot plane, --acgt mode: idx site mask
+    uint32_t slow[WC];            // bit k: warp k has an ambiguous (multi-base) query site in this word
+    uint32_t rem[QTILE];          // max ACGT matches query can still collect in the chunks AFTER this one
+};
+static_assert(sizeof(QChunk) % 16 == 0, "bulk copy size must be a multiple of 16");
+
+// Survivor record emitted by the pair-count kernel and consumed by the replay kernel (32 B).
+struct __align__(16) Survivor {
+    int32_t q;
+    int32_t r;                    // global ordinal of the accepted reference
+    int32_t s[6];
+};
+
+// Heap slot (32 B): the reference's q_item (src/min_heap.h:14-18) with name -> ordinal.
+struct __align__(16) HeapItem {
+    int32_t s[6];
+    int32_t r;
+    int32_t pad;
+};
+
+// Per-query threshold snapshot read by the pair-count kernel: the heap root (worst kept item) once the heap is full.
+struct __align__(16) Threshold {
+    int32_t s[6];
+    int32_t full;
+    int32_t pad;
+};
+
+struct PairParams {
+    const uint4*    db;           // whole local database
+    const uint32_t* refamb;       // [group][ambw] bit w%32 of word w/32: some reference of the group is ambiguous in column word w
+    const QChunk*   qdata;        // [n_qtiles][n_chunks]
+    const Threshold* thr;         // [n_qtiles*QTILE]
+    const int32_t*  non_n;        // per local reference
+    const int32_t*  c0;           // per local reference: consensus-stage matches (c0 / cmatch)
+    const int32_t*  ci;           // per local reference: consensus-stage mismatches
+    int32_t Wp, n_chunks, ambw, n_qtiles, n_query;
+    int64_t local_begin, local_end;   // local reference range of this launch
+    int64_t global_minus_local;       // global ordinal = local index + this
+    Survivor* surv; int32_t* surv_ci; unsigned long long* surv_count; int64_t surv_cap;
+    int32_t* qcount;              // [n_query] survivors per query (bucket sizes)
+    int32_t early_abort;
+    int32_t* dbg_counts;          // optional [n_query][n][4] dump (debug hook); n = local_end-local_begin
+};
+
+__host__ __device__ inline int64_t db_word_index(int64_t group, int w, int lane, int Wp)
+{
+    return (group * Wp + w) * GROUP + lane;
+}
+
+}  // namespace uvg
