@@ -24,8 +24,7 @@ cudaError_t paircount_setup();       // opt in to the dynamic shared memory size
 
 // ---- replay.cu (K3) ----
 struct ReplayParams {
-    const Survivor* surv; const int32_t* surv_ci; int64_t n_surv;    // unsorted survivors of the round
-    Survivor* bucketed; int32_t* bucketed_ci;                         // scratch of the same capacity
+    const Survivor* bucketed; const int32_t* bucketed_ci;             // survivors of the round grouped by query
     int32_t* qcount; int32_t* qoffset; int32_t* qcursor;              // [n_query] (+1 for qoffset)
     HeapItem* heaps; int32_t* heap_n; int32_t* max_inc;               // [n_query][K+1], [n_query], [n_query]
     int32_t* batch_id; int32_t* max_inc_batch;                        // H1 bookkeeping per query
@@ -35,7 +34,11 @@ struct ReplayParams {
     int32_t n_query, K, acgt_mode, pool;
     int32_t round_first, round_count;                                 // global ordinal range of the round
 };
-cudaError_t launch_replay(const ReplayParams& p, cudaStream_t st);
+cudaError_t launch_bucket_count(const Survivor* seg, int64_t n, int32_t* qcount, cudaStream_t st);
+cudaError_t launch_bucket_scan(const int32_t* qcount, int32_t* qoffset, int32_t* qcursor, int n_query, cudaStream_t st);
+cudaError_t launch_bucket_scatter(const Survivor* seg, const int32_t* seg_ci, int64_t n, const int32_t* qoffset, int32_t* qcursor,
+                                  Survivor* out, int32_t* out_ci, cudaStream_t st);
+cudaError_t launch_replay_only(const ReplayParams& p, cudaStream_t st);
 cudaError_t replay_setup(int K);
 
 }  // namespace uvg

@@ -10,6 +10,7 @@
 // (at most one survivor per (query, reference)), and one thread performs the sequential admission.
 #include "common.cuh"
 #include "kernels.h"
+#include <algorithm>
 
 namespace uvg {
 
@@ -212,16 +213,36 @@ cudaError_t replay_setup(int K)
     return cudaFuncSetAttribute(k_replay, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
 
-cudaError_t launch_replay(const ReplayParams& p, cudaStream_t st)
+__global__ void __launch_bounds__(256) k_bucket_count(const Survivor* __restrict__ surv, int64_t n, int32_t* __restrict__ qcount)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        atomicAdd(qcount + surv[i].q, 1);
+}
+
+cudaError_t launch_bucket_count(const Survivor* seg, int64_t n, int32_t* qcount, cudaStream_t st)
+{
+    if (n <= 0) return cudaSuccess;
+    int64_t blocks = std::min<int64_t>((n + 255) / 256, 148 * 32);
+    k_bucket_count<<<(unsigned)blocks, 256, 0, st>>>(seg, n, qcount);
+    return cudaGetLastError();
+}
+cudaError_t launch_bucket_scan(const int32_t* qcount, int32_t* qoffset, int32_t* qcursor, int n_query, cudaStream_t st)
+{
+    k_bucket_scan<<<1, 1024, 0, st>>>(qcount, qoffset, qcursor, n_query);
+    return cudaGetLastError();
+}
+cudaError_t launch_bucket_scatter(const Survivor* seg, const int32_t* seg_ci, int64_t n, const int32_t* qoffset, int32_t* qcursor,
+                                  Survivor* out, int32_t* out_ci, cudaStream_t st)
+{
+    if (n <= 0) return cudaSuccess;
+    int64_t blocks = std::min<int64_t>((n + 255) / 256, 148 * 32);
+    k_bucket_scatter<<<(unsigned)blocks, 256, 0, st>>>(seg, seg_ci, n, qoffset, qcursor, out, out_ci);
+    return cudaGetLastError();
+}
+cudaError_t launch_replay_only(const ReplayParams& p, cudaStream_t st)
 {
     if (p.n_query <= 0) return cudaSuccess;
     if ((p.round_count + RP_WIN - 1) / RP_WIN > RP_MAXWIN_WORDS * 32) return cudaErrorInvalidValue;
-    k_bucket_scan<<<1, 1024, 0, st>>>(p.qcount, p.qoffset, p.qcursor, p.n_query);
-    if (p.n_surv > 0) {
-        int64_t blocks = (p.n_surv + 255) / 256;
-        if (blocks > 148 * 32) blocks = 148 * 32;
-        k_bucket_scatter<<<(unsigned)blocks, 256, 0, st>>>(p.surv, p.surv_ci, p.n_surv, p.qoffset, p.qcursor, p.bucketed, p.bucketed_ci);
-    }
     int in_smem;
     size_t bytes = replay_smem_bytes(p.K, &in_smem);
     k_replay<<<p.n_query, RP_THREADS, bytes, st>>>(p, in_smem);
