@@ -1,0 +1,197 @@
+"""Thin object wrapper over the C ABI (uvaia_b200/_capi.py): numpy arrays in, numpy arrays out.
+
+Mirrors the seam of the reference that the CUDA layer replaces (src/nearest.c): `set_queries` ~ create_query_indices,
+`push_refs` ~ the batch fill with quick_count_sequence_non_N + ref filter (nearest.c:250-286), `search` ~ the two
+OpenMP loops (nearest.c:293-299), `heap` ~ heap_finalise_heap_qsort + save_distance_table reads.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+
+
+class UvgError(RuntimeError):
+    pass
+
+
+class Engine:
+    def __init__(self, nchar, nbest=100, trim=0, acgt=False, pool=512, device=0, first_round=0, max_round=0,
+                 early_abort=False, rank=0, world=1, max_survivors=0, db_capacity=0):
+        self._lib = _capi.lib()
+        p = _capi.uvg_params(_capi.UVG_ABI_VERSION, int(nchar), int(trim), int(nbest), int(bool(acgt)), int(pool),
+                             int(device), int(first_round), int(max_round), int(bool(early_abort)), int(rank), int(world),
+                             int(max_survivors), int(db_capacity))
+        h = C.c_void_p()
+        rc = self._lib.uvg_create(C.byref(p), C.byref(h))
+        if rc != 0:
+            raise UvgError(f"uvg_create failed ({rc}): {self._lib.uvg_last_error(None).decode()}")
+        self._h = h
+        self.nchar = int(nchar)
+        self.K = max(2, int(nbest))
+        self.acgt = bool(acgt)
+        self.n_query = 0
+        self.info = None
+        self.rank, self.world = int(rank), int(world)
+        self.first_round, self.max_round = int(first_round), int(max_round)
+
+    # ---- plumbing ----
+    def _ck(self, rc, what):
+        if rc != 0:
+            raise UvgError(f"{what} failed ({rc}): {self._lib.uvg_last_error(self._h).decode()}")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.uvg_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ---- queries ----
+    def set_queries(self, text: np.ndarray):
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        assert text.ndim == 2 and text.shape[1] == self.nchar
+        info = _capi.uvg_query_info()
+        self._ck(self._lib.uvg_set_queries(self._h, text.ctypes.data, text.shape[0], C.byref(info)), "uvg_set_queries")
+        self.n_query = text.shape[0]
+        self.info = info
+        return info
+
+    # ---- references ----
+    def push_refs(self, text: np.ndarray, min_non_n=0):
+        """-> (non_n int32[n], accepted uint8[n], n_accepted)"""
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        if text.size == 0:
+            return np.zeros(0, np.int32), np.zeros(0, np.uint8), 0
+        assert text.ndim == 2 and text.shape[1] == self.nchar
+        n = text.shape[0]
+        nn = np.empty(n, np.int32)
+        acc = np.empty(n, np.uint8)
+        na = C.c_int64(0)
+        self._ck(self._lib.uvg_push_refs(self._h, text.ctypes.data, n, int(min_non_n), nn.ctypes.data, acc.ctypes.data,
+                                         C.byref(na)), "uvg_push_refs")
+        return nn, acc, na.value
+
+    def push_refs_ptr(self, host_ptr, n, min_non_n=0):
+        """host buffer given as a raw address (e.g. pinned memory); returns n_accepted"""
+        na = C.c_int64(0)
+        self._ck(self._lib.uvg_push_refs(self._h, host_ptr, int(n), int(min_non_n), None, None, C.byref(na)), "uvg_push_refs")
+        return na.value
+
+    def push_refs_device(self, d_ptr, n, min_non_n=0, want_outputs=False):
+        na = C.c_int64(0)
+        if want_outputs:
+            nn = np.empty(n, np.int32)
+            acc = np.empty(n, np.uint8)
+            self._ck(self._lib.uvg_push_refs_device(self._h, d_ptr, int(n), int(min_non_n), nn.ctypes.data, acc.ctypes.data,
+                                                    C.byref(na)), "uvg_push_refs_device")
+            return nn, acc, na.value
+        self._ck(self._lib.uvg_push_refs_device(self._h, d_ptr, int(n), int(min_non_n), None, None, C.byref(na)),
+                 "uvg_push_refs_device")
+        return na.value
+
+    def drop_refs(self):
+        self._ck(self._lib.uvg_drop_refs(self._h), "uvg_drop_refs")
+
+    @property
+    def db_count(self):
+        return int(self._lib.uvg_db_count(self._h))
+
+    # ---- search ----
+    def search(self):
+        self._ck(self._lib.uvg_search(self._h), "uvg_search")
+
+    def reset_search(self):
+        self._ck(self._lib.uvg_reset_search(self._h), "uvg_reset_search")
+
+    def heap(self, iq):
+        """-> (scores int32[n,6], refs int64[n]) in the reference's output order"""
+        buf = (_capi.uvg_item * self.K)()
+        n = C.c_int32(0)
+        self._ck(self._lib.uvg_get_heap(self._h, int(iq), buf, C.byref(n)), "uvg_get_heap")
+        arr = np.frombuffer(buf, dtype=np.dtype([("score", np.int32, 6), ("ref", np.int64)]), count=n.value)
+        return arr["score"].copy(), arr["ref"].copy()
+
+    def heaps(self):
+        return [self.heap(q) for q in range(self.n_query)]
+
+    def ever_best(self, first, n):
+        flags = np.zeros(int(n), np.uint8)
+        if n:
+            self._ck(self._lib.uvg_get_ever_best(self._h, int(first), int(n), flags.ctypes.data), "uvg_get_ever_best")
+        return flags
+
+    def stats(self):
+        s = _capi.uvg_stats()
+        self._ck(self._lib.uvg_get_stats(self._h, C.byref(s)), "uvg_get_stats")
+        return {k: getattr(s, k) for k, _ in _capi.uvg_stats._fields_}
+
+    # ---- sharding ----
+    @staticmethod
+    def shard_of(ordinal, world, first_round=0, max_round=0):
+        r = C.c_int32(0)
+        l = C.c_int64(0)
+        rc = _capi.lib().uvg_shard_of(int(ordinal), int(world), int(first_round), int(max_round), C.byref(r), C.byref(l))
+        if rc != 0:
+            raise UvgError("uvg_shard_of: bad arguments")
+        return r.value, l.value
+
+    @staticmethod
+    def nccl_unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        rc = _capi.lib().uvg_nccl_unique_id(buf)
+        if rc != 0:
+            raise UvgError(f"uvg_nccl_unique_id failed: {_capi.lib().uvg_last_error(None).decode()}")
+        return buf.raw
+
+    def nccl_init(self, uid: bytes):
+        buf = C.create_string_buffer(uid, 128)
+        self._ck(self._lib.uvg_nccl_init(self._h, buf), "uvg_nccl_init")
+
+    def set_global_count(self, n):
+        self._ck(self._lib.uvg_set_global_count(self._h, int(n)), "uvg_set_global_count")
+
+    # ---- utilities ----
+    def device_alloc(self, nbytes):
+        p = self._lib.uvg_device_alloc(self._h, int(nbytes))
+        if not p:
+            raise UvgError(f"uvg_device_alloc({nbytes}) failed: {self._lib.uvg_last_error(self._h).decode()}")
+        return p
+
+    def device_free(self, p):
+        self._lib.uvg_device_free(self._h, p)
+
+    def synth_rows_device(self, clades: np.ndarray, seed, first, n, d_ptr, n_frac_mean=0.197, ambiguous_frac=0.0):
+        clades = np.ascontiguousarray(clades, dtype=np.uint8)
+        self._ck(self._lib.uvg_synth_rows_device(self._h, clades.ctypes.data, clades.shape[0], int(seed), int(first), int(n),
+                                                 float(n_frac_mean), float(ambiguous_frac), d_ptr), "uvg_synth_rows_device")
+
+    def d2h(self, d_ptr, nbytes):
+        out = np.empty(int(nbytes), np.uint8)
+        self._ck(self._lib.uvg_memcpy_d2h(self._h, out.ctypes.data, d_ptr, int(nbytes)), "uvg_memcpy_d2h")
+        return out
+
+    def d2h_into(self, host_ptr, d_ptr, nbytes):
+        self._ck(self._lib.uvg_memcpy_d2h(self._h, host_ptr, d_ptr, int(nbytes)), "uvg_memcpy_d2h")
+
+    def debug_pair_counts(self, first, n):
+        out = np.empty((self.n_query, int(n), 4), np.int32)
+        self._ck(self._lib.uvg_debug_pair_counts(self._h, int(first), int(n), out.ctypes.data), "uvg_debug_pair_counts")
+        return out
+
+    def debug_unpack_ref(self, local):
+        out = np.empty(self.nchar, np.uint8)
+        self._ck(self._lib.uvg_debug_unpack_ref(self._h, int(local), out.ctypes.data), "uvg_debug_unpack_ref")
+        return out
