@@ -1,0 +1,418 @@
+#!/usr/bin/env python
+"""Benchmark of the uvaia n-best database search hot path on B200 (BASELINE.json metric).
+
+A "step" = one complete search of all queries against the whole device-resident packed database (K2 pair counts +
+K3 replay over every round), i.e. BASELINE.json configs[1]: 1k synthetic SARS-CoV-2 queries vs a 1M-sequence
+synthetic 29,903-site reference alignment, nbest=100.  `value` = queries/s with the packed DB and the query planes
+already in HBM; `e2e` = the same search driven through the C ABI from HOST buffers (query text + reference text in
+pinned memory -> H2D -> encode -> search -> heaps D2H inside the timed region).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--refs R] [--queries Q]
+For N>1 launch with torchrun (one rank per GPU); the database is row-sharded, rounds are merged with NCCL all-gathers.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NCHAR = 29903
+LOP3_PER_PAIRWORD = 5          # algorithmic LOP3 per (pair, 32-site word): DESIGN.md section 4
+POPC_PER_PAIRWORD = 2
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--refs", type=int, default=1_000_000)
+    ap.add_argument("--queries", type=int, default=1000)
+    ap.add_argument("--nbest", type=int, default=100)
+    ap.add_argument("--nchar", type=int, default=NCHAR)
+    ap.add_argument("--ambiguous", type=float, default=0.0, help="config-4 stress: fraction of ambiguous query sites")
+    ap.add_argument("--early-abort", type=int, default=0)
+    ap.add_argument("--max-round", type=int, default=0)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--cpu-refs", type=int, default=3000, help="references in the bounded CPU-baseline sample")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# clocks sampler (B200_PROFILING.md "clocks DURING the timed region")
+# ---------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        # median over the samples taken under load (power above the idle floor)
+        load = [s for s, p in zip(sm, pw) if p > 0.5 * max(pw)] or sm
+        return {"sm_mhz": float(np.median(load)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm), "power_w_max": max(pw)}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# workload
+# ---------------------------------------------------------------------------------------------------------------
+def make_model(nchar):
+    from uvaia_b200.synth import SynthModel
+    m = SynthModel(nsites=nchar, n_clades=200, seed=1)
+    return np.stack(m.clades)
+
+
+def make_queries(eng, clades, nq, nchar, ambiguous):
+    """synthetic query rows from the device generator (seed 2002), filtered and ordered like the uvaia host does"""
+    from uvaia_b200 import host
+    d = eng.device_alloc(nq * nchar)
+    eng.synth_rows_device(clades, 2002, 0, nq, d, ambiguous_frac=ambiguous)
+    text = eng.d2h(d, nq * nchar).reshape(nq, nchar)
+    eng.device_free(d)
+    keep = host.filter_queries([r.tobytes() for r in text], 0.5)
+    text = text[keep]
+    order = host.query_order(text, 0, False)
+    return np.ascontiguousarray(text[order]), [b"Q%06d" % keep[i] for i in order]
+
+
+def rank_tiles(total, rank, world, first_round, max_round):
+    """[(global_first, count)] of the reference ordinals this rank holds, round by round (uvg_shard_of schedule)"""
+    out, S, T = [], 0, first_round
+    while S < total:
+        gb = S + rank * T
+        ge = min(gb + T, total)
+        if ge > gb:
+            out.append((gb, ge - gb))
+        S += world * T
+        T = min(4 * T, max_round)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own multithreaded search (oracle/_ref/uvaia_ref) on a bounded sample of the workload
+# ---------------------------------------------------------------------------------------------------------------
+def write_fasta(path, names, text):
+    with open(path, "wb") as fh:
+        for nm, row in zip(names, text):
+            fh.write(b">" + nm + b"\n" + row.tobytes() + b"\n")
+
+
+def run_reference_sample(qtext, qnames, rtext, nbest, threads, workdir):
+    """-> (seconds, csv_text or None, kind).  kind 'reference' = compiled reference binary, 'port' = numpy oracle."""
+    ref_bin = os.path.join(ROOT, "oracle", "_ref", "uvaia_ref")
+    rnames = [b"R%07d" % i for i in range(len(rtext))]
+    if os.path.exists(ref_bin):
+        import gzip
+        qf, rf, pre = os.path.join(workdir, "q.fa"), os.path.join(workdir, "r.fa"), os.path.join(workdir, "out")
+        write_fasta(qf, qnames, qtext)
+        write_fasta(rf, rnames, rtext)
+        cmd = [ref_bin, "-n", str(nbest), "-t", str(threads), "-A", "1.0", "-r", rf, "-o", pre, qf]
+        t0 = time.perf_counter()
+        p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, cwd=workdir)
+        dt = time.perf_counter() - t0
+        if p.returncode != 0:
+            raise RuntimeError("uvaia_ref failed: " + p.stderr.decode(errors="replace")[-400:])
+        raw = open(pre + ".csv.xz", "rb").read()
+        try:
+            csv = gzip.decompress(raw).decode()           # zlib-only build writes gzip data under the .xz name (H4)
+        except OSError:
+            import lzma
+            csv = lzma.decompress(raw).decode()
+        return dt, csv, "reference"
+    from oracle import uvaia_oracle as orc
+    t0 = time.perf_counter()
+    res = orc.search(list(qnames), [r.tobytes() for r in qtext], None, nbest=nbest, ambig_r=1.0,
+                     refs=[(rnames, [r.tobytes() for r in rtext])])
+    return time.perf_counter() - t0, res.csv(), "port"
+
+
+def gpu_csv_for_sample(qtext, qnames, rtext, nbest):
+    from uvaia_b200 import host
+    from uvaia_b200.engine import Engine
+    with Engine(qtext.shape[1], nbest=nbest) as e:
+        e.set_queries(qtext)
+        e.push_refs(rtext, 0)
+        e.search()
+        out = host.SearchOutput()
+        out.qnames = list(qnames)
+        out.rows = e.heaps()
+        out.ref_names = [b"R%07d" % i for i in range(len(rtext))]
+        return out.csv()
+
+
+def cpu_baseline(eng, clades, qtext, qnames, args, steps=1):
+    L = args.nchar
+    n = min(args.cpu_refs, args.refs)
+    d = eng.device_alloc(n * L)
+    eng.synth_rows_device(clades, 1001, 0, n, d)
+    rtext = eng.d2h(d, n * L).reshape(n, L)
+    eng.device_free(d)
+    threads = os.cpu_count() or 1
+    times, csv, kind = [], None, None
+    with tempfile.TemporaryDirectory() as wd:
+        for _ in range(steps):
+            dt, csv, kind = run_reference_sample(qtext, qnames, rtext, args.nbest, threads, wd)
+            times.append(dt)
+    mine = gpu_csv_for_sample(qtext, qnames, rtext, args.nbest)
+    dt = float(np.mean(times))
+    qps = len(qtext) / (dt * args.refs / n)              # scaled linearly to the full database
+    return {"value": qps, "unit": "queries/s", "cores": threads if kind == "reference" else 1, "kind": kind,
+            "sample": f"{len(qtext)} queries x first {n} of {args.refs} references, {dt:.2f} s per run, scaled x{args.refs / n:.1f}",
+            "seconds": dt, "gsite_cmp_per_s": len(qtext) * n * L / dt / 1e9,
+            "parity_with_gpu_on_sample": bool(mine == csv)}, times
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# main
+# ---------------------------------------------------------------------------------------------------------------
+def load_peaks():
+    peaks = {"hbm_gbs": 6650.0, "hbm_src": "fallback"}
+    try:
+        m = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        peaks["hbm_gbs"], peaks["hbm_src"] = float(m["hbm_gbs"]), "measured"
+    except Exception:
+        pass
+    try:
+        u = json.load(open(os.path.join(ROOT, "profiles", "int_pipes_b200_r01.json")))
+        peaks["lop3_gips"] = float(u["lop3"]["gthread_inst_per_s"])
+        peaks["popc_gips"] = float(u["popc"]["gthread_inst_per_s"])
+    except Exception:
+        peaks["lop3_gips"], peaks["popc_gips"] = 18400.0, 4630.0
+    return peaks
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference" and rank != 0:
+        return 0                                            # rank 0 alone runs the CPU arm
+    import torch
+    dist = None
+    if world > 1 and args.impl == "ours":
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group(backend="nccl", device_id=torch.device("cuda", local_rank))
+    from uvaia_b200.engine import Engine
+
+    L, R = args.nchar, args.refs
+    first_round, max_round = 1024, (args.max_round or 65536)
+    clades = make_model(L)
+    dev = local_rank if torch.cuda.is_available() else 0
+    tiles = rank_tiles(R, rank, world, first_round, max_round)
+    n_local = sum(c for _, c in tiles)
+    eng = Engine(L, nbest=args.nbest, device=dev, first_round=first_round, max_round=max_round, early_abort=bool(args.early_abort),
+                 rank=rank, world=world, db_capacity=n_local if args.impl == "ours" else 4096)
+    qtext, qnames = make_queries(eng, clades, args.queries, L, args.ambiguous)
+    Q = len(qtext)
+    workload = f"{Q} synthetic SARS-CoV-2 queries (of {args.queries} generated; -a 0.5 filter) x {R} references x {L} sites, nbest={args.nbest}"
+    base = {"metric": "queries_per_s_vs_%dk_db" % (R // 1000), "unit": "queries/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32 bit-planes / int32 counts",
+            "data": "synthetic (device generator, seeds 1/1001/2002)",
+            "config": {"workload": workload, "nbest": args.nbest, "early_abort": bool(args.early_abort), "sharding": "rows x%d" % world,
+                       "l2": "inputs larger than L2 (packed DB %.1f GB per pass)" % (R * ((L + 511) // 512 * 512) / 2 / 1e9)}}
+
+    if args.impl == "reference":
+        times = []
+        cb = None
+        for i in range(args.warmup + args.steps):
+            cb, t = cpu_baseline(eng, clades, qtext, qnames, args, steps=1)
+            if i >= args.warmup:
+                times += t
+        dt = float(np.mean(times))
+        n = min(args.cpu_refs, R)
+        v = Q / (dt * R / n)
+        cb["value"] = v
+        line = dict(base, impl="reference", value=v, ms_per_step=dt * 1e3, n_gpus=args.gpus, cpu_baseline=cb,
+                    gsite_cmp_per_s=Q * n * L / dt / 1e9,
+                    e2e={"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, gpu_launches=0)
+        print(json.dumps(line))
+        return 0
+
+    # ---- build the device-resident database (K1), optionally keeping the text on the host for the e2e leg ----
+    want_e2e = not args.no_e2e
+    host_buf = None
+    if want_e2e:
+        import psutil
+        need = n_local * L
+        if psutil.virtual_memory().available < need * 1.5 + (8 << 30):
+            want_e2e = False
+        else:
+            host_buf = eng._lib.uvg_host_alloc_pinned(need)
+            want_e2e = bool(host_buf)
+    eng.set_queries(qtext)
+    tile_rows = 16384
+    d_tile = eng.device_alloc(tile_rows * L)
+    t_build = time.perf_counter()
+    off = 0
+    for gb, cnt in tiles:
+        for s in range(0, cnt, tile_rows):
+            m = min(tile_rows, cnt - s)
+            eng.synth_rows_device(clades, 1001, gb + s, m, d_tile)
+            eng.push_refs_device(d_tile, m, 0)
+            if want_e2e:
+                eng.d2h_into(host_buf + off * L, d_tile, m * L)
+            off += m
+    eng.device_free(d_tile)
+    t_build = time.perf_counter() - t_build
+    assert eng.db_count == n_local
+    if world > 1:
+        uid = [Engine.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        eng.nccl_init(uid[0])
+        eng.set_global_count(R)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- timed: device-resident search ----
+    for _ in range(args.warmup):
+        eng.reset_search(); eng.search()
+    sampler = ClockSampler(dev)
+    barrier()
+    sampler.start()
+    ev_ms, pair_ms, replay_ms, launches = 0.0, 0.0, 0.0, 0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        eng.reset_search(); eng.search()
+        st = eng.stats()
+        ev_ms += st["search_ms"]; pair_ms += st["pair_kernel_ms"]; replay_ms += st["replay_ms"]
+        launches += st["pair_kernel_launches"] + st["other_kernel_launches"]
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop()
+    tt = torch.tensor([ev_ms, wall * 1e3, pair_ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ev_ms, wall_ms, pair_ms_max = [float(x) for x in tt.tolist()]
+    ms_step = ev_ms / args.steps
+    qps = Q / (ms_step * 1e-3)
+    st = eng.stats()
+    checksum = int(sum(int(sc.astype(np.int64).sum()) + int(r.sum()) for sc, r in eng.heaps()) & 0xffffffffffff)
+
+    # ---- e2e: same search through the C ABI from host buffers ----
+    e2e = None
+    if want_e2e:
+        e2e_t = []
+        for i in range(1 + args.e2e_steps):
+            barrier()
+            t1 = time.perf_counter()
+            eng.clear_refs()
+            eng.set_queries(qtext)
+            o = 0
+            for gb, cnt in tiles:
+                eng.push_refs_ptr(host_buf + o * L, cnt, 0)
+                o += cnt
+            if world > 1:
+                eng.set_global_count(R)
+            eng.search()
+            heaps = eng.heaps()
+            barrier()
+            if i > 0:
+                e2e_t.append(time.perf_counter() - t1)
+        t = torch.tensor([float(np.mean(e2e_t))], dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+        chk2 = int(sum(int(sc.astype(np.int64).sum()) + int(r.sum()) for sc, r in heaps) & 0xffffffffffff)
+        e2e = {"value": Q / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(Q * L * world + R * L),
+               "d2h_bytes_per_step": int(world * Q * ((args.nbest + 1) * 32 + 8)), "seconds_per_step": e2e_s,
+               "same_result_as_resident_run": chk2 == checksum}
+        eng._lib.uvg_host_free_pinned(host_buf)
+
+    # ---- roofline of the dominant kernel (k_paircount) ----
+    peaks = load_peaks()
+    W = (L + 31) // 32
+    pairwords_rank = Q * n_local * W                          # per step on this rank
+    k_ms = (pair_ms_max / args.steps)
+    lop3 = LOP3_PER_PAIRWORD * pairwords_rank / (k_ms * 1e-3) / 1e9
+    popc = POPC_PER_PAIRWORD * pairwords_rank / (k_ms * 1e-3) / 1e9
+    f_l, f_p = lop3 / peaks["lop3_gips"], popc / peaks["popc_gips"]
+    bound = "int-popc" if f_p >= f_l else "int-lop3"
+    n_qtiles = (Q + 63) // 64
+    db_bytes = n_local * ((W + 15) // 16 * 16) * 16
+    roofline = {"kernel": "k_paircount", "bound": bound, "achieved": popc if bound == "int-popc" else lop3,
+                "peak": peaks["popc_gips"] if bound == "int-popc" else peaks["lop3_gips"], "unit": "Gthread-inst/s",
+                "frac": max(f_l, f_p), "traffic": None,
+                "note": "INT pipes bind (north_star): algorithmic %d LOP3 + %d POPC per pair x 32-site word; peaks = profiles/int_pipes_b200_r01.json (measured)"
+                        % (LOP3_PER_PAIRWORD, POPC_PER_PAIRWORD),
+                "lop3": {"achieved": lop3, "peak": peaks["lop3_gips"], "frac": f_l}, "popc": {"achieved": popc, "peak": peaks["popc_gips"], "frac": f_p},
+                "hbm": {"bound": "hbm", "achieved": db_bytes / (k_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                        "frac": db_bytes / (k_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "peak_src": peaks["hbm_src"],
+                        "note": "algorithmic = one pass over the packed DB per step; L2-level re-reads x%d query tiles" % n_qtiles},
+                "kernel_ms_per_step": k_ms, "kernel_share_of_step": k_ms / ms_step}
+
+    cb = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cb, _ = cpu_baseline(eng, clades, qtext, qnames, args)
+
+    if rank == 0:
+        line = dict(base, value=qps, ms_per_step=ms_step, wall_ms_per_step=wall_ms / args.steps, gsite_cmp_per_s=Q * R * L / (ms_step * 1e-3) / 1e9,
+                    clocks=clocks, e2e=e2e, gpu_launches=int(launches), roofline=roofline, cpu_baseline=cb,
+                    replay_ms_per_step=replay_ms / args.steps, db_build_s=t_build,
+                    search_stats={k: st[k] for k in ("n_rounds", "n_survivors", "n_admitted", "n_h1_flags", "n_overflow_splits", "max_mismatch")},
+                    result_checksum=checksum)
+        print(json.dumps(line))
+    eng.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -100,6 +100,8 @@ int uvg_push_refs_device(uvg_ctx* ctx, const uint8_t* d_text, int64_t n, int32_t
                          int32_t* non_n_out, uint8_t* accepted_out, int64_t* n_accepted);
 /* Forget the packed references scored so far but keep heaps and ordinals (streaming hosts: push, search, drop). */
 int uvg_drop_refs(uvg_ctx* ctx);
+/* Forget every reference and restart ordinals at 0 (heaps are emptied too). */
+int uvg_clear_refs(uvg_ctx* ctx);
 int64_t uvg_db_count(const uvg_ctx* ctx);              /* accepted references resident on this rank */
 
 /* ---- search: replaces the two OpenMP loops nearest.c:293-299 (consensus stage, per-query heap updates) ----

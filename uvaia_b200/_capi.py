@@ -48,6 +48,7 @@ SYMBOLS = {
     "uvg_push_refs": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P, _P, C.POINTER(C.c_int64)]),
     "uvg_push_refs_device": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P, _P, C.POINTER(C.c_int64)]),
     "uvg_drop_refs": (C.c_int, [_P]),
+    "uvg_clear_refs": (C.c_int, [_P]),
     "uvg_db_count": (C.c_int64, [_P]),
     "uvg_search": (C.c_int, [_P]),
     "uvg_reset_search": (C.c_int, [_P]),

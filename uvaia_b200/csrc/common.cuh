@@ -43,10 +43,14 @@ struct __align__(16) HeapItem {
 };
 
 // Per-query threshold snapshot read by the pair-count kernel: the heap root (worst kept item) once the heap is full.
+// dmax bounds the reference's max_incompatible for the rest of the search: once a heap is full,
+//   max_incompatible(t') <= 1 + max over items kept at time t <= t' of (valid - acgt)
+// (every later root is either one of those items or was admitted under a limit that already obeyed the bound), so a
+// pair with valid - acgt >= dmax can never be admitted (src/nearest.c:488-496 / 450-460).
 struct __align__(16) Threshold {
     int32_t s[6];
     int32_t full;
-    int32_t pad;
+    int32_t dmax;
 };
 
 struct PairParams {

@@ -317,7 +317,7 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     UVG_CUDA(c, cudaMalloc(&c->d_batch_id, Q * 4)); UVG_CUDA(c, cudaMalloc(&c->d_max_inc_batch, Q * 4));
     UVG_CUDA(c, cudaMalloc(&c->d_qcount, Q * 4)); UVG_CUDA(c, cudaMalloc(&c->d_qoffset, (Q + 1) * 4)); UVG_CUDA(c, cudaMalloc(&c->d_qcursor, Q * 4));
     // survivor capacity: the first round keeps every pair (Q x first_round); later rounds keep ~K*ln(growth) per query
-    int64_t cap = c->prm.max_survivors > 0 ? c->prm.max_survivors : std::max<int64_t>((int64_t)Q * round_size_first(c->prm) * 2, 1 << 22);
+    int64_t cap = c->prm.max_survivors > 0 ? c->prm.max_survivors : std::max<int64_t>((int64_t)Q * round_size_first(c->prm) * 2, 1 << 24);
     cap = std::max<int64_t>(cap, (int64_t)Qp * GROUP);
     c->surv_cap = cap;
     UVG_CUDA(c, cudaMalloc(&c->d_surv, cap * sizeof(Survivor))); UVG_CUDA(c, cudaMalloc(&c->d_surv_ci, cap * 4));
@@ -490,6 +490,15 @@ extern "C" int uvg_drop_refs(uvg_ctx* c)
     c->global_base += c->db_n;
     c->db_n = 0; c->db_scored = 0; c->round_local_start = 0;
     return UVG_OK;
+}
+
+extern "C" int uvg_clear_refs(uvg_ctx* c)
+{
+    if (!c) return UVG_EINVAL;
+    UVG_CUDA(c, cudaSetDevice(c->prm.device));
+    if (c->d_refamb) UVG_CUDA(c, cudaMemsetAsync(c->d_refamb, 0, (size_t)(c->db_cap / GROUP) * c->ambw * 4, c->st));
+    c->global_base = 0; c->db_n = 0; c->db_scored = 0; c->round_local_start = 0; c->global_total = -1;
+    return c->n_query ? reset_heaps(c) : UVG_OK;
 }
 
 extern "C" int64_t uvg_db_count(const uvg_ctx* c) { return c ? c->db_n : 0; }

@@ -148,7 +148,9 @@ __global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams 
 #pragma unroll
                     for (int j = 0; j < QPW; ++j) {
                         const Threshold& t = s_thr[q0 + j];
-                        if (!t.full || accP[j] + (int32_t)ch.rem[q0 + j] >= t.s[0]) dead = false;
+                        // mismatches so far (monotone along the genome) and the best ACGT count still reachable
+                        const int32_t dsofar = (MODE == 0) ? (accV[j] - accP[j] + accY[j]) : (accV[j] - accP[j]);
+                        if (!t.full || (dsofar < t.dmax && accP[j] + (int32_t)ch.rem[q0 + j] >= t.s[0])) dead = false;
                     }
                 }
                 warp_dead = __all_sync(0xffffffffu, dead);
@@ -185,7 +187,8 @@ __global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams 
         bool pass = false;
         if (in_range && q < p.n_query && !warp_dead) {
             const Threshold& t = s_thr[q0 + j];
-            pass = !t.full || lex_greater(sc, t);
+            const int32_t D = (MODE == 0) ? (sc[3] - sc[0]) : (sc[1] - sc[0]);
+            pass = !t.full || (D < t.dmax && lex_greater(sc, t));
             if (p.dbg_counts) {
                 int32_t* o = p.dbg_counts + ((size_t)q * n_launch + (local - p.local_begin)) * 4;
                 if (MODE == 0) { o[0] = sc[0]; o[1] = sc[1]; o[2] = sc[2]; o[3] = sc[3]; }

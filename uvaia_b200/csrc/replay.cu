@@ -186,16 +186,29 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
         p.qcount[q] = 0;
         if (admitted) atomicAdd(p.counters + 0, (unsigned long long)admitted);
         if (h1) atomicAdd(p.counters + 1, (unsigned long long)h1);
-        if (n == K) {
-            Threshold t;
-#pragma unroll
-            for (int k = 0; k < 6; ++k) t.s[k] = a[1].s[k];
-            t.full = 1; t.pad = 0;
-            p.thr[q] = t;
-        }
     }
     __syncthreads();
     n = s_misc[40];
+    if (n == K) {
+        // threshold snapshot for the next rounds: heap root + the bound on every future max_incompatible
+        int dm = 0;
+        for (int i = 1 + threadIdx.x; i <= n; i += blockDim.x) {
+            const int d = p.acgt_mode ? (a[i].s[1] - a[i].s[0]) : (a[i].s[3] - a[i].s[0]);
+            dm = max(dm, d);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) dm = max(dm, __shfl_xor_sync(0xffffffffu, dm, o));
+        if ((threadIdx.x & 31) == 0) s_misc[48 + (threadIdx.x >> 5)] = dm;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int k = 0; k < RP_THREADS / 32; ++k) dm = max(dm, s_misc[48 + k]);
+            Threshold t;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) t.s[k] = a[1].s[k];
+            t.full = 1; t.dmax = dm + 1;
+            p.thr[q] = t;
+        }
+    }
     if (heap_in_smem) for (int i = 1 + threadIdx.x; i <= n; i += blockDim.x) gheap[i] = a[i];
 }
 

@@ -105,6 +105,9 @@ class Engine:
     def drop_refs(self):
         self._ck(self._lib.uvg_drop_refs(self._h), "uvg_drop_refs")
 
+    def clear_refs(self):
+        self._ck(self._lib.uvg_clear_refs(self._h), "uvg_clear_refs")
+
     @property
     def db_count(self):
         return int(self._lib.uvg_db_count(self._h))
