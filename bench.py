@@ -325,13 +325,14 @@ def main():
     sampler = ClockSampler(dev)
     barrier()
     sampler.start()
-    ev_ms, pair_ms, replay_ms, launches = 0.0, 0.0, 0.0, 0
+    ev_ms, pair_ms, replay_ms, launches, chunks = 0.0, 0.0, 0.0, 0, 0
     t0 = time.perf_counter()
     for _ in range(args.steps):
         eng.reset_search(); eng.search()
         st = eng.stats()
         ev_ms += st["search_ms"]; pair_ms += st["pair_kernel_ms"]; replay_ms += st["replay_ms"]
         launches += st["pair_kernel_launches"] + st["other_kernel_launches"]
+        chunks += st["warp_chunks_executed"]
     barrier()
     wall = time.perf_counter() - t0
     clocks = sampler.stop()
@@ -377,7 +378,8 @@ def main():
     # ---- roofline of the dominant kernel (k_paircount) ----
     peaks = load_peaks()
     W = (L + 31) // 32
-    pairwords_rank = Q * n_local * W                          # per step on this rank
+    pairwords_dense = Q * n_local * W                         # per step on this rank, no early abort
+    pairwords_rank = chunks / args.steps * 4096.0             # executed: (warp, chunk) iterations x 8 words x 16 pairs x 32 lanes
     k_ms = (pair_ms_max / args.steps)
     lop3 = LOP3_PER_PAIRWORD * pairwords_rank / (k_ms * 1e-3) / 1e9
     popc = POPC_PER_PAIRWORD * pairwords_rank / (k_ms * 1e-3) / 1e9
@@ -388,13 +390,15 @@ def main():
     roofline = {"kernel": "k_paircount", "bound": bound, "achieved": popc if bound == "int-popc" else lop3,
                 "peak": peaks["popc_gips"] if bound == "int-popc" else peaks["lop3_gips"], "unit": "Gthread-inst/s",
                 "frac": max(f_l, f_p), "traffic": None,
-                "note": "INT pipes bind (north_star): algorithmic %d LOP3 + %d POPC per pair x 32-site word; peaks = profiles/int_pipes_b200_r01.json (measured)"
+                "note": "INT pipes bind (north_star): %d LOP3 + %d POPC per EXECUTED pair x 32-site word (padding and early abort accounted for); peaks = profiles/int_pipes_b200_r01.json (measured)"
                         % (LOP3_PER_PAIRWORD, POPC_PER_PAIRWORD),
                 "lop3": {"achieved": lop3, "peak": peaks["lop3_gips"], "frac": f_l}, "popc": {"achieved": popc, "peak": peaks["popc_gips"], "frac": f_p},
                 "hbm": {"bound": "hbm", "achieved": db_bytes / (k_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                         "frac": db_bytes / (k_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "peak_src": peaks["hbm_src"],
                         "note": "algorithmic = one pass over the packed DB per step; L2-level re-reads x%d query tiles" % n_qtiles},
-                "kernel_ms_per_step": k_ms, "kernel_share_of_step": k_ms / ms_step}
+                "kernel_ms_per_step": k_ms, "kernel_share_of_step": k_ms / ms_step,
+                "executed_pairwords_per_step": pairwords_rank, "dense_pairwords_per_step": pairwords_dense,
+                "executed_fraction_of_dense": pairwords_rank / max(1, pairwords_dense)}
 
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu:

@@ -72,6 +72,8 @@ typedef struct uvg_stats {
     double  replay_ms;          /* ... of bucket+replay */
     double  search_ms;          /* ... whole uvg_search */
     double  encode_ms;          /* ... of the encoder launches of the last uvg_push_refs* */
+    int64_t warp_chunks_executed; /* (warp, chunk) iterations the pair-count kernel ran in the last uvg_search: x 8 words x 16 pairs x 32 lanes
+                                     = executed pair-words (early abort makes this smaller than queries x refs x words) */
     int64_t max_mismatch;       /* "Highest number of ACGT mismatches" (nearest.c:324): max over queries of max_incompatible-1 */
 } uvg_stats;
 

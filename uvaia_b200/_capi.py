@@ -34,7 +34,8 @@ class uvg_stats(C.Structure):
     _fields_ = [("n_refs", C.c_int64), ("n_rounds", C.c_int64), ("n_survivors", C.c_int64), ("n_admitted", C.c_int64),
                 ("n_h1_flags", C.c_int64), ("n_overflow_splits", C.c_int64), ("pair_kernel_launches", C.c_int64),
                 ("other_kernel_launches", C.c_int64), ("pair_kernel_ms", C.c_double), ("replay_ms", C.c_double),
-                ("search_ms", C.c_double), ("encode_ms", C.c_double), ("max_mismatch", C.c_int64)]
+                ("search_ms", C.c_double), ("encode_ms", C.c_double), ("warp_chunks_executed", C.c_int64),
+                ("max_mismatch", C.c_int64)]
 
 
 # every symbol include/uvaia_b200.h declares: name -> (restype, argtypes)

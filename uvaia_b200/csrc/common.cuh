@@ -12,11 +12,13 @@ namespace uvg {
 //     uint4 db[group][Wp][32]      (lane = reference within group)
 // so a warp reading column word w of its group issues one fully coalesced 512-byte request of 128-bit loads.
 constexpr int GROUP = 32;
-constexpr int WC = 16;            // column words per staged query chunk
+constexpr int WC = 8;             // column words per staged chunk
 constexpr int QTILE = 64;         // queries per thread block (8 warps x QPW)
 constexpr int QPW = 8;            // queries per warp (register tile)
 constexpr int PAIR_THREADS = 256;
-constexpr int STAGES = 3;
+constexpr int STAGES = 4;
+constexpr int RPL = 2;            // references per lane (a block scores 2 groups = 64 references)
+constexpr int NBAR = 16;          // steps of the admission staircase kept per query
 
 // One staged chunk of a query tile: WC column words of 64 queries.  Contiguous in global memory so that one
 // cp.async.bulk (TMA 1-D bulk copy) moves it into shared memory.
@@ -42,16 +44,21 @@ struct __align__(16) HeapItem {
     int32_t pad;
 };
 
-// Per-query threshold snapshot read by the pair-count kernel: the heap root (worst kept item) once the heap is full.
-// dmax bounds the reference's max_incompatible for the rest of the search: once a heap is full,
-//   max_incompatible(t') <= 1 + max over items kept at time t <= t' of (valid - acgt)
-// (every later root is either one of those items or was admitted under a limit that already obeyed the bound), so a
-// pair with valid - acgt >= dmax can never be admitted (src/nearest.c:488-496 / 450-460).
+// Per-query threshold snapshot read by the pair-count kernel (written by the replay kernel once the heap is full).
+// A pair c with D(c) = valid - acgt mismatches can be admitted at some later time only if the heap root r' at that time
+// has D(r') >= D(c) (src/nearest.c:488-496: D < max_incompatible = D(root)+1) and c is strictly better than r'
+// (min_heap.c:97).  Every future root is either an item kept NOW or was itself admitted under the same rule, so by
+// induction:  c is ever admissible  =>  some item h kept now has D(h) >= D(c) and h < c.   Hence with
+//   bar[b] = min ACGT count (first key) over kept items with D >= b << sh      (non-decreasing in b; bar[0] = root)
+//   dmax   = 1 + max D over kept items
+// a pair with D >= dmax, or with ACGT count < bar[D >> sh], or not strictly better than the root, is never admitted.
 struct __align__(16) Threshold {
-    int32_t s[6];
-    int32_t full;
+    int32_t s[6];                 // heap root (worst kept item)
+    int32_t full;                 // 0: heap not full (every pair survives); else 1 + sh
     int32_t dmax;
+    int32_t bar[NBAR];
 };
+static_assert(sizeof(Threshold) == 96, "Threshold layout");
 
 struct PairParams {
     const uint4*    db;           // whole local database
@@ -67,6 +74,7 @@ struct PairParams {
     Survivor* surv; int32_t* surv_ci; unsigned long long* surv_count; int64_t surv_cap;
     int32_t* qcount;              // [n_query] survivors per query (bucket sizes)
     int32_t early_abort;
+    unsigned long long* work;     // executed (warp, chunk) iterations (early abort makes this < the dense count)
     int32_t* dbg_counts;          // optional [n_query][n][4] dump (debug hook); n = local_end-local_begin
 };
 

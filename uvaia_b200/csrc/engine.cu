@@ -90,6 +90,7 @@ struct uvg_ctx {
     ncclComm_t comm = nullptr;
     int32_t* dbg_counts = nullptr;
     // host cache of the heaps (filled lazily by uvg_get_heap, invalidated by every search / reset)
+    int64_t work_base = 0;
     bool heaps_cached = false;
     std::vector<HeapItem> h_heaps; std::vector<int32_t> h_heap_n, h_max_inc;
 };
@@ -371,7 +372,7 @@ static int ensure_db_capacity(uvg_ctx* c, int64_t need_refs)
     int64_t cap = std::max<int64_t>(need_refs, c->db_cap * 2);
     cap = std::max<int64_t>(cap, c->prm.db_capacity);
     cap = std::max<int64_t>(cap, 4096);
-    cap = (cap + GROUP - 1) / GROUP * GROUP;
+    cap = (cap + GROUP * RPL - 1) / (GROUP * RPL) * (GROUP * RPL);
     const size_t og = (size_t)(c->db_cap / GROUP), ng = (size_t)(cap / GROUP);
     UVG_CUDA(c, grow_array(&c->d_db, og * c->Wp * GROUP, ng * c->Wp * GROUP, false, c->st));
     UVG_CUDA(c, grow_array(&c->d_refamb, og * c->ambw, ng * c->ambw, true, c->st));
@@ -538,7 +539,7 @@ static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t
         pp.local_begin = lstart + b; pp.local_end = lstart + e;
         pp.global_minus_local = tile_global - lstart;
         pp.surv = c->d_surv; pp.surv_ci = c->d_surv_ci; pp.surv_count = c->d_surv_count; pp.surv_cap = c->surv_cap;
-        pp.qcount = c->d_qcount; pp.early_abort = c->prm.early_abort; pp.dbg_counts = nullptr;
+        pp.qcount = c->d_qcount; pp.early_abort = c->prm.early_abort; pp.dbg_counts = nullptr; pp.work = c->d_counters + 2;
         if (mine && e > b) {
             UVG_CUDA(c, launch_consensus(c->d_db, c->d_cons_acgt, c->d_cons_vo, c->Wp, c->prm.acgt_mode, pp.local_begin, pp.local_end,
                                          c->d_c0, c->d_ci, c->st));
@@ -628,6 +629,9 @@ extern "C" int uvg_search(uvg_ctx* c)
     size_t n_ev = 0;
     c->heaps_cached = false;
     c->stats.pair_kernel_ms = 0; c->stats.replay_ms = 0;
+    UVG_CUDA(c, cudaMemcpyAsync(c->h_pinned + 20, c->d_counters + 2, 8, cudaMemcpyDeviceToHost, c->st));
+    UVG_CUDA(c, cudaStreamSynchronize(c->st));
+    c->work_base = (int64_t)c->h_pinned[20];
     UVG_CUDA(c, cudaEventRecord(c->ev_a, c->st));
     for (;;) {
         const int64_t T = c->next_round;
@@ -730,11 +734,10 @@ extern "C" int uvg_get_stats(uvg_ctx* c, uvg_stats* out)
 {
     if (!c || !out) return UVG_EINVAL;
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
-    unsigned long long cnt[2] = {0, 0};
-    UVG_CUDA(c, cudaMemcpyAsync(c->h_pinned + 16, c->d_counters, 16, cudaMemcpyDeviceToHost, c->st));
+    UVG_CUDA(c, cudaMemcpyAsync(c->h_pinned + 16, c->d_counters, 24, cudaMemcpyDeviceToHost, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
-    cnt[0] = c->h_pinned[16]; cnt[1] = c->h_pinned[17];
-    c->stats.n_admitted = (int64_t)cnt[0]; c->stats.n_h1_flags = (int64_t)cnt[1];
+    c->stats.n_admitted = (int64_t)c->h_pinned[16]; c->stats.n_h1_flags = (int64_t)c->h_pinned[17];
+    c->stats.warp_chunks_executed = (int64_t)c->h_pinned[18] - c->work_base;
     if (c->n_query) {
         int rc = cache_heaps(c);
         if (rc) return rc;
@@ -861,7 +864,7 @@ extern "C" int uvg_debug_pair_counts(uvg_ctx* c, int64_t first, int64_t n, int32
     pp.Wp = c->Wp; pp.n_chunks = c->n_chunks; pp.ambw = c->ambw; pp.n_qtiles = c->n_qtiles; pp.n_query = c->n_query;
     pp.local_begin = first; pp.local_end = first + n; pp.global_minus_local = 0;
     pp.surv = c->d_surv; pp.surv_ci = c->d_surv_ci; pp.surv_count = c->d_surv_count; pp.surv_cap = 0;
-    pp.qcount = c->d_qcount; pp.early_abort = 0; pp.dbg_counts = d_out;
+    pp.qcount = c->d_qcount; pp.early_abort = 0; pp.dbg_counts = d_out; pp.work = nullptr;
     cudaError_t e = launch_paircount(pp, c->prm.acgt_mode, c->st);
     if (e == cudaSuccess) e = cudaMemsetAsync(c->d_surv_count, 0, 8, c->st);
     if (e == cudaSuccess) e = cudaMemsetAsync(c->d_qcount, 0, c->n_query * 4, c->st);

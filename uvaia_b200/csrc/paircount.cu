@@ -8,9 +8,10 @@
 //   V = rv & qv                               both valid                           -> valid
 //   Y = P & ~(r_onehot & q_onehot)            intersecting but not a plain base    -> acgt = P - Y   (rare words only)
 //   E = q_ambiguous & (r == q)                identical ambiguity codes            -> text = acgt + E (rare words only)
-// Lane = reference (32 references of a group interleaved per column word -> one coalesced 512 B request per warp and
-// word), warp = 8 queries whose planes are broadcast from shared memory, block = 64 queries x 32 references.
-// Query chunks are staged by TMA bulk copies (cp.async.bulk + mbarrier) through a 3-deep ring.
+// Lane = 2 references (one of each of the block's two groups; 32 references interleaved per column word -> a group's
+// chunk is one contiguous 4 KB run), warp = 8 queries whose planes are broadcast from shared memory, block = 64 queries
+// x 64 references.  Both operands are staged by TMA bulk copies (cp.async.bulk + mbarrier) through a 4-deep ring, so
+// the inner loop issues only LDS, LOP3 (ALU pipe), POPC (XU pipe) and IMAD (FMA pipe).
 #include "common.cuh"
 #include "kernels.h"
 
@@ -64,93 +65,169 @@ __device__ __forceinline__ bool lex_greater(const int32_t (&s)[6], const Thresho
     return false;
 }
 
-constexpr size_t PAIR_SMEM = STAGES * sizeof(QChunk) + 64 /*barriers*/ + QTILE * sizeof(Threshold);
+// One pipeline stage: a query chunk (64 queries x WC words) and the same WC words of the block's 64 references.
+struct __align__(16) Stage {
+    QChunk q;
+    uint4  ref[RPL][WC][GROUP];
+};
+constexpr uint32_t STAGE_REF_BYTES = WC * GROUP * sizeof(uint4);
+constexpr size_t PAIR_SMEM = STAGES * sizeof(Stage) + 64 /*barriers*/ + QTILE * sizeof(Threshold);
+constexpr int FLUSH_CHUNKS = 2040 / WC;        // packed 16-bit counters are flushed before they can overflow
 
-template <int MODE>
-__global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams p)
+// a*b+c on the FMA pipe (IMAD): keeps the accumulations off the ALU pipe that issues the LOP3s
+__device__ __forceinline__ uint32_t imad(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+__device__ __forceinline__ bool survives(const int32_t (&sc)[6], int32_t D, const Threshold& t)
+{
+    if (!t.full) return true;
+    if (D >= t.dmax) return false;
+    if (sc[0] < t.bar[D >> (t.full - 1)]) return false;
+    return lex_greater(sc, t);
+}
+
+// LONG = alignments of 65,536 columns or more (counters may exceed 16 bits): packed counters are flushed into
+// 32-bit totals every FLUSH_CHUNKS chunks.
+template <int MODE, bool LONG>
+__global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams p, const uint32_t k1, const uint32_t k64k)
 {
     extern __shared__ __align__(128) uint8_t smem[];
-    QChunk* stage = reinterpret_cast<QChunk*>(smem);
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * sizeof(QChunk));
-    Threshold* s_thr = reinterpret_cast<Threshold*>(smem + STAGES * sizeof(QChunk) + 64);
+    Stage* stage = reinterpret_cast<Stage*>(smem);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * sizeof(Stage));
+    Threshold* s_thr = reinterpret_cast<Threshold*>(smem + STAGES * sizeof(Stage) + 64);
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int qt = blockIdx.x % p.n_qtiles;
-    const int64_t group = p.local_begin / GROUP + blockIdx.x / p.n_qtiles;
-    const int64_t local = group * GROUP + lane;
-    const bool in_range = local >= p.local_begin && local < p.local_end;
+    const int64_t group0 = (p.local_begin / (GROUP * RPL) + blockIdx.x / p.n_qtiles) * RPL;
     const QChunk* qsrc = p.qdata + (size_t)qt * p.n_chunks;
+    const uint4* rsrc = p.db + (size_t)group0 * p.Wp * GROUP;
+    const size_t group_stride = (size_t)p.Wp * GROUP;                // uint4 elements between consecutive groups
+    bool in_range[RPL];
+    int64_t local[RPL];
+#pragma unroll
+    for (int g = 0; g < RPL; ++g) {
+        local[g] = (group0 + g) * GROUP + lane;
+        in_range[g] = local[g] >= p.local_begin && local[g] < p.local_end;
+    }
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) mbar_init(full + s, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (threadIdx.x < QTILE) s_thr[threadIdx.x] = p.thr[qt * QTILE + threadIdx.x];
+    {
+        const uint4* tsrc = reinterpret_cast<const uint4*>(p.thr + (size_t)qt * QTILE);
+        uint4* tdst = reinterpret_cast<uint4*>(s_thr);
+        for (int i = threadIdx.x; i < (int)(QTILE * sizeof(Threshold) / 16); i += blockDim.x) tdst[i] = tsrc[i];
+    }
     __syncthreads();
+    auto issue = [&](int c, int s) {
+        mbar_expect_tx(full + s, (uint32_t)(sizeof(QChunk) + RPL * STAGE_REF_BYTES));
+        bulk_g2s(&stage[s].q, qsrc + c, (uint32_t)sizeof(QChunk), full + s);
+#pragma unroll
+        for (int g = 0; g < RPL; ++g)
+            bulk_g2s(&stage[s].ref[g][0][0], rsrc + g * group_stride + (size_t)c * WC * GROUP, STAGE_REF_BYTES, full + s);
+    };
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES && s < p.n_chunks; ++s) {
-            mbar_expect_tx(full + s, (uint32_t)sizeof(QChunk));
-            bulk_g2s(stage + s, qsrc + s, (uint32_t)sizeof(QChunk), full + s);
-        }
+        for (int s = 0; s < STAGES && s < p.n_chunks; ++s) issue(s, s);
     }
 
-    int32_t accP[QPW], accV[QPW], accY[QPW], accE[QPW];
+    uint32_t accPV[RPL][QPW], accYE[RPL][QPW];                 // packed: P | V << 16  and  Y | E << 16
+    int32_t tot[LONG ? 4 : 1][RPL][QPW];
 #pragma unroll
-    for (int j = 0; j < QPW; ++j) { accP[j] = 0; accV[j] = 0; accY[j] = 0; accE[j] = 0; }
+    for (int g = 0; g < RPL; ++g)
+#pragma unroll
+        for (int j = 0; j < QPW; ++j) {
+            accPV[g][j] = 0; accYE[g][j] = 0;
+#pragma unroll
+            for (int k = 0; k < (LONG ? 4 : 1); ++k) tot[k][g][j] = 0;
+        }
+    auto flush = [&]() {
+        if (LONG) {
+#pragma unroll
+            for (int g = 0; g < RPL; ++g)
+#pragma unroll
+                for (int j = 0; j < QPW; ++j) {
+                    tot[0][g][j] += accPV[g][j] & 0xffffu; tot[LONG ? 1 : 0][g][j] += accPV[g][j] >> 16;
+                    tot[LONG ? 2 : 0][g][j] += accYE[g][j] & 0xffffu; tot[LONG ? 3 : 0][g][j] += accYE[g][j] >> 16;
+                    accPV[g][j] = 0; accYE[g][j] = 0;
+                }
+        }
+    };
+    auto cntP = [&](int g, int j) { return (int32_t)(accPV[g][j] & 0xffffu) + (LONG ? tot[0][g][j] : 0); };
+    auto cntV = [&](int g, int j) { return (int32_t)(accPV[g][j] >> 16) + (LONG ? tot[LONG ? 1 : 0][g][j] : 0); };
+    auto cntY = [&](int g, int j) { return (int32_t)(accYE[g][j] & 0xffffu) + (LONG ? tot[LONG ? 2 : 0][g][j] : 0); };
+    auto cntE = [&](int g, int j) { return (int32_t)(accYE[g][j] >> 16) + (LONG ? tot[LONG ? 3 : 0][g][j] : 0); };
 
-    const uint4* rp = p.db + (size_t)group * p.Wp * GROUP + lane;
-    const uint32_t* ambp = p.refamb + (size_t)group * p.ambw;
+    const uint32_t* ambp = p.refamb + (size_t)group0 * p.ambw;
     const int q0 = warp * QPW;
     bool warp_dead = false;
+    uint32_t executed = 0;
     int c = 0;
     for (; c < p.n_chunks; ++c) {
         const int s = c % STAGES;
         mbar_wait(full + s, (uint32_t)((c / STAGES) & 1));
-        const QChunk& ch = stage[s];
+        const Stage& st = stage[s];
         if (!warp_dead) {
-            const uint32_t ambbits = (__ldg(ambp + ((c * WC) >> 5)) >> ((c * WC) & 31)) & 0xffffu;
-            const uint4* rw = rp + (size_t)(c * WC) * GROUP;
-#pragma unroll 4
+            ++executed;
+            uint32_t ambbits = 0;
+            if (MODE == 0) {
+#pragma unroll
+                for (int g = 0; g < RPL; ++g) ambbits |= (__ldg(ambp + g * p.ambw + ((c * WC) >> 5)) >> ((c * WC) & 31)) & ((1u << WC) - 1u);
+            }
+#pragma unroll
             for (int wl = 0; wl < WC; ++wl) {
-                const uint4 r = __ldg(rw + (size_t)wl * GROUP);
-                const uint32_t rv = plane_any(r);
-                const bool slow = (MODE == 0) && ((((ch.slow[wl] >> warp) | (ambbits >> wl)) & 1u) != 0u);
+                uint4 r[RPL];
+                uint32_t rv[RPL];
+#pragma unroll
+                for (int g = 0; g < RPL; ++g) { r[g] = st.ref[g][wl][lane]; rv[g] = plane_any(r[g]); }
+                const bool slow = (MODE == 0) && ((((st.q.slow[wl] >> warp) | (ambbits >> wl)) & 1u) != 0u);
                 if (!slow) {
 #pragma unroll
                     for (int j = 0; j < QPW; ++j) {
-                        const uint4 q = ch.acgt[wl][q0 + j];
-                        const uint2 vo = ch.vo[wl][q0 + j];
-                        const uint32_t P = plane_overlap(r, q);
-                        const uint32_t V = rv & vo.x;
-                        accP[j] += __popc(P);
-                        accV[j] += __popc(V);
-                        if (MODE == 1) accY[j] += __popc(V & ~P & vo.y);     // mismatches on the idx sites
+                        const uint4 q = st.q.acgt[wl][q0 + j];
+                        const uint2 vo = st.q.vo[wl][q0 + j];
+#pragma unroll
+                        for (int g = 0; g < RPL; ++g) {
+                            const uint32_t P = plane_overlap(r[g], q);
+                            const uint32_t V = rv[g] & vo.x;
+                            accPV[g][j] = imad(__popc(V), k64k, imad(__popc(P), k1, accPV[g][j]));
+                            if (MODE == 1) accYE[g][j] = imad(__popc(V & ~P & vo.y), k1, accYE[g][j]);   // mismatches on idx sites
+                        }
                     }
                 } else {
-                    const uint32_t rone = plane_onehot(r);
 #pragma unroll
-                    for (int j = 0; j < QPW; ++j) {
-                        const uint4 q = ch.acgt[wl][q0 + j];
-                        const uint2 vo = ch.vo[wl][q0 + j];
-                        const uint32_t P = plane_overlap(r, q);
-                        const uint32_t V = rv & vo.x;
-                        accP[j] += __popc(P);
-                        accV[j] += __popc(V);
-                        accY[j] += __popc(P & ~(rone & vo.y));
-                        accE[j] += __popc(vo.x & ~vo.y & ~plane_differ(r, q));
+                    for (int g = 0; g < RPL; ++g) {
+                        const uint32_t rone = plane_onehot(r[g]);
+#pragma unroll
+                        for (int j = 0; j < QPW; ++j) {
+                            const uint4 q = st.q.acgt[wl][q0 + j];
+                            const uint2 vo = st.q.vo[wl][q0 + j];
+                            const uint32_t P = plane_overlap(r[g], q);
+                            const uint32_t V = rv[g] & vo.x;
+                            accPV[g][j] += __popc(P) + (__popc(V) << 16);
+                            accYE[g][j] += __popc(P & ~(rone & vo.y)) + (__popc(vo.x & ~vo.y & ~plane_differ(r[g], q)) << 16);
+                        }
                     }
                 }
             }
+            if (LONG && (c + 1) % FLUSH_CHUNKS == 0) flush();
             if (p.early_abort) {
-                // exact: a pair whose ACGT matches cannot reach the query's k-th best first key is never a survivor
+                // exact: a pair that can no longer satisfy the admission staircase is never a survivor.  Mismatches so
+                // far only grow along the genome and the best reachable ACGT count is what is left of the query.
                 bool dead = true;
-                if (in_range) {
+#pragma unroll
+                for (int g = 0; g < RPL; ++g) {
+                    if (!in_range[g]) continue;
 #pragma unroll
                     for (int j = 0; j < QPW; ++j) {
                         const Threshold& t = s_thr[q0 + j];
-                        // mismatches so far (monotone along the genome) and the best ACGT count still reachable
-                        const int32_t dsofar = (MODE == 0) ? (accV[j] - accP[j] + accY[j]) : (accV[j] - accP[j]);
-                        if (!t.full || (dsofar < t.dmax && accP[j] + (int32_t)ch.rem[q0 + j] >= t.s[0])) dead = false;
+                        if (!t.full) { dead = false; continue; }
+                        const int32_t dsofar = (MODE == 0) ? (cntV(g, j) - cntP(g, j) + cntY(g, j)) : (cntV(g, j) - cntP(g, j));
+                        if (dsofar < t.dmax && cntP(g, j) + (int32_t)st.q.rem[q0 + j] >= t.bar[dsofar >> (t.full - 1)]) dead = false;
                     }
                 }
                 warp_dead = __all_sync(0xffffffffu, dead);
@@ -158,60 +235,64 @@ __global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams 
         }
         const int all_dead = __syncthreads_and(warp_dead ? 1 : 0);
         if (all_dead) break;
-        if (threadIdx.x == 0 && c + STAGES < p.n_chunks) {
-            mbar_expect_tx(full + s, (uint32_t)sizeof(QChunk));
-            bulk_g2s(stage + s, qsrc + c + STAGES, (uint32_t)sizeof(QChunk), full + s);
-        }
+        if (threadIdx.x == 0 && c + STAGES < p.n_chunks) issue(c + STAGES, s);
     }
+    if (lane == 0 && p.work) atomicAdd(p.work, (unsigned long long)executed);
     if (c < p.n_chunks) {
         // whole block aborted: drain the bulk copies still in flight before the shared memory is released
         for (int cc = c + 1; cc < p.n_chunks && cc < c + STAGES; ++cc) mbar_wait(full + cc % STAGES, (uint32_t)((cc / STAGES) & 1));
         return;
     }
-    // ---- epilogue: 6-tuple, threshold test, warp-aggregated survivor append ----
-    const int32_t non_n = in_range ? p.non_n[local] : 0;
-    const int32_t c0 = in_range ? p.c0[local] : 0;
-    const int32_t ci = in_range ? p.ci[local] : 0;
+
+    // ---- epilogue: 6-tuple, staircase test, warp-aggregated survivor append ----
     const int64_t n_launch = p.local_end - p.local_begin;
 #pragma unroll
-    for (int j = 0; j < QPW; ++j) {
-        const int q = qt * QTILE + q0 + j;
-        int32_t sc[6];
-        if (MODE == 0) {
-            const int32_t A = accP[j] - accY[j];
-            sc[0] = A; sc[1] = A + accE[j]; sc[2] = accP[j]; sc[3] = accV[j]; sc[4] = A - c0; sc[5] = non_n;
-        } else {
-            const int32_t M = accV[j] - accP[j];
-            sc[0] = accP[j]; sc[1] = accV[j]; sc[2] = accP[j] - c0; sc[3] = non_n; sc[4] = M - accY[j]; sc[5] = accY[j];
-        }
-        bool pass = false;
-        if (in_range && q < p.n_query && !warp_dead) {
-            const Threshold& t = s_thr[q0 + j];
-            const int32_t D = (MODE == 0) ? (sc[3] - sc[0]) : (sc[1] - sc[0]);
-            pass = !t.full || (D < t.dmax && lex_greater(sc, t));
-            if (p.dbg_counts) {
-                int32_t* o = p.dbg_counts + ((size_t)q * n_launch + (local - p.local_begin)) * 4;
-                if (MODE == 0) { o[0] = sc[0]; o[1] = sc[1]; o[2] = sc[2]; o[3] = sc[3]; }
-                else { o[0] = accP[j]; o[1] = accV[j]; o[2] = accY[j]; o[3] = 0; }
-            }
-        }
-        const uint32_t m = __ballot_sync(0xffffffffu, pass);
-        if (m) {
-            unsigned long long base = 0;
-            if (lane == 0) {
-                base = atomicAdd(p.surv_count, (unsigned long long)__popc(m));
-                atomicAdd(p.qcount + q, __popc(m));
-            }
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (pass) {
-                const unsigned long long slot = base + __popc(m & ((1u << lane) - 1u));
-                if (slot < (unsigned long long)p.surv_cap) {
-                    Survivor sv;
-                    sv.q = q; sv.r = (int32_t)(local + p.global_minus_local);
+    for (int g = 0; g < RPL; ++g) {
+        const int32_t non_n = in_range[g] ? p.non_n[local[g]] : 0;
+        const int32_t c0 = in_range[g] ? p.c0[local[g]] : 0;
+        const int32_t ci = in_range[g] ? p.ci[local[g]] : 0;
 #pragma unroll
-                    for (int k = 0; k < 6; ++k) sv.s[k] = sc[k];
-                    p.surv[slot] = sv;
-                    p.surv_ci[slot] = ci;
+        for (int j = 0; j < QPW; ++j) {
+            const int q = qt * QTILE + q0 + j;
+            const int32_t cP = cntP(g, j), cV = cntV(g, j), cY = cntY(g, j), cE = cntE(g, j);
+            int32_t sc[6];
+            int32_t D;
+            if (MODE == 0) {
+                const int32_t A = cP - cY;
+                sc[0] = A; sc[1] = A + cE; sc[2] = cP; sc[3] = cV; sc[4] = A - c0; sc[5] = non_n;
+                D = cV - A;
+            } else {
+                const int32_t M = cV - cP;
+                sc[0] = cP; sc[1] = cV; sc[2] = cP - c0; sc[3] = non_n; sc[4] = M - cY; sc[5] = cY;
+                D = M;
+            }
+            bool pass = false;
+            if (in_range[g] && q < p.n_query && !warp_dead) {
+                pass = survives(sc, D, s_thr[q0 + j]);
+                if (p.dbg_counts) {
+                    int32_t* o = p.dbg_counts + ((size_t)q * n_launch + (local[g] - p.local_begin)) * 4;
+                    if (MODE == 0) { o[0] = sc[0]; o[1] = sc[1]; o[2] = sc[2]; o[3] = sc[3]; }
+                    else { o[0] = cP; o[1] = cV; o[2] = cY; o[3] = 0; }
+                }
+            }
+            const uint32_t m = __ballot_sync(0xffffffffu, pass);
+            if (m) {
+                unsigned long long base = 0;
+                if (lane == 0) {
+                    base = atomicAdd(p.surv_count, (unsigned long long)__popc(m));
+                    atomicAdd(p.qcount + q, __popc(m));
+                }
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (pass) {
+                    const unsigned long long slot = base + __popc(m & ((1u << lane) - 1u));
+                    if (slot < (unsigned long long)p.surv_cap) {
+                        Survivor sv;
+                        sv.q = q; sv.r = (int32_t)(local[g] + p.global_minus_local);
+#pragma unroll
+                        for (int k = 0; k < 6; ++k) sv.s[k] = sc[k];
+                        p.surv[slot] = sv;
+                        p.surv_ci[slot] = ci;
+                    }
                 }
             }
         }
@@ -246,19 +327,29 @@ __global__ void __launch_bounds__(256) k_consensus(const uint4* __restrict__ db,
 
 cudaError_t paircount_setup()
 {
-    cudaError_t e = cudaFuncSetAttribute(k_paircount<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PAIR_SMEM);
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(k_paircount<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PAIR_SMEM);
+    cudaError_t e;
+#define SETUP_(K) e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PAIR_SMEM); if (e != cudaSuccess) return e;
+    SETUP_((k_paircount<0, false>)) SETUP_((k_paircount<1, false>)) SETUP_((k_paircount<0, true>)) SETUP_((k_paircount<1, true>))
+#undef SETUP_
+    return cudaSuccess;
 }
 
 cudaError_t launch_paircount(const PairParams& p, int acgt_mode, cudaStream_t st)
 {
     if (p.local_end <= p.local_begin) return cudaSuccess;
-    const int64_t g0 = p.local_begin / GROUP, g1 = (p.local_end + GROUP - 1) / GROUP;
+    const int64_t per = GROUP * RPL;
+    const int64_t g0 = p.local_begin / per, g1 = (p.local_end + per - 1) / per;
     const int64_t blocks = (g1 - g0) * p.n_qtiles;
     if (blocks > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
-    if (acgt_mode) k_paircount<1><<<(unsigned)blocks, PAIR_THREADS, PAIR_SMEM, st>>>(p);
-    else k_paircount<0><<<(unsigned)blocks, PAIR_THREADS, PAIR_SMEM, st>>>(p);
+    const bool lng = (int64_t)p.Wp * 32 > 65535;
+    const uint32_t k1 = 1u, k64k = 65536u;
+    if (acgt_mode) {
+        if (lng) k_paircount<1, true><<<(unsigned)blocks, PAIR_THREADS, PAIR_SMEM, st>>>(p, k1, k64k);
+        else k_paircount<1, false><<<(unsigned)blocks, PAIR_THREADS, PAIR_SMEM, st>>>(p, k1, k64k);
+    } else {
+        if (lng) k_paircount<0, true><<<(unsigned)blocks, PAIR_THREADS, PAIR_SMEM, st>>>(p, k1, k64k);
+        else k_paircount<0, false><<<(unsigned)blocks, PAIR_THREADS, PAIR_SMEM, st>>>(p, k1, k64k);
+    }
     return cudaGetLastError();
 }
 

@@ -190,7 +190,7 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
     __syncthreads();
     n = s_misc[40];
     if (n == K) {
-        // threshold snapshot for the next rounds: heap root + the bound on every future max_incompatible
+        // threshold snapshot for the next rounds: heap root + admission staircase (see Threshold in common.cuh)
         int dm = 0;
         for (int i = 1 + threadIdx.x; i <= n; i += blockDim.x) {
             const int d = p.acgt_mode ? (a[i].s[1] - a[i].s[0]) : (a[i].s[3] - a[i].s[0]);
@@ -200,13 +200,23 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
         for (int o = 16; o > 0; o >>= 1) dm = max(dm, __shfl_xor_sync(0xffffffffu, dm, o));
         if ((threadIdx.x & 31) == 0) s_misc[48 + (threadIdx.x >> 5)] = dm;
         __syncthreads();
+        for (int k = 0; k < RP_THREADS / 32; ++k) dm = max(dm, s_misc[48 + k]);
+        int sh = 0;
+        while ((dm >> sh) >= NBAR) ++sh;
+        if (threadIdx.x < NBAR) {
+            const int lo = (int)threadIdx.x << sh;
+            int mn = 0x7fffffff;
+            for (int i = 1; i <= n; ++i) {
+                const int d = p.acgt_mode ? (a[i].s[1] - a[i].s[0]) : (a[i].s[3] - a[i].s[0]);
+                if (d >= lo) mn = min(mn, a[i].s[0]);
+            }
+            p.thr[q].bar[threadIdx.x] = mn;
+        }
         if (threadIdx.x == 0) {
-            for (int k = 0; k < RP_THREADS / 32; ++k) dm = max(dm, s_misc[48 + k]);
-            Threshold t;
 #pragma unroll
-            for (int k = 0; k < 6; ++k) t.s[k] = a[1].s[k];
-            t.full = 1; t.dmax = dm + 1;
-            p.thr[q] = t;
+            for (int k = 0; k < 6; ++k) p.thr[q].s[k] = a[1].s[k];
+            p.thr[q].dmax = dm + 1;
+            p.thr[q].full = 1 + sh;
         }
     }
     if (heap_in_smem) for (int i = 1 + threadIdx.x; i <= n; i += blockDim.x) gheap[i] = a[i];
