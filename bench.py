@@ -408,7 +408,7 @@ def main():
         line = dict(base, value=qps, ms_per_step=ms_step, wall_ms_per_step=wall_ms / args.steps, gsite_cmp_per_s=Q * R * L / (ms_step * 1e-3) / 1e9,
                     clocks=clocks, e2e=e2e, gpu_launches=int(launches), roofline=roofline, cpu_baseline=cb,
                     replay_ms_per_step=replay_ms / args.steps, db_build_s=t_build,
-                    search_stats={k: st[k] for k in ("n_rounds", "n_survivors", "n_admitted", "n_h1_flags", "n_overflow_splits", "max_mismatch")},
+                    search_stats={k: st[k] for k in ("n_rounds", "n_admitted", "n_h1_flags", "max_mismatch")},
                     result_checksum=checksum)
         print(json.dumps(line))
     eng.close()

@@ -48,10 +48,10 @@ typedef struct uvg_params {
     int32_t pool;           /* --pool: only used to detect hazard H1 (pool-dependent truncation) */
     int32_t device;         /* CUDA ordinal */
     int32_t first_round;    /* references in the first scoring round per rank (0 = default 1024) */
-    int32_t max_round;      /* largest round per rank (0 = default 65536) */
+    int32_t max_round;      /* largest round per rank (0 = default 65536; also capped so the score tile stays <= 2 GiB) */
     int32_t early_abort;    /* 1 = warp-granular abort of pairs that cannot beat the k-th best (exact, perf only) */
     int32_t rank, world;    /* row sharding: this context holds tile `rank` of every round (world<=1: single GPU) */
-    int64_t max_survivors;  /* capacity of the survivor buffer in records of 32 B (0 = default) */
+    int64_t reserved0;      /* must be 0 */
     int64_t db_capacity;    /* references to reserve HBM for (0 = grow on demand) */
 } uvg_params;
 
@@ -63,10 +63,8 @@ typedef struct uvg_query_info {
 typedef struct uvg_stats {
     int64_t n_refs;             /* references scored so far */
     int64_t n_rounds;
-    int64_t n_survivors;        /* records emitted by the pair-count kernel */
     int64_t n_admitted;         /* successful heap insertions */
     int64_t n_h1_flags;         /* admissions that MAY depend on --pool in the reference (hazard H1) */
-    int64_t n_overflow_splits;  /* rounds that had to be split because the survivor buffer filled */
     int64_t pair_kernel_launches, other_kernel_launches;
     double  pair_kernel_ms;     /* CUDA-event time of the pair-count launches of the last uvg_search */
     double  replay_ms;          /* ... of bucket+replay */

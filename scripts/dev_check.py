@@ -6,7 +6,7 @@ from uvaia_b200.synth import SynthModel
 from uvaia_b200.engine import Engine
 from oracle import uvaia_oracle as orc
 
-def run_case(L, nq, nr, nbest, acgt=False, trim=0, amb=0.0, first_round=0, max_round=0, max_surv=0, early_abort=False, seed=5):
+def run_case(L, nq, nr, nbest, acgt=False, trim=0, amb=0.0, first_round=0, max_round=0, early_abort=False, seed=5):
     m = SynthModel(nsites=L, n_clades=12, seed=seed, clade_subs=max(3, L // 500))
     qn, Q = m.sample(nq, seed + 1, ambiguous_frac=amb, prefix="Q")
     rn, R = m.sample(nr, seed + 2, ambiguous_frac=amb / 2, prefix="R")
@@ -16,7 +16,7 @@ def run_case(L, nq, nr, nbest, acgt=False, trim=0, amb=0.0, first_round=0, max_r
     t1 = time.time()
     names, Qo, tr, cons, idx, idx_m, idx_c = orc.prepare_queries(qn, qs, trim, acgt, 0.5)
     with Engine(L, nbest=nbest, trim=trim, acgt=acgt, pool=64, first_round=first_round, max_round=max_round,
-                max_survivors=max_surv, early_abort=early_abort) as eng:
+                early_abort=early_abort) as eng:
         info = eng.set_queries(Qo)
         assert (info.n_idx, info.n_idx_m, info.n_idx_c) == (len(idx), len(idx_m), len(idx_c)), (info.n_idx, info.n_idx_m, info.n_idx_c, len(idx), len(idx_m), len(idx_c))
         nn, acc, na = eng.push_refs(R, int(L * 0.5))
@@ -50,9 +50,9 @@ def run_case(L, nq, nr, nbest, acgt=False, trim=0, amb=0.0, first_round=0, max_r
                     print("  MISMATCH query", iq, "\n   got", sc[:3], refs[:3], "\n  want", ws[:3], wr[:3], len(refs), len(wr))
         eb = eng.ever_best(0, na)
         eb_ok = np.array_equal(np.nonzero(eb)[0], np.array(ref.ever_best, np.int64))
-    print(f"L={L} nq={nq} nr={nr} K={nbest} acgt={acgt} trim={trim} amb={amb} fr={first_round} mr={max_round} ms={max_surv} ea={early_abort}: "
-          f"{'OK' if bad == 0 and eb_ok else 'FAIL'} bad={bad} ever_best_ok={eb_ok} oracle={t1-t0:.1f}s rounds={st['n_rounds']} surv={st['n_survivors']} "
-          f"adm={st['n_admitted']} splits={st['n_overflow_splits']} h1={st['n_h1_flags']} pair_ms={st['pair_kernel_ms']:.2f}")
+    print(f"L={L} nq={nq} nr={nr} K={nbest} acgt={acgt} trim={trim} amb={amb} fr={first_round} mr={max_round} ea={early_abort}: "
+          f"{'OK' if bad == 0 and eb_ok else 'FAIL'} bad={bad} ever_best_ok={eb_ok} oracle={t1-t0:.1f}s rounds={st['n_rounds']} "
+          f"adm={st['n_admitted']} h1={st['n_h1_flags']} pair_ms={st['pair_kernel_ms']:.2f}")
     return bad == 0 and eb_ok
 
 ok = True
@@ -62,7 +62,8 @@ ok &= run_case(2000, 70, 2500, 10, first_round=64, max_round=512, early_abort=Tr
 ok &= run_case(2000, 33, 1500, 10, acgt=True)
 ok &= run_case(2000, 33, 1500, 10, trim=100)
 ok &= run_case(2000, 33, 1500, 1, amb=0.1)
-ok &= run_case(2000, 40, 3000, 20, amb=0.2, first_round=32, max_round=256, max_surv=4096)
+ok &= run_case(2000, 40, 3000, 20, amb=0.2, first_round=32, max_round=256)
+ok &= run_case(2000, 40, 3000, 20, amb=0.2, first_round=32, max_round=256, early_abort=True, acgt=True)
 ok &= run_case(29903, 20, 2000, 10, early_abort=True)
 print("ALL OK" if ok else "SOME FAILED")
 sys.exit(0 if ok else 1)

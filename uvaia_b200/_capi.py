@@ -22,7 +22,7 @@ class uvg_params(C.Structure):
     _fields_ = [("abi_version", C.c_int32), ("nchar", C.c_int32), ("trim", C.c_int32), ("nbest", C.c_int32),
                 ("acgt_mode", C.c_int32), ("pool", C.c_int32), ("device", C.c_int32), ("first_round", C.c_int32),
                 ("max_round", C.c_int32), ("early_abort", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
-                ("max_survivors", C.c_int64), ("db_capacity", C.c_int64)]
+                ("reserved0", C.c_int64), ("db_capacity", C.c_int64)]
 
 
 class uvg_query_info(C.Structure):
@@ -31,8 +31,8 @@ class uvg_query_info(C.Structure):
 
 
 class uvg_stats(C.Structure):
-    _fields_ = [("n_refs", C.c_int64), ("n_rounds", C.c_int64), ("n_survivors", C.c_int64), ("n_admitted", C.c_int64),
-                ("n_h1_flags", C.c_int64), ("n_overflow_splits", C.c_int64), ("pair_kernel_launches", C.c_int64),
+    _fields_ = [("n_refs", C.c_int64), ("n_rounds", C.c_int64), ("n_admitted", C.c_int64),
+                ("n_h1_flags", C.c_int64), ("pair_kernel_launches", C.c_int64),
                 ("other_kernel_launches", C.c_int64), ("pair_kernel_ms", C.c_double), ("replay_ms", C.c_double),
                 ("search_ms", C.c_double), ("encode_ms", C.c_double), ("warp_chunks_executed", C.c_int64),
                 ("max_mismatch", C.c_int64)]

@@ -30,13 +30,6 @@ struct __align__(16) QChunk {
 };
 static_assert(sizeof(QChunk) % 16 == 0, "bulk copy size must be a multiple of 16");
 
-// Survivor record emitted by the pair-count kernel and consumed by the replay kernel (32 B).
-struct __align__(16) Survivor {
-    int32_t q;
-    int32_t r;                    // global ordinal of the accepted reference
-    int32_t s[6];
-};
-
 // Heap slot (32 B): the reference's q_item (src/min_heap.h:14-18) with name -> ordinal.
 struct __align__(16) HeapItem {
     int32_t s[6];
@@ -65,17 +58,13 @@ struct PairParams {
     const uint32_t* refamb;       // [group][ambw] bit w%32 of word w/32: some reference of the group is ambiguous in column word w
     const QChunk*   qdata;        // [n_qtiles][n_chunks]
     const Threshold* thr;         // [n_qtiles*QTILE]
-    const int32_t*  non_n;        // per local reference
-    const int32_t*  c0;           // per local reference: consensus-stage matches (c0 / cmatch)
-    const int32_t*  ci;           // per local reference: consensus-stage mismatches
     int32_t Wp, n_chunks, ambw, n_qtiles, n_query;
     int64_t local_begin, local_end;   // local reference range of this launch
     int64_t global_minus_local;       // global ordinal = local index + this
-    Survivor* surv; int32_t* surv_ci; unsigned long long* surv_count; int64_t surv_cap;
-    int32_t* qcount;              // [n_query] survivors per query (bucket sizes)
+    uint4*   scores;              // dense output: scores[q * score_stride + score_col0 + (local - local_begin)]
+    int64_t  score_stride, score_col0;   //   default mode (acgt, text, partial, valid); --acgt mode (match, valid, mism_idx, 0)
     int32_t early_abort;
     unsigned long long* work;     // executed (warp, chunk) iterations (early abort makes this < the dense count)
-    int32_t* dbg_counts;          // optional [n_query][n][4] dump (debug hook); n = local_end-local_begin
 };
 
 __host__ __device__ inline int64_t db_word_index(int64_t group, int w, int lane, int Wp)

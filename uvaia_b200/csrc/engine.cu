@@ -64,17 +64,15 @@ struct uvg_ctx {
     Threshold* d_thr = nullptr;
     HeapItem* d_heaps = nullptr;
     int32_t *d_heap_n = nullptr, *d_max_inc = nullptr, *d_batch_id = nullptr, *d_max_inc_batch = nullptr;
-    int32_t *d_qcount = nullptr, *d_qoffset = nullptr, *d_qcursor = nullptr;
     // database (local shard)
     int64_t db_cap = 0, db_n = 0, db_scored = 0, global_base = 0, global_total = -1;
     uint4* d_db = nullptr; uint32_t* d_refamb = nullptr;
     int32_t *d_non_n = nullptr, *d_c0 = nullptr, *d_ci = nullptr;
     uint8_t* d_ever = nullptr; int64_t ever_cap = 0;
-    // survivors
-    int64_t surv_cap = 0;
-    Survivor *d_surv = nullptr, *d_gather = nullptr, *d_bucket = nullptr;
-    int32_t *d_surv_ci = nullptr, *d_gather_ci = nullptr, *d_bucket_ci = nullptr;
-    unsigned long long *d_surv_count = nullptr, *d_counters = nullptr, *d_gcounts = nullptr;
+    // dense score tile of one round: [n_query][score_cap] x (4 counts)
+    int64_t score_cap = 0;
+    uint4* d_scores = nullptr;
+    unsigned long long* d_counters = nullptr;
     unsigned long long* h_pinned = nullptr;          // small pinned read-back area
     // push staging
     uint8_t* d_stage_text = nullptr; size_t stage_text_bytes = 0;
@@ -151,9 +149,8 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
     CK_(upload_luts());
     CK_(paircount_setup());
     CK_(replay_setup(c->K));
-    CK_(cudaMalloc(&c->d_surv_count, 64)); CK_(cudaMalloc(&c->d_counters, 64)); CK_(cudaMalloc(&c->d_nacc, 64));
-    CK_(cudaMalloc(&c->d_gcounts, 8 * 64));
-    CK_(cudaMemset(c->d_surv_count, 0, 64)); CK_(cudaMemset(c->d_counters, 0, 64));
+    CK_(cudaMalloc(&c->d_counters, 64)); CK_(cudaMalloc(&c->d_nacc, 64));
+    CK_(cudaMemset(c->d_counters, 0, 64));
     CK_(cudaMallocHost(&c->h_pinned, 1024));
 #undef CK_
     *out = c;
@@ -164,11 +161,10 @@ static void free_queries(uvg_ctx* c)
 {
     cudaFree(c->d_qdata); cudaFree(c->d_cons_acgt); cudaFree(c->d_cons_vo); cudaFree(c->d_thr); cudaFree(c->d_heaps);
     cudaFree(c->d_heap_n); cudaFree(c->d_max_inc); cudaFree(c->d_batch_id); cudaFree(c->d_max_inc_batch);
-    cudaFree(c->d_qcount); cudaFree(c->d_qoffset); cudaFree(c->d_qcursor);
-    cudaFree(c->d_surv); cudaFree(c->d_gather); cudaFree(c->d_bucket); cudaFree(c->d_surv_ci); cudaFree(c->d_gather_ci); cudaFree(c->d_bucket_ci);
+    cudaFree(c->d_scores);
     c->d_qdata = nullptr; c->d_cons_acgt = nullptr; c->d_cons_vo = nullptr; c->d_thr = nullptr; c->d_heaps = nullptr;
-    c->d_heap_n = c->d_max_inc = c->d_batch_id = c->d_max_inc_batch = c->d_qcount = c->d_qoffset = c->d_qcursor = nullptr;
-    c->d_surv = c->d_gather = c->d_bucket = nullptr; c->d_surv_ci = c->d_gather_ci = c->d_bucket_ci = nullptr;
+    c->d_heap_n = c->d_max_inc = c->d_batch_id = c->d_max_inc_batch = nullptr;
+    c->d_scores = nullptr; c->score_cap = 0;
 }
 
 extern "C" void uvg_destroy(uvg_ctx* c)
@@ -179,7 +175,7 @@ extern "C" void uvg_destroy(uvg_ctx* c)
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     free_queries(c);
     cudaFree(c->d_db); cudaFree(c->d_refamb); cudaFree(c->d_non_n); cudaFree(c->d_c0); cudaFree(c->d_ci); cudaFree(c->d_ever);
-    cudaFree(c->d_surv_count); cudaFree(c->d_counters); cudaFree(c->d_nacc); cudaFree(c->d_gcounts);
+    cudaFree(c->d_counters); cudaFree(c->d_nacc);
     cudaFree(c->d_stage_text); cudaFree(c->d_stage_nn); cudaFree(c->d_stage_acc); cudaFree(c->d_stage_dst);
     cudaFree(c->dbg_counts);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
@@ -201,10 +197,8 @@ static int reset_heaps(uvg_ctx* c)
     UVG_CUDA(c, cudaMemcpyAsync(c->d_max_inc_batch, init.data(), Q * 4, cudaMemcpyHostToDevice, c->st));
     UVG_CUDA(c, cudaMemsetAsync(c->d_batch_id, 0xff, Q * 4, c->st));
     UVG_CUDA(c, cudaMemsetAsync(c->d_heap_n, 0, Q * 4, c->st));
-    UVG_CUDA(c, cudaMemsetAsync(c->d_qcount, 0, Q * 4, c->st));
     UVG_CUDA(c, cudaMemsetAsync(c->d_thr, 0, (size_t)c->n_qtiles * QTILE * sizeof(Threshold), c->st));
     UVG_CUDA(c, cudaMemsetAsync(c->d_heaps, 0, (size_t)Q * (c->K + 1) * sizeof(HeapItem), c->st));
-    UVG_CUDA(c, cudaMemsetAsync(c->d_surv_count, 0, 64, c->st));
     UVG_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 64, c->st));
     if (c->d_ever && c->ever_cap) UVG_CUDA(c, cudaMemsetAsync(c->d_ever, 0, c->ever_cap, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));                              // `init` goes out of scope
@@ -316,16 +310,13 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     UVG_CUDA(c, cudaMalloc(&c->d_heaps, (size_t)Q * (c->K + 1) * sizeof(HeapItem)));
     UVG_CUDA(c, cudaMalloc(&c->d_heap_n, Q * 4)); UVG_CUDA(c, cudaMalloc(&c->d_max_inc, Q * 4));
     UVG_CUDA(c, cudaMalloc(&c->d_batch_id, Q * 4)); UVG_CUDA(c, cudaMalloc(&c->d_max_inc_batch, Q * 4));
-    UVG_CUDA(c, cudaMalloc(&c->d_qcount, Q * 4)); UVG_CUDA(c, cudaMalloc(&c->d_qoffset, (Q + 1) * 4)); UVG_CUDA(c, cudaMalloc(&c->d_qcursor, Q * 4));
-    // survivor capacity: the first round keeps every pair (Q x first_round); later rounds keep ~K*ln(growth) per query
-    int64_t cap = c->prm.max_survivors > 0 ? c->prm.max_survivors : std::max<int64_t>((int64_t)Q * round_size_first(c->prm) * 2, 1 << 24);
-    cap = std::max<int64_t>(cap, (int64_t)Qp * GROUP);
-    c->surv_cap = cap;
-    UVG_CUDA(c, cudaMalloc(&c->d_surv, cap * sizeof(Survivor))); UVG_CUDA(c, cudaMalloc(&c->d_surv_ci, cap * 4));
-    UVG_CUDA(c, cudaMalloc(&c->d_bucket, cap * sizeof(Survivor) * c->world)); UVG_CUDA(c, cudaMalloc(&c->d_bucket_ci, cap * 4 * c->world));
-    if (c->world > 1) {
-        UVG_CUDA(c, cudaMalloc(&c->d_gather, cap * sizeof(Survivor) * c->world));
-        UVG_CUDA(c, cudaMalloc(&c->d_gather_ci, cap * 4 * c->world));
+    // dense score tile: rounds are capped so that n_query x round x 16 B stays within ~2 GiB
+    {
+        int64_t cap = round_size_max(c->prm);
+        const int64_t fit = ((int64_t)2 << 30) / ((int64_t)Q * 16) / (GROUP * RPL) * (GROUP * RPL);
+        cap = std::max<int64_t>(GROUP * RPL, std::min(cap, fit));
+        c->score_cap = cap;
+        UVG_CUDA(c, cudaMalloc(&c->d_scores, (size_t)Q * cap * sizeof(uint4)));
     }
     UVG_CUDA(c, cudaMemcpyAsync(c->d_qdata, qd.data(), n_chunk_total * sizeof(QChunk), cudaMemcpyHostToDevice, c->st));
     UVG_CUDA(c, cudaMemcpyAsync(c->d_cons_acgt, ca.data(), Wp * sizeof(uint4), cudaMemcpyHostToDevice, c->st));
@@ -507,8 +498,6 @@ extern "C" int64_t uvg_db_count(const uvg_ctx* c) { return c ? c->db_n : 0; }
 // =====================================================================================================================
 // search: rounds of K2 (pair counts -> survivors) and K3 (exact replay)
 // =====================================================================================================================
-struct WorkItem { int owner; int64_t ob, oe; };        // owner -1: every rank scores its tile; else only `owner` does
-
 static int event_pair(uvg_ctx* c, size_t idx, cudaEvent_t* a, cudaEvent_t* b)
 {
     while (c->pair_events.size() <= idx) {
@@ -520,101 +509,50 @@ static int event_pair(uvg_ctx* c, size_t idx, cudaEvent_t* a, cudaEvent_t* b)
     return UVG_OK;
 }
 
-// one scoring round over the local tile [lstart, lstart+cnt) whose nominal (per-rank) size is T
+static void fill_pair_params(uvg_ctx* c, PairParams& pp, int64_t lb, int64_t le)
+{
+    pp.db = c->d_db; pp.refamb = c->d_refamb; pp.qdata = c->d_qdata; pp.thr = c->d_thr;
+    pp.Wp = c->Wp; pp.n_chunks = c->n_chunks; pp.ambw = c->ambw; pp.n_qtiles = c->n_qtiles; pp.n_query = c->n_query;
+    pp.local_begin = lb; pp.local_end = le; pp.global_minus_local = 0;
+    pp.scores = c->d_scores; pp.score_stride = c->score_cap; pp.score_col0 = 0;
+    pp.early_abort = c->prm.early_abort; pp.work = c->d_counters + 2;
+}
+
+// one scoring round over the local tile [lstart, lstart+cnt): consensus stage, pair counts into the dense tile, replay.
+// Everything is asynchronous on the context's stream: there is no host synchronisation inside a search.
 static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t tile_global, int64_t round_first,
                      int64_t round_count, size_t* n_pair_events)
 {
-    std::vector<WorkItem> work;
-    work.push_back({c->world > 1 ? -1 : 0, 0, T});
-    unsigned long long* h = c->h_pinned;
-    while (!work.empty()) {
-        WorkItem it = work.front();
-        work.erase(work.begin());
-        const bool mine = it.owner < 0 || it.owner == c->rank;
-        const int64_t b = std::min(it.ob, cnt), e = std::min(it.oe, cnt);
-        PairParams pp{};
-        pp.db = c->d_db; pp.refamb = c->d_refamb; pp.qdata = c->d_qdata; pp.thr = c->d_thr;
-        pp.non_n = c->d_non_n; pp.c0 = c->d_c0; pp.ci = c->d_ci;
-        pp.Wp = c->Wp; pp.n_chunks = c->n_chunks; pp.ambw = c->ambw; pp.n_qtiles = c->n_qtiles; pp.n_query = c->n_query;
-        pp.local_begin = lstart + b; pp.local_end = lstart + e;
-        pp.global_minus_local = tile_global - lstart;
-        pp.surv = c->d_surv; pp.surv_ci = c->d_surv_ci; pp.surv_count = c->d_surv_count; pp.surv_cap = c->surv_cap;
-        pp.qcount = c->d_qcount; pp.early_abort = c->prm.early_abort; pp.dbg_counts = nullptr; pp.work = c->d_counters + 2;
-        if (mine && e > b) {
-            UVG_CUDA(c, launch_consensus(c->d_db, c->d_cons_acgt, c->d_cons_vo, c->Wp, c->prm.acgt_mode, pp.local_begin, pp.local_end,
-                                         c->d_c0, c->d_ci, c->st));
-            cudaEvent_t ea, eb;
-            int rc = event_pair(c, *n_pair_events, &ea, &eb);
-            if (rc) return rc;
-            UVG_CUDA(c, cudaEventRecord(ea, c->st));
-            UVG_CUDA(c, launch_paircount(pp, c->prm.acgt_mode, c->st));
-            UVG_CUDA(c, cudaEventRecord(eb, c->st));
-            ++*n_pair_events;
-            c->stats.pair_kernel_launches += 1; c->stats.other_kernel_launches += 1;
-        }
-        // ---- survivor counts (all ranks) ----
-        unsigned long long counts[64];
-        if (c->world > 1) {
-            if (g_nccl.AllGather(c->d_surv_count, c->d_gcounts, 1, ncclUint64, c->comm, c->st) != 0) UVG_FAIL(c, UVG_ENCCL, "ncclAllGather(counts) failed");
-            UVG_CUDA(c, cudaMemcpyAsync(h, c->d_gcounts, 8 * c->world, cudaMemcpyDeviceToHost, c->st));
-        } else {
-            UVG_CUDA(c, cudaMemcpyAsync(h, c->d_surv_count, 8, cudaMemcpyDeviceToHost, c->st));
-        }
-        UVG_CUDA(c, cudaStreamSynchronize(c->st));
-        unsigned long long mx = 0, total = 0;
-        for (int g = 0; g < c->world; ++g) { counts[g] = h[g]; mx = std::max(mx, counts[g]); total += counts[g]; }
-        if (mx > (unsigned long long)c->surv_cap) {
-            // survivor buffer overflow: redo this piece in smaller, globally contiguous pieces (thresholds refresh in between)
-            UVG_CUDA(c, cudaMemsetAsync(c->d_surv_count, 0, 8, c->st));
-            UVG_CUDA(c, cudaMemsetAsync(c->d_qcount, 0, c->n_query * 4, c->st));
-            ++c->stats.n_overflow_splits;
-            if (it.owner < 0) {
-                for (int g = c->world - 1; g >= 0; --g) work.insert(work.begin(), WorkItem{g, it.ob, it.oe});
-            } else {
-                if (it.oe - it.ob <= GROUP) UVG_FAIL(c, UVG_ENOMEM, "survivor buffer too small for %d queries", c->n_query);
-                int64_t mid = it.ob + ((it.oe - it.ob) / 2 + GROUP - 1) / GROUP * GROUP;
-                work.insert(work.begin(), WorkItem{it.owner, mid, it.oe});
-                work.insert(work.begin(), WorkItem{it.owner, it.ob, mid});
-            }
-            continue;
-        }
-        c->stats.n_survivors += (int64_t)total;
-        if (total == 0) continue;
-        // ---- gather (sharded) + bucket by query + replay ----
-        ReplayParams rp{};
-        rp.bucketed = c->d_bucket; rp.bucketed_ci = c->d_bucket_ci;
-        rp.qcount = c->d_qcount; rp.qoffset = c->d_qoffset; rp.qcursor = c->d_qcursor;
-        rp.heaps = c->d_heaps; rp.heap_n = c->d_heap_n; rp.max_inc = c->d_max_inc;
-        rp.batch_id = c->d_batch_id; rp.max_inc_batch = c->d_max_inc_batch; rp.thr = c->d_thr;
-        rp.ever_best = c->d_ever; rp.counters = c->d_counters;
-        rp.n_query = c->n_query; rp.K = c->K; rp.acgt_mode = c->prm.acgt_mode; rp.pool = c->prm.pool;
-        rp.round_first = (int32_t)round_first; rp.round_count = (int32_t)round_count;
-        UVG_CUDA(c, cudaEventRecord(c->ev_c, c->st));
-        if (c->world > 1) {
-            const size_t m = (size_t)mx;
-            if (g_nccl.AllGather(c->d_surv, c->d_gather, m * sizeof(Survivor), ncclUint8, c->comm, c->st) != 0) UVG_FAIL(c, UVG_ENCCL, "ncclAllGather(survivors) failed");
-            if (g_nccl.AllGather(c->d_surv_ci, c->d_gather_ci, m * 4, ncclUint8, c->comm, c->st) != 0) UVG_FAIL(c, UVG_ENCCL, "ncclAllGather(ci) failed");
-            UVG_CUDA(c, cudaMemsetAsync(c->d_qcount, 0, c->n_query * 4, c->st));
-            for (int g = 0; g < c->world; ++g)
-                UVG_CUDA(c, launch_bucket_count(c->d_gather + g * m, (int64_t)counts[g], c->d_qcount, c->st));
-            UVG_CUDA(c, launch_bucket_scan(c->d_qcount, c->d_qoffset, c->d_qcursor, c->n_query, c->st));
-            for (int g = 0; g < c->world; ++g)
-                UVG_CUDA(c, launch_bucket_scatter(c->d_gather + g * m, c->d_gather_ci + g * m, (int64_t)counts[g], c->d_qoffset, c->d_qcursor,
-                                                  c->d_bucket, c->d_bucket_ci, c->st));
-            c->stats.other_kernel_launches += 2 * c->world + 1;
-        } else {
-            UVG_CUDA(c, launch_bucket_scan(c->d_qcount, c->d_qoffset, c->d_qcursor, c->n_query, c->st));
-            UVG_CUDA(c, launch_bucket_scatter(c->d_surv, c->d_surv_ci, (int64_t)total, c->d_qoffset, c->d_qcursor, c->d_bucket, c->d_bucket_ci, c->st));
-            c->stats.other_kernel_launches += 2;
-        }
-        UVG_CUDA(c, launch_replay_only(rp, c->st));
-        c->stats.other_kernel_launches += 1;
-        UVG_CUDA(c, cudaMemsetAsync(c->d_surv_count, 0, 8, c->st));
-        UVG_CUDA(c, cudaEventRecord(c->ev_d, c->st));
-        UVG_CUDA(c, cudaEventSynchronize(c->ev_d));
-        float ms = 0; cudaEventElapsedTime(&ms, c->ev_c, c->ev_d);
-        c->stats.replay_ms += ms;
-    }
+    (void)T; (void)round_first; (void)round_count;
+    if (c->world > 1) UVG_FAIL(c, UVG_ESTATE, "sharded search is not wired to the dense score tile yet");
+    if (cnt <= 0) return UVG_OK;
+    PairParams pp{};
+    fill_pair_params(c, pp, lstart, lstart + cnt);
+    UVG_CUDA(c, launch_consensus(c->d_db, c->d_cons_acgt, c->d_cons_vo, c->Wp, c->prm.acgt_mode, pp.local_begin, pp.local_end,
+                                 c->d_c0, c->d_ci, c->st));
+    cudaEvent_t ea, eb;
+    int rc = event_pair(c, *n_pair_events, &ea, &eb);
+    if (rc) return rc;
+    UVG_CUDA(c, cudaEventRecord(ea, c->st));
+    UVG_CUDA(c, launch_paircount(pp, c->prm.acgt_mode, c->st));
+    UVG_CUDA(c, cudaEventRecord(eb, c->st));
+    ++*n_pair_events;
+    ReplayParams rp{};
+    rp.scores = c->d_scores; rp.row_stride = c->score_cap;
+    rp.nseg = 1; rp.seg_stride = (int32_t)cnt; rp.seg_cnt[0] = (int32_t)cnt; rp.seg_global[0] = tile_global;
+    rp.non_n = c->d_non_n + lstart; rp.c0 = c->d_c0 + lstart; rp.ci = c->d_ci + lstart;
+    rp.heaps = c->d_heaps; rp.heap_n = c->d_heap_n; rp.max_inc = c->d_max_inc;
+    rp.batch_id = c->d_batch_id; rp.max_inc_batch = c->d_max_inc_batch; rp.thr = c->d_thr;
+    rp.ever_best = c->d_ever; rp.counters = c->d_counters;
+    rp.q_first = 0; rp.n_query = c->n_query; rp.K = c->K; rp.acgt_mode = c->prm.acgt_mode; rp.pool = c->prm.pool;
+    cudaEvent_t ra, rb;
+    rc = event_pair(c, *n_pair_events, &ra, &rb);
+    if (rc) return rc;
+    UVG_CUDA(c, cudaEventRecord(ra, c->st));
+    UVG_CUDA(c, launch_replay(rp, c->st));
+    UVG_CUDA(c, cudaEventRecord(rb, c->st));
+    ++*n_pair_events;
+    c->stats.pair_kernel_launches += 1; c->stats.other_kernel_launches += 2;
     return UVG_OK;
 }
 
@@ -625,7 +563,7 @@ extern "C" int uvg_search(uvg_ctx* c)
     if (c->n_query == 0) UVG_FAIL(c, UVG_ESTATE, "uvg_search: no queries set");
     if (c->world > 1 && !c->comm) UVG_FAIL(c, UVG_ESTATE, "uvg_search: sharded context without uvg_nccl_init");
     if (c->world > 1 && c->global_total < 0) UVG_FAIL(c, UVG_ESTATE, "uvg_search: sharded context without uvg_set_global_count");
-    const int32_t mx = round_size_max(c->prm);
+    const int32_t mx = (int32_t)std::min<int64_t>(round_size_max(c->prm), c->score_cap);
     size_t n_ev = 0;
     c->heaps_cached = false;
     c->stats.pair_kernel_ms = 0; c->stats.replay_ms = 0;
@@ -663,7 +601,10 @@ extern "C" int uvg_search(uvg_ctx* c)
     UVG_CUDA(c, cudaEventSynchronize(c->ev_b));
     float ms = 0; cudaEventElapsedTime(&ms, c->ev_a, c->ev_b);
     c->stats.search_ms = ms;
-    for (size_t i = 0; i < n_ev; ++i) { float t = 0; cudaEventElapsedTime(&t, c->pair_events[i].first, c->pair_events[i].second); c->stats.pair_kernel_ms += t; }
+    for (size_t i = 0; i < n_ev; ++i) {           // events alternate: pair-count launch, replay launch
+        float t = 0; cudaEventElapsedTime(&t, c->pair_events[i].first, c->pair_events[i].second);
+        if (i % 2 == 0) c->stats.pair_kernel_ms += t; else c->stats.replay_ms += t;
+    }
     return UVG_OK;
 }
 
@@ -851,27 +792,14 @@ extern "C" int uvg_debug_pair_counts(uvg_ctx* c, int64_t first, int64_t n, int32
 {
     if (!c || !out || first < 0 || n < 1) { if (c) c->err = "uvg_debug_pair_counts: bad arguments"; return UVG_EINVAL; }
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
-    if (c->n_query == 0 || first + n > c->db_n) UVG_FAIL(c, UVG_ESTATE, "uvg_debug_pair_counts: range not resident or no queries");
-    int32_t* d_out = nullptr; Threshold* d_thr0 = nullptr;
-    const size_t cnt = (size_t)c->n_query * n * 4;
-    UVG_CUDA(c, cudaMalloc(&d_out, cnt * 4));
-    UVG_CUDA(c, cudaMalloc(&d_thr0, (size_t)c->n_qtiles * QTILE * sizeof(Threshold)));
-    UVG_CUDA(c, cudaMemsetAsync(d_out, 0, cnt * 4, c->st));
-    UVG_CUDA(c, cudaMemsetAsync(d_thr0, 0, (size_t)c->n_qtiles * QTILE * sizeof(Threshold), c->st));
+    if (c->n_query == 0 || first + n > c->db_n || n > c->score_cap) UVG_FAIL(c, UVG_ESTATE, "uvg_debug_pair_counts: range not resident, too long, or no queries");
     PairParams pp{};
-    pp.db = c->d_db; pp.refamb = c->d_refamb; pp.qdata = c->d_qdata; pp.thr = d_thr0;
-    pp.non_n = c->d_non_n; pp.c0 = c->d_c0; pp.ci = c->d_ci;
-    pp.Wp = c->Wp; pp.n_chunks = c->n_chunks; pp.ambw = c->ambw; pp.n_qtiles = c->n_qtiles; pp.n_query = c->n_query;
-    pp.local_begin = first; pp.local_end = first + n; pp.global_minus_local = 0;
-    pp.surv = c->d_surv; pp.surv_ci = c->d_surv_ci; pp.surv_count = c->d_surv_count; pp.surv_cap = 0;
-    pp.qcount = c->d_qcount; pp.early_abort = 0; pp.dbg_counts = d_out; pp.work = nullptr;
-    cudaError_t e = launch_paircount(pp, c->prm.acgt_mode, c->st);
-    if (e == cudaSuccess) e = cudaMemsetAsync(c->d_surv_count, 0, 8, c->st);
-    if (e == cudaSuccess) e = cudaMemsetAsync(c->d_qcount, 0, c->n_query * 4, c->st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, cnt * 4, cudaMemcpyDeviceToHost, c->st);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(c->st);
-    cudaFree(d_out); cudaFree(d_thr0);
-    UVG_CUDA(c, e);
+    fill_pair_params(c, pp, first, first + n);
+    pp.early_abort = 0; pp.work = nullptr;
+    UVG_CUDA(c, launch_paircount(pp, c->prm.acgt_mode, c->st));
+    UVG_CUDA(c, cudaMemcpy2DAsync(out, (size_t)n * 16, c->d_scores, (size_t)c->score_cap * 16, (size_t)n * 16, (size_t)c->n_query,
+                                  cudaMemcpyDeviceToHost, c->st));
+    UVG_CUDA(c, cudaStreamSynchronize(c->st));
     return UVG_OK;
 }
 

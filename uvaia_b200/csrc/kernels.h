@@ -23,22 +23,25 @@ cudaError_t launch_paircount(const PairParams& p, int acgt_mode, cudaStream_t st
 cudaError_t paircount_setup();       // opt in to the dynamic shared memory size
 
 // ---- replay.cu (K3) ----
+constexpr int MAX_SEG = 16;
 struct ReplayParams {
-    const Survivor* bucketed; const int32_t* bucketed_ci;             // survivors of the round grouped by query
-    int32_t* qcount; int32_t* qoffset; int32_t* qcursor;              // [n_query] (+1 for qoffset)
-    HeapItem* heaps; int32_t* heap_n; int32_t* max_inc;               // [n_query][K+1], [n_query], [n_query]
+    const uint4* scores;          // dense counts of the round: row = query (q_first + block), column = position in the round
+    int64_t row_stride;           // uint4 elements between rows
+    // a row is nseg segments of seg_stride positions (one per source rank); segment g holds seg_cnt[g] references whose
+    // global ordinals start at seg_global[g].  Single GPU: one segment.
+    int32_t nseg, seg_stride;
+    int32_t seg_cnt[MAX_SEG];
+    int64_t seg_global[MAX_SEG];
+    const int32_t* non_n; const int32_t* c0; const int32_t* ci;      // per position of the round
+    HeapItem* heaps; int32_t* heap_n; int32_t* max_inc;               // [n_query_total][K+1], [..], [..]
     int32_t* batch_id; int32_t* max_inc_batch;                        // H1 bookkeeping per query
     Threshold* thr;                                                   // [n_qtiles*QTILE]
     uint8_t* ever_best;                                               // per GLOBAL ordinal
     unsigned long long* counters;                                     // [0]=admitted, [1]=H1 flags
-    int32_t n_query, K, acgt_mode, pool;
-    int32_t round_first, round_count;                                 // global ordinal range of the round
+    int32_t q_first, n_query;                                         // queries replayed by this launch (rows)
+    int32_t K, acgt_mode, pool;
 };
-cudaError_t launch_bucket_count(const Survivor* seg, int64_t n, int32_t* qcount, cudaStream_t st);
-cudaError_t launch_bucket_scan(const int32_t* qcount, int32_t* qoffset, int32_t* qcursor, int n_query, cudaStream_t st);
-cudaError_t launch_bucket_scatter(const Survivor* seg, const int32_t* seg_ci, int64_t n, const int32_t* qoffset, int32_t* qcursor,
-                                  Survivor* out, int32_t* out_ci, cudaStream_t st);
-cudaError_t launch_replay_only(const ReplayParams& p, cudaStream_t st);
+cudaError_t launch_replay(const ReplayParams& p, cudaStream_t st);
 cudaError_t replay_setup(int K);
 
 }  // namespace uvg

@@ -55,16 +55,6 @@ __device__ __forceinline__ uint32_t plane_differ(const uint4& r, const uint4& q)
     return (r.x ^ q.x) | (r.y ^ q.y) | (r.z ^ q.z) | (r.w ^ q.w);
 }
 
-// strictly better than the threshold item in the order of compare_q_item_score (src/min_heap.c:41-47)
-__device__ __forceinline__ bool lex_greater(const int32_t (&s)[6], const Threshold& t)
-{
-#pragma unroll
-    for (int i = 0; i < 6; ++i) {
-        if (s[i] != t.s[i]) return s[i] > t.s[i];
-    }
-    return false;
-}
-
 // One pipeline stage: a query chunk (64 queries x WC words) and the same WC words of the block's 64 references.
 struct __align__(16) Stage {
     QChunk q;
@@ -80,14 +70,6 @@ __device__ __forceinline__ uint32_t imad(uint32_t a, uint32_t b, uint32_t c)
     uint32_t d;
     asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
     return d;
-}
-
-__device__ __forceinline__ bool survives(const int32_t (&sc)[6], int32_t D, const Threshold& t)
-{
-    if (!t.full) return true;
-    if (D >= t.dmax) return false;
-    if (sc[0] < t.bar[D >> (t.full - 1)]) return false;
-    return lex_greater(sc, t);
 }
 
 // LONG = alignments of 65,536 columns or more (counters may exceed 16 bits): packed counters are flushed into
@@ -241,60 +223,29 @@ __global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams 
     if (c < p.n_chunks) {
         // whole block aborted: drain the bulk copies still in flight before the shared memory is released
         for (int cc = c + 1; cc < p.n_chunks && cc < c + STAGES; ++cc) mbar_wait(full + cc % STAGES, (uint32_t)((cc / STAGES) & 1));
-        return;
     }
 
-    // ---- epilogue: 6-tuple, staircase test, warp-aggregated survivor append ----
-    const int64_t n_launch = p.local_end - p.local_begin;
+    // ---- epilogue: the four counts of every pair go to the dense score tile of the round (coalesced 512 B per warp
+    // and query); the replay kernel assembles the 6-tuple (src/nearest.c:466-470, 499-501) for the pairs it admits.
+    // Aborted pairs get a sentinel whose mismatch count can never pass the admission test.
 #pragma unroll
     for (int g = 0; g < RPL; ++g) {
-        const int32_t non_n = in_range[g] ? p.non_n[local[g]] : 0;
-        const int32_t c0 = in_range[g] ? p.c0[local[g]] : 0;
-        const int32_t ci = in_range[g] ? p.ci[local[g]] : 0;
+        if (!in_range[g]) continue;
+        uint4* out = p.scores + p.score_col0 + (local[g] - p.local_begin);
 #pragma unroll
         for (int j = 0; j < QPW; ++j) {
             const int q = qt * QTILE + q0 + j;
-            const int32_t cP = cntP(g, j), cV = cntV(g, j), cY = cntY(g, j), cE = cntE(g, j);
-            int32_t sc[6];
-            int32_t D;
-            if (MODE == 0) {
-                const int32_t A = cP - cY;
-                sc[0] = A; sc[1] = A + cE; sc[2] = cP; sc[3] = cV; sc[4] = A - c0; sc[5] = non_n;
-                D = cV - A;
+            if (q >= p.n_query) continue;
+            uint4 v;
+            if (warp_dead) {
+                v = (MODE == 0) ? make_uint4(0u, 0u, 0u, 0x7fffffffu) : make_uint4(0u, 0x7fffffffu, 0u, 0u);
+            } else if (MODE == 0) {
+                const int32_t A = cntP(g, j) - cntY(g, j);
+                v = make_uint4((uint32_t)A, (uint32_t)(A + cntE(g, j)), (uint32_t)cntP(g, j), (uint32_t)cntV(g, j));
             } else {
-                const int32_t M = cV - cP;
-                sc[0] = cP; sc[1] = cV; sc[2] = cP - c0; sc[3] = non_n; sc[4] = M - cY; sc[5] = cY;
-                D = M;
+                v = make_uint4((uint32_t)cntP(g, j), (uint32_t)cntV(g, j), (uint32_t)cntY(g, j), 0u);
             }
-            bool pass = false;
-            if (in_range[g] && q < p.n_query && !warp_dead) {
-                pass = survives(sc, D, s_thr[q0 + j]);
-                if (p.dbg_counts) {
-                    int32_t* o = p.dbg_counts + ((size_t)q * n_launch + (local[g] - p.local_begin)) * 4;
-                    if (MODE == 0) { o[0] = sc[0]; o[1] = sc[1]; o[2] = sc[2]; o[3] = sc[3]; }
-                    else { o[0] = cP; o[1] = cV; o[2] = cY; o[3] = 0; }
-                }
-            }
-            const uint32_t m = __ballot_sync(0xffffffffu, pass);
-            if (m) {
-                unsigned long long base = 0;
-                if (lane == 0) {
-                    base = atomicAdd(p.surv_count, (unsigned long long)__popc(m));
-                    atomicAdd(p.qcount + q, __popc(m));
-                }
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (pass) {
-                    const unsigned long long slot = base + __popc(m & ((1u << lane) - 1u));
-                    if (slot < (unsigned long long)p.surv_cap) {
-                        Survivor sv;
-                        sv.q = q; sv.r = (int32_t)(local[g] + p.global_minus_local);
-#pragma unroll
-                        for (int k = 0; k < 6; ++k) sv.s[k] = sc[k];
-                        p.surv[slot] = sv;
-                        p.surv_ci[slot] = ci;
-                    }
-                }
-            }
+            out[(size_t)q * p.score_stride] = v;
         }
     }
 }

@@ -1,13 +1,13 @@
-// K3: exact replay of the reference's per-query sequential admission over the survivors of one scoring round.
+// K3: exact replay of the reference's per-query sequential admission over the dense score tile of one round.
 // Replaces heap_insert / heap_bubble_up / heap_bubble_down (src/min_heap.c:93-147) and the max_incompatible update
 // of queue_update_min_heaps (src/nearest.c:488, 504-508 / 450, 472-475).  The reference admits a pair only if
 //   D = valid - acgt  <  heap.max_incompatible      (a limit that is re-derived from the worst kept item after every
 //                                                    insertion and can go UP as well as down, README.md:337-342)
 // and then only if its 6-tuple is strictly better than the heap root, so the result depends on the order in which
-// references arrive.  The pair-count kernel therefore only filters with a STALE root (safe: the root never gets
-// worse) and this kernel re-applies the exact rule to the survivors of each query in file order.
-// One thread block per query: the heap lives in shared memory, survivors are ordered by a direct-address window
-// (at most one survivor per (query, reference)), and one thread performs the sequential admission.
+// references arrive: a parallel top-k is not bit-exact.  Here the pair-count kernel stores the four counts of EVERY
+// pair of the round (16 B per pair, coalesced; a few ms of HBM traffic per million references), and one thread block
+// per query streams its row in file order: all threads pre-filter 1024 references at a time with a bound that is
+// safe for the whole window (Threshold in common.cuh), then one thread applies the exact rule to the few candidates.
 #include "common.cuh"
 #include "kernels.h"
 #include <algorithm>
@@ -15,8 +15,7 @@
 namespace uvg {
 
 constexpr int RP_THREADS = 128;
-constexpr int RP_WIN = 1024;                 // references per ordering window
-constexpr int RP_MAXWIN_WORDS = 256;         // occupancy bitmap: up to 8192 windows = 8.4M references per round
+constexpr int RP_WIN = 1024;                 // references per window
 constexpr int RP_HEAP_SMEM_ITEMS = 4096;     // heaps up to this many slots live in shared memory
 
 __device__ __forceinline__ bool item_less(const HeapItem& x, const HeapItem& y)
@@ -47,169 +46,135 @@ __device__ __forceinline__ void heap_up(HeapItem* a, int i)
         i = par;
     }
 }
-
-__global__ void __launch_bounds__(1024) k_bucket_scan(const int32_t* __restrict__ qcount, int32_t* __restrict__ qoffset,
-                                                      int32_t* __restrict__ qcursor, int n_query)
+__device__ __forceinline__ int item_mismatch(const HeapItem& it, int acgt_mode)
 {
-    __shared__ int s_warp[32];
-    __shared__ int s_run;
-    if (threadIdx.x == 0) s_run = 0;
-    __syncthreads();
-    for (int base = 0; base < n_query; base += blockDim.x) {
-        int i = base + threadIdx.x;
-        int a = (i < n_query) ? qcount[i] : 0;
-        int incl = a;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, o); if ((int)(threadIdx.x & 31) >= o) incl += t; }
-        if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = incl;
-        __syncthreads();
-        if (threadIdx.x < 32) {
-            int v = s_warp[threadIdx.x], inc2 = v;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, inc2, o); if ((int)threadIdx.x >= o) inc2 += t; }
-            s_warp[threadIdx.x] = inc2 - v;
-        }
-        __syncthreads();
-        int excl = incl - a + s_warp[threadIdx.x >> 5];
-        int run = s_run;
-        if (i < n_query) { qoffset[i] = run + excl; qcursor[i] = 0; }
-        __syncthreads();
-        if (threadIdx.x == blockDim.x - 1) s_run = run + excl + a;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) qoffset[n_query] = s_run;
+    return acgt_mode ? (it.s[1] - it.s[0]) : (it.s[3] - it.s[0]);
 }
 
-__global__ void __launch_bounds__(256) k_bucket_scatter(const Survivor* __restrict__ surv, const int32_t* __restrict__ surv_ci,
-                                                        int64_t n, const int32_t* __restrict__ qoffset, int32_t* __restrict__ qcursor,
-                                                        Survivor* __restrict__ out, int32_t* __restrict__ out_ci)
-{
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        Survivor s = surv[i];
-        int pos = qoffset[s.q] + atomicAdd(qcursor + s.q, 1);
-        out[pos] = s;
-        out_ci[pos] = surv_ci[i];
-    }
-}
+struct RpState { int n, max_inc, dmax, root_s0; };
 
 __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int heap_in_smem)
 {
     extern __shared__ __align__(16) uint8_t smem[];
-    Survivor* s_rec = reinterpret_cast<Survivor*>(smem);                       // RP_WIN
-    int32_t* s_ci = reinterpret_cast<int32_t*>(smem + RP_WIN * sizeof(Survivor));
-    int32_t* s_slot = s_ci + RP_WIN;                                           // RP_WIN
-    uint32_t* s_occ = reinterpret_cast<uint32_t*>(s_slot + RP_WIN);            // RP_MAXWIN_WORDS
-    int32_t* s_misc = reinterpret_cast<int32_t*>(s_occ + RP_MAXWIN_WORDS);     // 64 ints
-    HeapItem* s_heap = reinterpret_cast<HeapItem*>(s_misc + 64);
+    uint4* s_sc = reinterpret_cast<uint4*>(smem);                                  // RP_WIN raw counts
+    uint32_t* s_mask = reinterpret_cast<uint32_t*>(smem + RP_WIN * sizeof(uint4)); // RP_WIN / 32 candidate bits
+    int32_t* s_misc = reinterpret_cast<int32_t*>(s_mask + RP_WIN / 32);            // 32 ints
+    HeapItem* s_heap = reinterpret_cast<HeapItem*>(s_misc + 32);
+    RpState* st = reinterpret_cast<RpState*>(s_misc);
 
-    const int q = blockIdx.x;
-    const int cnt = p.qcount[q];
-    if (cnt == 0) return;
-    const int off = p.qoffset[q];
-    const int K = p.K;
+    const int q = p.q_first + blockIdx.x;                 // global query index
+    const int K = p.K, acgt = p.acgt_mode;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     HeapItem* gheap = p.heaps + (size_t)q * (K + 1);
     HeapItem* a = heap_in_smem ? s_heap : gheap;
-    int n = p.heap_n[q];
-    if (heap_in_smem) for (int i = 1 + threadIdx.x; i <= n; i += blockDim.x) a[i] = gheap[i];
-    const int nwin = (p.round_count + RP_WIN - 1) / RP_WIN;
-    for (int i = threadIdx.x; i < RP_MAXWIN_WORDS; i += blockDim.x) s_occ[i] = 0;
-    __syncthreads();
-    for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
-        int w = (p.bucketed[off + i].r - p.round_first) / RP_WIN;
-        atomicOr(s_occ + (w >> 5), 1u << (w & 31));
+    const uint4* row = p.scores + (size_t)blockIdx.x * p.row_stride;
+    {
+        const int n0 = p.heap_n[q];
+        if (heap_in_smem) for (int i = 1 + threadIdx.x; i <= n0; i += blockDim.x) a[i] = gheap[i];
+        if (threadIdx.x == 0) {
+            st->n = n0; st->max_inc = p.max_inc[q];
+            const Threshold& t = p.thr[q];
+            st->dmax = t.full ? t.dmax : 0x7fffffff;
+            st->root_s0 = t.full ? t.s[0] : -0x7fffffff;
+        }
     }
-    // sequential state (thread 0)
-    int max_inc = p.max_inc[q], batch_id = p.batch_id[q], max_inc_batch = p.max_inc_batch[q];
+    int batch_id = p.batch_id[q], max_inc_batch = p.max_inc_batch[q];      // used by thread 0 only
     int admitted = 0, h1 = 0;
     __syncthreads();
-    for (int w = 0; w < nwin; ++w) {
-        if (!((s_occ[w >> 5] >> (w & 31)) & 1u)) continue;                      // uniform across the block
-        const int w0 = p.round_first + w * RP_WIN;
-        for (int i = threadIdx.x; i < RP_WIN; i += blockDim.x) s_slot[i] = -1;
-        __syncthreads();
-        for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
-            int d = p.bucketed[off + i].r - w0;
-            if (d >= 0 && d < RP_WIN) s_slot[d] = i;
-        }
-        __syncthreads();
-        // ordered compaction: thread t owns slots [t*8, t*8+8)
-        constexpr int PER = RP_WIN / RP_THREADS;
-        int mine = 0;
+
+    const int total = p.nseg * p.seg_stride;
+    for (int w0 = 0; w0 < total; w0 += RP_WIN) {
+        // ---- parallel part: stage the window and flag candidates with a bound that holds for the whole window ----
+        const int dmax = st->dmax, root_s0 = st->root_s0;
+        bool any_valid = false;
 #pragma unroll
-        for (int k = 0; k < PER; ++k) mine += (s_slot[threadIdx.x * PER + k] >= 0);
-        int incl = mine;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, o); if ((int)(threadIdx.x & 31) >= o) incl += t; }
-        if ((threadIdx.x & 31) == 31) s_misc[threadIdx.x >> 5] = incl;
-        __syncthreads();
-        int before = incl - mine;
-        for (int k = 0; k < (int)(threadIdx.x >> 5); ++k) before += s_misc[k];
-        int total = 0;
-        for (int k = 0; k < RP_THREADS / 32; ++k) total += s_misc[k];
-#pragma unroll
-        for (int k = 0; k < PER; ++k) {
-            int i = s_slot[threadIdx.x * PER + k];
-            if (i >= 0) { s_rec[before] = p.bucketed[off + i]; s_ci[before] = p.bucketed_ci[off + i]; ++before; }
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            for (int t = 0; t < total; ++t) {
-                const Survivor& sv = s_rec[t];
-                const int b = sv.r / p.pool;
-                if (b != batch_id) { batch_id = b; max_inc_batch = max_inc; }
-                const int D = p.acgt_mode ? (sv.s[1] - sv.s[0]) : (sv.s[3] - sv.s[0]);
-                if (D >= max_inc) continue;                                     // nearest.c:488-496 / 450-460 (closed form)
-                HeapItem it;
-#pragma unroll
-                for (int k = 0; k < 6; ++k) it.s[k] = sv.s[k];
-                it.r = sv.r; it.pad = 0;
-                if (n == K) {                                                   // heap_insert, min_heap.c:95-106
-                    if (!item_less(a[1], it)) continue;
-                    a[1] = it;
-                    heap_down(a, n, 1);
-                } else {                                                        // min_heap.c:108-116
-                    ++n;
-                    a[n] = it;
-                    heap_up(a, n);
+        for (int k = 0; k < RP_WIN / RP_THREADS; ++k) {
+            const int i = k * RP_THREADS + threadIdx.x, pos = w0 + i;
+            bool cand = false;
+            if (pos < total) {
+                const int g = pos / p.seg_stride, within = pos - g * p.seg_stride;
+                if (within < p.seg_cnt[g]) {
+                    const uint4 sc = row[pos];
+                    s_sc[i] = sc;
+                    const int D = acgt ? (int)(sc.y - sc.x) : (int)(sc.w - sc.x);
+                    cand = (D >= 0) && (D < dmax) && ((int)sc.x >= root_s0);
+                    any_valid = true;
                 }
-                ++admitted;
-                p.ever_best[sv.r] = 1;                                          // is_best, nearest.c:505
-                if (s_ci[t] >= max_inc_batch) ++h1;                             // hazard H1 (necessary condition)
-                if (n == K) max_inc = p.acgt_mode ? (a[1].s[1] - a[1].s[0] + 1) : (a[1].s[3] - a[1].s[0] + 1);   // :475 / :508
+            }
+            const uint32_t m = __ballot_sync(0xffffffffu, cand);
+            if (lane == 0) s_mask[k * (RP_THREADS / 32) + warp] = m;
+        }
+        if (!__syncthreads_or(any_valid ? 1 : 0)) continue;      // padding between segments
+        // ---- sequential part: exact admission in file order ----
+        if (threadIdx.x == 0) {
+            int n = st->n, max_inc = st->max_inc;
+            bool changed = false;
+            for (int mw = 0; mw < RP_WIN / 32; ++mw) {
+                uint32_t m = s_mask[mw];
+                while (m) {
+                    const int b = __ffs(m) - 1;
+                    m &= m - 1;
+                    const int i = mw * 32 + b, pos = w0 + i;
+                    const uint4 sc = s_sc[i];
+                    const int D = acgt ? (int)(sc.y - sc.x) : (int)(sc.w - sc.x);
+                    const int g = pos / p.seg_stride, within = pos - g * p.seg_stride;
+                    const int r = (int)(p.seg_global[g] + within);
+                    const int bt = r / p.pool;
+                    if (bt != batch_id) { batch_id = bt; max_inc_batch = max_inc; }
+                    if (D >= max_inc) continue;                                     // nearest.c:488-496 / 450-460 (closed form)
+                    HeapItem it;
+                    const int c0 = p.c0[pos], nn = p.non_n[pos];
+                    if (!acgt) { it.s[0] = sc.x; it.s[1] = sc.y; it.s[2] = sc.z; it.s[3] = sc.w; it.s[4] = (int)sc.x - c0; it.s[5] = nn; }
+                    else { it.s[0] = sc.x; it.s[1] = sc.y; it.s[2] = (int)sc.x - c0; it.s[3] = nn; it.s[4] = D - (int)sc.z; it.s[5] = sc.z; }
+                    it.r = r; it.pad = 0;
+                    if (n == K) {                                                   // heap_insert, min_heap.c:95-106
+                        if (!item_less(a[1], it)) continue;
+                        a[1] = it;
+                        heap_down(a, n, 1);
+                    } else {                                                        // min_heap.c:108-116
+                        ++n;
+                        a[n] = it;
+                        heap_up(a, n);
+                    }
+                    ++admitted;
+                    changed = true;
+                    p.ever_best[r] = 1;                                             // is_best, nearest.c:505
+                    if (p.ci[pos] >= max_inc_batch) ++h1;                           // hazard H1 (necessary condition)
+                    if (n == K) max_inc = item_mismatch(a[1], acgt) + 1;            // nearest.c:475 / :508
+                }
+            }
+            st->n = n; st->max_inc = max_inc;
+            if (changed && n == K) {
+                int dm = 0;
+                for (int i = 1; i <= n; ++i) dm = max(dm, item_mismatch(a[i], acgt));
+                st->dmax = dm + 1; st->root_s0 = a[1].s[0];
             }
         }
         __syncthreads();
     }
+
+    const int n = st->n;
     if (threadIdx.x == 0) {
-        s_misc[40] = n;
-        p.heap_n[q] = n; p.max_inc[q] = max_inc; p.batch_id[q] = batch_id; p.max_inc_batch[q] = max_inc_batch;
-        p.qcount[q] = 0;
+        p.heap_n[q] = n; p.max_inc[q] = st->max_inc; p.batch_id[q] = batch_id; p.max_inc_batch[q] = max_inc_batch;
         if (admitted) atomicAdd(p.counters + 0, (unsigned long long)admitted);
         if (h1) atomicAdd(p.counters + 1, (unsigned long long)h1);
     }
-    __syncthreads();
-    n = s_misc[40];
     if (n == K) {
         // threshold snapshot for the next rounds: heap root + admission staircase (see Threshold in common.cuh)
         int dm = 0;
-        for (int i = 1 + threadIdx.x; i <= n; i += blockDim.x) {
-            const int d = p.acgt_mode ? (a[i].s[1] - a[i].s[0]) : (a[i].s[3] - a[i].s[0]);
-            dm = max(dm, d);
-        }
+        for (int i = 1 + threadIdx.x; i <= n; i += blockDim.x) dm = max(dm, item_mismatch(a[i], acgt));
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) dm = max(dm, __shfl_xor_sync(0xffffffffu, dm, o));
-        if ((threadIdx.x & 31) == 0) s_misc[48 + (threadIdx.x >> 5)] = dm;
+        if (lane == 0) s_misc[16 + warp] = dm;
         __syncthreads();
-        for (int k = 0; k < RP_THREADS / 32; ++k) dm = max(dm, s_misc[48 + k]);
+        for (int k = 0; k < RP_THREADS / 32; ++k) dm = max(dm, s_misc[16 + k]);
         int sh = 0;
         while ((dm >> sh) >= NBAR) ++sh;
         if (threadIdx.x < NBAR) {
             const int lo = (int)threadIdx.x << sh;
             int mn = 0x7fffffff;
-            for (int i = 1; i <= n; ++i) {
-                const int d = p.acgt_mode ? (a[i].s[1] - a[i].s[0]) : (a[i].s[3] - a[i].s[0]);
-                if (d >= lo) mn = min(mn, a[i].s[0]);
-            }
+            for (int i = 1; i <= n; ++i)
+                if (item_mismatch(a[i], acgt) >= lo) mn = min(mn, a[i].s[0]);
             p.thr[q].bar[threadIdx.x] = mn;
         }
         if (threadIdx.x == 0) {
@@ -224,7 +189,7 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
 
 static size_t replay_smem_bytes(int K, int* in_smem)
 {
-    size_t fixed = RP_WIN * sizeof(Survivor) + RP_WIN * 4 * 2 + RP_MAXWIN_WORDS * 4 + 64 * 4;
+    size_t fixed = RP_WIN * sizeof(uint4) + RP_WIN / 32 * 4 + 32 * 4;
     *in_smem = (K + 1) <= RP_HEAP_SMEM_ITEMS;
     return fixed + (*in_smem ? (size_t)(K + 1) * sizeof(HeapItem) : 0);
 }
@@ -236,36 +201,9 @@ cudaError_t replay_setup(int K)
     return cudaFuncSetAttribute(k_replay, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
 
-__global__ void __launch_bounds__(256) k_bucket_count(const Survivor* __restrict__ surv, int64_t n, int32_t* __restrict__ qcount)
-{
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-        atomicAdd(qcount + surv[i].q, 1);
-}
-
-cudaError_t launch_bucket_count(const Survivor* seg, int64_t n, int32_t* qcount, cudaStream_t st)
-{
-    if (n <= 0) return cudaSuccess;
-    int64_t blocks = std::min<int64_t>((n + 255) / 256, 148 * 32);
-    k_bucket_count<<<(unsigned)blocks, 256, 0, st>>>(seg, n, qcount);
-    return cudaGetLastError();
-}
-cudaError_t launch_bucket_scan(const int32_t* qcount, int32_t* qoffset, int32_t* qcursor, int n_query, cudaStream_t st)
-{
-    k_bucket_scan<<<1, 1024, 0, st>>>(qcount, qoffset, qcursor, n_query);
-    return cudaGetLastError();
-}
-cudaError_t launch_bucket_scatter(const Survivor* seg, const int32_t* seg_ci, int64_t n, const int32_t* qoffset, int32_t* qcursor,
-                                  Survivor* out, int32_t* out_ci, cudaStream_t st)
-{
-    if (n <= 0) return cudaSuccess;
-    int64_t blocks = std::min<int64_t>((n + 255) / 256, 148 * 32);
-    k_bucket_scatter<<<(unsigned)blocks, 256, 0, st>>>(seg, seg_ci, n, qoffset, qcursor, out, out_ci);
-    return cudaGetLastError();
-}
-cudaError_t launch_replay_only(const ReplayParams& p, cudaStream_t st)
+cudaError_t launch_replay(const ReplayParams& p, cudaStream_t st)
 {
     if (p.n_query <= 0) return cudaSuccess;
-    if ((p.round_count + RP_WIN - 1) / RP_WIN > RP_MAXWIN_WORDS * 32) return cudaErrorInvalidValue;
     int in_smem;
     size_t bytes = replay_smem_bytes(p.K, &in_smem);
     k_replay<<<p.n_query, RP_THREADS, bytes, st>>>(p, in_smem);

@@ -19,11 +19,11 @@ class UvgError(RuntimeError):
 
 class Engine:
     def __init__(self, nchar, nbest=100, trim=0, acgt=False, pool=512, device=0, first_round=0, max_round=0,
-                 early_abort=False, rank=0, world=1, max_survivors=0, db_capacity=0):
+                 early_abort=False, rank=0, world=1, db_capacity=0):
         self._lib = _capi.lib()
         p = _capi.uvg_params(_capi.UVG_ABI_VERSION, int(nchar), int(trim), int(nbest), int(bool(acgt)), int(pool),
                              int(device), int(first_round), int(max_round), int(bool(early_abort)), int(rank), int(world),
-                             int(max_survivors), int(db_capacity))
+                             0, int(db_capacity))
         h = C.c_void_p()
         rc = self._lib.uvg_create(C.byref(p), C.byref(h))
         if rc != 0:
