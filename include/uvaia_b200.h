@@ -142,6 +142,11 @@ void  uvg_host_free_pinned(void* p);
 /* Raw per-pair counts of queries x resident references [first, first+n): out[(iq*n + i)*4 + k], k = the four
  * counters of the mode (default: acgt,text,partial,valid; --acgt: match,valid,mism_idx,0).  Unit-test hook. */
 int uvg_debug_pair_counts(uvg_ctx* ctx, int64_t first, int64_t n, int32_t* out);
+/* Same for the query rows [q_first, q_first+q_count) only: out[((iq-q_first)*n + i)*4 + k]. */
+int uvg_debug_pair_counts_rows(uvg_ctx* ctx, int32_t q_first, int32_t q_count, int64_t first, int64_t n, int32_t* out);
+/* Per-reference values of resident references [first, first+n): valid_ref_sites (non_n), consensus-stage ACGT matches
+ * c0 and mismatches ci (queue_distance_to_consensus, nearest.c:428-433, untruncated).  Pointers may be NULL. */
+int uvg_debug_ref_meta(uvg_ctx* ctx, int64_t first, int64_t n, int32_t* non_n, int32_t* c0, int32_t* ci);
 /* Unpack resident reference `local` back to its 4-bit codes (nchar bytes, values 0..15).  Unit-test hook. */
 int uvg_debug_unpack_ref(uvg_ctx* ctx, int64_t local, uint8_t* codes_out);
 

@@ -1,0 +1,316 @@
+"""Parity tests proper: the CUDA path, called through the C ABI (ctypes -> libuvaia_b200.so), against
+  * the golden CSV tables written by the compiled reference binary (tests/golden/cases),
+  * the numpy oracle on seeded random inputs,
+  * the reference binary itself when oracle/_ref travelled to the box.
+Bit-exact: same neighbours, same six counts, same order."""
+import gzip
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+import pytest
+
+from helpers import ROOT, Case, case_names, orc
+from uvaia_b200 import host
+from uvaia_b200.engine import Engine, UvgError
+from uvaia_b200.synth import SynthModel, write_fasta
+
+pytestmark = pytest.mark.gpu
+
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "uvaia_ref")
+NON_H1 = [n for n in case_names() if not Case(n).h1]
+H1 = [n for n in case_names() if Case(n).h1]
+
+
+def gpu_csv(case, **engine_kw):
+    kw = case.options()
+    out = host.search_files(case.query_file, case.ref_files, **kw, **engine_kw)
+    return out, out.csv(kw["acgt"])
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# golden tables of the reference binary
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", NON_H1)
+def test_golden_csv_bit_exact(name):
+    c = Case(name)
+    out, csv = gpu_csv(c)
+    assert csv == c.expected_csv
+    # .aln.xz content: every reference that ever entered a heap, in file order (nearest.c:303-314)
+    got = [out.ref_names[i] for i in np.nonzero(out.ever_best)[0]]
+    assert got == c.expected_aln_names
+    assert out.stats["n_h1_flags"] == 0
+
+
+@pytest.mark.parametrize("name", ["syn_default", "syn_acgt", "syn_n100", "ties_n5", "amb_default", "c2_shape", "syn_exclude_self"])
+@pytest.mark.parametrize("knobs", [dict(first_round=32, max_round=64), dict(first_round=32, max_round=256, early_abort=True),
+                                   dict(batch_rows=97), dict(batch_rows=1000, first_round=64, max_round=64, early_abort=True)])
+def test_golden_csv_independent_of_round_schedule(name, knobs):
+    """rounds, streaming batches and the early abort are performance knobs: the table must not move"""
+    c = Case(name)
+    _, csv = gpu_csv(c, **knobs)
+    assert csv == c.expected_csv
+
+
+@pytest.mark.parametrize("name", H1)
+def test_h1_hazard_is_detected(name):
+    """the reference's own output depends on --pool for these inputs.  The CUDA path computes the
+    pool-independent closed form and must FLAG that the reference would have truncated (never silently differ)."""
+    c = Case(name)
+    kw = c.options()
+    out, csv = gpu_csv(c)
+    closed = orc.run_files(c.query_file, c.ref_files, **kw).csv(kw["acgt"])
+    assert csv == closed
+    lit = orc.run_files(c.query_file, c.ref_files, literal=True, **kw)
+    assert lit.csv(kw["acgt"]) == c.expected_csv
+    if lit.h1_events:
+        assert out.stats["n_h1_flags"] > 0
+    if csv != c.expected_csv:
+        assert out.stats["n_h1_flags"] > 0
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# kernels one by one against the oracle
+# ---------------------------------------------------------------------------------------------------------------
+def make_inputs(L, nq, nr, seed, amb_q=0.0, amb_r=0.0, clades=12):
+    m = SynthModel(nsites=L, n_clades=clades, seed=seed, clade_subs=max(3, L // 500))
+    qn, Q = m.sample(nq, seed + 1, ambiguous_frac=amb_q, prefix="Q")
+    rn, R = m.sample(nr, seed + 2, ambiguous_frac=amb_r, prefix="R")
+    return qn, Q, rn, R
+
+
+@pytest.mark.parametrize("L,acgt", [(1000, False), (1000, True), (2017, False), (29903, False), (33, False), (7, True)])
+def test_encoder_parity(L, acgt):
+    qn, Q, rn, R = make_inputs(L, 5, 300, 7 + L, amb_r=0.05)
+    R[3, :] = ord("N")                       # a reference the filter must drop
+    R[4, : L // 2 + 1] = ord("-")
+    R[5] = np.frombuffer((b"acgtnxo?.-RYKMSWBDHVUEZ*" * (L // 24 + 1))[:L], np.uint8)      # every symbol class, lower case too
+    names, Qo, tr, cons, idx, idx_m, idx_c = orc.prepare_queries(qn, [q.tobytes() for q in Q], 0, acgt, 1.0)
+    with Engine(L, nbest=5, acgt=acgt) as eng:
+        eng.set_queries(Qo)
+        min_non_n = int(L * 0.5)
+        nn, acc, na = eng.push_refs(R, min_non_n)
+        want_nn = (~orc.INDEL[R]).sum(1)
+        assert np.array_equal(nn, want_nn)                                   # quick_count_sequence_non_N
+        assert np.array_equal(acc.astype(bool), want_nn >= min_non_n)       # nearest.c:264
+        assert na == int((want_nn >= min_non_n).sum()) == eng.db_count
+        lut = orc.CODE.copy()
+        lut[[ord(c) for c in "acgtumrwsykvhdb"]] = lut[[ord(c) for c in "ACGTUMRWSYKVHDB"]]      # reader upper-cases
+        if acgt:
+            lut = np.zeros(256, np.uint8)
+            for k, ch in enumerate(b"ACGT"):
+                lut[ch] = 1 << k
+                lut[ch + 32] = 1 << k
+        kept = np.nonzero(acc)[0]
+        for j in list(range(min(6, len(kept)))) + [len(kept) // 2, len(kept) - 1]:
+            assert np.array_equal(eng.debug_unpack_ref(j), lut[R[kept[j]]]), j
+
+
+@pytest.mark.parametrize("L,nq,nr,amb_q,amb_r,trim", [(1000, 70, 200, 0.0, 0.0, 0), (1500, 33, 130, 0.2, 0.05, 0), (2000, 9, 97, 0.1, 0.1, 123),
+                                                      (29903, 10, 64, 0.02, 0.01, 0), (40, 3, 33, 0.1, 0.1, 0)])
+def test_pair_counts_default_mode(L, nq, nr, amb_q, amb_r, trim):
+    qn, Q, rn, R = make_inputs(L, nq, nr, 17 + L, amb_q, amb_r)
+    names, Qo, tr, cons, idx, idx_m, idx_c = orc.prepare_queries(qn, [q.tobytes() for q in Q], trim, False, 1.0)
+    inS = np.zeros(L, bool)
+    inS[tr:L - tr] = True
+    qc = np.where(inS[None, :], orc.CODE[Qo], 0).astype(np.uint8)
+    with Engine(L, nbest=5, trim=trim) as eng:
+        info = eng.set_queries(Qo)
+        assert (info.n_idx, info.n_idx_m, info.n_idx_c, info.trim) == (len(idx), len(idx_m), len(idx_c), tr)
+        eng.push_refs(R, 0)
+        got = eng.debug_pair_counts(0, nr)
+        want = np.stack(orc.pair_counts(qc, orc.CODE[R]), -1)
+        assert np.array_equal(got, want)
+        # a sub-range that does not start at a group boundary, and the row-restricted variant
+        if nr > 40:
+            assert np.array_equal(eng.debug_pair_counts(5, 30), want[:, 5:35])
+            assert np.array_equal(eng.debug_pair_counts_rows(1, 2, 7, 20), want[1:3, 7:27])
+        # per-reference consensus-stage values
+        nn, c0, ci = eng.debug_ref_meta(0, nr)
+        rc = orc.CODE[R]
+        mask_c = np.zeros(L, bool)
+        mask_c[idx_c] = True
+        cc = orc.CODE[cons]
+        want_c0 = ((cc[None, :] == rc) & (orc.POPC4[rc] == 1) & mask_c[None, :]).sum(1)
+        want_v = ((rc != 0) & (cc[None, :] != 0) & mask_c[None, :]).sum(1)
+        assert np.array_equal(c0, want_c0) and np.array_equal(ci, want_v - want_c0)
+        assert np.array_equal(nn, (~orc.INDEL[R]).sum(1))
+
+
+@pytest.mark.parametrize("L,nq,nr,amb,trim", [(1000, 70, 200, 0.0, 0), (1500, 33, 130, 0.2, 0), (2000, 9, 97, 0.1, 77)])
+def test_pair_counts_acgt_mode(L, nq, nr, amb, trim):
+    qn, Q, rn, R = make_inputs(L, nq, nr, 23 + L, amb, amb / 2)
+    names, Qo, tr, cons, idx, idx_m, idx_c = orc.prepare_queries(qn, [q.tobytes() for q in Q], trim, True, 1.0)
+    inS = np.zeros(L, bool)
+    inS[tr:L - tr] = True
+    qa = orc.ACGT[Qo] & inS[None, :]
+    ra = orc.ACGT[R]
+    mask_i = np.zeros(L, bool)
+    mask_i[idx] = True
+    f = np.float32
+    V = (qa.astype(f) @ ra.astype(f).T).astype(np.int32)
+    eq = sum(((qa & (Qo == ch)).astype(f) @ (R == ch).astype(f).T).astype(np.int32) for ch in b"ACGT")
+    eqi = sum((((qa & (Qo == ch)) & mask_i[None, :]).astype(f) @ (R == ch).astype(f).T).astype(np.int32) for ch in b"ACGT")
+    Vi = ((qa & mask_i[None, :]).astype(f) @ ra.astype(f).T).astype(np.int32)
+    with Engine(L, nbest=5, trim=trim, acgt=True) as eng:
+        eng.set_queries(Qo)
+        eng.push_refs(R, 0)
+        got = eng.debug_pair_counts(0, nr)
+    assert np.array_equal(got[..., 0], eq)              # matches
+    assert np.array_equal(got[..., 1], V)               # valid ACGT pairs
+    assert np.array_equal(got[..., 2], Vi - eqi)        # mismatches on segregating (idx) sites
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# whole searches against the oracle on seeded random inputs
+# ---------------------------------------------------------------------------------------------------------------
+def run_vs_oracle(L, nq, nr, nbest, acgt=False, trim=0, amb=0.0, seed=5, ambig_r=0.5, **engine_kw):
+    qn, Q, rn, R = make_inputs(L, nq, nr, seed, amb, amb / 2)
+    qs = [q.tobytes() for q in Q]
+    rs = [r.tobytes() for r in R]
+    ref = orc.search(qn, qs, None, nbest=nbest, trim=trim, acgt=acgt, refs=[(rn, rs)], pool=64, ambig_r=ambig_r)
+    names, Qo, tr, *_ = orc.prepare_queries(qn, qs, trim, acgt, 0.5)
+    with Engine(L, nbest=nbest, trim=trim, acgt=acgt, pool=64, **engine_kw) as eng:
+        eng.set_queries(Qo)
+        nn, acc, na = eng.push_refs(R, int(L * (1 - ambig_r)))
+        eng.search()
+        assert na == ref.n_ref_accepted
+        for iq in range(len(names)):
+            sc, refs = eng.heap(iq)
+            want = ref.rows[iq]
+            ws = np.array([w[0] for w in want], np.int32).reshape(-1, 6)
+            wr = np.array([w[2] for w in want], np.int64)
+            assert np.array_equal(sc, ws) and np.array_equal(refs, wr), f"query {iq}"
+        eb = eng.ever_best(0, na)
+        assert np.array_equal(np.nonzero(eb)[0], np.array(ref.ever_best, np.int64))
+        st = eng.stats()
+    return st
+
+
+@pytest.mark.parametrize("kw", [
+    dict(L=1000, nq=10, nr=300, nbest=5),
+    dict(L=2000, nq=70, nr=2500, nbest=10, first_round=64, max_round=512),
+    dict(L=2000, nq=70, nr=2500, nbest=10, first_round=64, max_round=512, early_abort=True),
+    dict(L=2000, nq=33, nr=1500, nbest=10, acgt=True),
+    dict(L=2000, nq=33, nr=1500, nbest=10, trim=100),
+    dict(L=2000, nq=33, nr=1500, nbest=1, amb=0.1),
+    dict(L=2000, nq=40, nr=3000, nbest=20, amb=0.2, first_round=32, max_round=256),
+    dict(L=2000, nq=40, nr=3000, nbest=20, amb=0.2, first_round=32, max_round=256, early_abort=True, acgt=True),
+    dict(L=29903, nq=20, nr=2000, nbest=10, early_abort=True),
+    dict(L=500, nq=130, nr=5000, nbest=100, ambig_r=0.2),
+    dict(L=64, nq=1, nr=100, nbest=3, seed=9),
+    dict(L=31, nq=65, nr=33, nbest=40, seed=10),
+])
+def test_search_vs_oracle(kw):
+    run_vs_oracle(**kw)
+
+
+def test_long_alignment_counters_do_not_wrap():
+    """alignments of 65,536 columns or more take the wide-counter variant of the pair-count kernel"""
+    run_vs_oracle(L=70001, nq=6, nr=96, nbest=4, amb=0.02, seed=77)
+
+
+def test_streaming_push_search_drop_equals_resident_search():
+    L = 1200
+    qn, Q, rn, R = make_inputs(L, 20, 4000, 41, 0.05, 0.02)
+    names, Qo, *_ = orc.prepare_queries(qn, [q.tobytes() for q in Q], 0, False, 0.5)
+    with Engine(L, nbest=15, first_round=64, max_round=1024) as a, Engine(L, nbest=15) as b:
+        a.set_queries(Qo)
+        b.set_queries(Qo)
+        a.push_refs(R, 600)
+        a.search()
+        for s in range(0, len(R), 333):
+            b.push_refs(R[s:s + 333], 600)
+            b.search()
+            b.drop_refs()
+        for iq in range(len(names)):
+            sa, ra = a.heap(iq)
+            sb, rb = b.heap(iq)
+            assert np.array_equal(sa, sb) and np.array_equal(ra, rb)
+        na = a.db_count
+        assert np.array_equal(a.ever_best(0, na), b.ever_best(0, na))
+        # repeating the search over the same resident database is idempotent
+        h0 = [a.heap(i) for i in range(len(names))]
+        a.reset_search()
+        a.search()
+        for iq in range(len(names)):
+            assert np.array_equal(a.heap(iq)[0], h0[iq][0]) and np.array_equal(a.heap(iq)[1], h0[iq][1])
+
+
+def test_edge_cases():
+    L = 300
+    qn, Q, rn, R = make_inputs(L, 4, 40, 51)
+    names, Qo, *_ = orc.prepare_queries(qn, [q.tobytes() for q in Q], 0, False, 1.0)
+    with Engine(L, nbest=6) as eng:
+        with pytest.raises(UvgError):
+            eng.search()                                   # no queries yet
+        eng.set_queries(Qo)
+        eng.search()                                       # empty database
+        assert all(len(eng.heap(i)[1]) == 0 for i in range(len(names)))
+        nn, acc, na = eng.push_refs(np.full((7, L), ord("N"), np.uint8), 10)
+        assert na == 0 and eng.db_count == 0               # everything filtered
+        eng.search()
+        assert all(len(eng.heap(i)[1]) == 0 for i in range(len(names)))
+        # hazard H2: K-1 neighbours crash the reference's writer; we return the K-1 rows
+        eng.push_refs(R[:5], 0)
+        eng.search()
+        for i in range(len(names)):
+            sc, refs = eng.heap(i)
+            assert len(refs) == 5 and sorted(refs.tolist()) == [0, 1, 2, 3, 4]
+            assert all(tuple(sc[j]) >= tuple(sc[j + 1]) for j in range(4))
+        with pytest.raises(UvgError):
+            eng.heap(99)
+    with pytest.raises(UvgError):
+        Engine(0)
+    # nbest 1 keeps two neighbours (min_heap.c:58, hazard H3)
+    with Engine(L, nbest=1) as eng:
+        eng.set_queries(Qo)
+        eng.push_refs(R, 0)
+        eng.search()
+        assert all(len(eng.heap(i)[1]) == 2 for i in range(len(names)))
+
+
+def test_query_identical_to_a_reference_ranks_first():
+    L = 2500
+    qn, Q, rn, R = make_inputs(L, 12, 1500, 61, 0.03, 0.01)
+    names, Qo, *_ = orc.prepare_queries(qn, [q.tobytes() for q in Q], 0, False, 0.5)
+    R = R.copy()
+    planted = {}
+    for iq in range(len(names)):
+        pos = 100 + 97 * iq
+        R[pos] = Qo[iq]
+        planted[iq] = pos
+    with Engine(L, nbest=10, first_round=128, max_round=512) as eng:
+        eng.set_queries(Qo)
+        eng.push_refs(R, 0)
+        eng.search()
+        for iq, pos in planted.items():
+            sc, refs = eng.heap(iq)
+            code = orc.CODE[Qo[iq]]
+            n_valid = int((code != 0).sum())
+            n_one = int((orc.POPC4[code] == 1).sum())
+            j = list(refs).index(pos)
+            assert sc[j, 3] == n_valid and sc[j, 0] == n_one and sc[j, 1] == n_valid and sc[j, 2] == n_valid
+            assert sc[0, 0] >= sc[j, 0]
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# the reference binary itself, when it travelled to the box (oracle/_ref is git-ignored but not gpurun-ignored)
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.skipif(not os.path.exists(REF_BIN), reason="oracle/_ref/uvaia_ref not present")
+@pytest.mark.parametrize("seed,acgt,trim,nbest", [(201, False, 0, 25), (202, True, 0, 8), (203, False, 150, 100)])
+def test_vs_live_reference_binary(seed, acgt, trim, nbest):
+    m = SynthModel(nsites=4000, n_clades=10, seed=seed, clade_subs=10)
+    qn, Q = m.sample(90, seed + 1, ambiguous_frac=0.03, prefix="Q")
+    rn, R = m.sample(2500, seed + 2, ambiguous_frac=0.01, prefix="R")
+    with tempfile.TemporaryDirectory() as wd:
+        qf, rf = os.path.join(wd, "q.fa"), os.path.join(wd, "r.fa")
+        write_fasta(qf, qn, Q)
+        write_fasta(rf, rn, R, width=80)
+        cmd = [REF_BIN, "-n", str(nbest), "-t", "4", "--trim", str(trim)] + (["--acgt"] if acgt else []) + ["-r", rf, "-o", os.path.join(wd, "o"), qf]
+        p = subprocess.run(cmd, cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert p.returncode == 0, p.stderr.decode()[-500:]
+        want = gzip.decompress(open(os.path.join(wd, "o.csv.xz"), "rb").read()).decode()
+        out = host.search_files(qf, [rf], nbest=nbest, trim=trim, acgt=acgt, first_round=256, max_round=1024)
+    assert out.csv(acgt) == want

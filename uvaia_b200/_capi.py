@@ -68,6 +68,8 @@ SYMBOLS = {
     "uvg_host_alloc_pinned": (_P, [C.c_size_t]),
     "uvg_host_free_pinned": (None, [_P]),
     "uvg_debug_pair_counts": (C.c_int, [_P, C.c_int64, C.c_int64, _P]),
+    "uvg_debug_pair_counts_rows": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, C.c_int64, _P]),
+    "uvg_debug_ref_meta": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, _P]),
     "uvg_debug_unpack_ref": (C.c_int, [_P, C.c_int64, _P]),
 }
 

@@ -803,6 +803,35 @@ extern "C" int uvg_debug_pair_counts(uvg_ctx* c, int64_t first, int64_t n, int32
     return UVG_OK;
 }
 
+extern "C" int uvg_debug_pair_counts_rows(uvg_ctx* c, int32_t q_first, int32_t q_count, int64_t first, int64_t n, int32_t* out)
+{
+    if (!c || !out || first < 0 || n < 1 || q_first < 0 || q_count < 1) { if (c) c->err = "uvg_debug_pair_counts_rows: bad arguments"; return UVG_EINVAL; }
+    UVG_CUDA(c, cudaSetDevice(c->prm.device));
+    if (c->n_query == 0 || first + n > c->db_n || n > c->score_cap || q_first + q_count > c->n_query)
+        UVG_FAIL(c, UVG_ESTATE, "uvg_debug_pair_counts_rows: range not resident, too long, or no such queries");
+    PairParams pp{};
+    fill_pair_params(c, pp, first, first + n);
+    pp.early_abort = 0; pp.work = nullptr;
+    UVG_CUDA(c, launch_paircount(pp, c->prm.acgt_mode, c->st));
+    UVG_CUDA(c, cudaMemcpy2DAsync(out, (size_t)n * 16, c->d_scores + (size_t)q_first * c->score_cap, (size_t)c->score_cap * 16,
+                                  (size_t)n * 16, (size_t)q_count, cudaMemcpyDeviceToHost, c->st));
+    UVG_CUDA(c, cudaStreamSynchronize(c->st));
+    return UVG_OK;
+}
+
+extern "C" int uvg_debug_ref_meta(uvg_ctx* c, int64_t first, int64_t n, int32_t* non_n, int32_t* c0, int32_t* ci)
+{
+    if (!c || first < 0 || n < 1) { if (c) c->err = "uvg_debug_ref_meta: bad arguments"; return UVG_EINVAL; }
+    UVG_CUDA(c, cudaSetDevice(c->prm.device));
+    if (c->n_query == 0 || first + n > c->db_n) UVG_FAIL(c, UVG_ESTATE, "uvg_debug_ref_meta: range not resident or no queries");
+    UVG_CUDA(c, launch_consensus(c->d_db, c->d_cons_acgt, c->d_cons_vo, c->Wp, c->prm.acgt_mode, first, first + n, c->d_c0, c->d_ci, c->st));
+    if (non_n) UVG_CUDA(c, cudaMemcpyAsync(non_n, c->d_non_n + first, (size_t)n * 4, cudaMemcpyDeviceToHost, c->st));
+    if (c0) UVG_CUDA(c, cudaMemcpyAsync(c0, c->d_c0 + first, (size_t)n * 4, cudaMemcpyDeviceToHost, c->st));
+    if (ci) UVG_CUDA(c, cudaMemcpyAsync(ci, c->d_ci + first, (size_t)n * 4, cudaMemcpyDeviceToHost, c->st));
+    UVG_CUDA(c, cudaStreamSynchronize(c->st));
+    return UVG_OK;
+}
+
 extern "C" int uvg_debug_unpack_ref(uvg_ctx* c, int64_t local, uint8_t* codes_out)
 {
     if (!c || !codes_out || local < 0 || local >= c->db_n) { if (c) c->err = "uvg_debug_unpack_ref: bad arguments"; return UVG_EINVAL; }

@@ -194,6 +194,19 @@ class Engine:
         self._ck(self._lib.uvg_debug_pair_counts(self._h, int(first), int(n), out.ctypes.data), "uvg_debug_pair_counts")
         return out
 
+    def debug_pair_counts_rows(self, q_first, q_count, first, n):
+        out = np.empty((int(q_count), int(n), 4), np.int32)
+        self._ck(self._lib.uvg_debug_pair_counts_rows(self._h, int(q_first), int(q_count), int(first), int(n), out.ctypes.data),
+                 "uvg_debug_pair_counts_rows")
+        return out
+
+    def debug_ref_meta(self, first, n):
+        """-> (non_n, c0, ci) int32[n]"""
+        nn, c0, ci = (np.empty(int(n), np.int32) for _ in range(3))
+        self._ck(self._lib.uvg_debug_ref_meta(self._h, int(first), int(n), nn.ctypes.data, c0.ctypes.data, ci.ctypes.data),
+                 "uvg_debug_ref_meta")
+        return nn, c0, ci
+
     def debug_unpack_ref(self, local):
         out = np.empty(self.nchar, np.uint8)
         self._ck(self._lib.uvg_debug_unpack_ref(self._h, int(local), out.ctypes.data), "uvg_debug_unpack_ref")

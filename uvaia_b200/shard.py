@@ -1,0 +1,64 @@
+"""Row sharding of the reference database over the GPUs of one box (host-side mirror of uvg_shard_of, engine.cu).
+
+The reference is a single process; the partition is ours.  The per-query admission of the reference is
+order dependent, so shards are NOT independent top-k problems: references are dealt to ranks in rounds of contiguous
+tiles in file order -- round j covers global ordinals [S_j, S_j + world*T_j), rank g scores [S_j + g*T_j, S_j + (g+1)*T_j),
+T_1 = first_round, T_{j+1} = min(4*T_j, max_round) -- and the scores of every round are handed to the rank that owns
+the query (query tile qt belongs to rank qt % world), which replays them in global file order.
+"""
+from __future__ import annotations
+
+GROUP = 32          # references interleaved per 16-byte column word (csrc/common.cuh)
+QTILE = 64          # queries per thread block of the pair-count kernel
+
+
+def round_sizes(first_round=0, max_round=0):
+    """(first, max) after the library's rounding (round_size_first / round_size_max, engine.cu)"""
+    first = first_round if first_round > 0 else 1024
+    first = (first + GROUP - 1) // GROUP * GROUP
+    mx = max_round if max_round > 0 else 65536
+    mx = (mx + GROUP - 1) // GROUP * GROUP
+    return first, max(mx, first)
+
+
+def rounds(total, world, first_round=0, max_round=0):
+    """[(S_j, T_j)] for every round needed to cover `total` accepted references"""
+    T, mx = round_sizes(first_round, max_round)
+    out, S = [], 0
+    while S < total:
+        out.append((S, T))
+        S += world * T
+        T = min(4 * T, mx)
+    return out
+
+
+def rank_tiles(total, rank, world, first_round=0, max_round=0):
+    """[(global_first, count)] of the reference ordinals rank `rank` holds, round by round"""
+    out = []
+    for S, T in rounds(total, world, first_round, max_round):
+        gb = S + rank * T
+        ge = min(gb + T, total)
+        if ge > gb:
+            out.append((gb, ge - gb))
+    return out
+
+
+def shard_of(ordinal, world, first_round=0, max_round=0):
+    """(rank, local index) of a global ordinal: python twin of uvg_shard_of"""
+    T, mx = round_sizes(first_round, max_round)
+    S = Ls = 0
+    while True:
+        if ordinal < S + world * T:
+            return (ordinal - S) // T, Ls + (ordinal - S) % T
+        S += world * T
+        Ls += T
+        T = min(4 * T, mx)
+
+
+def query_owner(iq, world):
+    """rank that replays query iq (ownership goes by tiles of QTILE queries, round-robin)"""
+    return (iq // QTILE) % world
+
+
+def owned_queries(n_query, rank, world):
+    return [q for q in range(n_query) if query_owner(q, world) == rank]
