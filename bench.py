@@ -27,8 +27,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 NCHAR = 29903
-LOP3_PER_PAIRWORD = 5          # algorithmic LOP3 per (pair, 32-site word): DESIGN.md section 4
-POPC_PER_PAIRWORD = 2
+LOP3_PER_PAIRWORD = 4.5        # LOP3 per (pair, 32-site word): 3 for valid+match, 1.5 for the carry-save tree
+POPC_PER_PAIRWORD = 1.25       # 1 for valid, 0.25 for the weight-4 carries of the match words
 
 
 def parse_args():
@@ -126,17 +126,7 @@ def make_queries(eng, clades, nq, nchar, ambiguous):
     return np.ascontiguousarray(text[order]), [b"Q%06d" % keep[i] for i in order]
 
 
-def rank_tiles(total, rank, world, first_round, max_round):
-    """[(global_first, count)] of the reference ordinals this rank holds, round by round (uvg_shard_of schedule)"""
-    out, S, T = [], 0, first_round
-    while S < total:
-        gb = S + rank * T
-        ge = min(gb + T, total)
-        if ge > gb:
-            out.append((gb, ge - gb))
-        S += world * T
-        T = min(4 * T, max_round)
-    return out
+from uvaia_b200.shard import rank_tiles  # noqa: E402  (round schedule of the row sharding, twin of uvg_shard_of)
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -262,7 +252,7 @@ def main():
             "warmup": args.warmup, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32 bit-planes / int32 counts",
             "data": "synthetic (device generator, seeds 1/1001/2002)",
             "config": {"workload": workload, "nbest": args.nbest, "early_abort": bool(args.early_abort), "sharding": "rows x%d" % world,
-                       "l2": "inputs larger than L2 (packed DB %.1f GB per pass)" % (R * ((L + 511) // 512 * 512) / 2 / 1e9)}}
+                       "l2": "inputs larger than L2 (packed DB %.1f GB per pass)" % (R * ((L + 255) // 256 * 256) * 3 / 8 / 1e9)}}
 
     if args.impl == "reference":
         times = []
@@ -385,12 +375,12 @@ def main():
     popc = POPC_PER_PAIRWORD * pairwords_rank / (k_ms * 1e-3) / 1e9
     f_l, f_p = lop3 / peaks["lop3_gips"], popc / peaks["popc_gips"]
     bound = "int-popc" if f_p >= f_l else "int-lop3"
-    n_qtiles = (Q + 63) // 64
-    db_bytes = n_local * ((W + 15) // 16 * 16) * 16
+    n_qtiles = (Q + 1 + 63) // 64                             # + the consensus pseudo-query
+    db_bytes = n_local * ((W + 7) // 8 * 8) * 12              # three bit-planes per 32-site word
     roofline = {"kernel": "k_paircount", "bound": bound, "achieved": popc if bound == "int-popc" else lop3,
                 "peak": peaks["popc_gips"] if bound == "int-popc" else peaks["lop3_gips"], "unit": "Gthread-inst/s",
                 "frac": max(f_l, f_p), "traffic": None,
-                "note": "INT pipes bind (north_star): %d LOP3 + %d POPC per EXECUTED pair x 32-site word (padding and early abort accounted for); peaks = profiles/int_pipes_b200_r01.json (measured)"
+                "note": "INT pipes bind (north_star): %.2f LOP3 + %.2f POPC per EXECUTED pair x 32-site word (padding and early abort accounted for); peaks = profiles/int_pipes_b200_r01.json (measured)"
                         % (LOP3_PER_PAIRWORD, POPC_PER_PAIRWORD),
                 "lop3": {"achieved": lop3, "peak": peaks["lop3_gips"], "frac": f_l}, "popc": {"achieved": popc, "peak": peaks["popc_gips"], "frac": f_p},
                 "hbm": {"bound": "hbm", "achieved": db_bytes / (k_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",

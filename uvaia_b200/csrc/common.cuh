@@ -7,26 +7,37 @@ namespace uvg {
 
 // ---- packed database layout -------------------------------------------------------------------------------
 // A site is a 4-bit IUPAC set (A=1,C=2,G=4,T=8; 0 = invalid: N,O,X,?,- and unknown bytes; biomcmc alignment.c:906-931
-// with the skip rule of :870).  32 consecutive sites of ONE reference form a "column word" of four bit-planes
-// (uint4: x=A, y=C, z=G, w=T; bit i = site 32*w+i).  32 consecutive references form a GROUP; the database is
-//     uint4 db[group][Wp][32]      (lane = reference within group)
-// so a warp reading column word w of its group issues one fully coalesced 512-byte request of 128-bit loads.
+// with the skip rule of :870).  The database keeps, per reference and 32-site column word, THREE bit-planes
+//     plane 0  "base"  bit i set <=> site 32*w+i is a plain base (one-hot code A, C, G or T)
+//     plane 1  "b0"    bit i set <=> the plain base is C or T
+//     plane 2  "b1"    bit i set <=> the plain base is G or T
+// so two plain bases are equal iff both b0 and b1 agree (3 LOP3 per pair and word give the valid AND the match mask).
+// Sites holding an ambiguity code (M R W S Y K V H D B: 2-3 bases) are rare (~1.7 per SARS-CoV-2 genome); they are
+// kept out of the planes (treated as invalid there) and listed per reference as (site, code) entries; the pair-count
+// kernel adds their exact contribution in its epilogue (paircount.cu).
+// Four consecutive column words of one plane form one uint4 "unit"; 32 consecutive references form a GROUP; the
+// database is
+//     uint4 db[group][Wp/4][NPLANE][32]      (lane = reference within group)
+// so that (a) a lane reads 128 sites of one plane of its reference with one conflict-free 128-bit shared-memory load
+// and (b) one chunk (WC = 8 column words) of a group is a single contiguous 3 KB run for a TMA bulk copy.
 constexpr int GROUP = 32;
 constexpr int WC = 8;             // column words per staged chunk
-constexpr int QTILE = 64;         // queries per thread block (8 warps x QPW)
+constexpr int W4 = WC / 4;        // uint4 units per chunk
+constexpr int NPLANE = 3;
+constexpr int QTILE = 64;         // query slots per thread block (8 warps x QPW)
 constexpr int QPW = 8;            // queries per warp (register tile)
 constexpr int PAIR_THREADS = 256;
-constexpr int STAGES = 4;
+constexpr int STAGES = 6;
 constexpr int RPL = 2;            // references per lane (a block scores 2 groups = 64 references)
-constexpr int NBAR = 16;          // steps of the admission staircase kept per query
+constexpr int MAX_RANKS = 8;      // GPUs of one box
+constexpr uint32_t AMB_SITE_MASK = 0x0fffffffu;       // ambiguity entry = site | code << 28
 
-// One staged chunk of a query tile: WC column words of 64 queries.  Contiguous in global memory so that one
+// One staged chunk of a query tile: WC column words of 64 query slots.  Contiguous in global memory so that one
 // cp.async.bulk (TMA 1-D bulk copy) moves it into shared memory.
 struct __align__(16) QChunk {
-    uint4    acgt[WC][QTILE];     // query bit-planes (zero outside the trimmed range / beyond nchar)
-    uint2    vo[WC][QTILE];       // x = valid plane (a|c|g|t); y = default mode: one-hot plane, --acgt mode: idx site mask
-    uint32_t slow[WC];            // bit k: warp k has an ambiguous (multi-base) query site in this word
-    uint32_t rem[QTILE];          // max ACGT matches query can still collect in the chunks AFTER this one
+    uint4    pl[W4][QTILE][4];    // [unit][slot][plane]: 0 base (plain base, inside the trimmed range), 1 b0, 2 b1,
+                                  //                      3 --acgt mode: segregating-site (idx) mask
+    uint32_t rem[QTILE];          // plain bases of the query in the chunks AFTER this one (upper bound of matches to come)
 };
 static_assert(sizeof(QChunk) % 16 == 0, "bulk copy size must be a multiple of 16");
 
@@ -37,39 +48,46 @@ struct __align__(16) HeapItem {
     int32_t pad;
 };
 
-// Per-query threshold snapshot read by the pair-count kernel (written by the replay kernel once the heap is full).
-// A pair c with D(c) = valid - acgt mismatches can be admitted at some later time only if the heap root r' at that time
-// has D(r') >= D(c) (src/nearest.c:488-496: D < max_incompatible = D(root)+1) and c is strictly better than r'
-// (min_heap.c:97).  Every future root is either an item kept NOW or was itself admitted under the same rule, so by
-// induction:  c is ever admissible  =>  some item h kept now has D(h) >= D(c) and h < c.   Hence with
-//   bar[b] = min ACGT count (first key) over kept items with D >= b << sh      (non-decreasing in b; bar[0] = root)
-//   dmax   = 1 + max D over kept items
-// a pair with D >= dmax, or with ACGT count < bar[D >> sh], or not strictly better than the root, is never admitted.
+// Per-query bounds for the warp-granular early abort of the pair-count kernel, written by the replay kernel once the
+// heap is full.  A pair with D = valid - acgt mismatches is admitted only if D < max_incompatible = D(root) + 1
+// (src/nearest.c:488-496, 506-508) where the root is a kept item; every kept item was itself admitted under that
+// rule, so by induction D(c) < dmax := 1 + max D over the items kept NOW holds for every pair admitted from now on.
+// And an admitted pair is strictly better than the root (min_heap.c:97), whose first key never decreases, so its ACGT
+// count is >= root_s0.  Both bounds only tighten with time: a stale snapshot is always safe.
 struct __align__(16) Threshold {
-    int32_t s[6];                 // heap root (worst kept item)
-    int32_t full;                 // 0: heap not full (every pair survives); else 1 + sh
+    int32_t full;                 // 0: heap not full (nothing can be discarded)
     int32_t dmax;
-    int32_t bar[NBAR];
+    int32_t root_s0;
+    int32_t pad;
 };
-static_assert(sizeof(Threshold) == 96, "Threshold layout");
 
 struct PairParams {
-    const uint4*    db;           // whole local database
-    const uint32_t* refamb;       // [group][ambw] bit w%32 of word w/32: some reference of the group is ambiguous in column word w
-    const QChunk*   qdata;        // [n_qtiles][n_chunks]
-    const Threshold* thr;         // [n_qtiles*QTILE]
-    int32_t Wp, n_chunks, ambw, n_qtiles, n_query;
+    const uint4*     db;          // whole local database
+    const QChunk*    qdata;       // [n_qtiles][n_chunks]
+    const Threshold* thr;         // indexed like the score rows: owner * rows_cap + row
+    const uint32_t*  qnib;        // 4-bit codes of every query slot (trimmed), qnib_stride words per slot, 8 sites per word
+    const uint32_t*  qamb_off;    // [n_slots + 1] ambiguity entries of the query slots
+    const uint32_t*  qamb_ent;
+    const uint32_t*  ramb_off;    // [local refs + 1] ambiguity entries of the references
+    const uint32_t*  ramb_ent;
+    const int32_t*   non_n;       // per local reference
+    int32_t qnib_stride;
+    int32_t Wp, n_chunks, n_qtiles;
+    int32_t n_slots;              // real queries + 1: the last slot is the consensus pseudo-query (nearest.c:428-433)
     int64_t local_begin, local_end;   // local reference range of this launch
-    int64_t global_minus_local;       // global ordinal = local index + this
-    uint4*   scores;              // dense output: scores[q * score_stride + score_col0 + (local - local_begin)]
-    int64_t  score_stride, score_col0;   //   default mode (acgt, text, partial, valid); --acgt mode (match, valid, mism_idx, 0)
-    int32_t early_abort;
+    // dense score tile(s): slot q of query tile qt goes to rank (qt % world), row (qt / world) * QTILE + q % QTILE; the
+    // consensus slot goes to row rows_cap of EVERY rank and the per-reference meta record (non_n) to row rows_cap + 1.
+    uint4*   out[MAX_RANKS];      // tile base on every rank (peer-mapped pointers when world > 1)
+    int64_t  row_stride;          // uint4 elements between rows
+    int64_t  col0;                // column of local_begin in the destination tiles
+    int32_t  world, rows_cap;
+    int32_t  early_abort;
     unsigned long long* work;     // executed (warp, chunk) iterations (early abort makes this < the dense count)
 };
 
-__host__ __device__ inline int64_t db_word_index(int64_t group, int w, int lane, int Wp)
+__host__ __device__ inline size_t db_unit_index(int64_t group, int unit, int plane, int lane, int Wp)
 {
-    return (group * Wp + w) * GROUP + lane;
+    return (((size_t)group * (size_t)(Wp / 4) + (size_t)unit) * NPLANE + (size_t)plane) * GROUP + (size_t)lane;
 }
 
 }  // namespace uvg

@@ -1,7 +1,15 @@
-// Host side of the C ABI (include/uvaia_b200.h): context, query preparation, database residency, round driver.
+// Host side of the C ABI (include/uvaia_b200.h): context, query preparation, database residency, round pipeline.
 // Replaces the orchestration of src/nearest.c:233-338 (queue_t, batch loop, two OpenMP loops) around the kernels
 // of encode.cu (K1), paircount.cu (K2) and replay.cu (K3).  No scoring happens on the host: without a CUDA device
 // uvg_create() fails (there is no CPU fallback by design).
+//
+// Round pipeline.  References are scored in rounds, in file order.  Round j runs
+//     stream A:  K2 pair counts of this rank's tile  --> stores every pair's counts into the score tile of the rank that
+//                                                        OWNS the query (query tile qt belongs to rank qt % world; peer
+//                                                        memory over NVLink), buffer j % 2
+//     stream B:  [NCCL all-gather of the owners' early-abort bounds = the cross-rank barrier]  -->  K3 exact replay of
+//                the owned queries over the whole round (all ranks' segments, in file order)
+// K2 of round j+1 overlaps K3 of round j; K2 of round j+2 waits until every rank has replayed round j (buffer reuse).
 #include "../../include/uvaia_b200.h"
 #include "common.cuh"
 #include "kernels.h"
@@ -18,17 +26,20 @@ using namespace uvg;
 
 namespace {
 std::string g_create_error;
+constexpr int NBUF = 2;
 
 // ---- NCCL through dlopen (the library loads without NCCL for single-GPU use) ------------------------------------
 typedef struct ncclComm* ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 typedef int ncclResult_t;
 enum { ncclInt8 = 0, ncclUint8 = 1, ncclInt32 = 2, ncclUint32 = 3, ncclInt64 = 4, ncclUint64 = 5 };
+enum { ncclSum = 0, ncclProd = 1, ncclMax = 2, ncclMin = 3 };
 struct NcclApi {
     void* handle = nullptr;
     ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
     bool load(std::string& err)
@@ -40,9 +51,10 @@ struct NcclApi {
         GetUniqueId = (decltype(GetUniqueId))dlsym(handle, "ncclGetUniqueId");
         CommInitRank = (decltype(CommInitRank))dlsym(handle, "ncclCommInitRank");
         AllGather = (decltype(AllGather))dlsym(handle, "ncclAllGather");
+        AllReduce = (decltype(AllReduce))dlsym(handle, "ncclAllReduce");
         CommDestroy = (decltype(CommDestroy))dlsym(handle, "ncclCommDestroy");
         GetErrorString = (decltype(GetErrorString))dlsym(handle, "ncclGetErrorString");
-        if (!GetUniqueId || !CommInitRank || !AllGather || !CommDestroy) { err = "NCCL symbols missing"; return false; }
+        if (!GetUniqueId || !CommInitRank || !AllGather || !AllReduce || !CommDestroy) { err = "NCCL symbols missing"; handle = nullptr; return false; }
         return true;
     }
 };
@@ -52,31 +64,39 @@ NcclApi g_nccl;
 struct uvg_ctx {
     uvg_params prm{};
     std::string err;
-    int K = 0, nchar = 0, trim = 0, W = 0, Wp = 0, n_chunks = 0, ambw = 0;
+    int K = 0, nchar = 0, trim = 0, W = 0, Wp = 0, n_chunks = 0;
     int rank = 0, world = 1;
-    cudaStream_t st = nullptr;
+    cudaStream_t st = nullptr, st_rp = nullptr;
     cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_d = nullptr;
+    cudaEvent_t ev_pair[NBUF]{}, ev_replay[NBUF]{}, ev_ag[NBUF]{};
     // queries
-    int n_query = 0, n_qtiles = 0;
+    int n_query = 0, n_slots = 0, n_qtiles = 0, rows_cap = 0, qnib_stride = 0;
     uvg_query_info qinfo{};
     QChunk* d_qdata = nullptr;
-    uint4* d_cons_acgt = nullptr; uint2* d_cons_vo = nullptr;
-    Threshold* d_thr = nullptr;
-    HeapItem* d_heaps = nullptr;
+    uint32_t *d_qnib = nullptr, *d_qamb_off = nullptr, *d_qamb_ent = nullptr;
+    Threshold* d_thr_local = nullptr;                 // [rows_cap] bounds of the owned rows (written by K3)
+    Threshold* d_thr_all[NBUF]{};                     // [world * rows_cap] what K2 reads (double buffered)
+    HeapItem* d_heaps = nullptr;                      // [rows_cap][K+1] owned rows
+    HeapItem* d_heaps_all = nullptr;                  // [world][rows_cap][K+1] (sharded mode: gathered at the end of a search)
     int32_t *d_heap_n = nullptr, *d_max_inc = nullptr, *d_batch_id = nullptr, *d_max_inc_batch = nullptr;
+    int32_t *d_heap_n_all = nullptr, *d_max_inc_all = nullptr;
     // database (local shard)
     int64_t db_cap = 0, db_n = 0, db_scored = 0, global_base = 0, global_total = -1;
-    uint4* d_db = nullptr; uint32_t* d_refamb = nullptr;
-    int32_t *d_non_n = nullptr, *d_c0 = nullptr, *d_ci = nullptr;
+    uint4* d_db = nullptr;
+    int32_t* d_non_n = nullptr;
+    uint32_t* d_ramb_off = nullptr; uint32_t* d_ramb_ent = nullptr; int64_t amb_cap = 0, amb_n = 0;
     uint8_t* d_ever = nullptr; int64_t ever_cap = 0;
-    // dense score tile of one round: [n_query][score_cap] x (4 counts)
-    int64_t score_cap = 0;
-    uint4* d_scores = nullptr;
+    // dense score tiles of a round: NBUF x [rows_cap + 2][world * seg_cap] x (4 counts)
+    int64_t seg_cap = 0;                              // references per rank and round the tiles can hold
+    uint4* d_tiles = nullptr; size_t tile_elems = 0;  // one buffer = tile_elems uint4
+    uint4* peer_tiles[MAX_RANKS]{};                   // base of d_tiles on every rank (peer-mapped)
+    bool peers_ready = false;
     unsigned long long* d_counters = nullptr;
-    unsigned long long* h_pinned = nullptr;          // small pinned read-back area
+    unsigned long long* h_pinned = nullptr;           // small pinned read-back area
+    void* d_ipc = nullptr;                            // staging for the handle exchange
     // push staging
     uint8_t* d_stage_text = nullptr; size_t stage_text_bytes = 0;
-    int32_t* d_stage_nn = nullptr; uint8_t* d_stage_acc = nullptr; int64_t* d_stage_dst = nullptr; int64_t stage_rows = 0;
+    int32_t *d_stage_nn = nullptr, *d_stage_namb = nullptr; uint8_t* d_stage_acc = nullptr; int64_t* d_stage_dst = nullptr; int64_t stage_rows = 0;
     int64_t* d_nacc = nullptr;
     // round schedule
     int64_t rounds_done = 0, round_local_start = 0, round_global_start = 0;
@@ -86,7 +106,6 @@ struct uvg_ctx {
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pair_events;
     // nccl
     ncclComm_t comm = nullptr;
-    int32_t* dbg_counts = nullptr;
     // host cache of the heaps (filled lazily by uvg_get_heap, invalidated by every search / reset)
     int64_t work_base = 0;
     bool heaps_cached = false;
@@ -97,6 +116,9 @@ struct uvg_ctx {
 #define UVG_CUDA(ctx, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { \
     char b_[512]; snprintf(b_, sizeof b_, "%s:%d CUDA error: %s", __FILE__, __LINE__, cudaGetErrorString(e_)); (ctx)->err = b_; \
     return e_ == cudaErrorMemoryAllocation ? UVG_ENOMEM : UVG_ECUDA; } } while (0)
+#define UVG_NCCL(ctx, call) do { ncclResult_t r_ = (call); if (r_ != 0) { \
+    char b_[512]; snprintf(b_, sizeof b_, "%s:%d NCCL error: %s", __FILE__, __LINE__, g_nccl.GetErrorString ? g_nccl.GetErrorString(r_) : "?"); \
+    (ctx)->err = b_; return UVG_ENCCL; } } while (0)
 
 static int32_t round_size_first(const uvg_params& p) { int32_t v = p.first_round > 0 ? p.first_round : 1024; return (v + GROUP - 1) / GROUP * GROUP; }
 static int32_t round_size_max(const uvg_params& p)
@@ -117,6 +139,9 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
     *out = nullptr;
     if (p->abi_version != UVG_ABI_VERSION) { g_create_error = "ABI version mismatch"; return UVG_EINVAL; }
     if (p->nchar < 1 || p->nbest < 1) { g_create_error = "nchar and nbest must be positive"; return UVG_EINVAL; }
+    if (p->nchar > (int32_t)AMB_SITE_MASK) { g_create_error = "alignments longer than 2^28 columns are not supported"; return UVG_EINVAL; }
+    if (p->world > MAX_RANKS) { g_create_error = "at most 8 ranks (one box)"; return UVG_EINVAL; }
+    if (p->world > 1 && (p->rank < 0 || p->rank >= p->world)) { g_create_error = "rank out of range"; return UVG_EINVAL; }
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev < 1) {
@@ -134,7 +159,6 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
     c->W = (p->nchar + 31) / 32;
     c->n_chunks = (c->W + WC - 1) / WC;
     c->Wp = c->n_chunks * WC;
-    c->ambw = (c->Wp + 31) / 32;
     c->rank = p->world > 1 ? p->rank : 0;
     c->world = p->world > 1 ? p->world : 1;
     c->next_round = round_size_first(*p);
@@ -144,27 +168,49 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
     cudaDeviceProp prop;
     CK_(cudaGetDeviceProperties(&prop, p->device));
     if (prop.major < 10) { g_create_error = "device is not sm_100 or newer; this library ships sm_100a code only"; delete c; return UVG_ENODEV; }
-    CK_(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
+    int lo = 0, hi = 0;
+    CK_(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CK_(cudaStreamCreateWithPriority(&c->st, cudaStreamNonBlocking, lo));
+    CK_(cudaStreamCreateWithPriority(&c->st_rp, cudaStreamNonBlocking, hi));       // the short replay / collective work goes first
     CK_(cudaEventCreate(&c->ev_a)); CK_(cudaEventCreate(&c->ev_b)); CK_(cudaEventCreate(&c->ev_c)); CK_(cudaEventCreate(&c->ev_d));
+    for (int b = 0; b < NBUF; ++b) {
+        CK_(cudaEventCreateWithFlags(&c->ev_pair[b], cudaEventDisableTiming));
+        CK_(cudaEventCreateWithFlags(&c->ev_replay[b], cudaEventDisableTiming));
+        CK_(cudaEventCreateWithFlags(&c->ev_ag[b], cudaEventDisableTiming));
+    }
     CK_(upload_luts());
     CK_(paircount_setup());
     CK_(replay_setup(c->K));
-    CK_(cudaMalloc(&c->d_counters, 64)); CK_(cudaMalloc(&c->d_nacc, 64));
+    CK_(cudaMalloc(&c->d_counters, 64)); CK_(cudaMalloc(&c->d_nacc, 64)); CK_(cudaMalloc(&c->d_ipc, 64 * MAX_RANKS + 64));
     CK_(cudaMemset(c->d_counters, 0, 64));
-    CK_(cudaMallocHost(&c->h_pinned, 1024));
+    CK_(cudaMallocHost(&c->h_pinned, 2048));
 #undef CK_
     *out = c;
     return UVG_OK;
 }
 
+static void close_peers(uvg_ctx* c)
+{
+    for (int r = 0; r < MAX_RANKS; ++r) {
+        if (c->peer_tiles[r] && r != c->rank && c->world > 1) cudaIpcCloseMemHandle(c->peer_tiles[r]);
+        c->peer_tiles[r] = nullptr;
+    }
+    c->peers_ready = false;
+}
+
 static void free_queries(uvg_ctx* c)
 {
-    cudaFree(c->d_qdata); cudaFree(c->d_cons_acgt); cudaFree(c->d_cons_vo); cudaFree(c->d_thr); cudaFree(c->d_heaps);
+    close_peers(c);
+    cudaFree(c->d_qdata); cudaFree(c->d_qnib); cudaFree(c->d_qamb_off); cudaFree(c->d_qamb_ent);
+    cudaFree(c->d_thr_local); for (int b = 0; b < NBUF; ++b) { cudaFree(c->d_thr_all[b]); c->d_thr_all[b] = nullptr; }
+    cudaFree(c->d_heaps); cudaFree(c->d_heaps_all);
     cudaFree(c->d_heap_n); cudaFree(c->d_max_inc); cudaFree(c->d_batch_id); cudaFree(c->d_max_inc_batch);
-    cudaFree(c->d_scores);
-    c->d_qdata = nullptr; c->d_cons_acgt = nullptr; c->d_cons_vo = nullptr; c->d_thr = nullptr; c->d_heaps = nullptr;
-    c->d_heap_n = c->d_max_inc = c->d_batch_id = c->d_max_inc_batch = nullptr;
-    c->d_scores = nullptr; c->score_cap = 0;
+    cudaFree(c->d_heap_n_all); cudaFree(c->d_max_inc_all);
+    cudaFree(c->d_tiles);
+    c->d_qdata = nullptr; c->d_qnib = c->d_qamb_off = c->d_qamb_ent = nullptr; c->d_thr_local = nullptr;
+    c->d_heaps = c->d_heaps_all = nullptr;
+    c->d_heap_n = c->d_max_inc = c->d_batch_id = c->d_max_inc_batch = c->d_heap_n_all = c->d_max_inc_all = nullptr;
+    c->d_tiles = nullptr; c->seg_cap = 0; c->tile_elems = 0;
 }
 
 extern "C" void uvg_destroy(uvg_ctx* c)
@@ -172,17 +218,30 @@ extern "C" void uvg_destroy(uvg_ctx* c)
     if (!c) return;
     cudaSetDevice(c->prm.device);
     if (c->st) cudaStreamSynchronize(c->st);
-    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    if (c->st_rp) cudaStreamSynchronize(c->st_rp);
     free_queries(c);
-    cudaFree(c->d_db); cudaFree(c->d_refamb); cudaFree(c->d_non_n); cudaFree(c->d_c0); cudaFree(c->d_ci); cudaFree(c->d_ever);
-    cudaFree(c->d_counters); cudaFree(c->d_nacc);
-    cudaFree(c->d_stage_text); cudaFree(c->d_stage_nn); cudaFree(c->d_stage_acc); cudaFree(c->d_stage_dst);
-    cudaFree(c->dbg_counts);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    cudaFree(c->d_db); cudaFree(c->d_non_n); cudaFree(c->d_ramb_off); cudaFree(c->d_ramb_ent); cudaFree(c->d_ever);
+    cudaFree(c->d_counters); cudaFree(c->d_nacc); cudaFree(c->d_ipc);
+    cudaFree(c->d_stage_text); cudaFree(c->d_stage_nn); cudaFree(c->d_stage_namb); cudaFree(c->d_stage_acc); cudaFree(c->d_stage_dst);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (auto& pr : c->pair_events) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
     if (c->ev_a) { cudaEventDestroy(c->ev_a); cudaEventDestroy(c->ev_b); cudaEventDestroy(c->ev_c); cudaEventDestroy(c->ev_d); }
+    for (int b = 0; b < NBUF; ++b) {
+        if (c->ev_pair[b]) cudaEventDestroy(c->ev_pair[b]);
+        if (c->ev_replay[b]) cudaEventDestroy(c->ev_replay[b]);
+        if (c->ev_ag[b]) cudaEventDestroy(c->ev_ag[b]);
+    }
     if (c->st) cudaStreamDestroy(c->st);
+    if (c->st_rp) cudaStreamDestroy(c->st_rp);
     delete c;
+}
+
+static int sync_all(uvg_ctx* c)
+{
+    UVG_CUDA(c, cudaStreamSynchronize(c->st));
+    UVG_CUDA(c, cudaStreamSynchronize(c->st_rp));
+    return UVG_OK;
 }
 
 // =====================================================================================================================
@@ -190,15 +249,18 @@ extern "C" void uvg_destroy(uvg_ctx* c)
 // =====================================================================================================================
 static int reset_heaps(uvg_ctx* c)
 {
-    const int Q = c->n_query;
-    if (Q == 0) return UVG_OK;
-    std::vector<int32_t> init(Q, c->nchar);                                 // max_incompatible = nchar (nearest.c:375,387)
-    UVG_CUDA(c, cudaMemcpyAsync(c->d_max_inc, init.data(), Q * 4, cudaMemcpyHostToDevice, c->st));
-    UVG_CUDA(c, cudaMemcpyAsync(c->d_max_inc_batch, init.data(), Q * 4, cudaMemcpyHostToDevice, c->st));
-    UVG_CUDA(c, cudaMemsetAsync(c->d_batch_id, 0xff, Q * 4, c->st));
-    UVG_CUDA(c, cudaMemsetAsync(c->d_heap_n, 0, Q * 4, c->st));
-    UVG_CUDA(c, cudaMemsetAsync(c->d_thr, 0, (size_t)c->n_qtiles * QTILE * sizeof(Threshold), c->st));
-    UVG_CUDA(c, cudaMemsetAsync(c->d_heaps, 0, (size_t)Q * (c->K + 1) * sizeof(HeapItem), c->st));
+    const int rows = c->rows_cap;
+    if (c->n_query == 0) return UVG_OK;
+    int rc = sync_all(c);
+    if (rc) return rc;
+    std::vector<int32_t> init(rows, c->nchar);                              // max_incompatible = nchar (nearest.c:375,387)
+    UVG_CUDA(c, cudaMemcpyAsync(c->d_max_inc, init.data(), rows * 4, cudaMemcpyHostToDevice, c->st));
+    UVG_CUDA(c, cudaMemcpyAsync(c->d_max_inc_batch, init.data(), rows * 4, cudaMemcpyHostToDevice, c->st));
+    UVG_CUDA(c, cudaMemsetAsync(c->d_batch_id, 0xff, rows * 4, c->st));
+    UVG_CUDA(c, cudaMemsetAsync(c->d_heap_n, 0, rows * 4, c->st));
+    UVG_CUDA(c, cudaMemsetAsync(c->d_thr_local, 0, (size_t)rows * sizeof(Threshold), c->st));
+    for (int b = 0; b < NBUF; ++b) UVG_CUDA(c, cudaMemsetAsync(c->d_thr_all[b], 0, (size_t)c->world * rows * sizeof(Threshold), c->st));
+    UVG_CUDA(c, cudaMemsetAsync(c->d_heaps, 0, (size_t)rows * (c->K + 1) * sizeof(HeapItem), c->st));
     UVG_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 64, c->st));
     if (c->d_ever && c->ever_cap) UVG_CUDA(c, cudaMemsetAsync(c->d_ever, 0, c->ever_cap, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));                              // `init` goes out of scope
@@ -215,9 +277,10 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
 {
     if (!c || !text || n_query < 1) { if (c) c->err = "uvg_set_queries: bad arguments"; return UVG_EINVAL; }
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
-    UVG_CUDA(c, cudaStreamSynchronize(c->st));
+    int rc = sync_all(c);
+    if (rc) return rc;
     free_queries(c);
-    const int L = c->nchar, trim = c->trim, Wp = c->Wp, Q = n_query;
+    const int L = c->nchar, trim = c->trim, Q = n_query;
     const bool acgt = c->prm.acgt_mode != 0;
     uint8_t lut[3][256];
     build_luts(lut);
@@ -245,82 +308,83 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
         else { site_class[i] = 2; ++n_idx_m; cons[i] = first; }
     }
     c->n_query = Q;
-    c->n_qtiles = (Q + QTILE - 1) / QTILE;
+    c->n_slots = Q + 1;                                                     // + the consensus pseudo-query (nearest.c:428-433)
+    c->n_qtiles = (c->n_slots + QTILE - 1) / QTILE;
+    c->rows_cap = (c->n_qtiles + c->world - 1) / c->world * QTILE;
+    c->qnib_stride = (L + 7) / 8;
     c->qinfo.n_query = Q; c->qinfo.nchar = L; c->qinfo.trim = trim;
     c->qinfo.n_idx = n_idx; c->qinfo.n_idx_m = n_idx_m; c->qinfo.n_idx_c = n_idx_c;
     if (info) *info = c->qinfo;
 
-    // ---- bit-planes of every query (zero outside the trimmed range) ----
+    // ---- planes, nibble codes and ambiguity lists of every slot (zero outside the trimmed range) ----
     const size_t n_chunk_total = (size_t)c->n_qtiles * c->n_chunks;
     std::vector<QChunk> qd(n_chunk_total);
     memset(qd.data(), 0, n_chunk_total * sizeof(QChunk));
-    std::vector<uint32_t> one_count((size_t)Q * c->n_chunks, 0);            // potential ACGT matches per (query, chunk)
-    for (int q = 0; q < Q; ++q) {
-        const int qt = q / QTILE, qi = q % QTILE, warp = qi / QPW;
-        const uint8_t* row = text + (size_t)q * L;
-        for (int w = 0; w < c->W; ++w) {
-            uint32_t a = 0, cc = 0, g = 0, t = 0, im = 0;
-            const int s0 = w * 32, s1 = std::min(L, s0 + 32);
-            for (int s = std::max(s0, trim); s < std::min(s1, L - trim); ++s) {
-                const uint8_t code = code_lut[up[row[s]]];
-                const uint32_t bit = 1u << (s - s0);
-                if (code & 1) a |= bit;
-                if (code & 2) cc |= bit;
-                if (code & 4) g |= bit;
-                if (code & 8) t |= bit;
-                if (site_class[s] == 1) im |= bit;
-            }
-            const uint32_t v = a | cc | g | t;
-            const uint32_t multi = (a & cc) | (g & t) | ((a | cc) & (g | t));
-            const uint32_t one = v & ~multi;
+    std::vector<uint32_t> qnib((size_t)c->n_slots * c->qnib_stride, 0);
+    std::vector<uint32_t> amb_off(c->n_slots + 1, 0), amb_ent;
+    std::vector<uint32_t> plain_in_chunk(c->n_chunks);
+    for (int q = 0; q < c->n_slots; ++q) {
+        const int qt = q / QTILE, qi = q % QTILE;
+        const bool is_cons = q == Q;
+        const uint8_t* row = is_cons ? cons.data() : text + (size_t)q * L;
+        std::fill(plain_in_chunk.begin(), plain_in_chunk.end(), 0u);
+        amb_off[q] = (uint32_t)amb_ent.size();
+        for (int s = trim; s < L - trim; ++s) {
+            if (is_cons && site_class[s] != 3) continue;                    // the consensus is scored on idx_c only
+            const uint32_t code = code_lut[up[row[s]]];
+            const int w = s >> 5, k = w & 3;
+            const uint32_t bit = 1u << (s & 31);
             QChunk& ch = qd[(size_t)qt * c->n_chunks + w / WC];
-            ch.acgt[w % WC][qi] = make_uint4(a, cc, g, t);
-            ch.vo[w % WC][qi] = make_uint2(v, acgt ? im : one);
-            if (!acgt && (v & ~one)) ch.slow[w % WC] |= 1u << warp;
-            one_count[(size_t)q * c->n_chunks + w / WC] += (uint32_t)__builtin_popcount(acgt ? v : one);
+            uint4* pl = ch.pl[(w % WC) / 4][qi];
+            uint32_t* p0 = &pl[0].x; uint32_t* p1 = &pl[1].x; uint32_t* p2 = &pl[2].x; uint32_t* p3 = &pl[3].x;
+            if (acgt && site_class[s] == 1) p3[k] |= bit;                   // segregating-site mask (dist_unique, nearest.c:459-470)
+            if (!code) continue;
+            qnib[(size_t)q * c->qnib_stride + (s >> 3)] |= code << ((s & 7) * 4);
+            if (code & (code - 1)) { amb_ent.push_back((uint32_t)s | (code << 28)); continue; }
+            p0[k] |= bit;
+            if (code & 10u) p1[k] |= bit;                                   // C or T
+            if (code & 12u) p2[k] |= bit;                                   // G or T
+            ++plain_in_chunk[w / WC];
         }
         uint32_t run = 0;
         for (int k = c->n_chunks - 1; k >= 0; --k) {
             qd[(size_t)qt * c->n_chunks + k].rem[qi] = run;
-            run += one_count[(size_t)q * c->n_chunks + k];
+            run += plain_in_chunk[k];
         }
     }
-    // ---- consensus pseudo-query restricted to idx_c (queue_distance_to_consensus, nearest.c:428-433) ----
-    std::vector<uint4> ca(Wp, make_uint4(0, 0, 0, 0));
-    std::vector<uint2> cv(Wp, make_uint2(0, 0));
-    for (int s = trim; s < L - trim; ++s) {
-        if (site_class[s] != 3) continue;
-        const uint8_t code = code_lut[cons[s]];
-        const uint32_t bit = 1u << (s & 31);
-        uint4& x = ca[s >> 5];
-        if (code & 1) x.x |= bit;
-        if (code & 2) x.y |= bit;
-        if (code & 4) x.z |= bit;
-        if (code & 8) x.w |= bit;
-        if (code) cv[s >> 5].x |= bit;
-        if (code && !(code & (code - 1))) cv[s >> 5].y |= bit;
-    }
+    amb_off[c->n_slots] = (uint32_t)amb_ent.size();
 
     // ---- device allocations ----
-    const size_t Qp = (size_t)c->n_qtiles * QTILE;
+    const int rows = c->rows_cap;
     UVG_CUDA(c, cudaMalloc(&c->d_qdata, n_chunk_total * sizeof(QChunk)));
-    UVG_CUDA(c, cudaMalloc(&c->d_cons_acgt, Wp * sizeof(uint4)));
-    UVG_CUDA(c, cudaMalloc(&c->d_cons_vo, Wp * sizeof(uint2)));
-    UVG_CUDA(c, cudaMalloc(&c->d_thr, Qp * sizeof(Threshold)));
-    UVG_CUDA(c, cudaMalloc(&c->d_heaps, (size_t)Q * (c->K + 1) * sizeof(HeapItem)));
-    UVG_CUDA(c, cudaMalloc(&c->d_heap_n, Q * 4)); UVG_CUDA(c, cudaMalloc(&c->d_max_inc, Q * 4));
-    UVG_CUDA(c, cudaMalloc(&c->d_batch_id, Q * 4)); UVG_CUDA(c, cudaMalloc(&c->d_max_inc_batch, Q * 4));
-    // dense score tile: rounds are capped so that n_query x round x 16 B stays within ~2 GiB
+    UVG_CUDA(c, cudaMalloc(&c->d_qnib, qnib.size() * 4));
+    UVG_CUDA(c, cudaMalloc(&c->d_qamb_off, amb_off.size() * 4));
+    UVG_CUDA(c, cudaMalloc(&c->d_qamb_ent, std::max<size_t>(1, amb_ent.size()) * 4));
+    UVG_CUDA(c, cudaMalloc(&c->d_thr_local, (size_t)rows * sizeof(Threshold)));
+    for (int b = 0; b < NBUF; ++b) UVG_CUDA(c, cudaMalloc(&c->d_thr_all[b], (size_t)c->world * rows * sizeof(Threshold)));
+    UVG_CUDA(c, cudaMalloc(&c->d_heaps, (size_t)rows * (c->K + 1) * sizeof(HeapItem)));
+    UVG_CUDA(c, cudaMalloc(&c->d_heap_n, rows * 4)); UVG_CUDA(c, cudaMalloc(&c->d_max_inc, rows * 4));
+    UVG_CUDA(c, cudaMalloc(&c->d_batch_id, rows * 4)); UVG_CUDA(c, cudaMalloc(&c->d_max_inc_batch, rows * 4));
+    if (c->world > 1) {
+        UVG_CUDA(c, cudaMalloc(&c->d_heaps_all, (size_t)c->world * rows * (c->K + 1) * sizeof(HeapItem)));
+        UVG_CUDA(c, cudaMalloc(&c->d_heap_n_all, (size_t)c->world * rows * 4));
+        UVG_CUDA(c, cudaMalloc(&c->d_max_inc_all, (size_t)c->world * rows * 4));
+    }
+    // dense score tiles: rounds are capped so that one buffer stays within ~3 GiB
     {
         int64_t cap = round_size_max(c->prm);
-        const int64_t fit = ((int64_t)2 << 30) / ((int64_t)Q * 16) / (GROUP * RPL) * (GROUP * RPL);
+        const int64_t per_ref = (int64_t)(rows + 2) * c->world * 16;        // bytes of one column position over all segments
+        const int64_t fit = ((int64_t)3 << 30) / per_ref / (GROUP * RPL) * (GROUP * RPL);
         cap = std::max<int64_t>(GROUP * RPL, std::min(cap, fit));
-        c->score_cap = cap;
-        UVG_CUDA(c, cudaMalloc(&c->d_scores, (size_t)Q * cap * sizeof(uint4)));
+        c->seg_cap = cap;
+        c->tile_elems = (size_t)(rows + 2) * c->world * cap;
+        UVG_CUDA(c, cudaMalloc(&c->d_tiles, NBUF * c->tile_elems * sizeof(uint4)));
+        if (c->world == 1) { c->peer_tiles[0] = c->d_tiles; c->peers_ready = true; }
     }
     UVG_CUDA(c, cudaMemcpyAsync(c->d_qdata, qd.data(), n_chunk_total * sizeof(QChunk), cudaMemcpyHostToDevice, c->st));
-    UVG_CUDA(c, cudaMemcpyAsync(c->d_cons_acgt, ca.data(), Wp * sizeof(uint4), cudaMemcpyHostToDevice, c->st));
-    UVG_CUDA(c, cudaMemcpyAsync(c->d_cons_vo, cv.data(), Wp * sizeof(uint2), cudaMemcpyHostToDevice, c->st));
+    UVG_CUDA(c, cudaMemcpyAsync(c->d_qnib, qnib.data(), qnib.size() * 4, cudaMemcpyHostToDevice, c->st));
+    UVG_CUDA(c, cudaMemcpyAsync(c->d_qamb_off, amb_off.data(), amb_off.size() * 4, cudaMemcpyHostToDevice, c->st));
+    if (!amb_ent.empty()) UVG_CUDA(c, cudaMemcpyAsync(c->d_qamb_ent, amb_ent.data(), amb_ent.size() * 4, cudaMemcpyHostToDevice, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
     return reset_heaps(c);
 }
@@ -364,13 +428,23 @@ static int ensure_db_capacity(uvg_ctx* c, int64_t need_refs)
     cap = std::max<int64_t>(cap, c->prm.db_capacity);
     cap = std::max<int64_t>(cap, 4096);
     cap = (cap + GROUP * RPL - 1) / (GROUP * RPL) * (GROUP * RPL);
+    const size_t per_group = (size_t)(c->Wp / 4) * NPLANE * GROUP;            // uint4 per group
     const size_t og = (size_t)(c->db_cap / GROUP), ng = (size_t)(cap / GROUP);
-    UVG_CUDA(c, grow_array(&c->d_db, og * c->Wp * GROUP, ng * c->Wp * GROUP, false, c->st));
-    UVG_CUDA(c, grow_array(&c->d_refamb, og * c->ambw, ng * c->ambw, true, c->st));
+    UVG_CUDA(c, grow_array(&c->d_db, og * per_group, ng * per_group, true, c->st));
     UVG_CUDA(c, grow_array(&c->d_non_n, (size_t)c->db_cap, (size_t)cap, true, c->st));
-    UVG_CUDA(c, grow_array(&c->d_c0, (size_t)c->db_cap, (size_t)cap, true, c->st));
-    UVG_CUDA(c, grow_array(&c->d_ci, (size_t)c->db_cap, (size_t)cap, true, c->st));
+    UVG_CUDA(c, grow_array(&c->d_ramb_off, c->db_cap ? (size_t)c->db_cap + 1 : 0, (size_t)cap + 1, true, c->st));
     c->db_cap = cap;
+    return UVG_OK;
+}
+
+static int ensure_amb_capacity(uvg_ctx* c, int64_t need)
+{
+    if (need <= c->amb_cap) return UVG_OK;
+    if (need > 0xfffffff0LL) UVG_FAIL(c, UVG_ENOMEM, "more than 2^32 ambiguity codes in the resident references");
+    int64_t cap = std::max<int64_t>(need, c->amb_cap * 2);
+    cap = std::max<int64_t>(cap, 1 << 16);
+    UVG_CUDA(c, grow_array(&c->d_ramb_ent, (size_t)c->amb_cap, (size_t)cap, false, c->st));
+    c->amb_cap = cap;
     return UVG_OK;
 }
 
@@ -379,6 +453,8 @@ static int ensure_ever(uvg_ctx* c, int64_t n_global)
     if (n_global <= c->ever_cap) return UVG_OK;
     int64_t cap = std::max<int64_t>(n_global, c->ever_cap * 2);
     cap = std::max<int64_t>(cap, 4096);
+    int rc = sync_all(c);
+    if (rc) return rc;
     UVG_CUDA(c, grow_array(&c->d_ever, (size_t)c->ever_cap, (size_t)cap, true, c->st));
     c->ever_cap = cap;
     return UVG_OK;
@@ -387,9 +463,10 @@ static int ensure_ever(uvg_ctx* c, int64_t n_global)
 static int ensure_stage_rows(uvg_ctx* c, int64_t rows)
 {
     if (rows <= c->stage_rows) return UVG_OK;
-    cudaFree(c->d_stage_nn); cudaFree(c->d_stage_acc); cudaFree(c->d_stage_dst);
-    c->d_stage_nn = nullptr; c->d_stage_acc = nullptr; c->d_stage_dst = nullptr; c->stage_rows = 0;
+    cudaFree(c->d_stage_nn); cudaFree(c->d_stage_namb); cudaFree(c->d_stage_acc); cudaFree(c->d_stage_dst);
+    c->d_stage_nn = c->d_stage_namb = nullptr; c->d_stage_acc = nullptr; c->d_stage_dst = nullptr; c->stage_rows = 0;
     UVG_CUDA(c, cudaMalloc(&c->d_stage_nn, rows * 4));
+    UVG_CUDA(c, cudaMalloc(&c->d_stage_namb, rows * 4));
     UVG_CUDA(c, cudaMalloc(&c->d_stage_acc, rows));
     UVG_CUDA(c, cudaMalloc(&c->d_stage_dst, rows * 8));
     c->stage_rows = rows;
@@ -404,18 +481,23 @@ static int push_device_rows(uvg_ctx* c, const uint8_t* d_text, int64_t n, int32_
     if (rc) return rc;
     rc = ensure_db_capacity(c, c->db_n + n);
     if (rc) return rc;
-    UVG_CUDA(c, launch_count_non_n(d_text, n, c->nchar, min_non_n, c->d_stage_nn, c->d_stage_acc, c->st));
-    UVG_CUDA(c, launch_scan_accept(c->d_stage_acc, n, c->db_n, c->d_stage_dst, c->d_nacc, c->st));
-    UVG_CUDA(c, launch_encode(d_text, n, c->nchar, c->W, c->Wp, c->ambw, c->prm.acgt_mode, c->d_stage_dst, c->d_stage_nn,
-                              c->d_db, c->d_refamb, c->d_non_n, c->st));
-    c->stats.other_kernel_launches += 3;
+    UVG_CUDA(c, launch_count_non_n(d_text, n, c->nchar, min_non_n, c->prm.acgt_mode, c->d_stage_nn, c->d_stage_acc, c->d_stage_namb, c->st));
+    UVG_CUDA(c, launch_scan_accept(c->d_stage_acc, c->d_stage_namb, n, c->db_n, (uint32_t)c->amb_n, c->d_stage_dst, c->d_ramb_off, c->d_nacc, c->st));
     int64_t* h_n = reinterpret_cast<int64_t*>(c->h_pinned);
-    UVG_CUDA(c, cudaMemcpyAsync(h_n, c->d_nacc, 8, cudaMemcpyDeviceToHost, c->st));
+    UVG_CUDA(c, cudaMemcpyAsync(h_n, c->d_nacc, 16, cudaMemcpyDeviceToHost, c->st));
     if (non_n_out) UVG_CUDA(c, cudaMemcpyAsync(non_n_out, c->d_stage_nn, n * 4, cudaMemcpyDeviceToHost, c->st));
     if (accepted_out) UVG_CUDA(c, cudaMemcpyAsync(accepted_out, c->d_stage_acc, n, cudaMemcpyDeviceToHost, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
-    c->db_n += *h_n;
-    if (n_acc_out) *n_acc_out += *h_n;
+    const int64_t n_acc = h_n[0], n_amb = h_n[1];
+    rc = ensure_amb_capacity(c, c->amb_n + n_amb);
+    if (rc) return rc;
+    UVG_CUDA(c, launch_encode(d_text, n, c->nchar, c->Wp, c->prm.acgt_mode, c->d_stage_dst, c->d_stage_nn, c->d_db, c->d_ramb_off,
+                              c->d_ramb_ent, c->d_non_n, c->st));
+    c->stats.other_kernel_launches += 3;
+    UVG_CUDA(c, cudaStreamSynchronize(c->st));             // the caller may reuse d_text
+    c->db_n += n_acc;
+    c->amb_n += n_amb;
+    if (n_acc_out) *n_acc_out += n_acc;
     return UVG_OK;
 }
 
@@ -449,7 +531,8 @@ extern "C" int uvg_push_refs(uvg_ctx* c, const uint8_t* text, int64_t n, int32_t
     if (n_accepted) *n_accepted = 0;
     if (n == 0) return UVG_OK;
     // stage through a device text buffer of <= 256 MiB per step
-    const int64_t rows_per_step = std::max<int64_t>(1, std::min<int64_t>(n, (256ll << 20) / c->nchar));
+    int64_t rows_per_step = std::max<int64_t>(1, std::min<int64_t>(n, (256ll << 20) / c->nchar));
+    rows_per_step = std::min<int64_t>(rows_per_step, 1 << 16);
     const size_t need = (size_t)rows_per_step * c->nchar;
     if (need > c->stage_text_bytes) {
         cudaFree(c->d_stage_text); c->d_stage_text = nullptr; c->stage_text_bytes = 0;
@@ -478,9 +561,8 @@ extern "C" int uvg_drop_refs(uvg_ctx* c)
     if (c->world > 1) UVG_FAIL(c, UVG_ESTATE, "uvg_drop_refs is not available in sharded mode");
     if (c->db_scored != c->db_n) UVG_FAIL(c, UVG_ESTATE, "uvg_drop_refs: %lld resident references have not been searched yet",
                                          (long long)(c->db_n - c->db_scored));
-    if (c->d_refamb) UVG_CUDA(c, cudaMemsetAsync(c->d_refamb, 0, (size_t)(c->db_cap / GROUP) * c->ambw * 4, c->st));
     c->global_base += c->db_n;
-    c->db_n = 0; c->db_scored = 0; c->round_local_start = 0;
+    c->db_n = 0; c->db_scored = 0; c->round_local_start = 0; c->amb_n = 0;
     return UVG_OK;
 }
 
@@ -488,15 +570,14 @@ extern "C" int uvg_clear_refs(uvg_ctx* c)
 {
     if (!c) return UVG_EINVAL;
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
-    if (c->d_refamb) UVG_CUDA(c, cudaMemsetAsync(c->d_refamb, 0, (size_t)(c->db_cap / GROUP) * c->ambw * 4, c->st));
-    c->global_base = 0; c->db_n = 0; c->db_scored = 0; c->round_local_start = 0; c->global_total = -1;
+    c->global_base = 0; c->db_n = 0; c->db_scored = 0; c->round_local_start = 0; c->global_total = -1; c->amb_n = 0;
     return c->n_query ? reset_heaps(c) : UVG_OK;
 }
 
 extern "C" int64_t uvg_db_count(const uvg_ctx* c) { return c ? c->db_n : 0; }
 
 // =====================================================================================================================
-// search: rounds of K2 (pair counts -> survivors) and K3 (exact replay)
+// search: rounds of K2 (pair counts -> score tiles of the owners) and K3 (exact replay)
 // =====================================================================================================================
 static int event_pair(uvg_ctx* c, size_t idx, cudaEvent_t* a, cudaEvent_t* b)
 {
@@ -509,50 +590,97 @@ static int event_pair(uvg_ctx* c, size_t idx, cudaEvent_t* a, cudaEvent_t* b)
     return UVG_OK;
 }
 
-static void fill_pair_params(uvg_ctx* c, PairParams& pp, int64_t lb, int64_t le)
+// sharded mode: every rank maps the score tiles of all ranks (CUDA IPC; the handles travel through a tiny NCCL all-gather)
+static int ensure_peers(uvg_ctx* c)
 {
-    pp.db = c->d_db; pp.refamb = c->d_refamb; pp.qdata = c->d_qdata; pp.thr = c->d_thr;
-    pp.Wp = c->Wp; pp.n_chunks = c->n_chunks; pp.ambw = c->ambw; pp.n_qtiles = c->n_qtiles; pp.n_query = c->n_query;
-    pp.local_begin = lb; pp.local_end = le; pp.global_minus_local = 0;
-    pp.scores = c->d_scores; pp.score_stride = c->score_cap; pp.score_col0 = 0;
+    if (c->peers_ready) return UVG_OK;
+    cudaIpcMemHandle_t mine;
+    UVG_CUDA(c, cudaIpcGetMemHandle(&mine, c->d_tiles));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    uint8_t* stage = static_cast<uint8_t*>(c->d_ipc);
+    UVG_CUDA(c, cudaMemcpyAsync(stage, &mine, 64, cudaMemcpyHostToDevice, c->st));
+    UVG_NCCL(c, g_nccl.AllGather(stage, stage + 64, 64, ncclUint8, c->comm, c->st));
+    std::vector<cudaIpcMemHandle_t> all(c->world);
+    UVG_CUDA(c, cudaMemcpyAsync(all.data(), stage + 64, 64 * (size_t)c->world, cudaMemcpyDeviceToHost, c->st));
+    UVG_CUDA(c, cudaStreamSynchronize(c->st));
+    for (int r = 0; r < c->world; ++r) {
+        if (r == c->rank) { c->peer_tiles[r] = c->d_tiles; continue; }
+        void* p = nullptr;
+        UVG_CUDA(c, cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess));
+        c->peer_tiles[r] = static_cast<uint4*>(p);
+    }
+    c->peers_ready = true;
+    return UVG_OK;
+}
+
+static void fill_pair_params(uvg_ctx* c, PairParams& pp, int64_t lb, int64_t le, int buf, int64_t col0)
+{
+    pp.db = c->d_db; pp.qdata = c->d_qdata; pp.thr = c->d_thr_all[buf];
+    pp.qnib = c->d_qnib; pp.qamb_off = c->d_qamb_off; pp.qamb_ent = c->d_qamb_ent;
+    pp.ramb_off = c->d_ramb_off; pp.ramb_ent = c->d_ramb_ent; pp.non_n = c->d_non_n;
+    pp.qnib_stride = c->qnib_stride;
+    pp.Wp = c->Wp; pp.n_chunks = c->n_chunks; pp.n_qtiles = c->n_qtiles; pp.n_slots = c->n_slots;
+    pp.local_begin = lb; pp.local_end = le;
+    for (int r = 0; r < c->world; ++r) pp.out[r] = c->peer_tiles[r] + (size_t)buf * c->tile_elems;
+    pp.row_stride = (int64_t)c->world * c->seg_cap; pp.col0 = col0;
+    pp.world = c->world; pp.rows_cap = c->rows_cap;
     pp.early_abort = c->prm.early_abort; pp.work = c->d_counters + 2;
 }
 
-// one scoring round over the local tile [lstart, lstart+cnt): consensus stage, pair counts into the dense tile, replay.
-// Everything is asynchronous on the context's stream: there is no host synchronisation inside a search.
-static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t tile_global, int64_t round_first,
-                     int64_t round_count, size_t* n_pair_events)
+// one scoring round: this rank's tile [lstart, lstart+cnt) -> score tiles of the owners, then replay of the owned rows
+// over the segments of all ranks.  Asynchronous on the two streams: there is no host synchronisation inside a search.
+static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t round_first, int64_t round_count, size_t* n_ev)
 {
-    (void)T; (void)round_first; (void)round_count;
-    if (c->world > 1) UVG_FAIL(c, UVG_ESTATE, "sharded search is not wired to the dense score tile yet");
-    if (cnt <= 0) return UVG_OK;
-    PairParams pp{};
-    fill_pair_params(c, pp, lstart, lstart + cnt);
-    UVG_CUDA(c, launch_consensus(c->d_db, c->d_cons_acgt, c->d_cons_vo, c->Wp, c->prm.acgt_mode, pp.local_begin, pp.local_end,
-                                 c->d_c0, c->d_ci, c->st));
+    const int b = (int)(c->rounds_done % NBUF);
+    // buffer b was last read by the replay of round j-2: single GPU -> our own replay; sharded -> every rank's replay,
+    // which the all-gather of round j-1 (issued after it on each rank's stream B) has already waited for
+    UVG_CUDA(c, cudaStreamWaitEvent(c->st, c->world > 1 ? c->ev_ag[(b + 1) % NBUF] : c->ev_replay[b], 0));
     cudaEvent_t ea, eb;
-    int rc = event_pair(c, *n_pair_events, &ea, &eb);
+    int rc = event_pair(c, *n_ev, &ea, &eb);
     if (rc) return rc;
     UVG_CUDA(c, cudaEventRecord(ea, c->st));
-    UVG_CUDA(c, launch_paircount(pp, c->prm.acgt_mode, c->st));
+    if (cnt > 0) {
+        PairParams pp{};
+        fill_pair_params(c, pp, lstart, lstart + cnt, b, (int64_t)c->rank * c->seg_cap);
+        UVG_CUDA(c, launch_paircount(pp, c->prm.acgt_mode, c->st));
+        c->stats.pair_kernel_launches += 1;
+    }
     UVG_CUDA(c, cudaEventRecord(eb, c->st));
-    ++*n_pair_events;
+    ++*n_ev;
+    UVG_CUDA(c, cudaEventRecord(c->ev_pair[b], c->st));
+
+    UVG_CUDA(c, cudaStreamWaitEvent(c->st_rp, c->ev_pair[b], 0));
+    if (c->world > 1) {
+        // bounds of the owned rows (state after round j-1) to everybody; doubles as the barrier "all tiles of round j are
+        // written".  K2 of round j+1 reads buffer (j+1) % 2.
+        UVG_NCCL(c, g_nccl.AllGather(c->d_thr_local, c->d_thr_all[(b + 1) % NBUF], (size_t)c->rows_cap * sizeof(Threshold), ncclUint8,
+                                     c->comm, c->st_rp));
+        UVG_CUDA(c, cudaEventRecord(c->ev_ag[b], c->st_rp));
+    }
     ReplayParams rp{};
-    rp.scores = c->d_scores; rp.row_stride = c->score_cap;
-    rp.nseg = 1; rp.seg_stride = (int32_t)cnt; rp.seg_cnt[0] = (int32_t)cnt; rp.seg_global[0] = tile_global;
-    rp.non_n = c->d_non_n + lstart; rp.c0 = c->d_c0 + lstart; rp.ci = c->d_ci + lstart;
+    rp.tile = c->d_tiles + (size_t)b * c->tile_elems; rp.row_stride = (int64_t)c->world * c->seg_cap;
+    rp.nseg = c->world; rp.seg_stride = (int32_t)c->seg_cap;
+    for (int g = 0; g < c->world; ++g) {
+        const int64_t gb = round_first + (int64_t)g * T;
+        rp.seg_global[g] = gb;
+        rp.seg_cnt[g] = (int32_t)std::max<int64_t>(0, std::min<int64_t>(T, round_first + round_count - gb));
+    }
+    rp.rows_cap = c->rows_cap;
     rp.heaps = c->d_heaps; rp.heap_n = c->d_heap_n; rp.max_inc = c->d_max_inc;
-    rp.batch_id = c->d_batch_id; rp.max_inc_batch = c->d_max_inc_batch; rp.thr = c->d_thr;
+    rp.batch_id = c->d_batch_id; rp.max_inc_batch = c->d_max_inc_batch;
+    rp.thr = c->world > 1 ? c->d_thr_local : c->d_thr_all[b];              // single GPU: straight into what K2 of round j+2 reads
     rp.ever_best = c->d_ever; rp.counters = c->d_counters;
-    rp.q_first = 0; rp.n_query = c->n_query; rp.K = c->K; rp.acgt_mode = c->prm.acgt_mode; rp.pool = c->prm.pool;
+    rp.n_query = c->n_query; rp.world = c->world; rp.rank = c->rank;
+    rp.K = c->K; rp.acgt_mode = c->prm.acgt_mode; rp.pool = c->prm.pool;
     cudaEvent_t ra, rb;
-    rc = event_pair(c, *n_pair_events, &ra, &rb);
+    rc = event_pair(c, *n_ev, &ra, &rb);
     if (rc) return rc;
-    UVG_CUDA(c, cudaEventRecord(ra, c->st));
-    UVG_CUDA(c, launch_replay(rp, c->st));
-    UVG_CUDA(c, cudaEventRecord(rb, c->st));
-    ++*n_pair_events;
-    c->stats.pair_kernel_launches += 1; c->stats.other_kernel_launches += 2;
+    UVG_CUDA(c, cudaEventRecord(ra, c->st_rp));
+    UVG_CUDA(c, launch_replay(rp, c->st_rp));
+    UVG_CUDA(c, cudaEventRecord(rb, c->st_rp));
+    ++*n_ev;
+    UVG_CUDA(c, cudaEventRecord(c->ev_replay[b], c->st_rp));
+    c->stats.other_kernel_launches += 1;
     return UVG_OK;
 }
 
@@ -563,42 +691,63 @@ extern "C" int uvg_search(uvg_ctx* c)
     if (c->n_query == 0) UVG_FAIL(c, UVG_ESTATE, "uvg_search: no queries set");
     if (c->world > 1 && !c->comm) UVG_FAIL(c, UVG_ESTATE, "uvg_search: sharded context without uvg_nccl_init");
     if (c->world > 1 && c->global_total < 0) UVG_FAIL(c, UVG_ESTATE, "uvg_search: sharded context without uvg_set_global_count");
-    const int32_t mx = (int32_t)std::min<int64_t>(round_size_max(c->prm), c->score_cap);
+    int rc = sync_all(c);
+    if (rc) return rc;
+    if (c->world > 1) { rc = ensure_peers(c); if (rc) return rc; }
+    const int32_t mx = (int32_t)std::min<int64_t>(round_size_max(c->prm), c->seg_cap);
+    if (c->next_round > mx) c->next_round = mx;
     size_t n_ev = 0;
     c->heaps_cached = false;
     c->stats.pair_kernel_ms = 0; c->stats.replay_ms = 0;
     UVG_CUDA(c, cudaMemcpyAsync(c->h_pinned + 20, c->d_counters + 2, 8, cudaMemcpyDeviceToHost, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
     c->work_base = (int64_t)c->h_pinned[20];
+    // every array the rounds touch is sized before the first launch (no reallocation while kernels are in flight)
+    {
+        const int64_t upto = c->world == 1 ? c->global_base + c->db_n : c->global_total;
+        if (upto > 0x7fffffffLL) UVG_FAIL(c, UVG_EINVAL, "more than 2^31 references are not supported");
+        rc = ensure_ever(c, upto);
+        if (rc) return rc;
+    }
     UVG_CUDA(c, cudaEventRecord(c->ev_a, c->st));
     for (;;) {
         const int64_t T = c->next_round;
-        int64_t lstart, cnt, tile_global, rfirst, rcount;
+        int64_t lstart, cnt, rfirst, rcount;
         if (c->world == 1) {
             cnt = std::min<int64_t>(T, c->db_n - c->db_scored);
             if (cnt <= 0) break;
-            lstart = c->db_scored; tile_global = c->global_base + lstart; rfirst = tile_global; rcount = cnt;
+            lstart = c->db_scored; rfirst = c->global_base + lstart; rcount = cnt;
         } else {
             const int64_t S = c->round_global_start;
             if (S >= c->global_total) break;
             const int64_t gb = S + (int64_t)c->rank * T, ge = std::min(gb + T, c->global_total);
             cnt = std::max<int64_t>(0, ge - gb);
-            lstart = c->round_local_start; tile_global = gb; rfirst = S; rcount = std::min<int64_t>((int64_t)c->world * T, c->global_total - S);
+            lstart = c->round_local_start; rfirst = S; rcount = std::min<int64_t>((int64_t)c->world * T, c->global_total - S);
             if (lstart + cnt > c->db_n) UVG_FAIL(c, UVG_ESTATE, "rank %d holds %lld references but round %lld needs local rows up to %lld",
                                                  c->rank, (long long)c->db_n, (long long)c->rounds_done, (long long)(lstart + cnt));
         }
-        int rc = ensure_ever(c, rfirst + rcount);
-        if (rc) return rc;
-        if (rfirst + rcount > 0x7fffffffLL) UVG_FAIL(c, UVG_EINVAL, "more than 2^31 references are not supported");
-        rc = run_round(c, lstart, cnt, T, tile_global, rfirst, rcount, &n_ev);
+        rc = run_round(c, lstart, cnt, T, rfirst, rcount, &n_ev);
         if (rc) return rc;
         if (c->world == 1) { c->db_scored += cnt; c->stats.n_refs += cnt; }
         else { c->round_global_start += (int64_t)c->world * T; c->round_local_start += T; c->db_scored = std::min(c->db_n, c->round_local_start); c->stats.n_refs += rcount; }
         ++c->rounds_done; ++c->stats.n_rounds;
         c->next_round = round_size_next(c->next_round, mx);
     }
+    // the search ends when the last replay has finished: join stream B into stream A
+    UVG_CUDA(c, cudaEventRecord(c->ev_d, c->st_rp));
+    UVG_CUDA(c, cudaStreamWaitEvent(c->st, c->ev_d, 0));
+    if (c->world > 1) {
+        // the tables of all queries to every rank (small all-gathers over NVLink), OR of the ever-best flags
+        const size_t hb = (size_t)c->rows_cap * (c->K + 1) * sizeof(HeapItem);
+        UVG_NCCL(c, g_nccl.AllGather(c->d_heaps, c->d_heaps_all, hb, ncclUint8, c->comm, c->st));
+        UVG_NCCL(c, g_nccl.AllGather(c->d_heap_n, c->d_heap_n_all, (size_t)c->rows_cap, ncclInt32, c->comm, c->st));
+        UVG_NCCL(c, g_nccl.AllGather(c->d_max_inc, c->d_max_inc_all, (size_t)c->rows_cap, ncclInt32, c->comm, c->st));
+        if (c->global_total > 0) UVG_NCCL(c, g_nccl.AllReduce(c->d_ever, c->d_ever, (size_t)c->global_total, ncclUint8, ncclMax, c->comm, c->st));
+    }
     UVG_CUDA(c, cudaEventRecord(c->ev_b, c->st));
     UVG_CUDA(c, cudaEventSynchronize(c->ev_b));
+    rc = sync_all(c);
+    if (rc) return rc;
     float ms = 0; cudaEventElapsedTime(&ms, c->ev_a, c->ev_b);
     c->stats.search_ms = ms;
     for (size_t i = 0; i < n_ev; ++i) {           // events alternate: pair-count launch, replay launch
@@ -625,14 +774,21 @@ static int compare_items_desc(const void* pa, const void* pb)
 static int cache_heaps(uvg_ctx* c)
 {
     if (c->heaps_cached) return UVG_OK;
-    const size_t Q = c->n_query, stride = c->K + 1;
-    c->h_heaps.resize(Q * stride); c->h_heap_n.resize(Q); c->h_max_inc.resize(Q);
-    UVG_CUDA(c, cudaMemcpyAsync(c->h_heaps.data(), c->d_heaps, Q * stride * sizeof(HeapItem), cudaMemcpyDeviceToHost, c->st));
-    UVG_CUDA(c, cudaMemcpyAsync(c->h_heap_n.data(), c->d_heap_n, Q * 4, cudaMemcpyDeviceToHost, c->st));
-    UVG_CUDA(c, cudaMemcpyAsync(c->h_max_inc.data(), c->d_max_inc, Q * 4, cudaMemcpyDeviceToHost, c->st));
+    const size_t rows = (size_t)c->world * c->rows_cap, stride = c->K + 1;
+    c->h_heaps.resize(rows * stride); c->h_heap_n.resize(rows); c->h_max_inc.resize(rows);
+    const bool sh = c->world > 1;
+    UVG_CUDA(c, cudaMemcpyAsync(c->h_heaps.data(), sh ? c->d_heaps_all : c->d_heaps, rows * stride * sizeof(HeapItem), cudaMemcpyDeviceToHost, c->st));
+    UVG_CUDA(c, cudaMemcpyAsync(c->h_heap_n.data(), sh ? c->d_heap_n_all : c->d_heap_n, rows * 4, cudaMemcpyDeviceToHost, c->st));
+    UVG_CUDA(c, cudaMemcpyAsync(c->h_max_inc.data(), sh ? c->d_max_inc_all : c->d_max_inc, rows * 4, cudaMemcpyDeviceToHost, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
     c->heaps_cached = true;
     return UVG_OK;
+}
+
+static size_t row_of_query(const uvg_ctx* c, int iq)
+{
+    const int qt = iq / QTILE;
+    return (size_t)(qt % c->world) * c->rows_cap + (size_t)(qt / c->world) * QTILE + iq % QTILE;
 }
 
 extern "C" int uvg_get_heap(uvg_ctx* c, int32_t iq, uvg_item* out, int32_t* n_out)
@@ -642,10 +798,11 @@ extern "C" int uvg_get_heap(uvg_ctx* c, int32_t iq, uvg_item* out, int32_t* n_ou
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
     int rc = cache_heaps(c);
     if (rc) return rc;
-    const int n = c->h_heap_n[iq];
+    const size_t row = row_of_query(c, iq);
+    const int n = c->h_heap_n[row];
     *n_out = n;
     if (n == 0) return UVG_OK;
-    const HeapItem* a = c->h_heaps.data() + (size_t)iq * (c->K + 1);
+    const HeapItem* a = c->h_heaps.data() + row * (c->K + 1);
     // heap_finalise_heap_qsort (src/min_heap.c:149-153): slot 0 <-> slot n, then libc qsort over [0, n)
     std::vector<HeapItem> arr(n);
     arr[0] = a[n];
@@ -683,7 +840,7 @@ extern "C" int uvg_get_stats(uvg_ctx* c, uvg_stats* out)
         int rc = cache_heaps(c);
         if (rc) return rc;
         int64_t mm = 0;
-        for (int q = 0; q < c->n_query; ++q) mm = std::max<int64_t>(mm, c->h_max_inc[q] - 1);
+        for (int q = 0; q < c->n_query; ++q) mm = std::max<int64_t>(mm, c->h_max_inc[row_of_query(c, q)] - 1);
         c->stats.max_mismatch = mm;
     }
     *out = c->stats;
@@ -728,8 +885,7 @@ extern "C" int uvg_nccl_init(uvg_ctx* c, const void* id128)
     if (!g_nccl.load(c->err)) return UVG_ENCCL;
     ncclUniqueId id;
     memcpy(&id, id128, 128);
-    ncclResult_t r = g_nccl.CommInitRank(&c->comm, c->world, id, c->rank);
-    if (r != 0) UVG_FAIL(c, UVG_ENCCL, "ncclCommInitRank failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+    UVG_NCCL(c, g_nccl.CommInitRank(&c->comm, c->world, id, c->rank));
     return UVG_OK;
 }
 
@@ -788,18 +944,17 @@ extern "C" int uvg_memcpy_h2d(uvg_ctx* c, void* d_dst, const void* src, size_t b
 extern "C" void* uvg_host_alloc_pinned(size_t bytes) { void* p = nullptr; return cudaMallocHost(&p, bytes) == cudaSuccess ? p : nullptr; }
 extern "C" void uvg_host_free_pinned(void* p) { if (p) cudaFreeHost(p); }
 
-extern "C" int uvg_debug_pair_counts(uvg_ctx* c, int64_t first, int64_t n, int32_t* out)
+// scores of resident references [first, first+n) against every slot into tile buffer 0 (test hooks only; single GPU)
+static int debug_score(uvg_ctx* c, int64_t first, int64_t n, const char* who)
 {
-    if (!c || !out || first < 0 || n < 1) { if (c) c->err = "uvg_debug_pair_counts: bad arguments"; return UVG_EINVAL; }
-    UVG_CUDA(c, cudaSetDevice(c->prm.device));
-    if (c->n_query == 0 || first + n > c->db_n || n > c->score_cap) UVG_FAIL(c, UVG_ESTATE, "uvg_debug_pair_counts: range not resident, too long, or no queries");
+    if (c->world > 1) UVG_FAIL(c, UVG_ESTATE, "%s: not available in sharded mode", who);
+    if (c->n_query == 0 || first + n > c->db_n || n > c->seg_cap) UVG_FAIL(c, UVG_ESTATE, "%s: range not resident, too long, or no queries", who);
+    int rc = sync_all(c);
+    if (rc) return rc;
     PairParams pp{};
-    fill_pair_params(c, pp, first, first + n);
+    fill_pair_params(c, pp, first, first + n, 0, 0);
     pp.early_abort = 0; pp.work = nullptr;
     UVG_CUDA(c, launch_paircount(pp, c->prm.acgt_mode, c->st));
-    UVG_CUDA(c, cudaMemcpy2DAsync(out, (size_t)n * 16, c->d_scores, (size_t)c->score_cap * 16, (size_t)n * 16, (size_t)c->n_query,
-                                  cudaMemcpyDeviceToHost, c->st));
-    UVG_CUDA(c, cudaStreamSynchronize(c->st));
     return UVG_OK;
 }
 
@@ -807,28 +962,36 @@ extern "C" int uvg_debug_pair_counts_rows(uvg_ctx* c, int32_t q_first, int32_t q
 {
     if (!c || !out || first < 0 || n < 1 || q_first < 0 || q_count < 1) { if (c) c->err = "uvg_debug_pair_counts_rows: bad arguments"; return UVG_EINVAL; }
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
-    if (c->n_query == 0 || first + n > c->db_n || n > c->score_cap || q_first + q_count > c->n_query)
-        UVG_FAIL(c, UVG_ESTATE, "uvg_debug_pair_counts_rows: range not resident, too long, or no such queries");
-    PairParams pp{};
-    fill_pair_params(c, pp, first, first + n);
-    pp.early_abort = 0; pp.work = nullptr;
-    UVG_CUDA(c, launch_paircount(pp, c->prm.acgt_mode, c->st));
-    UVG_CUDA(c, cudaMemcpy2DAsync(out, (size_t)n * 16, c->d_scores + (size_t)q_first * c->score_cap, (size_t)c->score_cap * 16,
+    if (q_first + q_count > c->n_query) UVG_FAIL(c, UVG_ESTATE, "uvg_debug_pair_counts_rows: no such queries");
+    int rc = debug_score(c, first, n, "uvg_debug_pair_counts_rows");
+    if (rc) return rc;
+    UVG_CUDA(c, cudaMemcpy2DAsync(out, (size_t)n * 16, c->d_tiles + (size_t)q_first * c->seg_cap, (size_t)c->seg_cap * 16,
                                   (size_t)n * 16, (size_t)q_count, cudaMemcpyDeviceToHost, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
     return UVG_OK;
+}
+
+extern "C" int uvg_debug_pair_counts(uvg_ctx* c, int64_t first, int64_t n, int32_t* out)
+{
+    if (!c) return UVG_EINVAL;
+    return uvg_debug_pair_counts_rows(c, 0, c->n_query, first, n, out);
 }
 
 extern "C" int uvg_debug_ref_meta(uvg_ctx* c, int64_t first, int64_t n, int32_t* non_n, int32_t* c0, int32_t* ci)
 {
     if (!c || first < 0 || n < 1) { if (c) c->err = "uvg_debug_ref_meta: bad arguments"; return UVG_EINVAL; }
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
-    if (c->n_query == 0 || first + n > c->db_n) UVG_FAIL(c, UVG_ESTATE, "uvg_debug_ref_meta: range not resident or no queries");
-    UVG_CUDA(c, launch_consensus(c->d_db, c->d_cons_acgt, c->d_cons_vo, c->Wp, c->prm.acgt_mode, first, first + n, c->d_c0, c->d_ci, c->st));
+    int rc = debug_score(c, first, n, "uvg_debug_ref_meta");
+    if (rc) return rc;
+    std::vector<uint4> cons((size_t)n);
+    UVG_CUDA(c, cudaMemcpyAsync(cons.data(), c->d_tiles + (size_t)c->rows_cap * c->seg_cap, (size_t)n * 16, cudaMemcpyDeviceToHost, c->st));
     if (non_n) UVG_CUDA(c, cudaMemcpyAsync(non_n, c->d_non_n + first, (size_t)n * 4, cudaMemcpyDeviceToHost, c->st));
-    if (c0) UVG_CUDA(c, cudaMemcpyAsync(c0, c->d_c0 + first, (size_t)n * 4, cudaMemcpyDeviceToHost, c->st));
-    if (ci) UVG_CUDA(c, cudaMemcpyAsync(ci, c->d_ci + first, (size_t)n * 4, cudaMemcpyDeviceToHost, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
+    const bool acgt = c->prm.acgt_mode != 0;
+    for (int64_t i = 0; i < n; ++i) {
+        if (c0) c0[i] = (int32_t)cons[i].x;
+        if (ci) ci[i] = acgt ? (int32_t)(cons[i].y - cons[i].x) : (int32_t)(cons[i].w - cons[i].x);
+    }
     return UVG_OK;
 }
 
@@ -838,7 +1001,7 @@ extern "C" int uvg_debug_unpack_ref(uvg_ctx* c, int64_t local, uint8_t* codes_ou
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
     uint8_t* d = nullptr;
     UVG_CUDA(c, cudaMalloc(&d, c->nchar));
-    cudaError_t e = launch_unpack_ref(c->d_db, local, c->nchar, c->Wp, d, c->st);
+    cudaError_t e = launch_unpack_ref(c->d_db, c->d_ramb_off, c->d_ramb_ent, local, c->nchar, c->Wp, d, c->st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(codes_out, d, c->nchar, cudaMemcpyDeviceToHost, c->st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->st);
     cudaFree(d);

@@ -1,17 +1,24 @@
-// K2: pair-count kernels for sm_100a.  Replace the reference's scoring calls
+// K2: pair-count kernel for sm_100a.  Replaces the reference's scoring calls
 //   biomcmc_pairwise_score_matches_truncated_idx   biomcmc alignment.c:855-884   (default mode, x3 per pair)
 //   quick_pairwise_score_acgt_and_valid            src/fastaseq.c:585-596        (--acgt mode)
-//   queue_distance_to_consensus                    src/nearest.c:428-433         (k_consensus)
-//   the 6-tuple assembly of queue_update_min_heaps src/nearest.c:466-470, 499-501
-// by closed-form bit-plane arithmetic: per 32-site column word and (query, reference) pair
-//   P = (ra&qa)|(rc&qc)|(rg&qg)|(rt&qt)      sites whose IUPAC sets intersect     -> partial
-//   V = rv & qv                               both valid                           -> valid
-//   Y = P & ~(r_onehot & q_onehot)            intersecting but not a plain base    -> acgt = P - Y   (rare words only)
-//   E = q_ambiguous & (r == q)                identical ambiguity codes            -> text = acgt + E (rare words only)
-// Lane = 2 references (one of each of the block's two groups; 32 references interleaved per column word -> a group's
-// chunk is one contiguous 4 KB run), warp = 8 queries whose planes are broadcast from shared memory, block = 64 queries
-// x 64 references.  Both operands are staged by TMA bulk copies (cp.async.bulk + mbarrier) through a 4-deep ring, so
-// the inner loop issues only LDS, LOP3 (ALU pipe), POPC (XU pipe) and IMAD (FMA pipe).
+//   queue_distance_to_consensus                    src/nearest.c:428-433         (the consensus is one more query slot)
+//   the count part of queue_update_min_heaps       src/nearest.c:466-470, 499-501
+// by closed-form bit-plane arithmetic.  Per 32-site column word and (query, reference) pair, with the
+// three planes of common.cuh (base = plain base present, b0, b1 = which base):
+//   V = r.base & q.base                         both are plain bases                       -> valid  (3 LOP3 in all)
+//   M = V & ~(r.b0 ^ q.b0) & ~(r.b1 ^ q.b1)     ... and the same base                      -> acgt = text = partial
+// popcount(M) is not taken per word: the M words of a pair go through a carry-save adder tree (Harley-Seal, two LOP3
+// per 3:2 compressor: xor3 = 0x96, majority = 0xE8) that emits one weight-4 word per four column words, so the XU pipe
+// (POPC, 16 lanes/clk/SM) sees 1.25 POPC per pair-word instead of 2 and the ALU pipe 4.5 LOP3 instead of 5; the
+// popcounts are summed by IMAD on the FMA pipe into packed 16-bit counters.
+// Sites where either sequence holds an ambiguity code are outside the planes; their exact contribution to valid /
+// partial / text (never to acgt: alignment.c:871-874 needs a plain base) is added in the epilogue from the sparse
+// (site, code) lists of the reference and of the query.
+// Lane = 2 references (one of each of the block's two groups), warp = 8 query slots whose planes are broadcast from
+// shared memory, block = 64 slots x 64 references.  Both operands are staged by TMA bulk copies (cp.async.bulk +
+// mbarrier) through a 6-deep ring, so the inner loop issues only LDS, LOP3 (ALU), POPC (XU) and IMAD (FMA).
+// The epilogue stores the four counts of every pair straight into the score tile of the rank that owns the query
+// (peer-mapped memory over NVLink when the database is sharded): the all-to-all of the sharded search is fused here.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -40,30 +47,21 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-__device__ __forceinline__ uint32_t plane_any(const uint4& r) { return r.x | r.y | r.z | r.w; }
-__device__ __forceinline__ uint32_t plane_onehot(const uint4& r)
+template <int LUT>
+__device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c)
 {
-    uint32_t multi = (r.x & r.y) | (r.z & r.w) | ((r.x | r.y) & (r.z | r.w));
-    return plane_any(r) & ~multi;
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(d) : "r"(a), "r"(b), "r"(c), "n"(LUT));
+    return d;
 }
-__device__ __forceinline__ uint32_t plane_overlap(const uint4& r, const uint4& q)
+// a & ~(b ^ c): keep the sites of `a` where planes b and c agree
+__device__ __forceinline__ uint32_t keep_eq(uint32_t a, uint32_t b, uint32_t c) { return lop3<0x90>(a, b, c); }
+// 3:2 compressor: (sum, carry) of three bit-vectors
+__device__ __forceinline__ void csa(uint32_t& sum, uint32_t& carry, uint32_t a, uint32_t b, uint32_t c)
 {
-    return (r.x & q.x) | (r.y & q.y) | (r.z & q.z) | (r.w & q.w);
+    carry = lop3<0xE8>(a, b, c);
+    sum = lop3<0x96>(a, b, c);
 }
-__device__ __forceinline__ uint32_t plane_differ(const uint4& r, const uint4& q)
-{
-    return (r.x ^ q.x) | (r.y ^ q.y) | (r.z ^ q.z) | (r.w ^ q.w);
-}
-
-// One pipeline stage: a query chunk (64 queries x WC words) and the same WC words of the block's 64 references.
-struct __align__(16) Stage {
-    QChunk q;
-    uint4  ref[RPL][WC][GROUP];
-};
-constexpr uint32_t STAGE_REF_BYTES = WC * GROUP * sizeof(uint4);
-constexpr size_t PAIR_SMEM = STAGES * sizeof(Stage) + 64 /*barriers*/ + QTILE * sizeof(Threshold);
-constexpr int FLUSH_CHUNKS = 2040 / WC;        // packed 16-bit counters are flushed before they can overflow
-
 // a*b+c on the FMA pipe (IMAD): keeps the accumulations off the ALU pipe that issues the LOP3s
 __device__ __forceinline__ uint32_t imad(uint32_t a, uint32_t b, uint32_t c)
 {
@@ -72,10 +70,20 @@ __device__ __forceinline__ uint32_t imad(uint32_t a, uint32_t b, uint32_t c)
     return d;
 }
 
-// LONG = alignments of 65,536 columns or more (counters may exceed 16 bits): packed counters are flushed into
-// 32-bit totals every FLUSH_CHUNKS chunks.
+// One pipeline stage: a query chunk (64 slots x WC words) and the same WC words of the block's 64 references.
+struct __align__(16) Stage {
+    QChunk q;
+    uint4  ref[RPL][W4][NPLANE][GROUP];
+};
+constexpr uint32_t STAGE_REF_BYTES = W4 * NPLANE * GROUP * sizeof(uint4);
+constexpr size_t PAIR_SMEM = STAGES * sizeof(Stage) + 64 /*barriers*/ + QTILE * sizeof(Threshold);
+constexpr int FLUSH_CHUNKS = 65535 / (WC * 32);        // packed 16-bit counters are flushed before they can overflow
+constexpr int ABORT_EVERY = 4;                         // chunks between two early-abort checks
+
+// MODE 0: default (IUPAC) scoring; MODE 1: --acgt.  LONG = alignments of 65,536 columns or more: the packed counters are
+// flushed into 32-bit totals every FLUSH_CHUNKS chunks.
 template <int MODE, bool LONG>
-__global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams p, const uint32_t k1, const uint32_t k64k)
+__global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams p, const uint32_t k4, const uint32_t k64k)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     Stage* stage = reinterpret_cast<Stage*>(smem);
@@ -86,8 +94,9 @@ __global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams 
     const int qt = blockIdx.x % p.n_qtiles;
     const int64_t group0 = (p.local_begin / (GROUP * RPL) + blockIdx.x / p.n_qtiles) * RPL;
     const QChunk* qsrc = p.qdata + (size_t)qt * p.n_chunks;
-    const uint4* rsrc = p.db + (size_t)group0 * p.Wp * GROUP;
-    const size_t group_stride = (size_t)p.Wp * GROUP;                // uint4 elements between consecutive groups
+    const size_t group_stride = (size_t)(p.Wp / 4) * NPLANE * GROUP;         // uint4 elements between consecutive groups
+    const uint4* rsrc = p.db + (size_t)group0 * group_stride;
+    const int owner = qt % p.world, row0 = (qt / p.world) * QTILE;           // where this query tile's rows live
     bool in_range[RPL];
     int64_t local[RPL];
 #pragma unroll
@@ -100,51 +109,35 @@ __global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams 
         for (int s = 0; s < STAGES; ++s) mbar_init(full + s, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    {
-        const uint4* tsrc = reinterpret_cast<const uint4*>(p.thr + (size_t)qt * QTILE);
-        uint4* tdst = reinterpret_cast<uint4*>(s_thr);
-        for (int i = threadIdx.x; i < (int)(QTILE * sizeof(Threshold) / 16); i += blockDim.x) tdst[i] = tsrc[i];
-    }
+    if (threadIdx.x < QTILE) s_thr[threadIdx.x] = p.thr[(size_t)owner * p.rows_cap + row0 + threadIdx.x];
     __syncthreads();
     auto issue = [&](int c, int s) {
         mbar_expect_tx(full + s, (uint32_t)(sizeof(QChunk) + RPL * STAGE_REF_BYTES));
         bulk_g2s(&stage[s].q, qsrc + c, (uint32_t)sizeof(QChunk), full + s);
 #pragma unroll
         for (int g = 0; g < RPL; ++g)
-            bulk_g2s(&stage[s].ref[g][0][0], rsrc + g * group_stride + (size_t)c * WC * GROUP, STAGE_REF_BYTES, full + s);
+            bulk_g2s(&stage[s].ref[g][0][0][0], rsrc + g * group_stride + (size_t)c * (W4 * NPLANE * GROUP), STAGE_REF_BYTES, full + s);
     };
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES && s < p.n_chunks; ++s) issue(s, s);
     }
 
-    uint32_t accPV[RPL][QPW], accYE[RPL][QPW];                 // packed: P | V << 16  and  Y | E << 16
-    int32_t tot[LONG ? 4 : 1][RPL][QPW];
+    // carry-save accumulators of the match words (weights 1 and 2) and packed counters: acc = M4 | V << 16 where M4 counts
+    // the weight-4 carries (already multiplied by 4); accI (--acgt): mismatches on segregating sites
+    uint32_t ones[RPL][QPW], twos[RPL][QPW], acc[RPL][QPW], accI[MODE == 1 ? RPL : 1][MODE == 1 ? QPW : 1] = {};
+    int32_t tot[LONG ? 3 : 1][LONG ? RPL : 1][LONG ? QPW : 1] = {};
 #pragma unroll
     for (int g = 0; g < RPL; ++g)
 #pragma unroll
         for (int j = 0; j < QPW; ++j) {
-            accPV[g][j] = 0; accYE[g][j] = 0;
-#pragma unroll
-            for (int k = 0; k < (LONG ? 4 : 1); ++k) tot[k][g][j] = 0;
+            ones[g][j] = 0; twos[g][j] = 0; acc[g][j] = 0;
+            if constexpr (MODE == 1) accI[g][j] = 0;
+            if constexpr (LONG) { tot[0][g][j] = 0; tot[1][g][j] = 0; tot[2][g][j] = 0; }
         }
-    auto flush = [&]() {
-        if (LONG) {
-#pragma unroll
-            for (int g = 0; g < RPL; ++g)
-#pragma unroll
-                for (int j = 0; j < QPW; ++j) {
-                    tot[0][g][j] += accPV[g][j] & 0xffffu; tot[LONG ? 1 : 0][g][j] += accPV[g][j] >> 16;
-                    tot[LONG ? 2 : 0][g][j] += accYE[g][j] & 0xffffu; tot[LONG ? 3 : 0][g][j] += accYE[g][j] >> 16;
-                    accPV[g][j] = 0; accYE[g][j] = 0;
-                }
-        }
-    };
-    auto cntP = [&](int g, int j) { return (int32_t)(accPV[g][j] & 0xffffu) + (LONG ? tot[0][g][j] : 0); };
-    auto cntV = [&](int g, int j) { return (int32_t)(accPV[g][j] >> 16) + (LONG ? tot[LONG ? 1 : 0][g][j] : 0); };
-    auto cntY = [&](int g, int j) { return (int32_t)(accYE[g][j] & 0xffffu) + (LONG ? tot[LONG ? 2 : 0][g][j] : 0); };
-    auto cntE = [&](int g, int j) { return (int32_t)(accYE[g][j] >> 16) + (LONG ? tot[LONG ? 3 : 0][g][j] : 0); };
+    auto cntM4 = [&](int g, int j) { return (int32_t)(acc[g][j] & 0xffffu) + (LONG ? tot[0][LONG ? g : 0][LONG ? j : 0] : 0); };
+    auto cntV = [&](int g, int j) { return (int32_t)(acc[g][j] >> 16) + (LONG ? tot[LONG ? 1 : 0][LONG ? g : 0][LONG ? j : 0] : 0); };
+    auto cntI = [&](int g, int j) { return (int32_t)(accI[MODE == 1 ? g : 0][MODE == 1 ? j : 0]) + (LONG ? tot[LONG ? 2 : 0][LONG ? g : 0][LONG ? j : 0] : 0); };
 
-    const uint32_t* ambp = p.refamb + (size_t)group0 * p.ambw;
     const int q0 = warp * QPW;
     bool warp_dead = false;
     uint32_t executed = 0;
@@ -155,67 +148,73 @@ __global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams 
         const Stage& st = stage[s];
         if (!warp_dead) {
             ++executed;
-            uint32_t ambbits = 0;
-            if (MODE == 0) {
 #pragma unroll
-                for (int g = 0; g < RPL; ++g) ambbits |= (__ldg(ambp + g * p.ambw + ((c * WC) >> 5)) >> ((c * WC) & 31)) & ((1u << WC) - 1u);
-            }
+            for (int u = 0; u < W4; ++u) {
+                uint4 rb[RPL], r0[RPL], r1[RPL];
 #pragma unroll
-            for (int wl = 0; wl < WC; ++wl) {
-                uint4 r[RPL];
-                uint32_t rv[RPL];
+                for (int g = 0; g < RPL; ++g) { rb[g] = st.ref[g][u][0][lane]; r0[g] = st.ref[g][u][1][lane]; r1[g] = st.ref[g][u][2][lane]; }
 #pragma unroll
-                for (int g = 0; g < RPL; ++g) { r[g] = st.ref[g][wl][lane]; rv[g] = plane_any(r[g]); }
-                const bool slow = (MODE == 0) && ((((st.q.slow[wl] >> warp) | (ambbits >> wl)) & 1u) != 0u);
-                if (!slow) {
-#pragma unroll
-                    for (int j = 0; j < QPW; ++j) {
-                        const uint4 q = st.q.acgt[wl][q0 + j];
-                        const uint2 vo = st.q.vo[wl][q0 + j];
-#pragma unroll
-                        for (int g = 0; g < RPL; ++g) {
-                            const uint32_t P = plane_overlap(r[g], q);
-                            const uint32_t V = rv[g] & vo.x;
-                            accPV[g][j] = imad(__popc(V), k64k, imad(__popc(P), k1, accPV[g][j]));
-                            if (MODE == 1) accYE[g][j] = imad(__popc(V & ~P & vo.y), k1, accYE[g][j]);   // mismatches on idx sites
-                        }
-                    }
-                } else {
+                for (int j = 0; j < QPW; ++j) {
+                    const uint4 qb = st.q.pl[u][q0 + j][0], qx = st.q.pl[u][q0 + j][1], qy = st.q.pl[u][q0 + j][2];
+                    uint4 qi = make_uint4(0u, 0u, 0u, 0u);
+                    if constexpr (MODE == 1) qi = st.q.pl[u][q0 + j][3];
 #pragma unroll
                     for (int g = 0; g < RPL; ++g) {
-                        const uint32_t rone = plane_onehot(r[g]);
-#pragma unroll
-                        for (int j = 0; j < QPW; ++j) {
-                            const uint4 q = st.q.acgt[wl][q0 + j];
-                            const uint2 vo = st.q.vo[wl][q0 + j];
-                            const uint32_t P = plane_overlap(r[g], q);
-                            const uint32_t V = rv[g] & vo.x;
-                            accPV[g][j] += __popc(P) + (__popc(V) << 16);
-                            accYE[g][j] += __popc(P & ~(rone & vo.y)) + (__popc(vo.x & ~vo.y & ~plane_differ(r[g], q)) << 16);
+                        const uint32_t V0 = rb[g].x & qb.x, V1 = rb[g].y & qb.y, V2 = rb[g].z & qb.z, V3 = rb[g].w & qb.w;
+                        const uint32_t M0 = keep_eq(keep_eq(V0, r0[g].x, qx.x), r1[g].x, qy.x);
+                        const uint32_t M1 = keep_eq(keep_eq(V1, r0[g].y, qx.y), r1[g].y, qy.y);
+                        const uint32_t M2 = keep_eq(keep_eq(V2, r0[g].z, qx.z), r1[g].z, qy.z);
+                        const uint32_t M3 = keep_eq(keep_eq(V3, r0[g].w, qx.w), r1[g].w, qy.w);
+                        uint32_t o = ones[g][j], ta, tb, f, t;
+                        csa(o, ta, o, M0, M1);
+                        csa(o, tb, o, M2, M3);
+                        csa(t, f, twos[g][j], ta, tb);
+                        ones[g][j] = o; twos[g][j] = t;
+                        uint32_t a = acc[g][j];
+                        a = imad(__popc(f), k4, a);
+                        a = imad(__popc(V0), k64k, a);
+                        a = imad(__popc(V1), k64k, a);
+                        a = imad(__popc(V2), k64k, a);
+                        a = imad(__popc(V3), k64k, a);
+                        acc[g][j] = a;
+                        if constexpr (MODE == 1) {
+                            // mismatches on the segregating (idx) sites: valid, not equal, inside the mask
+                            const uint32_t I0 = lop3<0x20>(V0, M0, qi.x), I1 = lop3<0x20>(V1, M1, qi.y);
+                            const uint32_t I2 = lop3<0x20>(V2, M2, qi.z), I3 = lop3<0x20>(V3, M3, qi.w);
+                            accI[MODE == 1 ? g : 0][MODE == 1 ? j : 0] += __popc(I0) + __popc(I1) + __popc(I2) + __popc(I3);
                         }
                     }
                 }
             }
-            if (LONG && (c + 1) % FLUSH_CHUNKS == 0) flush();
-            if (p.early_abort) {
-                // exact: a pair that can no longer satisfy the admission staircase is never a survivor.  Mismatches so
-                // far only grow along the genome and the best reachable ACGT count is what is left of the query.
+            if constexpr (LONG) if ((c + 1) % FLUSH_CHUNKS == 0) {
+#pragma unroll
+                for (int g = 0; g < RPL; ++g)
+#pragma unroll
+                    for (int j = 0; j < QPW; ++j) {
+                        tot[0][LONG ? g : 0][LONG ? j : 0] += acc[g][j] & 0xffffu; tot[LONG ? 1 : 0][LONG ? g : 0][LONG ? j : 0] += acc[g][j] >> 16;
+                        acc[g][j] = 0;
+                        if constexpr (MODE == 1) { tot[LONG ? 2 : 0][LONG ? g : 0][LONG ? j : 0] += accI[MODE == 1 ? g : 0][MODE == 1 ? j : 0]; accI[MODE == 1 ? g : 0][MODE == 1 ? j : 0] = 0; }
+                    }
+            }
+            if (p.early_abort && (c % ABORT_EVERY) == ABORT_EVERY - 1) {
+                // exact: mismatches only grow along the genome (ambiguity sites add to valid, never to acgt), and the ACGT
+                // count can grow by at most what is left of the query.  96 = the most the carry-save registers can hold.
                 bool dead = true;
 #pragma unroll
                 for (int g = 0; g < RPL; ++g) {
                     if (!in_range[g]) continue;
 #pragma unroll
                     for (int j = 0; j < QPW; ++j) {
-                        const Threshold& t = s_thr[q0 + j];
-                        if (!t.full) { dead = false; continue; }
-                        const int32_t dsofar = (MODE == 0) ? (cntV(g, j) - cntP(g, j) + cntY(g, j)) : (cntV(g, j) - cntP(g, j));
-                        if (dsofar < t.dmax && cntP(g, j) + (int32_t)st.q.rem[q0 + j] >= t.bar[dsofar >> (t.full - 1)]) dead = false;
+                        if (qt * QTILE + q0 + j >= p.n_slots) continue;          // padding slot
+                        const Threshold t = s_thr[q0 + j];
+                        const int32_t m_ub = cntM4(g, j) + 96;
+                        if (!t.full || (cntV(g, j) - m_ub < t.dmax && m_ub + (int32_t)st.q.rem[q0 + j] >= t.root_s0)) dead = false;
                     }
                 }
                 warp_dead = __all_sync(0xffffffffu, dead);
             }
         }
-        const int all_dead = __syncthreads_and(warp_dead ? 1 : 0);
+        const int all_dead = p.early_abort ? __syncthreads_and(warp_dead ? 1 : 0) : (__syncthreads(), 0);
         if (all_dead) break;
         if (threadIdx.x == 0 && c + STAGES < p.n_chunks) issue(c + STAGES, s);
     }
@@ -225,55 +224,64 @@ __global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams 
         for (int cc = c + 1; cc < p.n_chunks && cc < c + STAGES; ++cc) mbar_wait(full + cc % STAGES, (uint32_t)((cc / STAGES) & 1));
     }
 
-    // ---- epilogue: the four counts of every pair go to the dense score tile of the round (coalesced 512 B per warp
-    // and query); the replay kernel assembles the 6-tuple (src/nearest.c:466-470, 499-501) for the pairs it admits.
-    // Aborted pairs get a sentinel whose mismatch count can never pass the admission test.
+    // ---- epilogue: exact contribution of the ambiguity codes, then the four counts of every pair go to the dense score
+    // tile of the round on the rank that owns the query (coalesced 512 B per warp and query).  The replay kernel
+    // assembles the 6-tuple (src/nearest.c:466-470, 499-501) for the pairs it admits.  Aborted pairs get a sentinel whose
+    // mismatch count can never pass the admission test.
+    const uint32_t* dbw = reinterpret_cast<const uint32_t*>(p.db);
 #pragma unroll
-    for (int g = 0; g < RPL; ++g) {
-        if (!in_range[g]) continue;
-        uint4* out = p.scores + p.score_col0 + (local[g] - p.local_begin);
+    for (int j = 0; j < QPW; ++j) {
+        const int slot = qt * QTILE + q0 + j;
+        if (slot >= p.n_slots) continue;
+        const bool is_cons = slot == p.n_slots - 1;
+        uint32_t qe0 = 0, qe1 = 0;
+        if (MODE == 0) { qe0 = p.qamb_off[slot]; qe1 = p.qamb_off[slot + 1]; }
 #pragma unroll
-        for (int j = 0; j < QPW; ++j) {
-            const int q = qt * QTILE + q0 + j;
-            if (q >= p.n_query) continue;
+        for (int g = 0; g < RPL; ++g) {
+            if (!in_range[g]) continue;
             uint4 v;
             if (warp_dead) {
                 v = (MODE == 0) ? make_uint4(0u, 0u, 0u, 0x7fffffffu) : make_uint4(0u, 0x7fffffffu, 0u, 0u);
-            } else if (MODE == 0) {
-                const int32_t A = cntP(g, j) - cntY(g, j);
-                v = make_uint4((uint32_t)A, (uint32_t)(A + cntE(g, j)), (uint32_t)cntP(g, j), (uint32_t)cntV(g, j));
             } else {
-                v = make_uint4((uint32_t)cntP(g, j), (uint32_t)cntV(g, j), (uint32_t)cntY(g, j), 0u);
+                const int32_t M = cntM4(g, j) + __popc(ones[g][j]) + 2 * __popc(twos[g][j]);
+                const int32_t V = cntV(g, j);
+                if (MODE == 0) {
+                    int32_t dv = 0, dp = 0, dt = 0;
+                    // (b) sites where the REFERENCE holds an ambiguity code: look the query's code up
+                    const uint32_t re1 = p.ramb_off[local[g] + 1];
+                    for (uint32_t e = p.ramb_off[local[g]]; e < re1; ++e) {
+                        const uint32_t ent = __ldg(p.ramb_ent + e), site = ent & AMB_SITE_MASK, rc = ent >> 28;
+                        const uint32_t qc = (__ldg(p.qnib + (size_t)slot * p.qnib_stride + (site >> 3)) >> ((site & 7u) * 4u)) & 15u;
+                        dv += qc != 0u; dp += (qc & rc) != 0u; dt += qc == rc;
+                    }
+                    // (c) sites where the QUERY holds an ambiguity code and the reference a plain base
+                    for (uint32_t e = qe0; e < qe1; ++e) {
+                        const uint32_t ent = __ldg(p.qamb_ent + e), site = ent & AMB_SITE_MASK, qc = ent >> 28;
+                        const uint32_t w = site >> 5, b = site & 31u;
+                        const size_t base = db_unit_index(group0 + g, (int)(w >> 2), 0, lane, p.Wp) * 4 + (w & 3u);
+                        if ((__ldg(dbw + base) >> b) & 1u) {
+                            const uint32_t x = (__ldg(dbw + base + GROUP * 4) >> b) & 1u, y = (__ldg(dbw + base + 2 * GROUP * 4) >> b) & 1u;
+                            dv += 1; dp += (qc >> (x + 2u * y)) & 1u;
+                        }
+                    }
+                    v = make_uint4((uint32_t)M, (uint32_t)(M + dt), (uint32_t)(M + dp), (uint32_t)(V + dv));
+                } else {
+                    v = make_uint4((uint32_t)M, (uint32_t)V, (uint32_t)cntI(g, j), 0u);
+                }
             }
-            out[(size_t)q * p.score_stride] = v;
+            const int64_t col = p.col0 + (local[g] - p.local_begin);
+            if (!is_cons) {
+                p.out[owner][(size_t)(row0 + q0 + j) * p.row_stride + col] = v;
+            } else {
+                // the consensus counts and the per-reference record are needed by every rank's replay
+                const uint4 meta = make_uint4((uint32_t)p.non_n[local[g]], 0u, 0u, 0u);
+                for (int r = 0; r < p.world; ++r) {
+                    p.out[r][(size_t)p.rows_cap * p.row_stride + col] = v;
+                    p.out[r][(size_t)(p.rows_cap + 1) * p.row_stride + col] = meta;
+                }
+            }
         }
     }
-}
-
-// ---- consensus stage: one warp per group -------------------------------------------------------------------------
-template <int MODE>
-__global__ void __launch_bounds__(256) k_consensus(const uint4* __restrict__ db, const uint4* __restrict__ cons_acgt,
-                                                   const uint2* __restrict__ cons_vo, int Wp, int64_t local_begin, int64_t local_end,
-                                                   int32_t* __restrict__ c0, int32_t* __restrict__ ci)
-{
-    const int lane = threadIdx.x & 31;
-    const int64_t wid = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const int64_t group = local_begin / GROUP + wid;
-    const int64_t local = group * GROUP + lane;
-    if (group * GROUP >= local_end) return;
-    const uint4* rp = db + (size_t)group * Wp * GROUP + lane;
-    int32_t m = 0, v = 0;
-#pragma unroll 4
-    for (int w = 0; w < Wp; ++w) {
-        const uint4 r = __ldg(rp + (size_t)w * GROUP);
-        const uint4 q = __ldg(cons_acgt + w);
-        const uint2 vo = __ldg(cons_vo + w);
-        const uint32_t P = plane_overlap(r, q);
-        v += __popc(plane_any(r) & vo.x);
-        if (MODE == 0) m += __popc(P & plane_onehot(r) & vo.y);       // cons == r and r is a plain base
-        else m += __popc(P);
-    }
-    if (local >= local_begin && local < local_end) { c0[local] = m; ci[local] = v - m; }
 }
 
 cudaError_t paircount_setup()
@@ -293,25 +301,14 @@ cudaError_t launch_paircount(const PairParams& p, int acgt_mode, cudaStream_t st
     const int64_t blocks = (g1 - g0) * p.n_qtiles;
     if (blocks > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
     const bool lng = (int64_t)p.Wp * 32 > 65535;
-    const uint32_t k1 = 1u, k64k = 65536u;
+    const uint32_t k4 = 4u, k64k = 65536u;       // passed at run time so that the compiler keeps IMAD (no shift/add on the ALU pipe)
     if (acgt_mode) {
-        if (lng) k_paircount<1, true><<<(unsigned)blocks, PAIR_THREADS, PAIR_SMEM, st>>>(p, k1, k64k);
-        else k_paircount<1, false><<<(unsigned)blocks, PAIR_THREADS, PAIR_SMEM, st>>>(p, k1, k64k);
+        if (lng) k_paircount<1, true><<<(unsigned)blocks, PAIR_THREADS, PAIR_SMEM, st>>>(p, k4, k64k);
+        else k_paircount<1, false><<<(unsigned)blocks, PAIR_THREADS, PAIR_SMEM, st>>>(p, k4, k64k);
     } else {
-        if (lng) k_paircount<0, true><<<(unsigned)blocks, PAIR_THREADS, PAIR_SMEM, st>>>(p, k1, k64k);
-        else k_paircount<0, false><<<(unsigned)blocks, PAIR_THREADS, PAIR_SMEM, st>>>(p, k1, k64k);
+        if (lng) k_paircount<0, true><<<(unsigned)blocks, PAIR_THREADS, PAIR_SMEM, st>>>(p, k4, k64k);
+        else k_paircount<0, false><<<(unsigned)blocks, PAIR_THREADS, PAIR_SMEM, st>>>(p, k4, k64k);
     }
-    return cudaGetLastError();
-}
-
-cudaError_t launch_consensus(const uint4* db, const uint4* cons_acgt, const uint2* cons_vo, int Wp, int acgt_mode,
-                             int64_t local_begin, int64_t local_end, int32_t* c0, int32_t* ci, cudaStream_t st)
-{
-    if (local_end <= local_begin) return cudaSuccess;
-    const int64_t g0 = local_begin / GROUP, g1 = (local_end + GROUP - 1) / GROUP;
-    const int64_t blocks = (g1 - g0 + 7) / 8;
-    if (acgt_mode) k_consensus<1><<<(unsigned)blocks, 256, 0, st>>>(db, cons_acgt, cons_vo, Wp, local_begin, local_end, c0, ci);
-    else k_consensus<0><<<(unsigned)blocks, 256, 0, st>>>(db, cons_acgt, cons_vo, Wp, local_begin, local_end, c0, ci);
     return cudaGetLastError();
 }
 
