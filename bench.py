@@ -345,12 +345,20 @@ def main():
             eng.clear_refs()
             eng.set_queries(qtext)
             o = 0
-            for gb, cnt in tiles:
-                eng.push_refs_ptr(host_buf + o * L, cnt, 0)
-                o += cnt
-            if world > 1:
+            if world == 1:
+                # pipelined host loop (the reference's pool loop, nearest.c:245-338): the copy + encoder of piece i+1 run
+                # under the search rounds of piece i
+                for s0 in range(0, n_local, 65536):
+                    m = min(65536, n_local - s0)
+                    eng.push_refs_ptr(host_buf + s0 * L, m, 0)
+                    eng.search_async()
+                eng.wait()
+            else:
+                for gb, cnt in tiles:
+                    eng.push_refs_ptr(host_buf + o * L, cnt, 0)
+                    o += cnt
                 eng.set_global_count(R)
-            eng.search()
+                eng.search()
             heaps = eng.heaps()
             barrier()
             if i > 0:

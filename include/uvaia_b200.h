@@ -90,8 +90,8 @@ int uvg_set_queries(uvg_ctx* ctx, const uint8_t* text, int32_t n_query, uvg_quer
 /* ---- references: replaces quick_count_sequence_non_N + the ref filter (nearest.c:263-270) + the char2bit lookups.
  * text = n rows of nchar bytes (host memory; pinned memory makes the copy asynchronous).  Each row gets
  * non_n_out[i] = #bytes not in "NnXx-?Oo." over the whole row and accepted_out[i] = (non_n >= min_non_n);
- * accepted rows are appended, in order, to the device-resident packed database (4-bit IUPAC sets as four
- * bit-planes, 32 references interleaved per 16-byte column word).  Either output pointer may be NULL.
+ * accepted rows are appended, in order, to the device-resident packed database (4-bit IUPAC sets as three
+ * bit-planes + a sparse list of ambiguity codes, 32 references interleaved per 16-byte unit: DESIGN.md 3).  Either output pointer may be NULL.
  * *n_accepted (may be NULL) receives the number appended. */
 int uvg_push_refs(uvg_ctx* ctx, const uint8_t* text, int64_t n, int32_t min_non_n,
                   int32_t* non_n_out, uint8_t* accepted_out, int64_t* n_accepted);
@@ -108,6 +108,11 @@ int64_t uvg_db_count(const uvg_ctx* ctx);              /* accepted references re
  * Scores every resident reference not scored yet against every query, in file order, in rounds.  Bit-exact with
  * the reference's sequential admission (order-dependent max_incompatible rule and first-come tie-break). */
 int uvg_search(uvg_ctx* ctx);
+/* Pipelined hosts: uvg_search_async enqueues the rounds for the references pushed so far and returns at once, so that
+ * the next uvg_push_refs (host->device copy + encoder, on their own streams) runs under them; uvg_wait blocks until
+ * everything enqueued has finished (uvg_search = uvg_search_async + uvg_wait).  Results and statistics wait implicitly. */
+int uvg_search_async(uvg_ctx* ctx);
+int uvg_wait(uvg_ctx* ctx);
 /* Empty all heaps and mark every resident reference as not scored (repeat a search over the same database). */
 int uvg_reset_search(uvg_ctx* ctx);
 

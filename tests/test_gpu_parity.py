@@ -215,15 +215,26 @@ def test_streaming_push_search_drop_equals_resident_search():
     L = 1200
     qn, Q, rn, R = make_inputs(L, 20, 4000, 41, 0.05, 0.02)
     names, Qo, *_ = orc.prepare_queries(qn, [q.tobytes() for q in Q], 0, False, 0.5)
-    with Engine(L, nbest=15, first_round=64, max_round=1024) as a, Engine(L, nbest=15) as b:
+    with Engine(L, nbest=15, first_round=64, max_round=1024) as a, Engine(L, nbest=15) as b, Engine(L, nbest=15, first_round=32, max_round=256) as p:
         a.set_queries(Qo)
         b.set_queries(Qo)
+        p.set_queries(Qo)
         a.push_refs(R, 600)
         a.search()
         for s in range(0, len(R), 333):
             b.push_refs(R[s:s + 333], 600)
             b.search()
             b.drop_refs()
+        # pipelined host: the next push (copy + encoder) runs under the rounds enqueued by search_async
+        for s in range(0, len(R), 700):
+            p.push_refs(R[s:s + 700], 600)
+            p.search_async()
+        p.wait()
+        for iq in range(len(names)):
+            sa, ra = a.heap(iq)
+            sp, rp = p.heap(iq)
+            assert np.array_equal(sa, sp) and np.array_equal(ra, rp)
+        assert np.array_equal(a.ever_best(0, a.db_count), p.ever_best(0, a.db_count))
         for iq in range(len(names)):
             sa, ra = a.heap(iq)
             sb, rb = b.heap(iq)

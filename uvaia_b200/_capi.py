@@ -52,6 +52,8 @@ SYMBOLS = {
     "uvg_clear_refs": (C.c_int, [_P]),
     "uvg_db_count": (C.c_int64, [_P]),
     "uvg_search": (C.c_int, [_P]),
+    "uvg_search_async": (C.c_int, [_P]),
+    "uvg_wait": (C.c_int, [_P]),
     "uvg_reset_search": (C.c_int, [_P]),
     "uvg_get_heap": (C.c_int, [_P, C.c_int32, C.POINTER(uvg_item), C.POINTER(C.c_int32)]),
     "uvg_get_ever_best": (C.c_int, [_P, C.c_int64, C.c_int64, _P]),

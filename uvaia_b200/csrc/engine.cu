@@ -66,8 +66,11 @@ struct uvg_ctx {
     std::string err;
     int K = 0, nchar = 0, trim = 0, W = 0, Wp = 0, n_chunks = 0;
     int rank = 0, world = 1;
-    cudaStream_t st = nullptr, st_rp = nullptr;
+    cudaStream_t st = nullptr, st_rp = nullptr, st_push = nullptr, st_copy = nullptr;
     cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_d = nullptr;
+    cudaEvent_t ev_copied[2]{}, ev_stage_free[2]{};  // host->device staging ring of uvg_push_refs
+    bool search_open = false;                         // rounds enqueued by uvg_search_async and not yet waited for
+    size_t n_ev = 0;
     cudaEvent_t ev_pair[NBUF]{}, ev_replay[NBUF]{}, ev_ag[NBUF]{};
     // queries
     int n_query = 0, n_slots = 0, n_qtiles = 0, rows_cap = 0, qnib_stride = 0;
@@ -95,7 +98,7 @@ struct uvg_ctx {
     unsigned long long* h_pinned = nullptr;           // small pinned read-back area
     void* d_ipc = nullptr;                            // staging for the handle exchange
     // push staging
-    uint8_t* d_stage_text = nullptr; size_t stage_text_bytes = 0;
+    uint8_t* d_stage_text[2]{}; size_t stage_text_bytes = 0;
     int32_t *d_stage_nn = nullptr, *d_stage_namb = nullptr; uint8_t* d_stage_acc = nullptr; int64_t* d_stage_dst = nullptr; int64_t stage_rows = 0;
     int64_t* d_nacc = nullptr;
     // round schedule
@@ -107,7 +110,7 @@ struct uvg_ctx {
     // nccl
     ncclComm_t comm = nullptr;
     // host cache of the heaps (filled lazily by uvg_get_heap, invalidated by every search / reset)
-    int64_t work_base = 0;
+    int64_t work_seen = 0, work_last = 0;
     bool heaps_cached = false;
     std::vector<HeapItem> h_heaps; std::vector<int32_t> h_heap_n, h_max_inc;
 };
@@ -172,6 +175,12 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
     CK_(cudaDeviceGetStreamPriorityRange(&lo, &hi));
     CK_(cudaStreamCreateWithPriority(&c->st, cudaStreamNonBlocking, lo));
     CK_(cudaStreamCreateWithPriority(&c->st_rp, cudaStreamNonBlocking, hi));       // the short replay / collective work goes first
+    CK_(cudaStreamCreateWithPriority(&c->st_push, cudaStreamNonBlocking, hi));     // encoder: short memory-bound kernels
+    CK_(cudaStreamCreateWithFlags(&c->st_copy, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) {
+        CK_(cudaEventCreateWithFlags(&c->ev_copied[b], cudaEventDisableTiming));
+        CK_(cudaEventCreateWithFlags(&c->ev_stage_free[b], cudaEventDisableTiming));
+    }
     CK_(cudaEventCreate(&c->ev_a)); CK_(cudaEventCreate(&c->ev_b)); CK_(cudaEventCreate(&c->ev_c)); CK_(cudaEventCreate(&c->ev_d));
     for (int b = 0; b < NBUF; ++b) {
         CK_(cudaEventCreateWithFlags(&c->ev_pair[b], cudaEventDisableTiming));
@@ -219,11 +228,13 @@ extern "C" void uvg_destroy(uvg_ctx* c)
     cudaSetDevice(c->prm.device);
     if (c->st) cudaStreamSynchronize(c->st);
     if (c->st_rp) cudaStreamSynchronize(c->st_rp);
+    if (c->st_push) cudaStreamSynchronize(c->st_push);
+    if (c->st_copy) cudaStreamSynchronize(c->st_copy);
     free_queries(c);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->d_db); cudaFree(c->d_non_n); cudaFree(c->d_ramb_off); cudaFree(c->d_ramb_ent); cudaFree(c->d_ever);
     cudaFree(c->d_counters); cudaFree(c->d_nacc); cudaFree(c->d_ipc);
-    cudaFree(c->d_stage_text); cudaFree(c->d_stage_nn); cudaFree(c->d_stage_namb); cudaFree(c->d_stage_acc); cudaFree(c->d_stage_dst);
+    cudaFree(c->d_stage_text[0]); cudaFree(c->d_stage_text[1]); cudaFree(c->d_stage_nn); cudaFree(c->d_stage_namb); cudaFree(c->d_stage_acc); cudaFree(c->d_stage_dst);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (auto& pr : c->pair_events) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
     if (c->ev_a) { cudaEventDestroy(c->ev_a); cudaEventDestroy(c->ev_b); cudaEventDestroy(c->ev_c); cudaEventDestroy(c->ev_d); }
@@ -232,8 +243,14 @@ extern "C" void uvg_destroy(uvg_ctx* c)
         if (c->ev_replay[b]) cudaEventDestroy(c->ev_replay[b]);
         if (c->ev_ag[b]) cudaEventDestroy(c->ev_ag[b]);
     }
+    for (int b = 0; b < 2; ++b) {
+        if (c->ev_copied[b]) cudaEventDestroy(c->ev_copied[b]);
+        if (c->ev_stage_free[b]) cudaEventDestroy(c->ev_stage_free[b]);
+    }
     if (c->st) cudaStreamDestroy(c->st);
     if (c->st_rp) cudaStreamDestroy(c->st_rp);
+    if (c->st_push) cudaStreamDestroy(c->st_push);
+    if (c->st_copy) cudaStreamDestroy(c->st_copy);
     delete c;
 }
 
@@ -241,6 +258,8 @@ static int sync_all(uvg_ctx* c)
 {
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st_rp));
+    UVG_CUDA(c, cudaStreamSynchronize(c->st_push));
+    UVG_CUDA(c, cudaStreamSynchronize(c->st_copy));
     return UVG_OK;
 }
 
@@ -264,7 +283,7 @@ static int reset_heaps(uvg_ctx* c)
     UVG_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 64, c->st));
     if (c->d_ever && c->ever_cap) UVG_CUDA(c, cudaMemsetAsync(c->d_ever, 0, c->ever_cap, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));                              // `init` goes out of scope
-    c->db_scored = 0; c->heaps_cached = false;
+    c->db_scored = 0; c->heaps_cached = false; c->work_seen = 0; c->search_open = false; c->n_ev = 0;
     c->rounds_done = 0; c->round_local_start = 0; c->round_global_start = 0;
     c->next_round = round_size_first(c->prm);
     uvg_stats z{};
@@ -293,19 +312,26 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     std::vector<uint8_t> cons(L, 'N');
     std::vector<uint8_t> site_class(L, 0);                                  // 1 = idx, 2 = idx_m, 3 = idx_c
     int n_idx = 0, n_idx_m = 0, n_idx_c = 0;
-    for (int i = trim; i < L - trim; ++i) {
-        uint8_t first = 0; bool any = false, all = true, same = true;
+    {
+        // row-major sweep (one pass over the query text): per site the first usable byte, whether any / all queries are
+        // usable and whether the usable ones agree
+        std::vector<uint8_t> first(L, 0), any(L, 0), all(L, 1), same(L, 1);
         for (int q = 0; q < Q; ++q) {
-            uint8_t ch = up[text[(size_t)q * L + i]];
-            bool usable = acgt ? (ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T') : (lut[2][ch] != 0);
-            if (!usable) { all = false; continue; }
-            if (!any) { any = true; first = ch; }
-            else if (ch != first) same = false;
+            const uint8_t* row = text + (size_t)q * L;
+            for (int i = trim; i < L - trim; ++i) {
+                const uint8_t ch = up[row[i]];
+                const bool usable = acgt ? (ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T') : (lut[2][ch] != 0);
+                if (!usable) { all[i] = 0; continue; }
+                if (!any[i]) { any[i] = 1; first[i] = ch; }
+                else if (ch != first[i]) same[i] = 0;
+            }
         }
-        if (!any) continue;
-        if (!same) { site_class[i] = 1; ++n_idx; cons[i] = '#'; }
-        else if (all) { site_class[i] = 3; ++n_idx_c; cons[i] = first; }
-        else { site_class[i] = 2; ++n_idx_m; cons[i] = first; }
+        for (int i = trim; i < L - trim; ++i) {
+            if (!any[i]) continue;
+            if (!same[i]) { site_class[i] = 1; ++n_idx; cons[i] = '#'; }
+            else if (all[i]) { site_class[i] = 3; ++n_idx_c; cons[i] = first[i]; }
+            else { site_class[i] = 2; ++n_idx_m; cons[i] = first[i]; }
+        }
     }
     c->n_query = Q;
     c->n_slots = Q + 1;                                                     // + the consensus pseudo-query (nearest.c:428-433)
@@ -421,18 +447,21 @@ static cudaError_t grow_array(T** ptr, size_t old_count, size_t new_count, bool 
     return cudaSuccess;
 }
 
+// Growing a device array moves it: nothing may be in flight (a host that reserves db_capacity never pays for this).
 static int ensure_db_capacity(uvg_ctx* c, int64_t need_refs)
 {
     if (need_refs <= c->db_cap) return UVG_OK;
+    int rc = sync_all(c);
+    if (rc) return rc;
     int64_t cap = std::max<int64_t>(need_refs, c->db_cap * 2);
     cap = std::max<int64_t>(cap, c->prm.db_capacity);
     cap = std::max<int64_t>(cap, 4096);
     cap = (cap + GROUP * RPL - 1) / (GROUP * RPL) * (GROUP * RPL);
     const size_t per_group = (size_t)(c->Wp / 4) * NPLANE * GROUP;            // uint4 per group
     const size_t og = (size_t)(c->db_cap / GROUP), ng = (size_t)(cap / GROUP);
-    UVG_CUDA(c, grow_array(&c->d_db, og * per_group, ng * per_group, true, c->st));
-    UVG_CUDA(c, grow_array(&c->d_non_n, (size_t)c->db_cap, (size_t)cap, true, c->st));
-    UVG_CUDA(c, grow_array(&c->d_ramb_off, c->db_cap ? (size_t)c->db_cap + 1 : 0, (size_t)cap + 1, true, c->st));
+    UVG_CUDA(c, grow_array(&c->d_db, og * per_group, ng * per_group, true, c->st_push));
+    UVG_CUDA(c, grow_array(&c->d_non_n, (size_t)c->db_cap, (size_t)cap, true, c->st_push));
+    UVG_CUDA(c, grow_array(&c->d_ramb_off, c->db_cap ? (size_t)c->db_cap + 1 : 0, (size_t)cap + 1, true, c->st_push));
     c->db_cap = cap;
     return UVG_OK;
 }
@@ -441,9 +470,11 @@ static int ensure_amb_capacity(uvg_ctx* c, int64_t need)
 {
     if (need <= c->amb_cap) return UVG_OK;
     if (need > 0xfffffff0LL) UVG_FAIL(c, UVG_ENOMEM, "more than 2^32 ambiguity codes in the resident references");
+    int rc = sync_all(c);
+    if (rc) return rc;
     int64_t cap = std::max<int64_t>(need, c->amb_cap * 2);
-    cap = std::max<int64_t>(cap, 1 << 16);
-    UVG_CUDA(c, grow_array(&c->d_ramb_ent, (size_t)c->amb_cap, (size_t)cap, false, c->st));
+    cap = std::max<int64_t>(cap, std::max<int64_t>(1 << 16, c->prm.db_capacity * 4));   // ~1.7 codes per SARS-CoV-2 genome
+    UVG_CUDA(c, grow_array(&c->d_ramb_ent, (size_t)c->amb_cap, (size_t)cap, false, c->st_push));
     c->amb_cap = cap;
     return UVG_OK;
 }
@@ -452,7 +483,7 @@ static int ensure_ever(uvg_ctx* c, int64_t n_global)
 {
     if (n_global <= c->ever_cap) return UVG_OK;
     int64_t cap = std::max<int64_t>(n_global, c->ever_cap * 2);
-    cap = std::max<int64_t>(cap, 4096);
+    cap = std::max<int64_t>(cap, std::max<int64_t>(4096, c->prm.db_capacity * (int64_t)c->world));
     int rc = sync_all(c);
     if (rc) return rc;
     UVG_CUDA(c, grow_array(&c->d_ever, (size_t)c->ever_cap, (size_t)cap, true, c->st));
@@ -463,6 +494,7 @@ static int ensure_ever(uvg_ctx* c, int64_t n_global)
 static int ensure_stage_rows(uvg_ctx* c, int64_t rows)
 {
     if (rows <= c->stage_rows) return UVG_OK;
+    UVG_CUDA(c, cudaStreamSynchronize(c->st_push));
     cudaFree(c->d_stage_nn); cudaFree(c->d_stage_namb); cudaFree(c->d_stage_acc); cudaFree(c->d_stage_dst);
     c->d_stage_nn = c->d_stage_namb = nullptr; c->d_stage_acc = nullptr; c->d_stage_dst = nullptr; c->stage_rows = 0;
     UVG_CUDA(c, cudaMalloc(&c->d_stage_nn, rows * 4));
@@ -473,7 +505,8 @@ static int ensure_stage_rows(uvg_ctx* c, int64_t rows)
     return UVG_OK;
 }
 
-// encode n rows already on the device; appends the accepted ones
+// encode n rows already on the device (stream st_push); appends the accepted ones.  Search rounds that are in flight
+// only read rows below db_n, so the encoder may run under them.
 static int push_device_rows(uvg_ctx* c, const uint8_t* d_text, int64_t n, int32_t min_non_n, int32_t* non_n_out,
                             uint8_t* accepted_out, int64_t* n_acc_out)
 {
@@ -481,20 +514,20 @@ static int push_device_rows(uvg_ctx* c, const uint8_t* d_text, int64_t n, int32_
     if (rc) return rc;
     rc = ensure_db_capacity(c, c->db_n + n);
     if (rc) return rc;
-    UVG_CUDA(c, launch_count_non_n(d_text, n, c->nchar, min_non_n, c->prm.acgt_mode, c->d_stage_nn, c->d_stage_acc, c->d_stage_namb, c->st));
-    UVG_CUDA(c, launch_scan_accept(c->d_stage_acc, c->d_stage_namb, n, c->db_n, (uint32_t)c->amb_n, c->d_stage_dst, c->d_ramb_off, c->d_nacc, c->st));
+    cudaStream_t sp = c->st_push;
+    UVG_CUDA(c, launch_count_non_n(d_text, n, c->nchar, min_non_n, c->prm.acgt_mode, c->d_stage_nn, c->d_stage_acc, c->d_stage_namb, sp));
+    UVG_CUDA(c, launch_scan_accept(c->d_stage_acc, c->d_stage_namb, n, c->db_n, (uint32_t)c->amb_n, c->d_stage_dst, c->d_ramb_off, c->d_nacc, sp));
     int64_t* h_n = reinterpret_cast<int64_t*>(c->h_pinned);
-    UVG_CUDA(c, cudaMemcpyAsync(h_n, c->d_nacc, 16, cudaMemcpyDeviceToHost, c->st));
-    if (non_n_out) UVG_CUDA(c, cudaMemcpyAsync(non_n_out, c->d_stage_nn, n * 4, cudaMemcpyDeviceToHost, c->st));
-    if (accepted_out) UVG_CUDA(c, cudaMemcpyAsync(accepted_out, c->d_stage_acc, n, cudaMemcpyDeviceToHost, c->st));
-    UVG_CUDA(c, cudaStreamSynchronize(c->st));
+    UVG_CUDA(c, cudaMemcpyAsync(h_n, c->d_nacc, 16, cudaMemcpyDeviceToHost, sp));
+    if (non_n_out) UVG_CUDA(c, cudaMemcpyAsync(non_n_out, c->d_stage_nn, n * 4, cudaMemcpyDeviceToHost, sp));
+    if (accepted_out) UVG_CUDA(c, cudaMemcpyAsync(accepted_out, c->d_stage_acc, n, cudaMemcpyDeviceToHost, sp));
+    UVG_CUDA(c, cudaStreamSynchronize(sp));
     const int64_t n_acc = h_n[0], n_amb = h_n[1];
     rc = ensure_amb_capacity(c, c->amb_n + n_amb);
     if (rc) return rc;
     UVG_CUDA(c, launch_encode(d_text, n, c->nchar, c->Wp, c->prm.acgt_mode, c->d_stage_dst, c->d_stage_nn, c->d_db, c->d_ramb_off,
-                              c->d_ramb_ent, c->d_non_n, c->st));
+                              c->d_ramb_ent, c->d_non_n, sp));
     c->stats.other_kernel_launches += 3;
-    UVG_CUDA(c, cudaStreamSynchronize(c->st));             // the caller may reuse d_text
     c->db_n += n_acc;
     c->amb_n += n_amb;
     if (n_acc_out) *n_acc_out += n_acc;
@@ -508,7 +541,7 @@ extern "C" int uvg_push_refs_device(uvg_ctx* c, const uint8_t* d_text, int64_t n
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
     if (n_accepted) *n_accepted = 0;
     if (n == 0) return UVG_OK;
-    UVG_CUDA(c, cudaEventRecord(c->ev_c, c->st));
+    UVG_CUDA(c, cudaEventRecord(c->ev_c, c->st_push));
     const int64_t step = 1 << 16;
     for (int64_t i = 0; i < n; i += step) {
         const int64_t m = std::min(step, n - i);
@@ -516,13 +549,15 @@ extern "C" int uvg_push_refs_device(uvg_ctx* c, const uint8_t* d_text, int64_t n
                                   accepted_out ? accepted_out + i : nullptr, n_accepted);
         if (rc) return rc;
     }
-    UVG_CUDA(c, cudaEventRecord(c->ev_d, c->st));
-    UVG_CUDA(c, cudaEventSynchronize(c->ev_d));
+    UVG_CUDA(c, cudaEventRecord(c->ev_d, c->st_push));
+    UVG_CUDA(c, cudaEventSynchronize(c->ev_d));            // the caller may reuse d_text
     float ms = 0; cudaEventElapsedTime(&ms, c->ev_c, c->ev_d);
     c->stats.encode_ms = ms;
     return UVG_OK;
 }
 
+// Host text -> device: a two-buffer staging ring.  The copy of piece i+1 (copy engine, stream st_copy) runs under the
+// encoder kernels of piece i (stream st_push) and under whatever search rounds are in flight.
 extern "C" int uvg_push_refs(uvg_ctx* c, const uint8_t* text, int64_t n, int32_t min_non_n, int32_t* non_n_out,
                              uint8_t* accepted_out, int64_t* n_accepted)
 {
@@ -530,25 +565,39 @@ extern "C" int uvg_push_refs(uvg_ctx* c, const uint8_t* text, int64_t n, int32_t
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
     if (n_accepted) *n_accepted = 0;
     if (n == 0) return UVG_OK;
-    // stage through a device text buffer of <= 256 MiB per step
-    int64_t rows_per_step = std::max<int64_t>(1, std::min<int64_t>(n, (256ll << 20) / c->nchar));
-    rows_per_step = std::min<int64_t>(rows_per_step, 1 << 16);
-    const size_t need = (size_t)rows_per_step * c->nchar;
+    int64_t rows_per_piece = std::max<int64_t>(1, std::min<int64_t>(n, (128ll << 20) / c->nchar));
+    rows_per_piece = std::min<int64_t>(rows_per_piece, 1 << 16);
+    const size_t need = (size_t)rows_per_piece * c->nchar;
     if (need > c->stage_text_bytes) {
-        cudaFree(c->d_stage_text); c->d_stage_text = nullptr; c->stage_text_bytes = 0;
-        UVG_CUDA(c, cudaMalloc(&c->d_stage_text, need));
+        UVG_CUDA(c, cudaStreamSynchronize(c->st_push)); UVG_CUDA(c, cudaStreamSynchronize(c->st_copy));
+        for (int b = 0; b < 2; ++b) { cudaFree(c->d_stage_text[b]); c->d_stage_text[b] = nullptr; }
+        c->stage_text_bytes = 0;
+        for (int b = 0; b < 2; ++b) UVG_CUDA(c, cudaMalloc(&c->d_stage_text[b], need));
         c->stage_text_bytes = need;
     }
-    UVG_CUDA(c, cudaEventRecord(c->ev_c, c->st));
-    for (int64_t i = 0; i < n; i += rows_per_step) {
-        const int64_t m = std::min(rows_per_step, n - i);
-        UVG_CUDA(c, cudaMemcpyAsync(c->d_stage_text, text + i * (int64_t)c->nchar, (size_t)m * c->nchar, cudaMemcpyHostToDevice, c->st));
-        int rc = push_device_rows(c, c->d_stage_text, m, min_non_n, non_n_out ? non_n_out + i : nullptr,
+    const int64_t n_pieces = (n + rows_per_piece - 1) / rows_per_piece;
+    auto issue_copy = [&](int64_t k) -> cudaError_t {
+        const int b = (int)(k & 1);
+        const int64_t i = k * rows_per_piece, m = std::min(rows_per_piece, n - i);
+        cudaError_t e = cudaStreamWaitEvent(c->st_copy, c->ev_stage_free[b], 0);          // encoder of piece k-2 is done with it
+        if (e == cudaSuccess) e = cudaMemcpyAsync(c->d_stage_text[b], text + i * (int64_t)c->nchar, (size_t)m * c->nchar, cudaMemcpyHostToDevice, c->st_copy);
+        if (e == cudaSuccess) e = cudaEventRecord(c->ev_copied[b], c->st_copy);
+        return e;
+    };
+    UVG_CUDA(c, cudaEventRecord(c->ev_c, c->st_push));
+    UVG_CUDA(c, issue_copy(0));
+    for (int64_t k = 0; k < n_pieces; ++k) {
+        const int b = (int)(k & 1);
+        const int64_t i = k * rows_per_piece, m = std::min(rows_per_piece, n - i);
+        if (k + 1 < n_pieces) UVG_CUDA(c, issue_copy(k + 1));
+        UVG_CUDA(c, cudaStreamWaitEvent(c->st_push, c->ev_copied[b], 0));
+        int rc = push_device_rows(c, c->d_stage_text[b], m, min_non_n, non_n_out ? non_n_out + i : nullptr,
                                   accepted_out ? accepted_out + i : nullptr, n_accepted);
         if (rc) return rc;
+        UVG_CUDA(c, cudaEventRecord(c->ev_stage_free[b], c->st_push));
     }
-    UVG_CUDA(c, cudaEventRecord(c->ev_d, c->st));
-    UVG_CUDA(c, cudaEventSynchronize(c->ev_d));
+    UVG_CUDA(c, cudaEventRecord(c->ev_d, c->st_push));
+    UVG_CUDA(c, cudaEventSynchronize(c->ev_d));            // rows are resident when the call returns
     float ms = 0; cudaEventElapsedTime(&ms, c->ev_c, c->ev_d);
     c->stats.encode_ms = ms;
     return UVG_OK;
@@ -559,6 +608,7 @@ extern "C" int uvg_drop_refs(uvg_ctx* c)
     if (!c) return UVG_EINVAL;
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
     if (c->world > 1) UVG_FAIL(c, UVG_ESTATE, "uvg_drop_refs is not available in sharded mode");
+    if (c->search_open) UVG_FAIL(c, UVG_ESTATE, "uvg_drop_refs: a search is in flight (call uvg_wait first)");
     if (c->db_scored != c->db_n) UVG_FAIL(c, UVG_ESTATE, "uvg_drop_refs: %lld resident references have not been searched yet",
                                          (long long)(c->db_n - c->db_scored));
     c->global_base += c->db_n;
@@ -570,6 +620,9 @@ extern "C" int uvg_clear_refs(uvg_ctx* c)
 {
     if (!c) return UVG_EINVAL;
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
+    int rc = sync_all(c);
+    if (rc) return rc;
+    c->search_open = false; c->n_ev = 0;
     c->global_base = 0; c->db_n = 0; c->db_scored = 0; c->round_local_start = 0; c->global_total = -1; c->amb_n = 0;
     return c->n_query ? reset_heaps(c) : UVG_OK;
 }
@@ -684,32 +737,29 @@ static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t
     return UVG_OK;
 }
 
-extern "C" int uvg_search(uvg_ctx* c)
+// enqueue the rounds that cover every resident reference not scored yet; returns without waiting
+static int search_enqueue(uvg_ctx* c)
 {
-    if (!c) return UVG_EINVAL;
-    UVG_CUDA(c, cudaSetDevice(c->prm.device));
     if (c->n_query == 0) UVG_FAIL(c, UVG_ESTATE, "uvg_search: no queries set");
     if (c->world > 1 && !c->comm) UVG_FAIL(c, UVG_ESTATE, "uvg_search: sharded context without uvg_nccl_init");
     if (c->world > 1 && c->global_total < 0) UVG_FAIL(c, UVG_ESTATE, "uvg_search: sharded context without uvg_set_global_count");
-    int rc = sync_all(c);
-    if (rc) return rc;
+    int rc;
     if (c->world > 1) { rc = ensure_peers(c); if (rc) return rc; }
     const int32_t mx = (int32_t)std::min<int64_t>(round_size_max(c->prm), c->seg_cap);
     if (c->next_round > mx) c->next_round = mx;
-    size_t n_ev = 0;
     c->heaps_cached = false;
-    c->stats.pair_kernel_ms = 0; c->stats.replay_ms = 0;
-    UVG_CUDA(c, cudaMemcpyAsync(c->h_pinned + 20, c->d_counters + 2, 8, cudaMemcpyDeviceToHost, c->st));
-    UVG_CUDA(c, cudaStreamSynchronize(c->st));
-    c->work_base = (int64_t)c->h_pinned[20];
-    // every array the rounds touch is sized before the first launch (no reallocation while kernels are in flight)
+    // every array the rounds touch is sized before the first launch (growing one synchronises everything first)
     {
         const int64_t upto = c->world == 1 ? c->global_base + c->db_n : c->global_total;
         if (upto > 0x7fffffffLL) UVG_FAIL(c, UVG_EINVAL, "more than 2^31 references are not supported");
         rc = ensure_ever(c, upto);
         if (rc) return rc;
     }
-    UVG_CUDA(c, cudaEventRecord(c->ev_a, c->st));
+    if (!c->search_open) {
+        c->search_open = true; c->n_ev = 0;
+        c->stats.pair_kernel_ms = 0; c->stats.replay_ms = 0;
+        UVG_CUDA(c, cudaEventRecord(c->ev_a, c->st));
+    }
     for (;;) {
         const int64_t T = c->next_round;
         int64_t lstart, cnt, rfirst, rcount;
@@ -726,13 +776,28 @@ extern "C" int uvg_search(uvg_ctx* c)
             if (lstart + cnt > c->db_n) UVG_FAIL(c, UVG_ESTATE, "rank %d holds %lld references but round %lld needs local rows up to %lld",
                                                  c->rank, (long long)c->db_n, (long long)c->rounds_done, (long long)(lstart + cnt));
         }
-        rc = run_round(c, lstart, cnt, T, rfirst, rcount, &n_ev);
+        rc = run_round(c, lstart, cnt, T, rfirst, rcount, &c->n_ev);
         if (rc) return rc;
         if (c->world == 1) { c->db_scored += cnt; c->stats.n_refs += cnt; }
         else { c->round_global_start += (int64_t)c->world * T; c->round_local_start += T; c->db_scored = std::min(c->db_n, c->round_local_start); c->stats.n_refs += rcount; }
         ++c->rounds_done; ++c->stats.n_rounds;
         c->next_round = round_size_next(c->next_round, mx);
     }
+    return UVG_OK;
+}
+
+extern "C" int uvg_search_async(uvg_ctx* c)
+{
+    if (!c) return UVG_EINVAL;
+    UVG_CUDA(c, cudaSetDevice(c->prm.device));
+    return search_enqueue(c);
+}
+
+extern "C" int uvg_wait(uvg_ctx* c)
+{
+    if (!c) return UVG_EINVAL;
+    UVG_CUDA(c, cudaSetDevice(c->prm.device));
+    if (!c->search_open) return sync_all(c);
     // the search ends when the last replay has finished: join stream B into stream A
     UVG_CUDA(c, cudaEventRecord(c->ev_d, c->st_rp));
     UVG_CUDA(c, cudaStreamWaitEvent(c->st, c->ev_d, 0));
@@ -745,16 +810,30 @@ extern "C" int uvg_search(uvg_ctx* c)
         if (c->global_total > 0) UVG_NCCL(c, g_nccl.AllReduce(c->d_ever, c->d_ever, (size_t)c->global_total, ncclUint8, ncclMax, c->comm, c->st));
     }
     UVG_CUDA(c, cudaEventRecord(c->ev_b, c->st));
+    UVG_CUDA(c, cudaMemcpyAsync(c->h_pinned + 20, c->d_counters + 2, 8, cudaMemcpyDeviceToHost, c->st));
     UVG_CUDA(c, cudaEventSynchronize(c->ev_b));
-    rc = sync_all(c);
+    int rc = sync_all(c);
     if (rc) return rc;
+    c->search_open = false;
+    c->work_last = (int64_t)c->h_pinned[20] - c->work_seen;
+    c->work_seen = (int64_t)c->h_pinned[20];
     float ms = 0; cudaEventElapsedTime(&ms, c->ev_a, c->ev_b);
     c->stats.search_ms = ms;
-    for (size_t i = 0; i < n_ev; ++i) {           // events alternate: pair-count launch, replay launch
+    for (size_t i = 0; i < c->n_ev; ++i) {        // events alternate: pair-count launch, replay launch
         float t = 0; cudaEventElapsedTime(&t, c->pair_events[i].first, c->pair_events[i].second);
         if (i % 2 == 0) c->stats.pair_kernel_ms += t; else c->stats.replay_ms += t;
     }
+    c->n_ev = 0;
     return UVG_OK;
+}
+
+extern "C" int uvg_search(uvg_ctx* c)
+{
+    if (!c) return UVG_EINVAL;
+    UVG_CUDA(c, cudaSetDevice(c->prm.device));
+    int rc = search_enqueue(c);
+    if (rc) return rc;
+    return uvg_wait(c);
 }
 
 // =====================================================================================================================
@@ -773,6 +852,7 @@ static int compare_items_desc(const void* pa, const void* pb)
 
 static int cache_heaps(uvg_ctx* c)
 {
+    if (c->search_open) { int rc = uvg_wait(c); if (rc) return rc; }
     if (c->heaps_cached) return UVG_OK;
     const size_t rows = (size_t)c->world * c->rows_cap, stride = c->K + 1;
     c->h_heaps.resize(rows * stride); c->h_heap_n.resize(rows); c->h_max_inc.resize(rows);
@@ -819,6 +899,7 @@ extern "C" int uvg_get_ever_best(uvg_ctx* c, int64_t first, int64_t n, uint8_t* 
 {
     if (!c || !flags || first < 0 || n < 0) { if (c) c->err = "uvg_get_ever_best: bad arguments"; return UVG_EINVAL; }
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
+    if (c->search_open) { int rc = uvg_wait(c); if (rc) return rc; }
     memset(flags, 0, (size_t)n);
     const int64_t m = std::min(n, c->ever_cap - first);
     if (m > 0) {
@@ -832,10 +913,11 @@ extern "C" int uvg_get_stats(uvg_ctx* c, uvg_stats* out)
 {
     if (!c || !out) return UVG_EINVAL;
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
+    if (c->search_open) { int rc = uvg_wait(c); if (rc) return rc; }
     UVG_CUDA(c, cudaMemcpyAsync(c->h_pinned + 16, c->d_counters, 24, cudaMemcpyDeviceToHost, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
     c->stats.n_admitted = (int64_t)c->h_pinned[16]; c->stats.n_h1_flags = (int64_t)c->h_pinned[17];
-    c->stats.warp_chunks_executed = (int64_t)c->h_pinned[18] - c->work_base;
+    c->stats.warp_chunks_executed = c->work_last;
     if (c->n_query) {
         int rc = cache_heaps(c);
         if (rc) return rc;

@@ -116,6 +116,12 @@ class Engine:
     def search(self):
         self._ck(self._lib.uvg_search(self._h), "uvg_search")
 
+    def search_async(self):
+        self._ck(self._lib.uvg_search_async(self._h), "uvg_search_async")
+
+    def wait(self):
+        self._ck(self._lib.uvg_wait(self._h), "uvg_wait")
+
     def reset_search(self):
         self._ck(self._lib.uvg_reset_search(self._h), "uvg_reset_search")
 
