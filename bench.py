@@ -27,8 +27,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 NCHAR = 29903
-LOP3_PER_PAIRWORD = 4.5        # LOP3 per (pair, 32-site word): 3 for valid+match, 1.5 for the carry-save tree
-POPC_PER_PAIRWORD = 1.25       # 1 for valid, 0.25 for the weight-4 carries of the match words
+# algorithmic instruction counts per (pair, 32-site word) of the two pair-count kernels
+OPS = {"pivot": {"kernel": "k_pairpivot", "lop3": 4.0, "popc": 1.0},       # 2 AND + 2 x (one 3:2 compressor per two words); 2 x 0.5 POPC
+       "general": {"kernel": "k_paircount", "lop3": 4.5, "popc": 1.25}}    # 3 for valid+match, 1.5 carry-save tree; 1 + 0.25 POPC
 
 
 def parse_args():
@@ -44,6 +45,7 @@ def parse_args():
     ap.add_argument("--ambiguous", type=float, default=0.0, help="config-4 stress: fraction of ambiguous query sites")
     ap.add_argument("--early-abort", type=int, default=0)
     ap.add_argument("--max-round", type=int, default=0)
+    ap.add_argument("--pair-kernel", default="auto", choices=["auto", "general", "pivot"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=2)
@@ -244,7 +246,8 @@ def main():
     tiles = rank_tiles(R, rank, world, first_round, max_round)
     n_local = sum(c for _, c in tiles)
     eng = Engine(L, nbest=args.nbest, device=dev, first_round=first_round, max_round=max_round, early_abort=bool(args.early_abort),
-                 rank=rank, world=world, db_capacity=n_local if args.impl == "ours" else 4096)
+                 rank=rank, world=world, db_capacity=n_local if args.impl == "ours" else 4096,
+                 pair_kernel={"auto": 0, "general": 1, "pivot": 2}[args.pair_kernel])
     qtext, qnames = make_queries(eng, clades, args.queries, L, args.ambiguous)
     Q = len(qtext)
     workload = f"{Q} synthetic SARS-CoV-2 queries (of {args.queries} generated; -a 0.5 filter) x {R} references x {L} sites, nbest={args.nbest}"
@@ -379,24 +382,26 @@ def main():
     pairwords_dense = Q * n_local * W                         # per step on this rank, no early abort
     pairwords_rank = chunks / args.steps * 4096.0             # executed: (warp, chunk) iterations x 8 words x 16 pairs x 32 lanes
     k_ms = (pair_ms_max / args.steps)
-    lop3 = LOP3_PER_PAIRWORD * pairwords_rank / (k_ms * 1e-3) / 1e9
-    popc = POPC_PER_PAIRWORD * pairwords_rank / (k_ms * 1e-3) / 1e9
+    ops = OPS["pivot" if st["pivot_fix_entries"] >= 0 else "general"]
+    lop3 = ops["lop3"] * pairwords_rank / (k_ms * 1e-3) / 1e9
+    popc = ops["popc"] * pairwords_rank / (k_ms * 1e-3) / 1e9
     f_l, f_p = lop3 / peaks["lop3_gips"], popc / peaks["popc_gips"]
     bound = "int-popc" if f_p >= f_l else "int-lop3"
     n_qtiles = (Q + 1 + 63) // 64                             # + the consensus pseudo-query
     db_bytes = n_local * ((W + 7) // 8 * 8) * 12              # three bit-planes per 32-site word
-    roofline = {"kernel": "k_paircount", "bound": bound, "achieved": popc if bound == "int-popc" else lop3,
+    roofline = {"kernel": ops["kernel"], "bound": bound, "achieved": popc if bound == "int-popc" else lop3,
                 "peak": peaks["popc_gips"] if bound == "int-popc" else peaks["lop3_gips"], "unit": "Gthread-inst/s",
                 "frac": max(f_l, f_p), "traffic": None,
                 "note": "INT pipes bind (north_star): %.2f LOP3 + %.2f POPC per EXECUTED pair x 32-site word (padding and early abort accounted for); peaks = profiles/int_pipes_b200_r01.json (measured)"
-                        % (LOP3_PER_PAIRWORD, POPC_PER_PAIRWORD),
+                        % (ops["lop3"], ops["popc"]),
                 "lop3": {"achieved": lop3, "peak": peaks["lop3_gips"], "frac": f_l}, "popc": {"achieved": popc, "peak": peaks["popc_gips"], "frac": f_p},
                 "hbm": {"bound": "hbm", "achieved": db_bytes / (k_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                         "frac": db_bytes / (k_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "peak_src": peaks["hbm_src"],
                         "note": "algorithmic = one pass over the packed DB per step; L2-level re-reads x%d query tiles" % n_qtiles},
                 "kernel_ms_per_step": k_ms, "kernel_share_of_step": k_ms / ms_step,
                 "executed_pairwords_per_step": pairwords_rank, "dense_pairwords_per_step": pairwords_dense,
-                "executed_fraction_of_dense": pairwords_rank / max(1, pairwords_dense)}
+                "executed_fraction_of_dense": pairwords_rank / max(1, pairwords_dense),
+                "pivot_fix_entries_per_query": (st["pivot_fix_entries"] / max(1, Q + 1)) if st["pivot_fix_entries"] >= 0 else None}
 
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu:

@@ -29,6 +29,8 @@ extern "C" {
 
 enum { UVG_OK = 0, UVG_EINVAL = -1, UVG_ENODEV = -2, UVG_ENOMEM = -3, UVG_ECUDA = -4, UVG_ESTATE = -5, UVG_ENCCL = -6 };
 
+enum { UVG_PAIR_AUTO = 0, UVG_PAIR_GENERAL = 1, UVG_PAIR_PIVOT = 2 };
+
 typedef struct uvg_ctx uvg_ctx;
 
 /* One kept neighbour = the reference's q_item (src/min_heap.h:14-18) with the strdup'ed name replaced by the
@@ -51,7 +53,11 @@ typedef struct uvg_params {
     int32_t max_round;      /* largest round per rank (0 = default 65536; also capped so the score tile stays <= 2 GiB) */
     int32_t early_abort;    /* 1 = warp-granular abort of pairs that cannot beat the k-th best (exact, perf only) */
     int32_t rank, world;    /* row sharding: this context holds tile `rank` of every round (world<=1: single GPU) */
-    int64_t reserved0;      /* must be 0 */
+    int32_t pair_kernel;    /* UVG_PAIR_AUTO (0): pivot form of the pair-count kernel when the mode and the query set allow it
+                               (default mode, < 65,536 columns, no early abort, queries close to one pivot sequence), else the
+                               general 3-plane kernel; UVG_PAIR_GENERAL / UVG_PAIR_PIVOT force one (PIVOT only skips the
+                               closeness test).  Results are identical either way. */
+    int32_t reserved1;      /* must be 0 */
     int64_t db_capacity;    /* references to reserve HBM for (0 = grow on demand) */
 } uvg_params;
 
@@ -73,6 +79,7 @@ typedef struct uvg_stats {
     int64_t warp_chunks_executed; /* (warp, chunk) iterations the pair-count kernel ran in the last uvg_search: x 8 words x 16 pairs x 32 lanes
                                      = executed pair-words (early abort makes this smaller than queries x refs x words) */
     int64_t max_mismatch;       /* "Highest number of ACGT mismatches" (nearest.c:324): max over queries of max_incompatible-1 */
+    int64_t pivot_fix_entries;  /* pivot form of the pair-count kernel in use: fix entries over all query slots; -1: general kernel */
 } uvg_stats;
 
 /* ---- life cycle ---- */

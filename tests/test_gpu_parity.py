@@ -18,6 +18,16 @@ from uvaia_b200.synth import SynthModel, write_fasta
 
 pytestmark = pytest.mark.gpu
 
+
+
+@pytest.fixture(autouse=True, params=["pivot", "general"])
+def pair_kernel(request, monkeypatch):
+    """every test of this module runs twice: with the pivot form of the pair-count kernel forced wherever the mode allows
+    it (default scoring, < 65,536 columns, no early abort) and with the general 3-plane kernel; the tables must not move"""
+    monkeypatch.setenv("UVG_PAIR_KERNEL", request.param)
+    return request.param
+
+
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "uvaia_ref")
 NON_H1 = [n for n in case_names() if not Case(n).h1]
 H1 = [n for n in case_names() if Case(n).h1]
@@ -330,3 +340,32 @@ def test_vs_live_reference_binary(seed, acgt, trim, nbest):
         want = gzip.decompress(open(os.path.join(wd, "o.csv.xz"), "rb").read()).decode()
         out = host.search_files(qf, [rf], nbest=nbest, trim=trim, acgt=acgt, first_round=256, max_round=1024)
     assert out.csv(acgt) == want
+
+
+def test_pivot_form_resident_db_requery_and_divergent_queries(pair_kernel):
+    """pivot form of the pair-count kernel: (1) references pushed BEFORE the queries get their derived planes in
+    uvg_set_queries, (2) a second query set on the same resident database re-derives them, (3) queries far from any
+    pivot (independent random sequences: thousands of fix entries each) stay exact when the form is forced."""
+    L, nr = 3000, 700
+    qn, Q, rn, R = make_inputs(L, 40, nr, 91, 0.03, 0.02)
+    rng = np.random.default_rng(3)
+    Qdiv = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, size=(70, L))]          # no common pivot
+    Qdiv[:, :50] = ord("N")
+    with Engine(L, nbest=7) as eng:
+        eng.push_refs(R, 0)
+        for Qset in (Q, Qdiv, Q[::-1]):
+            names, Qo, *_ = orc.prepare_queries([b"q%d" % i for i in range(len(Qset))], [q.tobytes() for q in Qset], 0, False, 1.0)
+            eng.set_queries(Qo)
+            got = eng.debug_pair_counts(0, nr)
+            want = np.stack(orc.pair_counts(orc.CODE[Qo], orc.CODE[R]), -1)
+            assert np.array_equal(got, want)
+            st = eng.stats()
+            assert (st["pivot_fix_entries"] >= 0) == (pair_kernel == "pivot")
+        # automatic choice: close queries take the pivot form, divergent ones the general kernel
+    with Engine(L, nbest=7, pair_kernel=0) as eng:
+        eng.push_refs(R, 0)
+        for Qset, want_pivot in ((Q, True), (Qdiv, False)):
+            names, Qo, *_ = orc.prepare_queries([b"q%d" % i for i in range(len(Qset))], [q.tobytes() for q in Qset], 0, False, 1.0)
+            eng.set_queries(Qo)
+            assert (eng.stats()["pivot_fix_entries"] >= 0) == want_pivot
+            assert np.array_equal(eng.debug_pair_counts(0, nr), np.stack(orc.pair_counts(orc.CODE[Qo], orc.CODE[R]), -1))

@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libuvaia_b200.so")
+LIB_PATH = os.environ.get("UVG_LIB") or os.path.join(_HERE, "lib", "libuvaia_b200.so")     # UVG_LIB: kernel-variant experiments
 
 UVG_ABI_VERSION = 1
 
@@ -22,7 +22,7 @@ class uvg_params(C.Structure):
     _fields_ = [("abi_version", C.c_int32), ("nchar", C.c_int32), ("trim", C.c_int32), ("nbest", C.c_int32),
                 ("acgt_mode", C.c_int32), ("pool", C.c_int32), ("device", C.c_int32), ("first_round", C.c_int32),
                 ("max_round", C.c_int32), ("early_abort", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
-                ("reserved0", C.c_int64), ("db_capacity", C.c_int64)]
+                ("pair_kernel", C.c_int32), ("reserved1", C.c_int32), ("db_capacity", C.c_int64)]
 
 
 class uvg_query_info(C.Structure):
@@ -35,7 +35,7 @@ class uvg_stats(C.Structure):
                 ("n_h1_flags", C.c_int64), ("pair_kernel_launches", C.c_int64),
                 ("other_kernel_launches", C.c_int64), ("pair_kernel_ms", C.c_double), ("replay_ms", C.c_double),
                 ("search_ms", C.c_double), ("encode_ms", C.c_double), ("warp_chunks_executed", C.c_int64),
-                ("max_mismatch", C.c_int64)]
+                ("max_mismatch", C.c_int64), ("pivot_fix_entries", C.c_int64)]
 
 
 # every symbol include/uvaia_b200.h declares: name -> (restype, argtypes)

@@ -41,6 +41,38 @@ struct __align__(16) QChunk {
 };
 static_assert(sizeof(QChunk) % 16 == 0, "bulk copy size must be a multiple of 16");
 
+// ---- pivot form (pairpivot.cu) ----------------------------------------------------------------------------------
+// All queries of a search are close to one "pivot" sequence (per site: the plain base most queries hold).  With
+//     mc  = sites where the REFERENCE holds the pivot base         (derived database plane, one pass per query set)
+//     qeq = sites where the QUERY holds the pivot base
+// the match word of a pair is mc & qeq and the valid word r.base & q.base: two ANDs instead of three LOP3 with five
+// inputs, and both popcounts go through a 2-word carry-save step (4 LOP3 + 1 POPC per pair-word in all, balanced for
+// the measured 4:1 LOP3:POPC issue ratio).  Query sites holding a plain base that differs from the pivot (~the SNPs of
+// the query, a few dozen per genome) are "fix" entries: (slot, word, base, bit mask).  They travel with the query chunk
+// and are resolved inside the main loop against ONE-HOT planes of the staged references (one conflict-free 4-byte
+// shared-memory load and one AND per entry and reference); what does not fit a chunk's fix block, and every ambiguity
+// code, is resolved by the epilogue (pair_epilogue.cuh).
+// Derived database: per (group of 32 references, unit of 4 column words) one contiguous 3 KB record
+//     uint4 base[32]  |  uint4 mc[32]  |  uint32 onehot[4 words][4 bases A,C,G,T][32]
+// so one chunk (WC words) of a group is one TMA bulk copy of W4 * 3 KB.
+constexpr int STAGES2 = 5;
+constexpr int UNIT2_BYTES = 2 * GROUP * 16 + 4 * 4 * GROUP * 4;      // 3072
+constexpr int UNIT2_ONEHOT = 2 * GROUP * 16;                         // byte offset of the one-hot planes inside a unit record
+constexpr int FIXCAP = 124;                                          // fix entries a chunk of a query tile can carry
+constexpr int PIVOT_QW = 4;                                          // query slots per warp of k_pairpivot
+constexpr int PIVOT_WARPS = QTILE / PIVOT_QW;
+struct __align__(16) QChunk2 {
+    uint4    pl[W4][QTILE][2];       // [unit][slot][plane]: 0 base, 1 qeq
+    uint8_t  fix_begin[32];          // [warp] first entry of the warp's slots; [PIVOT_WARPS] = total
+    uint2    fix[FIXCAP];            // x = bit mask inside the word, y = byte offset of the one-hot word (lane 0) inside the
+                                     //     staged chunk of a group | slot-within-warp << 16
+};
+static_assert(sizeof(QChunk2) % 16 == 0 && PIVOT_WARPS < 32 && FIXCAP < 256, "QChunk2 layout");
+__host__ __device__ inline size_t db2_unit_bytes(int64_t group, int unit, int Wp)
+{
+    return ((size_t)group * (size_t)(Wp / 4) + (size_t)unit) * UNIT2_BYTES;
+}
+
 // Heap slot (32 B): the reference's q_item (src/min_heap.h:14-18) with name -> ordinal.
 struct __align__(16) HeapItem {
     int32_t s[6];
@@ -68,6 +100,11 @@ struct PairParams {
     const uint32_t*  qnib;        // 4-bit codes of every query slot (trimmed), qnib_stride words per slot, 8 sites per word
     const uint32_t*  qamb_off;    // [n_slots + 1] ambiguity entries of the query slots
     const uint32_t*  qamb_ent;
+    // pivot form (null when the general kernel runs)
+    const uint8_t*   db2;         // derived database: 3 KB records (base, mc, one-hot planes)
+    const QChunk2*   qdata2;      // [n_qtiles][n_chunks]
+    const uint32_t*  qfix_off;    // [n_slots + 1] entries the EPILOGUE resolves: ambiguity codes + fix entries that overflowed a chunk
+    const uint32_t*  qfix_ent;
     const uint32_t*  ramb_off;    // [local refs + 1] ambiguity entries of the references
     const uint32_t*  ramb_ent;
     const int32_t*   non_n;       // per local reference
@@ -82,7 +119,7 @@ struct PairParams {
     int64_t  col0;                // column of local_begin in the destination tiles
     int32_t  world, rows_cap;
     int32_t  early_abort;
-    unsigned long long* work;     // executed (warp, chunk) iterations (early abort makes this < the dense count)
+    unsigned long long* work;     // executed (lane-pair, chunk) iterations per warp: x 8 words x 32 lanes = pair-words (early abort makes this < dense)
 };
 
 __host__ __device__ inline size_t db_unit_index(int64_t group, int unit, int plane, int lane, int Wp)

@@ -75,8 +75,15 @@ struct uvg_ctx {
     // queries
     int n_query = 0, n_slots = 0, n_qtiles = 0, rows_cap = 0, qnib_stride = 0;
     uvg_query_info qinfo{};
+    int64_t qinfo_pivot_fix = -1;                     // fix entries of the pivot form (-1: general kernel)
     QChunk* d_qdata = nullptr;
     uint32_t *d_qnib = nullptr, *d_qamb_off = nullptr, *d_qamb_ent = nullptr;
+    // pivot form of the pair-count kernel (pairpivot.cu): chosen per query set by uvg_set_queries
+    bool pivot_on = false;
+    QChunk2* d_qdata2 = nullptr;
+    uint32_t *d_qfix_off = nullptr, *d_qfix_ent = nullptr;
+    uint4* d_pivot = nullptr;                         // [Wp/4][2]: b0, b1 planes of the pivot sequence
+    uint8_t* d_db2 = nullptr; int64_t db2_cap = 0;    // derived database (base, mc, one-hot planes: 3 KB records) of the resident references
     Threshold* d_thr_local = nullptr;                 // [rows_cap] bounds of the owned rows (written by K3)
     Threshold* d_thr_all[NBUF]{};                     // [world * rows_cap] what K2 reads (double buffered)
     HeapItem* d_heaps = nullptr;                      // [rows_cap][K+1] owned rows
@@ -189,6 +196,7 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
     }
     CK_(upload_luts());
     CK_(paircount_setup());
+    CK_(pairpivot_setup());
     CK_(replay_setup(c->K));
     CK_(cudaMalloc(&c->d_counters, 64)); CK_(cudaMalloc(&c->d_nacc, 64)); CK_(cudaMalloc(&c->d_ipc, 64 * MAX_RANKS + 64));
     CK_(cudaMemset(c->d_counters, 0, 64));
@@ -211,6 +219,8 @@ static void free_queries(uvg_ctx* c)
 {
     close_peers(c);
     cudaFree(c->d_qdata); cudaFree(c->d_qnib); cudaFree(c->d_qamb_off); cudaFree(c->d_qamb_ent);
+    cudaFree(c->d_qdata2); cudaFree(c->d_qfix_off); cudaFree(c->d_qfix_ent); cudaFree(c->d_pivot);
+    c->d_qdata2 = nullptr; c->d_qfix_off = c->d_qfix_ent = nullptr; c->d_pivot = nullptr; c->pivot_on = false;
     cudaFree(c->d_thr_local); for (int b = 0; b < NBUF; ++b) { cudaFree(c->d_thr_all[b]); c->d_thr_all[b] = nullptr; }
     cudaFree(c->d_heaps); cudaFree(c->d_heaps_all);
     cudaFree(c->d_heap_n); cudaFree(c->d_max_inc); cudaFree(c->d_batch_id); cudaFree(c->d_max_inc_batch);
@@ -232,7 +242,7 @@ extern "C" void uvg_destroy(uvg_ctx* c)
     if (c->st_copy) cudaStreamSynchronize(c->st_copy);
     free_queries(c);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
-    cudaFree(c->d_db); cudaFree(c->d_non_n); cudaFree(c->d_ramb_off); cudaFree(c->d_ramb_ent); cudaFree(c->d_ever);
+    cudaFree(c->d_db); cudaFree(c->d_db2); cudaFree(c->d_non_n); cudaFree(c->d_ramb_off); cudaFree(c->d_ramb_ent); cudaFree(c->d_ever);
     cudaFree(c->d_counters); cudaFree(c->d_nacc); cudaFree(c->d_ipc);
     cudaFree(c->d_stage_text[0]); cudaFree(c->d_stage_text[1]); cudaFree(c->d_stage_nn); cudaFree(c->d_stage_namb); cudaFree(c->d_stage_acc); cudaFree(c->d_stage_dst);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
@@ -260,6 +270,22 @@ static int sync_all(uvg_ctx* c)
     UVG_CUDA(c, cudaStreamSynchronize(c->st_rp));
     UVG_CUDA(c, cudaStreamSynchronize(c->st_push));
     UVG_CUDA(c, cudaStreamSynchronize(c->st_copy));
+    return UVG_OK;
+}
+
+// derived database of the pivot form: sized like the packed database, allocated when a query set first asks for it
+static int ensure_db2(uvg_ctx* c)
+{
+    if (!c->pivot_on || c->db2_cap >= c->db_cap) return UVG_OK;
+    int rc = sync_all(c);
+    if (rc) return rc;
+    const size_t per_group = (size_t)(c->Wp / 4) * UNIT2_BYTES;             // bytes
+    uint8_t* n = nullptr;
+    UVG_CUDA(c, cudaMalloc(&n, (size_t)(c->db_cap / GROUP) * per_group));
+    if (c->d_db2 && c->db2_cap) UVG_CUDA(c, cudaMemcpy(n, c->d_db2, (size_t)(c->db2_cap / GROUP) * per_group, cudaMemcpyDeviceToDevice));
+    UVG_CUDA(c, cudaMemset(n + (size_t)(c->db2_cap / GROUP) * per_group, 0, (size_t)((c->db_cap - c->db2_cap) / GROUP) * per_group));
+    cudaFree(c->d_db2);
+    c->d_db2 = n; c->db2_cap = c->db_cap;
     return UVG_OK;
 }
 
@@ -380,6 +406,97 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     }
     amb_off[c->n_slots] = (uint32_t)amb_ent.size();
 
+    // ---- pivot form (pairpivot.cu): pivot sequence, query planes (base, equals-pivot) and fix lists ----
+    std::vector<QChunk2> qd2;
+    std::vector<uint32_t> fix_off, fix_ent, pivot_words;
+    int64_t n_fix_total = 0;
+    bool pivot_ok = !acgt && (int64_t)c->Wp * 32 <= 65535 && !c->prm.early_abort && c->prm.pair_kernel != UVG_PAIR_GENERAL;
+    if (pivot_ok) {
+        // per site the plain base most queries hold (ties: A before C before G before T; a site nobody holds a base at: A)
+        std::vector<uint32_t> cnt((size_t)L * 4, 0);
+        for (int q = 0; q < Q; ++q) {
+            const uint8_t* row = text + (size_t)q * L;
+            for (int s = trim; s < L - trim; ++s) {
+                const uint32_t code = code_lut[up[row[s]]];
+                if (code && !(code & (code - 1))) ++cnt[(size_t)s * 4 + (code == 1 ? 0 : code == 2 ? 1 : code == 4 ? 2 : 3)];
+            }
+        }
+        std::vector<uint8_t> pv(L, 1);
+        pivot_words.assign((size_t)(c->Wp / 4) * 8, 0u);                     // [unit][plane b0, b1][4 words]
+        for (int s = 0; s < L; ++s) {
+            int best = 0;
+            for (int k = 1; k < 4; ++k) if (cnt[(size_t)s * 4 + k] > cnt[(size_t)s * 4 + best]) best = k;
+            pv[s] = (uint8_t)(1u << best);
+            const int w = s >> 5;
+            uint32_t* u = &pivot_words[(size_t)(w >> 2) * 8];
+            if (pv[s] & 10u) u[w & 3] |= 1u << (s & 31);
+            if (pv[s] & 12u) u[4 + (w & 3)] |= 1u << (s & 31);
+        }
+        qd2.resize(n_chunk_total);
+        memset(qd2.data(), 0, n_chunk_total * sizeof(QChunk2));
+        // planes + per slot: the bases that differ from the pivot (site, one-hot code) and the ambiguity codes
+        std::vector<std::vector<uint32_t>> snp(c->n_slots), epi(c->n_slots);
+        size_t n_snp = 0;
+        for (int q = 0; q < c->n_slots; ++q) {
+            const int qt = q / QTILE, qi = q % QTILE;
+            const bool is_cons = q == Q;
+            const uint8_t* row = is_cons ? cons.data() : text + (size_t)q * L;
+            for (int s = trim; s < L - trim; ++s) {
+                if (is_cons && site_class[s] != 3) continue;
+                const uint32_t code = code_lut[up[row[s]]];
+                if (!code) continue;
+                if (code & (code - 1)) { epi[q].push_back((uint32_t)s | (code << 28)); continue; }
+                const int w = s >> 5, k = w & 3;
+                const uint32_t bit = 1u << (s & 31);
+                uint4* pl = qd2[(size_t)qt * c->n_chunks + w / WC].pl[(w % WC) / 4][qi];
+                (&pl[0].x)[k] |= bit;
+                if (code == pv[s]) (&pl[1].x)[k] |= bit;
+                else { snp[q].push_back((uint32_t)s | (code << 28)); ++n_snp; }
+            }
+        }
+        // fix blocks: entries of a (tile, chunk) ordered by warp; what does not fit goes to the slot's epilogue list
+        size_t n_overflow = 0;
+        std::vector<size_t> cur(c->n_slots, 0);
+        for (int qt = 0; qt < c->n_qtiles; ++qt)
+            for (int ch = 0; ch < c->n_chunks; ++ch) {
+                QChunk2& blk = qd2[(size_t)qt * c->n_chunks + ch];
+                const uint32_t site_end = (uint32_t)(ch + 1) * WC * 32;
+                int n = 0;
+                for (int wp = 0; wp < PIVOT_WARPS; ++wp) {
+                    blk.fix_begin[wp] = (uint8_t)n;
+                    for (int j = 0; j < PIVOT_QW; ++j) {
+                        const int q = qt * QTILE + wp * PIVOT_QW + j;
+                        if (q >= c->n_slots) continue;
+                        int last = -1; uint32_t last_key = 0;
+                        while (cur[q] < snp[q].size() && (snp[q][cur[q]] & AMB_SITE_MASK) < site_end) {
+                            const uint32_t ent = snp[q][cur[q]++], site = ent & AMB_SITE_MASK, code = ent >> 28;
+                            const uint32_t w = site >> 5, a = code == 1 ? 0 : code == 2 ? 1 : code == 4 ? 2 : 3;
+                            const uint32_t key = w * 4 + a;
+                            if (last >= 0 && key == last_key) { blk.fix[last].x |= 1u << (site & 31); continue; }
+                            if (n >= FIXCAP) { epi[q].push_back(ent); ++n_overflow; continue; }
+                            const uint32_t off = ((w % WC) / 4) * UNIT2_BYTES + UNIT2_ONEHOT + ((w & 3) * 4 + a) * (GROUP * 4);
+                            blk.fix[n].x = 1u << (site & 31);
+                            blk.fix[n].y = off | ((uint32_t)j << 16);
+                            last = n++; last_key = key;
+                        }
+                    }
+                }
+                blk.fix_begin[PIVOT_WARPS] = (uint8_t)n;
+            }
+        fix_off.assign(c->n_slots + 1, 0);
+        for (int q = 0; q < c->n_slots; ++q) {
+            fix_off[q] = (uint32_t)fix_ent.size();
+            std::sort(epi[q].begin(), epi[q].end(), [](uint32_t x, uint32_t y) { return (x & AMB_SITE_MASK) < (y & AMB_SITE_MASK); });
+            fix_ent.insert(fix_ent.end(), epi[q].begin(), epi[q].end());
+        }
+        fix_off[c->n_slots] = (uint32_t)fix_ent.size();
+        n_fix_total = (int64_t)n_snp;
+        // an in-loop fix entry costs ~15 instructions against ~520 per warp and chunk, an epilogue entry ~3 scattered
+        // loads per pair: divergent query sets (many bases != pivot, or chunks that overflow) stay on the general kernel
+        if (c->prm.pair_kernel != UVG_PAIR_PIVOT &&
+            (n_snp > (size_t)c->n_slots * (size_t)std::max(4, c->W / 8) || n_overflow > (size_t)c->n_slots * 2)) pivot_ok = false;
+    }
+
     // ---- device allocations ----
     const int rows = c->rows_cap;
     UVG_CUDA(c, cudaMalloc(&c->d_qdata, n_chunk_total * sizeof(QChunk)));
@@ -411,6 +528,23 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     UVG_CUDA(c, cudaMemcpyAsync(c->d_qnib, qnib.data(), qnib.size() * 4, cudaMemcpyHostToDevice, c->st));
     UVG_CUDA(c, cudaMemcpyAsync(c->d_qamb_off, amb_off.data(), amb_off.size() * 4, cudaMemcpyHostToDevice, c->st));
     if (!amb_ent.empty()) UVG_CUDA(c, cudaMemcpyAsync(c->d_qamb_ent, amb_ent.data(), amb_ent.size() * 4, cudaMemcpyHostToDevice, c->st));
+    if (pivot_ok) {
+        UVG_CUDA(c, cudaMalloc(&c->d_qdata2, n_chunk_total * sizeof(QChunk2)));
+        UVG_CUDA(c, cudaMalloc(&c->d_qfix_off, fix_off.size() * 4));
+        UVG_CUDA(c, cudaMalloc(&c->d_qfix_ent, std::max<size_t>(1, fix_ent.size()) * 4));
+        UVG_CUDA(c, cudaMalloc(&c->d_pivot, pivot_words.size() * 4));
+        UVG_CUDA(c, cudaMemcpyAsync(c->d_qdata2, qd2.data(), n_chunk_total * sizeof(QChunk2), cudaMemcpyHostToDevice, c->st));
+        UVG_CUDA(c, cudaMemcpyAsync(c->d_qfix_off, fix_off.data(), fix_off.size() * 4, cudaMemcpyHostToDevice, c->st));
+        if (!fix_ent.empty()) UVG_CUDA(c, cudaMemcpyAsync(c->d_qfix_ent, fix_ent.data(), fix_ent.size() * 4, cudaMemcpyHostToDevice, c->st));
+        UVG_CUDA(c, cudaMemcpyAsync(c->d_pivot, pivot_words.data(), pivot_words.size() * 4, cudaMemcpyHostToDevice, c->st));
+        c->pivot_on = true;
+        // references that are already resident get their derived planes now (one pass over the packed database)
+        int rc2 = ensure_db2(c);
+        if (rc2) return rc2;
+        UVG_CUDA(c, launch_derive_pivot(c->d_db, c->d_db2, c->d_pivot, 0, c->db_n, c->Wp, c->st));
+        if (c->db_n) c->stats.other_kernel_launches += 1;
+    }
+    c->qinfo_pivot_fix = pivot_ok ? n_fix_total : -1;
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
     return reset_heaps(c);
 }
@@ -463,7 +597,7 @@ static int ensure_db_capacity(uvg_ctx* c, int64_t need_refs)
     UVG_CUDA(c, grow_array(&c->d_non_n, (size_t)c->db_cap, (size_t)cap, true, c->st_push));
     UVG_CUDA(c, grow_array(&c->d_ramb_off, c->db_cap ? (size_t)c->db_cap + 1 : 0, (size_t)cap + 1, true, c->st_push));
     c->db_cap = cap;
-    return UVG_OK;
+    return ensure_db2(c);
 }
 
 static int ensure_amb_capacity(uvg_ctx* c, int64_t need)
@@ -528,6 +662,10 @@ static int push_device_rows(uvg_ctx* c, const uint8_t* d_text, int64_t n, int32_
     UVG_CUDA(c, launch_encode(d_text, n, c->nchar, c->Wp, c->prm.acgt_mode, c->d_stage_dst, c->d_stage_nn, c->d_db, c->d_ramb_off,
                               c->d_ramb_ent, c->d_non_n, sp));
     c->stats.other_kernel_launches += 3;
+    if (c->pivot_on && n_acc > 0) {
+        UVG_CUDA(c, launch_derive_pivot(c->d_db, c->d_db2, c->d_pivot, c->db_n, c->db_n + n_acc, c->Wp, sp));
+        c->stats.other_kernel_launches += 1;
+    }
     c->db_n += n_acc;
     c->amb_n += n_amb;
     if (n_acc_out) *n_acc_out += n_acc;
@@ -670,6 +808,7 @@ static void fill_pair_params(uvg_ctx* c, PairParams& pp, int64_t lb, int64_t le,
 {
     pp.db = c->d_db; pp.qdata = c->d_qdata; pp.thr = c->d_thr_all[buf];
     pp.qnib = c->d_qnib; pp.qamb_off = c->d_qamb_off; pp.qamb_ent = c->d_qamb_ent;
+    pp.db2 = c->d_db2; pp.qdata2 = c->d_qdata2; pp.qfix_off = c->d_qfix_off; pp.qfix_ent = c->d_qfix_ent;
     pp.ramb_off = c->d_ramb_off; pp.ramb_ent = c->d_ramb_ent; pp.non_n = c->d_non_n;
     pp.qnib_stride = c->qnib_stride;
     pp.Wp = c->Wp; pp.n_chunks = c->n_chunks; pp.n_qtiles = c->n_qtiles; pp.n_slots = c->n_slots;
@@ -695,7 +834,7 @@ static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t
     if (cnt > 0) {
         PairParams pp{};
         fill_pair_params(c, pp, lstart, lstart + cnt, b, (int64_t)c->rank * c->seg_cap);
-        UVG_CUDA(c, launch_paircount(pp, c->prm.acgt_mode, c->st));
+        UVG_CUDA(c, c->pivot_on ? launch_pairpivot(pp, c->st) : launch_paircount(pp, c->prm.acgt_mode, c->st));
         c->stats.pair_kernel_launches += 1;
     }
     UVG_CUDA(c, cudaEventRecord(eb, c->st));
@@ -917,7 +1056,8 @@ extern "C" int uvg_get_stats(uvg_ctx* c, uvg_stats* out)
     UVG_CUDA(c, cudaMemcpyAsync(c->h_pinned + 16, c->d_counters, 24, cudaMemcpyDeviceToHost, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
     c->stats.n_admitted = (int64_t)c->h_pinned[16]; c->stats.n_h1_flags = (int64_t)c->h_pinned[17];
-    c->stats.warp_chunks_executed = c->work_last;
+    c->stats.warp_chunks_executed = c->work_last / 16;          // the counter is in (pair, chunk) units; 16 pairs per lane and warp
+    c->stats.pivot_fix_entries = c->pivot_on ? c->qinfo_pivot_fix : -1;
     if (c->n_query) {
         int rc = cache_heaps(c);
         if (rc) return rc;
@@ -1036,7 +1176,7 @@ static int debug_score(uvg_ctx* c, int64_t first, int64_t n, const char* who)
     PairParams pp{};
     fill_pair_params(c, pp, first, first + n, 0, 0);
     pp.early_abort = 0; pp.work = nullptr;
-    UVG_CUDA(c, launch_paircount(pp, c->prm.acgt_mode, c->st));
+    UVG_CUDA(c, c->pivot_on ? launch_pairpivot(pp, c->st) : launch_paircount(pp, c->prm.acgt_mode, c->st));
     return UVG_OK;
 }
 

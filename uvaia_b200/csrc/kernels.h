@@ -23,6 +23,12 @@ cudaError_t launch_synth_rows(const uint8_t* d_clades, int n_clades, int nchar, 
 cudaError_t launch_paircount(const PairParams& p, int acgt_mode, cudaStream_t st);
 cudaError_t paircount_setup();       // opt in to the dynamic shared memory size
 
+// ---- pairpivot.cu (K2 in pivot form: default mode, < 65,536 columns, no early abort) ----
+cudaError_t launch_pairpivot(const PairParams& p, cudaStream_t st);
+cudaError_t pairpivot_setup();
+// derived planes (base, mc) of the resident references [begin, end) from the packed database and the pivot planes
+cudaError_t launch_derive_pivot(const uint4* db, uint8_t* db2, const uint4* pivot, int64_t begin, int64_t end, int Wp, cudaStream_t st);
+
 // ---- replay.cu (K3) ----
 struct ReplayParams {
     const uint4* tile;            // this rank's score tile of the round: row = owned query row, column = position in the round

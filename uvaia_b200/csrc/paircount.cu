@@ -21,54 +21,10 @@
 // (peer-mapped memory over NVLink when the database is sharded): the all-to-all of the sharded search is fused here.
 #include "common.cuh"
 #include "kernels.h"
+#include "pair_epilogue.cuh"
+#include "sm100_prims.cuh"
 
 namespace uvg {
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
-{
-    uint32_t ok;
-    do {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-    } while (!ok);
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
-{
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-
-template <int LUT>
-__device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c)
-{
-    uint32_t d;
-    asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(d) : "r"(a), "r"(b), "r"(c), "n"(LUT));
-    return d;
-}
-// a & ~(b ^ c): keep the sites of `a` where planes b and c agree
-__device__ __forceinline__ uint32_t keep_eq(uint32_t a, uint32_t b, uint32_t c) { return lop3<0x90>(a, b, c); }
-// 3:2 compressor: (sum, carry) of three bit-vectors
-__device__ __forceinline__ void csa(uint32_t& sum, uint32_t& carry, uint32_t a, uint32_t b, uint32_t c)
-{
-    carry = lop3<0xE8>(a, b, c);
-    sum = lop3<0x96>(a, b, c);
-}
-// a*b+c on the FMA pipe (IMAD): keeps the accumulations off the ALU pipe that issues the LOP3s
-__device__ __forceinline__ uint32_t imad(uint32_t a, uint32_t b, uint32_t c)
-{
-    uint32_t d;
-    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-    return d;
-}
 
 // One pipeline stage: a query chunk (64 slots x WC words) and the same WC words of the block's 64 references.
 struct __align__(16) Stage {
@@ -218,7 +174,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams 
         if (all_dead) break;
         if (threadIdx.x == 0 && c + STAGES < p.n_chunks) issue(c + STAGES, s);
     }
-    if (lane == 0 && p.work) atomicAdd(p.work, (unsigned long long)executed);
+    if (lane == 0 && p.work) atomicAdd(p.work, (unsigned long long)executed * (QPW * RPL));
     if (c < p.n_chunks) {
         // whole block aborted: drain the bulk copies still in flight before the shared memory is released
         for (int cc = c + 1; cc < p.n_chunks && cc < c + STAGES; ++cc) mbar_wait(full + cc % STAGES, (uint32_t)((cc / STAGES) & 1));
@@ -228,14 +184,11 @@ __global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams 
     // tile of the round on the rank that owns the query (coalesced 512 B per warp and query).  The replay kernel
     // assembles the 6-tuple (src/nearest.c:466-470, 499-501) for the pairs it admits.  Aborted pairs get a sentinel whose
     // mismatch count can never pass the admission test.
-    const uint32_t* dbw = reinterpret_cast<const uint32_t*>(p.db);
 #pragma unroll
     for (int j = 0; j < QPW; ++j) {
         const int slot = qt * QTILE + q0 + j;
         if (slot >= p.n_slots) continue;
         const bool is_cons = slot == p.n_slots - 1;
-        uint32_t qe0 = 0, qe1 = 0;
-        if (MODE == 0) { qe0 = p.qamb_off[slot]; qe1 = p.qamb_off[slot + 1]; }
 #pragma unroll
         for (int g = 0; g < RPL; ++g) {
             if (!in_range[g]) continue;
@@ -245,41 +198,10 @@ __global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams 
             } else {
                 const int32_t M = cntM4(g, j) + __popc(ones[g][j]) + 2 * __popc(twos[g][j]);
                 const int32_t V = cntV(g, j);
-                if (MODE == 0) {
-                    int32_t dv = 0, dp = 0, dt = 0;
-                    // (b) sites where the REFERENCE holds an ambiguity code: look the query's code up
-                    const uint32_t re1 = p.ramb_off[local[g] + 1];
-                    for (uint32_t e = p.ramb_off[local[g]]; e < re1; ++e) {
-                        const uint32_t ent = __ldg(p.ramb_ent + e), site = ent & AMB_SITE_MASK, rc = ent >> 28;
-                        const uint32_t qc = (__ldg(p.qnib + (size_t)slot * p.qnib_stride + (site >> 3)) >> ((site & 7u) * 4u)) & 15u;
-                        dv += qc != 0u; dp += (qc & rc) != 0u; dt += qc == rc;
-                    }
-                    // (c) sites where the QUERY holds an ambiguity code and the reference a plain base
-                    for (uint32_t e = qe0; e < qe1; ++e) {
-                        const uint32_t ent = __ldg(p.qamb_ent + e), site = ent & AMB_SITE_MASK, qc = ent >> 28;
-                        const uint32_t w = site >> 5, b = site & 31u;
-                        const size_t base = db_unit_index(group0 + g, (int)(w >> 2), 0, lane, p.Wp) * 4 + (w & 3u);
-                        if ((__ldg(dbw + base) >> b) & 1u) {
-                            const uint32_t x = (__ldg(dbw + base + GROUP * 4) >> b) & 1u, y = (__ldg(dbw + base + 2 * GROUP * 4) >> b) & 1u;
-                            dv += 1; dp += (qc >> (x + 2u * y)) & 1u;
-                        }
-                    }
-                    v = make_uint4((uint32_t)M, (uint32_t)(M + dt), (uint32_t)(M + dp), (uint32_t)(V + dv));
-                } else {
-                    v = make_uint4((uint32_t)M, (uint32_t)V, (uint32_t)cntI(g, j), 0u);
-                }
+                if (MODE == 0) v = pair_epilogue_default(p, p.qamb_off, p.qamb_ent, slot, group0 + g, lane, local[g], M, V);
+                else v = make_uint4((uint32_t)M, (uint32_t)V, (uint32_t)cntI(g, j), 0u);
             }
-            const int64_t col = p.col0 + (local[g] - p.local_begin);
-            if (!is_cons) {
-                p.out[owner][(size_t)(row0 + q0 + j) * p.row_stride + col] = v;
-            } else {
-                // the consensus counts and the per-reference record are needed by every rank's replay
-                const uint4 meta = make_uint4((uint32_t)p.non_n[local[g]], 0u, 0u, 0u);
-                for (int r = 0; r < p.world; ++r) {
-                    p.out[r][(size_t)p.rows_cap * p.row_stride + col] = v;
-                    p.out[r][(size_t)(p.rows_cap + 1) * p.row_stride + col] = meta;
-                }
-            }
+            pair_store(p, owner, row0 + q0 + j, is_cons, local[g], v);
         }
     }
 }

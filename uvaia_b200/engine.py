@@ -7,10 +7,14 @@ OpenMP loops (nearest.c:293-299), `heap` ~ heap_finalise_heap_qsort + save_dista
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 
 from . import _capi
+
+
+PAIR_KERNELS = {"auto": 0, "general": 1, "pivot": 2}
 
 
 class UvgError(RuntimeError):
@@ -19,11 +23,13 @@ class UvgError(RuntimeError):
 
 class Engine:
     def __init__(self, nchar, nbest=100, trim=0, acgt=False, pool=512, device=0, first_round=0, max_round=0,
-                 early_abort=False, rank=0, world=1, db_capacity=0):
+                 early_abort=False, rank=0, world=1, db_capacity=0, pair_kernel=None):
+        if pair_kernel is None:      # test / debug knob: UVG_PAIR_KERNEL=auto|general|pivot (include/uvaia_b200.h, uvg_params.pair_kernel)
+            pair_kernel = PAIR_KERNELS[os.environ.get("UVG_PAIR_KERNEL", "auto")]
         self._lib = _capi.lib()
         p = _capi.uvg_params(_capi.UVG_ABI_VERSION, int(nchar), int(trim), int(nbest), int(bool(acgt)), int(pool),
                              int(device), int(first_round), int(max_round), int(bool(early_abort)), int(rank), int(world),
-                             0, int(db_capacity))
+                             int(pair_kernel), 0, int(db_capacity))
         h = C.c_void_p()
         rc = self._lib.uvg_create(C.byref(p), C.byref(h))
         if rc != 0:
