@@ -55,7 +55,7 @@ static_assert(sizeof(QChunk) % 16 == 0, "bulk copy size must be a multiple of 16
 // Derived database: per (group of 32 references, unit of 4 column words) one contiguous 3 KB record
 //     uint4 base[32]  |  uint4 mc[32]  |  uint32 onehot[4 words][4 bases A,C,G,T][32]
 // so one chunk (WC words) of a group is one TMA bulk copy of W4 * 3 KB.
-constexpr int STAGES2 = 5;
+constexpr int STAGES2 = 6;
 constexpr int UNIT2_BYTES = 2 * GROUP * 16 + 4 * 4 * GROUP * 4;      // 3072
 constexpr int UNIT2_ONEHOT = 2 * GROUP * 16;                         // byte offset of the one-hot planes inside a unit record
 constexpr int FIXCAP = 124;                                          // fix entries a chunk of a query tile can carry

@@ -18,7 +18,7 @@
 // which balances the ALU and XU pipes at the measured 4:1 LOP3:POPC rate of sm_100 (profiles/int_pipes_b200_r01.json);
 // the general kernel needs 4.5 LOP3 + 1.25 POPC.
 // Shape: block = 64 query slots x 64 references, 16 warps x 4 slots, lane = 2 references, 64 registers, 2 blocks per
-// SM (32 warps per SM).  Staging: one TMA bulk copy per operand into a 5-deep ring with full/empty mbarriers (no
+// SM (32 warps per SM).  Staging: one TMA bulk copy per operand into a 6-deep ring with full/empty mbarriers (no
 // __syncthreads in the loop: warps drift up to the ring depth apart); one elected thread refills a stage two chunks
 // after it was consumed.
 #include "common.cuh"
