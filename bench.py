@@ -347,6 +347,7 @@ def main():
             t1 = time.perf_counter()
             eng.clear_refs()
             eng.set_queries(qtext)
+            t_sq = time.perf_counter() - t1
             o = 0
             if world == 1:
                 # pipelined host loop (the reference's pool loop, nearest.c:245-338): the copy + encoder of piece i+1 run
@@ -362,10 +363,13 @@ def main():
                     o += cnt
                 eng.set_global_count(R)
                 eng.search()
+            t_ps = time.perf_counter() - t1 - t_sq
             heaps = eng.heaps()
             barrier()
             if i > 0:
                 e2e_t.append(time.perf_counter() - t1)
+                _s = eng.stats()
+                e2e_parts = {"set_queries_s": t_sq, "set_queries_host_ms": _s["set_queries_host_ms"], "set_queries_device_ms": _s["set_queries_device_ms"], "push_and_search_s": t_ps, "tables_d2h_s": time.perf_counter() - t1 - t_sq - t_ps}
         t = torch.tensor([float(np.mean(e2e_t))], dtype=torch.float64, device="cuda")
         if dist is not None:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -373,7 +377,7 @@ def main():
         chk2 = int(sum(int(sc.astype(np.int64).sum()) + int(r.sum()) for sc, r in heaps) & 0xffffffffffff)
         e2e = {"value": Q / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(Q * L * world + R * L),
                "d2h_bytes_per_step": int(world * Q * ((args.nbest + 1) * 32 + 8)), "seconds_per_step": e2e_s,
-               "same_result_as_resident_run": chk2 == checksum}
+               "same_result_as_resident_run": chk2 == checksum, "last_step_breakdown": e2e_parts}
         eng._lib.uvg_host_free_pinned(host_buf)
 
     # ---- roofline of the dominant kernel (k_paircount) ----

@@ -80,6 +80,7 @@ typedef struct uvg_stats {
                                      = executed pair-words (early abort makes this smaller than queries x refs x words) */
     int64_t max_mismatch;       /* "Highest number of ACGT mismatches" (nearest.c:324): max over queries of max_incompatible-1 */
     int64_t pivot_fix_entries;  /* pivot form of the pair-count kernel in use: fix entries over all query slots; -1: general kernel */
+    double  set_queries_host_ms, set_queries_device_ms;   /* last uvg_set_queries: host preparation / allocations + uploads */
 } uvg_stats;
 
 /* ---- life cycle ---- */

@@ -35,7 +35,8 @@ class uvg_stats(C.Structure):
                 ("n_h1_flags", C.c_int64), ("pair_kernel_launches", C.c_int64),
                 ("other_kernel_launches", C.c_int64), ("pair_kernel_ms", C.c_double), ("replay_ms", C.c_double),
                 ("search_ms", C.c_double), ("encode_ms", C.c_double), ("warp_chunks_executed", C.c_int64),
-                ("max_mismatch", C.c_int64), ("pivot_fix_entries", C.c_int64)]
+                ("max_mismatch", C.c_int64), ("pivot_fix_entries", C.c_int64),
+                ("set_queries_host_ms", C.c_double), ("set_queries_device_ms", C.c_double)]
 
 
 # every symbol include/uvaia_b200.h declares: name -> (restype, argtypes)

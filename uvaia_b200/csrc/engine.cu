@@ -15,10 +15,12 @@
 #include "kernels.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 #include <dlfcn.h>
 
@@ -75,7 +77,8 @@ struct uvg_ctx {
     // queries
     int n_query = 0, n_slots = 0, n_qtiles = 0, rows_cap = 0, qnib_stride = 0;
     uvg_query_info qinfo{};
-    int64_t qinfo_pivot_fix = -1;                     // fix entries of the pivot form (-1: general kernel)
+    int64_t qinfo_pivot_fix = -1;
+    double set_queries_host_ms = 0, set_queries_device_ms = 0;                     // fix entries of the pivot form (-1: general kernel)
     QChunk* d_qdata = nullptr;
     uint32_t *d_qnib = nullptr, *d_qamb_off = nullptr, *d_qamb_ent = nullptr;
     // pivot form of the pair-count kernel (pairpivot.cu): chosen per query set by uvg_set_queries
@@ -99,6 +102,7 @@ struct uvg_ctx {
     // dense score tiles of a round: NBUF x [rows_cap + 2][world * seg_cap] x (4 counts)
     int64_t seg_cap = 0;                              // references per rank and round the tiles can hold
     uint4* d_tiles = nullptr; size_t tile_elems = 0;  // one buffer = tile_elems uint4
+    size_t tiles_alloc = 0;                           // uint4 elements allocated (single GPU: kept across query sets)
     uint4* peer_tiles[MAX_RANKS]{};                   // base of d_tiles on every rank (peer-mapped)
     bool peers_ready = false;
     unsigned long long* d_counters = nullptr;
@@ -215,7 +219,7 @@ static void close_peers(uvg_ctx* c)
     c->peers_ready = false;
 }
 
-static void free_queries(uvg_ctx* c)
+static void free_queries(uvg_ctx* c, bool final = false)
 {
     close_peers(c);
     cudaFree(c->d_qdata); cudaFree(c->d_qnib); cudaFree(c->d_qamb_off); cudaFree(c->d_qamb_ent);
@@ -225,11 +229,11 @@ static void free_queries(uvg_ctx* c)
     cudaFree(c->d_heaps); cudaFree(c->d_heaps_all);
     cudaFree(c->d_heap_n); cudaFree(c->d_max_inc); cudaFree(c->d_batch_id); cudaFree(c->d_max_inc_batch);
     cudaFree(c->d_heap_n_all); cudaFree(c->d_max_inc_all);
-    cudaFree(c->d_tiles);
+    if (c->world > 1 || final) { cudaFree(c->d_tiles); c->d_tiles = nullptr; c->tiles_alloc = 0; }
     c->d_qdata = nullptr; c->d_qnib = c->d_qamb_off = c->d_qamb_ent = nullptr; c->d_thr_local = nullptr;
     c->d_heaps = c->d_heaps_all = nullptr;
     c->d_heap_n = c->d_max_inc = c->d_batch_id = c->d_max_inc_batch = c->d_heap_n_all = c->d_max_inc_all = nullptr;
-    c->d_tiles = nullptr; c->seg_cap = 0; c->tile_elems = 0;
+    c->seg_cap = 0; c->tile_elems = 0;
 }
 
 extern "C" void uvg_destroy(uvg_ctx* c)
@@ -240,7 +244,7 @@ extern "C" void uvg_destroy(uvg_ctx* c)
     if (c->st_rp) cudaStreamSynchronize(c->st_rp);
     if (c->st_push) cudaStreamSynchronize(c->st_push);
     if (c->st_copy) cudaStreamSynchronize(c->st_copy);
-    free_queries(c);
+    free_queries(c, true);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->d_db); cudaFree(c->d_db2); cudaFree(c->d_non_n); cudaFree(c->d_ramb_off); cudaFree(c->d_ramb_ent); cudaFree(c->d_ever);
     cudaFree(c->d_counters); cudaFree(c->d_nacc); cudaFree(c->d_ipc);
@@ -289,6 +293,21 @@ static int ensure_db2(uvg_ctx* c)
     return UVG_OK;
 }
 
+// host threads for the one-off query preparation (the reference does this serially, fastaseq.c:732-777)
+static int host_threads(int64_t useful)
+{
+    const unsigned hw = std::thread::hardware_concurrency();
+    return (int)std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(hw ? hw : 1, 32), useful));
+}
+template <typename F>
+static void parallel_ranges(int n, int T, F&& fn)                  // fn(thread, begin, end) over T contiguous ranges of [0, n)
+{
+    if (T <= 1) { fn(0, 0, n); return; }
+    std::vector<std::thread> th;
+    for (int t = 0; t < T; ++t) th.emplace_back([&, t] { fn(t, (int)((int64_t)n * t / T), (int)((int64_t)n * (t + 1) / T)); });
+    for (auto& x : th) x.join();
+}
+
 // =====================================================================================================================
 // queries
 // =====================================================================================================================
@@ -324,6 +343,7 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
     int rc = sync_all(c);
     if (rc) return rc;
+    const auto t_begin = std::chrono::steady_clock::now();
     free_queries(c);
     const int L = c->nchar, trim = c->trim, Q = n_query;
     const bool acgt = c->prm.acgt_mode != 0;
@@ -335,28 +355,60 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
 
     // ---- site partition (create_query_indices, src/fastaseq.c:732-777) ----
     // usable byte: --acgt: one of ACGT (is_site_acgt, utils.c:285-289); default: valid text (is_site_valid, utils.c:291-295)
+    // Host threads sweep disjoint query ranges (row-major: one pass over the query text); per site and range: the first
+    // usable byte, whether any / all queries are usable, whether the usable ones agree, and -- for the pivot form of the
+    // pair-count kernel -- how many queries hold each plain base.  The ranges are merged in query order.
+    bool pivot_ok = !acgt && (int64_t)c->Wp * 32 <= 65535 && !c->prm.early_abort && c->prm.pair_kernel != UVG_PAIR_GENERAL;
     std::vector<uint8_t> cons(L, 'N');
     std::vector<uint8_t> site_class(L, 0);                                  // 1 = idx, 2 = idx_m, 3 = idx_c
+    std::vector<uint8_t> pv(pivot_ok ? L : 0, 1);                           // pivot base per site (one-hot code)
     int n_idx = 0, n_idx_m = 0, n_idx_c = 0;
     {
-        // row-major sweep (one pass over the query text): per site the first usable byte, whether any / all queries are
-        // usable and whether the usable ones agree
-        std::vector<uint8_t> first(L, 0), any(L, 0), all(L, 1), same(L, 1);
-        for (int q = 0; q < Q; ++q) {
-            const uint8_t* row = text + (size_t)q * L;
-            for (int i = trim; i < L - trim; ++i) {
-                const uint8_t ch = up[row[i]];
-                const bool usable = acgt ? (ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T') : (lut[2][ch] != 0);
-                if (!usable) { all[i] = 0; continue; }
-                if (!any[i]) { any[i] = 1; first[i] = ch; }
-                else if (ch != first[i]) same[i] = 0;
+        const int T = host_threads(std::min<int64_t>(Q, std::max<int64_t>(1, ((int64_t)256 << 20) / ((int64_t)L * 20))));
+        std::vector<uint8_t> first((size_t)T * L, 0), any((size_t)T * L, 0), all((size_t)T * L, 1), same((size_t)T * L, 1);
+        std::vector<uint32_t> cnt(pivot_ok ? (size_t)T * L * 4 : 0, 0);
+        parallel_ranges(Q, T, [&](int t, int qa, int qb) {
+            uint8_t *f = &first[(size_t)t * L], *an = &any[(size_t)t * L], *al = &all[(size_t)t * L], *sm = &same[(size_t)t * L];
+            uint32_t* cn = pivot_ok ? &cnt[(size_t)t * L * 4] : nullptr;
+            for (int q = qa; q < qb; ++q) {
+                const uint8_t* row = text + (size_t)q * L;
+                for (int i = trim; i < L - trim; ++i) {
+                    const uint8_t ch = up[row[i]];
+                    const bool usable = acgt ? (ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T') : (lut[2][ch] != 0);
+                    if (!usable) { al[i] = 0; continue; }
+                    if (!an[i]) { an[i] = 1; f[i] = ch; }
+                    else if (ch != f[i]) sm[i] = 0;
+                    if (cn) {
+                        const uint32_t code = code_lut[ch];
+                        if (code && !(code & (code - 1))) ++cn[(size_t)i * 4 + (code == 1 ? 0 : code == 2 ? 1 : code == 4 ? 2 : 3)];
+                    }
+                }
             }
-        }
+        });
         for (int i = trim; i < L - trim; ++i) {
-            if (!any[i]) continue;
-            if (!same[i]) { site_class[i] = 1; ++n_idx; cons[i] = '#'; }
-            else if (all[i]) { site_class[i] = 3; ++n_idx_c; cons[i] = first[i]; }
-            else { site_class[i] = 2; ++n_idx_m; cons[i] = first[i]; }
+            uint8_t f0 = 0; bool an = false, al = true, sm = true;
+            for (int t = 0; t < T; ++t) {
+                const size_t k = (size_t)t * L + i;
+                if (!all[k]) al = false;
+                if (!any[k]) continue;
+                if (!same[k]) sm = false;
+                if (!an) { an = true; f0 = first[k]; }
+                else if (first[k] != f0) sm = false;
+            }
+            if (!an) continue;
+            if (!sm) { site_class[i] = 1; ++n_idx; cons[i] = '#'; }
+            else if (al) { site_class[i] = 3; ++n_idx_c; cons[i] = f0; }
+            else { site_class[i] = 2; ++n_idx_m; cons[i] = f0; }
+        }
+        if (pivot_ok) {
+            // the plain base most queries hold (ties: A before C before G before T; a site nobody holds a base at: A)
+            for (int i = trim; i < L - trim; ++i) {
+                uint32_t tot[4] = {0, 0, 0, 0};
+                for (int t = 0; t < T; ++t) for (int k = 0; k < 4; ++k) tot[k] += cnt[((size_t)t * L + i) * 4 + k];
+                int best = 0;
+                for (int k = 1; k < 4; ++k) if (tot[k] > tot[best]) best = k;
+                pv[i] = (uint8_t)(1u << best);
+            }
         }
     }
     c->n_query = Q;
@@ -368,92 +420,73 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     c->qinfo.n_idx = n_idx; c->qinfo.n_idx_m = n_idx_m; c->qinfo.n_idx_c = n_idx_c;
     if (info) *info = c->qinfo;
 
-    // ---- planes, nibble codes and ambiguity lists of every slot (zero outside the trimmed range) ----
+    // ---- planes, nibble codes and ambiguity lists of every slot (zero outside the trimmed range); for the pivot form
+    // also the (base, equals-pivot) planes and, per slot, the bases that differ from the pivot.  One pass, host threads
+    // over disjoint slot ranges (every slot owns its words of the chunk arrays). ----
     const size_t n_chunk_total = (size_t)c->n_qtiles * c->n_chunks;
     std::vector<QChunk> qd(n_chunk_total);
     memset(qd.data(), 0, n_chunk_total * sizeof(QChunk));
     std::vector<uint32_t> qnib((size_t)c->n_slots * c->qnib_stride, 0);
+    std::vector<std::vector<uint32_t>> amb(c->n_slots), snp(pivot_ok ? c->n_slots : 0);
+    std::vector<QChunk2> qd2;
+    if (pivot_ok) { qd2.resize(n_chunk_total); memset(qd2.data(), 0, n_chunk_total * sizeof(QChunk2)); }
+    parallel_ranges(c->n_slots, host_threads(c->n_slots), [&](int, int sa, int sb) {
+        std::vector<uint32_t> plain_in_chunk(c->n_chunks);
+        for (int q = sa; q < sb; ++q) {
+            const int qt = q / QTILE, qi = q % QTILE;
+            const bool is_cons = q == Q;
+            const uint8_t* row = is_cons ? cons.data() : text + (size_t)q * L;
+            std::fill(plain_in_chunk.begin(), plain_in_chunk.end(), 0u);
+            for (int s = trim; s < L - trim; ++s) {
+                if (is_cons && site_class[s] != 3) continue;                // the consensus is scored on idx_c only
+                const uint32_t code = code_lut[up[row[s]]];
+                const int w = s >> 5, k = w & 3;
+                const uint32_t bit = 1u << (s & 31);
+                const size_t ci = (size_t)qt * c->n_chunks + w / WC;
+                uint4* pl = qd[ci].pl[(w % WC) / 4][qi];
+                if (acgt && site_class[s] == 1) (&pl[3].x)[k] |= bit;       // segregating-site mask (dist_unique, nearest.c:459-470)
+                if (!code) continue;
+                qnib[(size_t)q * c->qnib_stride + (s >> 3)] |= code << ((s & 7) * 4);
+                if (code & (code - 1)) { amb[q].push_back((uint32_t)s | (code << 28)); continue; }
+                (&pl[0].x)[k] |= bit;
+                if (code & 10u) (&pl[1].x)[k] |= bit;                       // C or T
+                if (code & 12u) (&pl[2].x)[k] |= bit;                       // G or T
+                ++plain_in_chunk[w / WC];
+                if (pivot_ok) {
+                    uint4* p2 = qd2[ci].pl[(w % WC) / 4][qi];
+                    (&p2[0].x)[k] |= bit;
+                    if (code == pv[s]) (&p2[1].x)[k] |= bit;
+                    else snp[q].push_back((uint32_t)s | (code << 28));
+                }
+            }
+            uint32_t run = 0;
+            for (int k = c->n_chunks - 1; k >= 0; --k) {
+                qd[(size_t)qt * c->n_chunks + k].rem[qi] = run;
+                run += plain_in_chunk[k];
+            }
+        }
+    });
     std::vector<uint32_t> amb_off(c->n_slots + 1, 0), amb_ent;
-    std::vector<uint32_t> plain_in_chunk(c->n_chunks);
     for (int q = 0; q < c->n_slots; ++q) {
-        const int qt = q / QTILE, qi = q % QTILE;
-        const bool is_cons = q == Q;
-        const uint8_t* row = is_cons ? cons.data() : text + (size_t)q * L;
-        std::fill(plain_in_chunk.begin(), plain_in_chunk.end(), 0u);
         amb_off[q] = (uint32_t)amb_ent.size();
-        for (int s = trim; s < L - trim; ++s) {
-            if (is_cons && site_class[s] != 3) continue;                    // the consensus is scored on idx_c only
-            const uint32_t code = code_lut[up[row[s]]];
-            const int w = s >> 5, k = w & 3;
-            const uint32_t bit = 1u << (s & 31);
-            QChunk& ch = qd[(size_t)qt * c->n_chunks + w / WC];
-            uint4* pl = ch.pl[(w % WC) / 4][qi];
-            uint32_t* p0 = &pl[0].x; uint32_t* p1 = &pl[1].x; uint32_t* p2 = &pl[2].x; uint32_t* p3 = &pl[3].x;
-            if (acgt && site_class[s] == 1) p3[k] |= bit;                   // segregating-site mask (dist_unique, nearest.c:459-470)
-            if (!code) continue;
-            qnib[(size_t)q * c->qnib_stride + (s >> 3)] |= code << ((s & 7) * 4);
-            if (code & (code - 1)) { amb_ent.push_back((uint32_t)s | (code << 28)); continue; }
-            p0[k] |= bit;
-            if (code & 10u) p1[k] |= bit;                                   // C or T
-            if (code & 12u) p2[k] |= bit;                                   // G or T
-            ++plain_in_chunk[w / WC];
-        }
-        uint32_t run = 0;
-        for (int k = c->n_chunks - 1; k >= 0; --k) {
-            qd[(size_t)qt * c->n_chunks + k].rem[qi] = run;
-            run += plain_in_chunk[k];
-        }
+        amb_ent.insert(amb_ent.end(), amb[q].begin(), amb[q].end());
     }
     amb_off[c->n_slots] = (uint32_t)amb_ent.size();
 
-    // ---- pivot form (pairpivot.cu): pivot sequence, query planes (base, equals-pivot) and fix lists ----
-    std::vector<QChunk2> qd2;
+    // ---- pivot form (pairpivot.cu): pivot planes, fix blocks of the chunks, epilogue lists ----
     std::vector<uint32_t> fix_off, fix_ent, pivot_words;
     int64_t n_fix_total = 0;
-    bool pivot_ok = !acgt && (int64_t)c->Wp * 32 <= 65535 && !c->prm.early_abort && c->prm.pair_kernel != UVG_PAIR_GENERAL;
     if (pivot_ok) {
-        // per site the plain base most queries hold (ties: A before C before G before T; a site nobody holds a base at: A)
-        std::vector<uint32_t> cnt((size_t)L * 4, 0);
-        for (int q = 0; q < Q; ++q) {
-            const uint8_t* row = text + (size_t)q * L;
-            for (int s = trim; s < L - trim; ++s) {
-                const uint32_t code = code_lut[up[row[s]]];
-                if (code && !(code & (code - 1))) ++cnt[(size_t)s * 4 + (code == 1 ? 0 : code == 2 ? 1 : code == 4 ? 2 : 3)];
-            }
-        }
-        std::vector<uint8_t> pv(L, 1);
         pivot_words.assign((size_t)(c->Wp / 4) * 8, 0u);                     // [unit][plane b0, b1][4 words]
         for (int s = 0; s < L; ++s) {
-            int best = 0;
-            for (int k = 1; k < 4; ++k) if (cnt[(size_t)s * 4 + k] > cnt[(size_t)s * 4 + best]) best = k;
-            pv[s] = (uint8_t)(1u << best);
             const int w = s >> 5;
             uint32_t* u = &pivot_words[(size_t)(w >> 2) * 8];
             if (pv[s] & 10u) u[w & 3] |= 1u << (s & 31);
             if (pv[s] & 12u) u[4 + (w & 3)] |= 1u << (s & 31);
         }
-        qd2.resize(n_chunk_total);
-        memset(qd2.data(), 0, n_chunk_total * sizeof(QChunk2));
-        // planes + per slot: the bases that differ from the pivot (site, one-hot code) and the ambiguity codes
-        std::vector<std::vector<uint32_t>> snp(c->n_slots), epi(c->n_slots);
+        std::vector<std::vector<uint32_t>> epi = amb;                       // the epilogue resolves the ambiguity codes ...
         size_t n_snp = 0;
-        for (int q = 0; q < c->n_slots; ++q) {
-            const int qt = q / QTILE, qi = q % QTILE;
-            const bool is_cons = q == Q;
-            const uint8_t* row = is_cons ? cons.data() : text + (size_t)q * L;
-            for (int s = trim; s < L - trim; ++s) {
-                if (is_cons && site_class[s] != 3) continue;
-                const uint32_t code = code_lut[up[row[s]]];
-                if (!code) continue;
-                if (code & (code - 1)) { epi[q].push_back((uint32_t)s | (code << 28)); continue; }
-                const int w = s >> 5, k = w & 3;
-                const uint32_t bit = 1u << (s & 31);
-                uint4* pl = qd2[(size_t)qt * c->n_chunks + w / WC].pl[(w % WC) / 4][qi];
-                (&pl[0].x)[k] |= bit;
-                if (code == pv[s]) (&pl[1].x)[k] |= bit;
-                else { snp[q].push_back((uint32_t)s | (code << 28)); ++n_snp; }
-            }
-        }
+        for (int q = 0; q < c->n_slots; ++q) n_snp += snp[q].size();
         // fix blocks: entries of a (tile, chunk) ordered by warp; what does not fit goes to the slot's epilogue list
         size_t n_overflow = 0;
         std::vector<size_t> cur(c->n_slots, 0);
@@ -497,6 +530,7 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
             (n_snp > (size_t)c->n_slots * (size_t)std::max(4, c->W / 8) || n_overflow > (size_t)c->n_slots * 2)) pivot_ok = false;
     }
 
+    const auto t_host = std::chrono::steady_clock::now();
     // ---- device allocations ----
     const int rows = c->rows_cap;
     UVG_CUDA(c, cudaMalloc(&c->d_qdata, n_chunk_total * sizeof(QChunk)));
@@ -521,7 +555,11 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
         cap = std::max<int64_t>(GROUP * RPL, std::min(cap, fit));
         c->seg_cap = cap;
         c->tile_elems = (size_t)(rows + 2) * c->world * cap;
-        UVG_CUDA(c, cudaMalloc(&c->d_tiles, NBUF * c->tile_elems * sizeof(uint4)));
+        if (NBUF * c->tile_elems > c->tiles_alloc) {                       // the multi-GiB buffer is kept when the next query set fits
+            cudaFree(c->d_tiles); c->d_tiles = nullptr; c->tiles_alloc = 0;
+            UVG_CUDA(c, cudaMalloc(&c->d_tiles, NBUF * c->tile_elems * sizeof(uint4)));
+            c->tiles_alloc = NBUF * c->tile_elems;
+        }
         if (c->world == 1) { c->peer_tiles[0] = c->d_tiles; c->peers_ready = true; }
     }
     UVG_CUDA(c, cudaMemcpyAsync(c->d_qdata, qd.data(), n_chunk_total * sizeof(QChunk), cudaMemcpyHostToDevice, c->st));
@@ -546,7 +584,11 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     }
     c->qinfo_pivot_fix = pivot_ok ? n_fix_total : -1;
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
-    return reset_heaps(c);
+    rc = reset_heaps(c);
+    const auto t_end = std::chrono::steady_clock::now();
+    c->set_queries_host_ms = std::chrono::duration<double, std::milli>(t_host - t_begin).count();
+    c->set_queries_device_ms = std::chrono::duration<double, std::milli>(t_end - t_host).count();
+    return rc;
 }
 
 extern "C" int uvg_reset_search(uvg_ctx* c)
@@ -1058,6 +1100,7 @@ extern "C" int uvg_get_stats(uvg_ctx* c, uvg_stats* out)
     c->stats.n_admitted = (int64_t)c->h_pinned[16]; c->stats.n_h1_flags = (int64_t)c->h_pinned[17];
     c->stats.warp_chunks_executed = c->work_last / 16;          // the counter is in (pair, chunk) units; 16 pairs per lane and warp
     c->stats.pivot_fix_entries = c->pivot_on ? c->qinfo_pivot_fix : -1;
+    c->stats.set_queries_host_ms = c->set_queries_host_ms; c->stats.set_queries_device_ms = c->set_queries_device_ms;
     if (c->n_query) {
         int rc = cache_heaps(c);
         if (rc) return rc;
