@@ -134,8 +134,10 @@ int uvg_get_stats(uvg_ctx* ctx, uvg_stats* out);
 
 /* ---- row sharding over several GPUs (one context per GPU / process) ----
  * Round j covers global ordinals [S_j, S_j + world*T_j) and rank g holds [S_j + g*T_j, S_j + (g+1)*T_j), with
- * T_1 = first_round, T_{j+1} = min(4*T_j, max_round).  uvg_shard_of maps a global ordinal to (rank, local index). */
-int uvg_shard_of(int64_t ordinal, int32_t world, int32_t first_round, int32_t max_round, int32_t* rank, int64_t* local);
+ * T_1 = first_round, T_{j+1} = min(4*T_j, max_round); the last round, which the remaining references cannot fill, is cut
+ * to ceil(remaining / world) rounded up to 64 so that the tail is shared evenly.  uvg_shard_of maps a global ordinal to
+ * (rank, local index); n_total = accepted references in all (the value given to uvg_set_global_count). */
+int uvg_shard_of(int64_t ordinal, int64_t n_total, int32_t world, int32_t first_round, int32_t max_round, int32_t* rank, int64_t* local);
 int uvg_nccl_unique_id(void* out128);                          /* 128 bytes, made by rank 0, sent to all by the host */
 int uvg_nccl_init(uvg_ctx* ctx, const void* id128);            /* collective over all `world` contexts */
 /* In sharded mode every rank declares how many accepted references exist in total before uvg_search. */

@@ -72,11 +72,11 @@ def test_shard_schedule_partitions_ordinals_in_file_order():
             local = 0
             for gb, cnt in rank_tiles(total, rank, world, first, mx):
                 for o in (gb, gb + cnt - 1):
-                    r, l = Engine.shard_of(o, world, first, mx)
+                    r, l = Engine.shard_of(o, world, first, mx, total)
                     assert r == rank
                 seen[rank] = seen.get(rank, []) + [(gb, cnt, local)]
                 # local index of the tile start as the library computes it
-                r, l = Engine.shard_of(gb, world, first, mx)
+                r, l = Engine.shard_of(gb, world, first, mx, total)
                 assert l >= local
                 local = l + cnt
         # tiles of all ranks cover [0, total) exactly once
@@ -86,3 +86,6 @@ def test_shard_schedule_partitions_ordinals_in_file_order():
             assert gb == pos
             pos += cnt
         assert pos == total
+        # the tail round is shared evenly: no rank holds more than 64 + one round's rounding above the mean
+        per = [sum(cnt for _, cnt, _ in seen.get(r, [])) for r in range(world)]
+        assert max(per) - min(per) <= 64 + first, per

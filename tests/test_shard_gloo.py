@@ -135,6 +135,6 @@ def test_ownership_and_tiles_are_partitions():
             assert pos == total
             for o in (0, total // 2, total - 1):
                 if total:
-                    r, l = shard.shard_of(o, world, 64, 4096)
+                    r, l = shard.shard_of(o, world, 64, 4096, total)
                     tiles = shard.rank_tiles(total, r, world, 64, 4096)
                     assert any(gb <= o < gb + cnt for gb, cnt in tiles)

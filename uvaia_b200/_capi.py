@@ -59,7 +59,7 @@ SYMBOLS = {
     "uvg_get_heap": (C.c_int, [_P, C.c_int32, C.POINTER(uvg_item), C.POINTER(C.c_int32)]),
     "uvg_get_ever_best": (C.c_int, [_P, C.c_int64, C.c_int64, _P]),
     "uvg_get_stats": (C.c_int, [_P, C.POINTER(uvg_stats)]),
-    "uvg_shard_of": (C.c_int, [C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
+    "uvg_shard_of": (C.c_int, [C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
     "uvg_nccl_unique_id": (C.c_int, [_P]),
     "uvg_nccl_init": (C.c_int, [_P, _P]),
     "uvg_set_global_count": (C.c_int, [_P, C.c_int64]),

@@ -142,6 +142,14 @@ static int32_t round_size_max(const uvg_params& p)
     return std::max(v, round_size_first(p));
 }
 static int32_t round_size_next(int32_t cur, int32_t mx) { int64_t n = (int64_t)cur * 4; return (int32_t)std::min<int64_t>(n, mx); }
+// sharded mode: the last round, which the remaining references cannot fill, is cut so that every rank gets the same share
+// of the tail (ceil(remaining / world) rounded up to a block's 64 references); total < 0 = unknown: nominal size
+static int64_t round_size_at(int64_t S, int64_t T, int64_t total, int world)
+{
+    if (total < 0 || S + (int64_t)world * T <= total) return T;
+    const int64_t rem = total - S, per = GROUP * RPL;
+    return std::min<int64_t>(T, std::max<int64_t>(per, ((rem + world - 1) / world + per - 1) / per * per));
+}
 
 extern "C" int uvg_abi_version(void) { return UVG_ABI_VERSION; }
 
@@ -942,7 +950,7 @@ static int search_enqueue(uvg_ctx* c)
         UVG_CUDA(c, cudaEventRecord(c->ev_a, c->st));
     }
     for (;;) {
-        const int64_t T = c->next_round;
+        const int64_t T = c->world == 1 ? (int64_t)c->next_round : round_size_at(c->round_global_start, c->next_round, c->global_total, c->world);
         int64_t lstart, cnt, rfirst, rcount;
         if (c->world == 1) {
             cnt = std::min<int64_t>(T, c->db_n - c->db_scored);
@@ -1115,19 +1123,20 @@ extern "C" int uvg_get_stats(uvg_ctx* c, uvg_stats* out)
 // =====================================================================================================================
 // sharding helpers + NCCL
 // =====================================================================================================================
-extern "C" int uvg_shard_of(int64_t ordinal, int32_t world, int32_t first_round, int32_t max_round, int32_t* rank, int64_t* local)
+extern "C" int uvg_shard_of(int64_t ordinal, int64_t n_total, int32_t world, int32_t first_round, int32_t max_round, int32_t* rank, int64_t* local)
 {
-    if (ordinal < 0 || world < 1) return UVG_EINVAL;
+    if (ordinal < 0 || world < 1 || (n_total >= 0 && ordinal >= n_total)) return UVG_EINVAL;
     uvg_params p{}; p.first_round = first_round; p.max_round = max_round;
     int64_t T = round_size_first(p), S = 0, Ls = 0;
     const int32_t mx = round_size_max(p);
     for (;;) {
-        if (ordinal < S + (int64_t)world * T) {
-            if (rank) *rank = (int32_t)((ordinal - S) / T);
-            if (local) *local = Ls + (ordinal - S) % T;
+        const int64_t Te = round_size_at(S, T, n_total, world);
+        if (ordinal < S + (int64_t)world * Te) {
+            if (rank) *rank = (int32_t)((ordinal - S) / Te);
+            if (local) *local = Ls + (ordinal - S) % Te;
             return UVG_OK;
         }
-        S += (int64_t)world * T; Ls += T;
+        S += (int64_t)world * Te; Ls += Te;
         T = round_size_next((int32_t)T, mx);
     }
 }

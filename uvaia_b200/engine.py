@@ -155,10 +155,10 @@ class Engine:
 
     # ---- sharding ----
     @staticmethod
-    def shard_of(ordinal, world, first_round=0, max_round=0):
+    def shard_of(ordinal, world, first_round=0, max_round=0, total=-1):
         r = C.c_int32(0)
         l = C.c_int64(0)
-        rc = _capi.lib().uvg_shard_of(int(ordinal), int(world), int(first_round), int(max_round), C.byref(r), C.byref(l))
+        rc = _capi.lib().uvg_shard_of(int(ordinal), int(total), int(world), int(first_round), int(max_round), C.byref(r), C.byref(l))
         if rc != 0:
             raise UvgError("uvg_shard_of: bad arguments")
         return r.value, l.value

@@ -3,7 +3,8 @@
 The reference is a single process; the partition is ours.  The per-query admission of the reference is
 order dependent, so shards are NOT independent top-k problems: references are dealt to ranks in rounds of contiguous
 tiles in file order -- round j covers global ordinals [S_j, S_j + world*T_j), rank g scores [S_j + g*T_j, S_j + (g+1)*T_j),
-T_1 = first_round, T_{j+1} = min(4*T_j, max_round) -- and the scores of every round are handed to the rank that owns
+T_1 = first_round, T_{j+1} = min(4*T_j, max_round); the LAST round, which the remaining references cannot fill, is cut
+to ceil(remaining / world) rounded up to 64 so that every rank gets the same share of the tail -- and the scores of every round are handed to the rank that owns
 the query (query tile qt belongs to rank qt % world), which replays them in global file order.
 """
 from __future__ import annotations
@@ -21,13 +22,22 @@ def round_sizes(first_round=0, max_round=0):
     return first, max(mx, first)
 
 
+def round_size_at(S, T, total, world):
+    """size per rank of the round that starts at global ordinal S with nominal size T (twin of round_size_at, engine.cu)"""
+    if total is None or total < 0 or S + world * T <= total:
+        return T
+    rem = total - S
+    return min(T, max(64, ((rem + world - 1) // world + 63) // 64 * 64))
+
+
 def rounds(total, world, first_round=0, max_round=0):
     """[(S_j, T_j)] for every round needed to cover `total` accepted references"""
     T, mx = round_sizes(first_round, max_round)
     out, S = [], 0
     while S < total:
-        out.append((S, T))
-        S += world * T
+        Te = round_size_at(S, T, total, world)
+        out.append((S, Te))
+        S += world * Te
         T = min(4 * T, mx)
     return out
 
@@ -43,15 +53,16 @@ def rank_tiles(total, rank, world, first_round=0, max_round=0):
     return out
 
 
-def shard_of(ordinal, world, first_round=0, max_round=0):
+def shard_of(ordinal, world, first_round=0, max_round=0, total=None):
     """(rank, local index) of a global ordinal: python twin of uvg_shard_of"""
     T, mx = round_sizes(first_round, max_round)
     S = Ls = 0
     while True:
-        if ordinal < S + world * T:
-            return (ordinal - S) // T, Ls + (ordinal - S) % T
-        S += world * T
-        Ls += T
+        Te = round_size_at(S, T, total, world)
+        if ordinal < S + world * Te:
+            return (ordinal - S) // Te, Ls + (ordinal - S) % Te
+        S += world * Te
+        Ls += Te
         T = min(4 * T, mx)
 
 
