@@ -28,8 +28,22 @@ sys.path.insert(0, ROOT)
 
 NCHAR = 29903
 # algorithmic instruction counts per (pair, 32-site word) of the two pair-count kernels
-OPS = {"pivot": {"kernel": "k_pairpivot", "lop3": 4.0, "popc": 1.0},       # 2 AND + 2 x (one 3:2 compressor per two words); 2 x 0.5 POPC
-       "general": {"kernel": "k_paircount", "lop3": 4.5, "popc": 1.25}}    # 3 for valid+match, 1.5 carry-save tree; 1 + 0.25 POPC
+OPS = {"pivot": {"kernel": "k_pairpivot", "lop3": 4.0, "popc": 1.0, "db_bytes_per_word": 24,     # 2 AND + 2 x (one 3:2 compressor per two words); 2 x 0.5 POPC
+                 "ncu": "ncu_pairpivot_r01g.json"},
+       "general": {"kernel": "k_paircount", "lop3": 4.5, "popc": 1.25, "db_bytes_per_word": 12,  # 3 for valid+match, 1.5 carry-save tree; 1 + 0.25 POPC
+                   "ncu": "ncu_paircount_r01e_csa.json"}}
+
+
+def ncu_traffic(name):
+    """DRAM bytes (read + write) of one launch of the dominant kernel from the committed `ncu --set full` capture"""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", name)))
+        unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        rd, wr = d["dram__bytes_read.sum"], d["dram__bytes_write.sum"]
+        grid = int(float(d["launch__grid_size"][0]))
+        return {"bytes": float(rd[0]) * unit[rd[1]] + float(wr[0]) * unit[wr[1]], "launch_grid_blocks": grid, "source": "profiles/" + name}
+    except Exception:
+        return None
 
 
 def parse_args():
@@ -255,7 +269,8 @@ def main():
             "warmup": args.warmup, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32 bit-planes / int32 counts",
             "data": "synthetic (device generator, seeds 1/1001/2002)",
             "config": {"workload": workload, "nbest": args.nbest, "early_abort": bool(args.early_abort), "sharding": "rows x%d" % world,
-                       "l2": "inputs larger than L2 (packed DB %.1f GB per pass)" % (R * ((L + 255) // 256 * 256) * 3 / 8 / 1e9)}}
+                       "l2": "inputs larger than L2 (packed DB %.1f GB; the pivot form streams its derived planes, %.1f GB, once per pass)"
+                             % (R * ((L + 255) // 256 * 256) * 3 / 8 / 1e9, R * ((L + 255) // 256 * 256) * 6 / 8 / 1e9)}}
 
     if args.impl == "reference":
         times = []
@@ -392,10 +407,15 @@ def main():
     f_l, f_p = lop3 / peaks["lop3_gips"], popc / peaks["popc_gips"]
     bound = "int-popc" if f_p >= f_l else "int-lop3"
     n_qtiles = (Q + 1 + 63) // 64                             # + the consensus pseudo-query
-    db_bytes = n_local * ((W + 7) // 8 * 8) * 12              # three bit-planes per 32-site word
+    db_bytes = n_local * ((W + 7) // 8 * 8) * ops["db_bytes_per_word"]        # streamed database bytes per 32-site word and reference
+    tr = ncu_traffic(ops["ncu"])
+    if tr:   # algorithmic bytes of the captured launch: its slice of the streamed database once + one 16-byte record per pair
+        refs = tr["launch_grid_blocks"] // n_qtiles * 64
+        tr["algorithmic_bytes"] = refs * ((W + 7) // 8 * 8) * ops["db_bytes_per_word"] + refs * (Q + 1) * 16
+        tr["launch_refs"] = refs
     roofline = {"kernel": ops["kernel"], "bound": bound, "achieved": popc if bound == "int-popc" else lop3,
                 "peak": peaks["popc_gips"] if bound == "int-popc" else peaks["lop3_gips"], "unit": "Gthread-inst/s",
-                "frac": max(f_l, f_p), "traffic": None,
+                "frac": max(f_l, f_p), "traffic": tr["bytes"] if tr else None, "traffic_detail": tr,
                 "note": "INT pipes bind (north_star): %.2f LOP3 + %.2f POPC per EXECUTED pair x 32-site word (padding and early abort accounted for); peaks = profiles/int_pipes_b200_r01.json (measured)"
                         % (ops["lop3"], ops["popc"]),
                 "lop3": {"achieved": lop3, "peak": peaks["lop3_gips"], "frac": f_l}, "popc": {"achieved": popc, "peak": peaks["popc_gips"], "frac": f_p},
