@@ -1,0 +1,513 @@
+/* uvaia_b200 -- C host program of the B200-native n-best search: the `uvaia` command line (src/nearest.c:57-84,
+ * 159-353 of the reference) on top of the C ABI of libuvaia_b200.so (include/uvaia_b200.h).
+ *
+ * The host does what the reference's host code does around the scoring seam and nothing else:
+ *   - FASTA reader with the reference's hygiene rules (fastaseq.c:410-486, nexus_common.c:133-145), codec by content
+ *     (file_compression.c:21-47): raw and gzip through zlib, xz / bzip2 through the command line tools;
+ *   - query quality filter (utils.c:10-48), ordering (fastaseq.c:779-795), trim clamp (fastaseq.c:708-712);
+ *   - the reference stream in batches: -x name lookup (nearest.c:255-261), length check (nearest.c:263-278);
+ *   - <prefix>.csv.xz (nearest.c:513-547) and <prefix>.aln.xz (nearest.c:308-314, align.c:346-355).
+ * Everything that scores a pair or keeps a neighbour runs on the GPU: without the library and a B200 the program
+ * fails, there is no CPU path.  Not supported: -k/--keep_resolved (query redundancy pruning, fastaseq.c:797-841).
+ */
+#define _GNU_SOURCE
+#include <ctype.h>
+#include <getopt.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+#include <unistd.h>
+#include <zlib.h>
+
+#include "uvaia_b200.h"
+
+#define PROGRAM_VERSION "uvaia_b200 0.1 (drop-in for uvaia 2.0.2)"
+
+static void die(const char* fmt, ...)
+{   /* biomcmc_error (lowlevel.c:39-52): message to stderr, exit(EXIT_FAILURE) */
+    va_list ap;
+    va_start(ap, fmt);
+    fprintf(stderr, "uvaia_b200 error: ");
+    vfprintf(stderr, fmt, ap);
+    fprintf(stderr, "\n");
+    va_end(ap);
+    exit(EXIT_FAILURE);
+}
+static void* xmalloc(size_t n) { void* p = malloc(n ? n : 1); if (!p) die("out of memory (%zu bytes)", n); return p; }
+static void* xrealloc(void* q, size_t n) { void* p = realloc(q, n ? n : 1); if (!p) die("out of memory (%zu bytes)", n); return p; }
+static double now_s(void) { struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return t.tv_sec + 1e-9 * t.tv_nsec; }
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * input: codec by content, lines ending at \n or \r
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct {
+    gzFile gz; FILE* pipe;
+    unsigned char* buf; size_t cap, beg, end; int eof;
+    unsigned char* line; size_t line_cap;
+} reader_t;
+
+static char* shell_quote(const char* s)
+{
+    size_t n = strlen(s), k = 0;
+    char* q = xmalloc(4 * n + 3);
+    q[k++] = '\'';
+    for (size_t i = 0; i < n; ++i) { if (s[i] == '\'') { memcpy(q + k, "'\\''", 4); k += 4; } else q[k++] = s[i]; }
+    q[k++] = '\''; q[k] = 0;
+    return q;
+}
+
+static void reader_open(reader_t* r, const char* path)
+{
+    memset(r, 0, sizeof *r);
+    unsigned char magic[6] = {0};
+    FILE* f = fopen(path, "rb");
+    if (!f) die("cannot open file %s", path);
+    size_t got = fread(magic, 1, 6, f);
+    fclose(f);
+    const char* tool = NULL;
+    if (got >= 6 && !memcmp(magic, "\xfd" "7zXZ\0", 6)) tool = "xz -dc -- ";
+    else if (got >= 3 && !memcmp(magic, "BZh", 3)) tool = "bzip2 -dc -- ";
+    if (tool) {
+        char* q = shell_quote(path);
+        char* cmd = xmalloc(strlen(tool) + strlen(q) + 1);
+        sprintf(cmd, "%s%s", tool, q);
+        r->pipe = popen(cmd, "r");
+        if (!r->pipe) die("cannot run '%s'", cmd);
+        free(cmd); free(q);
+    } else {
+        r->gz = gzopen(path, "rb");                         /* transparent for uncompressed files */
+        if (!r->gz) die("cannot open file %s", path);
+        gzbuffer(r->gz, 1 << 20);
+    }
+    r->cap = 4 << 20;
+    r->buf = xmalloc(r->cap);
+}
+
+static void reader_close(reader_t* r)
+{
+    if (r->gz) gzclose(r->gz);
+    if (r->pipe) pclose(r->pipe);
+    free(r->buf); free(r->line);
+    memset(r, 0, sizeof *r);
+}
+
+static int reader_fill(reader_t* r)
+{
+    if (r->eof) return 0;
+    if (r->beg > 0) { memmove(r->buf, r->buf + r->beg, r->end - r->beg); r->end -= r->beg; r->beg = 0; }
+    if (r->end == r->cap) { r->cap *= 2; r->buf = xrealloc(r->buf, r->cap); }
+    long n = r->gz ? gzread(r->gz, r->buf + r->end, (unsigned)(r->cap - r->end)) : (long)fread(r->buf + r->end, 1, r->cap - r->end, r->pipe);
+    if (n < 0) die("read error");
+    if (n == 0) { r->eof = 1; return 0; }
+    r->end += (size_t)n;
+    return 1;
+}
+
+/* next line without its terminator (\n or \r, file_compression.c:216); returns 0 at end of input */
+static int reader_line(reader_t* r, const unsigned char** line, size_t* len)
+{
+    size_t scan = r->beg;
+    for (;;) {
+        for (; scan < r->end; ++scan) {
+            const unsigned char* p = memchr(r->buf + scan, '\n', r->end - scan);
+            size_t stop = p ? (size_t)(p - r->buf) : r->end;
+            const unsigned char* c = memchr(r->buf + scan, '\r', stop - scan);
+            if (c) stop = (size_t)(c - r->buf);
+            else if (!p) { scan = r->end; break; }
+            *line = r->buf + r->beg; *len = stop - r->beg;
+            r->beg = stop + 1;
+            return 1;
+        }
+        const size_t done = scan - r->beg;
+        if (!reader_fill(r)) {
+            if (r->end > r->beg) { *line = r->buf + r->beg; *len = r->end - r->beg; r->beg = r->end; return 1; }
+            return 0;
+        }
+        scan = r->beg + done;
+    }
+}
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * FASTA records with the reference's hygiene (hazard H5): lines shorter than 2 bytes and lines whose first non-blank
+ * byte is # or ; are dropped (nexus_common.c:133-145); a line containing '>' starts a record named by everything after
+ * the first '>' (fastaseq.c:432-442); sequence lines lose white space and are upper-cased (fastaseq.c:451-452).
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct {
+    reader_t rd;
+    char* next_name;            /* name of the record whose header line has been read already */
+    char* name; unsigned char* seq; size_t len, cap;
+} fasta_t;
+
+static int is_blank(unsigned char c) { return c == ' ' || (c >= '\t' && c <= '\r'); }
+
+static void fasta_open(fasta_t* f, const char* path) { memset(f, 0, sizeof *f); reader_open(&f->rd, path); }
+static void fasta_close(fasta_t* f) { reader_close(&f->rd); free(f->next_name); free(f->name); free(f->seq); memset(f, 0, sizeof *f); }
+
+/* 1 = a record is in f->name / f->seq / f->len (owned by f until the next call) */
+static int fasta_next(fasta_t* f)
+{
+    const unsigned char* ln; size_t n;
+    free(f->name); f->name = NULL; f->len = 0;
+    for (;;) {
+        int have = reader_line(&f->rd, &ln, &n);
+        if (!have) {
+            if (f->next_name) { f->name = f->next_name; f->next_name = NULL; return 1; }
+            return 0;
+        }
+        if (n < 2) continue;
+        size_t i = 0;
+        while (i < n && is_blank(ln[i])) ++i;
+        if (i == n || ln[i] == '#' || ln[i] == ';') continue;
+        const unsigned char* gt = memchr(ln, '>', n);
+        if (gt) {
+            const size_t k = (size_t)(gt - ln) + 1;
+            char* nm = xmalloc(n - k + 1);
+            memcpy(nm, ln + k, n - k); nm[n - k] = 0;
+            if (f->next_name) { f->name = f->next_name; f->next_name = nm; return 1; }
+            f->next_name = nm;
+            continue;
+        }
+        if (!f->next_name) continue;                        /* sequence text before the first header */
+        if (f->len + n > f->cap) { f->cap = 2 * (f->len + n) + 1024; f->seq = xrealloc(f->seq, f->cap); }
+        for (i = 0; i < n; ++i) if (!is_blank(ln[i])) f->seq[f->len++] = (unsigned char)toupper(ln[i]);
+    }
+}
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * byte classes
+ * ------------------------------------------------------------------------------------------------------------- */
+static unsigned char g_degen[256], g_validtxt[256], g_isacgt[256];
+static void init_tables(void)
+{   /* degeneracy of the IUPAC codes (biomcmc alignment.c:906-931); indel bytes of quick_count_sequence_non_N (fastaseq.c:642-648) */
+    const char* d1 = "ACGTU"; const char* d2 = "MRWSYK"; const char* d3 = "VHDB";
+    for (const char* p = d1; *p; ++p) g_degen[(unsigned char)*p] = 1;
+    for (const char* p = d2; *p; ++p) g_degen[(unsigned char)*p] = 2;
+    for (const char* p = d3; *p; ++p) g_degen[(unsigned char)*p] = 3;
+    memset(g_validtxt, 1, 256);
+    for (const char* p = "NnXx-?Oo."; *p; ++p) g_validtxt[(unsigned char)*p] = 0;
+    for (const char* p = "ACGTacgt"; *p; ++p) g_isacgt[(unsigned char)*p] = 1;
+}
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * queries: read, filter (utils.c:10-48), order (fastaseq.c:779-795)
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct { char** name; unsigned char* text; int n, nchar; } queries_t;
+
+typedef struct { long cnt; int idx; } order_key;
+static int cmp_order(const void* a, const void* b)
+{
+    const order_key* x = a; const order_key* y = b;
+    if (x->cnt != y->cnt) return x->cnt < y->cnt ? -1 : 1;
+    return x->idx - y->idx;
+}
+
+static queries_t read_queries(const char* path, double ambiguity, int trim_arg, int acgt, int* n_read)
+{
+    fasta_t f;
+    fasta_open(&f, path);
+    char** name = NULL; unsigned char** seq = NULL; size_t* len = NULL; int n = 0, cap = 0;
+    *n_read = 0;
+    while (fasta_next(&f)) {
+        ++*n_read;
+        const size_t L = f.len;
+        if (L < 5) continue;
+        size_t d0 = 0, d1 = 0;
+        for (size_t i = 0; i < L; ++i) { const unsigned char d = g_degen[f.seq[i]]; d0 += d == 0; d1 += d == 1; }
+        if ((double)d0 / (double)L > ambiguity) continue;
+        if ((double)d1 / (double)L < 1.0 - 1.1 * ambiguity) continue;
+        if (n == cap) { cap = cap ? 2 * cap : 256; name = xrealloc(name, cap * sizeof *name); seq = xrealloc(seq, cap * sizeof *seq); len = xrealloc(len, cap * sizeof *len); }
+        name[n] = f.name; f.name = NULL;
+        seq[n] = xmalloc(L); memcpy(seq[n], f.seq, L); len[n] = L;
+        ++n;
+    }
+    fasta_close(&f);
+    queries_t q = {0};
+    if (n < 1) return q;
+    for (int i = 1; i < n; ++i) if (len[i] != len[0]) die("query sequences are not aligned");                  /* utils.c:38-42 */
+    const int L = (int)len[0];
+    int trim = trim_arg < 0 ? 0 : trim_arg;                                                                   /* fastaseq.c:708-712 */
+    if (trim > L / 2.1) trim = (int)(L / 2.1);
+    order_key* key = xmalloc(n * sizeof *key);
+    for (int i = 0; i < n; ++i) {
+        long c = 0;
+        for (int s = trim; s < L - trim; ++s) c += acgt ? g_isacgt[seq[i][s]] : g_validtxt[seq[i][s]];
+        key[i].cnt = c; key[i].idx = i;
+    }
+    qsort(key, n, sizeof *key, cmp_order);
+    q.n = n; q.nchar = L;
+    q.name = xmalloc(n * sizeof *q.name);
+    q.text = xmalloc((size_t)n * L);
+    for (int i = 0; i < n; ++i) {
+        q.name[i] = name[key[i].idx];
+        memcpy(q.text + (size_t)i * L, seq[key[i].idx], L);
+    }
+    for (int i = 0; i < n; ++i) free(seq[i]);
+    free(seq); free(len); free(name); free(key);
+    return q;
+}
+
+/* -x: names of the kept queries (open addressing over FNV-1a) */
+typedef struct { char** slot; size_t mask; } nameset_t;
+static uint64_t fnv(const char* s) { uint64_t h = 1469598103934665603ull; for (; *s; ++s) { h ^= (unsigned char)*s; h *= 1099511628211ull; } return h; }
+static nameset_t nameset_build(char** name, int n)
+{
+    nameset_t s; size_t cap = 16;
+    while (cap < (size_t)n * 2 + 2) cap *= 2;
+    s.mask = cap - 1; s.slot = calloc(cap, sizeof *s.slot);
+    if (!s.slot) die("out of memory");
+    for (int i = 0; i < n; ++i) { size_t h = fnv(name[i]) & s.mask; while (s.slot[h]) h = (h + 1) & s.mask; s.slot[h] = name[i]; }
+    return s;
+}
+static int nameset_has(const nameset_t* s, const char* nm)
+{
+    for (size_t h = fnv(nm) & s->mask; s->slot[h]; h = (h + 1) & s->mask) if (!strcmp(s->slot[h], nm)) return 1;
+    return 0;
+}
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * output: xz through the command line tool when there is one, else gzip under the same name (what the reference's
+ * zlib-only build does, file_compression.c:288-317)
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct { FILE* pipe; gzFile gz; } writer_t;
+static writer_t writer_open(const char* path)
+{
+    writer_t w = {0};
+    if (system("command -v xz > /dev/null 2>&1") == 0) {
+        char* q = shell_quote(path);
+        char* cmd = xmalloc(strlen(q) + 32);
+        sprintf(cmd, "xz -c -T0 -2 > %s", q);
+        w.pipe = popen(cmd, "w");
+        free(cmd); free(q);
+    }
+    if (!w.pipe) { w.gz = gzopen(path, "wb"); if (!w.gz) die("cannot write %s", path); }
+    return w;
+}
+static void writer_put(writer_t* w, const void* p, size_t n)
+{
+    if (!n) return;
+    if (w->pipe) { if (fwrite(p, 1, n, w->pipe) != n) die("write error"); }
+    else if (gzwrite(w->gz, p, (unsigned)n) != (int)n) die("write error");
+}
+static void writer_close(writer_t* w) { if (w->pipe && pclose(w->pipe) != 0) die("xz failed"); if (w->gz) gzclose(w->gz); }
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * main: nearest.c:159-353
+ * ------------------------------------------------------------------------------------------------------------- */
+static void usage(const char* prog, int full)
+{
+    printf("%s\nFor every query sequence, finds the closest neighbours in the reference alignment (n-best search on a B200 GPU)\n", PROGRAM_VERSION);
+    printf("Usage: %s [-hvx] [--acgt] [-n <int>] [--trim=<int>] [-A <double>] [-a <double>] [-p <int>] -r <ref.fa(.gz,.xz)> [-r ...] "
+           "[-t <int>] [-o <without suffix>] <seqs.fa(.gz,.xz)>\n", prog);
+    if (!full) return;
+    printf("  -n, --nbest            number of best reference sequences per query to store (default=100)\n"
+           "      --trim             number of sites to trim from both ends (default=0, suggested for sarscov2=230)\n"
+           "  -a, --query_ambiguity  maximum allowed ambiguity for QUERY sequence to be excluded (default=0.5)\n"
+           "  -A, --ref_ambiguity    maximum allowed ambiguity for REFERENCE sequence to be excluded (default=0.5)\n"
+           "      --acgt             considers only ACGT sites in query sequences (mismatch-based)\n"
+           "  -x, --exclude_self     exclude reference sequences with same name as a query sequence\n"
+           "  -p, --pool             pool size of the reference program (only used to flag pool-dependent results, hazard H1)\n"
+           "  -r, --reference        aligned reference sequences (can be several files)\n"
+           "  -t, --nthreads         accepted for compatibility (scoring runs on the GPU)\n"
+           "  -o, --output           prefix of xzipped output alignment and table with nearest neighbour sequences\n"
+           "      --device           CUDA device ordinal (default 0);  --batch: reference rows per push (default 65536)\n");
+}
+
+int main(int argc, char** argv)
+{
+    int nbest = 100, trim = 0, acgt = 0, xclude = 0, pool = 0, device = 0, hires = 0;
+    long batch_rows = 65536, max_resident = 1 << 20;
+    double ambig_q = 0.5, ambig_r = 0.5;
+    const char* out_prefix = NULL;
+    const char* ref_file[1024]; int n_ref_files = 0;
+    static struct option lo[] = {
+        {"help", 0, 0, 'h'}, {"version", 0, 0, 'v'}, {"acgt", 0, 0, 1000}, {"keep_resolved", 0, 0, 'k'}, {"exclude_self", 0, 0, 'x'},
+        {"nbest", 1, 0, 'n'}, {"trim", 1, 0, 1001}, {"query_ambiguity", 1, 0, 'a'}, {"ref_ambiguity", 1, 0, 'A'}, {"pool", 1, 0, 'p'},
+        {"reference", 1, 0, 'r'}, {"nthreads", 1, 0, 't'}, {"output", 1, 0, 'o'}, {"device", 1, 0, 1002}, {"batch", 1, 0, 1003},
+        {"max_resident", 1, 0, 1004}, {0, 0, 0, 0}};
+    int ch;
+    while ((ch = getopt_long(argc, argv, "hvkxn:a:A:p:r:t:o:", lo, NULL)) != -1) {
+        switch (ch) {
+        case 'h': usage(argv[0], 1); return EXIT_SUCCESS;                       /* nearest.c:113-157: help and version exit 0 */
+        case 'v': printf("%s\n", PROGRAM_VERSION); return EXIT_SUCCESS;
+        case 1000: acgt = 1; break;
+        case 'k': hires = 1; break;
+        case 'x': xclude = 1; break;
+        case 'n': nbest = atoi(optarg); break;
+        case 1001: trim = atoi(optarg); break;
+        case 'a': ambig_q = atof(optarg); break;
+        case 'A': ambig_r = atof(optarg); break;
+        case 'p': pool = atoi(optarg); break;
+        case 'r': if (n_ref_files == 1024) die("at most 1024 reference files"); ref_file[n_ref_files++] = optarg; break;
+        case 't': break;
+        case 'o': out_prefix = optarg; break;
+        case 1002: device = atoi(optarg); break;
+        case 1003: batch_rows = atol(optarg); break;
+        case 1004: max_resident = atol(optarg); break;
+        default: usage(argv[0], 0); return EXIT_FAILURE;
+        }
+    }
+    if (n_ref_files < 1 || argc - optind != 1) { usage(argv[0], 0); return EXIT_FAILURE; }
+    if (hires) die("-k/--keep_resolved is not supported by this host program");
+    const char* query_file = argv[optind];
+    if (ambig_q < 0.001) ambig_q = 0.001;                                       /* nearest.c:175-179 */
+    if (ambig_q > 1.) ambig_q = 1.;
+    if (ambig_r < 0.001) ambig_r = 0.001;
+    if (ambig_r > 1.) ambig_r = 1.;
+    if (nbest < 1) nbest = 1;
+    if (pool < 1) pool = 64 * (int)sysconf(_SC_NPROCESSORS_ONLN);               /* nearest.c:80: 64 per thread */
+    if (batch_rows < 1) batch_rows = 1;
+    if (!out_prefix) out_prefix = acgt ? "nn_uvaia_acgt" : "nn_uvaia";          /* nearest.c:198-200 */
+    init_tables();
+    const double t0 = now_s();
+    fprintf(stderr, "program: uvaia_b200 package: %s\n", PROGRAM_VERSION);
+
+    /* 1. queries */
+    int n_read = 0;
+    queries_t q = read_queries(query_file, ambig_q, trim, acgt, &n_read);
+    fprintf(stderr, "Finished reading %d query references in %lf secs;\n", n_read, now_s() - t0);
+    fprintf(stderr, "Query database composed of %d valid references, after excluding low quality.\n", q.n);
+    if (q.n < 1) die("No valid reference sequences found. Please check file %s.", query_file);
+    const int L = q.nchar, K = nbest < 2 ? 2 : nbest;
+    uvg_params prm;
+    memset(&prm, 0, sizeof prm);
+    prm.abi_version = UVG_ABI_VERSION; prm.nchar = L; prm.trim = trim; prm.nbest = nbest; prm.acgt_mode = acgt; prm.pool = pool; prm.device = device;
+    uvg_ctx* gpu = NULL;
+    uvg_query_info qi;
+    if (uvg_create(&prm, &gpu)) die("%s", uvg_last_error(NULL));
+    if (uvg_set_queries(gpu, q.text, q.n, &qi)) die("%s", uvg_last_error(gpu));
+    fprintf(stderr, "Query sequence alignment: %d segregating, %d non-segregating sites with indels, and %d constant sites (all are used in comparisons)\n",
+            qi.n_idx, qi.n_idx_m, qi.n_idx_c);                                  /* fastaseq.c:774 */
+    fprintf(stderr, acgt ? "Considering ACGT differences only (excluding all other characters). \n"
+                         : "Considering text match and partially ambiguous (excluding only gaps and Ns).\n");
+    nameset_t qset = {0};
+    if (xclude) {
+        fprintf(stderr, "Reference sequences with same name as query sequences will be excluded from the comparison.\n");
+        qset = nameset_build(q.name, q.n);
+    }
+
+    /* 2. reference stream: batches of rows in pinned memory -> uvg_push_refs (copy + encoder) -> uvg_search_async (the rounds
+     * of this batch run under the reading and the copy of the next one) */
+    const int min_non_n = (int)(L * (1.0 - ambig_r));                           /* nearest.c:237 */
+    if (batch_rows > ((long)1 << 30) / L) batch_rows = (((long)1 << 30) / L) > 0 ? ((long)1 << 30) / L : 1;
+    unsigned char* batch = uvg_host_alloc_pinned((size_t)batch_rows * L);
+    if (!batch) die("cannot allocate %zu bytes of pinned memory", (size_t)batch_rows * L);
+    char** bname = xmalloc(batch_rows * sizeof *bname);
+    int64_t* brec = xmalloc(batch_rows * sizeof *brec);                         /* record number of every batch row */
+    uint8_t* accepted = xmalloc(batch_rows);
+    char** rname = NULL; int64_t n_acc_total = 0, rname_cap = 0;                /* names of the accepted references, by ordinal */
+    uint8_t* rec_ok = NULL; int64_t n_rec = 0, rec_cap = 0;                     /* per streamed record: 1 = accepted (second pass for .aln) */
+    long count = 0, n_invalid = 0, same_name = 0, nb = 0;
+
+#define FLUSH_BATCH() do { if (nb > 0) { \
+        int64_t na_ = 0; \
+        if (uvg_push_refs(gpu, batch, nb, min_non_n, NULL, accepted, &na_)) die("%s", uvg_last_error(gpu)); \
+        if (n_acc_total + na_ > rname_cap) { rname_cap = 2 * (n_acc_total + na_) + 1024; rname = xrealloc(rname, rname_cap * sizeof *rname); } \
+        for (long i_ = 0; i_ < nb; ++i_) { \
+            rec_ok[brec[i_]] = accepted[i_]; \
+            if (accepted[i_]) rname[n_acc_total++] = bname[i_]; else { free(bname[i_]); ++n_invalid; } } \
+        if (uvg_search_async(gpu)) die("%s", uvg_last_error(gpu)); \
+        if (uvg_db_count(gpu) >= max_resident) { if (uvg_wait(gpu) || uvg_drop_refs(gpu)) die("%s", uvg_last_error(gpu)); } \
+        nb = 0; } } while (0)
+
+    for (int j = 0; j < n_ref_files; ++j) {
+        const double t1 = now_s();
+        fasta_t f;
+        fasta_open(&f, ref_file[j]);
+        while (fasta_next(&f)) {
+            ++count;
+            if (n_rec == rec_cap) { rec_cap = rec_cap ? 2 * rec_cap : 1 << 16; rec_ok = xrealloc(rec_ok, rec_cap); }
+            rec_ok[n_rec++] = 0;
+            if (xclude && nameset_has(&qset, f.name)) { ++same_name; continue; }                  /* nearest.c:255-261 */
+            if ((int64_t)f.len != L) {
+                /* nearest.c:263-278: a poor-quality reference of the wrong length is skipped, a good one is fatal */
+                long nn = 0;
+                for (size_t i = 0; i < f.len; ++i) nn += g_validtxt[f.seq[i]];
+                if (nn < min_non_n) { ++n_invalid; continue; }
+                die("all sequences must be aligned: reference %s has %zu sites, queries have %d", f.name, f.len, L);
+            }
+            memcpy(batch + (size_t)nb * L, f.seq, L);
+            bname[nb] = f.name; f.name = NULL;
+            brec[nb] = n_rec - 1;
+            ++nb;
+            if (nb == batch_rows) FLUSH_BATCH();
+        }
+        FLUSH_BATCH();
+        fasta_close(&f);
+        fprintf(stderr, "Finished reading file %s in %.3lf secs;\n", ref_file[j], now_s() - t1);
+        fprintf(stderr, "Total of %ld sequences read; %ld too ambiguous (excluded). %.3lf secs elapsed. \n", count, n_invalid, now_s() - t0);
+        if (xclude) fprintf(stderr, " %ld reference sequences already present in query alignment (based on name only).\n", same_name);
+    }
+    if (uvg_wait(gpu)) die("%s", uvg_last_error(gpu));
+
+    /* 3. <prefix>.aln.xz: every reference that ever entered a heap, in file order (nearest.c:303-314).  The text is not
+     * kept on the host: the reference files are streamed a second time and the flagged records are written. */
+    uvg_stats st;
+    if (uvg_get_stats(gpu, &st)) die("%s", uvg_last_error(gpu));
+    uint8_t* best = xmalloc((size_t)n_acc_total + 1);
+    if (n_acc_total && uvg_get_ever_best(gpu, 0, n_acc_total, best)) die("%s", uvg_last_error(gpu));
+    size_t plen = strlen(out_prefix);
+    char* outname = xmalloc(plen + 16);
+    sprintf(outname, "%s.aln.xz", out_prefix);
+    long n_output = 0;
+    {
+        writer_t w = writer_open(outname);
+        int64_t rec = 0, ord = 0;
+        for (int j = 0; j < n_ref_files; ++j) {
+            fasta_t f;
+            fasta_open(&f, ref_file[j]);
+            while (fasta_next(&f)) {
+                if (rec >= n_rec) die("reference file %s changed while running", ref_file[j]);
+                if (rec_ok[rec++] != 1) continue;
+                if (best[ord++]) {
+                    writer_put(&w, ">", 1); writer_put(&w, f.name, strlen(f.name)); writer_put(&w, "\n", 1);
+                    writer_put(&w, f.seq, f.len); writer_put(&w, "\n", 1);
+                    ++n_output;
+                }
+            }
+            fasta_close(&f);
+        }
+        writer_close(&w);
+    }
+    fprintf(stderr, "Total of %ld sequences read; %ld saved sequences include closest neighbours and intermediate, %ld too ambiguous (excluded). "
+                    "Highest number of ACGT mismatches = %lld in current neighbourhood.\n", count, n_output, n_invalid, (long long)st.max_mismatch);
+    fprintf(stderr, "Saved %ld sequences to file %s , %.3lf secs elapsed.\n", n_output, outname, now_s() - t0);
+    if (st.n_h1_flags)
+        fprintf(stderr, "Note: %lld admissions may depend on --pool in the reference program (its consensus stage truncates per batch); "
+                        "the table below is the pool-independent result.\n", (long long)st.n_h1_flags);
+
+    /* 4. <prefix>.csv.xz (save_distance_table, nearest.c:513-547) */
+    sprintf(outname, "%s.csv.xz", out_prefix);
+    {
+        writer_t w = writer_open(outname);
+        const char* hdr = acgt ? "query,reference,rank,ACGT_matches,valid_ACGT_comparisons,ACGT_matches_unique,valid_ref_sites,dist_consensus,dist_unique\n"
+                               : "query,reference,rank,ACGT_matches,text_matches,partial_matches,valid_pair_comparisons,ACGT_matches_unique,valid_ref_sites\n";
+        writer_put(&w, hdr, strlen(hdr));
+        uvg_item* rows = xmalloc((size_t)K * sizeof *rows);
+        size_t lcap = 1 << 16; char* line = xmalloc(lcap);
+        for (int iq = 0; iq < q.n; ++iq) {
+            int32_t n = 0;
+            if (uvg_get_heap(gpu, iq, rows, &n)) die("%s", uvg_last_error(gpu));
+            for (int i = 0; i < n; ++i) {
+                const char* rn = rname[rows[i].ref];
+                const size_t need = strlen(q.name[iq]) + strlen(rn) + 128;
+                if (need > lcap) { lcap = 2 * need; line = xrealloc(line, lcap); }
+                const int k = snprintf(line, lcap, "%s,%s,%d,%d,%d,%d,%d,%d,%d\n", q.name[iq], rn, i + 1, rows[i].score[0], rows[i].score[1],
+                                       rows[i].score[2], rows[i].score[3], rows[i].score[4], rows[i].score[5]);
+                writer_put(&w, line, (size_t)k);
+            }
+        }
+        writer_close(&w);
+        free(rows); free(line);
+    }
+    fprintf(stderr, "Saved distance table to file %s , %.3lf secs elapsed.\n", outname, now_s() - t0);
+
+    uvg_destroy(gpu);
+    uvg_host_free_pinned(batch);
+    for (int64_t i = 0; i < n_acc_total; ++i) free(rname[i]);
+    for (int i = 0; i < q.n; ++i) free(q.name[i]);
+    free(rname); free(rec_ok); free(bname); free(brec); free(accepted); free(best); free(outname); free(q.name); free(q.text); free(qset.slot);
+    return EXIT_SUCCESS;
+}
