@@ -48,24 +48,33 @@ static_assert(sizeof(QChunk) % 16 == 0, "bulk copy size must be a multiple of 16
 // the match word of a pair is mc & qeq and the valid word r.base & q.base: two ANDs instead of three LOP3 with five
 // inputs, and both popcounts go through a 2-word carry-save step (4 LOP3 + 1 POPC per pair-word in all, balanced for
 // the measured 4:1 LOP3:POPC issue ratio).  Query sites holding a plain base that differs from the pivot (~the SNPs of
-// the query, a few dozen per genome) are "fix" entries: (slot, word, base, bit mask).  They travel with the query chunk
-// and are resolved inside the main loop against ONE-HOT planes of the staged references (one conflict-free 4-byte
-// shared-memory load and one AND per entry and reference); what does not fit a chunk's fix block, and every ambiguity
-// code, is resolved by the epilogue (pair_epilogue.cuh).
+// the query, a few dozen per genome) are "fix" entries: (slot, site, base).  They travel with the query chunk and are
+// resolved against COLUMN MASKS of the derived database: for a site and a base, one 32-bit word whose bit l says
+// "reference l of the group holds that base there" -- a warp fetches the words of all its entries of a chunk with ONE
+// load (lane = entry x group) while it counts the chunk, and almost always finds them all zero.  What does not fit a
+// chunk's fix block, and every ambiguity code, is resolved by the epilogue (pair_epilogue.cuh).
 // Derived database: per (group of 32 references, unit of 4 column words) one contiguous 3 KB record
-//     uint4 base[32]  |  uint4 mc[32]  |  uint32 onehot[4 words][4 bases A,C,G,T][32]
-// so one chunk (WC words) of a group is one TMA bulk copy of W4 * 3 KB.
-constexpr int STAGES2 = 6;
+//     uint4 base[32]  |  uint4 mc[32]  |  uint32 colmask[4 words][4 bases A,C,G,T][32 sites]
+// of which the first 1 KB (base, mc: lane = reference) is staged by TMA bulk copies.
+#ifndef PIVOT_STAGES
+#define PIVOT_STAGES 8
+#endif
+constexpr int STAGES2 = PIVOT_STAGES;
 constexpr int UNIT2_BYTES = 2 * GROUP * 16 + 4 * 4 * GROUP * 4;      // 3072
 constexpr int UNIT2_ONEHOT = 2 * GROUP * 16;                         // byte offset of the one-hot planes inside a unit record
-constexpr int FIXCAP = 124;                                          // fix entries a chunk of a query tile can carry
-constexpr int PIVOT_QW = 4;                                          // query slots per warp of k_pairpivot
+constexpr int FIXCAP = 248;                                          // fix entries a chunk of a query tile can carry
+#ifndef PIVOT_QW_
+#define PIVOT_QW_ 4
+#endif
+constexpr int PIVOT_QW = PIVOT_QW_;                                  // query slots per warp of k_pairpivot
 constexpr int PIVOT_WARPS = QTILE / PIVOT_QW;
 struct __align__(16) QChunk2 {
-    uint4    pl[W4][QTILE][2];       // [unit][slot][plane]: 0 base, 1 qeq
+    uint4    pl[W4][QTILE][2];       // [unit][slot][plane], COMPLEMENTS: 0 = no plain base here (or trimmed / padding), 1 = not the pivot base
     uint8_t  fix_begin[32];          // [warp] first entry of the warp's slots; [PIVOT_WARPS] = total
-    uint2    fix[FIXCAP];            // x = bit mask inside the word, y = byte offset of the one-hot word (lane 0) inside the
-                                     //     staged chunk of a group | slot-within-warp << 16
+    uint32_t active[W4][2];          // per unit: bit s set <=> slot s has work in this unit (its plane 1 is not all zero)
+    uint32_t pad_[4 - (W4 * 2) % 4];
+    uint32_t fix[FIXCAP];            // byte offset of the entry's column-mask word inside a group's chunk of the derived
+                                     //     database | slot-within-warp << 16
 };
 static_assert(sizeof(QChunk2) % 16 == 0 && PIVOT_WARPS < 32 && FIXCAP < 256, "QChunk2 layout");
 __host__ __device__ inline size_t db2_unit_bytes(int64_t group, int unit, int Wp)
@@ -102,6 +111,8 @@ struct PairParams {
     const uint32_t*  qamb_ent;
     // pivot form (null when the general kernel runs)
     const uint8_t*   db2;         // derived database: 3 KB records (base, mc, one-hot planes)
+    const int32_t*   rb_cnt;      // per local reference: popcount of its base plane (all words)
+    const int32_t*   mc_cnt;      //                      popcount of its mc plane
     const QChunk2*   qdata2;      // [n_qtiles][n_chunks]
     const uint32_t*  qfix_off;    // [n_slots + 1] entries the EPILOGUE resolves: ambiguity codes + fix entries that overflowed a chunk
     const uint32_t*  qfix_ent;
@@ -119,7 +130,7 @@ struct PairParams {
     int64_t  col0;                // column of local_begin in the destination tiles
     int32_t  world, rows_cap;
     int32_t  early_abort;
-    unsigned long long* work;     // executed (lane-pair, chunk) iterations per warp: x 8 words x 32 lanes = pair-words (early abort makes this < dense)
+    unsigned long long* work;     // executed (pair, 4-word unit) iterations per lane: x 4 words x 32 lanes = pair-words (early abort / skipped units: < dense)
 };
 
 __host__ __device__ inline size_t db_unit_index(int64_t group, int unit, int plane, int lane, int Wp)

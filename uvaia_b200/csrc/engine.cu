@@ -87,6 +87,7 @@ struct uvg_ctx {
     uint32_t *d_qfix_off = nullptr, *d_qfix_ent = nullptr;
     uint4* d_pivot = nullptr;                         // [Wp/4][2]: b0, b1 planes of the pivot sequence
     uint8_t* d_db2 = nullptr; int64_t db2_cap = 0;    // derived database (base, mc, one-hot planes: 3 KB records) of the resident references
+    int32_t* d_ref_cnt = nullptr;                     // [2][db2_cap]: per reference popcount of its base plane / of its mc plane
     Threshold* d_thr_local = nullptr;                 // [rows_cap] bounds of the owned rows (written by K3)
     Threshold* d_thr_all[NBUF]{};                     // [world * rows_cap] what K2 reads (double buffered)
     HeapItem* d_heaps = nullptr;                      // [rows_cap][K+1] owned rows
@@ -254,7 +255,7 @@ extern "C" void uvg_destroy(uvg_ctx* c)
     if (c->st_copy) cudaStreamSynchronize(c->st_copy);
     free_queries(c, true);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
-    cudaFree(c->d_db); cudaFree(c->d_db2); cudaFree(c->d_non_n); cudaFree(c->d_ramb_off); cudaFree(c->d_ramb_ent); cudaFree(c->d_ever);
+    cudaFree(c->d_db); cudaFree(c->d_db2); cudaFree(c->d_ref_cnt); cudaFree(c->d_non_n); cudaFree(c->d_ramb_off); cudaFree(c->d_ramb_ent); cudaFree(c->d_ever);
     cudaFree(c->d_counters); cudaFree(c->d_nacc); cudaFree(c->d_ipc);
     cudaFree(c->d_stage_text[0]); cudaFree(c->d_stage_text[1]); cudaFree(c->d_stage_nn); cudaFree(c->d_stage_namb); cudaFree(c->d_stage_acc); cudaFree(c->d_stage_dst);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
@@ -296,8 +297,17 @@ static int ensure_db2(uvg_ctx* c)
     UVG_CUDA(c, cudaMalloc(&n, (size_t)(c->db_cap / GROUP) * per_group));
     if (c->d_db2 && c->db2_cap) UVG_CUDA(c, cudaMemcpy(n, c->d_db2, (size_t)(c->db2_cap / GROUP) * per_group, cudaMemcpyDeviceToDevice));
     UVG_CUDA(c, cudaMemset(n + (size_t)(c->db2_cap / GROUP) * per_group, 0, (size_t)((c->db_cap - c->db2_cap) / GROUP) * per_group));
-    cudaFree(c->d_db2);
-    c->d_db2 = n; c->db2_cap = c->db_cap;
+    // the per-reference plane totals are re-derived with the planes: new array, the resident range is filled by the caller
+    // (uvg_set_queries) or was filled by earlier pushes and is copied
+    int32_t* cn = nullptr;
+    UVG_CUDA(c, cudaMalloc(&cn, (size_t)c->db_cap * 2 * sizeof(int32_t)));
+    UVG_CUDA(c, cudaMemset(cn, 0, (size_t)c->db_cap * 2 * sizeof(int32_t)));
+    if (c->d_ref_cnt && c->db2_cap) {
+        UVG_CUDA(c, cudaMemcpy(cn, c->d_ref_cnt, (size_t)c->db2_cap * 4, cudaMemcpyDeviceToDevice));
+        UVG_CUDA(c, cudaMemcpy(cn + c->db_cap, c->d_ref_cnt + c->db2_cap, (size_t)c->db2_cap * 4, cudaMemcpyDeviceToDevice));
+    }
+    cudaFree(c->d_db2); cudaFree(c->d_ref_cnt);
+    c->d_db2 = n; c->d_ref_cnt = cn; c->db2_cap = c->db_cap;
     return UVG_OK;
 }
 
@@ -508,22 +518,36 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
                     for (int j = 0; j < PIVOT_QW; ++j) {
                         const int q = qt * QTILE + wp * PIVOT_QW + j;
                         if (q >= c->n_slots) continue;
-                        int last = -1; uint32_t last_key = 0;
                         while (cur[q] < snp[q].size() && (snp[q][cur[q]] & AMB_SITE_MASK) < site_end) {
                             const uint32_t ent = snp[q][cur[q]++], site = ent & AMB_SITE_MASK, code = ent >> 28;
                             const uint32_t w = site >> 5, a = code == 1 ? 0 : code == 2 ? 1 : code == 4 ? 2 : 3;
-                            const uint32_t key = w * 4 + a;
-                            if (last >= 0 && key == last_key) { blk.fix[last].x |= 1u << (site & 31); continue; }
                             if (n >= FIXCAP) { epi[q].push_back(ent); ++n_overflow; continue; }
-                            const uint32_t off = ((w % WC) / 4) * UNIT2_BYTES + UNIT2_ONEHOT + ((w & 3) * 4 + a) * (GROUP * 4);
-                            blk.fix[n].x = 1u << (site & 31);
-                            blk.fix[n].y = off | ((uint32_t)j << 16);
-                            last = n++; last_key = key;
+                            const uint32_t off = ((w % WC) / 4) * UNIT2_BYTES + UNIT2_ONEHOT + (((w & 3) * 4 + a) * 32 + (site & 31)) * 4;
+                            blk.fix[n++] = off | ((uint32_t)j << 16);
                         }
                     }
                 }
                 blk.fix_begin[PIVOT_WARPS] = (uint8_t)n;
             }
+        // the kernel works on the COMPLEMENTS (pairpivot.cu): plane 0 = sites where the slot holds no plain base (or that
+        // are trimmed away / padding), plane 1 = sites where it does not hold the pivot base; units where plane 1 is zero
+        // are skipped.  Padding slots stay all-zero (always skipped, never stored).
+        parallel_ranges(c->n_qtiles, host_threads(c->n_qtiles), [&](int, int ta, int tb) {
+            for (int qt = ta; qt < tb; ++qt)
+                for (int ch = 0; ch < c->n_chunks; ++ch) {
+                    QChunk2& blk = qd2[(size_t)qt * c->n_chunks + ch];
+                    for (int u = 0; u < W4; ++u)
+                        for (int qi = 0; qi < QTILE && qt * QTILE + qi < c->n_slots; ++qi)
+                        {
+                            for (int pl = 0; pl < 2; ++pl) {
+                                uint4& v = blk.pl[u][qi][pl];
+                                v.x = ~v.x; v.y = ~v.y; v.z = ~v.z; v.w = ~v.w;
+                            }
+                            const uint4& e = blk.pl[u][qi][1];
+                            if (e.x | e.y | e.z | e.w) blk.active[u][qi >> 5] |= 1u << (qi & 31);
+                        }
+                }
+        });
         fix_off.assign(c->n_slots + 1, 0);
         for (int q = 0; q < c->n_slots; ++q) {
             fix_off[q] = (uint32_t)fix_ent.size();
@@ -587,7 +611,8 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
         // references that are already resident get their derived planes now (one pass over the packed database)
         int rc2 = ensure_db2(c);
         if (rc2) return rc2;
-        UVG_CUDA(c, launch_derive_pivot(c->d_db, c->d_db2, c->d_pivot, 0, c->db_n, c->Wp, c->st));
+        if (c->db2_cap) UVG_CUDA(c, cudaMemsetAsync(c->d_ref_cnt, 0, (size_t)c->db2_cap * 2 * sizeof(int32_t), c->st));
+        UVG_CUDA(c, launch_derive_pivot(c->d_db, c->d_db2, c->d_pivot, c->d_ref_cnt, c->d_ref_cnt + c->db2_cap, 0, c->db_n, c->Wp, c->st));
         if (c->db_n) c->stats.other_kernel_launches += 1;
     }
     c->qinfo_pivot_fix = pivot_ok ? n_fix_total : -1;
@@ -713,7 +738,10 @@ static int push_device_rows(uvg_ctx* c, const uint8_t* d_text, int64_t n, int32_
                               c->d_ramb_ent, c->d_non_n, sp));
     c->stats.other_kernel_launches += 3;
     if (c->pivot_on && n_acc > 0) {
-        UVG_CUDA(c, launch_derive_pivot(c->d_db, c->d_db2, c->d_pivot, c->db_n, c->db_n + n_acc, c->Wp, sp));
+        // rows above db_n still hold the totals of dropped / cleared references: zero the range first
+        UVG_CUDA(c, cudaMemsetAsync(c->d_ref_cnt + c->db_n, 0, (size_t)n_acc * 4, sp));
+        UVG_CUDA(c, cudaMemsetAsync(c->d_ref_cnt + c->db2_cap + c->db_n, 0, (size_t)n_acc * 4, sp));
+        UVG_CUDA(c, launch_derive_pivot(c->d_db, c->d_db2, c->d_pivot, c->d_ref_cnt, c->d_ref_cnt + c->db2_cap, c->db_n, c->db_n + n_acc, c->Wp, sp));
         c->stats.other_kernel_launches += 1;
     }
     c->db_n += n_acc;
@@ -858,6 +886,7 @@ static void fill_pair_params(uvg_ctx* c, PairParams& pp, int64_t lb, int64_t le,
 {
     pp.db = c->d_db; pp.qdata = c->d_qdata; pp.thr = c->d_thr_all[buf];
     pp.qnib = c->d_qnib; pp.qamb_off = c->d_qamb_off; pp.qamb_ent = c->d_qamb_ent;
+    pp.rb_cnt = c->d_ref_cnt; pp.mc_cnt = c->d_ref_cnt ? c->d_ref_cnt + c->db2_cap : nullptr;
     pp.db2 = c->d_db2; pp.qdata2 = c->d_qdata2; pp.qfix_off = c->d_qfix_off; pp.qfix_ent = c->d_qfix_ent;
     pp.ramb_off = c->d_ramb_off; pp.ramb_ent = c->d_ramb_ent; pp.non_n = c->d_non_n;
     pp.qnib_stride = c->qnib_stride;
@@ -1106,7 +1135,7 @@ extern "C" int uvg_get_stats(uvg_ctx* c, uvg_stats* out)
     UVG_CUDA(c, cudaMemcpyAsync(c->h_pinned + 16, c->d_counters, 24, cudaMemcpyDeviceToHost, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
     c->stats.n_admitted = (int64_t)c->h_pinned[16]; c->stats.n_h1_flags = (int64_t)c->h_pinned[17];
-    c->stats.warp_chunks_executed = c->work_last / 16;          // the counter is in (pair, chunk) units; 16 pairs per lane and warp
+    c->stats.warp_chunks_executed = c->work_last / 32;          // the counter is in (pair, 4-word unit) per lane; 16 pairs x 2 units = one (warp, chunk) of the general kernel
     c->stats.pivot_fix_entries = c->pivot_on ? c->qinfo_pivot_fix : -1;
     c->stats.set_queries_host_ms = c->set_queries_host_ms; c->stats.set_queries_device_ms = c->set_queries_device_ms;
     if (c->n_query) {

@@ -27,7 +27,9 @@ cudaError_t paircount_setup();       // opt in to the dynamic shared memory size
 cudaError_t launch_pairpivot(const PairParams& p, cudaStream_t st);
 cudaError_t pairpivot_setup();
 // derived planes (base, mc) of the resident references [begin, end) from the packed database and the pivot planes
-cudaError_t launch_derive_pivot(const uint4* db, uint8_t* db2, const uint4* pivot, int64_t begin, int64_t end, int Wp, cudaStream_t st);
+// rb_cnt / mc_cnt (zeroed by the caller for [begin, end)): popcount of the base plane / of the mc plane per reference
+cudaError_t launch_derive_pivot(const uint4* db, uint8_t* db2, const uint4* pivot, int32_t* rb_cnt, int32_t* mc_cnt, int64_t begin, int64_t end,
+                                int Wp, cudaStream_t st);
 
 // ---- replay.cu (K3) ----
 struct ReplayParams {

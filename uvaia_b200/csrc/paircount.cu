@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 2) k_paircount(const PairParams 
         if (all_dead) break;
         if (threadIdx.x == 0 && c + STAGES < p.n_chunks) issue(c + STAGES, s);
     }
-    if (lane == 0 && p.work) atomicAdd(p.work, (unsigned long long)executed * (QPW * RPL));
+    if (lane == 0 && p.work) atomicAdd(p.work, (unsigned long long)executed * (QPW * RPL * W4));
     if (c < p.n_chunks) {
         // whole block aborted: drain the bulk copies still in flight before the shared memory is released
         for (int cc = c + 1; cc < p.n_chunks && cc < c + STAGES; ++cc) mbar_wait(full + cc % STAGES, (uint32_t)((cc / STAGES) & 1));

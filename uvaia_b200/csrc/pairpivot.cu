@@ -9,16 +9,17 @@
 //     qeq (query plane)                                                    = q.base & (q == P)
 //     M' = mc & qeq        V = r.base & q.base                             (2 LOP3 per pair-word instead of 3)
 // Query sites with a plain base != P (the query's own SNPs, a few dozen per genome) are outside M'; they are "fix"
-// entries (slot, word, base, bit mask) that travel with the query chunk: the loop ANDs the mask with the one-hot plane
-// word of that base of each staged reference (one conflict-free LDS.32) and, on the rare lanes that hit, adds the
-// popcount to the match counter.  Entries that overflow a chunk's fix block and all ambiguity codes go to the epilogue
+// entries (slot, site, base) that travel with the query chunk and are resolved against column masks of the derived
+// database (per site and base one word: bit l = reference l of the group holds that base): a warp fetches the masks of
+// all its entries of a chunk with one load (lane = entry x group) while it counts the chunk, almost always finds them
+// all zero, and otherwise bumps a per-pair counter in shared memory.  Entries that overflow a chunk's fix block and all ambiguity codes go to the epilogue
 // (pair_epilogue.cuh).
 // Both popcount streams go through one 3:2 compressor per two words (ones register + one carry word of weight 2):
 //     4 LOP3 (ALU) + 1 POPC (XU) + 1 IMAD (FMA) per pair and 32-site word
 // which balances the ALU and XU pipes at the measured 4:1 LOP3:POPC rate of sm_100 (profiles/int_pipes_b200_r01.json);
 // the general kernel needs 4.5 LOP3 + 1.25 POPC.
 // Shape: block = 64 query slots x 64 references, 16 warps x 4 slots, lane = 2 references, 64 registers, 2 blocks per
-// SM (32 warps per SM).  Staging: one TMA bulk copy per operand into a 6-deep ring with full/empty mbarriers (no
+// SM (32 warps per SM).  Staging: one TMA bulk copy per operand into an 8-deep ring with full/empty mbarriers (no
 // __syncthreads in the loop: warps drift up to the ring depth apart); one elected thread refills a stage two chunks
 // after it was consumed.
 #include "common.cuh"
@@ -31,24 +32,32 @@ namespace uvg {
 struct __align__(16) RefUnit2 {
     uint4    base[GROUP];
     uint4    mc[GROUP];
-    uint32_t onehot[4][4][GROUP];                       // [word][base A,C,G,T][lane]
+    uint32_t colmask[4][4][32];                         // [word][base A,C,G,T][site in word]: bit l = reference l of the group holds that base
 };
 static_assert(sizeof(RefUnit2) == UNIT2_BYTES, "derived database record");
-struct __align__(16) Stage2 {
-    QChunk2  q;
-    RefUnit2 ref[RPL][W4];
+// staged part of a record: the base and mc planes (the one-hot planes stay in global memory / L2: only fix entries read them)
+struct __align__(16) RefPlanes2 {
+    uint4 base[GROUP];
+    uint4 mc[GROUP];
 };
-constexpr uint32_t STAGE2_REF_BYTES = W4 * UNIT2_BYTES;
-constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(uint64_t);
+static_assert(sizeof(RefPlanes2) == UNIT2_ONEHOT, "staged prefix of the derived database record");
+struct __align__(16) Stage2 {
+    QChunk2    q;
+    RefPlanes2 ref[RPL][W4];
+};
+constexpr uint32_t STAGE2_REF_BYTES = W4 * UNIT2_BYTES;             // bytes of a group's chunk in the derived database
+constexpr size_t PIVOT_FIXHIT_BYTES = QTILE * GROUP * RPL * sizeof(uint16_t);       // per (slot, reference of the block): matches found by fix entries
+constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + PIVOT_FIXHIT_BYTES + 2 * STAGES2 * sizeof(uint64_t);
 constexpr int REFILL_LAG = 2;
 constexpr int QW2 = PIVOT_QW;                           // query slots per warp (register tile QW2 x RPL pairs per lane)
 constexpr int PIVOT_THREADS = PIVOT_WARPS * 32;
 
-__global__ void __launch_bounds__(PIVOT_THREADS, 1024 / PIVOT_THREADS) k_pairpivot(const PairParams p, const uint32_t k2, const uint32_t k128k)
+__global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams p, const uint32_t k2, const uint32_t k128k)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     Stage2* stage = reinterpret_cast<Stage2*>(smem);
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES2 * sizeof(Stage2));
+    uint16_t* fixhit = reinterpret_cast<uint16_t*>(smem + STAGES2 * sizeof(Stage2));   // [slot][RPL * GROUP]: written and read by one thread each
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES2 * sizeof(Stage2) + PIVOT_FIXHIT_BYTES);
     uint64_t* empty = full + STAGES2;
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -63,20 +72,28 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 1024 / PIVOT_THREADS) k_pairpiv
         for (int s = 0; s < STAGES2; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, PIVOT_THREADS / 32); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    for (int i = threadIdx.x; i < (int)(PIVOT_FIXHIT_BYTES / sizeof(uint4)); i += PIVOT_THREADS) reinterpret_cast<uint4*>(fixhit)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
     auto issue = [&](int c, int s) {
-        mbar_expect_tx(full + s, (uint32_t)(sizeof(QChunk2) + RPL * STAGE2_REF_BYTES));
+        mbar_expect_tx(full + s, (uint32_t)(sizeof(QChunk2) + RPL * W4 * sizeof(RefPlanes2)));
         bulk_g2s(&stage[s].q, qsrc + c, (uint32_t)sizeof(QChunk2), full + s);
 #pragma unroll
         for (int g = 0; g < RPL; ++g)
-            bulk_g2s(&stage[s].ref[g][0], rsrc + g * group_stride + (size_t)c * STAGE2_REF_BYTES, STAGE2_REF_BYTES, full + s);
+#pragma unroll
+            for (int u = 0; u < W4; ++u)
+                bulk_g2s(&stage[s].ref[g][u], rsrc + g * group_stride + (size_t)c * STAGE2_REF_BYTES + (size_t)u * UNIT2_BYTES,
+                         (uint32_t)sizeof(RefPlanes2), full + s);
     };
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES2 && s < p.n_chunks; ++s) issue(s, s);
     }
 
-    // per pair: carry-save "ones" registers of the valid and the match stream and one packed counter
-    // acc = (#weight-2 carries of M) * 2 | (#weight-2 carries of V) * 2 << 16
+    // per pair: carry-save "ones" registers of the two COMPLEMENT streams and one packed counter.  The query planes are
+    // stored inverted (nq = no plain base here, ne = not the pivot's base; nq is a subset of ne):
+    //     valid   = popc(r.base) - popc(r.base & nq)        match' = popc(r.mc) - popc(r.mc & ne)
+    // The first terms are per-reference totals (k_derive_pivot); the second terms are zero wherever the query is complete
+    // and equal to the pivot, so a (slot, unit) whose `ne` words are all zero is SKIPPED (uniform branch: the planes
+    // are warp-wide broadcasts).  acc = (#weight-2 carries of r.mc & ne) * 2 | (#weight-2 carries of r.base & nq) * 2 << 16
     uint32_t oV[RPL][QW2], oM[RPL][QW2], acc[RPL][QW2];
 #pragma unroll
     for (int g = 0; g < RPL; ++g)
@@ -84,18 +101,45 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 1024 / PIVOT_THREADS) k_pairpiv
         for (int j = 0; j < QW2; ++j) { oV[g][j] = 0; oM[g][j] = 0; acc[g][j] = 0; }
 
     const int q0 = warp * QW2;
+    // resolve fetched column masks: a set bit = that reference holds the query's (non-pivot) base at the site, a match the
+    // planes did not see.  Almost always no lane holds a non-zero mask.
+    auto resolve = [&](uint32_t ent_l, uint32_t col_l) {
+        uint32_t any = __ballot_sync(0xffffffffu, col_l != 0u);
+        while (any) {
+            const int src = __ffs(any) - 1;
+            any &= any - 1u;
+            const uint32_t col = __shfl_sync(0xffffffffu, col_l, src), ent = __shfl_sync(0xffffffffu, ent_l, src);
+            if ((col >> lane) & 1u) fixhit[(q0 + (ent >> 16)) * (RPL * GROUP) + (src % RPL) * GROUP + lane] += 1;   // this thread owns the counter
+        }
+    };
+    uint32_t executed = 0;                                                   // (slot, unit) iterations that were not skipped
     for (int c = 0; c < p.n_chunks; ++c) {
         const int s = c % STAGES2;
         mbar_wait(full + s, (uint32_t)((c / STAGES2) & 1));
         const Stage2& st = stage[s];
+        // fix entries of this warp's slots in this chunk (usually 0..3): lane l fetches the column mask of entry l / RPL for
+        // reference group l % RPL (one load for the whole warp, consumed after the counting work of the chunk)
+        const uint32_t fb = st.q.fix_begin[warp], fe = st.q.fix_begin[warp + 1];
+        const uint8_t* gl0 = rsrc + (size_t)c * STAGE2_REF_BYTES;
+        uint32_t my_ent = 0, my_col = 0;
+        if (fb + lane / RPL < fe) {
+            my_ent = st.q.fix[fb + lane / RPL];
+            my_col = __ldg(reinterpret_cast<const uint32_t*>(gl0 + (lane % RPL) * group_stride + (my_ent & 0xffffu)));
+        }
 #pragma unroll
         for (int u = 0; u < W4; ++u) {
+            // which of this warp's slots have work in this unit (the others are complete and equal to the pivot over these
+            // 128 sites); nothing to do for any of them: not even the reference words are read
+            const uint32_t act = (st.q.active[u][q0 >> 5] >> (q0 & 31)) & ((1u << QW2) - 1u);
+            if (act == 0u) continue;
             uint4 rb[RPL], rm[RPL];
 #pragma unroll
             for (int g = 0; g < RPL; ++g) { rb[g] = st.ref[g][u].base[lane]; rm[g] = st.ref[g][u].mc[lane]; }
 #pragma unroll
             for (int j = 0; j < QW2; ++j) {
-                const uint4 qb = st.q.pl[u][q0 + j][0], qe = st.q.pl[u][q0 + j][1];
+                if (!((act >> j) & 1u)) continue;
+                const uint4 qe = st.q.pl[u][q0 + j][1], qb = st.q.pl[u][q0 + j][0];
+                ++executed;
 #pragma unroll
                 for (int g = 0; g < RPL; ++g) {
                     const uint32_t V0 = rb[g].x & qb.x, V1 = rb[g].y & qb.y, V2 = rb[g].z & qb.z, V3 = rb[g].w & qb.w;
@@ -115,22 +159,15 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 1024 / PIVOT_THREADS) k_pairpiv
                 }
             }
         }
-        // fix entries of this warp's slots in this chunk (usually 0..3): query base != pivot base at the masked bits
-        {
-            const uint32_t fb = st.q.fix_begin[warp], fe = st.q.fix_begin[warp + 1];
-            const uint8_t* r0 = reinterpret_cast<const uint8_t*>(&st.ref[0][0]) + lane * 4;
-            for (uint32_t e = fb; e < fe; ++e) {
-                const uint2 ent = st.q.fix[e];
-                const uint32_t off = ent.y & 0xffffu, jj = ent.y >> 16;
-#pragma unroll
-                for (int g = 0; g < RPL; ++g) {
-                    const uint32_t hit = *reinterpret_cast<const uint32_t*>(r0 + g * (W4 * UNIT2_BYTES) + off) & ent.x;
-                    if (hit) {
-                        const uint32_t n = __popc(hit);
-#pragma unroll
-                        for (int j = 0; j < QW2; ++j) if (jj == (uint32_t)j) acc[g][j] += n;
-                    }
+        if (fe > fb) {
+            resolve(my_ent, my_col);
+            for (uint32_t e0 = fb + 32 / RPL; e0 < fe; e0 += 32 / RPL) {    // more than 16 entries (rare)
+                my_col = 0;
+                if (e0 + lane / RPL < fe) {
+                    my_ent = st.q.fix[e0 + lane / RPL];
+                    my_col = __ldg(reinterpret_cast<const uint32_t*>(gl0 + (lane % RPL) * group_stride + (my_ent & 0xffffu)));
                 }
+                resolve(my_ent, my_col);
             }
         }
         // release the stage; the elected thread refills the stage consumed REFILL_LAG chunks ago (everybody is done with it
@@ -149,7 +186,7 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 1024 / PIVOT_THREADS) k_pairpiv
         }
         __syncwarp();
     }
-    if (lane == 0 && p.work) atomicAdd(p.work, (unsigned long long)p.n_chunks * (QW2 * RPL));
+    if (lane == 0 && p.work) atomicAdd(p.work, (unsigned long long)executed * RPL);
 
     // ---- epilogue: plane counts -> exact counts -> score tile of the owner ----
     bool in_range[RPL];
@@ -167,8 +204,8 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 1024 / PIVOT_THREADS) k_pairpiv
 #pragma unroll
         for (int g = 0; g < RPL; ++g) {
             if (!in_range[g]) continue;
-            const int32_t M = (int32_t)(acc[g][j] & 0xffffu) + __popc(oM[g][j]);
-            const int32_t V = (int32_t)(acc[g][j] >> 16) + __popc(oV[g][j]);
+            const int32_t M = p.mc_cnt[local[g]] - (int32_t)((acc[g][j] & 0xffffu) + __popc(oM[g][j])) + (int32_t)fixhit[(q0 + j) * (RPL * GROUP) + g * GROUP + lane];
+            const int32_t V = p.rb_cnt[local[g]] - (int32_t)((acc[g][j] >> 16) + __popc(oV[g][j]));
             const uint4 v = pair_epilogue_default(p, p.qfix_off, p.qfix_ent, slot, group0 + g, lane, local[g], M, V);
             pair_store(p, owner, row0 + q0 + j, is_cons, local[g], v);
         }
@@ -180,6 +217,7 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 1024 / PIVOT_THREADS) k_pairpiv
 // One thread per (group, unit, lane): 3 coalesced 16-byte loads, 2 16-byte + 16 coalesced 4-byte stores.
 // pivot[unit] = (b0, b1) planes of the pivot sequence, 4 words each.
 __global__ void __launch_bounds__(256) k_derive_pivot(const uint4* __restrict__ db, uint8_t* __restrict__ db2, const uint4* __restrict__ pivot,
+                                                      int32_t* __restrict__ rb_cnt, int32_t* __restrict__ mc_cnt,
                                                       int64_t begin, int64_t end, int64_t group_first, int units, int Wp)
 {
     const int lane = threadIdx.x & 31;
@@ -187,10 +225,15 @@ __global__ void __launch_bounds__(256) k_derive_pivot(const uint4* __restrict__ 
     const int64_t group = group_first + t / units;
     const int unit = (int)(t % units);
     const int64_t ordinal = group * GROUP + lane;
-    if (ordinal < begin || ordinal >= end) return;
-    const uint4 rb = db[db_unit_index(group, unit, 0, lane, Wp)];
-    const uint4 r0 = db[db_unit_index(group, unit, 1, lane, Wp)];
-    const uint4 r1 = db[db_unit_index(group, unit, 2, lane, Wp)];
+    if (group * GROUP >= end) return;                                                       // whole warp
+    const bool resident = ordinal < end;                     // lanes below `begin` were derived before: they only vote
+    const bool fresh = resident && ordinal >= begin;
+    uint4 rb = make_uint4(0u, 0u, 0u, 0u), r0 = rb, r1 = rb;
+    if (resident) {
+        rb = db[db_unit_index(group, unit, 0, lane, Wp)];
+        r0 = db[db_unit_index(group, unit, 1, lane, Wp)];
+        r1 = db[db_unit_index(group, unit, 2, lane, Wp)];
+    }
     const uint4 p0 = __ldg(pivot + 2 * unit), p1 = __ldg(pivot + 2 * unit + 1);
     uint4 mc;
     mc.x = keep_eq(keep_eq(rb.x, r0.x, p0.x), r1.x, p1.x);
@@ -198,15 +241,28 @@ __global__ void __launch_bounds__(256) k_derive_pivot(const uint4* __restrict__ 
     mc.z = keep_eq(keep_eq(rb.z, r0.z, p0.z), r1.z, p1.z);
     mc.w = keep_eq(keep_eq(rb.w, r0.w, p0.w), r1.w, p1.w);
     RefUnit2* rec = reinterpret_cast<RefUnit2*>(db2 + db2_unit_bytes(group, unit, Wp));
-    rec->base[lane] = rb;
-    rec->mc[lane] = mc;
+    if (fresh) {
+        rec->base[lane] = rb;
+        rec->mc[lane] = mc;
+        atomicAdd(rb_cnt + ordinal, __popc(rb.x) + __popc(rb.y) + __popc(rb.z) + __popc(rb.w));
+        atomicAdd(mc_cnt + ordinal, __popc(mc.x) + __popc(mc.y) + __popc(mc.z) + __popc(mc.w));
+    }
+    // column masks: 32 x 32 bit transposes of the one-hot planes (ballots); lane s keeps and stores the mask of site s.
+    // The whole word is rewritten: the bits of the references derived earlier do not change.
     const uint32_t b[4] = {rb.x, rb.y, rb.z, rb.w}, x[4] = {r0.x, r0.y, r0.z, r0.w}, y[4] = {r1.x, r1.y, r1.z, r1.w};
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        rec->onehot[k][0][lane] = b[k] & ~x[k] & ~y[k];      // A
-        rec->onehot[k][1][lane] = b[k] & x[k] & ~y[k];       // C
-        rec->onehot[k][2][lane] = b[k] & ~x[k] & y[k];       // G
-        rec->onehot[k][3][lane] = b[k] & x[k] & y[k];        // T
+        const uint32_t oh[4] = {b[k] & ~x[k] & ~y[k], b[k] & x[k] & ~y[k], b[k] & ~x[k] & y[k], b[k] & x[k] & y[k]};      // A, C, G, T
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            uint32_t mine = 0;
+#pragma unroll
+            for (int sbit = 0; sbit < 32; ++sbit) {
+                const uint32_t m = __ballot_sync(0xffffffffu, (oh[a] >> sbit) & 1u);
+                if (lane == sbit) mine = m;
+            }
+            rec->colmask[k][a][lane] = mine;
+        }
     }
 }
 
@@ -228,7 +284,8 @@ cudaError_t launch_pairpivot(const PairParams& p, cudaStream_t st)
     return cudaGetLastError();
 }
 
-cudaError_t launch_derive_pivot(const uint4* db, uint8_t* db2, const uint4* pivot, int64_t begin, int64_t end, int Wp, cudaStream_t st)
+cudaError_t launch_derive_pivot(const uint4* db, uint8_t* db2, const uint4* pivot, int32_t* rb_cnt, int32_t* mc_cnt, int64_t begin, int64_t end,
+                                int Wp, cudaStream_t st)
 {
     if (end <= begin) return cudaSuccess;
     const int64_t g0 = begin / GROUP, g1 = (end + GROUP - 1) / GROUP;
@@ -236,7 +293,7 @@ cudaError_t launch_derive_pivot(const uint4* db, uint8_t* db2, const uint4* pivo
     const int64_t warps = (g1 - g0) * units;
     const int64_t blocks = (warps + 7) / 8;
     if (blocks > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
-    k_derive_pivot<<<(unsigned)blocks, 256, 0, st>>>(db, db2, pivot, begin, end, g0, units, Wp);
+    k_derive_pivot<<<(unsigned)blocks, 256, 0, st>>>(db, db2, pivot, rb_cnt, mc_cnt, begin, end, g0, units, Wp);
     return cudaGetLastError();
 }
 
