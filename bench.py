@@ -29,7 +29,7 @@ sys.path.insert(0, ROOT)
 NCHAR = 29903
 # algorithmic instruction counts per (pair, 32-site word) of the two pair-count kernels
 OPS = {"pivot": {"kernel": "k_pairpivot", "lop3": 4.0, "popc": 1.0, "db_bytes_per_word": 24,     # 2 AND + 2 x (one 3:2 compressor per two words); 2 x 0.5 POPC
-                 "ncu": "ncu_pairpivot_r01g.json"},
+                 "ncu": "ncu_pairpivot_r01k_sparse.json"},
        "general": {"kernel": "k_paircount", "lop3": 4.5, "popc": 1.25, "db_bytes_per_word": 12,  # 3 for valid+match, 1.5 carry-save tree; 1 + 0.25 POPC
                    "ncu": "ncu_paircount_r01e_csa.json"}}
 
@@ -416,7 +416,7 @@ def main():
     roofline = {"kernel": ops["kernel"], "bound": bound, "achieved": popc if bound == "int-popc" else lop3,
                 "peak": peaks["popc_gips"] if bound == "int-popc" else peaks["lop3_gips"], "unit": "Gthread-inst/s",
                 "frac": max(f_l, f_p), "traffic": tr["bytes"] if tr else None, "traffic_detail": tr,
-                "note": "INT pipes bind (north_star): %.2f LOP3 + %.2f POPC per EXECUTED pair x 32-site word (padding and early abort accounted for); peaks = profiles/int_pipes_b200_r01.json (measured)"
+                "note": "INT pipes (north_star): %.2f LOP3 + %.2f POPC per EXECUTED pair x 32-site word (padding, early abort and skipped units accounted for); peaks = profiles/int_pipes_b200_r01.json (measured)"
                         % (ops["lop3"], ops["popc"]),
                 "lop3": {"achieved": lop3, "peak": peaks["lop3_gips"], "frac": f_l}, "popc": {"achieved": popc, "peak": peaks["popc_gips"], "frac": f_p},
                 "hbm": {"bound": "hbm", "achieved": db_bytes / (k_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
@@ -425,6 +425,9 @@ def main():
                 "kernel_ms_per_step": k_ms, "kernel_share_of_step": k_ms / ms_step,
                 "executed_pairwords_per_step": pairwords_rank, "dense_pairwords_per_step": pairwords_dense,
                 "executed_fraction_of_dense": pairwords_rank / max(1, pairwords_dense),
+                # the pivot form skips (query, 128-site unit) pairs where the query is complete and equal to the pivot: the same
+                # search priced with the DENSE op count of its formulation (what a kernel that does not skip would have to issue)
+                "frac_if_priced_dense": max(f_l, f_p) * pairwords_dense / max(1.0, pairwords_rank),
                 "pivot_fix_entries_per_query": (st["pivot_fix_entries"] / max(1, Q + 1)) if st["pivot_fix_entries"] >= 0 else None}
 
     cb = None
