@@ -254,7 +254,8 @@ def main():
     from uvaia_b200.engine import Engine
 
     L, R = args.nchar, args.refs
-    first_round, max_round = 1024, (args.max_round or 65536)
+    # small first rounds only serve the early-abort bounds (they fill fast); without early abort start with full waves
+    first_round, max_round = (1024 if args.early_abort else 16384), (args.max_round or 65536)
     clades = make_model(L)
     dev = local_rank if torch.cuda.is_available() else 0
     tiles = rank_tiles(R, rank, world, first_round, max_round)
