@@ -56,17 +56,11 @@ static_assert(sizeof(QChunk) % 16 == 0, "bulk copy size must be a multiple of 16
 // Derived database: per (group of 32 references, unit of 4 column words) one contiguous 3 KB record
 //     uint4 base[32]  |  uint4 mc[32]  |  uint32 colmask[4 words][4 bases A,C,G,T][32 sites]
 // of which the first 1 KB (base, mc: lane = reference) is staged by TMA bulk copies.
-#ifndef PIVOT_STAGES
-#define PIVOT_STAGES 8
-#endif
-constexpr int STAGES2 = PIVOT_STAGES;
+constexpr int STAGES2 = 8;
 constexpr int UNIT2_BYTES = 2 * GROUP * 16 + 4 * 4 * GROUP * 4;      // 3072
 constexpr int UNIT2_ONEHOT = 2 * GROUP * 16;                         // byte offset of the one-hot planes inside a unit record
 constexpr int FIXCAP = 248;                                          // fix entries a chunk of a query tile can carry
-#ifndef PIVOT_QW_
-#define PIVOT_QW_ 4
-#endif
-constexpr int PIVOT_QW = PIVOT_QW_;                                  // query slots per warp of k_pairpivot
+constexpr int PIVOT_QW = 4;                                          // query slots per warp of k_pairpivot
 constexpr int PIVOT_WARPS = QTILE / PIVOT_QW;
 struct __align__(16) QChunk2 {
     uint4    pl[W4][QTILE][2];       // [unit][slot][plane], COMPLEMENTS: 0 = no plain base here (or trimmed / padding), 1 = not the pivot base

@@ -5,23 +5,27 @@
 //
 // All queries of one search are close to a pivot sequence P (per site the plain base most queries hold; uvg_set_queries).
 // For a site where the query holds P's base, "query == reference" is "reference == P", which does not depend on the query:
-//     mc  (reference plane, derived once per query set by k_derive_pivot)  = r.base & (r == P)
-//     qeq (query plane)                                                    = q.base & (q == P)
-//     M' = mc & qeq        V = r.base & q.base                             (2 LOP3 per pair-word instead of 3)
-// Query sites with a plain base != P (the query's own SNPs, a few dozen per genome) are outside M'; they are "fix"
+//     mc (reference plane, derived once per query set by k_derive_pivot) = r.base & (r == P)
+// The query planes are stored INVERTED: nq = no plain base here (or trimmed away / padding), ne = not P's base (nq is a
+// subset of ne), so that
+//     valid  = popc(r.base) - sum popc(r.base & nq)        match' = popc(r.mc) - sum popc(r.mc & ne)
+// with per-reference totals (k_derive_pivot) as first terms and sums that only get contributions from 128-site units in
+// which the query has an N, a gap, an ambiguity code or a SNP: a (slot, unit) pair whose `ne` words are all zero is
+// skipped (QChunk2::active, warp-uniform branch).  Per executed pair-word: 2 LOP3 for the two ANDs, one 3:2 compressor
+// per two words and stream (ones register + one carry word of weight 2), IMAD adds the popcounts:
+//     4 LOP3 (ALU) + 1 POPC (XU) + 1 IMAD (FMA) per pair and 32-site word
+// which balances the ALU and XU pipes at the measured 4:1 LOP3:POPC rate of sm_100 (profiles/int_pipes_b200_r01.json);
+// the general kernel needs 4.5 LOP3 + 1.25 POPC and cannot skip.
+// Query sites with a plain base != P (the query's own SNPs, a few dozen per genome) are outside match'; they are "fix"
 // entries (slot, site, base) that travel with the query chunk and are resolved against column masks of the derived
 // database (per site and base one word: bit l = reference l of the group holds that base): a warp fetches the masks of
 // all its entries of a chunk with one load (lane = entry x group) while it counts the chunk, almost always finds them
-// all zero, and otherwise bumps a per-pair counter in shared memory.  Entries that overflow a chunk's fix block and all ambiguity codes go to the epilogue
-// (pair_epilogue.cuh).
-// Both popcount streams go through one 3:2 compressor per two words (ones register + one carry word of weight 2):
-//     4 LOP3 (ALU) + 1 POPC (XU) + 1 IMAD (FMA) per pair and 32-site word
-// which balances the ALU and XU pipes at the measured 4:1 LOP3:POPC rate of sm_100 (profiles/int_pipes_b200_r01.json);
-// the general kernel needs 4.5 LOP3 + 1.25 POPC.
+// all zero, and otherwise bumps a per-pair counter in shared memory.  Entries that overflow a chunk's fix block and all
+// ambiguity codes go to the epilogue (pair_epilogue.cuh).
 // Shape: block = 64 query slots x 64 references, 16 warps x 4 slots, lane = 2 references, 64 registers, 2 blocks per
-// SM (32 warps per SM).  Staging: one TMA bulk copy per operand into an 8-deep ring with full/empty mbarriers (no
-// __syncthreads in the loop: warps drift up to the ring depth apart); one elected thread refills a stage two chunks
-// after it was consumed.
+// SM (32 warps per SM).  Staging: TMA bulk copies (query chunk + the base/mc planes of the two reference groups) into an
+// 8-deep ring with full/empty mbarriers (no __syncthreads in the loop: warps drift up to the ring depth apart); one
+// elected thread refills a stage two chunks after it was consumed.
 #include "common.cuh"
 #include "kernels.h"
 #include "pair_epilogue.cuh"
