@@ -13,6 +13,8 @@
 #define _GNU_SOURCE
 #include <ctype.h>
 #include <getopt.h>
+#include <pthread.h>
+#include <semaphore.h>
 #include <stdarg.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -172,7 +174,17 @@ static int fasta_next(fasta_t* f)
         }
         if (!f->next_name) continue;                        /* sequence text before the first header */
         if (f->len + n > f->cap) { f->cap = 2 * (f->len + n) + 1024; f->seq = xrealloc(f->seq, f->cap); }
-        for (i = 0; i < n; ++i) if (!is_blank(ln[i])) f->seq[f->len++] = (unsigned char)toupper(ln[i]);
+        {   /* upper-case copy (branch-free, vectorised by the compiler); a line with blanks inside is compacted afterwards */
+            unsigned char* dst = f->seq + f->len;
+            unsigned any_blank = 0;
+            for (i = 0; i < n; ++i) {
+                const unsigned char ch = ln[i];
+                any_blank |= (unsigned)(ch == ' ') | (unsigned)((unsigned char)(ch - 9) < 5);
+                dst[i] = (unsigned char)(ch - (((unsigned char)(ch - 'a') < 26) << 5));
+            }
+            if (!any_blank) f->len += n;
+            else { size_t k = 0; for (i = 0; i < n; ++i) if (!is_blank(ln[i])) dst[k++] = dst[i]; f->len += k; }
+        }
     }
 }
 
@@ -294,6 +306,61 @@ static void writer_put(writer_t* w, const void* p, size_t n)
 static void writer_close(writer_t* w) { if (w->pipe && pclose(w->pipe) != 0) die("xz failed"); if (w->gz) gzclose(w->gz); }
 
 /* ---------------------------------------------------------------------------------------------------------------
+ * reference stream: the reader thread (nearest.c:245-286 without the scoring)
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct { unsigned char* text; char** name; long n; int last; } batch_t;
+typedef struct {
+    const char** file; int n_files, L, min_non_n; long batch_rows;
+    const nameset_t* qset; double t0;
+    batch_t batch[2];
+    sem_t free_slots, full_slots;
+    uint8_t* rec_state; int64_t n_rec, rec_cap;          /* per record: 0 = skipped, 2 = pushed (in stream order) */
+    long count, n_invalid, same_name;
+} stream_t;
+
+static void* stream_reader(void* arg)
+{
+    stream_t* sp = arg;
+    int k = 0;
+    sem_wait(&sp->free_slots);
+    batch_t* bt = &sp->batch[k];
+    bt->n = 0; bt->last = 0;
+    for (int j = 0; j < sp->n_files; ++j) {
+        const double t1 = now_s();
+        fasta_t f;
+        fasta_open(&f, sp->file[j]);
+        while (fasta_next(&f)) {
+            ++sp->count;
+            if (sp->n_rec == sp->rec_cap) { sp->rec_cap = sp->rec_cap ? 2 * sp->rec_cap : 1 << 16; sp->rec_state = xrealloc(sp->rec_state, sp->rec_cap); }
+            sp->rec_state[sp->n_rec++] = 0;
+            if (sp->qset && nameset_has(sp->qset, f.name)) { ++sp->same_name; continue; }             /* nearest.c:255-261 */
+            if ((int64_t)f.len != sp->L) {
+                /* nearest.c:263-278: a poor-quality reference of the wrong length is skipped, a good one is fatal */
+                long nn = 0;
+                for (size_t i = 0; i < f.len; ++i) nn += g_validtxt[f.seq[i]];
+                if (nn < sp->min_non_n) { ++sp->n_invalid; continue; }
+                die("all sequences must be aligned: reference %s has %zu sites, queries have %d", f.name, f.len, sp->L);
+            }
+            memcpy(bt->text + (size_t)bt->n * sp->L, f.seq, sp->L);
+            bt->name[bt->n++] = f.name; f.name = NULL;
+            sp->rec_state[sp->n_rec - 1] = 2;
+            if (bt->n == sp->batch_rows) {
+                sem_post(&sp->full_slots);
+                k ^= 1;
+                sem_wait(&sp->free_slots);
+                bt = &sp->batch[k];
+                bt->n = 0; bt->last = 0;
+            }
+        }
+        fasta_close(&f);
+        fprintf(stderr, "Finished reading file %s in %.3lf secs;\n", sp->file[j], now_s() - t1);
+    }
+    bt->last = 1;
+    sem_post(&sp->full_slots);
+    return NULL;
+}
+
+/* ---------------------------------------------------------------------------------------------------------------
  * main: nearest.c:159-353
  * ------------------------------------------------------------------------------------------------------------- */
 static void usage(const char* prog, int full)
@@ -388,58 +455,55 @@ int main(int argc, char** argv)
         qset = nameset_build(q.name, q.n);
     }
 
-    /* 2. reference stream: batches of rows in pinned memory -> uvg_push_refs (copy + encoder) -> uvg_search_async (the rounds
-     * of this batch run under the reading and the copy of the next one) */
+    /* 2. reference stream.  A reader thread parses the files into two batches of rows in pinned memory; this thread hands
+     * every full batch to uvg_push_refs (copy + encoder) and uvg_search_async: reading and parsing batch i+1, the copy of
+     * batch i and the scoring rounds of batch i-1 overlap. */
     const int min_non_n = (int)(L * (1.0 - ambig_r));                           /* nearest.c:237 */
     if (batch_rows > ((long)1 << 30) / L) batch_rows = (((long)1 << 30) / L) > 0 ? ((long)1 << 30) / L : 1;
-    unsigned char* batch = uvg_host_alloc_pinned((size_t)batch_rows * L);
-    if (!batch) die("cannot allocate %zu bytes of pinned memory", (size_t)batch_rows * L);
-    char** bname = xmalloc(batch_rows * sizeof *bname);
-    int64_t* brec = xmalloc(batch_rows * sizeof *brec);                         /* record number of every batch row */
+    stream_t sp;
+    memset(&sp, 0, sizeof sp);
+    sp.file = ref_file; sp.n_files = n_ref_files; sp.L = L; sp.min_non_n = min_non_n; sp.batch_rows = batch_rows;
+    sp.qset = xclude ? &qset : NULL; sp.t0 = t0;
+    for (int k = 0; k < 2; ++k) {
+        sp.batch[k].text = uvg_host_alloc_pinned((size_t)batch_rows * L);
+        if (!sp.batch[k].text) die("cannot allocate %zu bytes of pinned memory", (size_t)batch_rows * L);
+        sp.batch[k].name = xmalloc(batch_rows * sizeof(char*));
+    }
+    sem_init(&sp.free_slots, 0, 2);
+    sem_init(&sp.full_slots, 0, 0);
+    pthread_t reader;
+    if (pthread_create(&reader, NULL, stream_reader, &sp)) die("cannot start the reader thread");
     uint8_t* accepted = xmalloc(batch_rows);
     char** rname = NULL; int64_t n_acc_total = 0, rname_cap = 0;                /* names of the accepted references, by ordinal */
-    uint8_t* rec_ok = NULL; int64_t n_rec = 0, rec_cap = 0;                     /* per streamed record: 1 = accepted (second pass for .aln) */
-    long count = 0, n_invalid = 0, same_name = 0, nb = 0;
-
-#define FLUSH_BATCH() do { if (nb > 0) { \
-        int64_t na_ = 0; \
-        if (uvg_push_refs(gpu, batch, nb, min_non_n, NULL, accepted, &na_)) die("%s", uvg_last_error(gpu)); \
-        if (n_acc_total + na_ > rname_cap) { rname_cap = 2 * (n_acc_total + na_) + 1024; rname = xrealloc(rname, rname_cap * sizeof *rname); } \
-        for (long i_ = 0; i_ < nb; ++i_) { \
-            rec_ok[brec[i_]] = accepted[i_]; \
-            if (accepted[i_]) rname[n_acc_total++] = bname[i_]; else { free(bname[i_]); ++n_invalid; } } \
-        if (uvg_search_async(gpu)) die("%s", uvg_last_error(gpu)); \
-        if (uvg_db_count(gpu) >= max_resident) { if (uvg_wait(gpu) || uvg_drop_refs(gpu)) die("%s", uvg_last_error(gpu)); } \
-        nb = 0; } } while (0)
-
-    for (int j = 0; j < n_ref_files; ++j) {
-        const double t1 = now_s();
-        fasta_t f;
-        fasta_open(&f, ref_file[j]);
-        while (fasta_next(&f)) {
-            ++count;
-            if (n_rec == rec_cap) { rec_cap = rec_cap ? 2 * rec_cap : 1 << 16; rec_ok = xrealloc(rec_ok, rec_cap); }
-            rec_ok[n_rec++] = 0;
-            if (xclude && nameset_has(&qset, f.name)) { ++same_name; continue; }                  /* nearest.c:255-261 */
-            if ((int64_t)f.len != L) {
-                /* nearest.c:263-278: a poor-quality reference of the wrong length is skipped, a good one is fatal */
-                long nn = 0;
-                for (size_t i = 0; i < f.len; ++i) nn += g_validtxt[f.seq[i]];
-                if (nn < min_non_n) { ++n_invalid; continue; }
-                die("all sequences must be aligned: reference %s has %zu sites, queries have %d", f.name, f.len, L);
+    uint8_t* push_ok = NULL; int64_t n_pushed = 0, push_cap = 0;                /* per pushed row, in stream order: accepted by the filter */
+    long n_invalid = 0;
+    for (int k = 0;; k ^= 1) {
+        sem_wait(&sp.full_slots);
+        batch_t* bt = &sp.batch[k];
+        if (bt->n > 0) {
+            int64_t na = 0;
+            if (uvg_push_refs(gpu, bt->text, bt->n, min_non_n, NULL, accepted, &na)) die("%s", uvg_last_error(gpu));
+            if (n_acc_total + na > rname_cap) { rname_cap = 2 * (n_acc_total + na) + 1024; rname = xrealloc(rname, rname_cap * sizeof *rname); }
+            if (n_pushed + bt->n > push_cap) { push_cap = 2 * (n_pushed + bt->n) + 1024; push_ok = xrealloc(push_ok, push_cap); }
+            for (long i = 0; i < bt->n; ++i) {
+                push_ok[n_pushed++] = accepted[i];
+                if (accepted[i]) rname[n_acc_total++] = bt->name[i]; else { free(bt->name[i]); ++n_invalid; }
             }
-            memcpy(batch + (size_t)nb * L, f.seq, L);
-            bname[nb] = f.name; f.name = NULL;
-            brec[nb] = n_rec - 1;
-            ++nb;
-            if (nb == batch_rows) FLUSH_BATCH();
+            if (uvg_search_async(gpu)) die("%s", uvg_last_error(gpu));
+            if (uvg_db_count(gpu) >= max_resident) { if (uvg_wait(gpu) || uvg_drop_refs(gpu)) die("%s", uvg_last_error(gpu)); }
         }
-        FLUSH_BATCH();
-        fasta_close(&f);
-        fprintf(stderr, "Finished reading file %s in %.3lf secs;\n", ref_file[j], now_s() - t1);
-        fprintf(stderr, "Total of %ld sequences read; %ld too ambiguous (excluded). %.3lf secs elapsed. \n", count, n_invalid, now_s() - t0);
-        if (xclude) fprintf(stderr, " %ld reference sequences already present in query alignment (based on name only).\n", same_name);
+        const int last = bt->last;
+        sem_post(&sp.free_slots);
+        if (last) break;
     }
+    pthread_join(reader, NULL);
+    n_invalid += sp.n_invalid;
+    const long count = sp.count, same_name = sp.same_name;
+    /* per streamed record: 1 = accepted reference (the second pass for the .aln dump needs it) */
+    uint8_t* rec_ok = sp.rec_state; const int64_t n_rec = sp.n_rec;
+    { int64_t k = 0; for (int64_t i = 0; i < n_rec; ++i) rec_ok[i] = rec_ok[i] == 2 ? push_ok[k++] : 0; }
+    fprintf(stderr, "Total of %ld sequences read; %ld too ambiguous (excluded). %.3lf secs elapsed. \n", count, n_invalid, now_s() - t0);
+    if (xclude) fprintf(stderr, " %ld reference sequences already present in query alignment (based on name only).\n", same_name);
     if (uvg_wait(gpu)) die("%s", uvg_last_error(gpu));
 
     /* 3. <prefix>.aln.xz: every reference that ever entered a heap, in file order (nearest.c:303-314).  The text is not
@@ -505,9 +569,9 @@ int main(int argc, char** argv)
     fprintf(stderr, "Saved distance table to file %s , %.3lf secs elapsed.\n", outname, now_s() - t0);
 
     uvg_destroy(gpu);
-    uvg_host_free_pinned(batch);
+    for (int k = 0; k < 2; ++k) { uvg_host_free_pinned(sp.batch[k].text); free(sp.batch[k].name); }
     for (int64_t i = 0; i < n_acc_total; ++i) free(rname[i]);
     for (int i = 0; i < q.n; ++i) free(q.name[i]);
-    free(rname); free(rec_ok); free(bname); free(brec); free(accepted); free(best); free(outname); free(q.name); free(q.text); free(qset.slot);
+    free(rname); free(rec_ok); free(push_ok); free(accepted); free(best); free(outname); free(q.name); free(q.text); free(qset.slot);
     return EXIT_SUCCESS;
 }
