@@ -302,7 +302,7 @@ def main():
             host_buf = eng._lib.uvg_host_alloc_pinned(need)
             want_e2e = bool(host_buf)
     eng.set_queries(qtext)
-    tile_rows = 16384
+    tile_rows = max(64, min(16384, (1 << 30) // L))            # <= 1 GiB of generated text at a time (config 5: 5 Mb rows)
     d_tile = eng.device_alloc(tile_rows * L)
     t_build = time.perf_counter()
     off = 0
