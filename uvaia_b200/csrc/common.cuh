@@ -65,10 +65,9 @@ constexpr int PIVOT_WARPS = QTILE / PIVOT_QW;
 struct __align__(16) QChunk2 {
     uint4    pl[W4][QTILE][2];       // [unit][slot][plane], COMPLEMENTS: 0 = no plain base here (or trimmed / padding), 1 = not the pivot base
     uint8_t  fix_begin[32];          // [warp] first entry of the warp's slots; [PIVOT_WARPS] = total
-    uint32_t active[W4][2];          // per unit: bit s set <=> slot s has work in this unit (its plane 1 is not all zero)
-    uint32_t pad_[4 - (W4 * 2) % 4];
+    uint8_t  active[W4][16];         // per unit and warp: bit j set <=> the warp's j-th slot (PairParams::wslot) has work in this unit
     uint32_t fix[FIXCAP];            // byte offset of the entry's column-mask word inside a group's chunk of the derived
-                                     //     database | slot-within-warp << 16
+                                     //     database | slot-within-tile << 16
 };
 static_assert(sizeof(QChunk2) % 16 == 0 && PIVOT_WARPS < 32 && FIXCAP < 256, "QChunk2 layout");
 __host__ __device__ inline size_t db2_unit_bytes(int64_t group, int unit, int Wp)
@@ -108,6 +107,7 @@ struct PairParams {
     const int32_t*   rb_cnt;      // per local reference: popcount of its base plane (all words)
     const int32_t*   mc_cnt;      //                      popcount of its mc plane
     const QChunk2*   qdata2;      // [n_qtiles][n_chunks]
+    const uint8_t*   wslot;       // [n_qtiles][PIVOT_WARPS][PIVOT_QW]: which slots of the tile each warp counts (balanced by work)
     const uint32_t*  qfix_off;    // [n_slots + 1] entries the EPILOGUE resolves: ambiguity codes + fix entries that overflowed a chunk
     const uint32_t*  qfix_ent;
     const uint32_t*  ramb_off;    // [local refs + 1] ambiguity entries of the references

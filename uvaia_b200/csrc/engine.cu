@@ -86,6 +86,7 @@ struct uvg_ctx {
     QChunk2* d_qdata2 = nullptr;
     uint32_t *d_qfix_off = nullptr, *d_qfix_ent = nullptr;
     uint4* d_pivot = nullptr;                         // [Wp/4][2]: b0, b1 planes of the pivot sequence
+    uint8_t* d_wslot = nullptr;                       // [n_qtiles][16 warps][4]: slot of the tile each warp of k_pairpivot counts
     uint8_t* d_db2 = nullptr; int64_t db2_cap = 0;    // derived database (base, mc, one-hot planes: 3 KB records) of the resident references
     int32_t* d_ref_cnt = nullptr;                     // [2][db2_cap]: per reference popcount of its base plane / of its mc plane
     Threshold* d_thr_local = nullptr;                 // [rows_cap] bounds of the owned rows (written by K3)
@@ -232,7 +233,7 @@ static void free_queries(uvg_ctx* c, bool final = false)
 {
     close_peers(c);
     cudaFree(c->d_qdata); cudaFree(c->d_qnib); cudaFree(c->d_qamb_off); cudaFree(c->d_qamb_ent);
-    cudaFree(c->d_qdata2); cudaFree(c->d_qfix_off); cudaFree(c->d_qfix_ent); cudaFree(c->d_pivot);
+    cudaFree(c->d_qdata2); cudaFree(c->d_qfix_off); cudaFree(c->d_qfix_ent); cudaFree(c->d_pivot); cudaFree(c->d_wslot); c->d_wslot = nullptr;
     c->d_qdata2 = nullptr; c->d_qfix_off = c->d_qfix_ent = nullptr; c->d_pivot = nullptr; c->pivot_on = false;
     cudaFree(c->d_thr_local); for (int b = 0; b < NBUF; ++b) { cudaFree(c->d_thr_all[b]); c->d_thr_all[b] = nullptr; }
     cudaFree(c->d_heaps); cudaFree(c->d_heaps_all);
@@ -493,6 +494,7 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
 
     // ---- pivot form (pairpivot.cu): pivot planes, fix blocks of the chunks, epilogue lists ----
     std::vector<uint32_t> fix_off, fix_ent, pivot_words;
+    std::vector<uint8_t> wslot;                                             // [tile][warp][j]: slot of the tile the warp counts
     int64_t n_fix_total = 0;
     if (pivot_ok) {
         pivot_words.assign((size_t)(c->Wp / 4) * 8, 0u);                     // [unit][plane b0, b1][4 words]
@@ -505,7 +507,44 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
         std::vector<std::vector<uint32_t>> epi = amb;                       // the epilogue resolves the ambiguity codes ...
         size_t n_snp = 0;
         for (int q = 0; q < c->n_slots; ++q) n_snp += snp[q].size();
-        // fix blocks: entries of a (tile, chunk) ordered by warp; what does not fit goes to the slot's epilogue list
+        // the kernel works on the COMPLEMENTS (pairpivot.cu): plane 0 = sites where the slot holds no plain base (or that
+        // are trimmed away / padding), plane 1 = sites where it does not hold the pivot base; units where plane 1 is zero
+        // are skipped.  Padding slots stay all-zero (always skipped, never stored).  work[slot] = units that are not skipped.
+        std::vector<uint32_t> work((size_t)c->n_qtiles * QTILE, 0);
+        parallel_ranges(c->n_qtiles, host_threads(c->n_qtiles), [&](int, int ta, int tb) {
+            for (int qt = ta; qt < tb; ++qt)
+                for (int ch = 0; ch < c->n_chunks; ++ch) {
+                    QChunk2& blk = qd2[(size_t)qt * c->n_chunks + ch];
+                    for (int u = 0; u < W4; ++u)
+                        for (int qi = 0; qi < QTILE && qt * QTILE + qi < c->n_slots; ++qi) {
+                            for (int pl = 0; pl < 2; ++pl) {
+                                uint4& v = blk.pl[u][qi][pl];
+                                v.x = ~v.x; v.y = ~v.y; v.z = ~v.z; v.w = ~v.w;
+                            }
+                            const uint4& e = blk.pl[u][qi][1];
+                            if (e.x | e.y | e.z | e.w) ++work[(size_t)qt * QTILE + qi];
+                        }
+                }
+        });
+        // Which 4 slots of a tile a warp counts: the warps of a block share one staging ring, so the block runs at the pace
+        // of the warp with the most work.  Longest-processing-time first: slots by decreasing work, each to the least
+        // loaded warp that still has room.
+        wslot.assign((size_t)c->n_qtiles * QTILE, 0);
+        for (int qt = 0; qt < c->n_qtiles; ++qt) {
+            int order[QTILE];
+            for (int i = 0; i < QTILE; ++i) order[i] = i;
+            const uint32_t* wk = &work[(size_t)qt * QTILE];
+            std::stable_sort(order, order + QTILE, [&](int x, int y) { return wk[x] > wk[y]; });
+            uint64_t load[PIVOT_WARPS] = {0}; int cnt[PIVOT_WARPS] = {0};
+            for (int i = 0; i < QTILE; ++i) {
+                int best = -1;
+                for (int w = 0; w < PIVOT_WARPS; ++w) if (cnt[w] < PIVOT_QW && (best < 0 || load[w] < load[best])) best = w;
+                wslot[(size_t)qt * QTILE + best * PIVOT_QW + cnt[best]++] = (uint8_t)order[i];
+                load[best] += wk[order[i]];
+            }
+        }
+        // per chunk: the active-slot nibble of every warp and unit, and the fix block: entries ordered by warp; what does
+        // not fit goes to the slot's epilogue list
         size_t n_overflow = 0;
         std::vector<size_t> cur(c->n_slots, 0);
         for (int qt = 0; qt < c->n_qtiles; ++qt)
@@ -516,38 +555,24 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
                 for (int wp = 0; wp < PIVOT_WARPS; ++wp) {
                     blk.fix_begin[wp] = (uint8_t)n;
                     for (int j = 0; j < PIVOT_QW; ++j) {
-                        const int q = qt * QTILE + wp * PIVOT_QW + j;
+                        const int qi = wslot[(size_t)qt * QTILE + wp * PIVOT_QW + j];
+                        const int q = qt * QTILE + qi;
                         if (q >= c->n_slots) continue;
+                        for (int u = 0; u < W4; ++u) {
+                            const uint4& e = blk.pl[u][qi][1];
+                            if (e.x | e.y | e.z | e.w) blk.active[u][wp] |= (uint8_t)(1u << j);
+                        }
                         while (cur[q] < snp[q].size() && (snp[q][cur[q]] & AMB_SITE_MASK) < site_end) {
                             const uint32_t ent = snp[q][cur[q]++], site = ent & AMB_SITE_MASK, code = ent >> 28;
                             const uint32_t w = site >> 5, a = code == 1 ? 0 : code == 2 ? 1 : code == 4 ? 2 : 3;
                             if (n >= FIXCAP) { epi[q].push_back(ent); ++n_overflow; continue; }
                             const uint32_t off = ((w % WC) / 4) * UNIT2_BYTES + UNIT2_ONEHOT + (((w & 3) * 4 + a) * 32 + (site & 31)) * 4;
-                            blk.fix[n++] = off | ((uint32_t)j << 16);
+                            blk.fix[n++] = off | ((uint32_t)qi << 16);
                         }
                     }
                 }
                 blk.fix_begin[PIVOT_WARPS] = (uint8_t)n;
             }
-        // the kernel works on the COMPLEMENTS (pairpivot.cu): plane 0 = sites where the slot holds no plain base (or that
-        // are trimmed away / padding), plane 1 = sites where it does not hold the pivot base; units where plane 1 is zero
-        // are skipped.  Padding slots stay all-zero (always skipped, never stored).
-        parallel_ranges(c->n_qtiles, host_threads(c->n_qtiles), [&](int, int ta, int tb) {
-            for (int qt = ta; qt < tb; ++qt)
-                for (int ch = 0; ch < c->n_chunks; ++ch) {
-                    QChunk2& blk = qd2[(size_t)qt * c->n_chunks + ch];
-                    for (int u = 0; u < W4; ++u)
-                        for (int qi = 0; qi < QTILE && qt * QTILE + qi < c->n_slots; ++qi)
-                        {
-                            for (int pl = 0; pl < 2; ++pl) {
-                                uint4& v = blk.pl[u][qi][pl];
-                                v.x = ~v.x; v.y = ~v.y; v.z = ~v.z; v.w = ~v.w;
-                            }
-                            const uint4& e = blk.pl[u][qi][1];
-                            if (e.x | e.y | e.z | e.w) blk.active[u][qi >> 5] |= 1u << (qi & 31);
-                        }
-                }
-        });
         fix_off.assign(c->n_slots + 1, 0);
         for (int q = 0; q < c->n_slots; ++q) {
             fix_off[q] = (uint32_t)fix_ent.size();
@@ -603,6 +628,8 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
         UVG_CUDA(c, cudaMalloc(&c->d_qfix_off, fix_off.size() * 4));
         UVG_CUDA(c, cudaMalloc(&c->d_qfix_ent, std::max<size_t>(1, fix_ent.size()) * 4));
         UVG_CUDA(c, cudaMalloc(&c->d_pivot, pivot_words.size() * 4));
+        UVG_CUDA(c, cudaMalloc(&c->d_wslot, wslot.size()));
+        UVG_CUDA(c, cudaMemcpyAsync(c->d_wslot, wslot.data(), wslot.size(), cudaMemcpyHostToDevice, c->st));
         UVG_CUDA(c, cudaMemcpyAsync(c->d_qdata2, qd2.data(), n_chunk_total * sizeof(QChunk2), cudaMemcpyHostToDevice, c->st));
         UVG_CUDA(c, cudaMemcpyAsync(c->d_qfix_off, fix_off.data(), fix_off.size() * 4, cudaMemcpyHostToDevice, c->st));
         if (!fix_ent.empty()) UVG_CUDA(c, cudaMemcpyAsync(c->d_qfix_ent, fix_ent.data(), fix_ent.size() * 4, cudaMemcpyHostToDevice, c->st));
@@ -887,6 +914,7 @@ static void fill_pair_params(uvg_ctx* c, PairParams& pp, int64_t lb, int64_t le,
     pp.db = c->d_db; pp.qdata = c->d_qdata; pp.thr = c->d_thr_all[buf];
     pp.qnib = c->d_qnib; pp.qamb_off = c->d_qamb_off; pp.qamb_ent = c->d_qamb_ent;
     pp.rb_cnt = c->d_ref_cnt; pp.mc_cnt = c->d_ref_cnt ? c->d_ref_cnt + c->db2_cap : nullptr;
+    pp.wslot = c->d_wslot;
     pp.db2 = c->d_db2; pp.qdata2 = c->d_qdata2; pp.qfix_off = c->d_qfix_off; pp.qfix_ent = c->d_qfix_ent;
     pp.ramb_off = c->d_ramb_off; pp.ramb_ent = c->d_ramb_ent; pp.non_n = c->d_non_n;
     pp.qnib_stride = c->qnib_stride;

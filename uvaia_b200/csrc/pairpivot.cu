@@ -104,7 +104,10 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
 #pragma unroll
         for (int j = 0; j < QW2; ++j) { oV[g][j] = 0; oM[g][j] = 0; acc[g][j] = 0; }
 
-    const int q0 = warp * QW2;
+    // the slots of the tile this warp counts (uvg_set_queries balances the warps of a tile by work)
+    int sj[QW2];
+#pragma unroll
+    for (int j = 0; j < QW2; ++j) sj[j] = p.wslot[((size_t)qt * PIVOT_WARPS + warp) * QW2 + j];
     // resolve fetched column masks: a set bit = that reference holds the query's (non-pivot) base at the site, a match the
     // planes did not see.  Almost always no lane holds a non-zero mask.
     auto resolve = [&](uint32_t ent_l, uint32_t col_l) {
@@ -113,7 +116,7 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
             const int src = __ffs(any) - 1;
             any &= any - 1u;
             const uint32_t col = __shfl_sync(0xffffffffu, col_l, src), ent = __shfl_sync(0xffffffffu, ent_l, src);
-            if ((col >> lane) & 1u) fixhit[(q0 + (ent >> 16)) * (RPL * GROUP) + (src % RPL) * GROUP + lane] += 1;   // this thread owns the counter
+            if ((col >> lane) & 1u) fixhit[(ent >> 16) * (RPL * GROUP) + (src % RPL) * GROUP + lane] += 1;   // this thread owns the counter
         }
     };
     uint32_t executed = 0;                                                   // (slot, unit) iterations that were not skipped
@@ -134,7 +137,7 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         for (int u = 0; u < W4; ++u) {
             // which of this warp's slots have work in this unit (the others are complete and equal to the pivot over these
             // 128 sites); nothing to do for any of them: not even the reference words are read
-            const uint32_t act = (st.q.active[u][q0 >> 5] >> (q0 & 31)) & ((1u << QW2) - 1u);
+            const uint32_t act = st.q.active[u][warp];
             if (act == 0u) continue;
             uint4 rb[RPL], rm[RPL];
 #pragma unroll
@@ -142,7 +145,7 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
 #pragma unroll
             for (int j = 0; j < QW2; ++j) {
                 if (!((act >> j) & 1u)) continue;
-                const uint4 qe = st.q.pl[u][q0 + j][1], qb = st.q.pl[u][q0 + j][0];
+                const uint4 qe = st.q.pl[u][sj[j]][1], qb = st.q.pl[u][sj[j]][0];
                 ++executed;
 #pragma unroll
                 for (int g = 0; g < RPL; ++g) {
@@ -202,16 +205,16 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     }
 #pragma unroll
     for (int j = 0; j < QW2; ++j) {
-        const int slot = qt * QTILE + q0 + j;
+        const int slot = qt * QTILE + sj[j];
         if (slot >= p.n_slots) continue;
         const bool is_cons = slot == p.n_slots - 1;
 #pragma unroll
         for (int g = 0; g < RPL; ++g) {
             if (!in_range[g]) continue;
-            const int32_t M = p.mc_cnt[local[g]] - (int32_t)((acc[g][j] & 0xffffu) + __popc(oM[g][j])) + (int32_t)fixhit[(q0 + j) * (RPL * GROUP) + g * GROUP + lane];
+            const int32_t M = p.mc_cnt[local[g]] - (int32_t)((acc[g][j] & 0xffffu) + __popc(oM[g][j])) + (int32_t)fixhit[sj[j] * (RPL * GROUP) + g * GROUP + lane];
             const int32_t V = p.rb_cnt[local[g]] - (int32_t)((acc[g][j] >> 16) + __popc(oV[g][j]));
             const uint4 v = pair_epilogue_default(p, p.qfix_off, p.qfix_ent, slot, group0 + g, lane, local[g], M, V);
-            pair_store(p, owner, row0 + q0 + j, is_cons, local[g], v);
+            pair_store(p, owner, row0 + sj[j], is_cons, local[g], v);
         }
     }
 }
