@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
             const int src = __ffs(any) - 1;
             any &= any - 1u;
             const uint32_t col = __shfl_sync(0xffffffffu, col_l, src), ent = __shfl_sync(0xffffffffu, ent_l, src);
-            if ((col >> lane) & 1u) fixhit[(ent >> 16) * (RPL * GROUP) + (src % RPL) * GROUP + lane] += 1;   // this thread owns the counter
+            fixhit[(ent >> 16) * (RPL * GROUP) + (src % RPL) * GROUP + lane] += (uint16_t)((col >> lane) & 1u);   // branch-free; this thread owns the counter
         }
     };
     uint32_t executed = 0;                                                   // (slot, unit) iterations that were not skipped
