@@ -8,7 +8,7 @@
  *   - the reference stream in batches: -x name lookup (nearest.c:255-261), length check (nearest.c:263-278);
  *   - <prefix>.csv.xz (nearest.c:513-547) and <prefix>.aln.xz (nearest.c:308-314, align.c:346-355).
  * Everything that scores a pair or keeps a neighbour runs on the GPU: without the library and a B200 the program
- * fails, there is no CPU path.  Not supported: -k/--keep_resolved (query redundancy pruning, fastaseq.c:797-841).
+ * fails, there is no CPU path.  -k/--keep_resolved prunes redundant queries through uvg_prune_queries (fastaseq.c:797-841).
  */
 #define _GNU_SOURCE
 #include <ctype.h>
@@ -366,7 +366,7 @@ static void* stream_reader(void* arg)
 static void usage(const char* prog, int full)
 {
     printf("%s\nFor every query sequence, finds the closest neighbours in the reference alignment (n-best search on a B200 GPU)\n", PROGRAM_VERSION);
-    printf("Usage: %s [-hvx] [--acgt] [-n <int>] [--trim=<int>] [-A <double>] [-a <double>] [-p <int>] -r <ref.fa(.gz,.xz)> [-r ...] "
+    printf("Usage: %s [-hvxk] [--acgt] [-n <int>] [--trim=<int>] [-A <double>] [-a <double>] [-p <int>] -r <ref.fa(.gz,.xz)> [-r ...] "
            "[-t <int>] [-o <without suffix>] <seqs.fa(.gz,.xz)>\n", prog);
     if (!full) return;
     printf("  -n, --nbest            number of best reference sequences per query to store (default=100)\n"
@@ -374,6 +374,7 @@ static void usage(const char* prog, int full)
            "  -a, --query_ambiguity  maximum allowed ambiguity for QUERY sequence to be excluded (default=0.5)\n"
            "  -A, --ref_ambiguity    maximum allowed ambiguity for REFERENCE sequence to be excluded (default=0.5)\n"
            "      --acgt             considers only ACGT sites in query sequences (mismatch-based)\n"
+           "  -k, --keep_resolved    keep more resolved and exclude redundant query seqs (default is to keep all)\n"
            "  -x, --exclude_self     exclude reference sequences with same name as a query sequence\n"
            "  -p, --pool             pool size of the reference program (only used to flag pool-dependent results, hazard H1)\n"
            "  -r, --reference        aligned reference sequences (can be several files)\n"
@@ -417,7 +418,6 @@ int main(int argc, char** argv)
         }
     }
     if (n_ref_files < 1 || argc - optind != 1) { usage(argv[0], 0); return EXIT_FAILURE; }
-    if (hires) die("-k/--keep_resolved is not supported by this host program");
     const char* query_file = argv[optind];
     if (ambig_q < 0.001) ambig_q = 0.001;                                       /* nearest.c:175-179 */
     if (ambig_q > 1.) ambig_q = 1.;
@@ -444,6 +444,20 @@ int main(int argc, char** argv)
     uvg_ctx* gpu = NULL;
     uvg_query_info qi;
     if (uvg_create(&prm, &gpu)) die("%s", uvg_last_error(NULL));
+    if (hires) {                                                                /* nearest.c:219-224 */
+        uint8_t* keep = xmalloc(q.n);
+        int n_kept = 0;
+        if (uvg_prune_queries(q.text, q.n, L, trim, acgt, 1, keep, &n_kept)) die("uvg_prune_queries failed");
+        int w = 0;
+        for (int i = 0; i < q.n; ++i) {
+            if (!keep[i]) { free(q.name[i]); continue; }
+            if (w != i) { memmove(q.text + (size_t)w * L, q.text + (size_t)i * L, L); q.name[w] = q.name[i]; }
+            ++w;
+        }
+        q.n = n_kept;
+        free(keep);
+        fprintf(stderr, "Updated query database composed of %d valid references, after removing redundant (less resolved) sequences.\n", q.n);
+    }
     if (uvg_set_queries(gpu, q.text, q.n, &qi)) die("%s", uvg_last_error(gpu));
     fprintf(stderr, "Query sequence alignment: %d segregating, %d non-segregating sites with indels, and %d constant sites (all are used in comparisons)\n",
             qi.n_idx, qi.n_idx_m, qi.n_idx_c);                                  /* fastaseq.c:774 */

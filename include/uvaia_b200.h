@@ -94,6 +94,15 @@ int  uvg_abi_version(void);
  * host; case-insensitive.  Builds consensus / idx / idx_m / idx_c, the trimmed bit-planes of every query and the
  * consensus pseudo-query on the device, and empties all heaps (max_incompatible = nchar, nearest.c:375,387). */
 int uvg_set_queries(uvg_ctx* ctx, const uint8_t* text, int32_t n_query, uvg_query_info* info);
+/* -k / --keep_resolved: replaces exclude_redundant_query_sequences (fastaseq.c:797-841; called at nearest.c:219-224 and
+ * ball.c:190).  text = the filtered and ordered query rows as for uvg_set_queries; keep[i] = 1 if query i stays, *n_kept
+ * (may be NULL) = how many.  keep_more_resolved: of two equivalent queries drop the one with fewer usable sites (what
+ * `uvaia -k` asks for); 0 drops the more resolved one (uvaiaball's default).  The caller compacts the rows and calls
+ * uvg_set_queries with the survivors (the reference rebuilds its indices the same way, nearest.c:222).  nchar, trim and
+ * acgt_mode as in uvg_params (trim is clamped the same way).  Runs on host threads and needs no context: the walk over
+ * the pairs is sequential in the reference and short (first differing site ends a pair). */
+int uvg_prune_queries(const uint8_t* text, int32_t n_query, int32_t nchar, int32_t trim, int32_t acgt_mode,
+                      int32_t keep_more_resolved, uint8_t* keep, int32_t* n_kept);
 
 /* ---- references: replaces quick_count_sequence_non_N + the ref filter (nearest.c:263-270) + the char2bit lookups.
  * text = n rows of nchar bytes (host memory; pinned memory makes the copy asynchronous).  Each row gets
@@ -111,6 +120,17 @@ int uvg_drop_refs(uvg_ctx* ctx);
 /* Forget every reference and restart ordinals at 0 (heaps are emptied too). */
 int uvg_clear_refs(uvg_ctx* ctx);
 int64_t uvg_db_count(const uvg_ctx* ctx);              /* accepted references resident on this rank */
+
+/* ---- packed reference cache (no counterpart in the reference, which re-reads the FASTA text on every run) ----
+ * The packed references leave and enter the device as they are: planes of whole groups of 32 references, non_n and the
+ * ambiguity lists, behind a 64-byte header that names nchar and the mode they were encoded for.  A host keeps the blob
+ * (a file, pinned memory) and the names; the next search skips reading, parsing and encoding the text and moves 0.375
+ * bytes per site to the device instead of 1.  `first` must be a multiple of 32 and [first, first+n) resident;
+ * uvg_import_packed appends like uvg_push_refs (accepted rows only: the -A filter was applied when the blob was made) and
+ * needs the resident count to be a multiple of 32.  Pinned blobs (uvg_host_alloc_pinned) copy at full PCIe speed. */
+int uvg_packed_bytes(uvg_ctx* ctx, int64_t first, int64_t n, size_t* bytes);
+int uvg_export_packed(uvg_ctx* ctx, int64_t first, int64_t n, void* blob, size_t capacity);
+int uvg_import_packed(uvg_ctx* ctx, const void* blob, size_t bytes, int64_t* n_refs);
 
 /* ---- search: replaces the two OpenMP loops nearest.c:293-299 (consensus stage, per-query heap updates) ----
  * Scores every resident reference not scored yet against every query, in file order, in rounds.  Bit-exact with

@@ -158,6 +158,54 @@ def query_order(Q, trim, acgt):
     return sorted(range(Q.shape[0]), key=lambda i: (int(cnt[i]), i))
 
 
+def _resolved(v1, v2):
+    """left_is_resolved_right[_acgt] (src/fastaseq.c:598-641) on the usable-site flags of two sequences over one index
+    list: -1 if only the left sequence has usable sites the right lacks, +1 for the opposite, 0 if none, 0xff if both."""
+    left, right = bool((v1 & ~v2).any()), bool((~v1 & v2).any())
+    if left and right:
+        return 0xff
+    return -1 if left else (1 if right else 0)
+
+
+def exclude_redundant(Q, idx, idx_m, acgt, keep_more_resolved):
+    """exclude_redundant_query_sequences (src/fastaseq.c:797-841) on the ORDERED query text Q (n, L) with the index
+    lists of create_query_indices.  Returns the indices of the queries that stay.  Pairs (i < j) are visited in
+    lexicographic order and only while both are still kept; a pair is a candidate when no site of idx holds two usable,
+    different bytes (quick_pairwise_score_truncated_idx_indelcheck / quick_pairwise_score_acgt with maxdist 1,
+    fastaseq.c:562-583)."""
+    n = Q.shape[0]
+    use = ACGT if acgt else ~INDEL
+    A, Am = Q[:, idx], Q[:, idx_m]
+    U, Um = use[A], use[Am]
+    valid = np.ones(n, bool)
+    for i in range(n - 1):
+        if not valid[i]:
+            continue
+        # candidates of row i in one sweep (the classification of a pair does not depend on `valid`)
+        differ = (U[i][None, :] & U[i + 1:] & (A[i][None, :] != A[i + 1:])).any(1)
+        for j in (np.where(~differ)[0] + i + 1):
+            if not (valid[i] and valid[j]):
+                continue
+            red1 = _resolved(U[i], U[j])
+            if red1 > 1:
+                continue
+            red2 = _resolved(Um[i], Um[j])
+            if red2 > 1:
+                continue
+            if red1 == 0 and red2 == 0:
+                valid[j] = False
+            red1 += red2
+            if red1 == 0:
+                continue
+            if keep_more_resolved:
+                if red1 > 0: valid[i] = False
+                else: valid[j] = False
+            else:
+                if red1 > 0: valid[j] = False
+                else: valid[i] = False
+    return [i for i in range(n) if valid[i]]
+
+
 # ---------------------------------------------------------------------------------------------
 # heap (src/min_heap.c)
 # ---------------------------------------------------------------------------------------------
@@ -296,8 +344,8 @@ class SearchResult:
         return "\n".join(out) + "\n"
 
 
-def prepare_queries(qnames, qseqs, trim=0, acgt=False, ambiguity=0.5):
-    """filter -> trim clamp -> partition -> reorder (nearest.c:203-213)."""
+def prepare_queries(qnames, qseqs, trim=0, acgt=False, ambiguity=0.5, keep_resolved=False):
+    """filter -> trim clamp -> partition -> reorder -> with -k: prune and partition again (nearest.c:203-224)."""
     keep = filter_queries(qnames, qseqs, min(1.0, max(0.001, ambiguity)))
     if not keep:
         raise ValueError("no valid query sequences")
@@ -308,16 +356,21 @@ def prepare_queries(qnames, qseqs, trim=0, acgt=False, ambiguity=0.5):
     order = query_order(Q, trim, acgt)
     Q = Q[order]
     names = [names[i] for i in order]
+    if keep_resolved:                                          # nearest.c:219-224: hires->count is 1, so "keep more resolved"
+        kept = exclude_redundant(Q, idx, idx_m, acgt, True)
+        Q = Q[kept]
+        names = [names[i] for i in kept]
+        cons, idx, idx_m, idx_c = partition(Q, trim, acgt)
     return names, Q, trim, cons, idx, idx_m, idx_c
 
 
 def search(qnames, qseqs, ref_files, nbest=100, trim=0, acgt=False, ambig_q=0.5, ambig_r=0.5, pool=512,
-           exclude_self=False, literal=False, refs=None):
+           exclude_self=False, literal=False, refs=None, keep_resolved=False):
     """End-to-end restatement of nearest.c main (159-353).
     ref_files: list of FASTA paths, or pass refs=[(names, seqs), ...] directly (one entry per file)."""
     ambig_r = min(1.0, max(0.001, ambig_r))
     nbest = max(1, nbest)
-    names, Q, trim, cons, idx, idx_m, idx_c = prepare_queries(qnames, qseqs, trim, acgt, ambig_q)
+    names, Q, trim, cons, idx, idx_m, idx_c = prepare_queries(qnames, qseqs, trim, acgt, ambig_q, keep_resolved)
     nq, L = Q.shape
     qset = set(names) if exclude_self else None
     non_n_ref = int(L * (1.0 - ambig_r))                       # nearest.c:237

@@ -296,6 +296,60 @@ def case_hygiene():
               "multi-line records, lower case, blanks, tabs, CRLF, comments, names with spaces")
 
 
+def case_keep_resolved():
+    """-k / --keep_resolved (nearest.c:219-224, fastaseq.c:797-841): query sets with exact duplicates, masked (less
+    resolved) copies, chains of copies, copies masked at complementary places (both kept) and copies with a private SNP."""
+    m = SynthModel(nsites=2000, n_clades=12, seed=51, clade_subs=10)
+    qn, Q = m.sample(36, 52, prefix="Wales/QRY")
+    rn, R = m.sample(1500, 53, prefix="England/REF")
+    rng = np.random.default_rng(54)
+    names, rows = list(qn), [q.copy() for q in Q]
+
+    def add(tag, src, row):
+        names.append(qn[src] + b"|" + tag.encode())
+        rows.append(row)
+
+    def masked(row, n_runs, run, char=ord("N")):
+        out = row.copy()
+        for _ in range(n_runs):
+            a = int(rng.integers(200, 1800))
+            out[a:a + run] = char
+        return out
+
+    for src in range(0, 8):
+        add("dup", src, Q[src].copy())                                   # identical: the later one goes
+    for src in range(4, 16):
+        add("lessN", src, masked(Q[src], 3, 25))                         # less resolved copy
+    for src in range(12, 18):
+        a = masked(Q[src], 2, 30)
+        add("chain1", src, a)
+        add("chain2", src, masked(a, 2, 30, ord("-")))                   # chain: src > chain1 > chain2
+    for src in range(18, 24):
+        a, b = Q[src].copy(), Q[src].copy()
+        a[300:340] = ord("N"); b[900:960] = ord("N")                     # complementary masks: neither resolves the other
+        add("compA", src, a); add("compB", src, b)
+    for src in range(24, 30):
+        a = masked(Q[src], 2, 20)
+        pos = int(rng.integers(400, 1600))
+        while a[pos] not in b"ACGT":
+            pos += 1
+        a[pos] = b"ACGT"[(b"ACGT".index(bytes([a[pos]])) + 1) % 4]       # masked copy with a private SNP: not redundant
+        add("snp", src, a)
+    for src in range(30, 34):
+        a = Q[src].copy()
+        sel = np.where(np.isin(a, list(b"ACGT")))[0]
+        a[rng.choice(sel, 12, replace=False)] = ord("R")                 # IUPAC codes: differ as text, equal-ish as sets
+        add("iupac", src, a)
+    perm = rng.permutation(len(names))
+    names = [names[i] for i in perm]
+    text = np.stack([rows[i] for i in perm])
+    qf, rf = fasta_bytes(names, text), fasta_bytes(rn, R)
+    save_case("keep_default", qf, [rf], ["-n", "8", "-k"], "-k: redundant queries pruned, more resolved kept (default mode)")
+    save_case("keep_acgt", qf, [rf], ["-n", "8", "-k", "--acgt"], "-k with --acgt")
+    save_case("keep_trim", qf, [rf], ["-n", "8", "-k", "--trim", "350"], "-k with --trim 350: masks inside the trimmed ends do not count")
+    save_case("keep_off", qf, [rf], ["-n", "8"], "same inputs without -k: every query is searched")
+
+
 def case_c2_shape():
     m = SynthModel(nsites=29903, n_clades=40, seed=1)
     qn, Q = m.sample(24, 2002, prefix="England/QRY")
@@ -329,7 +383,7 @@ def case_bundled():
 
 
 GROUPS = {"unit": make_unit_vectors, "synthetic": case_synthetic, "ties": case_ties, "ambiguous": case_ambiguous,
-          "hygiene": case_hygiene, "c2_shape": case_c2_shape, "bundled": case_bundled}
+          "hygiene": case_hygiene, "keep_resolved": case_keep_resolved, "c2_shape": case_c2_shape, "bundled": case_bundled}
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()

@@ -44,7 +44,7 @@ class Case:
 
     def options(self):
         """the reference's CLI options as keyword arguments of oracle.search / host.search_files"""
-        kw = dict(nbest=100, trim=0, acgt=False, ambig_q=0.5, ambig_r=0.5, pool=512, exclude_self=False)
+        kw = dict(nbest=100, trim=0, acgt=False, ambig_q=0.5, ambig_r=0.5, pool=512, exclude_self=False, keep_resolved=False)
         a = self.args
         i = 0
         while i < len(a):
@@ -55,5 +55,6 @@ class Case:
             elif a[i] == "-p": kw["pool"] = int(a[i + 1]); i += 2
             elif a[i] == "--acgt": kw["acgt"] = True; i += 1
             elif a[i] == "-x": kw["exclude_self"] = True; i += 1
+            elif a[i] == "-k": kw["keep_resolved"] = True; i += 1
             else: raise ValueError(a[i])
         return kw

@@ -33,8 +33,7 @@ def test_help_version_and_usage_errors():
     assert run(["--no-such-option", "-r", "x.fa", "q.fa"]).returncode == 1
     p = run(["-r", "/nonexistent/r.fa", "/nonexistent/q.fa"])
     assert p.returncode == 1 and b"cannot open file" in p.stderr
-    p = run(["-k", "-r", "x.fa", "q.fa"])
-    assert p.returncode == 1 and b"not supported" in p.stderr
+    assert b"--keep_resolved" in run(["--help"]).stdout
 
 
 def test_no_gpu_means_failure_not_fallback():

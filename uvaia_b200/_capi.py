@@ -47,6 +47,7 @@ SYMBOLS = {
     "uvg_last_error": (C.c_char_p, [_P]),
     "uvg_abi_version": (C.c_int, []),
     "uvg_set_queries": (C.c_int, [_P, _P, C.c_int32, C.POINTER(uvg_query_info)]),
+    "uvg_prune_queries": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, C.POINTER(C.c_int32)]),
     "uvg_push_refs": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P, _P, C.POINTER(C.c_int64)]),
     "uvg_push_refs_device": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P, _P, C.POINTER(C.c_int64)]),
     "uvg_drop_refs": (C.c_int, [_P]),

@@ -651,6 +651,122 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     return rc;
 }
 
+// ---- -k / --keep_resolved: exclude_redundant_query_sequences (src/fastaseq.c:797-841) ----
+// The reference walks the pairs (i < j) of the ordered query set, skips a pair when either member is already out, and
+// calls a pair a candidate when no site of idx holds two usable, different bytes (fastaseq.c:562-583 with maxdist 1).  For
+// a candidate it compares which of the two has usable sites the other lacks, over idx and over idx_m (fastaseq.c:598-641),
+// and drops one of them.  Whether a pair is a candidate and which side is more resolved do not depend on who is still in,
+// so host threads classify blocks of rows in parallel (early exit at the first differing site) and the sequential walk
+// replays only the candidates in (i, j) order.
+extern "C" int uvg_prune_queries(const uint8_t* text, int32_t n_query, int32_t nchar, int32_t trim_arg, int32_t acgt_mode,
+                                 int32_t keep_more_resolved, uint8_t* keep, int32_t* n_kept)
+{
+    if (!text || !keep || n_query < 1 || nchar < 1) return UVG_EINVAL;
+    int trim = trim_arg < 0 ? 0 : trim_arg;                                  // fastaseq.c:708-712, as uvg_create
+    if (trim > nchar / 2.1) trim = (int)(nchar / 2.1);
+    const int L = nchar, Q = n_query;
+    const bool acgt = acgt_mode != 0;
+    uint8_t lut[3][256], up[256], usable[256];
+    build_luts(lut);
+    for (int i = 0; i < 256; ++i) up[i] = (uint8_t)((i >= 'a' && i <= 'z') ? i - 32 : i);
+    for (int i = 0; i < 256; ++i) usable[i] = acgt ? (i == 'A' || i == 'C' || i == 'G' || i == 'T') : (lut[2][i] != 0);
+
+    // site classes of create_query_indices (fastaseq.c:732-777): 1 = idx (segregating), 2 = idx_m (agree, somebody lacks the site)
+    std::vector<uint32_t> idx, idx_m;
+    {
+        const int T = host_threads(std::min<int64_t>(Q, std::max<int64_t>(1, ((int64_t)256 << 20) / ((int64_t)L * 4))));
+        std::vector<uint8_t> first((size_t)T * L, 0), all((size_t)T * L, 1), same((size_t)T * L, 1);
+        parallel_ranges(Q, T, [&](int t, int qa, int qb) {
+            uint8_t *f = &first[(size_t)t * L], *al = &all[(size_t)t * L], *sm = &same[(size_t)t * L];
+            for (int q = qa; q < qb; ++q) {
+                const uint8_t* row = text + (size_t)q * L;
+                for (int i = trim; i < L - trim; ++i) {
+                    const uint8_t ch = up[row[i]];
+                    if (!usable[ch]) { al[i] = 0; continue; }
+                    if (!f[i]) f[i] = ch;
+                    else if (ch != f[i]) sm[i] = 0;
+                }
+            }
+        });
+        for (int i = trim; i < L - trim; ++i) {
+            uint8_t f0 = 0; bool al = true, sm = true;
+            for (int t = 0; t < T; ++t) {
+                const size_t k = (size_t)t * L + i;
+                if (!all[k]) al = false;
+                if (!first[k]) continue;
+                if (!same[k]) sm = false;
+                if (!f0) f0 = first[k];
+                else if (first[k] != f0) sm = false;
+            }
+            if (!f0) continue;
+            if (!sm) idx.push_back((uint32_t)i);
+            else if (!al) idx_m.push_back((uint32_t)i);
+        }
+    }
+    // per query: the bytes at idx (0 where not usable), and bitmaps of the usable sites of idx and of idx_m
+    const size_t n1 = idx.size(), n2 = idx_m.size(), n1p = (n1 + 31) / 32 * 32, w1 = n1p / 64 + 1, w2 = n2 / 64 + 1;
+    std::vector<uint8_t> col((size_t)Q * n1p, 0);
+    std::vector<uint64_t> bm1((size_t)Q * w1, 0), bm2((size_t)Q * w2, 0);
+    const int T = host_threads(Q);
+    parallel_ranges(Q, T, [&](int, int qa, int qb) {
+        for (int q = qa; q < qb; ++q) {
+            const uint8_t* row = text + (size_t)q * L;
+            for (size_t k = 0; k < n1; ++k) {
+                const uint8_t ch = up[row[idx[k]]];
+                if (usable[ch]) { col[(size_t)q * n1p + k] = ch; bm1[(size_t)q * w1 + k / 64] |= 1ull << (k % 64); }
+            }
+            for (size_t k = 0; k < n2; ++k)
+                if (usable[up[row[idx_m[k]]]]) bm2[(size_t)q * w2 + k / 64] |= 1ull << (k % 64);
+        }
+    });
+    auto resolved = [](const uint64_t* a, const uint64_t* b, size_t w) {      // left_is_resolved_right: -1 / 0 / +1, 0xff if both
+        bool left = false, right = false;
+        for (size_t k = 0; k < w; ++k) { left |= (a[k] & ~b[k]) != 0; right |= (~a[k] & b[k]) != 0; }
+        return left && right ? 0xff : left ? -1 : right ? 1 : 0;
+    };
+    std::vector<uint8_t> valid(Q, 1);
+    const int BLOCK = 256;
+    std::vector<std::vector<uint32_t>> cand(BLOCK);
+    for (int i0 = 0; i0 < Q - 1; i0 += BLOCK) {
+        const int i1 = std::min(Q - 1, i0 + BLOCK);
+        const std::vector<uint8_t> snap = valid;                  // rows / columns already out never come back
+        parallel_ranges(i1 - i0, std::min(T, i1 - i0), [&](int, int a, int b) {
+            for (int i = i0 + a; i < i0 + b; ++i) {
+                cand[i - i0].clear();
+                if (!snap[i]) continue;
+                const uint8_t* ri = &col[(size_t)i * n1p];
+                for (int j = i + 1; j < Q; ++j) {
+                    if (!snap[j]) continue;
+                    const uint8_t* rj = &col[(size_t)j * n1p];
+                    bool differ = false;
+                    for (size_t k = 0; k < n1p && !differ; k += 32) {
+                        uint8_t acc = 0;
+                        for (int u = 0; u < 32; ++u) acc |= (uint8_t)((ri[k + u] != 0) & (rj[k + u] != 0) & (ri[k + u] != rj[k + u]));
+                        differ = acc != 0;
+                    }
+                    if (!differ) cand[i - i0].push_back((uint32_t)j);
+                }
+            }
+        });
+        for (int i = i0; i < i1; ++i) for (uint32_t j : cand[i - i0]) {
+            if (!valid[i] || !valid[j]) continue;
+            int red1 = resolved(&bm1[(size_t)i * w1], &bm1[(size_t)j * w1], w1);
+            if (red1 > 1) continue;                                // both hold sites the other lacks: not equivalent
+            const int red2 = resolved(&bm2[(size_t)i * w2], &bm2[(size_t)j * w2], w2);
+            if (red2 > 1) continue;
+            if (!red1 && !red2) valid[j] = 0;                      // identical, gaps and Ns included
+            red1 += red2;
+            if (!red1) continue;                                   // opposite signs: complementary information
+            if (keep_more_resolved) { if (red1 > 0) valid[i] = 0; else valid[j] = 0; }
+            else                    { if (red1 > 0) valid[j] = 0; else valid[i] = 0; }
+        }
+    }
+    int32_t n = 0;
+    for (int q = 0; q < Q; ++q) { keep[q] = valid[q]; n += valid[q]; }
+    if (n_kept) *n_kept = n;
+    return UVG_OK;
+}
+
 extern "C" int uvg_reset_search(uvg_ctx* c)
 {
     if (!c) return UVG_EINVAL;
@@ -871,6 +987,147 @@ extern "C" int uvg_clear_refs(uvg_ctx* c)
 }
 
 extern "C" int64_t uvg_db_count(const uvg_ctx* c) { return c ? c->db_n : 0; }
+
+
+// =====================================================================================================================
+// packed reference cache: the resident packed references leave / enter the device as they are, so a
+// host that searched a FASTA file once can keep the 3 bits per site the encoder made of it (planes + ambiguity lists +
+// non_n) and skip reading, parsing and encoding the text next time: 0.375 bytes per site cross PCIe instead of 1.
+// Blob: header | planes of whole groups of 32 references | non_n[n] | ambiguity offsets [n+1] (relative) | entries.
+// =====================================================================================================================
+namespace {
+struct PackedHeader {
+    char magic[8];
+    int32_t version, nchar, Wp, acgt_mode;
+    int64_t n_refs, n_amb;
+    uint64_t planes_bytes, reserved[2];
+};
+static_assert(sizeof(PackedHeader) == 64, "packed header is 64 bytes");
+const char PACKED_MAGIC[8] = {'U', 'V', 'G', 'P', 'A', 'C', 'K', '1'};
+inline size_t pad16(size_t b) { return (b + 15) / 16 * 16; }
+struct PackedLayout { size_t planes, non_n, off, ent, total; };
+inline PackedLayout packed_layout(int Wp, int64_t n, int64_t n_amb)
+{
+    PackedLayout l;
+    l.planes = (size_t)((n + GROUP - 1) / GROUP) * (size_t)(Wp / 4) * NPLANE * GROUP * sizeof(uint4);
+    l.non_n = pad16((size_t)n * 4); l.off = pad16((size_t)(n + 1) * 4); l.ent = pad16((size_t)n_amb * 4);
+    l.total = sizeof(PackedHeader) + l.planes + l.non_n + l.off + l.ent;
+    return l;
+}
+}  // namespace
+
+static int packed_range(uvg_ctx* c, int64_t first, int64_t n, uint32_t* amb_begin, uint32_t* amb_end, const char* who)
+{
+    if (first < 0 || n < 1 || first + n > c->db_n) UVG_FAIL(c, UVG_EINVAL, "%s: references [%lld, %lld) are not resident (%lld are)", who,
+                                                            (long long)first, (long long)(first + n), (long long)c->db_n);
+    if (first % GROUP) UVG_FAIL(c, UVG_EINVAL, "%s: the first reference must be a multiple of %d", who, GROUP);
+    UVG_CUDA(c, cudaStreamSynchronize(c->st_push));
+    UVG_CUDA(c, cudaMemcpy(amb_begin, c->d_ramb_off + first, 4, cudaMemcpyDeviceToHost));
+    UVG_CUDA(c, cudaMemcpy(amb_end, c->d_ramb_off + first + n, 4, cudaMemcpyDeviceToHost));
+    return UVG_OK;
+}
+
+extern "C" int uvg_packed_bytes(uvg_ctx* c, int64_t first, int64_t n, size_t* bytes)
+{
+    if (!c || !bytes) { if (c) c->err = "uvg_packed_bytes: bad arguments"; return UVG_EINVAL; }
+    UVG_CUDA(c, cudaSetDevice(c->prm.device));
+    uint32_t a = 0, b = 0;
+    int rc = packed_range(c, first, n, &a, &b, "uvg_packed_bytes");
+    if (rc) return rc;
+    *bytes = packed_layout(c->Wp, n, (int64_t)b - a).total;
+    return UVG_OK;
+}
+
+extern "C" int uvg_export_packed(uvg_ctx* c, int64_t first, int64_t n, void* blob, size_t capacity)
+{
+    if (!c || !blob) { if (c) c->err = "uvg_export_packed: bad arguments"; return UVG_EINVAL; }
+    UVG_CUDA(c, cudaSetDevice(c->prm.device));
+    uint32_t a = 0, b = 0;
+    int rc = packed_range(c, first, n, &a, &b, "uvg_export_packed");
+    if (rc) return rc;
+    const int64_t n_amb = (int64_t)b - a;
+    const PackedLayout l = packed_layout(c->Wp, n, n_amb);
+    if (capacity < l.total) UVG_FAIL(c, UVG_EINVAL, "uvg_export_packed: the blob needs %zu bytes, %zu given", l.total, capacity);
+    uint8_t* out = static_cast<uint8_t*>(blob);
+    PackedHeader h{};
+    memcpy(h.magic, PACKED_MAGIC, 8);
+    h.version = 1; h.nchar = c->nchar; h.Wp = c->Wp; h.acgt_mode = c->prm.acgt_mode != 0; h.n_refs = n; h.n_amb = n_amb; h.planes_bytes = l.planes;
+    memcpy(out, &h, sizeof h);
+    uint8_t* planes = out + sizeof h;
+    uint8_t* non_n = planes + l.planes;
+    uint32_t* off = reinterpret_cast<uint32_t*>(non_n + l.non_n);
+    uint8_t* ent = reinterpret_cast<uint8_t*>(off) + l.off;
+    const size_t per_group = (size_t)(c->Wp / 4) * NPLANE * GROUP;                    // uint4 per group
+    cudaStream_t sp = c->st_push;
+    UVG_CUDA(c, cudaMemcpyAsync(planes, c->d_db + (size_t)(first / GROUP) * per_group, l.planes, cudaMemcpyDeviceToHost, sp));
+    memset(non_n + (size_t)n * 4, 0, l.non_n - (size_t)n * 4);
+    UVG_CUDA(c, cudaMemcpyAsync(non_n, c->d_non_n + first, (size_t)n * 4, cudaMemcpyDeviceToHost, sp));
+    memset(reinterpret_cast<uint8_t*>(off) + (size_t)(n + 1) * 4, 0, l.off - (size_t)(n + 1) * 4);
+    UVG_CUDA(c, cudaMemcpyAsync(off, c->d_ramb_off + first, (size_t)(n + 1) * 4, cudaMemcpyDeviceToHost, sp));
+    if (l.ent) memset(ent + (size_t)n_amb * 4, 0, l.ent - (size_t)n_amb * 4);
+    if (n_amb) UVG_CUDA(c, cudaMemcpyAsync(ent, c->d_ramb_ent + a, (size_t)n_amb * 4, cudaMemcpyDeviceToHost, sp));
+    UVG_CUDA(c, cudaStreamSynchronize(sp));
+    for (int64_t i = 0; i <= n; ++i) off[i] -= a;
+    if (n % GROUP) {                                                                  // lanes above the range: whatever was there before
+        uint4* g = reinterpret_cast<uint4*>(planes) + (size_t)(n / GROUP) * per_group;
+        for (size_t u = 0; u < per_group; u += GROUP)
+            for (int lane = (int)(n % GROUP); lane < GROUP; ++lane) g[u + lane] = make_uint4(0, 0, 0, 0);
+    }
+    return UVG_OK;
+}
+
+extern "C" int uvg_import_packed(uvg_ctx* c, const void* blob, size_t bytes, int64_t* n_refs)
+{
+    if (!c || !blob || bytes < sizeof(PackedHeader)) { if (c) c->err = "uvg_import_packed: bad arguments"; return UVG_EINVAL; }
+    UVG_CUDA(c, cudaSetDevice(c->prm.device));
+    PackedHeader h;
+    memcpy(&h, blob, sizeof h);
+    if (memcmp(h.magic, PACKED_MAGIC, 8) || h.version != 1) UVG_FAIL(c, UVG_EINVAL, "uvg_import_packed: not a packed reference blob (magic / version)");
+    if (h.nchar != c->nchar || h.Wp != c->Wp || h.acgt_mode != (c->prm.acgt_mode != 0))
+        UVG_FAIL(c, UVG_EINVAL, "uvg_import_packed: the blob was made for nchar %d, acgt_mode %d; this context has nchar %d, acgt_mode %d",
+                 h.nchar, h.acgt_mode, c->nchar, (int)(c->prm.acgt_mode != 0));
+    if (h.n_refs < 1 || h.n_amb < 0) UVG_FAIL(c, UVG_EINVAL, "uvg_import_packed: corrupt header");
+    const int64_t n = h.n_refs, n_amb = h.n_amb;
+    const PackedLayout l = packed_layout(c->Wp, n, n_amb);
+    if (l.planes != h.planes_bytes || bytes < l.total) UVG_FAIL(c, UVG_EINVAL, "uvg_import_packed: truncated blob (%zu bytes, %zu expected)", bytes, l.total);
+    if (c->db_n % GROUP) UVG_FAIL(c, UVG_ESTATE, "uvg_import_packed: %lld references are resident; packed blobs append at multiples of %d",
+                                  (long long)c->db_n, GROUP);
+    const uint8_t* planes = static_cast<const uint8_t*>(blob) + sizeof h;
+    const uint8_t* non_n = planes + l.planes;
+    const uint32_t* off = reinterpret_cast<const uint32_t*>(non_n + l.non_n);
+    const uint8_t* ent = reinterpret_cast<const uint8_t*>(off) + l.off;
+    if (off[0] != 0 || off[n] != (uint32_t)n_amb) UVG_FAIL(c, UVG_EINVAL, "uvg_import_packed: corrupt ambiguity offsets");
+    int rc = ensure_db_capacity(c, c->db_n + n);
+    if (rc) return rc;
+    rc = ensure_amb_capacity(c, c->amb_n + n_amb);
+    if (rc) return rc;
+    cudaStream_t sp = c->st_push;
+    UVG_CUDA(c, cudaEventRecord(c->ev_c, sp));
+    const size_t per_group = (size_t)(c->Wp / 4) * NPLANE * GROUP;
+    UVG_CUDA(c, cudaMemcpyAsync(c->d_db + (size_t)(c->db_n / GROUP) * per_group, planes, l.planes, cudaMemcpyHostToDevice, sp));
+    UVG_CUDA(c, cudaMemcpyAsync(c->d_non_n + c->db_n, non_n, (size_t)n * 4, cudaMemcpyHostToDevice, sp));
+    std::vector<uint32_t> abs_off((size_t)n + 1);
+    for (int64_t i = 0; i <= n; ++i) {
+        if (i && off[i] < off[i - 1]) UVG_FAIL(c, UVG_EINVAL, "uvg_import_packed: corrupt ambiguity offsets");
+        abs_off[i] = off[i] + (uint32_t)c->amb_n;
+    }
+    UVG_CUDA(c, cudaMemcpyAsync(c->d_ramb_off + c->db_n, abs_off.data(), (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, sp));
+    if (n_amb) UVG_CUDA(c, cudaMemcpyAsync(c->d_ramb_ent + c->amb_n, ent, (size_t)n_amb * 4, cudaMemcpyHostToDevice, sp));
+    if (c->pivot_on) {
+        UVG_CUDA(c, cudaMemsetAsync(c->d_ref_cnt + c->db_n, 0, (size_t)n * 4, sp));
+        UVG_CUDA(c, cudaMemsetAsync(c->d_ref_cnt + c->db2_cap + c->db_n, 0, (size_t)n * 4, sp));
+        UVG_CUDA(c, launch_derive_pivot(c->d_db, c->d_db2, c->d_pivot, c->d_ref_cnt, c->d_ref_cnt + c->db2_cap, c->db_n, c->db_n + n, c->Wp, sp));
+        c->stats.other_kernel_launches += 1;
+    }
+    UVG_CUDA(c, cudaEventRecord(c->ev_d, sp));
+    UVG_CUDA(c, cudaEventSynchronize(c->ev_d));                                       // the caller may reuse the blob
+    float ms = 0; cudaEventElapsedTime(&ms, c->ev_c, c->ev_d);
+    c->stats.encode_ms = ms;
+    c->db_n += n;
+    c->amb_n += n_amb;
+    if (n_refs) *n_refs = n;
+    return UVG_OK;
+}
 
 // =====================================================================================================================
 // search: rounds of K2 (pair counts -> score tiles of the owners) and K3 (exact replay)

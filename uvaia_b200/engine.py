@@ -21,6 +21,21 @@ class UvgError(RuntimeError):
     pass
 
 
+def prune_queries(text: np.ndarray, trim=0, acgt=False, keep_more_resolved=True):
+    """-k / --keep_resolved (exclude_redundant_query_sequences, src/fastaseq.c:797-841): boolean mask of the ordered
+    query rows that stay; the caller passes text[mask] to Engine.set_queries (nearest.c:219-224)."""
+    text = np.ascontiguousarray(text, dtype=np.uint8)
+    assert text.ndim == 2
+    keep = np.empty(text.shape[0], np.uint8)
+    n = C.c_int32(0)
+    rc = _capi.lib().uvg_prune_queries(text.ctypes.data, text.shape[0], text.shape[1], int(trim), int(bool(acgt)),
+                                       int(bool(keep_more_resolved)), keep.ctypes.data, C.byref(n))
+    if rc != 0:
+        raise UvgError(f"uvg_prune_queries failed ({rc})")
+    assert int(keep.sum()) == n.value
+    return keep.astype(bool)
+
+
 class Engine:
     def __init__(self, nchar, nbest=100, trim=0, acgt=False, pool=512, device=0, first_round=0, max_round=0,
                  early_abort=False, rank=0, world=1, db_capacity=0, pair_kernel=None):

@@ -12,7 +12,7 @@ import lzma
 
 import numpy as np
 
-from .engine import Engine
+from .engine import Engine, prune_queries
 
 HEADER_FULL = ("query,reference,rank,ACGT_matches,text_matches,partial_matches,valid_pair_comparisons,"
                "ACGT_matches_unique,valid_ref_sites")          # src/nearest.c:525
@@ -126,7 +126,7 @@ class SearchOutput:
 
 
 def search_files(query_file, ref_files, nbest=100, trim=0, acgt=False, ambig_q=0.5, ambig_r=0.5, pool=512, exclude_self=False,
-                 batch_rows=4096, device=0, **engine_kw):
+                 keep_resolved=False, batch_rows=4096, device=0, **engine_kw):
     """End-to-end `uvaia` run (nearest.c:159-353) with scoring and heaps on the GPU.  Returns a SearchOutput."""
     ambig_q = min(1.0, max(0.001, ambig_q))                     # nearest.c:175-178
     ambig_r = min(1.0, max(0.001, ambig_r))
@@ -144,10 +144,14 @@ def search_files(query_file, ref_files, nbest=100, trim=0, acgt=False, ambig_q=0
     Q = np.ascontiguousarray(Q[order])
     names = [names[i] for i in order]
     out = SearchOutput()
-    out.qnames = names
-    qset = set(names) if exclude_self else None
     min_non_n = int(L * (1.0 - ambig_r))                        # nearest.c:237
     with Engine(L, nbest=nbest, trim=trim, acgt=acgt, pool=pool, device=device, **engine_kw) as eng:
+        if keep_resolved:                                        # nearest.c:219-224
+            mask = prune_queries(Q, trim, acgt, True)
+            Q = np.ascontiguousarray(Q[mask])
+            names = [nm for nm, k in zip(names, mask) if k]
+        out.qnames = names
+        qset = set(names) if exclude_self else None             # nearest.c:226-230 (after the pruning)
         out.info = eng.set_queries(Q)
         for rf in ref_files:
             buf_names, buf_rows = [], []
