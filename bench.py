@@ -61,6 +61,7 @@ def parse_args():
     ap.add_argument("--max-round", type=int, default=0)
     ap.add_argument("--pair-kernel", default="auto", choices=["auto", "general", "pivot"])
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-packed", action="store_true", help="skip the packed-cache variant of the e2e leg")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-refs", type=int, default=3000, help="references in the bounded CPU-baseline sample")
@@ -395,6 +396,50 @@ def main():
                "d2h_bytes_per_step": int(world * Q * ((args.nbest + 1) * 32 + 8)), "seconds_per_step": e2e_s,
                "same_result_as_resident_run": chk2 == checksum, "last_step_breakdown": e2e_parts}
         eng._lib.uvg_host_free_pinned(host_buf)
+        if world == 1 and not args.no_packed:
+            # same search fed from the packed reference cache (uvg_export_packed once, outside the timed region; what a
+            # host keeps in a .uvg file): the host pushes 0.375 bytes per site and the encoder does not run
+            import ctypes as C
+            piece = 65536
+            sizes = []
+            for s0 in range(0, n_local, piece):
+                nb = C.c_size_t(0)
+                eng._ck(eng._lib.uvg_packed_bytes(eng._h, s0, min(piece, n_local - s0), C.byref(nb)), "uvg_packed_bytes")
+                sizes.append(nb.value)
+            blob_buf = eng._lib.uvg_host_alloc_pinned(sum(sizes))
+            if blob_buf:
+                o = 0
+                for k, s0 in enumerate(range(0, n_local, piece)):
+                    eng._ck(eng._lib.uvg_export_packed(eng._h, s0, min(piece, n_local - s0), blob_buf + o, sizes[k]), "uvg_export_packed")
+                    o += sizes[k]
+                pk_t = []
+                for i in range(1 + args.e2e_steps):
+                    barrier()
+                    t1 = time.perf_counter()
+                    eng.clear_refs()
+                    eng.set_queries(qtext)
+                    t_sq = time.perf_counter() - t1
+                    o, t_imp = 0, 0.0
+                    for k in range(len(sizes)):
+                        t2 = time.perf_counter()
+                        eng.import_packed((blob_buf + o, sizes[k]))
+                        t_imp += time.perf_counter() - t2
+                        eng.search_async()
+                        o += sizes[k]
+                    t2 = time.perf_counter()
+                    eng.wait()
+                    t_wait = time.perf_counter() - t2
+                    heaps = eng.heaps()
+                    barrier()
+                    if i > 0:
+                        pk_t.append(time.perf_counter() - t1)
+                        pk_parts = {"set_queries_s": t_sq, "import_s": t_imp, "wait_s": t_wait, "tables_d2h_s": time.perf_counter() - t2 - t_wait}
+                chk3 = int(sum(int(sc.astype(np.int64).sum()) + int(r.sum()) for sc, r in heaps) & 0xffffffffffff)
+                pk_s = float(np.mean(pk_t))
+                e2e["packed_cache"] = {"value": Q / pk_s, "unit": "queries/s", "h2d_bytes_per_step": int(Q * L + sum(sizes)),
+                                       "seconds_per_step": pk_s, "same_result_as_resident_run": chk3 == checksum, "last_step_breakdown": pk_parts,
+                                       "note": "references enter as the packed blobs of uvg_export_packed (pinned host memory) instead of text"}
+                eng._lib.uvg_host_free_pinned(blob_buf)
 
     # ---- roofline of the dominant kernel (k_paircount) ----
     peaks = load_peaks()

@@ -50,6 +50,9 @@ SYMBOLS = {
     "uvg_prune_queries": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, C.POINTER(C.c_int32)]),
     "uvg_push_refs": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P, _P, C.POINTER(C.c_int64)]),
     "uvg_push_refs_device": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P, _P, C.POINTER(C.c_int64)]),
+    "uvg_packed_bytes": (C.c_int, [_P, C.c_int64, C.c_int64, C.POINTER(C.c_size_t)]),
+    "uvg_export_packed": (C.c_int, [_P, C.c_int64, C.c_int64, _P, C.c_size_t]),
+    "uvg_import_packed": (C.c_int, [_P, _P, C.c_size_t, C.POINTER(C.c_int64)]),
     "uvg_drop_refs": (C.c_int, [_P]),
     "uvg_clear_refs": (C.c_int, [_P]),
     "uvg_db_count": (C.c_int64, [_P]),

@@ -123,6 +123,29 @@ class Engine:
                  "uvg_push_refs_device")
         return na.value
 
+    # ---- packed reference cache ----
+    def export_packed(self, first=0, n=None, out=None) -> np.ndarray:
+        """the resident packed references [first, first+n) as one relocatable blob (uint8 array); `out` may be a
+        preallocated (e.g. pinned) uint8 array"""
+        n = self.db_count - first if n is None else n
+        nb = C.c_size_t(0)
+        self._ck(self._lib.uvg_packed_bytes(self._h, int(first), int(n), C.byref(nb)), "uvg_packed_bytes")
+        blob = np.empty(nb.value, np.uint8) if out is None else out[:nb.value]
+        assert blob.size == nb.value and blob.flags.c_contiguous
+        self._ck(self._lib.uvg_export_packed(self._h, int(first), int(n), blob.ctypes.data, blob.size), "uvg_export_packed")
+        return blob
+
+    def import_packed(self, blob) -> int:
+        """append a blob made by export_packed (uint8 array or a raw (address, bytes) pair); -> references appended"""
+        n = C.c_int64(0)
+        if isinstance(blob, tuple):
+            addr, size = blob
+        else:
+            blob = np.ascontiguousarray(blob, dtype=np.uint8)
+            addr, size = blob.ctypes.data, blob.size
+        self._ck(self._lib.uvg_import_packed(self._h, addr, size, C.byref(n)), "uvg_import_packed")
+        return n.value
+
     def drop_refs(self):
         self._ck(self._lib.uvg_drop_refs(self._h), "uvg_drop_refs")
 
