@@ -361,6 +361,77 @@ static void* stream_reader(void* arg)
 }
 
 /* ---------------------------------------------------------------------------------------------------------------
+ * --cache FILE: the packed references of a run (uvg_export_packed blobs + names + which FASTA records were accepted),
+ * so that the next run over the same reference files skips reading, parsing and encoding them.  Layout (host endian):
+ *   "UVGCACHE" u32 version, i32 nchar, i32 acgt, i32 min_non_n, i32 n_files, i32 pad; per file: u64 size, i64 mtime
+ *   records: u64 tag (1 blob, 2 record map, 3 end) ...
+ *     blob:       u64 blob_bytes, u64 n_refs, u64 names_bytes, blob, names (NUL terminated each), padding to 8
+ *     record map: u64 n_rec, i64 count, i64 n_invalid, rec_ok[n_rec], padding to 8
+ * A cache is used only if nchar, mode, the -A threshold and the size and mtime of every -r file match; not with -x (the
+ * set of pushed references then depends on the query names).
+ * ------------------------------------------------------------------------------------------------------------- */
+#include <sys/stat.h>
+#define CACHE_VERSION 1u
+typedef struct { FILE* fp; char* path; char* tmp; void* buf; size_t buf_cap; int64_t exported, base; } cache_writer_t;
+
+static void cache_put(FILE* fp, const void* p, size_t n) { if (n && fwrite(p, 1, n, fp) != n) die("cannot write the cache file"); }
+static void cache_pad8(FILE* fp, size_t n) { static const char z[8] = {0}; if (n % 8) cache_put(fp, z, 8 - n % 8); }
+static int cache_get(FILE* fp, void* p, size_t n) { return !n || fread(p, 1, n, fp) == n; }
+
+static void cache_header(FILE* fp, int nchar, int acgt, int min_non_n, const char** file, int n_files)
+{
+    const uint32_t ver = CACHE_VERSION; const int32_t v[5] = {nchar, acgt, min_non_n, n_files, 0};
+    cache_put(fp, "UVGCACHE", 8); cache_put(fp, &ver, 4); cache_put(fp, v, sizeof v);
+    for (int j = 0; j < n_files; ++j) {
+        struct stat sb;
+        if (stat(file[j], &sb)) die("cannot stat %s", file[j]);
+        const uint64_t size = (uint64_t)sb.st_size; const int64_t mtime = (int64_t)sb.st_mtime;
+        cache_put(fp, &size, 8); cache_put(fp, &mtime, 8);
+    }
+}
+/* -> open file positioned at the first record, or NULL when there is no usable cache */
+static FILE* cache_open_valid(const char* path, int nchar, int acgt, int min_non_n, const char** file, int n_files)
+{
+    FILE* fp = fopen(path, "rb");
+    if (!fp) return NULL;
+    char magic[8]; uint32_t ver = 0; int32_t v[5];
+    int ok = cache_get(fp, magic, 8) && !memcmp(magic, "UVGCACHE", 8) && cache_get(fp, &ver, 4) && ver == CACHE_VERSION && cache_get(fp, v, sizeof v)
+             && v[0] == nchar && v[1] == acgt && v[2] == min_non_n && v[3] == n_files;
+    for (int j = 0; ok && j < n_files; ++j) {
+        struct stat sb; uint64_t size; int64_t mtime;
+        ok = cache_get(fp, &size, 8) && cache_get(fp, &mtime, 8) && !stat(file[j], &sb) && (uint64_t)sb.st_size == size && (int64_t)sb.st_mtime == mtime;
+    }
+    if (!ok) { fclose(fp); return NULL; }
+    return fp;
+}
+/* export the resident references that are not in the file yet: whole groups of 32, everything when `final` (before a
+ * drop and at the end of the stream; the reader then drops at the same place) */
+static void cache_flush(cache_writer_t* cw, uvg_ctx* gpu, char** rname, int final)
+{
+    if (!cw->fp) return;
+    const int64_t db_n = uvg_db_count(gpu), hi = final ? db_n : db_n / 32 * 32;
+    if (hi > cw->exported) {
+        const int64_t first = cw->exported, n = hi - first;
+        size_t bytes = 0;
+        if (uvg_packed_bytes(gpu, first, n, &bytes)) die("%s", uvg_last_error(gpu));
+        if (bytes > cw->buf_cap) {
+            uvg_host_free_pinned(cw->buf);
+            cw->buf_cap = bytes + bytes / 8; cw->buf = uvg_host_alloc_pinned(cw->buf_cap);
+            if (!cw->buf) die("cannot allocate %zu bytes of pinned memory", cw->buf_cap);
+        }
+        if (uvg_export_packed(gpu, first, n, cw->buf, cw->buf_cap)) die("%s", uvg_last_error(gpu));
+        uint64_t names_bytes = 0;
+        for (int64_t i = 0; i < n; ++i) names_bytes += strlen(rname[cw->base + first + i]) + 1;
+        const uint64_t rec[4] = {1, bytes, (uint64_t)n, names_bytes};
+        cache_put(cw->fp, rec, sizeof rec); cache_put(cw->fp, cw->buf, bytes);
+        for (int64_t i = 0; i < n; ++i) { const char* nm = rname[cw->base + first + i]; cache_put(cw->fp, nm, strlen(nm) + 1); }
+        cache_pad8(cw->fp, names_bytes);
+        cw->exported = hi;
+    }
+    if (final) { cw->base += db_n; cw->exported = 0; }
+}
+
+/* ---------------------------------------------------------------------------------------------------------------
  * main: nearest.c:159-353
  * ------------------------------------------------------------------------------------------------------------- */
 static void usage(const char* prog, int full)
@@ -380,13 +451,16 @@ static void usage(const char* prog, int full)
            "  -r, --reference        aligned reference sequences (can be several files)\n"
            "  -t, --nthreads         accepted for compatibility (scoring runs on the GPU)\n"
            "  -o, --output           prefix of xzipped output alignment and table with nearest neighbour sequences\n"
-           "      --device           CUDA device ordinal (default 0);  --batch: reference rows per push (default 65536)\n");
+           "      --device           CUDA device ordinal (default 0);  --batch: reference rows per push (default 65536)\n"
+           "      --cache            file that keeps the packed references of this run; a later run over the same reference\n"
+           "                         files (same size and mtime, same -A, same mode) reads it instead of parsing them\n");
 }
 
 int main(int argc, char** argv)
 {
     int nbest = 100, trim = 0, acgt = 0, xclude = 0, pool = 0, device = 0, hires = 0;
     long batch_rows = 65536, max_resident = 1 << 20;
+    const char* cache_path = NULL;
     double ambig_q = 0.5, ambig_r = 0.5;
     const char* out_prefix = NULL;
     const char* ref_file[1024]; int n_ref_files = 0;
@@ -394,7 +468,7 @@ int main(int argc, char** argv)
         {"help", 0, 0, 'h'}, {"version", 0, 0, 'v'}, {"acgt", 0, 0, 1000}, {"keep_resolved", 0, 0, 'k'}, {"exclude_self", 0, 0, 'x'},
         {"nbest", 1, 0, 'n'}, {"trim", 1, 0, 1001}, {"query_ambiguity", 1, 0, 'a'}, {"ref_ambiguity", 1, 0, 'A'}, {"pool", 1, 0, 'p'},
         {"reference", 1, 0, 'r'}, {"nthreads", 1, 0, 't'}, {"output", 1, 0, 'o'}, {"device", 1, 0, 1002}, {"batch", 1, 0, 1003},
-        {"max_resident", 1, 0, 1004}, {0, 0, 0, 0}};
+        {"max_resident", 1, 0, 1004}, {"cache", 1, 0, 1005}, {0, 0, 0, 0}};
     int ch;
     while ((ch = getopt_long(argc, argv, "hvkxn:a:A:p:r:t:o:", lo, NULL)) != -1) {
         switch (ch) {
@@ -414,6 +488,7 @@ int main(int argc, char** argv)
         case 1002: device = atoi(optarg); break;
         case 1003: batch_rows = atol(optarg); break;
         case 1004: max_resident = atol(optarg); break;
+        case 1005: cache_path = optarg; break;
         default: usage(argv[0], 0); return EXIT_FAILURE;
         }
     }
@@ -474,48 +549,123 @@ int main(int argc, char** argv)
      * batch i and the scoring rounds of batch i-1 overlap. */
     const int min_non_n = (int)(L * (1.0 - ambig_r));                           /* nearest.c:237 */
     if (batch_rows > ((long)1 << 30) / L) batch_rows = (((long)1 << 30) / L) > 0 ? ((long)1 << 30) / L : 1;
-    stream_t sp;
-    memset(&sp, 0, sizeof sp);
-    sp.file = ref_file; sp.n_files = n_ref_files; sp.L = L; sp.min_non_n = min_non_n; sp.batch_rows = batch_rows;
-    sp.qset = xclude ? &qset : NULL; sp.t0 = t0;
-    for (int k = 0; k < 2; ++k) {
-        sp.batch[k].text = uvg_host_alloc_pinned((size_t)batch_rows * L);
-        if (!sp.batch[k].text) die("cannot allocate %zu bytes of pinned memory", (size_t)batch_rows * L);
-        sp.batch[k].name = xmalloc(batch_rows * sizeof(char*));
-    }
-    sem_init(&sp.free_slots, 0, 2);
-    sem_init(&sp.full_slots, 0, 0);
-    pthread_t reader;
-    if (pthread_create(&reader, NULL, stream_reader, &sp)) die("cannot start the reader thread");
     uint8_t* accepted = xmalloc(batch_rows);
     char** rname = NULL; int64_t n_acc_total = 0, rname_cap = 0;                /* names of the accepted references, by ordinal */
     uint8_t* push_ok = NULL; int64_t n_pushed = 0, push_cap = 0;                /* per pushed row, in stream order: accepted by the filter */
-    long n_invalid = 0;
-    for (int k = 0;; k ^= 1) {
-        sem_wait(&sp.full_slots);
-        batch_t* bt = &sp.batch[k];
-        if (bt->n > 0) {
-            int64_t na = 0;
-            if (uvg_push_refs(gpu, bt->text, bt->n, min_non_n, NULL, accepted, &na)) die("%s", uvg_last_error(gpu));
-            if (n_acc_total + na > rname_cap) { rname_cap = 2 * (n_acc_total + na) + 1024; rname = xrealloc(rname, rname_cap * sizeof *rname); }
-            if (n_pushed + bt->n > push_cap) { push_cap = 2 * (n_pushed + bt->n) + 1024; push_ok = xrealloc(push_ok, push_cap); }
-            for (long i = 0; i < bt->n; ++i) {
-                push_ok[n_pushed++] = accepted[i];
-                if (accepted[i]) rname[n_acc_total++] = bt->name[i]; else { free(bt->name[i]); ++n_invalid; }
-            }
-            if (uvg_search_async(gpu)) die("%s", uvg_last_error(gpu));
-            if (uvg_db_count(gpu) >= max_resident) { if (uvg_wait(gpu) || uvg_drop_refs(gpu)) die("%s", uvg_last_error(gpu)); }
+    long n_invalid = 0, count = 0, same_name = 0;
+    uint8_t* rec_ok = NULL; int64_t n_rec = 0;
+    void* pinned_text[2] = {NULL, NULL}; char** batch_names[2] = {NULL, NULL};
+    FILE* cache_in = NULL;
+    cache_writer_t cw;
+    memset(&cw, 0, sizeof cw);
+    if (cache_path && xclude) { fprintf(stderr, "Note: --cache is ignored with -x (the references that are pushed depend on the query names).\n"); cache_path = NULL; }
+    if (cache_path) {
+        cache_in = cache_open_valid(cache_path, L, acgt, min_non_n, ref_file, n_ref_files);
+        if (cache_in) fprintf(stderr, "Packed references are read from the cache %s; the reference files are not parsed.\n", cache_path);
+        else {
+            cw.path = xmalloc(strlen(cache_path) + 1); strcpy(cw.path, cache_path);
+            cw.tmp = xmalloc(strlen(cache_path) + 8); sprintf(cw.tmp, "%s.tmp", cache_path);
+            cw.fp = fopen(cw.tmp, "wb");
+            if (!cw.fp) die("cannot write the cache file %s", cw.tmp);
+            setvbuf(cw.fp, NULL, _IOFBF, 8 << 20);
+            cache_header(cw.fp, L, acgt, min_non_n, ref_file, n_ref_files);
+            fprintf(stderr, "Packed references will be saved to the cache %s.\n", cache_path);
         }
-        const int last = bt->last;
-        sem_post(&sp.free_slots);
-        if (last) break;
     }
-    pthread_join(reader, NULL);
-    n_invalid += sp.n_invalid;
-    const long count = sp.count, same_name = sp.same_name;
-    /* per streamed record: 1 = accepted reference (the second pass for the .aln dump needs it) */
-    uint8_t* rec_ok = sp.rec_state; const int64_t n_rec = sp.n_rec;
-    { int64_t k = 0; for (int64_t i = 0; i < n_rec; ++i) rec_ok[i] = rec_ok[i] == 2 ? push_ok[k++] : 0; }
+    if (cache_in) {
+        /* cached run: blob -> pinned buffer -> uvg_import_packed -> rounds; the next blob is read under them */
+        void* buf = NULL; size_t buf_cap = 0;
+        for (;;) {
+            uint64_t tag = 0;
+            if (!cache_get(cache_in, &tag, 8)) die("the cache file %s is truncated (delete it)", cache_path);
+            if (tag == 3) break;
+            if (tag == 1) {
+                uint64_t h[3];
+                if (!cache_get(cache_in, h, sizeof h)) die("the cache file %s is truncated (delete it)", cache_path);
+                const size_t bytes = h[0], names_bytes = h[2]; const int64_t n = (int64_t)h[1];
+                if (bytes > buf_cap) {
+                    uvg_host_free_pinned(buf);
+                    buf_cap = bytes + bytes / 8; buf = uvg_host_alloc_pinned(buf_cap);
+                    if (!buf) die("cannot allocate %zu bytes of pinned memory", buf_cap);
+                }
+                char* names = xmalloc(names_bytes + 8);
+                if (!cache_get(cache_in, buf, bytes) || !cache_get(cache_in, names, (names_bytes + 7) / 8 * 8)) die("the cache file %s is truncated (delete it)", cache_path);
+                if (n_acc_total + n > rname_cap) { rname_cap = 2 * (n_acc_total + n) + 1024; rname = xrealloc(rname, rname_cap * sizeof *rname); }
+                const char* nm = names;
+                for (int64_t i = 0; i < n; ++i) {
+                    const size_t len = strlen(nm);
+                    rname[n_acc_total] = xmalloc(len + 1); memcpy(rname[n_acc_total++], nm, len + 1);
+                    nm += len + 1;
+                }
+                free(names);
+                int64_t got = 0;
+                if (uvg_import_packed(gpu, buf, bytes, &got) || got != n) die("%s", uvg_last_error(gpu));
+                if (uvg_search_async(gpu)) die("%s", uvg_last_error(gpu));
+                if (n % 32 || uvg_db_count(gpu) >= max_resident) { if (uvg_wait(gpu) || uvg_drop_refs(gpu)) die("%s", uvg_last_error(gpu)); }
+            } else if (tag == 2) {
+                uint64_t nr = 0; int64_t v[2];
+                if (!cache_get(cache_in, &nr, 8) || !cache_get(cache_in, v, sizeof v)) die("the cache file %s is truncated (delete it)", cache_path);
+                n_rec = (int64_t)nr; count = (long)v[0]; n_invalid = (long)v[1];
+                rec_ok = xmalloc((nr + 7) / 8 * 8 + 8);
+                if (!cache_get(cache_in, rec_ok, (nr + 7) / 8 * 8)) die("the cache file %s is truncated (delete it)", cache_path);
+            } else die("the cache file %s is corrupt (delete it)", cache_path);
+        }
+        fclose(cache_in);
+        uvg_host_free_pinned(buf);
+        fprintf(stderr, "Finished reading the cache %s in %.3lf secs;\n", cache_path, now_s() - t0);
+    } else {
+        stream_t sp;
+        memset(&sp, 0, sizeof sp);
+        sp.file = ref_file; sp.n_files = n_ref_files; sp.L = L; sp.min_non_n = min_non_n; sp.batch_rows = batch_rows;
+        sp.qset = xclude ? &qset : NULL; sp.t0 = t0;
+        for (int k = 0; k < 2; ++k) {
+            sp.batch[k].text = uvg_host_alloc_pinned((size_t)batch_rows * L);
+            if (!sp.batch[k].text) die("cannot allocate %zu bytes of pinned memory", (size_t)batch_rows * L);
+            sp.batch[k].name = xmalloc(batch_rows * sizeof(char*));
+        }
+        sem_init(&sp.free_slots, 0, 2);
+        sem_init(&sp.full_slots, 0, 0);
+        pthread_t reader;
+        if (pthread_create(&reader, NULL, stream_reader, &sp)) die("cannot start the reader thread");
+        for (int k = 0;; k ^= 1) {
+            sem_wait(&sp.full_slots);
+            batch_t* bt = &sp.batch[k];
+            if (bt->n > 0) {
+                int64_t na = 0;
+                if (uvg_push_refs(gpu, bt->text, bt->n, min_non_n, NULL, accepted, &na)) die("%s", uvg_last_error(gpu));
+                if (n_acc_total + na > rname_cap) { rname_cap = 2 * (n_acc_total + na) + 1024; rname = xrealloc(rname, rname_cap * sizeof *rname); }
+                if (n_pushed + bt->n > push_cap) { push_cap = 2 * (n_pushed + bt->n) + 1024; push_ok = xrealloc(push_ok, push_cap); }
+                for (long i = 0; i < bt->n; ++i) {
+                    push_ok[n_pushed++] = accepted[i];
+                    if (accepted[i]) rname[n_acc_total++] = bt->name[i]; else { free(bt->name[i]); ++n_invalid; }
+                }
+                if (uvg_search_async(gpu)) die("%s", uvg_last_error(gpu));
+                const int drop = uvg_db_count(gpu) >= max_resident;
+                cache_flush(&cw, gpu, rname, drop);
+                if (drop) { if (uvg_wait(gpu) || uvg_drop_refs(gpu)) die("%s", uvg_last_error(gpu)); }
+            }
+            const int last = bt->last;
+            sem_post(&sp.free_slots);
+            if (last) break;
+        }
+        pthread_join(reader, NULL);
+        n_invalid += sp.n_invalid;
+        count = sp.count; same_name = sp.same_name;
+        /* per streamed record: 1 = accepted reference (the second pass for the .aln dump needs it) */
+        rec_ok = sp.rec_state; n_rec = sp.n_rec;
+        { int64_t k = 0; for (int64_t i = 0; i < n_rec; ++i) rec_ok[i] = rec_ok[i] == 2 ? push_ok[k++] : 0; }
+        pinned_text[0] = sp.batch[0].text; pinned_text[1] = sp.batch[1].text; batch_names[0] = sp.batch[0].name; batch_names[1] = sp.batch[1].name;
+        if (cw.fp) {
+            cache_flush(&cw, gpu, rname, 1);
+            const uint64_t rec[2] = {2, (uint64_t)n_rec}; const int64_t v[2] = {count, n_invalid};
+            cache_put(cw.fp, rec, sizeof rec); cache_put(cw.fp, v, sizeof v); cache_put(cw.fp, rec_ok, (size_t)n_rec); cache_pad8(cw.fp, (size_t)n_rec);
+            const uint64_t end = 3;
+            cache_put(cw.fp, &end, 8);
+            if (fclose(cw.fp) || rename(cw.tmp, cw.path)) die("cannot finish the cache file %s", cw.path);
+            uvg_host_free_pinned(cw.buf); free(cw.tmp); free(cw.path);
+            fprintf(stderr, "Saved the packed references to the cache %s, %.3lf secs elapsed.\n", cache_path, now_s() - t0);
+        }
+    }
     fprintf(stderr, "Total of %ld sequences read; %ld too ambiguous (excluded). %.3lf secs elapsed. \n", count, n_invalid, now_s() - t0);
     if (xclude) fprintf(stderr, " %ld reference sequences already present in query alignment (based on name only).\n", same_name);
     if (uvg_wait(gpu)) die("%s", uvg_last_error(gpu));
@@ -583,7 +733,7 @@ int main(int argc, char** argv)
     fprintf(stderr, "Saved distance table to file %s , %.3lf secs elapsed.\n", outname, now_s() - t0);
 
     uvg_destroy(gpu);
-    for (int k = 0; k < 2; ++k) { uvg_host_free_pinned(sp.batch[k].text); free(sp.batch[k].name); }
+    for (int k = 0; k < 2; ++k) { uvg_host_free_pinned(pinned_text[k]); free(batch_names[k]); }
     for (int64_t i = 0; i < n_acc_total; ++i) free(rname[i]);
     for (int i = 0; i < q.n; ++i) free(q.name[i]);
     free(rname); free(rec_ok); free(push_ok); free(accepted); free(best); free(outname); free(q.name); free(q.text); free(qset.slot);

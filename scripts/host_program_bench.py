@@ -34,10 +34,21 @@ with Engine(L, nbest=100) as eng:
                 fh.write(b">R%07d\n" % (s + i)); fh.write(t[i].tobytes()); fh.write(b"\n")
     eng.device_free(d)
 size = os.path.getsize(os.path.join(wd, "r.fa"))
-t0 = time.perf_counter()
-p = subprocess.run([os.path.join(ROOT, "uvaia_b200", "bin", "uvaia_b200"), "-n", "100", "-r", os.path.join(wd, "r.fa"), "-o", os.path.join(wd, "out"),
-                    os.path.join(wd, "q.fa")], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
-dt = time.perf_counter() - t0
-err = p.stderr.decode(errors="replace")
-print(json.dumps({"returncode": p.returncode, "refs": a.refs, "ref_file_bytes": size, "wall_s": dt, "ref_text_MB_per_s": size / dt / 1e6,
-                  "stderr_tail": err.strip().splitlines()[-6:]}))
+import lzma
+import re
+BIN = os.path.join(ROOT, "uvaia_b200", "bin", "uvaia_b200")
+runs = {}
+for label, extra in (("text", []), ("cache_write", ["--cache", os.path.join(wd, "refs.uvg")]), ("cache_read", ["--cache", os.path.join(wd, "refs.uvg")])):
+    t0 = time.perf_counter()
+    p = subprocess.run([BIN, "-n", "100", "-r", os.path.join(wd, "r.fa"), "-o", os.path.join(wd, "out_" + label)] + extra + [os.path.join(wd, "q.fa")],
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    dt = time.perf_counter() - t0
+    err = p.stderr.decode(errors="replace")
+    marks = {}
+    for key, pat in (("search_done_s", r"too ambiguous \(excluded\)\. ([0-9.]+) secs elapsed"), ("aln_done_s", r"Saved \d+ sequences to file .* ([0-9.]+) secs elapsed"),
+                     ("csv_done_s", r"Saved distance table to file .* ([0-9.]+) secs elapsed")):
+        m = re.search(pat, err)
+        marks[key] = float(m.group(1)) if m else None
+    runs[label] = {"returncode": p.returncode, "wall_s": dt, "ref_text_MB_per_s": size / dt / 1e6, **marks, "stderr_tail": err.strip().splitlines()[-4:]}
+same = all(lzma.open(os.path.join(wd, "out_%s.csv.xz" % k)).read() == lzma.open(os.path.join(wd, "out_text.csv.xz")).read() for k in runs)
+print(json.dumps({"refs": a.refs, "ref_file_bytes": size, "cache_file_bytes": os.path.getsize(os.path.join(wd, "refs.uvg")), "same_csv": same, "runs": runs}))

@@ -88,3 +88,30 @@ def test_host_program_streams_with_drops(tmp_path):
     p = run(args + ["-o", prefix, "--batch", "100", "--max_resident", "300", c.query_file])
     assert p.returncode == 0, p.stderr.decode(errors="replace")[-2000:]
     assert lzma.open(prefix + ".csv.xz", "rb").read().decode() == c.expected_csv
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,extra", [("syn_default", ["--batch", "700", "--max_resident", "1500"]), ("syn_ref_filter", []), ("syn_two_files", ["--batch", "333"]),
+                                       ("amb_default", ["--batch", "512"]), ("syn_acgt", []), ("keep_default", ["--batch", "96"])])
+def test_host_program_cache_gives_the_same_outputs(name, extra, tmp_path):
+    """--cache: the first run writes the packed references, the second one reads them instead of the FASTA files; both
+    must give the reference's table and alignment names.  A changed -A threshold makes the cache stale."""
+    c = Case(name)
+    args = list(c.args)
+    for rf in c.ref_files:
+        args += ["-r", rf]
+    cache = str(tmp_path / "refs.uvg")
+    for run_no in range(2):
+        prefix = str(tmp_path / f"out{run_no}")
+        p = run(args + extra + ["-o", prefix, "--cache", cache, c.query_file])
+        assert p.returncode == 0, p.stderr.decode(errors="replace")[-2000:]
+        assert (b"will be saved to the cache" if run_no == 0 else b"are read from the cache") in p.stderr
+        assert lzma.open(prefix + ".csv.xz", "rb").read().decode() == c.expected_csv
+        aln = read_fasta_text(lzma.open(prefix + ".aln.xz", "rb").read())
+        assert [r[0].encode() for r in aln] == c.expected_aln_names
+        assert os.path.exists(cache) and not os.path.exists(cache + ".tmp")
+    if "-A" not in args:
+        p = run(args + ["-A", "0.37", "-o", str(tmp_path / "out2"), "--cache", cache, c.query_file])
+        assert p.returncode == 0 and b"will be saved to the cache" in p.stderr          # stale: written again
+    p = run(args + ["-x", "-o", str(tmp_path / "out3"), "--cache", cache, c.query_file])
+    assert p.returncode == 0 and b"--cache is ignored with -x" in p.stderr
