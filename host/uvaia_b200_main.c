@@ -12,6 +12,7 @@
  */
 #define _GNU_SOURCE
 #include <ctype.h>
+#include <fcntl.h>
 #include <getopt.h>
 #include <pthread.h>
 #include <semaphore.h>
@@ -20,6 +21,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
 #include <time.h>
 #include <unistd.h>
 #include <zlib.h>
@@ -49,6 +52,7 @@ typedef struct {
     gzFile gz; FILE* pipe;
     unsigned char* buf; size_t cap, beg, end; int eof;
     unsigned char* line; size_t line_cap;
+    int mem;                    /* buf is a borrowed memory range (a slice of a mapped raw file): nothing to read, nothing to free */
 } reader_t;
 
 static char* shell_quote(const char* s)
@@ -88,11 +92,18 @@ static void reader_open(reader_t* r, const char* path)
     r->buf = xmalloc(r->cap);
 }
 
+static void reader_open_mem(reader_t* r, const unsigned char* base, size_t len)
+{
+    memset(r, 0, sizeof *r);
+    r->buf = (unsigned char*)base; r->end = r->cap = len; r->eof = 1; r->mem = 1;
+}
+
 static void reader_close(reader_t* r)
 {
     if (r->gz) gzclose(r->gz);
     if (r->pipe) pclose(r->pipe);
-    free(r->buf); free(r->line);
+    if (!r->mem) free(r->buf);
+    free(r->line);
     memset(r, 0, sizeof *r);
 }
 
@@ -141,18 +152,22 @@ typedef struct {
     reader_t rd;
     char* next_name;            /* name of the record whose header line has been read already */
     char* name; unsigned char* seq; size_t len, cap;
+    int accumulate; size_t start;   /* accumulate: records are laid one behind the other in seq; the current one is seq[start, start+len) */
 } fasta_t;
 
 static int is_blank(unsigned char c) { return c == ' ' || (c >= '\t' && c <= '\r'); }
 
 static void fasta_open(fasta_t* f, const char* path) { memset(f, 0, sizeof *f); reader_open(&f->rd, path); }
+static void fasta_open_mem(fasta_t* f, const unsigned char* base, size_t len) { memset(f, 0, sizeof *f); reader_open_mem(&f->rd, base, len); f->accumulate = 1; }
 static void fasta_close(fasta_t* f) { reader_close(&f->rd); free(f->next_name); free(f->name); free(f->seq); memset(f, 0, sizeof *f); }
 
 /* 1 = a record is in f->name / f->seq / f->len (owned by f until the next call) */
 static int fasta_next(fasta_t* f)
 {
     const unsigned char* ln; size_t n;
-    free(f->name); f->name = NULL; f->len = 0;
+    free(f->name); f->name = NULL;
+    if (f->accumulate) f->start += f->len;
+    f->len = 0;
     for (;;) {
         int have = reader_line(&f->rd, &ln, &n);
         if (!have) {
@@ -173,9 +188,9 @@ static int fasta_next(fasta_t* f)
             continue;
         }
         if (!f->next_name) continue;                        /* sequence text before the first header */
-        if (f->len + n > f->cap) { f->cap = 2 * (f->len + n) + 1024; f->seq = xrealloc(f->seq, f->cap); }
+        if (f->start + f->len + n > f->cap) { f->cap = 2 * (f->start + f->len + n) + 1024; f->seq = xrealloc(f->seq, f->cap); }
         {   /* upper-case copy (branch-free, vectorised by the compiler); a line with blanks inside is compacted afterwards */
-            unsigned char* dst = f->seq + f->len;
+            unsigned char* dst = f->seq + f->start + f->len;
             unsigned any_blank = 0;
             for (i = 0; i < n; ++i) {
                 const unsigned char ch = ln[i];
@@ -318,44 +333,184 @@ typedef struct {
     long count, n_invalid, same_name;
 } stream_t;
 
+/* one parsed record enters the stream: counters, -x, the length check, the copy into the pinned batch.  `name` is owned
+ * by the callee (kept for accepted rows, freed otherwise). */
+typedef struct {
+    stream_t* sp; batch_t* bt; int k;                        /* first pass: rows into the pinned batches */
+    uint64_t digest; long n_digest;                          /* --parse_only */
+    writer_t* aln; const uint8_t *rec_ok, *best; int64_t n_rec, rec, ord; long n_output;   /* second pass: the .aln.xz dump */
+} stream_pos_t;
+static void stream_take(stream_pos_t* ps, char* name, const unsigned char* seq, size_t len)
+{
+    stream_t* sp = ps->sp;
+    if (ps->aln) {                                           /* second pass: write the records that ever entered a heap */
+        if (ps->rec >= ps->n_rec) die("a reference file changed while running");
+        if (ps->rec_ok[ps->rec++] == 1 && ps->best[ps->ord++]) {
+            writer_put(ps->aln, ">", 1); writer_put(ps->aln, name, strlen(name)); writer_put(ps->aln, "\n", 1);
+            writer_put(ps->aln, seq, len); writer_put(ps->aln, "\n", 1);
+            ++ps->n_output;
+        }
+        free(name);
+        return;
+    }
+    if (!sp) {                                               /* --parse_only: a digest of what the parser delivers, in order */
+        uint64_t h = ps->digest ? ps->digest : 1469598103934665603ull;
+        for (const char* c = name; *c; ++c) { h ^= (unsigned char)*c; h *= 1099511628211ull; }
+        h ^= 0xff; h *= 1099511628211ull;
+        size_t i = 0;
+        for (; i + 8 <= len; i += 8) { uint64_t w; memcpy(&w, seq + i, 8); h ^= w; h *= 1099511628211ull; h ^= h >> 29; }
+        for (; i < len; ++i) { h ^= seq[i]; h *= 1099511628211ull; }
+        ps->digest = h; ++ps->n_digest;
+        free(name);
+        return;
+    }
+    ++sp->count;
+    if (sp->n_rec == sp->rec_cap) { sp->rec_cap = sp->rec_cap ? 2 * sp->rec_cap : 1 << 16; sp->rec_state = xrealloc(sp->rec_state, sp->rec_cap); }
+    sp->rec_state[sp->n_rec++] = 0;
+    if (sp->qset && nameset_has(sp->qset, name)) { ++sp->same_name; free(name); return; }        /* nearest.c:255-261 */
+    if ((int64_t)len != sp->L) {
+        /* nearest.c:263-278: a poor-quality reference of the wrong length is skipped, a good one is fatal */
+        long nn = 0;
+        for (size_t i = 0; i < len; ++i) nn += g_validtxt[seq[i]];
+        if (nn < sp->min_non_n) { ++sp->n_invalid; free(name); return; }
+        die("all sequences must be aligned: reference %s has %zu sites, queries have %d", name, len, sp->L);
+    }
+    batch_t* bt = ps->bt;
+    memcpy(bt->text + (size_t)bt->n * sp->L, seq, sp->L);
+    bt->name[bt->n++] = name;
+    sp->rec_state[sp->n_rec - 1] = 2;
+    if (bt->n == sp->batch_rows) {
+        sem_post(&sp->full_slots);
+        ps->k ^= 1;
+        sem_wait(&sp->free_slots);
+        ps->bt = &sp->batch[ps->k];
+        ps->bt->n = 0; ps->bt->last = 0;
+    }
+}
+
+/* Raw (uncompressed) FASTA files are mapped and parsed by several threads: a line that holds '>' starts a record whatever
+ * came before it, so a slice that begins at such a line parses on its own.  The file goes through in windows; every
+ * worker parses one slice of the window into its own buffer, then this thread takes the records in file order. */
+static size_t env_size(const char* name, size_t dflt) { const char* e = getenv(name); return e && atoll(e) > 0 ? (size_t)atoll(e) : dflt; }
+typedef struct { char* name; size_t off, len; } prec_t;
+typedef struct { const unsigned char* base; size_t len; prec_t* rec; size_t n, cap; unsigned char* seq; } pslice_t;
+
+static void* parse_slice(void* arg)
+{
+    pslice_t* ps = arg;
+    fasta_t f;
+    fasta_open_mem(&f, ps->base, ps->len);
+    while (fasta_next(&f)) {
+        if (ps->n == ps->cap) { ps->cap = ps->cap ? 2 * ps->cap : 1024; ps->rec = xrealloc(ps->rec, ps->cap * sizeof *ps->rec); }
+        ps->rec[ps->n].name = f.name; ps->rec[ps->n].off = f.start; ps->rec[ps->n].len = f.len; ++ps->n;
+        f.name = NULL;
+    }
+    ps->seq = f.seq; f.seq = NULL;
+    fasta_close(&f);
+    return NULL;
+}
+/* offset of the first line at or after `from` that starts a record (same hygiene as fasta_next), or `size` */
+static size_t next_header(const unsigned char* m, size_t size, size_t from)
+{
+    size_t p = from;
+    if (p > 0) { while (p < size && m[p - 1] != '\n' && m[p - 1] != '\r') ++p; }       /* to the start of a line */
+    while (p < size) {
+        size_t e = p;
+        while (e < size && m[e] != '\n' && m[e] != '\r') ++e;
+        const size_t n = e - p;
+        if (n >= 2) {
+            size_t i = p;
+            while (i < e && is_blank(m[i])) ++i;
+            if (i < e && m[i] != '#' && m[i] != ';' && memchr(m + p, '>', n)) return p;
+        }
+        p = e + 1;
+    }
+    return size;
+}
+
+static int parse_threads(void)
+{
+    const char* e = getenv("UVG_PARSE_THREADS");
+    long t = e ? atol(e) : sysconf(_SC_NPROCESSORS_ONLN) - 2;
+    return t < 1 ? 1 : t > 32 ? 32 : (int)t;
+}
+/* 1 = the file was raw text and has been streamed; 0 = compressed (or not mappable): the caller reads it serially */
+static int stream_file_parallel(stream_pos_t* pos, const char* path)
+{
+    const int T = parse_threads();
+    if (T < 2) return 0;
+    int fd = open(path, O_RDONLY);
+    if (fd < 0) die("cannot open file %s", path);
+    struct stat sb;
+    if (fstat(fd, &sb) || !S_ISREG(sb.st_mode) || sb.st_size < (off_t)env_size("UVG_PARSE_MIN_BYTES", 1 << 20)) { close(fd); return 0; }
+    const size_t size = (size_t)sb.st_size, window = env_size("UVG_PARSE_WINDOW", (size_t)256 << 20);
+    unsigned char* m = mmap(NULL, size, PROT_READ, MAP_PRIVATE, fd, 0);
+    close(fd);
+    if (m == MAP_FAILED) return 0;
+    if ((m[0] == 0x1f && m[1] == 0x8b) || !memcmp(m, "\xfd" "7zXZ", 5) || !memcmp(m, "BZh", 3)) { munmap(m, size); return 0; }
+    madvise(m, size, MADV_SEQUENTIAL);
+    /* two sets of slices: the parsers of the next window run while this thread takes the records of the current one */
+    pslice_t* sl[2]; pthread_t* th[2];
+    for (int k = 0; k < 2; ++k) { sl[k] = xmalloc(T * sizeof **sl); th[k] = xmalloc(T * sizeof **th); }
+    double t_join = 0, t_take = 0;
+    size_t w0 = 0;                                           /* start of the window: offset 0 or a header line */
+    int cur = 0, have = 0;
+    for (;;) {
+        /* launch the window that starts at w0 into the free set */
+        const int nxt = have ? cur ^ 1 : cur;
+        int launched = 0;
+        if (w0 < size) {
+            const size_t w1 = w0 + window >= size ? size : next_header(m, size, w0 + window);
+            size_t cut[33];
+            cut[0] = w0; cut[T] = w1;
+            for (int t = 1; t < T; ++t) {
+                cut[t] = next_header(m, w1, w0 + (w1 - w0) / T * t);
+                if (cut[t] < cut[t - 1]) cut[t] = cut[t - 1];
+            }
+            for (int t = 0; t < T; ++t) {
+                memset(&sl[nxt][t], 0, sizeof sl[nxt][t]);
+                sl[nxt][t].base = m + cut[t]; sl[nxt][t].len = cut[t + 1] - cut[t];
+                if (pthread_create(&th[nxt][t], NULL, parse_slice, &sl[nxt][t])) die("cannot start a parser thread");
+            }
+            w0 = w1; launched = 1;
+        }
+        if (!have) { if (!launched) break; have = 1; continue; }
+        for (int t = 0; t < T; ++t) {
+            const double ta = now_s();
+            pthread_join(th[cur][t], NULL);
+            const double tb = now_s();
+            pslice_t* ps = &sl[cur][t];
+            for (size_t i = 0; i < ps->n; ++i) stream_take(pos, ps->rec[i].name, ps->seq + ps->rec[i].off, ps->rec[i].len);
+            free(ps->rec); free(ps->seq);
+            t_join += tb - ta; t_take += now_s() - tb;
+        }
+        if (!launched) break;
+        cur ^= 1;
+    }
+    if (getenv("UVG_PARSE_TIMING")) fprintf(stderr, "parallel parse of %s: %d threads, waited %.3f s for the parsers, %.3f s taking the records\n", path, T, t_join, t_take);
+    for (int k = 0; k < 2; ++k) { free(sl[k]); free(th[k]); }
+    munmap(m, size);
+    return 1;
+}
+
 static void* stream_reader(void* arg)
 {
     stream_t* sp = arg;
-    int k = 0;
+    stream_pos_t pos = {sp, NULL, 0};
     sem_wait(&sp->free_slots);
-    batch_t* bt = &sp->batch[k];
-    bt->n = 0; bt->last = 0;
+    pos.bt = &sp->batch[0];
+    pos.bt->n = 0; pos.bt->last = 0;
     for (int j = 0; j < sp->n_files; ++j) {
         const double t1 = now_s();
-        fasta_t f;
-        fasta_open(&f, sp->file[j]);
-        while (fasta_next(&f)) {
-            ++sp->count;
-            if (sp->n_rec == sp->rec_cap) { sp->rec_cap = sp->rec_cap ? 2 * sp->rec_cap : 1 << 16; sp->rec_state = xrealloc(sp->rec_state, sp->rec_cap); }
-            sp->rec_state[sp->n_rec++] = 0;
-            if (sp->qset && nameset_has(sp->qset, f.name)) { ++sp->same_name; continue; }             /* nearest.c:255-261 */
-            if ((int64_t)f.len != sp->L) {
-                /* nearest.c:263-278: a poor-quality reference of the wrong length is skipped, a good one is fatal */
-                long nn = 0;
-                for (size_t i = 0; i < f.len; ++i) nn += g_validtxt[f.seq[i]];
-                if (nn < sp->min_non_n) { ++sp->n_invalid; continue; }
-                die("all sequences must be aligned: reference %s has %zu sites, queries have %d", f.name, f.len, sp->L);
-            }
-            memcpy(bt->text + (size_t)bt->n * sp->L, f.seq, sp->L);
-            bt->name[bt->n++] = f.name; f.name = NULL;
-            sp->rec_state[sp->n_rec - 1] = 2;
-            if (bt->n == sp->batch_rows) {
-                sem_post(&sp->full_slots);
-                k ^= 1;
-                sem_wait(&sp->free_slots);
-                bt = &sp->batch[k];
-                bt->n = 0; bt->last = 0;
-            }
+        if (!stream_file_parallel(&pos, sp->file[j])) {
+            fasta_t f;
+            fasta_open(&f, sp->file[j]);
+            while (fasta_next(&f)) { char* nm = f.name; f.name = NULL; stream_take(&pos, nm, f.seq, f.len); }
+            fasta_close(&f);
         }
-        fasta_close(&f);
         fprintf(stderr, "Finished reading file %s in %.3lf secs;\n", sp->file[j], now_s() - t1);
     }
-    bt->last = 1;
+    pos.bt->last = 1;
     sem_post(&sp->full_slots);
     return NULL;
 }
@@ -370,7 +525,6 @@ static void* stream_reader(void* arg)
  * A cache is used only if nchar, mode, the -A threshold and the size and mtime of every -r file match; not with -x (the
  * set of pushed references then depends on the query names).
  * ------------------------------------------------------------------------------------------------------------- */
-#include <sys/stat.h>
 #define CACHE_VERSION 1u
 typedef struct { FILE* fp; char* path; char* tmp; void* buf; size_t buf_cap; int64_t exported, base; } cache_writer_t;
 
@@ -461,6 +615,7 @@ int main(int argc, char** argv)
     int nbest = 100, trim = 0, acgt = 0, xclude = 0, pool = 0, device = 0, hires = 0;
     long batch_rows = 65536, max_resident = 1 << 20;
     const char* cache_path = NULL;
+    int parse_only = 0;
     double ambig_q = 0.5, ambig_r = 0.5;
     const char* out_prefix = NULL;
     const char* ref_file[1024]; int n_ref_files = 0;
@@ -468,7 +623,7 @@ int main(int argc, char** argv)
         {"help", 0, 0, 'h'}, {"version", 0, 0, 'v'}, {"acgt", 0, 0, 1000}, {"keep_resolved", 0, 0, 'k'}, {"exclude_self", 0, 0, 'x'},
         {"nbest", 1, 0, 'n'}, {"trim", 1, 0, 1001}, {"query_ambiguity", 1, 0, 'a'}, {"ref_ambiguity", 1, 0, 'A'}, {"pool", 1, 0, 'p'},
         {"reference", 1, 0, 'r'}, {"nthreads", 1, 0, 't'}, {"output", 1, 0, 'o'}, {"device", 1, 0, 1002}, {"batch", 1, 0, 1003},
-        {"max_resident", 1, 0, 1004}, {"cache", 1, 0, 1005}, {0, 0, 0, 0}};
+        {"max_resident", 1, 0, 1004}, {"cache", 1, 0, 1005}, {"parse_only", 0, 0, 1006}, {0, 0, 0, 0}};
     int ch;
     while ((ch = getopt_long(argc, argv, "hvkxn:a:A:p:r:t:o:", lo, NULL)) != -1) {
         switch (ch) {
@@ -489,8 +644,29 @@ int main(int argc, char** argv)
         case 1003: batch_rows = atol(optarg); break;
         case 1004: max_resident = atol(optarg); break;
         case 1005: cache_path = optarg; break;
+        case 1006: parse_only = 1; break;
         default: usage(argv[0], 0); return EXIT_FAILURE;
         }
+    }
+    if (parse_only) {
+        /* diagnostic: run the reference files through the FASTA reader (parallel for raw files, UVG_PARSE_THREADS) and
+         * print how many records came out and a digest of their names and sequences; needs no GPU */
+        init_tables();
+        for (int j = 0; j < n_ref_files; ++j) {
+            stream_pos_t pos;
+            memset(&pos, 0, sizeof pos);
+            const double t1 = now_s();
+            const int par = stream_file_parallel(&pos, ref_file[j]);
+            if (!par) {
+                fasta_t f;
+                fasta_open(&f, ref_file[j]);
+                while (fasta_next(&f)) { char* nm = f.name; f.name = NULL; stream_take(&pos, nm, f.seq, f.len); }
+                fasta_close(&f);
+            }
+            printf("%s records=%ld digest=%016llx parser=%s secs=%.3f\n", ref_file[j], pos.n_digest, (unsigned long long)pos.digest,
+                   par ? "parallel" : "serial", now_s() - t1);
+        }
+        return EXIT_SUCCESS;
     }
     if (n_ref_files < 1 || argc - optind != 1) { usage(argv[0], 0); return EXIT_FAILURE; }
     const char* query_file = argv[optind];
@@ -682,21 +858,17 @@ int main(int argc, char** argv)
     long n_output = 0;
     {
         writer_t w = writer_open(outname);
-        int64_t rec = 0, ord = 0;
+        stream_pos_t pos;
+        memset(&pos, 0, sizeof pos);
+        pos.aln = &w; pos.rec_ok = rec_ok; pos.best = best; pos.n_rec = n_rec;
         for (int j = 0; j < n_ref_files; ++j) {
+            if (stream_file_parallel(&pos, ref_file[j])) continue;
             fasta_t f;
             fasta_open(&f, ref_file[j]);
-            while (fasta_next(&f)) {
-                if (rec >= n_rec) die("reference file %s changed while running", ref_file[j]);
-                if (rec_ok[rec++] != 1) continue;
-                if (best[ord++]) {
-                    writer_put(&w, ">", 1); writer_put(&w, f.name, strlen(f.name)); writer_put(&w, "\n", 1);
-                    writer_put(&w, f.seq, f.len); writer_put(&w, "\n", 1);
-                    ++n_output;
-                }
-            }
+            while (fasta_next(&f)) { char* nm = f.name; f.name = NULL; stream_take(&pos, nm, f.seq, f.len); }
             fasta_close(&f);
         }
+        n_output = pos.n_output;
         writer_close(&w);
     }
     fprintf(stderr, "Total of %ld sequences read; %ld saved sequences include closest neighbours and intermediate, %ld too ambiguous (excluded). "

@@ -38,10 +38,13 @@ import lzma
 import re
 BIN = os.path.join(ROOT, "uvaia_b200", "bin", "uvaia_b200")
 runs = {}
-for label, extra in (("text", []), ("cache_write", ["--cache", os.path.join(wd, "refs.uvg")]), ("cache_read", ["--cache", os.path.join(wd, "refs.uvg")])):
+for label, extra in (("text_serial_parser", ["--serial"]), ("text", []), ("cache_write", ["--cache", os.path.join(wd, "refs.uvg")]), ("cache_read", ["--cache", os.path.join(wd, "refs.uvg")])):
     t0 = time.perf_counter()
+    env = dict(os.environ, UVG_PARSE_TIMING="1")
+    if extra == ["--serial"]:
+        extra, env["UVG_PARSE_THREADS"] = [], "1"
     p = subprocess.run([BIN, "-n", "100", "-r", os.path.join(wd, "r.fa"), "-o", os.path.join(wd, "out_" + label)] + extra + [os.path.join(wd, "q.fa")],
-                       stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env)
     dt = time.perf_counter() - t0
     err = p.stderr.decode(errors="replace")
     marks = {}
@@ -49,6 +52,7 @@ for label, extra in (("text", []), ("cache_write", ["--cache", os.path.join(wd, 
                      ("csv_done_s", r"Saved distance table to file .* ([0-9.]+) secs elapsed")):
         m = re.search(pat, err)
         marks[key] = float(m.group(1)) if m else None
-    runs[label] = {"returncode": p.returncode, "wall_s": dt, "ref_text_MB_per_s": size / dt / 1e6, **marks, "stderr_tail": err.strip().splitlines()[-4:]}
+    runs[label] = {"returncode": p.returncode, "wall_s": dt, "ref_text_MB_per_s": size / dt / 1e6, **marks, "parser": [ln for ln in err.splitlines() if "parallel parse" in ln or "Finished reading" in ln],
+                   "stderr_tail": err.strip().splitlines()[-4:]}
 same = all(lzma.open(os.path.join(wd, "out_%s.csv.xz" % k)).read() == lzma.open(os.path.join(wd, "out_text.csv.xz")).read() for k in runs)
 print(json.dumps({"refs": a.refs, "ref_file_bytes": size, "cache_file_bytes": os.path.getsize(os.path.join(wd, "refs.uvg")), "same_csv": same, "runs": runs}))

@@ -5,8 +5,10 @@ reference binary was when the goldens were made (same options, same xz inputs) a
 with the reference's: CSV byte for byte, alignment dump by record names and sequences."""
 import lzma
 import os
+
 import subprocess
 
+import numpy as np
 import pytest
 
 from helpers import ROOT, Case, case_names
@@ -115,3 +117,74 @@ def test_host_program_cache_gives_the_same_outputs(name, extra, tmp_path):
         assert p.returncode == 0 and b"will be saved to the cache" in p.stderr          # stale: written again
     p = run(args + ["-x", "-o", str(tmp_path / "out3"), "--cache", cache, c.query_file])
     assert p.returncode == 0 and b"--cache is ignored with -x" in p.stderr
+
+
+def _messy_fasta(rng, n_rec, L):
+    """records with the hazards the reader has to get right: CRLF, wrapped lines, blank and 1-byte lines, comments, text before
+    the first header, blanks inside sequence lines, '>' inside a header line, lower case, empty records"""
+    out = [b"ACGT stray text before any header\n", b"# a comment with > inside\n"]
+    alphabet = np.frombuffer(b"ACGTNacgtn-RYKM", np.uint8)
+    for i in range(n_rec):
+        eol = b"\r\n" if i % 7 == 3 else (b"\r" if i % 11 == 5 else b"\n")
+        hdr = b">rec%d|x" % i if i % 5 else b"  junk>rec%d after junk" % i
+        out.append(hdr + eol)
+        if i % 13 == 6:
+            continue                                                     # header without sequence
+        seq = alphabet[rng.integers(0, len(alphabet), size=L)].tobytes()
+        width = int(rng.integers(7, 120)) if i % 3 else L
+        for a in range(0, L, width):
+            line = seq[a:a + width]
+            if i % 9 == 4 and len(line) > 4:
+                line = line[:2] + b" \t" + line[2:]
+            out.append(line + eol)
+            if i % 4 == 1 and a == 0:
+                out.append(b"; comment inside a record" + eol + eol + b"A" + eol)    # comment, empty line, 1-byte line (dropped)
+    return b"".join(out)
+
+
+def test_parallel_parser_delivers_what_the_serial_one_does(tmp_path):
+    """raw FASTA files are parsed by several threads over slices that begin at header lines; --parse_only prints a digest of
+    the delivered records (no GPU needed): it must not depend on the number of threads or on where the slices are cut"""
+    rng = np.random.default_rng(5)
+    path = str(tmp_path / "messy.fa")
+    open(path, "wb").write(_messy_fasta(rng, 900, 333))
+    def digest(env):
+        e = dict(os.environ); e.update(env)
+        p = subprocess.run([BIN, "--parse_only", "-r", path], stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=e)
+        assert p.returncode == 0, p.stderr
+        f = p.stdout.decode().split()
+        return f[1], f[2], f[3]
+    serial = digest({"UVG_PARSE_THREADS": "1"})
+    assert serial[2] == "parser=serial" and serial[0] == "records=900"
+    for threads, window in (("2", "100000000"), ("5", "20000"), ("16", "3000"), ("3", "700"), ("32", "1")):
+        got = digest({"UVG_PARSE_THREADS": threads, "UVG_PARSE_MIN_BYTES": "1", "UVG_PARSE_WINDOW": window})
+        assert got[2] == "parser=parallel"
+        assert got[:2] == serial[:2], (threads, window)
+    # compressed input falls back to the serial reader
+    import gzip as gz
+    with gz.open(path + ".gz", "wb") as fh:
+        fh.write(open(path, "rb").read())
+    p = subprocess.run([BIN, "--parse_only", "-r", path + ".gz"], stdout=subprocess.PIPE, env=dict(os.environ, UVG_PARSE_MIN_BYTES="1"))
+    f = p.stdout.decode().split()
+    assert f[3] == "parser=serial" and (f[1], f[2]) == serial[:2]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["hygiene", "syn_default", "syn_two_files", "syn_exclude_self", "syn_ref_filter", "real_c1_small"])
+def test_host_program_parallel_parser_on_raw_files(name, tmp_path):
+    """raw reference files go through the multi-threaded parser (forced here on small files, with windows of a few records):
+    same table and alignment dump as from the compressed files"""
+    c = Case(name)
+    args = list(c.args)
+    for i, rf in enumerate(c.ref_files):
+        raw = str(tmp_path / f"r{i}.fa")
+        open(raw, "wb").write(lzma.open(rf, "rb").read())
+        args += ["-r", raw]
+    prefix = str(tmp_path / "out")
+    env = dict(os.environ, UVG_PARSE_THREADS="5", UVG_PARSE_MIN_BYTES="1", UVG_PARSE_WINDOW="50000", UVG_PARSE_TIMING="1")
+    p = subprocess.run([BIN] + args + ["-o", prefix, "--batch", "257", c.query_file], stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env)
+    assert p.returncode == 0, p.stderr.decode(errors="replace")[-2000:]
+    assert b"parallel parse of" in p.stderr
+    assert lzma.open(prefix + ".csv.xz", "rb").read().decode() == c.expected_csv
+    aln = read_fasta_text(lzma.open(prefix + ".aln.xz", "rb").read())
+    assert [r[0].encode() for r in aln] == c.expected_aln_names
