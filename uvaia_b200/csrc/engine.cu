@@ -79,6 +79,7 @@ struct uvg_ctx {
     uvg_query_info qinfo{};
     int64_t qinfo_pivot_fix = -1;
     double set_queries_host_ms = 0, set_queries_device_ms = 0;                     // fix entries of the pivot form (-1: general kernel)
+    size_t qcap[24]{};                                // single GPU: bytes of the query-side device arrays, kept across query sets (pooled_alloc)
     QChunk* d_qdata = nullptr;
     uint32_t *d_qnib = nullptr, *d_qamb_off = nullptr, *d_qamb_ent = nullptr;
     // pivot form of the pair-count kernel (pairpivot.cu): chosen per query set by uvg_set_queries
@@ -229,12 +230,29 @@ static void close_peers(uvg_ctx* c)
     c->peers_ready = false;
 }
 
+// query-side device arrays.  On a single GPU they are kept for the next query set (same sizes in a serving loop: no
+// cudaFree / cudaMalloc per uvg_set_queries, whose cost varies from microseconds to hundreds of milliseconds); pooled_alloc
+// grows them when needed.  Sharded contexts (peer-mapped tiles) and uvg_destroy release everything.
+template <typename T>
+static cudaError_t pooled_alloc(uvg_ctx* c, int slot, T** p, size_t bytes)
+{
+    bytes = std::max<size_t>(bytes, 16);
+    if (*p && c->qcap[slot] >= bytes) return cudaSuccess;
+    cudaFree(*p); *p = nullptr; c->qcap[slot] = 0;
+    const cudaError_t e = cudaMalloc(p, bytes);
+    if (e == cudaSuccess) c->qcap[slot] = bytes;
+    return e;
+}
+
 static void free_queries(uvg_ctx* c, bool final = false)
 {
     close_peers(c);
+    c->pivot_on = false;
+    if (c->world == 1 && !final) { c->seg_cap = 0; c->tile_elems = 0; return; }
+    for (size_t& b : c->qcap) b = 0;
     cudaFree(c->d_qdata); cudaFree(c->d_qnib); cudaFree(c->d_qamb_off); cudaFree(c->d_qamb_ent);
     cudaFree(c->d_qdata2); cudaFree(c->d_qfix_off); cudaFree(c->d_qfix_ent); cudaFree(c->d_pivot); cudaFree(c->d_wslot); c->d_wslot = nullptr;
-    c->d_qdata2 = nullptr; c->d_qfix_off = c->d_qfix_ent = nullptr; c->d_pivot = nullptr; c->pivot_on = false;
+    c->d_qdata2 = nullptr; c->d_qfix_off = c->d_qfix_ent = nullptr; c->d_pivot = nullptr;
     cudaFree(c->d_thr_local); for (int b = 0; b < NBUF; ++b) { cudaFree(c->d_thr_all[b]); c->d_thr_all[b] = nullptr; }
     cudaFree(c->d_heaps); cudaFree(c->d_heaps_all);
     cudaFree(c->d_heap_n); cudaFree(c->d_max_inc); cudaFree(c->d_batch_id); cudaFree(c->d_max_inc_batch);
@@ -371,6 +389,8 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     const uint8_t* code_lut = lut[acgt ? 1 : 0];
     uint8_t up[256];
     for (int i = 0; i < 256; ++i) up[i] = (uint8_t)((i >= 'a' && i <= 'z') ? i - 32 : i);     // uppercase_string, nexus_common.c:105-111
+    uint8_t code_raw[256];                                                  // 4-bit set of a raw (any case) byte
+    for (int i = 0; i < 256; ++i) code_raw[i] = code_lut[up[i]];
 
     // ---- site partition (create_query_indices, src/fastaseq.c:732-777) ----
     // usable byte: --acgt: one of ACGT (is_site_acgt, utils.c:285-289); default: valid text (is_site_valid, utils.c:291-295)
@@ -385,23 +405,32 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     {
         const int T = host_threads(std::min<int64_t>(Q, std::max<int64_t>(1, ((int64_t)256 << 20) / ((int64_t)L * 20))));
         std::vector<uint8_t> first((size_t)T * L, 0), any((size_t)T * L, 0), all((size_t)T * L, 1), same((size_t)T * L, 1);
-        std::vector<uint32_t> cnt(pivot_ok ? (size_t)T * L * 4 : 0, 0);
+        std::vector<uint32_t> cnt(pivot_ok ? (size_t)T * L * 4 : 0, 0);                // [thread][base][site]
+        // per raw byte: usable (0/1) and, for the pivot counts, the one-hot code of a usable plain base (else 0)
+        uint8_t usable_raw[256], onehot_raw[256];
+        for (int b = 0; b < 256; ++b) {
+            const uint8_t ch = up[b];
+            usable_raw[b] = acgt ? (ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T') : (lut[2][ch] != 0);
+            const uint32_t code = code_lut[ch];
+            onehot_raw[b] = (uint8_t)((usable_raw[b] && code && !(code & (code - 1))) ? code : 0);
+        }
         parallel_ranges(Q, T, [&](int t, int qa, int qb) {
             uint8_t *f = &first[(size_t)t * L], *an = &any[(size_t)t * L], *al = &all[(size_t)t * L], *sm = &same[(size_t)t * L];
             uint32_t* cn = pivot_ok ? &cnt[(size_t)t * L * 4] : nullptr;
             for (int q = qa; q < qb; ++q) {
                 const uint8_t* row = text + (size_t)q * L;
-                for (int i = trim; i < L - trim; ++i) {
-                    const uint8_t ch = up[row[i]];
-                    const bool usable = acgt ? (ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T') : (lut[2][ch] != 0);
-                    if (!usable) { al[i] = 0; continue; }
-                    if (!an[i]) { an[i] = 1; f[i] = ch; }
-                    else if (ch != f[i]) sm[i] = 0;
-                    if (cn) {
-                        const uint32_t code = code_lut[ch];
-                        if (code && !(code & (code - 1))) ++cn[(size_t)i * 4 + (code == 1 ? 0 : code == 2 ? 1 : code == 4 ? 2 : 3)];
-                    }
+                for (int i = trim; i < L - trim; ++i) {                                 // branch-free: sequential updates of four byte arrays
+                    const uint8_t b = row[i], ch = up[b], u = usable_raw[b], had = an[i], f0 = f[i];
+                    al[i] &= u;
+                    sm[i] &= (uint8_t)((uint8_t)!(u & had) | (uint8_t)(ch == f0));
+                    f[i] = (u & (uint8_t)!had) ? ch : f0;
+                    an[i] = had | u;
                 }
+                if (cn)
+                    for (int i = trim; i < L - trim; ++i) {
+                        const uint32_t oh = onehot_raw[row[i]];
+                        cn[i] += oh & 1u; cn[(size_t)L + i] += (oh >> 1) & 1u; cn[(size_t)2 * L + i] += (oh >> 2) & 1u; cn[(size_t)3 * L + i] += oh >> 3;
+                    }
             }
         });
         for (int i = trim; i < L - trim; ++i) {
@@ -423,7 +452,7 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
             // the plain base most queries hold (ties: A before C before G before T; a site nobody holds a base at: A)
             for (int i = trim; i < L - trim; ++i) {
                 uint32_t tot[4] = {0, 0, 0, 0};
-                for (int t = 0; t < T; ++t) for (int k = 0; k < 4; ++k) tot[k] += cnt[((size_t)t * L + i) * 4 + k];
+                for (int t = 0; t < T; ++t) for (int k = 0; k < 4; ++k) tot[k] += cnt[((size_t)t * 4 + k) * L + i];
                 int best = 0;
                 for (int k = 1; k < 4; ++k) if (tot[k] > tot[best]) best = k;
                 pv[i] = (uint8_t)(1u << best);
@@ -456,26 +485,39 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
             const bool is_cons = q == Q;
             const uint8_t* row = is_cons ? cons.data() : text + (size_t)q * L;
             std::fill(plain_in_chunk.begin(), plain_in_chunk.end(), 0u);
-            for (int s = trim; s < L - trim; ++s) {
-                if (is_cons && site_class[s] != 3) continue;                // the consensus is scored on idx_c only
-                const uint32_t code = code_lut[up[row[s]]];
-                const int w = s >> 5, k = w & 3;
-                const uint32_t bit = 1u << (s & 31);
+            // word by word: the bits of 32 sites are gathered in registers and stored once
+            for (int w = trim >> 5; w <= (L - trim - 1) >> 5 && trim < L - trim; ++w) {
+                const int s0 = std::max(w << 5, trim), s1 = std::min((w + 1) << 5, L - trim);
+                uint32_t mb = 0, m1 = 0, m2 = 0, mseg = 0, me = 0, n_plain = 0;
+                uint32_t nib[4] = {0, 0, 0, 0};
+                for (int s = s0; s < s1; ++s) {
+                    if (is_cons && site_class[s] != 3) continue;            // the consensus is scored on idx_c only
+                    const uint32_t code = code_raw[row[s]];
+                    const uint32_t j = (uint32_t)s & 31u, bit = 1u << j;
+                    if (acgt && site_class[s] == 1) mseg |= bit;            // segregating-site mask (dist_unique, nearest.c:459-470)
+                    nib[j >> 3] |= code << ((j & 7u) * 4u);
+                    const uint32_t plain = (uint32_t)(code != 0u) & (uint32_t)((code & (code - 1u)) == 0u);
+                    mb |= plain << j;
+                    m1 |= (plain & (uint32_t)((code & 10u) != 0u)) << j;    // C or T
+                    m2 |= (plain & (uint32_t)((code & 12u) != 0u)) << j;    // G or T
+                    n_plain += plain;
+                    if (code & (code - 1u)) { amb[q].push_back((uint32_t)s | (code << 28)); continue; }
+                    if (pivot_ok && plain) {
+                        if (code == pv[s]) me |= bit;
+                        else snp[q].push_back((uint32_t)s | (code << 28));
+                    }
+                }
+                const int k = w & 3;
                 const size_t ci = (size_t)qt * c->n_chunks + w / WC;
                 uint4* pl = qd[ci].pl[(w % WC) / 4][qi];
-                if (acgt && site_class[s] == 1) (&pl[3].x)[k] |= bit;       // segregating-site mask (dist_unique, nearest.c:459-470)
-                if (!code) continue;
-                qnib[(size_t)q * c->qnib_stride + (s >> 3)] |= code << ((s & 7) * 4);
-                if (code & (code - 1)) { amb[q].push_back((uint32_t)s | (code << 28)); continue; }
-                (&pl[0].x)[k] |= bit;
-                if (code & 10u) (&pl[1].x)[k] |= bit;                       // C or T
-                if (code & 12u) (&pl[2].x)[k] |= bit;                       // G or T
-                ++plain_in_chunk[w / WC];
+                (&pl[0].x)[k] = mb; (&pl[1].x)[k] = m1; (&pl[2].x)[k] = m2;
+                if (acgt) (&pl[3].x)[k] = mseg;
+                uint32_t* qn = &qnib[(size_t)q * c->qnib_stride];
+                for (int i = 0; i < 4; ++i) if (w * 4 + i < c->qnib_stride) qn[w * 4 + i] = nib[i];
+                plain_in_chunk[w / WC] += n_plain;
                 if (pivot_ok) {
                     uint4* p2 = qd2[ci].pl[(w % WC) / 4][qi];
-                    (&p2[0].x)[k] |= bit;
-                    if (code == pv[s]) (&p2[1].x)[k] |= bit;
-                    else snp[q].push_back((uint32_t)s | (code << 28));
+                    (&p2[0].x)[k] = mb; (&p2[1].x)[k] = me;
                 }
             }
             uint32_t run = 0;
@@ -590,19 +632,19 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     const auto t_host = std::chrono::steady_clock::now();
     // ---- device allocations ----
     const int rows = c->rows_cap;
-    UVG_CUDA(c, cudaMalloc(&c->d_qdata, n_chunk_total * sizeof(QChunk)));
-    UVG_CUDA(c, cudaMalloc(&c->d_qnib, qnib.size() * 4));
-    UVG_CUDA(c, cudaMalloc(&c->d_qamb_off, amb_off.size() * 4));
-    UVG_CUDA(c, cudaMalloc(&c->d_qamb_ent, std::max<size_t>(1, amb_ent.size()) * 4));
-    UVG_CUDA(c, cudaMalloc(&c->d_thr_local, (size_t)rows * sizeof(Threshold)));
-    for (int b = 0; b < NBUF; ++b) UVG_CUDA(c, cudaMalloc(&c->d_thr_all[b], (size_t)c->world * rows * sizeof(Threshold)));
-    UVG_CUDA(c, cudaMalloc(&c->d_heaps, (size_t)rows * (c->K + 1) * sizeof(HeapItem)));
-    UVG_CUDA(c, cudaMalloc(&c->d_heap_n, rows * 4)); UVG_CUDA(c, cudaMalloc(&c->d_max_inc, rows * 4));
-    UVG_CUDA(c, cudaMalloc(&c->d_batch_id, rows * 4)); UVG_CUDA(c, cudaMalloc(&c->d_max_inc_batch, rows * 4));
+    UVG_CUDA(c, pooled_alloc(c, 0, &c->d_qdata, n_chunk_total * sizeof(QChunk)));
+    UVG_CUDA(c, pooled_alloc(c, 1, &c->d_qnib, qnib.size() * 4));
+    UVG_CUDA(c, pooled_alloc(c, 2, &c->d_qamb_off, amb_off.size() * 4));
+    UVG_CUDA(c, pooled_alloc(c, 3, &c->d_qamb_ent, amb_ent.size() * 4));
+    UVG_CUDA(c, pooled_alloc(c, 4, &c->d_thr_local, (size_t)rows * sizeof(Threshold)));
+    for (int b = 0; b < NBUF; ++b) UVG_CUDA(c, pooled_alloc(c, 5 + b, &c->d_thr_all[b], (size_t)c->world * rows * sizeof(Threshold)));
+    UVG_CUDA(c, pooled_alloc(c, 7, &c->d_heaps, (size_t)rows * (c->K + 1) * sizeof(HeapItem)));
+    UVG_CUDA(c, pooled_alloc(c, 8, &c->d_heap_n, (size_t)rows * 4)); UVG_CUDA(c, pooled_alloc(c, 9, &c->d_max_inc, (size_t)rows * 4));
+    UVG_CUDA(c, pooled_alloc(c, 10, &c->d_batch_id, (size_t)rows * 4)); UVG_CUDA(c, pooled_alloc(c, 11, &c->d_max_inc_batch, (size_t)rows * 4));
     if (c->world > 1) {
-        UVG_CUDA(c, cudaMalloc(&c->d_heaps_all, (size_t)c->world * rows * (c->K + 1) * sizeof(HeapItem)));
-        UVG_CUDA(c, cudaMalloc(&c->d_heap_n_all, (size_t)c->world * rows * 4));
-        UVG_CUDA(c, cudaMalloc(&c->d_max_inc_all, (size_t)c->world * rows * 4));
+        UVG_CUDA(c, pooled_alloc(c, 12, &c->d_heaps_all, (size_t)c->world * rows * (c->K + 1) * sizeof(HeapItem)));
+        UVG_CUDA(c, pooled_alloc(c, 13, &c->d_heap_n_all, (size_t)c->world * rows * 4));
+        UVG_CUDA(c, pooled_alloc(c, 14, &c->d_max_inc_all, (size_t)c->world * rows * 4));
     }
     // dense score tiles: rounds are capped so that one buffer stays within ~3 GiB
     {
@@ -624,11 +666,11 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     UVG_CUDA(c, cudaMemcpyAsync(c->d_qamb_off, amb_off.data(), amb_off.size() * 4, cudaMemcpyHostToDevice, c->st));
     if (!amb_ent.empty()) UVG_CUDA(c, cudaMemcpyAsync(c->d_qamb_ent, amb_ent.data(), amb_ent.size() * 4, cudaMemcpyHostToDevice, c->st));
     if (pivot_ok) {
-        UVG_CUDA(c, cudaMalloc(&c->d_qdata2, n_chunk_total * sizeof(QChunk2)));
-        UVG_CUDA(c, cudaMalloc(&c->d_qfix_off, fix_off.size() * 4));
-        UVG_CUDA(c, cudaMalloc(&c->d_qfix_ent, std::max<size_t>(1, fix_ent.size()) * 4));
-        UVG_CUDA(c, cudaMalloc(&c->d_pivot, pivot_words.size() * 4));
-        UVG_CUDA(c, cudaMalloc(&c->d_wslot, wslot.size()));
+        UVG_CUDA(c, pooled_alloc(c, 15, &c->d_qdata2, n_chunk_total * sizeof(QChunk2)));
+        UVG_CUDA(c, pooled_alloc(c, 16, &c->d_qfix_off, fix_off.size() * 4));
+        UVG_CUDA(c, pooled_alloc(c, 17, &c->d_qfix_ent, fix_ent.size() * 4));
+        UVG_CUDA(c, pooled_alloc(c, 18, &c->d_pivot, pivot_words.size() * 4));
+        UVG_CUDA(c, pooled_alloc(c, 19, &c->d_wslot, wslot.size()));
         UVG_CUDA(c, cudaMemcpyAsync(c->d_wslot, wslot.data(), wslot.size(), cudaMemcpyHostToDevice, c->st));
         UVG_CUDA(c, cudaMemcpyAsync(c->d_qdata2, qd2.data(), n_chunk_total * sizeof(QChunk2), cudaMemcpyHostToDevice, c->st));
         UVG_CUDA(c, cudaMemcpyAsync(c->d_qfix_off, fix_off.data(), fix_off.size() * 4, cudaMemcpyHostToDevice, c->st));
