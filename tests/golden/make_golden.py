@@ -350,6 +350,30 @@ def case_keep_resolved():
     save_case("keep_off", qf, [rf], ["-n", "8"], "same inputs without -k: every query is searched")
 
 
+def case_alphabet_soup():
+    """every symbol class of the truth table inside end-to-end runs: U, lower case, the indel spellings (n x o ? . -),
+    letters outside the IUPAC alphabet (E Z *), two- and three-base codes, in the queries and in the references"""
+    m = SynthModel(nsites=1800, n_clades=10, seed=61, clade_subs=9)
+    qn, Q = m.sample(30, 62, prefix="Q")
+    rn, R = m.sample(1200, 63, prefix="R")
+    rng = np.random.default_rng(64)
+    soup = np.frombuffer(b"UuacgtnxXoO?.-EZ*MRWSYKVHDBmrwsykvhdb", np.uint8)
+
+    def sprinkle(T, frac):
+        T = T.copy()
+        mask = rng.random(T.shape) < frac
+        T[mask] = soup[rng.integers(0, len(soup), size=int(mask.sum()))]
+        return T
+
+    Qs, Rs = sprinkle(Q, 0.04), sprinkle(R, 0.04)
+    Rs[7] = Qs[3]                                                  # a reference identical to a query, odd bytes included
+    Rs[8] = np.frombuffer(Qs[3].tobytes().lower(), np.uint8)       # the same in lower case (the reader upper-cases)
+    qf, rf = fasta_bytes(qn, Qs), fasta_bytes(rn, Rs)
+    save_case("soup_default", qf, [rf], ["-n", "9"], "full symbol alphabet (U, lower case, indel spellings, non-IUPAC letters, IUPAC codes) at 4 % of the sites")
+    save_case("soup_acgt", qf, [rf], ["-n", "9", "--acgt"], "same, --acgt")
+    save_case("soup_trim_k", qf, [rf], ["-n", "9", "--trim", "77", "-k"], "same, --trim 77 -k")
+
+
 def case_c2_shape():
     m = SynthModel(nsites=29903, n_clades=40, seed=1)
     qn, Q = m.sample(24, 2002, prefix="England/QRY")
@@ -383,7 +407,7 @@ def case_bundled():
 
 
 GROUPS = {"unit": make_unit_vectors, "synthetic": case_synthetic, "ties": case_ties, "ambiguous": case_ambiguous,
-          "hygiene": case_hygiene, "keep_resolved": case_keep_resolved, "c2_shape": case_c2_shape, "bundled": case_bundled}
+          "hygiene": case_hygiene, "keep_resolved": case_keep_resolved, "alphabet_soup": case_alphabet_soup, "c2_shape": case_c2_shape, "bundled": case_bundled}
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
