@@ -46,6 +46,14 @@ def run_case(rank, world, L, nq, nr, nbest, acgt=False, amb=0.0, first_round=64,
         got = [eng.heap(iq) for iq in range(len(names))]
         eb = eng.ever_best(0, total)
         st = eng.stats()
+        # a second query set on the resident shards: the communicator exists now, so rank 0 alone prepares the queries and
+        # the other ranks receive the arrays by broadcast (uvg_set_queries)
+        names2, Qo2, *_ = orc.prepare_queries(qn[::2], qs[::2], 0, acgt, 0.5)
+        info2 = eng.set_queries(Qo2)
+        eng.search()
+        got2 = [eng.heap(iq) for iq in range(len(names2))]
+        eb2 = eng.ever_best(0, total)
+        idx2 = (info2.n_idx, info2.n_idx_m, info2.n_idx_c)
     bad = 0
     if check_oracle:
         ref = orc.search(qn, qs, None, nbest=nbest, acgt=acgt, refs=[(rn, [r.tobytes() for r in R])], pool=64)
@@ -67,6 +75,20 @@ def run_case(rank, world, L, nq, nr, nbest, acgt=False, amb=0.0, first_round=64,
                     bad += 1
             if not np.array_equal(eb, one.ever_best(0, total)):
                 bad += 1000
+            i2 = one.set_queries(Qo2)
+            one.search()
+            for iq in range(len(names2)):
+                sc, rf = one.heap(iq)
+                if not (np.array_equal(got2[iq][0], sc) and np.array_equal(got2[iq][1], rf)):
+                    bad += 1
+            if not np.array_equal(eb2, one.ever_best(0, total)):
+                bad += 1000
+            if idx2 != (i2.n_idx, i2.n_idx_m, i2.n_idx_c):
+                bad += 100000
+    if check_oracle:                                                    # every rank got the same site-set sizes through the broadcast
+        c2, x2, xm2, xc2 = orc.partition(Qo2, 0, acgt)
+        if idx2 != (len(x2), len(xm2), len(xc2)):
+            bad += 100000
     t = torch.tensor([bad], device=f"cuda:{dev}")
     dist.all_reduce(t)
     if rank == 0:

@@ -42,6 +42,7 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Bcast)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;      // optional
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
     bool load(std::string& err)
@@ -54,6 +55,7 @@ struct NcclApi {
         CommInitRank = (decltype(CommInitRank))dlsym(handle, "ncclCommInitRank");
         AllGather = (decltype(AllGather))dlsym(handle, "ncclAllGather");
         AllReduce = (decltype(AllReduce))dlsym(handle, "ncclAllReduce");
+        Bcast = (decltype(Bcast))dlsym(handle, "ncclBroadcast");
         CommDestroy = (decltype(CommDestroy))dlsym(handle, "ncclCommDestroy");
         GetErrorString = (decltype(GetErrorString))dlsym(handle, "ncclGetErrorString");
         if (!GetUniqueId || !CommInitRank || !AllGather || !AllReduce || !CommDestroy) { err = "NCCL symbols missing"; handle = nullptr; return false; }
@@ -402,7 +404,12 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     std::vector<uint8_t> site_class(L, 0);                                  // 1 = idx, 2 = idx_m, 3 = idx_c
     std::vector<uint8_t> pv(pivot_ok ? L : 0, 1);                           // pivot base per site (one-hot code)
     int n_idx = 0, n_idx_m = 0, n_idx_c = 0;
-    {
+    // Sharded contexts hold the same queries: once the communicator exists, rank 0 alone prepares them on the host and
+    // the arrays reach the other ranks by broadcast over NVLink (8 processes preparing the same planes on the host cores
+    // of one box cost 0.15 s per query set).  The other ranks only size their buffers.
+    const bool do_prep = !(c->world > 1 && c->comm && g_nccl.Bcast && c->rank != 0);
+    const bool bcast = c->world > 1 && c->comm && g_nccl.Bcast;
+    if (do_prep) {
         const int T = host_threads(std::min<int64_t>(Q, std::max<int64_t>(1, ((int64_t)256 << 20) / ((int64_t)L * 20))));
         std::vector<uint8_t> first((size_t)T * L, 0), any((size_t)T * L, 0), all((size_t)T * L, 1), same((size_t)T * L, 1);
         std::vector<uint32_t> cnt(pivot_ok ? (size_t)T * L * 4 : 0, 0);                // [thread][base][site]
@@ -465,8 +472,6 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     c->rows_cap = (c->n_qtiles + c->world - 1) / c->world * QTILE;
     c->qnib_stride = (L + 7) / 8;
     c->qinfo.n_query = Q; c->qinfo.nchar = L; c->qinfo.trim = trim;
-    c->qinfo.n_idx = n_idx; c->qinfo.n_idx_m = n_idx_m; c->qinfo.n_idx_c = n_idx_c;
-    if (info) *info = c->qinfo;
 
     // ---- planes, nibble codes and ambiguity lists of every slot (zero outside the trimmed range); for the pivot form
     // also the (base, equals-pivot) planes and, per slot, the bases that differ from the pivot.  One pass, host threads
@@ -478,7 +483,7 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     std::vector<std::vector<uint32_t>> amb(c->n_slots), snp(pivot_ok ? c->n_slots : 0);
     std::vector<QChunk2> qd2;
     if (pivot_ok) { qd2.resize(n_chunk_total); memset(qd2.data(), 0, n_chunk_total * sizeof(QChunk2)); }
-    parallel_ranges(c->n_slots, host_threads(c->n_slots), [&](int, int sa, int sb) {
+    if (do_prep) parallel_ranges(c->n_slots, host_threads(c->n_slots), [&](int, int sa, int sb) {
         std::vector<uint32_t> plain_in_chunk(c->n_chunks);
         for (int q = sa; q < sb; ++q) {
             const int qt = q / QTILE, qi = q % QTILE;
@@ -538,7 +543,7 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     std::vector<uint32_t> fix_off, fix_ent, pivot_words;
     std::vector<uint8_t> wslot;                                             // [tile][warp][j]: slot of the tile the warp counts
     int64_t n_fix_total = 0;
-    if (pivot_ok) {
+    if (pivot_ok && do_prep) {
         pivot_words.assign((size_t)(c->Wp / 4) * 8, 0u);                     // [unit][plane b0, b1][4 words]
         for (int s = 0; s < L; ++s) {
             const int w = s >> 5;
@@ -630,6 +635,30 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     }
 
     const auto t_host = std::chrono::steady_clock::now();
+    if (bcast) {
+        // what the other ranks cannot know: the form chosen, the sizes of the site sets and of the two variable lists
+        int64_t hdr[8] = {pivot_ok ? 1 : 0, n_idx, n_idx_m, n_idx_c, (int64_t)amb_ent.size(), (int64_t)fix_ent.size(), n_fix_total, 0x55564731};
+        int64_t* d_hdr = nullptr;
+        UVG_CUDA(c, cudaMalloc(&d_hdr, sizeof hdr));
+        UVG_CUDA(c, cudaMemcpyAsync(d_hdr, hdr, sizeof hdr, cudaMemcpyHostToDevice, c->st));
+        UVG_NCCL(c, g_nccl.Bcast(d_hdr, d_hdr, 8, ncclInt64, 0, c->comm, c->st));
+        UVG_CUDA(c, cudaMemcpyAsync(hdr, d_hdr, sizeof hdr, cudaMemcpyDeviceToHost, c->st));
+        UVG_CUDA(c, cudaStreamSynchronize(c->st));
+        cudaFree(d_hdr);
+        if (hdr[7] != 0x55564731) UVG_FAIL(c, UVG_ESTATE, "uvg_set_queries: the ranks disagree about the query broadcast");
+        if (!do_prep) {
+            pivot_ok = hdr[0] != 0; n_idx = (int)hdr[1]; n_idx_m = (int)hdr[2]; n_idx_c = (int)hdr[3]; n_fix_total = hdr[6];
+            amb_ent.assign((size_t)hdr[4], 0u);
+            if (pivot_ok) {
+                fix_ent.assign((size_t)hdr[5], 0u);
+                fix_off.assign(c->n_slots + 1, 0u);
+                pivot_words.assign((size_t)(c->Wp / 4) * 8, 0u);
+                wslot.assign((size_t)c->n_qtiles * QTILE, 0);
+            }
+        }
+    }
+    c->qinfo.n_idx = n_idx; c->qinfo.n_idx_m = n_idx_m; c->qinfo.n_idx_c = n_idx_c;
+    if (info) *info = c->qinfo;
     // ---- device allocations ----
     const int rows = c->rows_cap;
     UVG_CUDA(c, pooled_alloc(c, 0, &c->d_qdata, n_chunk_total * sizeof(QChunk)));
@@ -665,6 +694,15 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     UVG_CUDA(c, cudaMemcpyAsync(c->d_qnib, qnib.data(), qnib.size() * 4, cudaMemcpyHostToDevice, c->st));
     UVG_CUDA(c, cudaMemcpyAsync(c->d_qamb_off, amb_off.data(), amb_off.size() * 4, cudaMemcpyHostToDevice, c->st));
     if (!amb_ent.empty()) UVG_CUDA(c, cudaMemcpyAsync(c->d_qamb_ent, amb_ent.data(), amb_ent.size() * 4, cudaMemcpyHostToDevice, c->st));
+    auto share = [&](void* d, size_t bytes) -> ncclResult_t {             // rank 0's array to everybody (stream order: after its upload)
+        return bytes ? g_nccl.Bcast(d, d, bytes, ncclUint8, 0, c->comm, c->st) : 0;
+    };
+    if (bcast) {
+        UVG_NCCL(c, share(c->d_qdata, n_chunk_total * sizeof(QChunk)));
+        UVG_NCCL(c, share(c->d_qnib, qnib.size() * 4));
+        UVG_NCCL(c, share(c->d_qamb_off, amb_off.size() * 4));
+        UVG_NCCL(c, share(c->d_qamb_ent, amb_ent.size() * 4));
+    }
     if (pivot_ok) {
         UVG_CUDA(c, pooled_alloc(c, 15, &c->d_qdata2, n_chunk_total * sizeof(QChunk2)));
         UVG_CUDA(c, pooled_alloc(c, 16, &c->d_qfix_off, fix_off.size() * 4));
@@ -676,6 +714,13 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
         UVG_CUDA(c, cudaMemcpyAsync(c->d_qfix_off, fix_off.data(), fix_off.size() * 4, cudaMemcpyHostToDevice, c->st));
         if (!fix_ent.empty()) UVG_CUDA(c, cudaMemcpyAsync(c->d_qfix_ent, fix_ent.data(), fix_ent.size() * 4, cudaMemcpyHostToDevice, c->st));
         UVG_CUDA(c, cudaMemcpyAsync(c->d_pivot, pivot_words.data(), pivot_words.size() * 4, cudaMemcpyHostToDevice, c->st));
+        if (bcast) {
+            UVG_NCCL(c, share(c->d_wslot, wslot.size()));
+            UVG_NCCL(c, share(c->d_qdata2, n_chunk_total * sizeof(QChunk2)));
+            UVG_NCCL(c, share(c->d_qfix_off, fix_off.size() * 4));
+            UVG_NCCL(c, share(c->d_qfix_ent, fix_ent.size() * 4));
+            UVG_NCCL(c, share(c->d_pivot, pivot_words.size() * 4));
+        }
         c->pivot_on = true;
         // references that are already resident get their derived planes now (one pass over the packed database)
         int rc2 = ensure_db2(c);
