@@ -81,7 +81,7 @@ struct uvg_ctx {
     uvg_query_info qinfo{};
     int64_t qinfo_pivot_fix = -1;
     double set_queries_host_ms = 0, set_queries_device_ms = 0;                     // fix entries of the pivot form (-1: general kernel)
-    size_t qcap[24]{};                                // single GPU: bytes of the query-side device arrays, kept across query sets (pooled_alloc)
+    size_t qcap[24]{};                                // bytes of the query-side device arrays, kept across query sets (pooled_alloc)
     QChunk* d_qdata = nullptr;
     uint32_t *d_qnib = nullptr, *d_qamb_off = nullptr, *d_qamb_ent = nullptr;
     // pivot form of the pair-count kernel (pairpivot.cu): chosen per query set by uvg_set_queries
@@ -232,9 +232,9 @@ static void close_peers(uvg_ctx* c)
     c->peers_ready = false;
 }
 
-// query-side device arrays.  On a single GPU they are kept for the next query set (same sizes in a serving loop: no
-// cudaFree / cudaMalloc per uvg_set_queries, whose cost varies from microseconds to hundreds of milliseconds); pooled_alloc
-// grows them when needed.  Sharded contexts (peer-mapped tiles) and uvg_destroy release everything.
+// query-side device arrays and the score tiles (peer-mapped in sharded mode) are kept for the next query set (same sizes
+// in a serving loop: no cudaFree / cudaMalloc / IPC unmapping per uvg_set_queries, whose cost varies from microseconds to
+// hundreds of milliseconds); pooled_alloc grows them when needed.  uvg_destroy releases everything.
 template <typename T>
 static cudaError_t pooled_alloc(uvg_ctx* c, int slot, T** p, size_t bytes)
 {
@@ -248,9 +248,9 @@ static cudaError_t pooled_alloc(uvg_ctx* c, int slot, T** p, size_t bytes)
 
 static void free_queries(uvg_ctx* c, bool final = false)
 {
-    close_peers(c);
     c->pivot_on = false;
-    if (c->world == 1 && !final) { c->seg_cap = 0; c->tile_elems = 0; return; }
+    if (!final) { c->seg_cap = 0; c->tile_elems = 0; return; }
+    close_peers(c);
     for (size_t& b : c->qcap) b = 0;
     cudaFree(c->d_qdata); cudaFree(c->d_qnib); cudaFree(c->d_qamb_off); cudaFree(c->d_qamb_ent);
     cudaFree(c->d_qdata2); cudaFree(c->d_qfix_off); cudaFree(c->d_qfix_ent); cudaFree(c->d_pivot); cudaFree(c->d_wslot); c->d_wslot = nullptr;
@@ -259,7 +259,7 @@ static void free_queries(uvg_ctx* c, bool final = false)
     cudaFree(c->d_heaps); cudaFree(c->d_heaps_all);
     cudaFree(c->d_heap_n); cudaFree(c->d_max_inc); cudaFree(c->d_batch_id); cudaFree(c->d_max_inc_batch);
     cudaFree(c->d_heap_n_all); cudaFree(c->d_max_inc_all);
-    if (c->world > 1 || final) { cudaFree(c->d_tiles); c->d_tiles = nullptr; c->tiles_alloc = 0; }
+    cudaFree(c->d_tiles); c->d_tiles = nullptr; c->tiles_alloc = 0;
     c->d_qdata = nullptr; c->d_qnib = c->d_qamb_off = c->d_qamb_ent = nullptr; c->d_thr_local = nullptr;
     c->d_heaps = c->d_heaps_all = nullptr;
     c->d_heap_n = c->d_max_inc = c->d_batch_id = c->d_max_inc_batch = c->d_heap_n_all = c->d_max_inc_all = nullptr;
@@ -684,6 +684,8 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
         c->seg_cap = cap;
         c->tile_elems = (size_t)(rows + 2) * c->world * cap;
         if (NBUF * c->tile_elems > c->tiles_alloc) {                       // the multi-GiB buffer is kept when the next query set fits
+            if (c->world > 1) close_peers(c);                                // (every rank takes this branch alike: the size depends on shared parameters only);
+                                                                             // the new buffer is mapped by the peers at the next search
             cudaFree(c->d_tiles); c->d_tiles = nullptr; c->tiles_alloc = 0;
             UVG_CUDA(c, cudaMalloc(&c->d_tiles, NBUF * c->tile_elems * sizeof(uint4)));
             c->tiles_alloc = NBUF * c->tile_elems;
