@@ -15,6 +15,7 @@
 #include <fcntl.h>
 #include <getopt.h>
 #include <pthread.h>
+#include <sched.h>
 #include <semaphore.h>
 #include <stdarg.h>
 #include <stdint.h>
@@ -323,7 +324,7 @@ static void writer_close(writer_t* w) { if (w->pipe && pclose(w->pipe) != 0) die
 /* ---------------------------------------------------------------------------------------------------------------
  * reference stream: the reader thread (nearest.c:245-286 without the scoring)
  * ------------------------------------------------------------------------------------------------------------- */
-typedef struct { unsigned char* text; char** name; long n; int last; } batch_t;
+typedef struct { unsigned char* text; char** name; long n; int last; long fend[1025]; int n_fend; } batch_t;   /* fend: rows of the batch before each file end */
 typedef struct {
     const char** file; int n_files, L, min_non_n; long batch_rows;
     const nameset_t* qset; double t0;
@@ -384,7 +385,7 @@ static void stream_take(stream_pos_t* ps, char* name, const unsigned char* seq, 
         ps->k ^= 1;
         sem_wait(&sp->free_slots);
         ps->bt = &sp->batch[ps->k];
-        ps->bt->n = 0; ps->bt->last = 0;
+        ps->bt->n = 0; ps->bt->last = 0; ps->bt->n_fend = 0;
     }
 }
 
@@ -499,7 +500,7 @@ static void* stream_reader(void* arg)
     stream_pos_t pos = {sp, NULL, 0};
     sem_wait(&sp->free_slots);
     pos.bt = &sp->batch[0];
-    pos.bt->n = 0; pos.bt->last = 0;
+    pos.bt->n = 0; pos.bt->last = 0; pos.bt->n_fend = 0;
     for (int j = 0; j < sp->n_files; ++j) {
         const double t1 = now_s();
         if (!stream_file_parallel(&pos, sp->file[j])) {
@@ -508,6 +509,7 @@ static void* stream_reader(void* arg)
             while (fasta_next(&f)) { char* nm = f.name; f.name = NULL; stream_take(&pos, nm, f.seq, f.len); }
             fasta_close(&f);
         }
+        pos.bt->fend[pos.bt->n_fend++] = pos.bt->n;          /* the reference's batch ends with the file (nearest.c:245-286) */
         fprintf(stderr, "Finished reading file %s in %.3lf secs;\n", sp->file[j], now_s() - t1);
     }
     pos.bt->last = 1;
@@ -519,13 +521,13 @@ static void* stream_reader(void* arg)
  * --cache FILE: the packed references of a run (uvg_export_packed blobs + names + which FASTA records were accepted),
  * so that the next run over the same reference files skips reading, parsing and encoding them.  Layout (host endian):
  *   "UVGCACHE" u32 version, i32 nchar, i32 acgt, i32 min_non_n, i32 n_files, i32 pad; per file: u64 size, i64 mtime
- *   records: u64 tag (1 blob, 2 record map, 3 end) ...
+ *   records: u64 tag (1 blob, 2 record map, 3 end, 4 file end: u64 accepted references up to here) ...
  *     blob:       u64 blob_bytes, u64 n_refs, u64 names_bytes, blob, names (NUL terminated each), padding to 8
  *     record map: u64 n_rec, i64 count, i64 n_invalid, rec_ok[n_rec], padding to 8
  * A cache is used only if nchar, mode, the -A threshold and the size and mtime of every -r file match; not with -x (the
  * set of pushed references then depends on the query names).
  * ------------------------------------------------------------------------------------------------------------- */
-#define CACHE_VERSION 1u
+#define CACHE_VERSION 2u
 typedef struct { FILE* fp; char* path; char* tmp; void* buf; size_t buf_cap; int64_t exported, base; } cache_writer_t;
 
 static void cache_put(FILE* fp, const void* p, size_t n) { if (n && fwrite(p, 1, n, fp) != n) die("cannot write the cache file"); }
@@ -601,13 +603,26 @@ static void usage(const char* prog, int full)
            "      --acgt             considers only ACGT sites in query sequences (mismatch-based)\n"
            "  -k, --keep_resolved    keep more resolved and exclude redundant query seqs (default is to keep all)\n"
            "  -x, --exclude_self     exclude reference sequences with same name as a query sequence\n"
-           "  -p, --pool             pool size of the reference program (only used to flag pool-dependent results, hazard H1)\n"
+           "  -p, --pool             batch size of the reference program (default 64 per thread); its table can depend on it and\n"
+           "                         the search reproduces the table of this batch size\n"
            "  -r, --reference        aligned reference sequences (can be several files)\n"
            "  -t, --nthreads         accepted for compatibility (scoring runs on the GPU)\n"
            "  -o, --output           prefix of xzipped output alignment and table with nearest neighbour sequences\n"
            "      --device           CUDA device ordinal (default 0);  --batch: reference rows per push (default 65536)\n"
            "      --cache            file that keeps the packed references of this run; a later run over the same reference\n"
            "                         files (same size and mtime, same -A, same mode) reads it instead of parsing them\n");
+}
+
+/* what omp_get_max_threads() answers in the reference program before -t is applied (nearest.c:81): OMP_NUM_THREADS when it
+ * is set, else the processors this process may run on */
+static int omp_max_threads_like(void)
+{
+    const char* e = getenv("OMP_NUM_THREADS");
+    if (e && atoi(e) > 0) return atoi(e);
+    cpu_set_t set;
+    if (!sched_getaffinity(0, sizeof set, &set) && CPU_COUNT(&set) > 0) return CPU_COUNT(&set);
+    const long n = sysconf(_SC_NPROCESSORS_ONLN);
+    return n > 0 ? (int)n : 1;
 }
 
 int main(int argc, char** argv)
@@ -675,12 +690,13 @@ int main(int argc, char** argv)
     if (ambig_r < 0.001) ambig_r = 0.001;
     if (ambig_r > 1.) ambig_r = 1.;
     if (nbest < 1) nbest = 1;
-    if (pool < 1) pool = 64 * (int)sysconf(_SC_NPROCESSORS_ONLN);               /* nearest.c:80: 64 per thread */
+    if (pool < 1) pool = 64 * omp_max_threads_like();                            /* nearest.c:81: 64 x omp_get_max_threads(), set before -t is read */
     if (batch_rows < 1) batch_rows = 1;
     if (!out_prefix) out_prefix = acgt ? "nn_uvaia_acgt" : "nn_uvaia";          /* nearest.c:198-200 */
     init_tables();
     const double t0 = now_s();
     fprintf(stderr, "program: uvaia_b200 package: %s\n", PROGRAM_VERSION);
+    fprintf(stderr, "Creating a queue of %d sequences; for each query, the %d closest sequences will be stored\n", pool, nbest);   /* nearest.c:192 */
 
     /* 1. queries */
     int n_read = 0;
@@ -778,6 +794,10 @@ int main(int argc, char** argv)
                 if (uvg_import_packed(gpu, buf, bytes, &got) || got != n) die("%s", uvg_last_error(gpu));
                 if (uvg_search_async(gpu)) die("%s", uvg_last_error(gpu));
                 if (n % 32 || uvg_db_count(gpu) >= max_resident) { if (uvg_wait(gpu) || uvg_drop_refs(gpu)) die("%s", uvg_last_error(gpu)); }
+            } else if (tag == 4) {
+                uint64_t e = 0;
+                if (!cache_get(cache_in, &e, 8)) die("the cache file %s is truncated (delete it)", cache_path);
+                if (uvg_mark_file_end(gpu, (int64_t)e)) die("%s", uvg_last_error(gpu));
             } else if (tag == 2) {
                 uint64_t nr = 0; int64_t v[2];
                 if (!cache_get(cache_in, &nr, 8) || !cache_get(cache_in, v, sizeof v)) die("the cache file %s is truncated (delete it)", cache_path);
@@ -806,19 +826,30 @@ int main(int argc, char** argv)
         for (int k = 0;; k ^= 1) {
             sem_wait(&sp.full_slots);
             batch_t* bt = &sp.batch[k];
-            if (bt->n > 0) {
-                int64_t na = 0;
-                if (uvg_push_refs(gpu, bt->text, bt->n, min_non_n, NULL, accepted, &na)) die("%s", uvg_last_error(gpu));
-                if (n_acc_total + na > rname_cap) { rname_cap = 2 * (n_acc_total + na) + 1024; rname = xrealloc(rname, rname_cap * sizeof *rname); }
-                if (n_pushed + bt->n > push_cap) { push_cap = 2 * (n_pushed + bt->n) + 1024; push_ok = xrealloc(push_ok, push_cap); }
-                for (long i = 0; i < bt->n; ++i) {
-                    push_ok[n_pushed++] = accepted[i];
-                    if (accepted[i]) rname[n_acc_total++] = bt->name[i]; else { free(bt->name[i]); ++n_invalid; }
+            /* the rows of a batch go to the device in pieces that end where a file ends: uvg_mark_file_end tells the library
+             * where the reference's --pool batches restart (nearest.c:245-286) */
+            long row0 = 0;
+            for (int fe = 0; fe <= bt->n_fend; ++fe) {
+                const long row1 = fe < bt->n_fend ? bt->fend[fe] : bt->n, m = row1 - row0;
+                if (m > 0) {
+                    int64_t na = 0;
+                    if (uvg_push_refs(gpu, bt->text + (size_t)row0 * L, m, min_non_n, NULL, accepted, &na)) die("%s", uvg_last_error(gpu));
+                    if (n_acc_total + na > rname_cap) { rname_cap = 2 * (n_acc_total + na) + 1024; rname = xrealloc(rname, rname_cap * sizeof *rname); }
+                    if (n_pushed + m > push_cap) { push_cap = 2 * (n_pushed + m) + 1024; push_ok = xrealloc(push_ok, push_cap); }
+                    for (long i = 0; i < m; ++i) {
+                        push_ok[n_pushed++] = accepted[i];
+                        if (accepted[i]) rname[n_acc_total++] = bt->name[row0 + i]; else { free(bt->name[row0 + i]); ++n_invalid; }
+                    }
+                    if (uvg_search_async(gpu)) die("%s", uvg_last_error(gpu));
+                    const int drop = uvg_db_count(gpu) >= max_resident;
+                    cache_flush(&cw, gpu, rname, drop);
+                    if (drop) { if (uvg_wait(gpu) || uvg_drop_refs(gpu)) die("%s", uvg_last_error(gpu)); }
                 }
-                if (uvg_search_async(gpu)) die("%s", uvg_last_error(gpu));
-                const int drop = uvg_db_count(gpu) >= max_resident;
-                cache_flush(&cw, gpu, rname, drop);
-                if (drop) { if (uvg_wait(gpu) || uvg_drop_refs(gpu)) die("%s", uvg_last_error(gpu)); }
+                if (fe < bt->n_fend) {
+                    if (uvg_mark_file_end(gpu, n_acc_total)) die("%s", uvg_last_error(gpu));
+                    if (cw.fp) { const uint64_t rec[2] = {4, (uint64_t)n_acc_total}; cache_put(cw.fp, rec, sizeof rec); }
+                }
+                row0 = row1;
             }
             const int last = bt->last;
             sem_post(&sp.free_slots);
@@ -875,8 +906,8 @@ int main(int argc, char** argv)
                     "Highest number of ACGT mismatches = %lld in current neighbourhood.\n", count, n_output, n_invalid, (long long)st.max_mismatch);
     fprintf(stderr, "Saved %ld sequences to file %s , %.3lf secs elapsed.\n", n_output, outname, now_s() - t0);
     if (st.n_h1_flags)
-        fprintf(stderr, "Note: %lld admissions may depend on --pool in the reference program (its consensus stage truncates per batch); "
-                        "the table below is the pool-independent result.\n", (long long)st.n_h1_flags);
+        fprintf(stderr, "Note: %lld pairs were scored with consensus counts truncated at the batch-wide limit, as the reference program does "
+                        "with --pool %d (its table depends on the pool size for this input).\n", (long long)st.n_h1_flags, pool);
 
     /* 4. <prefix>.csv.xz (save_distance_table, nearest.c:513-547) */
     sprintf(outname, "%s.csv.xz", out_prefix);

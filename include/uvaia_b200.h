@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define UVG_ABI_VERSION 1
+#define UVG_ABI_VERSION 2
 
 enum { UVG_OK = 0, UVG_EINVAL = -1, UVG_ENODEV = -2, UVG_ENOMEM = -3, UVG_ECUDA = -4, UVG_ESTATE = -5, UVG_ENCCL = -6 };
 
@@ -47,17 +47,25 @@ typedef struct uvg_params {
     int32_t trim;           /* --trim, clamped by the library like fastaseq.c:708-712 */
     int32_t nbest;          /* --nbest; heap capacity is max(2, nbest) (min_heap.c:58) */
     int32_t acgt_mode;      /* --acgt */
-    int32_t pool;           /* --pool: only used to detect hazard H1 (pool-dependent truncation) */
+    int32_t pool;           /* --pool: accepted references per batch of the reference program (nearest.c:81,250).  The reference's
+                               consensus stage is truncated at a batch-wide limit (nearest.c:290-291,432), so its table can depend
+                               on this value (hazard H1); the search reproduces the table of THIS pool size */
     int32_t device;         /* CUDA ordinal */
     int32_t first_round;    /* references in the first scoring round per rank (0 = default 1024) */
-    int32_t max_round;      /* largest round per rank (0 = default 65536; also capped so the score tile stays <= 2 GiB) */
+    int32_t max_round;      /* largest round per rank (0 = default 65536).  Single GPU: also capped so that a score tile stays
+                               <= 3 GiB.  Sharded: never capped -- (first_round, max_round) is the row distribution of
+                               uvg_shard_of; uvg_set_queries fails with UVG_ENOMEM if the tiles of a query set do not fit */
     int32_t early_abort;    /* 1 = warp-granular abort of pairs that cannot beat the k-th best (exact, perf only) */
     int32_t rank, world;    /* row sharding: this context holds tile `rank` of every round (world<=1: single GPU) */
     int32_t pair_kernel;    /* UVG_PAIR_AUTO (0): pivot form of the pair-count kernel when the mode and the query set allow it
                                (default mode, < 65,536 columns, no early abort, queries close to one pivot sequence), else the
                                general 3-plane kernel; UVG_PAIR_GENERAL / UVG_PAIR_PIVOT force one (PIVOT only skips the
                                closeness test).  Results are identical either way. */
-    int32_t reserved1;      /* must be 0 */
+    int32_t closed_form;    /* 0 (default): literal emulation of the reference's batches -- the table is the reference's for this
+                               --pool and these file boundaries (uvg_mark_file_end); costs one replay launch per batch.
+                               1: pool-independent closed form (= the reference at --pool 1) in one replay launch per round;
+                               uvg_stats.n_h1_flags counts the pairs the reference might have scored differently (0 => the
+                               table is the reference's for every --pool).  Sharded contexts (world > 1) always run this form. */
     int64_t db_capacity;    /* references to reserve HBM for (0 = grow on demand) */
 } uvg_params;
 
@@ -70,7 +78,8 @@ typedef struct uvg_stats {
     int64_t n_refs;             /* references scored so far */
     int64_t n_rounds;
     int64_t n_admitted;         /* successful heap insertions */
-    int64_t n_h1_flags;         /* admissions that MAY depend on --pool in the reference (hazard H1) */
+    int64_t n_h1_flags;         /* closed form: pairs the reference MAY have scored differently for this --pool (hazard H1);
+                                   literal emulation: pairs that reached the heap with truncated consensus counts */
     int64_t pair_kernel_launches, other_kernel_launches;
     double  pair_kernel_ms;     /* CUDA-event time of the pair-count launches of the last uvg_search */
     double  replay_ms;          /* ... of bucket+replay */
@@ -120,6 +129,10 @@ int uvg_drop_refs(uvg_ctx* ctx);
 /* Forget every reference and restart ordinals at 0 (heaps are emptied too). */
 int uvg_clear_refs(uvg_ctx* ctx);
 int64_t uvg_db_count(const uvg_ctx* ctx);              /* accepted references resident on this rank */
+/* The references accepted so far end a -r file: the reference's batch ends with its file and the next file starts a new
+ * batch (nearest.c:245-286).  n_accepted_so_far = accepted references of all files up to here, or -1 = what this context
+ * has been given (single GPU).  Call it after the last uvg_push_refs of each file, before the next push. */
+int uvg_mark_file_end(uvg_ctx* ctx, int64_t n_accepted_so_far);
 
 /* ---- packed reference cache (no counterpart in the reference, which re-reads the FASTA text on every run) ----
  * The packed references leave and enter the device as they are: planes of whole groups of 32 references, non_n and the
@@ -148,7 +161,11 @@ int uvg_reset_search(uvg_ctx* ctx);
  * out must hold max(2,nbest) items; rows come in the reference's output order (heap array after the slot0<->slot n
  * swap, then libc qsort with compare_q_item); *n = rows (hazard H2: never the NULL-name rows). */
 int uvg_get_heap(uvg_ctx* ctx, int32_t iq, uvg_item* out, int32_t* n);
-/* flags[i] = 1 if accepted reference ordinal first+i ever entered any heap (is_best, nearest.c:303-314). */
+/* Every query's table in one call (one device->host copy, the qsorts on host threads): out holds n_query x max(2,nbest)
+ * items, the rows of query iq start at out + iq * max(2,nbest); n[iq] = rows of query iq. */
+int uvg_get_all_heaps(uvg_ctx* ctx, uvg_item* out, int32_t* n);
+/* flags[i] = 1 if accepted reference ordinal first+i ever entered any heap (is_best, nearest.c:303-314).  Sharded contexts:
+ * COLLECTIVE -- the first call after a search combines the flags of all ranks (NCCL all-reduce), so every rank calls it. */
 int uvg_get_ever_best(uvg_ctx* ctx, int64_t first, int64_t n, uint8_t* flags);
 int uvg_get_stats(uvg_ctx* ctx, uvg_stats* out);
 

@@ -404,6 +404,19 @@ def case_bundled():
     rf = b"".join(b">" + names[i] + b"\n" + seqs[i] + b"\n" for i in ri)
     save_case("real_c1_small", qf, [rf], ["-n", "10"],
               "config-1 shape: 20 queries x 400 references sampled (seed 20261104) from the reference's bundled data/03.unique_acgt.aln.xz")
+    # BASELINE.json configs[0] at its stated shape (SURVEY.md 8c golden iv): 100 sampled queries against the remaining
+    # 9,085 sequences of the bundled alignment, nbest 10 -- and the same with the database order reversed (the n-best SET
+    # depends on the order for most queries)
+    random.seed(20261104)
+    qi = random.sample(range(len(names)), 100)
+    qset = set(qi)
+    ri = [i for i in range(len(names)) if i not in qset]
+    qf = b"".join(b">" + names[i] + b"\n" + seqs[i] + b"\n" for i in qi)
+    rf = b"".join(b">" + names[i] + b"\n" + seqs[i] + b"\n" for i in ri)
+    save_case("real_c1_full", qf, [rf], ["-n", "10"],
+              "BASELINE config 1: 100 queries (random.seed(20261104); random.sample(range(9185), 100)) x the remaining 9,085 sequences of data/03.unique_acgt.aln.xz")
+    rf = b"".join(b">" + names[i] + b"\n" + seqs[i] + b"\n" for i in reversed(ri))
+    save_case("real_c1_full_reversed", qf, [rf], ["-n", "10"], "BASELINE config 1 with the database in reverse file order")
 
 
 GROUPS = {"unit": make_unit_vectors, "synthetic": case_synthetic, "ties": case_ties, "ambiguous": case_ambiguous,

@@ -65,7 +65,8 @@ def run_case(rank, world, L, nq, nr, nbest, acgt=False, amb=0.0, first_round=64,
         if not np.array_equal(np.nonzero(eb)[0], np.array(ref.ever_best, np.int64)):
             bad += 1000
     if rank == 0:
-        with Engine(L, nbest=nbest, acgt=acgt, pool=64, device=dev, first_round=first_round, max_round=max_round) as one:
+        # sharded contexts run the pool-independent closed form (uvg_params.closed_form): compare like with like
+        with Engine(L, nbest=nbest, acgt=acgt, pool=64, device=dev, first_round=first_round, max_round=max_round, closed_form=True) as one:
             one.set_queries(Qo)
             one.push_refs(Racc, min_non_n)
             one.search()
@@ -108,6 +109,9 @@ def main():
     ok &= run_case(rank, world, 2000, 130, 2500, 10, acgt=True)
     ok &= run_case(rank, world, 1500, 65, 999, 100, first_round=32, max_round=64, early_abort=True)
     ok &= run_case(rank, world, 29903, 300, 6000, 100, first_round=256, max_round=1024, check_oracle=False)
+    # many queries and full-size rounds: the score tiles exceed the 3 GiB a single-GPU context caps them at, and the round
+    # schedule of the shards must still be the one uvg_shard_of deals the rows with (first_round, max_round only)
+    ok &= run_case(rank, world, 400, 4200, 140000, 10, first_round=16384, max_round=65536, check_oracle=False, seed=11)
     dist.barrier()
     dist.destroy_process_group()
     if rank == 0:

@@ -42,15 +42,26 @@ def gpu_csv(case, **engine_kw):
 # ---------------------------------------------------------------------------------------------------------------
 # golden tables of the reference binary
 # ---------------------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("name", NON_H1)
+@pytest.mark.parametrize("name", case_names())
 def test_golden_csv_bit_exact(name):
+    """ALL cases, the pool-dependent ones (hazard H1) included: the search emulates the reference's --pool batches"""
     c = Case(name)
     out, csv = gpu_csv(c)
     assert csv == c.expected_csv
     # .aln.xz content: every reference that ever entered a heap, in file order (nearest.c:303-314)
     got = [out.ref_names[i] for i in np.nonzero(out.ever_best)[0]]
     assert got == c.expected_aln_names
-    assert out.stats["n_h1_flags"] == 0
+    if not c.h1:
+        assert out.stats["n_h1_flags"] == 0
+
+
+@pytest.mark.parametrize("name", H1)
+@pytest.mark.parametrize("knobs", [dict(first_round=32, max_round=64), dict(batch_rows=97), dict(batch_rows=5, first_round=64, max_round=64)])
+def test_h1_cases_independent_of_round_schedule(name, knobs):
+    """the reference's batches are independent of how the host cuts its pushes and of the scoring rounds"""
+    c = Case(name)
+    _, csv = gpu_csv(c, **knobs)
+    assert csv == c.expected_csv
 
 
 @pytest.mark.parametrize("name", ["syn_default", "syn_acgt", "syn_n100", "ties_n5", "amb_default", "c2_shape", "syn_exclude_self"])
@@ -64,12 +75,12 @@ def test_golden_csv_independent_of_round_schedule(name, knobs):
 
 
 @pytest.mark.parametrize("name", H1)
-def test_h1_hazard_is_detected(name):
-    """the reference's own output depends on --pool for these inputs.  The CUDA path computes the
-    pool-independent closed form and must FLAG that the reference would have truncated (never silently differ)."""
+def test_closed_form_mode_flags_the_h1_hazard(name):
+    """uvg_params.closed_form = 1: the pool-independent closed form (what sharded contexts run).  It must equal the
+    oracle's closed form and FLAG that the reference would have truncated (never silently differ)."""
     c = Case(name)
     kw = c.options()
-    out, csv = gpu_csv(c)
+    out, csv = gpu_csv(c, closed_form=True)
     closed = orc.run_files(c.query_file, c.ref_files, **kw).csv(kw["acgt"])
     assert csv == closed
     lit = orc.run_files(c.query_file, c.ref_files, literal=True, **kw)
@@ -181,7 +192,22 @@ def run_vs_oracle(L, nq, nr, nbest, acgt=False, trim=0, amb=0.0, seed=5, ambig_r
     rs = [r.tobytes() for r in R]
     ref = orc.search(qn, qs, None, nbest=nbest, trim=trim, acgt=acgt, refs=[(rn, rs)], pool=64, ambig_r=ambig_r)
     names, Qo, tr, *_ = orc.prepare_queries(qn, qs, trim, acgt, 0.5)
-    with Engine(L, nbest=nbest, trim=trim, acgt=acgt, pool=64, **engine_kw) as eng:
+    if nq * nr <= 60000:
+        # small enough for the oracle's literal (staged, truncated, batch by batch) mode: the library's default mode
+        # emulates the reference's --pool batches and must agree with it even where the closed form does not
+        for pool in (64, 5):
+            lit = orc.search(qn, qs, None, nbest=nbest, trim=trim, acgt=acgt, refs=[(rn, rs)], pool=pool, ambig_r=ambig_r, literal=True)
+            with Engine(L, nbest=nbest, trim=trim, acgt=acgt, pool=pool, **engine_kw) as eng:
+                eng.set_queries(Qo)
+                eng.push_refs(R, int(L * (1 - ambig_r)))
+                eng.search()
+                for iq in range(len(names)):
+                    sc, refs = eng.heap(iq)
+                    want = lit.rows[iq]
+                    assert np.array_equal(sc, np.array([w[0] for w in want], np.int32).reshape(-1, 6)), f"literal, pool {pool}, query {iq}"
+                    assert np.array_equal(refs, np.array([w[2] for w in want], np.int64)), f"literal, pool {pool}, query {iq}"
+                assert np.array_equal(np.nonzero(eng.ever_best(0, eng.db_count))[0], np.array(lit.ever_best, np.int64))
+    with Engine(L, nbest=nbest, trim=trim, acgt=acgt, pool=64, closed_form=True, **engine_kw) as eng:
         eng.set_queries(Qo)
         nn, acc, na = eng.push_refs(R, int(L * (1 - ambig_r)))
         eng.search()
@@ -339,6 +365,34 @@ def test_vs_live_reference_binary(seed, acgt, trim, nbest):
         assert p.returncode == 0, p.stderr.decode()[-500:]
         want = gzip.decompress(open(os.path.join(wd, "o.csv.xz"), "rb").read()).decode()
         out = host.search_files(qf, [rf], nbest=nbest, trim=trim, acgt=acgt, first_round=256, max_round=1024)
+    assert out.csv(acgt) == want
+
+
+@pytest.mark.skipif(not os.path.exists(REF_BIN), reason="oracle/_ref/uvaia_ref not present")
+@pytest.mark.parametrize("nq,acgt,seed", [(1, False, 301), (1, True, 302), (2, False, 303), (3, False, 304), (3, True, 305), (1, False, 306)])
+@pytest.mark.parametrize("pool", [1, 7, 64, 512])
+def test_pool_dependence_vs_live_reference_binary(nq, acgt, seed, pool):
+    """hazard H1 against the reference program itself: one to three queries (every / most sites are consensus sites),
+    N-rich references in two files, and the table the reference writes for this --pool"""
+    L = 1500
+    m = SynthModel(nsites=L, n_clades=6, seed=seed, clade_subs=12)
+    qn, Q = m.sample(nq, seed + 1, ambiguous_frac=0.0 if seed != 306 else 0.02, prefix="Q")
+    rn, R = m.sample(1300, seed + 2, ambiguous_frac=0.01, prefix="R")
+    rng = np.random.default_rng(seed)
+    for r in R:                                  # N runs anywhere: the consensus-stage mismatches move around
+        for _ in range(int(rng.integers(0, 4))):
+            a = int(rng.integers(0, L - 50))
+            r[a:a + int(rng.integers(5, 200))] = ord("N")
+    with tempfile.TemporaryDirectory() as wd:
+        qf, rf1, rf2 = os.path.join(wd, "q.fa"), os.path.join(wd, "r1.fa"), os.path.join(wd, "r2.fa")
+        write_fasta(qf, qn, Q)
+        write_fasta(rf1, rn[:801], R[:801], width=80)
+        write_fasta(rf2, rn[801:], R[801:])
+        cmd = [REF_BIN, "-n", "12", "-t", "2", "-p", str(pool)] + (["--acgt"] if acgt else []) + ["-r", rf1, "-r", rf2, "-o", os.path.join(wd, "o"), qf]
+        p = subprocess.run(cmd, cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert p.returncode == 0, p.stderr.decode()[-500:]
+        want = gzip.decompress(open(os.path.join(wd, "o.csv.xz"), "rb").read()).decode()
+        out = host.search_files(qf, [rf1, rf2], nbest=12, acgt=acgt, pool=pool, first_round=128, max_round=512, batch_rows=333)
     assert out.csv(acgt) == want
 
 

@@ -61,7 +61,7 @@ def read_fasta_text(raw):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", NON_H1)
+@pytest.mark.parametrize("name", case_names())
 def test_host_program_reproduces_the_reference_outputs(name, tmp_path):
     c = Case(name)
     args = list(c.args)

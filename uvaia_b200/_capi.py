@@ -11,7 +11,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("UVG_LIB") or os.path.join(_HERE, "lib", "libuvaia_b200.so")     # UVG_LIB: kernel-variant experiments
 
-UVG_ABI_VERSION = 1
+UVG_ABI_VERSION = 2
 
 
 class uvg_item(C.Structure):
@@ -22,7 +22,7 @@ class uvg_params(C.Structure):
     _fields_ = [("abi_version", C.c_int32), ("nchar", C.c_int32), ("trim", C.c_int32), ("nbest", C.c_int32),
                 ("acgt_mode", C.c_int32), ("pool", C.c_int32), ("device", C.c_int32), ("first_round", C.c_int32),
                 ("max_round", C.c_int32), ("early_abort", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
-                ("pair_kernel", C.c_int32), ("reserved1", C.c_int32), ("db_capacity", C.c_int64)]
+                ("pair_kernel", C.c_int32), ("closed_form", C.c_int32), ("db_capacity", C.c_int64)]
 
 
 class uvg_query_info(C.Structure):
@@ -56,11 +56,13 @@ SYMBOLS = {
     "uvg_drop_refs": (C.c_int, [_P]),
     "uvg_clear_refs": (C.c_int, [_P]),
     "uvg_db_count": (C.c_int64, [_P]),
+    "uvg_mark_file_end": (C.c_int, [_P, C.c_int64]),
     "uvg_search": (C.c_int, [_P]),
     "uvg_search_async": (C.c_int, [_P]),
     "uvg_wait": (C.c_int, [_P]),
     "uvg_reset_search": (C.c_int, [_P]),
     "uvg_get_heap": (C.c_int, [_P, C.c_int32, C.POINTER(uvg_item), C.POINTER(C.c_int32)]),
+    "uvg_get_all_heaps": (C.c_int, [_P, _P, _P]),
     "uvg_get_ever_best": (C.c_int, [_P, C.c_int64, C.c_int64, _P]),
     "uvg_get_stats": (C.c_int, [_P, C.POINTER(uvg_stats)]),
     "uvg_shard_of": (C.c_int, [C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),

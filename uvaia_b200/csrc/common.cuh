@@ -53,12 +53,15 @@ static_assert(sizeof(QChunk) % 16 == 0, "bulk copy size must be a multiple of 16
 // "reference l of the group holds that base there" -- a warp fetches the words of all its entries of a chunk with ONE
 // load (lane = entry x group) while it counts the chunk, and almost always finds them all zero.  What does not fit a
 // chunk's fix block, and every ambiguity code, is resolved by the epilogue (pair_epilogue.cuh).
-// Derived database: per (group of 32 references, unit of 4 column words) one contiguous 3 KB record
-//     uint4 base[32]  |  uint4 mc[32]  |  uint32 colmask[4 words][4 bases A,C,G,T][32 sites]
-// of which the first 1 KB (base, mc: lane = reference) is staged by TMA bulk copies.
+// Derived database: per (pair of groups = the 64 references of a thread block, chunk of WC column words) one contiguous
+// 12 KB record
+//     planes   [group of the pair][unit][ uint4 base[32] | uint4 mc[32] ]                    4 KB: ONE TMA bulk copy per chunk
+//     colmasks [group of the pair][unit][4 words][4 bases A,C,G,T][32 sites] uint32         8 KB: read by fix entries only
 constexpr int STAGES2 = 8;
-constexpr int UNIT2_BYTES = 2 * GROUP * 16 + 4 * 4 * GROUP * 4;      // 3072
-constexpr int UNIT2_ONEHOT = 2 * GROUP * 16;                         // byte offset of the one-hot planes inside a unit record
+constexpr int UNIT2_PLANES = 2 * GROUP * 16;                         // base + mc of one (group, unit): 1 KB
+constexpr int UNIT2_MASKS = 4 * 4 * GROUP * 4;                       // column masks of one (group, unit): 2 KB
+constexpr int CHUNK2_PLANES = RPL * W4 * UNIT2_PLANES;               // 4 KB
+constexpr int CHUNK2_BYTES = CHUNK2_PLANES + RPL * W4 * UNIT2_MASKS; // 12 KB per (pair of groups, chunk)
 constexpr int FIXCAP = 248;                                          // fix entries a chunk of a query tile can carry
 constexpr int PIVOT_QW = 4;                                          // query slots per warp of k_pairpivot
 constexpr int PIVOT_WARPS = QTILE / PIVOT_QW;
@@ -66,13 +69,21 @@ struct __align__(16) QChunk2 {
     uint4    pl[W4][QTILE][2];       // [unit][slot][plane], COMPLEMENTS: 0 = no plain base here (or trimmed / padding), 1 = not the pivot base
     uint8_t  fix_begin[32];          // [warp] first entry of the warp's slots; [PIVOT_WARPS] = total
     uint8_t  active[W4][16];         // per unit and warp: bit j set <=> the warp's j-th slot (PairParams::wslot) has work in this unit
-    uint32_t fix[FIXCAP];            // byte offset of the entry's column-mask word inside a group's chunk of the derived
-                                     //     database | slot-within-tile << 16
+    uint32_t fix[FIXCAP];            // byte offset of the entry's column-mask word inside the chunk record of the derived database
+                                     //     (for the first group of the pair; the second is W4 * UNIT2_MASKS further) | slot-within-tile << 16
 };
 static_assert(sizeof(QChunk2) % 16 == 0 && PIVOT_WARPS < 32 && FIXCAP < 256, "QChunk2 layout");
-__host__ __device__ inline size_t db2_unit_bytes(int64_t group, int unit, int Wp)
+__host__ __device__ inline size_t db2_chunk_bytes(int64_t group, int unit, int Wp)        // record of the chunk that holds (group, unit)
 {
-    return ((size_t)group * (size_t)(Wp / 4) + (size_t)unit) * UNIT2_BYTES;
+    return ((size_t)(group / RPL) * (size_t)(Wp / WC) + (size_t)(unit / W4)) * CHUNK2_BYTES;
+}
+__host__ __device__ inline size_t db2_planes_bytes(int64_t group, int unit, int Wp)       // base plane of (group, unit); mc follows at + GROUP * 16
+{
+    return db2_chunk_bytes(group, unit, Wp) + (size_t)((group % RPL) * W4 + unit % W4) * UNIT2_PLANES;
+}
+__host__ __device__ inline size_t db2_masks_bytes(int64_t group, int unit, int Wp)        // column masks of (group, unit)
+{
+    return db2_chunk_bytes(group, unit, Wp) + CHUNK2_PLANES + (size_t)((group % RPL) * W4 + unit % W4) * UNIT2_MASKS;
 }
 
 // Heap slot (32 B): the reference's q_item (src/min_heap.h:14-18) with name -> ordinal.

@@ -94,10 +94,13 @@ struct uvg_ctx {
     int32_t* d_ref_cnt = nullptr;                     // [2][db2_cap]: per reference popcount of its base plane / of its mc plane
     Threshold* d_thr_local = nullptr;                 // [rows_cap] bounds of the owned rows (written by K3)
     Threshold* d_thr_all[NBUF]{};                     // [world * rows_cap] what K2 reads (double buffered)
-    HeapItem* d_heaps = nullptr;                      // [rows_cap][K+1] owned rows
-    HeapItem* d_heaps_all = nullptr;                  // [world][rows_cap][K+1] (sharded mode: gathered at the end of a search)
-    int32_t *d_heap_n = nullptr, *d_max_inc = nullptr, *d_batch_id = nullptr, *d_max_inc_batch = nullptr;
-    int32_t *d_heap_n_all = nullptr, *d_max_inc_all = nullptr;
+    // results of the owned rows in ONE block: heaps [rows_cap][K+1] | heap_n [rows_cap] | max_inc [rows_cap] (own_bytes), so
+    // that a sharded search ends with a single all-gather into d_all [world][own_bytes]
+    uint8_t* d_own = nullptr; uint8_t* d_all = nullptr; size_t own_bytes = 0, own_off_n = 0, own_off_mi = 0;
+    HeapItem* d_heaps = nullptr;                      // = d_own
+    int32_t *d_heap_n = nullptr, *d_max_inc = nullptr;    // inside d_own
+    int32_t *d_batch_id = nullptr, *d_max_inc_batch = nullptr;
+    bool ever_reduced = true;                         // sharded: the ever-best flags of all ranks have been combined (lazily, uvg_get_ever_best)
     // database (local shard)
     int64_t db_cap = 0, db_n = 0, db_scored = 0, global_base = 0, global_total = -1;
     uint4* d_db = nullptr;
@@ -117,6 +120,12 @@ struct uvg_ctx {
     uint8_t* d_stage_text[2]{}; size_t stage_text_bytes = 0;
     int32_t *d_stage_nn = nullptr, *d_stage_namb = nullptr; uint8_t* d_stage_acc = nullptr; int64_t* d_stage_dst = nullptr; int64_t stage_rows = 0;
     int64_t* d_nacc = nullptr;
+    // literal emulation of the reference's --pool batches (hazard H1, replay.cu): batch-wide limit of the consensus stage
+    bool literal = false;                             // single GPU and not uvg_params.closed_form
+    int32_t* d_bstate = nullptr;                      // [0..2] accumulators of the replay launches (ring), [4..5] limit of the batch in progress
+    int64_t replay_seq = 0;                           // replay launches since the heaps were emptied
+    std::vector<int64_t> file_starts{0};              // global ordinals at which a reference file starts (a batch ends with its file)
+    uint32_t cons_amb_begin = 0, cons_amb_n = 0;      // ambiguity codes of the consensus slot inside d_qamb_ent
     // round schedule
     int64_t rounds_done = 0, round_local_start = 0, round_global_start = 0;
     int32_t next_round = 0;
@@ -190,6 +199,7 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
     c->world = p->world > 1 ? p->world : 1;
     c->next_round = round_size_first(*p);
     if (c->prm.pool < 1) c->prm.pool = 1;
+    c->literal = c->world == 1 && p->closed_form == 0;
 #define CK_(call) do { cudaError_t e2_ = (call); if (e2_ != cudaSuccess) { g_create_error = std::string("CUDA: ") + cudaGetErrorString(e2_); delete c; return UVG_ECUDA; } } while (0)
     CK_(cudaSetDevice(p->device));
     cudaDeviceProp prop;
@@ -215,6 +225,7 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
     CK_(paircount_setup());
     CK_(pairpivot_setup());
     CK_(replay_setup(c->K));
+    CK_(cudaMalloc(&c->d_bstate, 32));
     CK_(cudaMalloc(&c->d_counters, 64)); CK_(cudaMalloc(&c->d_nacc, 64)); CK_(cudaMalloc(&c->d_ipc, 64 * MAX_RANKS + 64));
     CK_(cudaMemset(c->d_counters, 0, 64));
     CK_(cudaMallocHost(&c->h_pinned, 2048));
@@ -256,13 +267,12 @@ static void free_queries(uvg_ctx* c, bool final = false)
     cudaFree(c->d_qdata2); cudaFree(c->d_qfix_off); cudaFree(c->d_qfix_ent); cudaFree(c->d_pivot); cudaFree(c->d_wslot); c->d_wslot = nullptr;
     c->d_qdata2 = nullptr; c->d_qfix_off = c->d_qfix_ent = nullptr; c->d_pivot = nullptr;
     cudaFree(c->d_thr_local); for (int b = 0; b < NBUF; ++b) { cudaFree(c->d_thr_all[b]); c->d_thr_all[b] = nullptr; }
-    cudaFree(c->d_heaps); cudaFree(c->d_heaps_all);
-    cudaFree(c->d_heap_n); cudaFree(c->d_max_inc); cudaFree(c->d_batch_id); cudaFree(c->d_max_inc_batch);
-    cudaFree(c->d_heap_n_all); cudaFree(c->d_max_inc_all);
+    cudaFree(c->d_own); cudaFree(c->d_all); c->d_own = c->d_all = nullptr;
+    cudaFree(c->d_batch_id); cudaFree(c->d_max_inc_batch);
     cudaFree(c->d_tiles); c->d_tiles = nullptr; c->tiles_alloc = 0;
     c->d_qdata = nullptr; c->d_qnib = c->d_qamb_off = c->d_qamb_ent = nullptr; c->d_thr_local = nullptr;
-    c->d_heaps = c->d_heaps_all = nullptr;
-    c->d_heap_n = c->d_max_inc = c->d_batch_id = c->d_max_inc_batch = c->d_heap_n_all = c->d_max_inc_all = nullptr;
+    c->d_heaps = nullptr;
+    c->d_heap_n = c->d_max_inc = c->d_batch_id = c->d_max_inc_batch = nullptr;
     c->seg_cap = 0; c->tile_elems = 0;
 }
 
@@ -277,7 +287,7 @@ extern "C" void uvg_destroy(uvg_ctx* c)
     free_queries(c, true);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->d_db); cudaFree(c->d_db2); cudaFree(c->d_ref_cnt); cudaFree(c->d_non_n); cudaFree(c->d_ramb_off); cudaFree(c->d_ramb_ent); cudaFree(c->d_ever);
-    cudaFree(c->d_counters); cudaFree(c->d_nacc); cudaFree(c->d_ipc);
+    cudaFree(c->d_counters); cudaFree(c->d_nacc); cudaFree(c->d_ipc); cudaFree(c->d_bstate);
     cudaFree(c->d_stage_text[0]); cudaFree(c->d_stage_text[1]); cudaFree(c->d_stage_nn); cudaFree(c->d_stage_namb); cudaFree(c->d_stage_acc); cudaFree(c->d_stage_dst);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (auto& pr : c->pair_events) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
@@ -313,11 +323,12 @@ static int ensure_db2(uvg_ctx* c)
     if (!c->pivot_on || c->db2_cap >= c->db_cap) return UVG_OK;
     int rc = sync_all(c);
     if (rc) return rc;
-    const size_t per_group = (size_t)(c->Wp / 4) * UNIT2_BYTES;             // bytes
+    const size_t per_pair = (size_t)c->n_chunks * CHUNK2_BYTES;             // bytes per pair of groups (capacities are multiples of a pair)
+    const size_t pairs_old = (size_t)(c->db2_cap / (GROUP * RPL)), pairs_new = (size_t)(c->db_cap / (GROUP * RPL));
     uint8_t* n = nullptr;
-    UVG_CUDA(c, cudaMalloc(&n, (size_t)(c->db_cap / GROUP) * per_group));
-    if (c->d_db2 && c->db2_cap) UVG_CUDA(c, cudaMemcpy(n, c->d_db2, (size_t)(c->db2_cap / GROUP) * per_group, cudaMemcpyDeviceToDevice));
-    UVG_CUDA(c, cudaMemset(n + (size_t)(c->db2_cap / GROUP) * per_group, 0, (size_t)((c->db_cap - c->db2_cap) / GROUP) * per_group));
+    UVG_CUDA(c, cudaMalloc(&n, pairs_new * per_pair));
+    if (c->d_db2 && c->db2_cap) UVG_CUDA(c, cudaMemcpy(n, c->d_db2, pairs_old * per_pair, cudaMemcpyDeviceToDevice));
+    UVG_CUDA(c, cudaMemset(n + pairs_old * per_pair, 0, (pairs_new - pairs_old) * per_pair));
     // the per-reference plane totals are re-derived with the planes: new array, the resident range is filled by the caller
     // (uvg_set_queries) or was filled by earlier pushes and is copied
     int32_t* cn = nullptr;
@@ -365,6 +376,11 @@ static int reset_heaps(uvg_ctx* c)
     for (int b = 0; b < NBUF; ++b) UVG_CUDA(c, cudaMemsetAsync(c->d_thr_all[b], 0, (size_t)c->world * rows * sizeof(Threshold), c->st));
     UVG_CUDA(c, cudaMemsetAsync(c->d_heaps, 0, (size_t)rows * (c->K + 1) * sizeof(HeapItem), c->st));
     UVG_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 64, c->st));
+    {   // every heap is empty: max_incompatible = nchar for all queries, so the first batch's limit is nchar
+        const int32_t b0[8] = {0, 0, c->nchar, 0, c->nchar, c->nchar, 0, 0};
+        UVG_CUDA(c, cudaMemcpyAsync(c->d_bstate, b0, sizeof b0, cudaMemcpyHostToDevice, c->st));
+        c->replay_seq = 0;
+    }
     if (c->d_ever && c->ever_cap) UVG_CUDA(c, cudaMemsetAsync(c->d_ever, 0, c->ever_cap, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));                              // `init` goes out of scope
     c->db_scored = 0; c->heaps_cached = false; c->work_seen = 0; c->search_open = false; c->n_ev = 0;
@@ -538,6 +554,7 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
         amb_ent.insert(amb_ent.end(), amb[q].begin(), amb[q].end());
     }
     amb_off[c->n_slots] = (uint32_t)amb_ent.size();
+    c->cons_amb_begin = amb_off[Q]; c->cons_amb_n = amb_off[Q + 1] - amb_off[Q];
 
     // ---- pivot form (pairpivot.cu): pivot planes, fix blocks of the chunks, epilogue lists ----
     std::vector<uint32_t> fix_off, fix_ent, pivot_words;
@@ -613,7 +630,7 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
                             const uint32_t ent = snp[q][cur[q]++], site = ent & AMB_SITE_MASK, code = ent >> 28;
                             const uint32_t w = site >> 5, a = code == 1 ? 0 : code == 2 ? 1 : code == 4 ? 2 : 3;
                             if (n >= FIXCAP) { epi[q].push_back(ent); ++n_overflow; continue; }
-                            const uint32_t off = ((w % WC) / 4) * UNIT2_BYTES + UNIT2_ONEHOT + (((w & 3) * 4 + a) * 32 + (site & 31)) * 4;
+                            const uint32_t off = CHUNK2_PLANES + ((w % WC) / 4) * UNIT2_MASKS + (((w & 3) * 4 + a) * 32 + (site & 31)) * 4;
                             blk.fix[n++] = off | ((uint32_t)qi << 16);
                         }
                     }
@@ -667,27 +684,35 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     UVG_CUDA(c, pooled_alloc(c, 3, &c->d_qamb_ent, amb_ent.size() * 4));
     UVG_CUDA(c, pooled_alloc(c, 4, &c->d_thr_local, (size_t)rows * sizeof(Threshold)));
     for (int b = 0; b < NBUF; ++b) UVG_CUDA(c, pooled_alloc(c, 5 + b, &c->d_thr_all[b], (size_t)c->world * rows * sizeof(Threshold)));
-    UVG_CUDA(c, pooled_alloc(c, 7, &c->d_heaps, (size_t)rows * (c->K + 1) * sizeof(HeapItem)));
-    UVG_CUDA(c, pooled_alloc(c, 8, &c->d_heap_n, (size_t)rows * 4)); UVG_CUDA(c, pooled_alloc(c, 9, &c->d_max_inc, (size_t)rows * 4));
+    c->own_off_n = (size_t)rows * (c->K + 1) * sizeof(HeapItem);
+    c->own_off_mi = c->own_off_n + (size_t)rows * 4;
+    c->own_bytes = (c->own_off_mi + (size_t)rows * 4 + 15) / 16 * 16;
+    UVG_CUDA(c, pooled_alloc(c, 7, &c->d_own, c->own_bytes));
+    c->d_heaps = reinterpret_cast<HeapItem*>(c->d_own);
+    c->d_heap_n = reinterpret_cast<int32_t*>(c->d_own + c->own_off_n); c->d_max_inc = reinterpret_cast<int32_t*>(c->d_own + c->own_off_mi);
     UVG_CUDA(c, pooled_alloc(c, 10, &c->d_batch_id, (size_t)rows * 4)); UVG_CUDA(c, pooled_alloc(c, 11, &c->d_max_inc_batch, (size_t)rows * 4));
-    if (c->world > 1) {
-        UVG_CUDA(c, pooled_alloc(c, 12, &c->d_heaps_all, (size_t)c->world * rows * (c->K + 1) * sizeof(HeapItem)));
-        UVG_CUDA(c, pooled_alloc(c, 13, &c->d_heap_n_all, (size_t)c->world * rows * 4));
-        UVG_CUDA(c, pooled_alloc(c, 14, &c->d_max_inc_all, (size_t)c->world * rows * 4));
-    }
+    if (c->world > 1) UVG_CUDA(c, pooled_alloc(c, 12, &c->d_all, (size_t)c->world * c->own_bytes));
     // dense score tiles: rounds are capped so that one buffer stays within ~3 GiB
     {
         int64_t cap = round_size_max(c->prm);
         const int64_t per_ref = (int64_t)(rows + 2) * c->world * 16;        // bytes of one column position over all segments
         const int64_t fit = ((int64_t)3 << 30) / per_ref / (GROUP * RPL) * (GROUP * RPL);
-        cap = std::max<int64_t>(GROUP * RPL, std::min(cap, fit));
+        // Single GPU: rounds shrink so that one buffer stays within ~3 GiB (nobody else depends on the round sizes).  Sharded:
+        // the round schedule IS the row distribution the hosts deal with uvg_shard_of (first_round, max_round): it must not
+        // depend on the query set, so the tiles take what max_round asks for (or the allocation fails loudly below).
+        if (c->world == 1) cap = std::max<int64_t>(GROUP * RPL, std::min(cap, fit));
         c->seg_cap = cap;
         c->tile_elems = (size_t)(rows + 2) * c->world * cap;
         if (NBUF * c->tile_elems > c->tiles_alloc) {                       // the multi-GiB buffer is kept when the next query set fits
             if (c->world > 1) close_peers(c);                                // (every rank takes this branch alike: the size depends on shared parameters only);
                                                                              // the new buffer is mapped by the peers at the next search
             cudaFree(c->d_tiles); c->d_tiles = nullptr; c->tiles_alloc = 0;
-            UVG_CUDA(c, cudaMalloc(&c->d_tiles, NBUF * c->tile_elems * sizeof(uint4)));
+            const cudaError_t e_t = cudaMalloc(&c->d_tiles, NBUF * c->tile_elems * sizeof(uint4));
+            if (e_t != cudaSuccess) {
+                cudaGetLastError();
+                UVG_FAIL(c, UVG_ENOMEM, "uvg_set_queries: the score tiles of %d queries need %.1f GiB per rank at max_round %lld; create the contexts (and deal "
+                         "the rows, uvg_shard_of) with a smaller max_round", Q, (double)(NBUF * c->tile_elems * sizeof(uint4)) / (1 << 30), (long long)cap);
+            }
             c->tiles_alloc = NBUF * c->tile_elems;
         }
         if (c->world == 1) { c->peer_tiles[0] = c->d_tiles; c->peers_ready = true; }
@@ -1072,10 +1097,23 @@ extern "C" int uvg_clear_refs(uvg_ctx* c)
     if (rc) return rc;
     c->search_open = false; c->n_ev = 0;
     c->global_base = 0; c->db_n = 0; c->db_scored = 0; c->round_local_start = 0; c->global_total = -1; c->amb_n = 0;
+    c->file_starts.assign(1, 0);
     return c->n_query ? reset_heaps(c) : UVG_OK;
 }
 
 extern "C" int64_t uvg_db_count(const uvg_ctx* c) { return c ? c->db_n : 0; }
+
+// The reference fills its batches per file: a batch ends at end-of-file and the next file starts a new one
+// (nearest.c:245-286), so where the files end is part of what --pool means.
+extern "C" int uvg_mark_file_end(uvg_ctx* c, int64_t n_accepted_so_far)
+{
+    if (!c) return UVG_EINVAL;
+    const int64_t at = n_accepted_so_far >= 0 ? n_accepted_so_far : c->global_base + c->db_n;
+    if (at < c->file_starts.back()) UVG_FAIL(c, UVG_EINVAL, "uvg_mark_file_end: %lld is before the previous file end", (long long)at);
+    if (c->world == 1 && at < c->global_base + c->db_scored) UVG_FAIL(c, UVG_ESTATE, "uvg_mark_file_end: references beyond %lld were searched already", (long long)at);
+    if (at > c->file_starts.back()) c->file_starts.push_back(at);
+    return UVG_OK;
+}
 
 
 // =====================================================================================================================
@@ -1321,11 +1359,38 @@ static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t
     rc = event_pair(c, *n_ev, &ra, &rb);
     if (rc) return rc;
     UVG_CUDA(c, cudaEventRecord(ra, c->st_rp));
-    UVG_CUDA(c, launch_replay(rp, c->st_rp));
+    rp.ord_begin = round_first; rp.ord_end = round_first + round_count;
+    if (!c->literal) {
+        UVG_CUDA(c, launch_replay(rp, c->st_rp));
+        c->stats.other_kernel_launches += 1;
+    } else {
+        // the reference's batches: --pool accepted references, restarting with every file (nearest.c:245-286).  One launch per
+        // piece of a batch inside this round; the batch-wide limit travels through d_bstate (see ReplayParams).
+        rp.literal = 1; rp.local_ord0 = c->global_base;
+        rp.db = c->d_db; rp.qcons = c->d_qdata + (size_t)(c->n_query / QTILE) * c->n_chunks; rp.cons_qi = c->n_query % QTILE;
+        rp.cons_nib = c->d_qnib + (size_t)c->n_query * c->qnib_stride;
+        rp.camb = c->d_qamb_ent + c->cons_amb_begin; rp.n_camb = (int32_t)c->cons_amb_n;
+        rp.ramb_off = c->d_ramb_off; rp.ramb_ent = c->d_ramb_ent; rp.Wp = c->Wp;
+        const int64_t pool = c->prm.pool, end = round_first + round_count;
+        size_t k = std::upper_bound(c->file_starts.begin(), c->file_starts.end(), round_first) - c->file_starts.begin() - 1;
+        for (int64_t o = round_first; o < end;) {
+            while (k + 1 < c->file_starts.size() && c->file_starts[k + 1] <= o) ++k;
+            const int64_t fs = c->file_starts[k];
+            int64_t nb = fs + ((o - fs) / pool + 1) * pool;
+            if (k + 1 < c->file_starts.size()) nb = std::min(nb, c->file_starts[k + 1]);
+            const int64_t e = std::min(end, nb);
+            const int64_t i = c->replay_seq++;
+            rp.ord_begin = o; rp.ord_end = e; rp.batch_start = (o - fs) % pool == 0;
+            rp.b_prev = c->d_bstate + (i + 2) % 3; rp.b_acc = c->d_bstate + i % 3; rp.b_zero = c->d_bstate + (i + 1) % 3;
+            rp.b_carry_in = c->d_bstate + 4 + (i + 1) % 2; rp.b_carry_out = c->d_bstate + 4 + i % 2;
+            UVG_CUDA(c, launch_replay(rp, c->st_rp));
+            c->stats.other_kernel_launches += 1;
+            o = e;
+        }
+    }
     UVG_CUDA(c, cudaEventRecord(rb, c->st_rp));
     ++*n_ev;
     UVG_CUDA(c, cudaEventRecord(c->ev_replay[b], c->st_rp));
-    c->stats.other_kernel_launches += 1;
     return UVG_OK;
 }
 
@@ -1370,6 +1435,10 @@ static int search_enqueue(uvg_ctx* c)
         }
         rc = run_round(c, lstart, cnt, T, rfirst, rcount, &c->n_ev);
         if (rc) return rc;
+        if (c->world > 1 && c->round_global_start + (int64_t)c->world * T >= c->global_total && lstart + cnt != c->db_n)
+            UVG_FAIL(c, UVG_ESTATE, "rank %d holds %lld references but the round schedule (first_round %d, max_round %d, %lld in all) gives it %lld: "
+                     "the rows were dealt with another schedule (uvg_shard_of)", c->rank, (long long)c->db_n, round_size_first(c->prm), round_size_max(c->prm),
+                     (long long)c->global_total, (long long)(lstart + cnt));
         if (c->world == 1) { c->db_scored += cnt; c->stats.n_refs += cnt; }
         else { c->round_global_start += (int64_t)c->world * T; c->round_local_start += T; c->db_scored = std::min(c->db_n, c->round_local_start); c->stats.n_refs += rcount; }
         ++c->rounds_done; ++c->stats.n_rounds;
@@ -1395,11 +1464,10 @@ extern "C" int uvg_wait(uvg_ctx* c)
     UVG_CUDA(c, cudaStreamWaitEvent(c->st, c->ev_d, 0));
     if (c->world > 1) {
         // the tables of all queries to every rank (small all-gathers over NVLink), OR of the ever-best flags
-        const size_t hb = (size_t)c->rows_cap * (c->K + 1) * sizeof(HeapItem);
-        UVG_NCCL(c, g_nccl.AllGather(c->d_heaps, c->d_heaps_all, hb, ncclUint8, c->comm, c->st));
-        UVG_NCCL(c, g_nccl.AllGather(c->d_heap_n, c->d_heap_n_all, (size_t)c->rows_cap, ncclInt32, c->comm, c->st));
-        UVG_NCCL(c, g_nccl.AllGather(c->d_max_inc, c->d_max_inc_all, (size_t)c->rows_cap, ncclInt32, c->comm, c->st));
-        if (c->global_total > 0) UVG_NCCL(c, g_nccl.AllReduce(c->d_ever, c->d_ever, (size_t)c->global_total, ncclUint8, ncclMax, c->comm, c->st));
+        // the tables of all queries to every rank: ONE all-gather over NVLink (heaps, sizes and limits are one block).  The
+        // ever-best flags are combined lazily by uvg_get_ever_best (nobody needs them inside the search).
+        UVG_NCCL(c, g_nccl.AllGather(c->d_own, c->d_all, c->own_bytes, ncclUint8, c->comm, c->st));
+        c->ever_reduced = false;
     }
     UVG_CUDA(c, cudaEventRecord(c->ev_b, c->st));
     UVG_CUDA(c, cudaMemcpyAsync(c->h_pinned + 20, c->d_counters + 2, 8, cudaMemcpyDeviceToHost, c->st));
@@ -1446,12 +1514,15 @@ static int cache_heaps(uvg_ctx* c)
 {
     if (c->search_open) { int rc = uvg_wait(c); if (rc) return rc; }
     if (c->heaps_cached) return UVG_OK;
-    const size_t rows = (size_t)c->world * c->rows_cap, stride = c->K + 1;
+    const size_t rows_r = (size_t)c->rows_cap, rows = (size_t)c->world * rows_r, stride = c->K + 1;
     c->h_heaps.resize(rows * stride); c->h_heap_n.resize(rows); c->h_max_inc.resize(rows);
-    const bool sh = c->world > 1;
-    UVG_CUDA(c, cudaMemcpyAsync(c->h_heaps.data(), sh ? c->d_heaps_all : c->d_heaps, rows * stride * sizeof(HeapItem), cudaMemcpyDeviceToHost, c->st));
-    UVG_CUDA(c, cudaMemcpyAsync(c->h_heap_n.data(), sh ? c->d_heap_n_all : c->d_heap_n, rows * 4, cudaMemcpyDeviceToHost, c->st));
-    UVG_CUDA(c, cudaMemcpyAsync(c->h_max_inc.data(), sh ? c->d_max_inc_all : c->d_max_inc, rows * 4, cudaMemcpyDeviceToHost, c->st));
+    const uint8_t* src = c->world > 1 ? c->d_all : c->d_own;
+    for (int r = 0; r < c->world; ++r) {
+        const uint8_t* blk = src + (size_t)r * c->own_bytes;
+        UVG_CUDA(c, cudaMemcpyAsync(c->h_heaps.data() + (size_t)r * rows_r * stride, blk, rows_r * stride * sizeof(HeapItem), cudaMemcpyDeviceToHost, c->st));
+        UVG_CUDA(c, cudaMemcpyAsync(c->h_heap_n.data() + (size_t)r * rows_r, blk + c->own_off_n, rows_r * 4, cudaMemcpyDeviceToHost, c->st));
+        UVG_CUDA(c, cudaMemcpyAsync(c->h_max_inc.data() + (size_t)r * rows_r, blk + c->own_off_mi, rows_r * 4, cudaMemcpyDeviceToHost, c->st));
+    }
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
     c->heaps_cached = true;
     return UVG_OK;
@@ -1463,19 +1534,13 @@ static size_t row_of_query(const uvg_ctx* c, int iq)
     return (size_t)(qt % c->world) * c->rows_cap + (size_t)(qt / c->world) * QTILE + iq % QTILE;
 }
 
-extern "C" int uvg_get_heap(uvg_ctx* c, int32_t iq, uvg_item* out, int32_t* n_out)
+// heap_finalise_heap_qsort (src/min_heap.c:149-153) of one cached heap: slot 0 <-> slot n, then libc qsort over [0, n)
+static int finalise_row(const uvg_ctx* c, int iq, uvg_item* out)
 {
-    if (!c || !out || !n_out) { if (c) c->err = "uvg_get_heap: bad arguments"; return UVG_EINVAL; }
-    if (iq < 0 || iq >= c->n_query) UVG_FAIL(c, UVG_EINVAL, "uvg_get_heap: query %d out of range", iq);
-    UVG_CUDA(c, cudaSetDevice(c->prm.device));
-    int rc = cache_heaps(c);
-    if (rc) return rc;
     const size_t row = row_of_query(c, iq);
     const int n = c->h_heap_n[row];
-    *n_out = n;
-    if (n == 0) return UVG_OK;
+    if (n == 0) return 0;
     const HeapItem* a = c->h_heaps.data() + row * (c->K + 1);
-    // heap_finalise_heap_qsort (src/min_heap.c:149-153): slot 0 <-> slot n, then libc qsort over [0, n)
     std::vector<HeapItem> arr(n);
     arr[0] = a[n];
     for (int i = 1; i < n; ++i) arr[i] = a[i];
@@ -1484,6 +1549,30 @@ extern "C" int uvg_get_heap(uvg_ctx* c, int32_t iq, uvg_item* out, int32_t* n_ou
         for (int k = 0; k < 6; ++k) out[i].score[k] = arr[i].s[k];
         out[i].ref = arr[i].r;
     }
+    return n;
+}
+
+extern "C" int uvg_get_heap(uvg_ctx* c, int32_t iq, uvg_item* out, int32_t* n_out)
+{
+    if (!c || !out || !n_out) { if (c) c->err = "uvg_get_heap: bad arguments"; return UVG_EINVAL; }
+    if (iq < 0 || iq >= c->n_query) UVG_FAIL(c, UVG_EINVAL, "uvg_get_heap: query %d out of range", iq);
+    UVG_CUDA(c, cudaSetDevice(c->prm.device));
+    int rc = cache_heaps(c);
+    if (rc) return rc;
+    *n_out = finalise_row(c, iq, out);
+    return UVG_OK;
+}
+
+// every query's table in one call: out holds n_query x max(2, nbest) items (row iq at out + iq * max(2, nbest)), n_out[iq] rows
+extern "C" int uvg_get_all_heaps(uvg_ctx* c, uvg_item* out, int32_t* n_out)
+{
+    if (!c || !out || !n_out) { if (c) c->err = "uvg_get_all_heaps: bad arguments"; return UVG_EINVAL; }
+    UVG_CUDA(c, cudaSetDevice(c->prm.device));
+    int rc = cache_heaps(c);
+    if (rc) return rc;
+    parallel_ranges(c->n_query, host_threads(c->n_query / 64), [&](int, int qa, int qb) {
+        for (int iq = qa; iq < qb; ++iq) n_out[iq] = finalise_row(c, iq, out + (size_t)iq * c->K);
+    });
     return UVG_OK;
 }
 
@@ -1492,6 +1581,11 @@ extern "C" int uvg_get_ever_best(uvg_ctx* c, int64_t first, int64_t n, uint8_t* 
     if (!c || !flags || first < 0 || n < 0) { if (c) c->err = "uvg_get_ever_best: bad arguments"; return UVG_EINVAL; }
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
     if (c->search_open) { int rc = uvg_wait(c); if (rc) return rc; }
+    if (c->world > 1 && !c->ever_reduced) {
+        // sharded: every rank marked the references its own queries admitted; combine (collective: every rank calls this)
+        if (c->global_total > 0) UVG_NCCL(c, g_nccl.AllReduce(c->d_ever, c->d_ever, (size_t)c->global_total, ncclUint8, ncclMax, c->comm, c->st));
+        c->ever_reduced = true;
+    }
     memset(flags, 0, (size_t)n);
     const int64_t m = std::min(n, c->ever_cap - first);
     if (m > 0) {

@@ -49,6 +49,21 @@ struct ReplayParams {
     int32_t n_query;                                                  // real queries (all ranks)
     int32_t world, rank;                                              // row -> query: ((row / QTILE) * world + rank) * QTILE + row % QTILE
     int32_t K, acgt_mode, pool;
+    // the launch replays the global ordinals [ord_begin, ord_end) of the round (literal mode: one launch per batch piece)
+    int64_t ord_begin, ord_end;
+    // ---- literal emulation of the reference's batch-wide consensus limit (hazard H1; single GPU) ----
+    int32_t literal;              // 0: pool-independent closed form + H1 flags; 1: the reference's result for this --pool
+    int32_t batch_start;          // the launch starts a batch: the limit is the maximum the previous launch accumulated
+    const int32_t* b_prev;        // max over the queries of max_incompatible after the previous launch
+    const int32_t* b_carry_in;    // limit of the batch in progress (written by the previous launch)
+    int32_t* b_carry_out;         // ... for the next launch
+    int32_t* b_acc;               // this launch's accumulator (atomicMax of every query's final max_incompatible)
+    int32_t* b_zero;              // the accumulator of the NEXT launch (zeroed here)
+    int64_t local_ord0;           // global ordinal of local reference 0 (local index = ordinal - local_ord0)
+    const uint4* db; const QChunk* qcons; int32_t cons_qi; const uint32_t* cons_nib;
+    const uint32_t* camb; int32_t n_camb;
+    const uint32_t* ramb_off; const uint32_t* ramb_ent;
+    int32_t Wp;
 };
 cudaError_t launch_replay(const ReplayParams& p, cudaStream_t st);
 cudaError_t replay_setup(int K);

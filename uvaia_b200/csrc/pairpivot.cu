@@ -33,26 +33,24 @@
 
 namespace uvg {
 
-struct __align__(16) RefUnit2 {
-    uint4    base[GROUP];
-    uint4    mc[GROUP];
-    uint32_t colmask[4][4][32];                         // [word][base A,C,G,T][site in word]: bit l = reference l of the group holds that base
-};
-static_assert(sizeof(RefUnit2) == UNIT2_BYTES, "derived database record");
-// staged part of a record: the base and mc planes (the one-hot planes stay in global memory / L2: only fix entries read them)
+// staged part of a chunk record: the base and mc planes of the block's two groups (the column masks stay in global memory /
+// L2: only fix entries read them)
 struct __align__(16) RefPlanes2 {
     uint4 base[GROUP];
     uint4 mc[GROUP];
 };
-static_assert(sizeof(RefPlanes2) == UNIT2_ONEHOT, "staged prefix of the derived database record");
+static_assert(sizeof(RefPlanes2) == UNIT2_PLANES, "planes of one (group, unit) of the derived database");
 struct __align__(16) Stage2 {
     QChunk2    q;
     RefPlanes2 ref[RPL][W4];
 };
-constexpr uint32_t STAGE2_REF_BYTES = W4 * UNIT2_BYTES;             // bytes of a group's chunk in the derived database
+static_assert(sizeof(RefPlanes2) * RPL * W4 == CHUNK2_PLANES, "staged prefix of a chunk record");
 constexpr size_t PIVOT_FIXHIT_BYTES = QTILE * GROUP * RPL * sizeof(uint16_t);       // per (slot, reference of the block): matches found by fix entries
 constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + PIVOT_FIXHIT_BYTES + 2 * STAGES2 * sizeof(uint64_t);
 constexpr int REFILL_LAG = 2;
+#ifndef PIVOT_ROTATE
+#define PIVOT_ROTATE 1          // 1: the warps take turns refilling the ring (chunk c: warp c % 16); 0: warp 0 refills (r01 kernel)
+#endif
 constexpr int QW2 = PIVOT_QW;                           // query slots per warp (register tile QW2 x RPL pairs per lane)
 constexpr int PIVOT_THREADS = PIVOT_WARPS * 32;
 
@@ -68,9 +66,12 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     const int qt = blockIdx.x % p.n_qtiles;
     const int64_t group0 = (p.local_begin / (GROUP * RPL) + blockIdx.x / p.n_qtiles) * RPL;
     const QChunk2* qsrc = p.qdata2 + (size_t)qt * p.n_chunks;
-    const size_t group_stride = (size_t)(p.Wp / 4) * UNIT2_BYTES;            // bytes between consecutive groups
-    const uint8_t* rsrc = p.db2 + (size_t)group0 * group_stride;
+    const uint8_t* rsrc = p.db2 + (size_t)(group0 / RPL) * (size_t)p.n_chunks * CHUNK2_BYTES;      // chunk records of this block's pair of groups
     const int owner = qt % p.world, row0 = (qt / p.world) * QTILE;
+    // shared-memory addresses as plain integers: nothing in the loop goes through a generic -> shared conversion
+    uint32_t stage_a = smem_u32(stage);
+    asm volatile("mov.u32 %0, %0;" : "+r"(stage_a));                         // opaque: kept in a register instead of being re-derived (S2R + LEA) per use
+    const uint32_t full_a = stage_a + (uint32_t)(STAGES2 * sizeof(Stage2) + PIVOT_FIXHIT_BYTES), empty_a = full_a + STAGES2 * 8u;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES2; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, PIVOT_THREADS / 32); }
@@ -78,15 +79,12 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     }
     for (int i = threadIdx.x; i < (int)(PIVOT_FIXHIT_BYTES / sizeof(uint4)); i += PIVOT_THREADS) reinterpret_cast<uint4*>(fixhit)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
+    // one stage = the query chunk + the planes of the pair's chunk record: two TMA bulk copies
     auto issue = [&](int c, int s) {
-        mbar_expect_tx(full + s, (uint32_t)(sizeof(QChunk2) + RPL * W4 * sizeof(RefPlanes2)));
-        bulk_g2s(&stage[s].q, qsrc + c, (uint32_t)sizeof(QChunk2), full + s);
-#pragma unroll
-        for (int g = 0; g < RPL; ++g)
-#pragma unroll
-            for (int u = 0; u < W4; ++u)
-                bulk_g2s(&stage[s].ref[g][u], rsrc + g * group_stride + (size_t)c * STAGE2_REF_BYTES + (size_t)u * UNIT2_BYTES,
-                         (uint32_t)sizeof(RefPlanes2), full + s);
+        const uint32_t bar = full_a + (uint32_t)s * 8u, dst = stage_a + (uint32_t)s * (uint32_t)sizeof(Stage2);
+        mbar_expect_tx_a(bar, (uint32_t)(sizeof(QChunk2) + CHUNK2_PLANES));
+        bulk_g2s_a(dst, qsrc + c, (uint32_t)sizeof(QChunk2), bar);
+        bulk_g2s_a(dst + (uint32_t)sizeof(QChunk2), rsrc + (size_t)c * CHUNK2_BYTES, (uint32_t)CHUNK2_PLANES, bar);
     };
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES2 && s < p.n_chunks; ++s) issue(s, s);
@@ -122,16 +120,16 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     uint32_t executed = 0;                                                   // (slot, unit) iterations that were not skipped
     for (int c = 0; c < p.n_chunks; ++c) {
         const int s = c % STAGES2;
-        mbar_wait(full + s, (uint32_t)((c / STAGES2) & 1));
+        mbar_wait_a(full_a + (uint32_t)s * 8u, (uint32_t)((c / STAGES2) & 1));
         const Stage2& st = stage[s];
         // fix entries of this warp's slots in this chunk (usually 0..3): lane l fetches the column mask of entry l / RPL for
         // reference group l % RPL (one load for the whole warp, consumed after the counting work of the chunk)
         const uint32_t fb = st.q.fix_begin[warp], fe = st.q.fix_begin[warp + 1];
-        const uint8_t* gl0 = rsrc + (size_t)c * STAGE2_REF_BYTES;
+        const uint8_t* gl0 = rsrc + (size_t)c * CHUNK2_BYTES;                  // fix entries: byte offsets inside this chunk record
         uint32_t my_ent = 0, my_col = 0;
         if (fb + lane / RPL < fe) {
             my_ent = st.q.fix[fb + lane / RPL];
-            my_col = __ldg(reinterpret_cast<const uint32_t*>(gl0 + (lane % RPL) * group_stride + (my_ent & 0xffffu)));
+            my_col = __ldg(reinterpret_cast<const uint32_t*>(gl0 + (lane % RPL) * (W4 * UNIT2_MASKS) + (my_ent & 0xffffu)));
         }
 #pragma unroll
         for (int u = 0; u < W4; ++u) {
@@ -172,21 +170,26 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
                 my_col = 0;
                 if (e0 + lane / RPL < fe) {
                     my_ent = st.q.fix[e0 + lane / RPL];
-                    my_col = __ldg(reinterpret_cast<const uint32_t*>(gl0 + (lane % RPL) * group_stride + (my_ent & 0xffffu)));
+                    my_col = __ldg(reinterpret_cast<const uint32_t*>(gl0 + (lane % RPL) * (W4 * UNIT2_MASKS) + (my_ent & 0xffffu)));
                 }
                 resolve(my_ent, my_col);
             }
         }
-        // release the stage; the elected thread refills the stage consumed REFILL_LAG chunks ago (everybody is done with it
-        // by now, or will be within a few hundred cycles)
+        // release the stage.  Refill: the stage consumed REFILL_LAG chunks ago gets the chunk STAGES2 further on.  The warps take
+        // turns (chunk c: warp c % 16), so that no warp carries the producer's instructions on top of its counting work -- with
+        // one fixed producer warp that warp sets the pace of the block and the other fifteen wait for it at the head of the ring.
         __syncwarp();
         if (lane == 0) {
-            mbar_arrive(empty + s);
+            mbar_arrive_a(empty_a + (uint32_t)s * 8u);
+#if PIVOT_ROTATE
+            if (warp == (c % PIVOT_WARPS)) {
+#else
             if (warp == 0) {
+#endif
                 const int cr = c - REFILL_LAG, cn = cr + STAGES2;
                 if (cr >= 0 && cn < p.n_chunks) {
                     const int sr = cr % STAGES2;
-                    mbar_wait(empty + sr, (uint32_t)((cr / STAGES2) & 1));
+                    mbar_wait_a(empty_a + (uint32_t)sr * 8u, (uint32_t)((cr / STAGES2) & 1));
                     issue(cn, sr);
                 }
             }
@@ -219,8 +222,8 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     }
 }
 
-// Derived database of the pivot form for the references [begin, end): per (group, unit) a RefUnit2 record with
-//   base (copy), mc = base & ~(b0 ^ P.b0) & ~(b1 ^ P.b1), and the four one-hot planes of every word.
+// Derived database of the pivot form for the references [begin, end): per (group, unit), inside the chunk record of the
+// group's pair (common.cuh): base (copy), mc = base & ~(b0 ^ P.b0) & ~(b1 ^ P.b1), and the column masks of every word.
 // One thread per (group, unit, lane): 3 coalesced 16-byte loads, 2 16-byte + 16 coalesced 4-byte stores.
 // pivot[unit] = (b0, b1) planes of the pivot sequence, 4 words each.
 __global__ void __launch_bounds__(256) k_derive_pivot(const uint4* __restrict__ db, uint8_t* __restrict__ db2, const uint4* __restrict__ pivot,
@@ -247,7 +250,8 @@ __global__ void __launch_bounds__(256) k_derive_pivot(const uint4* __restrict__ 
     mc.y = keep_eq(keep_eq(rb.y, r0.y, p0.y), r1.y, p1.y);
     mc.z = keep_eq(keep_eq(rb.z, r0.z, p0.z), r1.z, p1.z);
     mc.w = keep_eq(keep_eq(rb.w, r0.w, p0.w), r1.w, p1.w);
-    RefUnit2* rec = reinterpret_cast<RefUnit2*>(db2 + db2_unit_bytes(group, unit, Wp));
+    RefPlanes2* rec = reinterpret_cast<RefPlanes2*>(db2 + db2_planes_bytes(group, unit, Wp));
+    uint32_t* colmask = reinterpret_cast<uint32_t*>(db2 + db2_masks_bytes(group, unit, Wp));     // [word][base A,C,G,T][site in word]
     if (fresh) {
         rec->base[lane] = rb;
         rec->mc[lane] = mc;
@@ -268,7 +272,7 @@ __global__ void __launch_bounds__(256) k_derive_pivot(const uint4* __restrict__ 
                 const uint32_t m = __ballot_sync(0xffffffffu, (oh[a] >> sbit) & 1u);
                 if (lane == sbit) mine = m;
             }
-            rec->colmask[k][a][lane] = mine;
+            colmask[(k * 4 + a) * 32 + lane] = mine;
         }
     }
 }

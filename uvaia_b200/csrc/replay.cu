@@ -59,17 +59,161 @@ struct RpState {
     int root[4];          // first keys of the heap root (valid when n == K)
     int cur_batch, mib;   // batch (of --pool accepted references) of the last candidate and max_incompatible at its start
     int restart;          // first position to re-test after an admission, or -1
+    int pend;             // literal mode: window position of a pair whose consensus stage the reference truncated, or -1
+    int t[4];             // literal mode: the truncated consensus counts of that pair (cons_prefix)
 };
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Literal emulation of hazard H1 (nearest.c:289-294, 428-433, 485-501).  The reference scores the
+// consensus stage of a whole batch (--pool accepted references, a batch also ends with its file) with the batch-wide
+// limit B = max over the queries of max_incompatible AT THE START of the batch, through
+// biomcmc_pairwise_score_matches_truncated_idx (alignment.c:855-884) / quick_pairwise_score_acgt_and_valid
+// (fastaseq.c:585-596): the loop over idx_c stops right after the site at which (valid - acgt) reaches B.  For a
+// reference whose full consensus mismatches ci are >= B the stored counts are those of that PREFIX of idx_c, and their
+// mismatch count is exactly B.  A query whose own limit m rose above B inside the batch then accepts the pair if
+// B + (D - ci) < m and scores it with the prefix counts.  cons_prefix recomputes the prefix counts of one such pair from
+// the packed planes: block-wide, three passes (per-thread ranges -> the range that holds the B-th mismatch -> binary
+// search of the site inside it -> counts up to that site).
+// ---------------------------------------------------------------------------------------------------------------------
+struct ConsSrc {            // what cons_prefix reads (all device pointers)
+    const uint4* db; const QChunk* qcons;      // packed planes of the local references; first chunk of the consensus slot's tile
+    int cons_qi;                               // slot of the consensus inside its tile
+    const uint32_t* cons_nib;                  // 4-bit codes of the consensus (idx_c sites only)
+    const uint32_t* camb; int n_camb;          // ambiguity codes of the consensus (site | code << 28)
+    const uint32_t* ramb_off; const uint32_t* ramb_ent;
+    int Wp, acgt;
+};
+
+__device__ __forceinline__ int block_sum(int v, int* s_red)
+{   // sum over the block; s_red holds RP_THREADS / 32 + 1 ints
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    int t = 0;
+#pragma unroll
+    for (int k = 0; k < RP_THREADS / 32; ++k) t += s_red[k];
+    return t;
+}
+
+// counts [acgt, text, partial, valid] of reference `lr` against the consensus over the sites <= p of the units [ua, ub)
+// (plane part only: sites where both hold a plain base)
+__device__ __forceinline__ void cons_units(const ConsSrc& c, int64_t lr, int ua, int ub, int64_t p, int& m_out, int& v_out)
+{
+    const int64_t group = lr / GROUP; const int lane = (int)(lr % GROUP);
+    int m = 0, v = 0;
+    for (int u = ua; u < ub; ++u) {
+        if ((int64_t)u * 128 > p) break;
+        const uint4 rb = c.db[db_unit_index(group, u, 0, lane, c.Wp)], r0 = c.db[db_unit_index(group, u, 1, lane, c.Wp)],
+                    r1 = c.db[db_unit_index(group, u, 2, lane, c.Wp)];
+        const uint4* q = c.qcons[u / W4].pl[u % W4][c.cons_qi];
+        const uint4 qb = q[0], q0 = q[1], q1 = q[2];
+        const uint32_t R[3][4] = {{rb.x, rb.y, rb.z, rb.w}, {r0.x, r0.y, r0.z, r0.w}, {r1.x, r1.y, r1.z, r1.w}};
+        const uint32_t Qv[3][4] = {{qb.x, qb.y, qb.z, qb.w}, {q0.x, q0.y, q0.z, q0.w}, {q1.x, q1.y, q1.z, q1.w}};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int64_t s0 = ((int64_t)u * 4 + k) * 32;
+            if (s0 > p) break;
+            const uint32_t keep = (p - s0 >= 31) ? 0xffffffffu : ((2u << (uint32_t)(p - s0)) - 1u);
+            const uint32_t V = R[0][k] & Qv[0][k] & keep;
+            const uint32_t M = V & ~(R[1][k] ^ Qv[1][k]) & ~(R[2][k] ^ Qv[2][k]);
+            v += __popc(V); m += __popc(M);
+        }
+    }
+    m_out = m; v_out = v;
+}
+
+// sites outside the planes (an ambiguity code on either side), entries e = tid, tid + stride, ...: adds to [text, partial, valid]
+// the events with lo <= site <= p.  Never an ACGT match: every such valid site is a mismatch of the truncation rule.
+__device__ __forceinline__ void cons_events(const ConsSrc& c, int64_t lr, int64_t lo, int64_t p, int tid, int stride, int& t, int& pa, int& v)
+{
+    if (c.acgt) return;                                           // --acgt: only A, C, G, T are coded, no lists
+    const uint32_t r0 = c.ramb_off[lr], r1 = c.ramb_off[lr + 1];
+    for (uint32_t e = r0 + tid; e < r1; e += stride) {
+        const uint32_t ent = c.ramb_ent[e], site = ent & AMB_SITE_MASK, rc = ent >> 28;
+        if ((int64_t)site < lo || (int64_t)site > p) continue;
+        const uint32_t qc = (c.cons_nib[site >> 3] >> ((site & 7u) * 4u)) & 15u;
+        if (!qc) continue;
+        ++v; pa += (qc & rc) != 0u; t += qc == rc;
+    }
+    const int64_t group = lr / GROUP; const int lane = (int)(lr % GROUP);
+    const uint32_t* dbw = reinterpret_cast<const uint32_t*>(c.db);
+    for (int e = tid; e < c.n_camb; e += stride) {
+        const uint32_t ent = c.camb[e], site = ent & AMB_SITE_MASK, qc = ent >> 28;
+        if ((int64_t)site < lo || (int64_t)site > p) continue;
+        const uint32_t w = site >> 5, b = site & 31u;
+        const size_t base = db_unit_index(group, (int)(w >> 2), 0, lane, c.Wp) * 4 + (w & 3u);
+        if (!((dbw[base] >> b) & 1u)) continue;                   // the reference holds no plain base here (its own codes: loop above)
+        const uint32_t x = (dbw[base + GROUP * 4] >> b) & 1u, y = (dbw[base + 2 * GROUP * 4] >> b) & 1u;
+        ++v; pa += (qc >> (x + 2u * y)) & 1u;
+    }
+}
+
+// block-wide; returns (through st->t) the counts the reference's truncated consensus stage holds for reference `lr` at limit B:
+// default mode [acgt, text, partial, valid], --acgt [mismatches, valid, -, -]
+__device__ void cons_prefix(const ConsSrc& c, int64_t lr, int B, RpState* st, int* s_red, int* s_scan)
+{
+    const int tid = threadIdx.x;
+    const int nU = c.Wp / 4, per = (nU + RP_THREADS - 1) / RP_THREADS;
+    const int ua = min(nU, tid * per), ub = min(nU, ua + per);
+    const int64_t BIG = (int64_t)c.Wp * 32;
+    // pass 1: mismatches (valid - acgt) of every thread's range
+    int m, v, et = 0, ep = 0, ev = 0;
+    cons_units(c, lr, ua, ub, BIG, m, v);
+    if (ub > ua) cons_events(c, lr, (int64_t)ua * 128, (int64_t)ub * 128 - 1, 0, 1, et, ep, ev);
+    __syncthreads();
+    s_scan[tid] = (v - m) + ev;
+    __syncthreads();
+    if (tid == 0) {
+        int run = 0, win = -1;
+        for (int k = 0; k < RP_THREADS; ++k) {
+            const int x = s_scan[k];
+            if (win < 0 && run + x >= B) { win = k; s_scan[RP_THREADS] = B - run; }
+            run += x;
+        }
+        s_scan[RP_THREADS + 1] = win;
+    }
+    __syncthreads();
+    const int win = s_scan[RP_THREADS + 1], need = s_scan[RP_THREADS];
+    int64_t pstar = BIG;                                          // fewer than B mismatches in all: nothing was cut
+    if (win >= 0) {
+        // pass 2: smallest site p of the winner's range with `need` mismatches in [range start, p]
+        const int wa = min(nU, win * per), wb = min(nU, wa + per);
+        int64_t lo = (int64_t)wa * 128, hi = (int64_t)wb * 128 - 1;
+        while (lo < hi) {
+            const int64_t mid = (lo + hi) >> 1;
+            int mm = 0, vv = 0, a = 0, b2 = 0, e = 0;
+            if (tid < wb - wa) cons_units(c, lr, wa + tid, wa + tid + 1, mid, mm, vv);
+            cons_events(c, lr, (int64_t)wa * 128, mid, tid, RP_THREADS, a, b2, e);
+            const int cnt = block_sum((vv - mm) + e, s_red);
+            if (cnt >= need) hi = mid; else lo = mid + 1;
+        }
+        pstar = lo;
+    }
+    // pass 3: the four counts over the sites <= pstar
+    cons_units(c, lr, ua, ub, pstar, m, v);
+    et = ep = ev = 0;
+    cons_events(c, lr, 0, pstar, tid, RP_THREADS, et, ep, ev);
+    const int tm = block_sum(m, s_red), tv = block_sum(v, s_red), tt = block_sum(et, s_red), tp = block_sum(ep, s_red), te = block_sum(ev, s_red);
+    if (tid == 0) {
+        if (c.acgt) { st->t[0] = tv - tm; st->t[1] = tv; st->t[2] = 0; st->t[3] = 0; }
+        else { st->t[0] = tm; st->t[1] = tm + tt; st->t[2] = tm + tp; st->t[3] = tv + te; }
+    }
+    __syncthreads();
+}
 
 __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int heap_in_smem)
 {
     extern __shared__ __align__(16) uint8_t smem[];
     uint4* s_sc = reinterpret_cast<uint4*>(smem);                                  // RP_WIN raw counts
     uint32_t* s_mask = reinterpret_cast<uint32_t*>(smem + RP_WIN * sizeof(uint4)); // candidate bits
-    uint32_t* s_fmask = s_mask + RP_WIN / 32;                                      // hazard-H1 bits
+    uint32_t* s_fmask = s_mask + RP_WIN / 32;                                      // hazard-H1 bits (closed form: flags; literal: truncated pairs)
     int32_t* s_misc = reinterpret_cast<int32_t*>(s_fmask + RP_WIN / 32);           // 32 ints
-    HeapItem* s_heap = reinterpret_cast<HeapItem*>(s_misc + 32);
+    int32_t* s_scan = s_misc + 32;                                                 // RP_THREADS + 2 ints (cons_prefix)
+    HeapItem* s_heap = reinterpret_cast<HeapItem*>(s_scan + RP_THREADS + 32);
     RpState* st = reinterpret_cast<RpState*>(s_misc);
+    int* s_red = s_misc + 24;                                                      // RP_THREADS / 32 ints (block_sum)
 
     const int row = blockIdx.x;
     const int q = ((row / QTILE) * p.world + p.rank) * QTILE + row % QTILE;        // query this row belongs to
@@ -89,17 +233,29 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
             st->n = n0; st->max_inc = p.max_inc[row];
             for (int k = 0; k < 4; ++k) st->root[k] = n0 == K ? a[1].s[k] : 0;
             st->cur_batch = p.batch_id[row]; st->mib = p.max_inc_batch[row];
-            st->restart = -1;
+            st->restart = -1; st->pend = -1;
         }
+    }
+    // literal mode: the batch-wide limit of the consensus stage (nearest.c:290-291).  A launch never straddles a batch
+    // boundary; the first launch of a batch takes the maximum the previous launch accumulated, the others the carried value.
+    const int lit = p.literal;
+    const int B = lit ? (p.batch_start ? *p.b_prev : *p.b_carry_in) : 0;
+    if (lit && row == 0 && threadIdx.x == 0) { *p.b_carry_out = B; *p.b_zero = 0; }
+    ConsSrc csrc;
+    if (lit) {
+        csrc.db = p.db; csrc.qcons = p.qcons; csrc.cons_qi = p.cons_qi; csrc.cons_nib = p.cons_nib; csrc.camb = p.camb; csrc.n_camb = p.n_camb;
+        csrc.ramb_off = p.ramb_off; csrc.ramb_ent = p.ramb_ent; csrc.Wp = p.Wp; csrc.acgt = acgt;
     }
     int admitted = 0, h1 = 0;                                                      // thread 0 only
     __syncthreads();
 
     for (int g = 0; g < p.nseg; ++g) {
-        const int seg_n = p.seg_cnt[g];
         const int64_t seg_global = p.seg_global[g];
         const int64_t seg_col = (int64_t)g * p.seg_stride;
-        for (int w0 = 0; w0 < seg_n; w0 += RP_WIN) {
+        // the launch covers the global ordinals [ord_begin, ord_end) of the round (the whole round unless a batch ends inside it)
+        const int seg_lo = (int)max((int64_t)0, p.ord_begin - seg_global);
+        const int seg_n = (int)min((int64_t)p.seg_cnt[g], p.ord_end - seg_global);
+        for (int w0 = seg_lo; w0 < seg_n; w0 += RP_WIN) {
             const int cntw = min(RP_WIN, seg_n - w0);
 #pragma unroll
             for (int k = 0; k < RP_PER; ++k) {
@@ -120,13 +276,27 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
                         const uint4 sc = s_sc[i];
                         const int x = (int)sc.x, y = (int)sc.y, z = (int)sc.z, w = (int)sc.w;
                         const int D = acgt ? (y - x) : (w - x);
-                        if (D < max_inc) {
+                        if (lit && B < max_inc) {
+                            // this query's limit rose above the batch-wide limit inside the batch: references whose consensus
+                            // stage reached B were truncated there (their stored consensus mismatches ARE B)
+                            const uint4 cc = tcons[seg_col + w0 + i];
+                            const int ci = acgt ? (int)(cc.y - cc.x) : (int)(cc.w - cc.x);
+                            if (ci >= B) {
+                                // accepted by the three staged tests iff B + (D - ci) < max_inc (nearest.c:488-496); the truncated
+                                // item can only be worse than the full one on the first key, so x < root.s0 cannot enter a full heap
+                                flag = (D - ci + B < max_inc) && (n < K || x >= r0);
+                            } else if (D < max_inc) {
+                                if (n < K) cand = true;
+                                else if (acgt) cand = x > r0 || (x == r0 && y >= r1);
+                                else cand = x > r0 || (x == r0 && (y > r1 || (y == r1 && (z > r2 || (z == r2 && w >= r3)))));
+                            }
+                        } else if (D < max_inc) {
                             // strictly better than the root is decided on all six keys by thread 0; here: not worse on the
                             // keys the pair record holds
                             if (n < K) cand = true;
                             else if (acgt) cand = x > r0 || (x == r0 && y >= r1);
                             else cand = x > r0 || (x == r0 && (y > r1 || (y == r1 && (z > r2 || (z == r2 && w >= r3)))));
-                        } else if (mib < max_inc) {
+                        } else if (!lit && mib < max_inc) {
                             // hazard H1: max_incompatible rose inside the current batch; the reference would
                             // have scored this pair with consensus counts truncated at the batch-start limit.  Necessary
                             // condition for its result to differ from the closed form:
@@ -144,59 +314,110 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
                 __syncthreads();
                 // ---- thread 0: admit in file order until the state changes ----
                 if (threadIdx.x == 0) {
-                    int nn = n, mi = max_inc, restart = -1, cb = cur_batch, mb = mib;
+                    int nn = n, mi = max_inc, restart = -1, cb = cur_batch, mb = mib, pend = -1;
+                    // heap_insert (min_heap.c:93-117) + the max_incompatible update (nearest.c:475 / :508); true = the state changed
+                    auto admit = [&](const HeapItem& it) -> bool {
+                        if (nn == K) {
+                            if (!item_less(a[1], it)) return false;
+                            a[1] = it;
+                            heap_down(a, nn, 1);
+                        } else {
+                            ++nn;
+                            a[nn] = it;
+                            heap_up(a, nn);
+                        }
+                        ++admitted;
+                        p.ever_best[it.r] = 1;                                              // is_best, nearest.c:505
+                        if (nn == K) {
+                            mi = item_mismatch(a[1], acgt) + 1;
+                            for (int k = 0; k < 4; ++k) st->root[k] = a[1].s[k];
+                        }
+                        return true;
+                    };
                     for (int mw = start >> 5; mw < (cntw + 31) >> 5 && restart < 0; ++mw) {
-                        uint32_t m = s_mask[mw];
+                        const uint32_t hm = lit ? s_fmask[mw] : 0u;
+                        uint32_t m = s_mask[mw] | hm;
                         while (m) {
                             const int b = __ffs(m) - 1;
                             m &= m - 1;
                             const int i = mw * 32 + b;
                             if (i < start) continue;
+                            if ((hm >> b) & 1u) { pend = i; restart = i; break; }       // truncated in the reference: all threads recount the prefix
                             const uint4 sc = s_sc[i];
                             const int64_t col = seg_col + w0 + i;
                             const int r = (int)(seg_global + w0 + i);
-                            const int bt = r / p.pool;
-                            if (bt != cb) { cb = bt; mb = mi; }
+                            if (!lit) {
+                                const int bt = r / p.pool;
+                                if (bt != cb) { cb = bt; mb = mi; }
+                            }
                             const uint4 cc = tcons[col];
                             const int c0 = (int)cc.x, nonn = (int)tmeta[col].x;
                             HeapItem it;
                             if (!acgt) { it.s[0] = sc.x; it.s[1] = sc.y; it.s[2] = sc.z; it.s[3] = sc.w; it.s[4] = (int)sc.x - c0; it.s[5] = nonn; }
                             else { it.s[0] = sc.x; it.s[1] = sc.y; it.s[2] = (int)sc.x - c0; it.s[3] = nonn; it.s[4] = (int)(sc.y - sc.x) - (int)sc.z; it.s[5] = sc.z; }
                             it.r = r; it.pad = 0;
-                            if (nn == K) {                                                  // heap_insert, min_heap.c:95-106
-                                if (!item_less(a[1], it)) continue;
-                                a[1] = it;
-                                heap_down(a, nn, 1);
-                            } else {                                                        // min_heap.c:108-116
-                                ++nn;
-                                a[nn] = it;
-                                heap_up(a, nn);
-                            }
-                            ++admitted;
-                            p.ever_best[r] = 1;                                             // is_best, nearest.c:505
-                            {   // the closed form may differ from the reference for THIS pair too (consensus stage truncated)
+                            if (!admit(it)) continue;
+                            if (!lit) {   // the closed form may differ from the reference for THIS pair too (consensus stage truncated)
                                 const int ci = acgt ? (int)(cc.y - cc.x) : (int)(cc.w - cc.x);
                                 if (ci >= mb) ++h1;
                             }
-                            if (nn == K) {                                                  // nearest.c:475 / :508
-                                mi = item_mismatch(a[1], acgt) + 1;
-                                for (int k = 0; k < 4; ++k) st->root[k] = a[1].s[k];
-                                restart = i + 1;
-                                break;
-                            }
+                            if (nn == K) { restart = i + 1; break; }
                         }
                     }
-                    // hazard flags of the positions that were passed with the state they were tested against
-                    const int upto = restart < 0 ? cntw : restart;
-                    for (int mw = start >> 5; mw < (upto + 31) >> 5; ++mw) {
-                        uint32_t f = s_fmask[mw];
-                        if (mw == (start >> 5)) f &= 0xffffffffu << (start & 31);
-                        if (mw == (upto >> 5) && (upto & 31)) f &= (1u << (upto & 31)) - 1u;
-                        h1 += __popc(f);
+                    if (!lit) {
+                        // hazard flags of the positions that were passed with the state they were tested against
+                        const int upto = restart < 0 ? cntw : restart;
+                        for (int mw = start >> 5; mw < (upto + 31) >> 5; ++mw) {
+                            uint32_t f = s_fmask[mw];
+                            if (mw == (start >> 5)) f &= 0xffffffffu << (start & 31);
+                            if (mw == (upto >> 5) && (upto & 31)) f &= (1u << (upto & 31)) - 1u;
+                            h1 += __popc(f);
+                        }
                     }
-                    st->n = nn; st->max_inc = mi; st->cur_batch = cb; st->mib = mb; st->restart = restart;
+                    st->n = nn; st->max_inc = mi; st->cur_batch = cb; st->mib = mb; st->restart = restart; st->pend = pend;
                 }
                 __syncthreads();
+                const int pend = st->pend;
+                if (pend >= 0) {
+                    // literal mode: the pair at `pend` reaches the heap with the TRUNCATED consensus counts (block-wide recount)
+                    const int64_t ord = seg_global + w0 + pend;
+                    cons_prefix(csrc, ord - p.local_ord0, B, st, s_red, s_scan);
+                    if (threadIdx.x == 0) {
+                        const uint4 sc = s_sc[pend];
+                        const int64_t col = seg_col + w0 + pend;
+                        const uint4 cc = tcons[col];
+                        const int nonn = (int)tmeta[col].x;
+                        const int t0 = st->t[0], t1 = st->t[1], t2 = st->t[2], t3 = st->t[3];
+                        HeapItem it;
+                        if (!acgt) {
+                            // score[i] = stage counts + truncated consensus counts; score[4] = the stage counts' ACGT matches (nearest.c:499-500)
+                            it.s[0] = (int)sc.x - (int)cc.x + t0; it.s[1] = (int)sc.y - (int)cc.y + t1; it.s[2] = (int)sc.z - (int)cc.z + t2;
+                            it.s[3] = (int)sc.w - (int)cc.w + t3; it.s[4] = (int)sc.x - (int)cc.x; it.s[5] = nonn;
+                        } else {
+                            // tile: sc = (matches, valid, mismatches on idx); cc = (consensus matches, consensus valid).  nearest.c:456-470
+                            const int V = (int)sc.y - (int)cc.y + t1;                           // valid pairs with the prefix of idx_c
+                            const int M = ((int)sc.y - (int)sc.x) - ((int)cc.y - (int)cc.x) + t0;   // mismatches: stages + B
+                            it.s[0] = V - M; it.s[1] = V; it.s[2] = (V - M) - (t1 - t0); it.s[3] = nonn; it.s[4] = M - (int)sc.z; it.s[5] = sc.z;
+                        }
+                        it.r = (int)ord; it.pad = 0;
+                        int nn = st->n, mi = st->max_inc;
+                        ++h1;
+                        if (nn == K) {
+                            if (item_less(a[1], it)) {
+                                a[1] = it; heap_down(a, nn, 1);
+                                ++admitted; p.ever_best[it.r] = 1;
+                                mi = item_mismatch(a[1], acgt) + 1;
+                                for (int k = 0; k < 4; ++k) st->root[k] = a[1].s[k];
+                            }
+                        } else {
+                            ++nn; a[nn] = it; heap_up(a, nn);
+                            ++admitted; p.ever_best[it.r] = 1;
+                            if (nn == K) { mi = item_mismatch(a[1], acgt) + 1; for (int k = 0; k < 4; ++k) st->root[k] = a[1].s[k]; }
+                        }
+                        st->n = nn; st->max_inc = mi; st->pend = -1; st->restart = pend + 1;
+                    }
+                    __syncthreads();
+                }
                 const int restart = st->restart;
                 if (restart < 0 || restart >= cntw) break;
                 start = restart;
@@ -208,6 +429,7 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
     const int n = st->n;
     if (threadIdx.x == 0) {
         p.heap_n[row] = n; p.max_inc[row] = st->max_inc; p.batch_id[row] = st->cur_batch; p.max_inc_batch[row] = st->mib;
+        if (lit) atomicMax(p.b_acc, st->max_inc);                                  // batch-wide limit of the next batch = max over the queries
         if (admitted) atomicAdd(p.counters + 0, (unsigned long long)admitted);
         if (h1) atomicAdd(p.counters + 1, (unsigned long long)h1);
     }
@@ -231,7 +453,7 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
 
 static size_t replay_smem_bytes(int K, int* in_smem)
 {
-    size_t fixed = RP_WIN * sizeof(uint4) + 2 * (RP_WIN / 32) * 4 + 32 * 4;
+    size_t fixed = RP_WIN * sizeof(uint4) + 2 * (RP_WIN / 32) * 4 + 32 * 4 + (RP_THREADS + 32) * 4;
     *in_smem = (K + 1) <= RP_HEAP_SMEM_ITEMS;
     return fixed + (*in_smem ? (size_t)(K + 1) * sizeof(HeapItem) : 0);
 }

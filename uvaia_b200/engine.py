@@ -38,13 +38,13 @@ def prune_queries(text: np.ndarray, trim=0, acgt=False, keep_more_resolved=True)
 
 class Engine:
     def __init__(self, nchar, nbest=100, trim=0, acgt=False, pool=512, device=0, first_round=0, max_round=0,
-                 early_abort=False, rank=0, world=1, db_capacity=0, pair_kernel=None):
+                 early_abort=False, rank=0, world=1, db_capacity=0, pair_kernel=None, closed_form=False):
         if pair_kernel is None:      # test / debug knob: UVG_PAIR_KERNEL=auto|general|pivot (include/uvaia_b200.h, uvg_params.pair_kernel)
             pair_kernel = PAIR_KERNELS[os.environ.get("UVG_PAIR_KERNEL", "auto")]
         self._lib = _capi.lib()
         p = _capi.uvg_params(_capi.UVG_ABI_VERSION, int(nchar), int(trim), int(nbest), int(bool(acgt)), int(pool),
                              int(device), int(first_round), int(max_round), int(bool(early_abort)), int(rank), int(world),
-                             int(pair_kernel), 0, int(db_capacity))
+                             int(pair_kernel), int(bool(closed_form)), int(db_capacity))
         h = C.c_void_p()
         rc = self._lib.uvg_create(C.byref(p), C.byref(h))
         if rc != 0:
@@ -146,6 +146,10 @@ class Engine:
         self._ck(self._lib.uvg_import_packed(self._h, addr, size, C.byref(n)), "uvg_import_packed")
         return n.value
 
+    def mark_file_end(self, n_accepted_so_far=-1):
+        """the references accepted so far end a -r file (the reference's batch ends with its file, nearest.c:245-286)"""
+        self._ck(self._lib.uvg_mark_file_end(self._h, int(n_accepted_so_far)), "uvg_mark_file_end")
+
     def drop_refs(self):
         self._ck(self._lib.uvg_drop_refs(self._h), "uvg_drop_refs")
 
@@ -178,7 +182,12 @@ class Engine:
         return arr["score"].copy(), arr["ref"].copy()
 
     def heaps(self):
-        return [self.heap(q) for q in range(self.n_query)]
+        """every query's table: [(scores int32[n,6], refs int64[n])] (one call: uvg_get_all_heaps)"""
+        dt = np.dtype([("score", np.int32, 6), ("ref", np.int64)])
+        buf = np.empty((self.n_query, self.K), dt)
+        n = np.empty(self.n_query, np.int32)
+        self._ck(self._lib.uvg_get_all_heaps(self._h, buf.ctypes.data, n.ctypes.data), "uvg_get_all_heaps")
+        return [(buf["score"][q, :n[q]].copy(), buf["ref"][q, :n[q]].copy()) for q in range(self.n_query)]
 
     def ever_best(self, first, n):
         flags = np.zeros(int(n), np.uint8)

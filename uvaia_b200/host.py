@@ -184,6 +184,7 @@ def search_files(query_file, ref_files, nbest=100, trim=0, acgt=False, ambig_q=0
                 if len(buf_rows) >= batch_rows:
                     flush()
             flush()
+            eng.mark_file_end()                                  # the reference's batch ends with the file (nearest.c:245-286)
         out.rows = eng.heaps()
         out.ever_best = eng.ever_best(0, len(out.ref_names))
         out.stats = eng.stats()
