@@ -21,5 +21,7 @@ for f in hashtable lowlevel random_number_gen constant_random_lists random_numbe
 done
 CFLAGS="-std=gnu11 -O3 -funroll-loops -fopenmp -w -Dsave_neigbours_to_gz_file=save_neighbours_to_gz_file -I$HERE/cfg -I$HERE/stub -I$L -I$R/src"
 gcc $CFLAGS -o "$OUT/uvaia_ref" "$R/src/nearest.c" "$R/src/fastaseq.c" "$R/src/min_heap.c" "$R/src/utils.c" $LIBSRC -lz -lm
+# uvaiaball (src/ball.c): the reference's radius search, for the goldens of the uvg_ball_* entry points
+gcc $CFLAGS -o "$OUT/uvaiaball_ref" "$R/src/ball.c" "$R/src/fastaseq.c" "$R/src/utils.c" $LIBSRC -lz -lm
 gcc $CFLAGS -fPIC -shared -o "$OUT/libuvaia_ref_score.so" "$R/src/fastaseq.c" "$R/src/min_heap.c" "$R/src/utils.c" $LIBSRC -lz -lm
-echo "built $OUT/uvaia_ref and $OUT/libuvaia_ref_score.so"
+echo "built $OUT/uvaia_ref, $OUT/uvaiaball_ref and $OUT/libuvaia_ref_score.so"

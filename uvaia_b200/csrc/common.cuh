@@ -55,20 +55,34 @@ static_assert(sizeof(QChunk) % 16 == 0, "bulk copy size must be a multiple of 16
 // chunk's fix block, and every ambiguity code, is resolved by the epilogue (pair_epilogue.cuh).
 // Derived database: per (pair of groups = the 64 references of a thread block, chunk of WC column words) one contiguous
 // 12 KB record
-//     planes   [group of the pair][unit][ uint4 base[32] | uint4 mc[32] ]                    4 KB: ONE TMA bulk copy per chunk
+//     planes   [group of the pair][unit][ uint4 base[32] | uint4 mc[32] ]                    4 KB  \ staged by TMA bulk copies
+//     counts   [group of the pair][unit][32 references] uint32: popc(mc unit) | popc(base unit) << 16   512 B /
 //     colmasks [group of the pair][unit][4 words][4 bases A,C,G,T][32 sites] uint32         8 KB: read by fix entries only
-constexpr int STAGES2 = 8;
+// The counts serve the units in which a query holds no plain base at all (inside an N run, trimmed away): there
+// popc(r.base & nq) and popc(r.mc & ne) are the reference's own unit totals -- one add instead of 16 LOP3 + 4 POPC.
+#ifndef PIVOT_SKIP2
+#define PIVOT_SKIP2 1           // 1: all-N units through the counts table, the others in halves of 64 sites; 0: whole units (r01 kernel)
+#endif
+#ifndef PIVOT_STAGES
+#define PIVOT_STAGES 8
+#endif
+constexpr int STAGES2 = PIVOT_STAGES;
 constexpr int UNIT2_PLANES = 2 * GROUP * 16;                         // base + mc of one (group, unit): 1 KB
 constexpr int UNIT2_MASKS = 4 * 4 * GROUP * 4;                       // column masks of one (group, unit): 2 KB
 constexpr int CHUNK2_PLANES = RPL * W4 * UNIT2_PLANES;               // 4 KB
-constexpr int CHUNK2_BYTES = CHUNK2_PLANES + RPL * W4 * UNIT2_MASKS; // 12 KB per (pair of groups, chunk)
-constexpr int FIXCAP = 248;                                          // fix entries a chunk of a query tile can carry
+constexpr int CHUNK2_COUNTS = RPL * W4 * GROUP * 4;                  // 512 B
+constexpr int CHUNK2_STAGED = CHUNK2_PLANES + CHUNK2_COUNTS;         // what a ring stage holds of a chunk record
+constexpr int CHUNK2_BYTES = CHUNK2_STAGED + RPL * W4 * UNIT2_MASKS; // 12.5 KB per (pair of groups, chunk)
+constexpr int FIXCAP = 236;                                          // fix entries a chunk of a query tile can carry
 constexpr int PIVOT_QW = 4;                                          // query slots per warp of k_pairpivot
 constexpr int PIVOT_WARPS = QTILE / PIVOT_QW;
 struct __align__(16) QChunk2 {
     uint4    pl[W4][QTILE][2];       // [unit][slot][plane], COMPLEMENTS: 0 = no plain base here (or trimmed / padding), 1 = not the pivot base
     uint8_t  fix_begin[32];          // [warp] first entry of the warp's slots; [PIVOT_WARPS] = total
     uint8_t  active[W4][16];         // per unit and warp: bit j set <=> the warp's j-th slot (PairParams::wslot) has work in this unit
+    uint16_t half[16];               // per warp: bit u * 8 + j * 2 + h set <=> words 2h, 2h+1 of unit u hold a site where slot j differs
+                                     //     from the pivot (N, gap, code, SNP) and the unit is not all-N: that half is counted from the planes
+    uint8_t  fulln[16];              // per warp: bit u * 4 + j set <=> slot j holds no plain base in unit u: the counts table answers
     uint32_t fix[FIXCAP];            // byte offset of the entry's column-mask word inside the chunk record of the derived database
                                      //     (for the first group of the pair; the second is W4 * UNIT2_MASKS further) | slot-within-tile << 16
 };
@@ -83,7 +97,11 @@ __host__ __device__ inline size_t db2_planes_bytes(int64_t group, int unit, int 
 }
 __host__ __device__ inline size_t db2_masks_bytes(int64_t group, int unit, int Wp)        // column masks of (group, unit)
 {
-    return db2_chunk_bytes(group, unit, Wp) + CHUNK2_PLANES + (size_t)((group % RPL) * W4 + unit % W4) * UNIT2_MASKS;
+    return db2_chunk_bytes(group, unit, Wp) + CHUNK2_STAGED + (size_t)((group % RPL) * W4 + unit % W4) * UNIT2_MASKS;
+}
+__host__ __device__ inline size_t db2_counts_bytes(int64_t group, int unit, int Wp)       // unit totals of the 32 references of (group, unit)
+{
+    return db2_chunk_bytes(group, unit, Wp) + CHUNK2_PLANES + (size_t)((group % RPL) * W4 + unit % W4) * GROUP * 4;
 }
 
 // Heap slot (32 B): the reference's q_item (src/min_heap.h:14-18) with name -> ordinal.

@@ -136,6 +136,8 @@ struct uvg_ctx {
     ncclComm_t comm = nullptr;
     // host cache of the heaps (filled lazily by uvg_get_heap, invalidated by every search / reset)
     int64_t work_seen = 0, work_last = 0;
+    int64_t pivot_halves = 0;                         // pivot form: (slot, 64-site half) items a thread block of every tile counts, summed over the tiles
+    int64_t work_host = 0;                            // executed work the host derives from the masks (pairpivot.cu does not count in the kernel)
     bool heaps_cached = false;
     std::vector<HeapItem> h_heaps; std::vector<int32_t> h_heap_n, h_max_inc;
 };
@@ -383,7 +385,7 @@ static int reset_heaps(uvg_ctx* c)
     }
     if (c->d_ever && c->ever_cap) UVG_CUDA(c, cudaMemsetAsync(c->d_ever, 0, c->ever_cap, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));                              // `init` goes out of scope
-    c->db_scored = 0; c->heaps_cached = false; c->work_seen = 0; c->search_open = false; c->n_ev = 0;
+    c->db_scored = 0; c->heaps_cached = false; c->work_seen = 0; c->work_host = 0; c->search_open = false; c->n_ev = 0;
     c->rounds_done = 0; c->round_local_start = 0; c->round_global_start = 0;
     c->next_round = round_size_first(c->prm);
     uvg_stats z{};
@@ -586,7 +588,9 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
                                 v.x = ~v.x; v.y = ~v.y; v.z = ~v.z; v.w = ~v.w;
                             }
                             const uint4& e = blk.pl[u][qi][1];
-                            if (e.x | e.y | e.z | e.w) ++work[(size_t)qt * QTILE + qi];
+                            const uint4& b = blk.pl[u][qi][0];
+                            if ((b.x & b.y & b.z & b.w) == 0xffffffffu) work[(size_t)qt * QTILE + qi] += 1;               // table lookup
+                            else work[(size_t)qt * QTILE + qi] += 4 * (((e.x | e.y) != 0u) + ((e.z | e.w) != 0u));       // halves counted from the planes
                         }
                 }
         });
@@ -610,6 +614,7 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
         // per chunk: the active-slot nibble of every warp and unit, and the fix block: entries ordered by warp; what does
         // not fit goes to the slot's epilogue list
         size_t n_overflow = 0;
+        int64_t halves_total = 0;
         std::vector<size_t> cur(c->n_slots, 0);
         for (int qt = 0; qt < c->n_qtiles; ++qt)
             for (int ch = 0; ch < c->n_chunks; ++ch) {
@@ -624,19 +629,27 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
                         if (q >= c->n_slots) continue;
                         for (int u = 0; u < W4; ++u) {
                             const uint4& e = blk.pl[u][qi][1];
+                            const uint4& b = blk.pl[u][qi][0];
                             if (e.x | e.y | e.z | e.w) blk.active[u][wp] |= (uint8_t)(1u << j);
+                            if ((b.x & b.y & b.z & b.w) == 0xffffffffu) blk.fulln[wp] |= (uint8_t)(1u << (u * 4 + j));     // no plain base in the unit
+                            else {
+                                if (e.x | e.y) blk.half[wp] |= (uint16_t)(1u << (u * 8 + j * 2));
+                                if (e.z | e.w) blk.half[wp] |= (uint16_t)(1u << (u * 8 + j * 2 + 1));
+                            }
                         }
                         while (cur[q] < snp[q].size() && (snp[q][cur[q]] & AMB_SITE_MASK) < site_end) {
                             const uint32_t ent = snp[q][cur[q]++], site = ent & AMB_SITE_MASK, code = ent >> 28;
                             const uint32_t w = site >> 5, a = code == 1 ? 0 : code == 2 ? 1 : code == 4 ? 2 : 3;
                             if (n >= FIXCAP) { epi[q].push_back(ent); ++n_overflow; continue; }
-                            const uint32_t off = CHUNK2_PLANES + ((w % WC) / 4) * UNIT2_MASKS + (((w & 3) * 4 + a) * 32 + (site & 31)) * 4;
+                            const uint32_t off = CHUNK2_STAGED + ((w % WC) / 4) * UNIT2_MASKS + (((w & 3) * 4 + a) * 32 + (site & 31)) * 4;
                             blk.fix[n++] = off | ((uint32_t)qi << 16);
                         }
                     }
                 }
                 blk.fix_begin[PIVOT_WARPS] = (uint8_t)n;
+                for (int wp = 0; wp < PIVOT_WARPS; ++wp) halves_total += __builtin_popcount(blk.half[wp]);
             }
+        c->pivot_halves = halves_total;
         fix_off.assign(c->n_slots + 1, 0);
         for (int q = 0; q < c->n_slots; ++q) {
             fix_off[q] = (uint32_t)fix_ent.size();
@@ -654,7 +667,7 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     const auto t_host = std::chrono::steady_clock::now();
     if (bcast) {
         // what the other ranks cannot know: the form chosen, the sizes of the site sets and of the two variable lists
-        int64_t hdr[8] = {pivot_ok ? 1 : 0, n_idx, n_idx_m, n_idx_c, (int64_t)amb_ent.size(), (int64_t)fix_ent.size(), n_fix_total, 0x55564731};
+        int64_t hdr[8] = {pivot_ok ? 1 : 0, n_idx, n_idx_m, n_idx_c, (int64_t)amb_ent.size(), (int64_t)fix_ent.size(), n_fix_total | (c->pivot_halves << 32), 0x55564731};
         int64_t* d_hdr = nullptr;
         UVG_CUDA(c, cudaMalloc(&d_hdr, sizeof hdr));
         UVG_CUDA(c, cudaMemcpyAsync(d_hdr, hdr, sizeof hdr, cudaMemcpyHostToDevice, c->st));
@@ -664,7 +677,7 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
         cudaFree(d_hdr);
         if (hdr[7] != 0x55564731) UVG_FAIL(c, UVG_ESTATE, "uvg_set_queries: the ranks disagree about the query broadcast");
         if (!do_prep) {
-            pivot_ok = hdr[0] != 0; n_idx = (int)hdr[1]; n_idx_m = (int)hdr[2]; n_idx_c = (int)hdr[3]; n_fix_total = hdr[6];
+            pivot_ok = hdr[0] != 0; n_idx = (int)hdr[1]; n_idx_m = (int)hdr[2]; n_idx_c = (int)hdr[3]; n_fix_total = hdr[6] & 0xffffffffLL; c->pivot_halves = hdr[6] >> 32;
             amb_ent.assign((size_t)hdr[4], 0u);
             if (pivot_ok) {
                 fix_ent.assign((size_t)hdr[5], 0u);
@@ -1327,6 +1340,10 @@ static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t
         fill_pair_params(c, pp, lstart, lstart + cnt, b, (int64_t)c->rank * c->seg_cap);
         UVG_CUDA(c, c->pivot_on ? launch_pairpivot(pp, c->st) : launch_paircount(pp, c->prm.acgt_mode, c->st));
         c->stats.pair_kernel_launches += 1;
+        if (c->pivot_on && PIVOT_SKIP2) {   // executed (pair, 4-word unit) iterations per lane of this launch: blocks per tile x halves / 2 x references per lane
+            const int64_t per = GROUP * RPL, pairs = (lstart + cnt + per - 1) / per - lstart / per;
+            c->work_host += pairs * c->pivot_halves * RPL / 2;
+        }
     }
     UVG_CUDA(c, cudaEventRecord(eb, c->st));
     ++*n_ev;
@@ -1470,13 +1487,16 @@ extern "C" int uvg_wait(uvg_ctx* c)
         c->ever_reduced = false;
     }
     UVG_CUDA(c, cudaEventRecord(c->ev_b, c->st));
-    UVG_CUDA(c, cudaMemcpyAsync(c->h_pinned + 20, c->d_counters + 2, 8, cudaMemcpyDeviceToHost, c->st));
+    UVG_CUDA(c, cudaMemcpyAsync(c->h_pinned + 20, c->d_counters + 2, 16, cudaMemcpyDeviceToHost, c->st));
     UVG_CUDA(c, cudaEventSynchronize(c->ev_b));
     int rc = sync_all(c);
     if (rc) return rc;
     c->search_open = false;
-    c->work_last = (int64_t)c->h_pinned[20] - c->work_seen;
-    c->work_seen = (int64_t)c->h_pinned[20];
+    {   // executed (pair, 4-word unit) iterations per lane: whole units + halves / 2 (pairpivot.cu counts halves of two words)
+        const int64_t total = (int64_t)c->h_pinned[20] + c->work_host;
+        c->work_last = total - c->work_seen;
+        c->work_seen = total;
+    }
     float ms = 0; cudaEventElapsedTime(&ms, c->ev_a, c->ev_b);
     c->stats.search_ms = ms;
     for (size_t i = 0; i < c->n_ev; ++i) {        // events alternate: pair-count launch, replay launch

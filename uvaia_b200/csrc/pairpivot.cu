@@ -43,14 +43,22 @@ static_assert(sizeof(RefPlanes2) == UNIT2_PLANES, "planes of one (group, unit) o
 struct __align__(16) Stage2 {
     QChunk2    q;
     RefPlanes2 ref[RPL][W4];
+    uint32_t   cnt[RPL][W4][GROUP];      // unit totals of every reference: popc(mc) | popc(base) << 16
 };
-static_assert(sizeof(RefPlanes2) * RPL * W4 == CHUNK2_PLANES, "staged prefix of a chunk record");
+static_assert(sizeof(RefPlanes2) * RPL * W4 == CHUNK2_PLANES && sizeof(Stage2) == sizeof(QChunk2) + CHUNK2_STAGED, "staged prefix of a chunk record");
 constexpr size_t PIVOT_FIXHIT_BYTES = QTILE * GROUP * RPL * sizeof(uint16_t);       // per (slot, reference of the block): matches found by fix entries
 constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + PIVOT_FIXHIT_BYTES + 2 * STAGES2 * sizeof(uint64_t);
-constexpr int REFILL_LAG = 2;
 #ifndef PIVOT_ROTATE
-#define PIVOT_ROTATE 1          // 1: the warps take turns refilling the ring (chunk c: warp c % 16); 0: warp 0 refills (r01 kernel)
+#define PIVOT_ROTATE 0          // 1: the warps take turns refilling the ring (chunk c: warp c % 16) -- measured 1.6x SLOWER; 0: warp 0 refills
 #endif
+#ifndef PIVOT_COPIES
+#define PIVOT_COPIES 1          // bulk copies per stage for the reference side: 1 (4.5 KB) or 4 (1 KB per (group, unit) + the counts)
+#endif
+#ifndef PIVOT_LAG
+#define PIVOT_LAG 2
+#endif
+constexpr int REFILL_LAG = PIVOT_LAG;
+
 constexpr int QW2 = PIVOT_QW;                           // query slots per warp (register tile QW2 x RPL pairs per lane)
 constexpr int PIVOT_THREADS = PIVOT_WARPS * 32;
 
@@ -82,9 +90,17 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     // one stage = the query chunk + the planes of the pair's chunk record: two TMA bulk copies
     auto issue = [&](int c, int s) {
         const uint32_t bar = full_a + (uint32_t)s * 8u, dst = stage_a + (uint32_t)s * (uint32_t)sizeof(Stage2);
-        mbar_expect_tx_a(bar, (uint32_t)(sizeof(QChunk2) + CHUNK2_PLANES));
+        mbar_expect_tx_a(bar, (uint32_t)(sizeof(QChunk2) + CHUNK2_STAGED));
         bulk_g2s_a(dst, qsrc + c, (uint32_t)sizeof(QChunk2), bar);
-        bulk_g2s_a(dst + (uint32_t)sizeof(QChunk2), rsrc + (size_t)c * CHUNK2_BYTES, (uint32_t)CHUNK2_PLANES, bar);
+        const uint8_t* src = rsrc + (size_t)c * CHUNK2_BYTES;
+#if PIVOT_COPIES == 1
+        bulk_g2s_a(dst + (uint32_t)sizeof(QChunk2), src, (uint32_t)CHUNK2_STAGED, bar);
+#else
+#pragma unroll
+        for (int k = 0; k < RPL * W4; ++k)
+            bulk_g2s_a(dst + (uint32_t)sizeof(QChunk2) + (uint32_t)k * UNIT2_PLANES, src + (size_t)k * UNIT2_PLANES, (uint32_t)UNIT2_PLANES, bar);
+        bulk_g2s_a(dst + (uint32_t)sizeof(QChunk2) + CHUNK2_PLANES, src + CHUNK2_PLANES, (uint32_t)CHUNK2_COUNTS, bar);
+#endif
     };
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES2 && s < p.n_chunks; ++s) issue(s, s);
@@ -103,9 +119,18 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         for (int j = 0; j < QW2; ++j) { oV[g][j] = 0; oM[g][j] = 0; acc[g][j] = 0; }
 
     // the slots of the tile this warp counts (uvg_set_queries balances the warps of a tile by work)
-    int sj[QW2];
-#pragma unroll
-    for (int j = 0; j < QW2; ++j) sj[j] = p.wslot[((size_t)qt * PIVOT_WARPS + warp) * QW2 + j];
+    // kept as byte offsets of the slot's planes inside QChunk2::pl[u], two per register (the loop is short of registers)
+    static_assert(QW2 == 4 && sizeof(uint4) * 2 * QTILE <= 65536, "slot offsets are packed as 4 x 16 bits");
+    uint32_t so[2];
+    {
+        const uint8_t* ws = p.wslot + ((size_t)qt * PIVOT_WARPS + warp) * QW2;
+        so[0] = (uint32_t)ws[0] * 32u | ((uint32_t)ws[1] * 32u) << 16;
+        so[1] = (uint32_t)ws[2] * 32u | ((uint32_t)ws[3] * 32u) << 16;
+        asm volatile("mov.u32 %0, %0;" : "+r"(so[0]));                       // opaque: unpacked where used, not hoisted into four spilled registers
+        asm volatile("mov.u32 %0, %0;" : "+r"(so[1]));
+    }
+    auto slot_off = [&](int j) -> uint32_t { return (j & 1) ? so[j >> 1] >> 16 : so[j >> 1] & 0xffffu; };
+    auto slot_of = [&](int j) -> int { return (int)(slot_off(j) >> 5); };
     // resolve fetched column masks: a set bit = that reference holds the query's (non-pivot) base at the site, a match the
     // planes did not see.  Almost always no lane holds a non-zero mask.
     auto resolve = [&](uint32_t ent_l, uint32_t col_l) {
@@ -117,7 +142,9 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
             fixhit[(ent >> 16) * (RPL * GROUP) + (src % RPL) * GROUP + lane] += (uint16_t)((col >> lane) & 1u);   // branch-free; this thread owns the counter
         }
     };
+#if !PIVOT_SKIP2
     uint32_t executed = 0;                                                   // (slot, unit) iterations that were not skipped
+#endif
     for (int c = 0; c < p.n_chunks; ++c) {
         const int s = c % STAGES2;
         mbar_wait_a(full_a + (uint32_t)s * 8u, (uint32_t)((c / STAGES2) & 1));
@@ -131,6 +158,60 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
             my_ent = st.q.fix[fb + lane / RPL];
             my_col = __ldg(reinterpret_cast<const uint32_t*>(gl0 + (lane % RPL) * (W4 * UNIT2_MASKS) + (my_ent & 0xffffu)));
         }
+#if PIVOT_SKIP2
+        // what this warp has to do in the chunk: per unit u and slot j either nothing (the query is complete and equal to
+        // the pivot over the unit), or one add from the counts table (the query holds no plain base in the unit: all-N), or
+        // up to two halves of 64 sites counted from the planes
+        const uint32_t hmask = st.q.half[warp], nmask = st.q.fulln[warp];
+#pragma unroll
+        for (int u = 0; u < W4; ++u) {
+            const uint32_t nu = (nmask >> (u * 4)) & 15u;
+            if (nu) {
+                uint32_t ct[RPL];
+#pragma unroll
+                for (int g = 0; g < RPL; ++g) ct[g] = st.cnt[g][u][lane];
+#pragma unroll
+                for (int j = 0; j < QW2; ++j)
+                    if ((nu >> j) & 1u) {
+#pragma unroll
+                        for (int g = 0; g < RPL; ++g) acc[g][j] += ct[g];
+                    }
+            }
+            const uint32_t hu = (hmask >> (u * 8)) & 255u;
+            if (hu == 0u) continue;
+            uint4 rb[RPL], rm[RPL];
+#pragma unroll
+            for (int g = 0; g < RPL; ++g) { rb[g] = st.ref[g][u].base[lane]; rm[g] = st.ref[g][u].mc[lane]; }
+#pragma unroll
+            for (int j = 0; j < QW2; ++j) {
+                const uint32_t hj = (hu >> (j * 2)) & 3u;
+                if (hj == 0u) continue;
+                const uint2* qp = reinterpret_cast<const uint2*>(reinterpret_cast<const uint8_t*>(&st.q.pl[u][0][0]) + slot_off(j));
+                if (hj & 1u) {
+                    const uint2 qb = qp[0], qe = qp[2];                      // words 0, 1 of the two complement planes
+#pragma unroll
+                    for (int g = 0; g < RPL; ++g) {
+                        uint32_t ov = oV[g][j], om = oM[g][j], cv, cm;
+                        csa(ov, cv, ov, rb[g].x & qb.x, rb[g].y & qb.y);
+                        csa(om, cm, om, rm[g].x & qe.x, rm[g].y & qe.y);
+                        oV[g][j] = ov; oM[g][j] = om;
+                        acc[g][j] = imad(__popc(cm), k2, imad(__popc(cv), k128k, acc[g][j]));
+                    }
+                }
+                if (hj & 2u) {
+                    const uint2 qb = qp[1], qe = qp[3];                      // words 2, 3
+#pragma unroll
+                    for (int g = 0; g < RPL; ++g) {
+                        uint32_t ov = oV[g][j], om = oM[g][j], cv, cm;
+                        csa(ov, cv, ov, rb[g].z & qb.x, rb[g].w & qb.y);
+                        csa(om, cm, om, rm[g].z & qe.x, rm[g].w & qe.y);
+                        oV[g][j] = ov; oM[g][j] = om;
+                        acc[g][j] = imad(__popc(cm), k2, imad(__popc(cv), k128k, acc[g][j]));
+                    }
+                }
+            }
+        }
+#else
 #pragma unroll
         for (int u = 0; u < W4; ++u) {
             // which of this warp's slots have work in this unit (the others are complete and equal to the pivot over these
@@ -143,7 +224,8 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
 #pragma unroll
             for (int j = 0; j < QW2; ++j) {
                 if (!((act >> j) & 1u)) continue;
-                const uint4 qe = st.q.pl[u][sj[j]][1], qb = st.q.pl[u][sj[j]][0];
+                const uint4* qp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(&st.q.pl[u][0][0]) + slot_off(j));
+                const uint4 qb = qp[0], qe = qp[1];
                 ++executed;
 #pragma unroll
                 for (int g = 0; g < RPL; ++g) {
@@ -164,6 +246,7 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
                 }
             }
         }
+#endif
         if (fe > fb) {
             resolve(my_ent, my_col);
             for (uint32_t e0 = fb + 32 / RPL; e0 < fe; e0 += 32 / RPL) {    // more than 16 entries (rare)
@@ -196,7 +279,11 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         }
         __syncwarp();
     }
+    // p.work counts (pair, 4-word unit) iterations per lane.  The half-unit variant does not count in the kernel (no register
+    // to spare): the host knows the masks and adds halves x references per launch (engine.cu, run_round)
+#if !PIVOT_SKIP2
     if (lane == 0 && p.work) atomicAdd(p.work, (unsigned long long)executed * RPL);
+#endif
 
     // ---- epilogue: plane counts -> exact counts -> score tile of the owner ----
     bool in_range[RPL];
@@ -208,16 +295,17 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     }
 #pragma unroll
     for (int j = 0; j < QW2; ++j) {
-        const int slot = qt * QTILE + sj[j];
+        const int sjj = slot_of(j);
+        const int slot = qt * QTILE + sjj;
         if (slot >= p.n_slots) continue;
         const bool is_cons = slot == p.n_slots - 1;
 #pragma unroll
         for (int g = 0; g < RPL; ++g) {
             if (!in_range[g]) continue;
-            const int32_t M = p.mc_cnt[local[g]] - (int32_t)((acc[g][j] & 0xffffu) + __popc(oM[g][j])) + (int32_t)fixhit[sj[j] * (RPL * GROUP) + g * GROUP + lane];
+            const int32_t M = p.mc_cnt[local[g]] - (int32_t)((acc[g][j] & 0xffffu) + __popc(oM[g][j])) + (int32_t)fixhit[sjj * (RPL * GROUP) + g * GROUP + lane];
             const int32_t V = p.rb_cnt[local[g]] - (int32_t)((acc[g][j] >> 16) + __popc(oV[g][j]));
             const uint4 v = pair_epilogue_default(p, p.qfix_off, p.qfix_ent, slot, group0 + g, lane, local[g], M, V);
-            pair_store(p, owner, row0 + sj[j], is_cons, local[g], v);
+            pair_store(p, owner, row0 + sjj, is_cons, local[g], v);
         }
     }
 }
@@ -255,6 +343,8 @@ __global__ void __launch_bounds__(256) k_derive_pivot(const uint4* __restrict__ 
     if (fresh) {
         rec->base[lane] = rb;
         rec->mc[lane] = mc;
+        reinterpret_cast<uint32_t*>(db2 + db2_counts_bytes(group, unit, Wp))[lane] =
+            (uint32_t)(__popc(mc.x) + __popc(mc.y) + __popc(mc.z) + __popc(mc.w)) | (uint32_t)(__popc(rb.x) + __popc(rb.y) + __popc(rb.z) + __popc(rb.w)) << 16;
         atomicAdd(rb_cnt + ordinal, __popc(rb.x) + __popc(rb.y) + __popc(rb.z) + __popc(rb.w));
         atomicAdd(mc_cnt + ordinal, __popc(mc.x) + __popc(mc.y) + __popc(mc.z) + __popc(mc.w));
     }
