@@ -517,6 +517,91 @@ def _literal_pair(acgt, h, cres, r, rcode, q, qcode, idx, idx_m, nn):
     return (s[0], s[1], s[2], s[3], r1[0] + r2[0], nn)
 
 
+# ---------------------------------------------------------------------------------------------
+# uvaiaball (src/ball.c): radius search
+# ---------------------------------------------------------------------------------------------
+def ball_clamp_dist(dist, nchar, trim):
+    """new_query_structure_from_fasta (src/fastaseq.c:713-715); trim already clamped"""
+    dist = max(0, int(dist))
+    if dist > (nchar - 2 * trim) / 10:
+        dist = int((nchar - 2 * trim) / 10)
+    return dist
+
+
+def ball_prepare_queries(qnames, qseqs, trim=0, acgt=False, ambiguity=0.5, keep_more_resolved=False):
+    """ball.c:172-194: filter -> partition -> reorder -> ALWAYS prune (-k keeps the more resolved) -> partition again"""
+    keep = filter_queries(qnames, qseqs, min(1.0, max(0.001, ambiguity)))
+    if not keep:
+        raise ValueError("no valid query sequences")
+    Q = np.frombuffer(b"".join(qseqs[i] for i in keep), np.uint8).reshape(len(keep), -1).copy()
+    names = [qnames[i] for i in keep]
+    trim = clamp_trim(trim, Q.shape[1])
+    cons, idx, idx_m, idx_c = partition(Q, trim, acgt)
+    order = query_order(Q, trim, acgt)
+    Q = Q[order]
+    names = [names[i] for i in order]
+    kept = exclude_redundant(Q, idx, idx_m, acgt, keep_more_resolved)
+    Q = Q[kept]
+    names = [names[i] for i in kept]
+    cons, idx, idx_m, idx_c = partition(Q, trim, acgt)
+    return names, Q, trim, cons, idx, idx_m, idx_c
+
+
+def _ball_count(s1, s2, idx, maxdist, acgt):
+    """quick_pairwise_score_truncated_idx_indelcheck / quick_pairwise_score_acgt (src/fastaseq.c:562-583): sites of idx
+    where both bytes are usable and differ, the loop stops when the count reaches maxdist"""
+    if len(idx) == 0 or maxdist <= 0:
+        return 0
+    a, b = s1[idx], s2[idx]
+    use = (ACGT[a] & ACGT[b]) if acgt else (~INDEL[a] & ~INDEL[b])
+    d = int((use & (a != b)).sum())
+    return min(d, maxdist)
+
+
+def ball_min_dist(r, Q, cons, idx, idx_m, idx_c, radius, acgt):
+    """seq_ball_against_query_structure (src/fastaseq.c:660-696), literally: `radius` = dist + 1"""
+    md = _ball_count(r, cons, idx_c, radius, acgt)
+    if md >= radius:
+        return md
+    c = md
+    md = _ball_count(r, cons, idx_m, radius, acgt) + c
+    if md >= radius:
+        return md
+    c = md
+    i = 0
+    while i < Q.shape[0] and (md + c) >= radius:               # NB the first test compares 2c with the radius
+        md = _ball_count(r, Q[i], idx, radius - c, acgt)
+        i += 1
+    return md + c
+
+
+def ball_search(qnames, qseqs, refs, dist=5, trim=0, acgt=False, ambig_q=0.5, ambig_r=0.5, keep_more_resolved=False):
+    """End-to-end restatement of uvaiaball (src/ball.c:138-291).  refs = [(names, seqs), ...] one entry per -r file.
+    -> (names of the references kept, in file order; clamped dist; number too ambiguous)"""
+    ambig_r = min(1.0, max(0.001, ambig_r))
+    names, Q, trim, cons, idx, idx_m, idx_c = ball_prepare_queries(qnames, qseqs, trim, acgt, ambig_q, keep_more_resolved)
+    L = Q.shape[1]
+    dist = ball_clamp_dist(dist, L, trim)
+    non_n_ref = int(L * ambig_r)                               # ball.c:201 -- A, not 1 - A
+    kept, n_invalid = [], 0
+    for rnames, rseqs in refs:
+        for nm, sq in zip(rnames, rseqs):
+            r = np.frombuffer(sq, np.uint8)
+            if int((~INDEL[r]).sum()) < non_n_ref:
+                n_invalid += 1
+                continue
+            if len(r) != L:
+                raise ValueError("all sequences must be aligned")
+            if ball_min_dist(r, Q, cons, idx, idx_m, idx_c, dist + 1, acgt) <= dist:
+                kept.append(nm)
+    return kept, dist, n_invalid
+
+
+def ball_run_files(query_file, ref_files, **kw):
+    qn, qs = read_fasta(query_file)
+    return ball_search(qn, qs, [read_fasta(f) for f in ref_files], **kw)
+
+
 def run_files(query_file, ref_files, **kw):
     qn, qs = read_fasta(query_file)
     return search(qn, qs, ref_files, **kw)

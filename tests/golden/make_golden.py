@@ -35,6 +35,7 @@ from uvaia_b200.synth import SynthModel, write_fasta  # noqa: E402
 
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "uvaia_ref")
 REF_LIB = os.path.join(ROOT, "oracle", "_ref", "libuvaia_ref_score.so")
+BALL_BIN = os.path.join(ROOT, "oracle", "_ref", "uvaiaball_ref")
 BUNDLED = "/root/reference/data/03.unique_acgt.aln.xz"
 ALPHABET = "ACGTUMRWSYKVHDBNOX?-.EZ*acgtn"
 
@@ -419,7 +420,73 @@ def case_bundled():
     save_case("real_c1_full_reversed", qf, [rf], ["-n", "10"], "BASELINE config 1 with the database in reverse file order")
 
 
-GROUPS = {"unit": make_unit_vectors, "synthetic": case_synthetic, "ties": case_ties, "ambiguous": case_ambiguous,
+# ------------------------------------------------------------------------------------------------------------------
+# uvaiaball (src/ball.c): which references are within the radius of some query
+# ------------------------------------------------------------------------------------------------------------------
+def save_ball_case(name, q_fa: bytes, r_fas, args, note):
+    d = os.path.join(HERE, "ball_cases", name)
+    shutil.rmtree(d, ignore_errors=True)
+    os.makedirs(d)
+    with tempfile.TemporaryDirectory() as wd:
+        qf = os.path.join(wd, "q.fa")
+        open(qf, "wb").write(q_fa)
+        rfs = []
+        for i, r in enumerate(r_fas):
+            rf = os.path.join(wd, f"r{i}.fa")
+            open(rf, "wb").write(r)
+            rfs.append(rf)
+        cmd = [BALL_BIN] + args + sum((["-r", r] for r in rfs), []) + ["-o", os.path.join(wd, "out"), qf]
+        p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, cwd=wd)
+        if p.returncode != 0:
+            raise RuntimeError(f"uvaiaball_ref failed ({p.returncode}): {p.stderr.decode(errors='replace')[-800:]}")
+        aln = gzip.decompress(open(os.path.join(wd, "out.aln.xz"), "rb").read())         # zlib-only build: names are intact, sequences are not (H4)
+        kept = [ln[1:] for ln in aln.split(b"\n") if ln.startswith(b">")]
+        stderr = p.stderr.decode(errors="replace")
+    xz_write(os.path.join(d, "q.fa.xz"), q_fa)
+    for i, r in enumerate(r_fas):
+        xz_write(os.path.join(d, f"r{i}.fa.xz"), r)
+    open(os.path.join(d, "expected_kept_names.txt"), "wb").write(b"\n".join(kept) + b"\n")
+    lines = [ln for ln in stderr.split("\n") if "Query database" in ln or "radius distance" in ln or "sequences within radius" in ln]
+    json.dump({"args": args, "n_ref_files": len(r_fas), "note": note, "n_kept": len(kept), "reference_stderr": lines},
+              open(os.path.join(d, "args.json"), "w"), indent=1)
+    print(f"ball case {name}: {len(kept)} kept")
+
+
+def case_ball():
+    m = SynthModel(nsites=3000, n_clades=24, seed=11, clade_subs=12)
+    qn, Q = m.sample(40, 12, prefix="Wales/QRY")
+    rn, R = m.sample(3000, 13, prefix="England/REF")
+    # some references are copies of queries with 0..7 extra substitutions, so that every radius keeps a different set
+    rng = np.random.default_rng(5)
+    for k in range(300):
+        row = Q[k % len(Q)].copy()
+        pos = rng.choice(3000, size=k % 8, replace=False)
+        row[pos] = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, size=len(pos))]
+        R[10 * k] = row
+    qf, rf = fasta_bytes(qn, Q), fasta_bytes(rn, R)
+    save_ball_case("ball_default", qf, [rf], [], "radius 5 (default), 40 queries x 3000 references")
+    save_ball_case("ball_d0", qf, [rf], ["-d", "0"], "radius 0: only references identical on the compared sites")
+    save_ball_case("ball_d2", qf, [rf], ["-d", "2"], "radius 2")
+    save_ball_case("ball_d40", qf, [rf], ["-d", "40"], "radius 40: most references")
+    save_ball_case("ball_acgt", qf, [rf], ["-d", "3", "-x"], "--acgt (-x) mode")
+    save_ball_case("ball_keep", qf, [rf], ["-d", "3", "-k"], "-k: the more resolved of two equivalent queries stays")
+    save_ball_case("ball_trim", qf, [rf], ["-d", "4", "--trim", "230"], "--trim 230")
+    save_ball_case("ball_filters", qf, [rf], ["-d", "6", "-a", "0.2", "-A", "0.85"], "-a 0.2, -A 0.85 (the reference filter is non_n >= nchar * A)")
+    save_ball_case("ball_two_files", qf, [fasta_bytes(rn[:1500], R[:1500]), fasta_bytes(rn[1500:], R[1500:])], ["-d", "5"], "two -r files")
+    save_ball_case("ball_one_query", fasta_bytes(qn[:1], Q[:1]), [rf], ["-d", "5"], "a single query: every site is a consensus site")
+    # the whole alphabet: U, lower case, codes, letters outside IUPAC -- the ball distance compares BYTES
+    m2 = SynthModel(nsites=900, n_clades=5, seed=77, clade_subs=6)
+    qn2, Q2 = m2.sample(12, 78, prefix="Q")
+    rn2, R2 = m2.sample(400, 79, prefix="R")
+    soup = np.frombuffer(ALPHABET.encode(), np.uint8)
+    for T, frac in ((Q2, 0.01), (R2, 0.02)):
+        mask = rng.random(T.shape) < frac
+        T[mask] = soup[rng.integers(0, len(soup), size=int(mask.sum()))]
+    save_ball_case("ball_soup", fasta_bytes(qn2, Q2), [fasta_bytes(rn2, R2)], ["-d", "40"], "every symbol class in queries and references")
+    save_ball_case("ball_soup_acgt", fasta_bytes(qn2, Q2), [fasta_bytes(rn2, R2)], ["-d", "6", "-x"], "same, --acgt")
+
+
+GROUPS = {"unit": make_unit_vectors, "ball": case_ball, "synthetic": case_synthetic, "ties": case_ties, "ambiguous": case_ambiguous,
           "hygiene": case_hygiene, "keep_resolved": case_keep_resolved, "alphabet_soup": case_alphabet_soup, "c2_shape": case_c2_shape, "bundled": case_bundled}
 
 if __name__ == "__main__":

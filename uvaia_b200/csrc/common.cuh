@@ -46,13 +46,10 @@ static_assert(sizeof(QChunk) % 16 == 0, "bulk copy size must be a multiple of 16
 //     mc  = sites where the REFERENCE holds the pivot base         (derived database plane, one pass per query set)
 //     qeq = sites where the QUERY holds the pivot base
 // the match word of a pair is mc & qeq and the valid word r.base & q.base: two ANDs instead of three LOP3 with five
-// inputs, and both popcounts go through a 2-word carry-save step (4 LOP3 + 1 POPC per pair-word in all, balanced for
-// the measured 4:1 LOP3:POPC issue ratio).  Query sites holding a plain base that differs from the pivot (~the SNPs of
-// the query, a few dozen per genome) are "fix" entries: (slot, site, base).  They travel with the query chunk and are
-// resolved against COLUMN MASKS of the derived database: for a site and a base, one 32-bit word whose bit l says
-// "reference l of the group holds that base there" -- a warp fetches the words of all its entries of a chunk with ONE
-// load (lane = entry x group) while it counts the chunk, and almost always finds them all zero.  What does not fit a
-// chunk's fix block, and every ambiguity code, is resolved by the epilogue (pair_epilogue.cuh).
+// inputs.  The kernel works on the COMPLEMENTS (nq = no plain base here, ne = not the pivot's base): valid = popc(r.base) -
+// sum popc(r.base & nq), match' = popc(r.mc) - sum popc(r.mc & ne), with per-reference totals as first terms and sums
+// that only get contributions where the query has an N, a gap, a code or a SNP; both popcounts go through a 2-word
+// carry-save step (4 LOP3 + 1 POPC per counted pair-word, balanced for the measured 4:1 LOP3:POPC issue ratio).
 // Derived database: per (pair of groups = the 64 references of a thread block, chunk of WC column words) one contiguous
 // 12 KB record
 //     planes   [group of the pair][unit][ uint4 base[32] | uint4 mc[32] ]                    4 KB  \ staged by TMA bulk copies
@@ -60,11 +57,8 @@ static_assert(sizeof(QChunk) % 16 == 0, "bulk copy size must be a multiple of 16
 //     colmasks [group of the pair][unit][4 words][4 bases A,C,G,T][32 sites] uint32         8 KB: read by fix entries only
 // The counts serve the units in which a query holds no plain base at all (inside an N run, trimmed away): there
 // popc(r.base & nq) and popc(r.mc & ne) are the reference's own unit totals -- one add instead of 16 LOP3 + 4 POPC.
-#ifndef PIVOT_SKIP2
-#define PIVOT_SKIP2 1           // 1: all-N units through the counts table, the others in halves of 64 sites; 0: whole units (r01 kernel)
-#endif
 #ifndef PIVOT_STAGES
-#define PIVOT_STAGES 8
+#define PIVOT_STAGES 9
 #endif
 constexpr int STAGES2 = PIVOT_STAGES;
 constexpr int UNIT2_PLANES = 2 * GROUP * 16;                         // base + mc of one (group, unit): 1 KB
@@ -73,20 +67,32 @@ constexpr int CHUNK2_PLANES = RPL * W4 * UNIT2_PLANES;               // 4 KB
 constexpr int CHUNK2_COUNTS = RPL * W4 * GROUP * 4;                  // 512 B
 constexpr int CHUNK2_STAGED = CHUNK2_PLANES + CHUNK2_COUNTS;         // what a ring stage holds of a chunk record
 constexpr int CHUNK2_BYTES = CHUNK2_STAGED + RPL * W4 * UNIT2_MASKS; // 12.5 KB per (pair of groups, chunk)
-constexpr int FIXCAP = 236;                                          // fix entries a chunk of a query tile can carry
 constexpr int PIVOT_QW = 4;                                          // query slots per warp of k_pairpivot
 constexpr int PIVOT_WARPS = QTILE / PIVOT_QW;
-struct __align__(16) QChunk2 {
-    uint4    pl[W4][QTILE][2];       // [unit][slot][plane], COMPLEMENTS: 0 = no plain base here (or trimmed / padding), 1 = not the pivot base
-    uint8_t  fix_begin[32];          // [warp] first entry of the warp's slots; [PIVOT_WARPS] = total
-    uint8_t  active[W4][16];         // per unit and warp: bit j set <=> the warp's j-th slot (PairParams::wslot) has work in this unit
-    uint16_t half[16];               // per warp: bit u * 8 + j * 2 + h set <=> words 2h, 2h+1 of unit u hold a site where slot j differs
-                                     //     from the pivot (N, gap, code, SNP) and the unit is not all-N: that half is counted from the planes
-    uint8_t  fulln[16];              // per warp: bit u * 4 + j set <=> slot j holds no plain base in unit u: the counts table answers
-    uint32_t fix[FIXCAP];            // byte offset of the entry's column-mask word inside the chunk record of the derived database
-                                     //     (for the first group of the pair; the second is W4 * UNIT2_MASKS further) | slot-within-tile << 16
+// Query side of the pivot form: per (query tile, chunk) one variable-length record of a byte stream (PairParams::qstream,
+// offsets in PairParams::qoff), staged by one TMA bulk copy of exactly its size:
+//     QWarpHead head[16 warps]                          what each warp has to do in the chunk
+//     uint4     item[n]                                 per half (64 sites) that is counted from the planes: words 2h, 2h+1 of the
+//                                                       two COMPLEMENT planes of the slot -- nq (no plain base here, or trimmed /
+//                                                       padding) in .x .y, ne (not the pivot's base) in .z .w; the items of a warp
+//                                                       are contiguous, in the order the kernel walks them (unit, slot, half)
+// Only ~16 % of the (slot, half) pairs of a SARS-CoV-2 query set need an item: the record averages ~0.8 KB where the dense
+// planes of the tile took 4 KB of every ring stage.
+struct __align__(8) QWarpHead {
+    uint16_t half;        // bit u * 8 + j * 2 + h: words 2h, 2h+1 of unit u of the warp's slot j are counted from the planes (an item)
+    uint8_t  fulln;       // bit u * 4 + j: slot j holds no plain base in unit u (inside an N run, trimmed): the counts table answers
+    uint8_t  n_items;
+    uint16_t item0;       // index of the warp's first item in the record
+    uint16_t pad;
 };
-static_assert(sizeof(QChunk2) % 16 == 0 && PIVOT_WARPS < 32 && FIXCAP < 256, "QChunk2 layout");
+constexpr int QHEAD_BYTES = PIVOT_WARPS * (int)sizeof(QWarpHead);    // 128
+constexpr int QITEMS_MAX = QTILE * W4 * 2;                           // every half of every slot: 256
+constexpr int QREC_MAX = QHEAD_BYTES + QITEMS_MAX * 16;              // 4224: what a ring stage reserves
+// A query site holding a plain base that differs from the pivot is outside the planes' match count; a reference holding
+// the same base there is one more match.  These "fix" entries (~the SNPs of the query, a few dozen per genome) are resolved
+// after the main loop against the column masks of the derived database: entry = chunk << 16 | unit << 9 | word << 7 |
+// base (A,C,G,T) << 5 | site in word; per slot a range of PairParams::snp_ent.
+static_assert(W4 == 2 && PIVOT_WARPS == 16 && sizeof(QWarpHead) == 8, "QWarpHead bit layout");
 __host__ __device__ inline size_t db2_chunk_bytes(int64_t group, int unit, int Wp)        // record of the chunk that holds (group, unit)
 {
     return ((size_t)(group / RPL) * (size_t)(Wp / WC) + (size_t)(unit / W4)) * CHUNK2_BYTES;
@@ -135,10 +141,11 @@ struct PairParams {
     const uint8_t*   db2;         // derived database: 3 KB records (base, mc, one-hot planes)
     const int32_t*   rb_cnt;      // per local reference: popcount of its base plane (all words)
     const int32_t*   mc_cnt;      //                      popcount of its mc plane
-    const QChunk2*   qdata2;      // [n_qtiles][n_chunks]
+    const uint8_t*   qstream;     // records of every (query tile, chunk), see QWarpHead
+    const uint32_t*  qoff;        // [n_qtiles][n_chunks + 1] byte offsets of the records (multiples of 16)
     const uint8_t*   wslot;       // [n_qtiles][PIVOT_WARPS][PIVOT_QW]: which slots of the tile each warp counts (balanced by work)
-    const uint32_t*  qfix_off;    // [n_slots + 1] entries the EPILOGUE resolves: ambiguity codes + fix entries that overflowed a chunk
-    const uint32_t*  qfix_ent;
+    const uint32_t*  snp_off;     // [n_slots + 1] fix entries of every slot: plain bases that differ from the pivot
+    const uint32_t*  snp_ent;
     const uint32_t*  ramb_off;    // [local refs + 1] ambiguity entries of the references
     const uint32_t*  ramb_ent;
     const int32_t*   non_n;       // per local reference

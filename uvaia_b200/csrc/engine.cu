@@ -86,8 +86,8 @@ struct uvg_ctx {
     uint32_t *d_qnib = nullptr, *d_qamb_off = nullptr, *d_qamb_ent = nullptr;
     // pivot form of the pair-count kernel (pairpivot.cu): chosen per query set by uvg_set_queries
     bool pivot_on = false;
-    QChunk2* d_qdata2 = nullptr;
-    uint32_t *d_qfix_off = nullptr, *d_qfix_ent = nullptr;
+    uint8_t* d_qstream = nullptr; uint32_t* d_qoff = nullptr;      // query stream of the pivot form: records of every (tile, chunk) + their offsets
+    uint32_t *d_snp_off = nullptr, *d_snp_ent = nullptr;           // fix entries per slot
     uint4* d_pivot = nullptr;                         // [Wp/4][2]: b0, b1 planes of the pivot sequence
     uint8_t* d_wslot = nullptr;                       // [n_qtiles][16 warps][4]: slot of the tile each warp of k_pairpivot counts
     uint8_t* d_db2 = nullptr; int64_t db2_cap = 0;    // derived database (base, mc, one-hot planes: 3 KB records) of the resident references
@@ -266,8 +266,8 @@ static void free_queries(uvg_ctx* c, bool final = false)
     close_peers(c);
     for (size_t& b : c->qcap) b = 0;
     cudaFree(c->d_qdata); cudaFree(c->d_qnib); cudaFree(c->d_qamb_off); cudaFree(c->d_qamb_ent);
-    cudaFree(c->d_qdata2); cudaFree(c->d_qfix_off); cudaFree(c->d_qfix_ent); cudaFree(c->d_pivot); cudaFree(c->d_wslot); c->d_wslot = nullptr;
-    c->d_qdata2 = nullptr; c->d_qfix_off = c->d_qfix_ent = nullptr; c->d_pivot = nullptr;
+    cudaFree(c->d_qstream); cudaFree(c->d_qoff); cudaFree(c->d_snp_off); cudaFree(c->d_snp_ent); cudaFree(c->d_pivot); cudaFree(c->d_wslot); c->d_wslot = nullptr;
+    c->d_qstream = nullptr; c->d_qoff = c->d_snp_off = c->d_snp_ent = nullptr; c->d_pivot = nullptr;
     cudaFree(c->d_thr_local); for (int b = 0; b < NBUF; ++b) { cudaFree(c->d_thr_all[b]); c->d_thr_all[b] = nullptr; }
     cudaFree(c->d_own); cudaFree(c->d_all); c->d_own = c->d_all = nullptr;
     cudaFree(c->d_batch_id); cudaFree(c->d_max_inc_batch);
@@ -499,8 +499,9 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     memset(qd.data(), 0, n_chunk_total * sizeof(QChunk));
     std::vector<uint32_t> qnib((size_t)c->n_slots * c->qnib_stride, 0);
     std::vector<std::vector<uint32_t>> amb(c->n_slots), snp(pivot_ok ? c->n_slots : 0);
-    std::vector<QChunk2> qd2;
-    if (pivot_ok) { qd2.resize(n_chunk_total); memset(qd2.data(), 0, n_chunk_total * sizeof(QChunk2)); }
+    struct HostPlanes2 { uint4 pl[W4][QTILE][2]; };                          // host only: [unit][slot][plane 0 = plain base, 1 = pivot base], complemented below
+    std::vector<HostPlanes2> qd2;
+    if (pivot_ok) { qd2.resize(n_chunk_total); memset(qd2.data(), 0, n_chunk_total * sizeof(HostPlanes2)); }
     if (do_prep) parallel_ranges(c->n_slots, host_threads(c->n_slots), [&](int, int sa, int sb) {
         std::vector<uint32_t> plain_in_chunk(c->n_chunks);
         for (int q = sa; q < sb; ++q) {
@@ -558,9 +559,10 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     amb_off[c->n_slots] = (uint32_t)amb_ent.size();
     c->cons_amb_begin = amb_off[Q]; c->cons_amb_n = amb_off[Q + 1] - amb_off[Q];
 
-    // ---- pivot form (pairpivot.cu): pivot planes, fix blocks of the chunks, epilogue lists ----
-    std::vector<uint32_t> fix_off, fix_ent, pivot_words;
-    std::vector<uint8_t> wslot;                                             // [tile][warp][j]: slot of the tile the warp counts
+    // ---- pivot form (pairpivot.cu): pivot planes, the query stream (per tile and chunk: what every warp does + the plane
+    // words of the halves that are counted), fix entries per slot ----
+    std::vector<uint32_t> snp_off, snp_ent, pivot_words, qoff;
+    std::vector<uint8_t> wslot, qstream;                                    // wslot [tile][warp][j]: slot of the tile the warp counts
     int64_t n_fix_total = 0;
     if (pivot_ok && do_prep) {
         pivot_words.assign((size_t)(c->Wp / 4) * 8, 0u);                     // [unit][plane b0, b1][4 words]
@@ -570,17 +572,16 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
             if (pv[s] & 10u) u[w & 3] |= 1u << (s & 31);
             if (pv[s] & 12u) u[4 + (w & 3)] |= 1u << (s & 31);
         }
-        std::vector<std::vector<uint32_t>> epi = amb;                       // the epilogue resolves the ambiguity codes ...
         size_t n_snp = 0;
         for (int q = 0; q < c->n_slots; ++q) n_snp += snp[q].size();
         // the kernel works on the COMPLEMENTS (pairpivot.cu): plane 0 = sites where the slot holds no plain base (or that
-        // are trimmed away / padding), plane 1 = sites where it does not hold the pivot base; units where plane 1 is zero
-        // are skipped.  Padding slots stay all-zero (always skipped, never stored).  work[slot] = units that are not skipped.
+        // are trimmed away / padding), plane 1 = sites where it does not hold the pivot base.  Padding slots stay all-zero
+        // (nothing to do, never stored).  work[slot] = cost of the slot: 4 per half counted from the planes, 1 per all-N unit.
         std::vector<uint32_t> work((size_t)c->n_qtiles * QTILE, 0);
         parallel_ranges(c->n_qtiles, host_threads(c->n_qtiles), [&](int, int ta, int tb) {
             for (int qt = ta; qt < tb; ++qt)
                 for (int ch = 0; ch < c->n_chunks; ++ch) {
-                    QChunk2& blk = qd2[(size_t)qt * c->n_chunks + ch];
+                    HostPlanes2& blk = qd2[(size_t)qt * c->n_chunks + ch];
                     for (int u = 0; u < W4; ++u)
                         for (int qi = 0; qi < QTILE && qt * QTILE + qi < c->n_slots; ++qi) {
                             for (int pl = 0; pl < 2; ++pl) {
@@ -611,63 +612,83 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
                 load[best] += wk[order[i]];
             }
         }
-        // per chunk: the active-slot nibble of every warp and unit, and the fix block: entries ordered by warp; what does
-        // not fit goes to the slot's epilogue list
-        size_t n_overflow = 0;
-        int64_t halves_total = 0;
-        std::vector<size_t> cur(c->n_slots, 0);
-        for (int qt = 0; qt < c->n_qtiles; ++qt)
-            for (int ch = 0; ch < c->n_chunks; ++ch) {
-                QChunk2& blk = qd2[(size_t)qt * c->n_chunks + ch];
-                const uint32_t site_end = (uint32_t)(ch + 1) * WC * 32;
-                int n = 0;
-                for (int wp = 0; wp < PIVOT_WARPS; ++wp) {
-                    blk.fix_begin[wp] = (uint8_t)n;
-                    for (int j = 0; j < PIVOT_QW; ++j) {
-                        const int qi = wslot[(size_t)qt * QTILE + wp * PIVOT_QW + j];
-                        const int q = qt * QTILE + qi;
-                        if (q >= c->n_slots) continue;
-                        for (int u = 0; u < W4; ++u) {
-                            const uint4& e = blk.pl[u][qi][1];
-                            const uint4& b = blk.pl[u][qi][0];
-                            if (e.x | e.y | e.z | e.w) blk.active[u][wp] |= (uint8_t)(1u << j);
-                            if ((b.x & b.y & b.z & b.w) == 0xffffffffu) blk.fulln[wp] |= (uint8_t)(1u << (u * 4 + j));     // no plain base in the unit
-                            else {
-                                if (e.x | e.y) blk.half[wp] |= (uint16_t)(1u << (u * 8 + j * 2));
-                                if (e.z | e.w) blk.half[wp] |= (uint16_t)(1u << (u * 8 + j * 2 + 1));
+        // the stream: per (tile, chunk) the 16 warp heads, then the items of warp 0, warp 1, ... in the order the kernel walks
+        // them (unit, slot of the warp, half).  Tiles are built in parallel, then concatenated.
+        std::vector<std::vector<uint8_t>> tile_rec(c->n_qtiles);
+        std::vector<std::vector<uint32_t>> tile_off(c->n_qtiles);
+        std::vector<int64_t> tile_halves(c->n_qtiles, 0);
+        parallel_ranges(c->n_qtiles, host_threads(c->n_qtiles), [&](int, int ta, int tb) {
+            for (int qt = ta; qt < tb; ++qt) {
+                std::vector<uint8_t>& rec = tile_rec[qt];
+                std::vector<uint32_t>& off = tile_off[qt];
+                off.reserve(c->n_chunks + 1);
+                for (int ch = 0; ch < c->n_chunks; ++ch) {
+                    const HostPlanes2& blk = qd2[(size_t)qt * c->n_chunks + ch];
+                    off.push_back((uint32_t)rec.size());
+                    const size_t h0 = rec.size();
+                    rec.resize(h0 + QHEAD_BYTES, 0);
+                    int n_items = 0;
+                    for (int wp = 0; wp < PIVOT_WARPS; ++wp) {
+                        QWarpHead hd{};
+                        hd.item0 = (uint16_t)n_items;
+                        for (int u = 0; u < W4; ++u)
+                            for (int j = 0; j < PIVOT_QW; ++j) {
+                                const int qi = wslot[(size_t)qt * QTILE + wp * PIVOT_QW + j];
+                                if (qt * QTILE + qi >= c->n_slots) continue;
+                                const uint4& e = blk.pl[u][qi][1];
+                                const uint4& b = blk.pl[u][qi][0];
+                                if ((b.x & b.y & b.z & b.w) == 0xffffffffu) { hd.fulln |= (uint8_t)(1u << (u * 4 + j)); continue; }
+                                const uint32_t bw[4] = {b.x, b.y, b.z, b.w}, ew[4] = {e.x, e.y, e.z, e.w};
+                                for (int h = 0; h < 2; ++h) {
+                                    if (!(ew[2 * h] | ew[2 * h + 1])) continue;
+                                    hd.half |= (uint16_t)(1u << (u * 8 + j * 2 + h));
+                                    const uint32_t it[4] = {bw[2 * h], bw[2 * h + 1], ew[2 * h], ew[2 * h + 1]};
+                                    const uint8_t* ib = reinterpret_cast<const uint8_t*>(it);
+                                    rec.insert(rec.end(), ib, ib + 16);
+                                    ++n_items; ++hd.n_items;
+                                }
                             }
-                        }
-                        while (cur[q] < snp[q].size() && (snp[q][cur[q]] & AMB_SITE_MASK) < site_end) {
-                            const uint32_t ent = snp[q][cur[q]++], site = ent & AMB_SITE_MASK, code = ent >> 28;
-                            const uint32_t w = site >> 5, a = code == 1 ? 0 : code == 2 ? 1 : code == 4 ? 2 : 3;
-                            if (n >= FIXCAP) { epi[q].push_back(ent); ++n_overflow; continue; }
-                            const uint32_t off = CHUNK2_STAGED + ((w % WC) / 4) * UNIT2_MASKS + (((w & 3) * 4 + a) * 32 + (site & 31)) * 4;
-                            blk.fix[n++] = off | ((uint32_t)qi << 16);
-                        }
+                        memcpy(&rec[h0 + (size_t)wp * sizeof(QWarpHead)], &hd, sizeof hd);
                     }
+                    tile_halves[qt] += n_items;
                 }
-                blk.fix_begin[PIVOT_WARPS] = (uint8_t)n;
-                for (int wp = 0; wp < PIVOT_WARPS; ++wp) halves_total += __builtin_popcount(blk.half[wp]);
+                off.push_back((uint32_t)rec.size());
             }
-        c->pivot_halves = halves_total;
-        fix_off.assign(c->n_slots + 1, 0);
-        for (int q = 0; q < c->n_slots; ++q) {
-            fix_off[q] = (uint32_t)fix_ent.size();
-            std::sort(epi[q].begin(), epi[q].end(), [](uint32_t x, uint32_t y) { return (x & AMB_SITE_MASK) < (y & AMB_SITE_MASK); });
-            fix_ent.insert(fix_ent.end(), epi[q].begin(), epi[q].end());
+        });
+        int64_t halves_total = 0;
+        size_t total = 0;
+        for (int qt = 0; qt < c->n_qtiles; ++qt) { total += tile_rec[qt].size(); halves_total += tile_halves[qt]; }
+        if (total > 0xfffffff0ull) pivot_ok = false;                        // offsets are 32 bits (never reached: 16 tiles ~ 1.5 MB)
+        qstream.reserve(total);
+        qoff.reserve((size_t)c->n_qtiles * (c->n_chunks + 1));
+        for (int qt = 0; qt < c->n_qtiles && pivot_ok; ++qt) {
+            const uint32_t base = (uint32_t)qstream.size();
+            for (uint32_t o : tile_off[qt]) qoff.push_back(base + o);
+            qstream.insert(qstream.end(), tile_rec[qt].begin(), tile_rec[qt].end());
         }
-        fix_off[c->n_slots] = (uint32_t)fix_ent.size();
+        c->pivot_halves = halves_total;
+        // fix entries per slot: chunk << 16 | unit << 9 | word << 7 | base (A,C,G,T) << 5 | site in word (common.cuh)
+        snp_off.assign(c->n_slots + 1, 0);
+        for (int q = 0; q < c->n_slots; ++q) {
+            snp_off[q] = (uint32_t)snp_ent.size();
+            for (uint32_t ent : snp[q]) {
+                const uint32_t site = ent & AMB_SITE_MASK, code = ent >> 28, w = site >> 5;
+                const uint32_t a = code == 1 ? 0 : code == 2 ? 1 : code == 4 ? 2 : 3;
+                snp_ent.push_back((w / WC) << 16 | ((w % WC) / 4) << 9 | (w & 3u) << 7 | a << 5 | (site & 31u));
+            }
+        }
+        snp_off[c->n_slots] = (uint32_t)snp_ent.size();
         n_fix_total = (int64_t)n_snp;
-        // an in-loop fix entry costs ~15 instructions against ~520 per warp and chunk, an epilogue entry ~3 scattered
-        // loads per pair: divergent query sets (many bases != pivot, or chunks that overflow) stay on the general kernel
-        if (c->prm.pair_kernel != UVG_PAIR_PIVOT &&
-            (n_snp > (size_t)c->n_slots * (size_t)std::max(4, c->W / 8) || n_overflow > (size_t)c->n_slots * 2)) pivot_ok = false;
+        // a fix entry costs two scattered loads per thread block of every reference pair: divergent query sets (many plain
+        // bases != pivot) stay on the general kernel
+        if (c->prm.pair_kernel != UVG_PAIR_PIVOT && n_snp > (size_t)c->n_slots * (size_t)std::max(4, c->W / 8)) pivot_ok = false;
     }
 
     const auto t_host = std::chrono::steady_clock::now();
     if (bcast) {
         // what the other ranks cannot know: the form chosen, the sizes of the site sets and of the two variable lists
-        int64_t hdr[8] = {pivot_ok ? 1 : 0, n_idx, n_idx_m, n_idx_c, (int64_t)amb_ent.size(), (int64_t)fix_ent.size(), n_fix_total | (c->pivot_halves << 32), 0x55564731};
+        int64_t hdr[8] = {pivot_ok ? 1 : 0, n_idx, n_idx_m, n_idx_c, (int64_t)amb_ent.size(), (int64_t)snp_ent.size() | ((int64_t)qstream.size() << 32),
+                          n_fix_total | (c->pivot_halves << 32), 0x55564731};
         int64_t* d_hdr = nullptr;
         UVG_CUDA(c, cudaMalloc(&d_hdr, sizeof hdr));
         UVG_CUDA(c, cudaMemcpyAsync(d_hdr, hdr, sizeof hdr, cudaMemcpyHostToDevice, c->st));
@@ -680,8 +701,10 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
             pivot_ok = hdr[0] != 0; n_idx = (int)hdr[1]; n_idx_m = (int)hdr[2]; n_idx_c = (int)hdr[3]; n_fix_total = hdr[6] & 0xffffffffLL; c->pivot_halves = hdr[6] >> 32;
             amb_ent.assign((size_t)hdr[4], 0u);
             if (pivot_ok) {
-                fix_ent.assign((size_t)hdr[5], 0u);
-                fix_off.assign(c->n_slots + 1, 0u);
+                snp_ent.assign((size_t)(hdr[5] & 0xffffffffLL), 0u);
+                snp_off.assign(c->n_slots + 1, 0u);
+                qstream.assign((size_t)(hdr[5] >> 32), 0);
+                qoff.assign((size_t)c->n_qtiles * (c->n_chunks + 1), 0u);
                 pivot_words.assign((size_t)(c->Wp / 4) * 8, 0u);
                 wslot.assign((size_t)c->n_qtiles * QTILE, 0);
             }
@@ -744,21 +767,24 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
         UVG_NCCL(c, share(c->d_qamb_ent, amb_ent.size() * 4));
     }
     if (pivot_ok) {
-        UVG_CUDA(c, pooled_alloc(c, 15, &c->d_qdata2, n_chunk_total * sizeof(QChunk2)));
-        UVG_CUDA(c, pooled_alloc(c, 16, &c->d_qfix_off, fix_off.size() * 4));
-        UVG_CUDA(c, pooled_alloc(c, 17, &c->d_qfix_ent, fix_ent.size() * 4));
+        UVG_CUDA(c, pooled_alloc(c, 15, &c->d_qstream, qstream.size()));
+        UVG_CUDA(c, pooled_alloc(c, 16, &c->d_snp_off, snp_off.size() * 4));
+        UVG_CUDA(c, pooled_alloc(c, 17, &c->d_snp_ent, snp_ent.size() * 4));
         UVG_CUDA(c, pooled_alloc(c, 18, &c->d_pivot, pivot_words.size() * 4));
         UVG_CUDA(c, pooled_alloc(c, 19, &c->d_wslot, wslot.size()));
+        UVG_CUDA(c, pooled_alloc(c, 20, &c->d_qoff, qoff.size() * 4));
         UVG_CUDA(c, cudaMemcpyAsync(c->d_wslot, wslot.data(), wslot.size(), cudaMemcpyHostToDevice, c->st));
-        UVG_CUDA(c, cudaMemcpyAsync(c->d_qdata2, qd2.data(), n_chunk_total * sizeof(QChunk2), cudaMemcpyHostToDevice, c->st));
-        UVG_CUDA(c, cudaMemcpyAsync(c->d_qfix_off, fix_off.data(), fix_off.size() * 4, cudaMemcpyHostToDevice, c->st));
-        if (!fix_ent.empty()) UVG_CUDA(c, cudaMemcpyAsync(c->d_qfix_ent, fix_ent.data(), fix_ent.size() * 4, cudaMemcpyHostToDevice, c->st));
+        UVG_CUDA(c, cudaMemcpyAsync(c->d_qstream, qstream.data(), qstream.size(), cudaMemcpyHostToDevice, c->st));
+        UVG_CUDA(c, cudaMemcpyAsync(c->d_qoff, qoff.data(), qoff.size() * 4, cudaMemcpyHostToDevice, c->st));
+        UVG_CUDA(c, cudaMemcpyAsync(c->d_snp_off, snp_off.data(), snp_off.size() * 4, cudaMemcpyHostToDevice, c->st));
+        if (!snp_ent.empty()) UVG_CUDA(c, cudaMemcpyAsync(c->d_snp_ent, snp_ent.data(), snp_ent.size() * 4, cudaMemcpyHostToDevice, c->st));
         UVG_CUDA(c, cudaMemcpyAsync(c->d_pivot, pivot_words.data(), pivot_words.size() * 4, cudaMemcpyHostToDevice, c->st));
         if (bcast) {
             UVG_NCCL(c, share(c->d_wslot, wslot.size()));
-            UVG_NCCL(c, share(c->d_qdata2, n_chunk_total * sizeof(QChunk2)));
-            UVG_NCCL(c, share(c->d_qfix_off, fix_off.size() * 4));
-            UVG_NCCL(c, share(c->d_qfix_ent, fix_ent.size() * 4));
+            UVG_NCCL(c, share(c->d_qstream, qstream.size()));
+            UVG_NCCL(c, share(c->d_qoff, qoff.size() * 4));
+            UVG_NCCL(c, share(c->d_snp_off, snp_off.size() * 4));
+            UVG_NCCL(c, share(c->d_snp_ent, snp_ent.size() * 4));
             UVG_NCCL(c, share(c->d_pivot, pivot_words.size() * 4));
         }
         c->pivot_on = true;
@@ -1312,7 +1338,7 @@ static void fill_pair_params(uvg_ctx* c, PairParams& pp, int64_t lb, int64_t le,
     pp.qnib = c->d_qnib; pp.qamb_off = c->d_qamb_off; pp.qamb_ent = c->d_qamb_ent;
     pp.rb_cnt = c->d_ref_cnt; pp.mc_cnt = c->d_ref_cnt ? c->d_ref_cnt + c->db2_cap : nullptr;
     pp.wslot = c->d_wslot;
-    pp.db2 = c->d_db2; pp.qdata2 = c->d_qdata2; pp.qfix_off = c->d_qfix_off; pp.qfix_ent = c->d_qfix_ent;
+    pp.db2 = c->d_db2; pp.qstream = c->d_qstream; pp.qoff = c->d_qoff; pp.snp_off = c->d_snp_off; pp.snp_ent = c->d_snp_ent;
     pp.ramb_off = c->d_ramb_off; pp.ramb_ent = c->d_ramb_ent; pp.non_n = c->d_non_n;
     pp.qnib_stride = c->qnib_stride;
     pp.Wp = c->Wp; pp.n_chunks = c->n_chunks; pp.n_qtiles = c->n_qtiles; pp.n_slots = c->n_slots;
@@ -1340,7 +1366,7 @@ static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t
         fill_pair_params(c, pp, lstart, lstart + cnt, b, (int64_t)c->rank * c->seg_cap);
         UVG_CUDA(c, c->pivot_on ? launch_pairpivot(pp, c->st) : launch_paircount(pp, c->prm.acgt_mode, c->st));
         c->stats.pair_kernel_launches += 1;
-        if (c->pivot_on && PIVOT_SKIP2) {   // executed (pair, 4-word unit) iterations per lane of this launch: blocks per tile x halves / 2 x references per lane
+        if (c->pivot_on) {   // executed (pair, 4-word unit) iterations per lane of this launch: blocks per tile x halves / 2 x references per lane
             const int64_t per = GROUP * RPL, pairs = (lstart + cnt + per - 1) / per - lstart / per;
             c->work_host += pairs * c->pivot_halves * RPL / 2;
         }

@@ -1,31 +1,32 @@
 // K2p: pair-count kernel in PIVOT form for sm_100a (default scoring mode; the general kernel is paircount.cu).
 // Same contract as k_paircount<0,false> -- the four counts of biomcmc_pairwise_score_matches_truncated_idx
 // (biomcmc alignment.c:855-884) of every (query slot, reference) pair of a round, untruncated, stored into the dense
-// score tile of the query's owner -- with a cheaper inner loop.
+// score tile of the query's owner -- with a much cheaper inner loop.
 //
 // All queries of one search are close to a pivot sequence P (per site the plain base most queries hold; uvg_set_queries).
 // For a site where the query holds P's base, "query == reference" is "reference == P", which does not depend on the query:
 //     mc (reference plane, derived once per query set by k_derive_pivot) = r.base & (r == P)
-// The query planes are stored INVERTED: nq = no plain base here (or trimmed away / padding), ne = not P's base (nq is a
+// The query planes are used INVERTED: nq = no plain base here (or trimmed away / padding), ne = not P's base (nq is a
 // subset of ne), so that
 //     valid  = popc(r.base) - sum popc(r.base & nq)        match' = popc(r.mc) - sum popc(r.mc & ne)
-// with per-reference totals (k_derive_pivot) as first terms and sums that only get contributions from 128-site units in
-// which the query has an N, a gap, an ambiguity code or a SNP: a (slot, unit) pair whose `ne` words are all zero is
-// skipped (QChunk2::active, warp-uniform branch).  Per executed pair-word: 2 LOP3 for the two ANDs, one 3:2 compressor
-// per two words and stream (ones register + one carry word of weight 2), IMAD adds the popcounts:
-//     4 LOP3 (ALU) + 1 POPC (XU) + 1 IMAD (FMA) per pair and 32-site word
-// which balances the ALU and XU pipes at the measured 4:1 LOP3:POPC rate of sm_100 (profiles/int_pipes_b200_r01.json);
-// the general kernel needs 4.5 LOP3 + 1.25 POPC and cannot skip.
-// Query sites with a plain base != P (the query's own SNPs, a few dozen per genome) are outside match'; they are "fix"
-// entries (slot, site, base) that travel with the query chunk and are resolved against column masks of the derived
-// database (per site and base one word: bit l = reference l of the group holds that base): a warp fetches the masks of
-// all its entries of a chunk with one load (lane = entry x group) while it counts the chunk, almost always finds them
-// all zero, and otherwise bumps a per-pair counter in shared memory.  Entries that overflow a chunk's fix block and all
-// ambiguity codes go to the epilogue (pair_epilogue.cuh).
+// with per-reference totals (k_derive_pivot) as first terms and sums that only get contributions from sites where the query
+// has an N, a gap, an ambiguity code or a SNP.  Per (slot, 128-site unit) a warp does one of three things (QWarpHead):
+//   * nothing: the query is complete and equal to the pivot over the unit (~62 % of the units of a SARS-CoV-2 query set);
+//   * one add from the counts table of the derived database: the query holds no plain base in the unit (inside an N run,
+//     trimmed away), so both sums are the reference's own unit totals (~12 %);
+//   * count up to two halves of 64 sites from the planes (~26 % of the units, 1.26 halves each): per pair and half 4 AND,
+//     one 3:2 compressor per stream (ones register + one carry word of weight 2), 2 POPC, 2 IMAD
+//         = 4 LOP3 (ALU) + 1 POPC (XU) + 1 IMAD (FMA) per counted pair and 32-site word,
+//     which balances the ALU and XU pipes at the measured 4:1 LOP3:POPC rate of sm_100 (profiles/int_pipes_b200_r01.json).
+// Query sites with a plain base != P (the query's own SNPs, a few dozen per genome) are outside match'; after the main loop
+// every warp resolves the fix entries of its four slots against the column masks of the derived database (per site and base
+// one word: bit l = reference l of the group holds that base): loads for 32 entries at a time, all independent.  Ambiguity
+// codes go through the shared epilogue (pair_epilogue.cuh).
 // Shape: block = 64 query slots x 64 references, 16 warps x 4 slots, lane = 2 references, 64 registers, 2 blocks per
-// SM (32 warps per SM).  Staging: TMA bulk copies (query chunk + the base/mc planes of the two reference groups) into an
-// 8-deep ring with full/empty mbarriers (no __syncthreads in the loop: warps drift up to the ring depth apart); one
-// elected thread refills a stage two chunks after it was consumed.
+// SM (32 warps per SM).  Staging: a ring of STAGES2 stages, each filled by two TMA bulk copies -- the (tile, chunk) record of
+// the query stream (variable length: 128-byte head + 16 bytes per counted half, ~0.8 KB on average) and the planes + counts
+// of the pair's chunk record (4.5 KB) -- with full/empty mbarriers (no __syncthreads in the loop: warps drift up to the ring
+// depth apart); one elected thread refills a stage PIVOT_LAG chunks after it was consumed.
 #include "common.cuh"
 #include "kernels.h"
 #include "pair_epilogue.cuh"
@@ -33,140 +34,88 @@
 
 namespace uvg {
 
-// staged part of a chunk record: the base and mc planes of the block's two groups (the column masks stay in global memory /
-// L2: only fix entries read them)
+// staged part of a chunk record of the derived database
 struct __align__(16) RefPlanes2 {
     uint4 base[GROUP];
     uint4 mc[GROUP];
 };
 static_assert(sizeof(RefPlanes2) == UNIT2_PLANES, "planes of one (group, unit) of the derived database");
 struct __align__(16) Stage2 {
-    QChunk2    q;
+    uint8_t    q[QREC_MAX];              // QWarpHead[16] | items
     RefPlanes2 ref[RPL][W4];
     uint32_t   cnt[RPL][W4][GROUP];      // unit totals of every reference: popc(mc) | popc(base) << 16
 };
-static_assert(sizeof(RefPlanes2) * RPL * W4 == CHUNK2_PLANES && sizeof(Stage2) == sizeof(QChunk2) + CHUNK2_STAGED, "staged prefix of a chunk record");
-constexpr size_t PIVOT_FIXHIT_BYTES = QTILE * GROUP * RPL * sizeof(uint16_t);       // per (slot, reference of the block): matches found by fix entries
-constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + PIVOT_FIXHIT_BYTES + 2 * STAGES2 * sizeof(uint64_t);
-#ifndef PIVOT_ROTATE
-#define PIVOT_ROTATE 0          // 1: the warps take turns refilling the ring (chunk c: warp c % 16) -- measured 1.6x SLOWER; 0: warp 0 refills
-#endif
-#ifndef PIVOT_COPIES
-#define PIVOT_COPIES 1          // bulk copies per stage for the reference side: 1 (4.5 KB) or 4 (1 KB per (group, unit) + the counts)
-#endif
+static_assert(sizeof(RefPlanes2) * RPL * W4 == CHUNK2_PLANES && sizeof(Stage2) == QREC_MAX + CHUNK2_STAGED, "ring stage");
+constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(uint64_t);
 #ifndef PIVOT_LAG
-#define PIVOT_LAG 2
+#define PIVOT_LAG 3
 #endif
 constexpr int REFILL_LAG = PIVOT_LAG;
-
 constexpr int QW2 = PIVOT_QW;                           // query slots per warp (register tile QW2 x RPL pairs per lane)
 constexpr int PIVOT_THREADS = PIVOT_WARPS * 32;
+static_assert(REFILL_LAG >= 0 && REFILL_LAG < STAGES2, "refill lag");
 
 __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams p, const uint32_t k2, const uint32_t k128k)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     Stage2* stage = reinterpret_cast<Stage2*>(smem);
-    uint16_t* fixhit = reinterpret_cast<uint16_t*>(smem + STAGES2 * sizeof(Stage2));   // [slot][RPL * GROUP]: written and read by one thread each
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES2 * sizeof(Stage2) + PIVOT_FIXHIT_BYTES);
-    uint64_t* empty = full + STAGES2;
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int qt = blockIdx.x % p.n_qtiles;
     const int64_t group0 = (p.local_begin / (GROUP * RPL) + blockIdx.x / p.n_qtiles) * RPL;
-    const QChunk2* qsrc = p.qdata2 + (size_t)qt * p.n_chunks;
+    const uint32_t* qoff = p.qoff + (size_t)qt * (p.n_chunks + 1);
     const uint8_t* rsrc = p.db2 + (size_t)(group0 / RPL) * (size_t)p.n_chunks * CHUNK2_BYTES;      // chunk records of this block's pair of groups
     const int owner = qt % p.world, row0 = (qt / p.world) * QTILE;
     // shared-memory addresses as plain integers: nothing in the loop goes through a generic -> shared conversion
     uint32_t stage_a = smem_u32(stage);
     asm volatile("mov.u32 %0, %0;" : "+r"(stage_a));                         // opaque: kept in a register instead of being re-derived (S2R + LEA) per use
-    const uint32_t full_a = stage_a + (uint32_t)(STAGES2 * sizeof(Stage2) + PIVOT_FIXHIT_BYTES), empty_a = full_a + STAGES2 * 8u;
+    const uint32_t full_a = stage_a + (uint32_t)(STAGES2 * sizeof(Stage2)), empty_a = full_a + STAGES2 * 8u;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES2; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, PIVOT_THREADS / 32); }
+        for (int s = 0; s < STAGES2; ++s) { mbar_init_a(full_a + s * 8u, 1); mbar_init_a(empty_a + s * 8u, PIVOT_THREADS / 32); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int i = threadIdx.x; i < (int)(PIVOT_FIXHIT_BYTES / sizeof(uint4)); i += PIVOT_THREADS) reinterpret_cast<uint4*>(fixhit)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
-    // one stage = the query chunk + the planes of the pair's chunk record: two TMA bulk copies
-    auto issue = [&](int c, int s) {
+    // one stage = the query record of the chunk (exactly its bytes) + planes and counts of the pair's chunk record
+    uint32_t o_next = 0;                                                     // producer thread: offset of the record to issue next
+    auto issue_at = [&](int c, int s, uint32_t o0, uint32_t o1) {
         const uint32_t bar = full_a + (uint32_t)s * 8u, dst = stage_a + (uint32_t)s * (uint32_t)sizeof(Stage2);
-        mbar_expect_tx_a(bar, (uint32_t)(sizeof(QChunk2) + CHUNK2_STAGED));
-        bulk_g2s_a(dst, qsrc + c, (uint32_t)sizeof(QChunk2), bar);
-        const uint8_t* src = rsrc + (size_t)c * CHUNK2_BYTES;
-#if PIVOT_COPIES == 1
-        bulk_g2s_a(dst + (uint32_t)sizeof(QChunk2), src, (uint32_t)CHUNK2_STAGED, bar);
-#else
-#pragma unroll
-        for (int k = 0; k < RPL * W4; ++k)
-            bulk_g2s_a(dst + (uint32_t)sizeof(QChunk2) + (uint32_t)k * UNIT2_PLANES, src + (size_t)k * UNIT2_PLANES, (uint32_t)UNIT2_PLANES, bar);
-        bulk_g2s_a(dst + (uint32_t)sizeof(QChunk2) + CHUNK2_PLANES, src + CHUNK2_PLANES, (uint32_t)CHUNK2_COUNTS, bar);
-#endif
+        mbar_expect_tx_a(bar, (o1 - o0) + (uint32_t)CHUNK2_STAGED);
+        bulk_g2s_a(dst, p.qstream + o0, o1 - o0, bar);
+        bulk_g2s_a(dst + (uint32_t)QREC_MAX, rsrc + (size_t)c * CHUNK2_BYTES, (uint32_t)CHUNK2_STAGED, bar);
     };
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES2 && s < p.n_chunks; ++s) issue(s, s);
+    if (warp == 0) {
+        // the offsets of the first records in one go (lane = record), then lane 0 fills the ring
+        static_assert(STAGES2 < 32, "one lane per prologue offset");
+        const uint32_t mine = lane <= min(STAGES2, p.n_chunks) ? __ldg(qoff + lane) : 0u;
+#pragma unroll
+        for (int s = 0; s < STAGES2; ++s) {
+            const uint32_t o0 = __shfl_sync(0xffffffffu, mine, s), o1 = __shfl_sync(0xffffffffu, mine, s + 1);
+            if (lane == 0 && s < p.n_chunks) { issue_at(s, s, o0, o1); o_next = o1; }
+        }
     }
 
-    // per pair: carry-save "ones" registers of the two COMPLEMENT streams and one packed counter.  The query planes are
-    // stored inverted (nq = no plain base here, ne = not the pivot's base; nq is a subset of ne):
-    //     valid   = popc(r.base) - popc(r.base & nq)        match' = popc(r.mc) - popc(r.mc & ne)
-    // The first terms are per-reference totals (k_derive_pivot); the second terms are zero wherever the query is complete
-    // and equal to the pivot, so a (slot, unit) whose `ne` words are all zero is SKIPPED (uniform branch: the planes
-    // are warp-wide broadcasts).  acc = (#weight-2 carries of r.mc & ne) * 2 | (#weight-2 carries of r.base & nq) * 2 << 16
+    // per pair: carry-save "ones" registers of the two complement streams and one packed counter
+    //     acc = (#weight-2 carries of r.mc & ne) * 2 | (#weight-2 carries of r.base & nq) * 2 << 16     (+ the unit totals of all-N units)
     uint32_t oV[RPL][QW2], oM[RPL][QW2], acc[RPL][QW2];
 #pragma unroll
     for (int g = 0; g < RPL; ++g)
 #pragma unroll
         for (int j = 0; j < QW2; ++j) { oV[g][j] = 0; oM[g][j] = 0; acc[g][j] = 0; }
 
-    // the slots of the tile this warp counts (uvg_set_queries balances the warps of a tile by work)
-    // kept as byte offsets of the slot's planes inside QChunk2::pl[u], two per register (the loop is short of registers)
-    static_assert(QW2 == 4 && sizeof(uint4) * 2 * QTILE <= 65536, "slot offsets are packed as 4 x 16 bits");
-    uint32_t so[2];
-    {
-        const uint8_t* ws = p.wslot + ((size_t)qt * PIVOT_WARPS + warp) * QW2;
-        so[0] = (uint32_t)ws[0] * 32u | ((uint32_t)ws[1] * 32u) << 16;
-        so[1] = (uint32_t)ws[2] * 32u | ((uint32_t)ws[3] * 32u) << 16;
-        asm volatile("mov.u32 %0, %0;" : "+r"(so[0]));                       // opaque: unpacked where used, not hoisted into four spilled registers
-        asm volatile("mov.u32 %0, %0;" : "+r"(so[1]));
-    }
-    auto slot_off = [&](int j) -> uint32_t { return (j & 1) ? so[j >> 1] >> 16 : so[j >> 1] & 0xffffu; };
-    auto slot_of = [&](int j) -> int { return (int)(slot_off(j) >> 5); };
-    // resolve fetched column masks: a set bit = that reference holds the query's (non-pivot) base at the site, a match the
-    // planes did not see.  Almost always no lane holds a non-zero mask.
-    auto resolve = [&](uint32_t ent_l, uint32_t col_l) {
-        uint32_t any = __ballot_sync(0xffffffffu, col_l != 0u);
-        while (any) {
-            const int src = __ffs(any) - 1;
-            any &= any - 1u;
-            const uint32_t col = __shfl_sync(0xffffffffu, col_l, src), ent = __shfl_sync(0xffffffffu, ent_l, src);
-            fixhit[(ent >> 16) * (RPL * GROUP) + (src % RPL) * GROUP + lane] += (uint16_t)((col >> lane) & 1u);   // branch-free; this thread owns the counter
-        }
-    };
-#if !PIVOT_SKIP2
-    uint32_t executed = 0;                                                   // (slot, unit) iterations that were not skipped
-#endif
+    int s = 0;                                                               // stage of chunk c = c % STAGES2, ph = (c / STAGES2) & 1
+    uint32_t ph = 0;
     for (int c = 0; c < p.n_chunks; ++c) {
-        const int s = c % STAGES2;
-        mbar_wait_a(full_a + (uint32_t)s * 8u, (uint32_t)((c / STAGES2) & 1));
+        mbar_wait_a(full_a + (uint32_t)s * 8u, ph);
         const Stage2& st = stage[s];
-        // fix entries of this warp's slots in this chunk (usually 0..3): lane l fetches the column mask of entry l / RPL for
-        // reference group l % RPL (one load for the whole warp, consumed after the counting work of the chunk)
-        const uint32_t fb = st.q.fix_begin[warp], fe = st.q.fix_begin[warp + 1];
-        const uint8_t* gl0 = rsrc + (size_t)c * CHUNK2_BYTES;                  // fix entries: byte offsets inside this chunk record
-        uint32_t my_ent = 0, my_col = 0;
-        if (fb + lane / RPL < fe) {
-            my_ent = st.q.fix[fb + lane / RPL];
-            my_col = __ldg(reinterpret_cast<const uint32_t*>(gl0 + (lane % RPL) * (W4 * UNIT2_MASKS) + (my_ent & 0xffffu)));
-        }
-#if PIVOT_SKIP2
-        // what this warp has to do in the chunk: per unit u and slot j either nothing (the query is complete and equal to
-        // the pivot over the unit), or one add from the counts table (the query holds no plain base in the unit: all-N), or
-        // up to two halves of 64 sites counted from the planes
-        const uint32_t hmask = st.q.half[warp], nmask = st.q.fulln[warp];
+        // what this warp has to do in the chunk, and where its items start
+        const uint2 hd = reinterpret_cast<const uint2*>(st.q)[warp];
+        const uint32_t hmask = hd.x & 0xffffu, nmask = (hd.x >> 16) & 0xffu;
+        const uint4* item = reinterpret_cast<const uint4*>(st.q + QHEAD_BYTES) + (hd.y & 0xffffu);
 #pragma unroll
         for (int u = 0; u < W4; ++u) {
             const uint32_t nu = (nmask >> (u * 4)) & 15u;
-            if (nu) {
+            if (nu) {                                                        // all-N units: the reference's own unit totals
                 uint32_t ct[RPL];
 #pragma unroll
                 for (int g = 0; g < RPL; ++g) ct[g] = st.cnt[g][u][lane];
@@ -185,105 +134,80 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
 #pragma unroll
             for (int j = 0; j < QW2; ++j) {
                 const uint32_t hj = (hu >> (j * 2)) & 3u;
-                if (hj == 0u) continue;
-                const uint2* qp = reinterpret_cast<const uint2*>(reinterpret_cast<const uint8_t*>(&st.q.pl[u][0][0]) + slot_off(j));
                 if (hj & 1u) {
-                    const uint2 qb = qp[0], qe = qp[2];                      // words 0, 1 of the two complement planes
+                    const uint4 q = *item++;                                 // nq words 0, 1 | ne words 0, 1
 #pragma unroll
                     for (int g = 0; g < RPL; ++g) {
                         uint32_t ov = oV[g][j], om = oM[g][j], cv, cm;
-                        csa(ov, cv, ov, rb[g].x & qb.x, rb[g].y & qb.y);
-                        csa(om, cm, om, rm[g].x & qe.x, rm[g].y & qe.y);
+                        csa(ov, cv, ov, rb[g].x & q.x, rb[g].y & q.y);
+                        csa(om, cm, om, rm[g].x & q.z, rm[g].y & q.w);
                         oV[g][j] = ov; oM[g][j] = om;
                         acc[g][j] = imad(__popc(cm), k2, imad(__popc(cv), k128k, acc[g][j]));
                     }
                 }
                 if (hj & 2u) {
-                    const uint2 qb = qp[1], qe = qp[3];                      // words 2, 3
+                    const uint4 q = *item++;                                 // words 2, 3
 #pragma unroll
                     for (int g = 0; g < RPL; ++g) {
                         uint32_t ov = oV[g][j], om = oM[g][j], cv, cm;
-                        csa(ov, cv, ov, rb[g].z & qb.x, rb[g].w & qb.y);
-                        csa(om, cm, om, rm[g].z & qe.x, rm[g].w & qe.y);
+                        csa(ov, cv, ov, rb[g].z & q.x, rb[g].w & q.y);
+                        csa(om, cm, om, rm[g].z & q.z, rm[g].w & q.w);
                         oV[g][j] = ov; oM[g][j] = om;
                         acc[g][j] = imad(__popc(cm), k2, imad(__popc(cv), k128k, acc[g][j]));
                     }
                 }
             }
         }
-#else
-#pragma unroll
-        for (int u = 0; u < W4; ++u) {
-            // which of this warp's slots have work in this unit (the others are complete and equal to the pivot over these
-            // 128 sites); nothing to do for any of them: not even the reference words are read
-            const uint32_t act = st.q.active[u][warp];
-            if (act == 0u) continue;
-            uint4 rb[RPL], rm[RPL];
-#pragma unroll
-            for (int g = 0; g < RPL; ++g) { rb[g] = st.ref[g][u].base[lane]; rm[g] = st.ref[g][u].mc[lane]; }
-#pragma unroll
-            for (int j = 0; j < QW2; ++j) {
-                if (!((act >> j) & 1u)) continue;
-                const uint4* qp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(&st.q.pl[u][0][0]) + slot_off(j));
-                const uint4 qb = qp[0], qe = qp[1];
-                ++executed;
-#pragma unroll
-                for (int g = 0; g < RPL; ++g) {
-                    const uint32_t V0 = rb[g].x & qb.x, V1 = rb[g].y & qb.y, V2 = rb[g].z & qb.z, V3 = rb[g].w & qb.w;
-                    const uint32_t M0 = rm[g].x & qe.x, M1 = rm[g].y & qe.y, M2 = rm[g].z & qe.z, M3 = rm[g].w & qe.w;
-                    uint32_t ov = oV[g][j], om = oM[g][j], cv0, cv1, cm0, cm1;
-                    csa(ov, cv0, ov, V0, V1);
-                    csa(ov, cv1, ov, V2, V3);
-                    csa(om, cm0, om, M0, M1);
-                    csa(om, cm1, om, M2, M3);
-                    oV[g][j] = ov; oM[g][j] = om;
-                    uint32_t a = acc[g][j];
-                    a = imad(__popc(cv0), k128k, a);
-                    a = imad(__popc(cm0), k2, a);
-                    a = imad(__popc(cv1), k128k, a);
-                    a = imad(__popc(cm1), k2, a);
-                    acc[g][j] = a;
-                }
-            }
-        }
-#endif
-        if (fe > fb) {
-            resolve(my_ent, my_col);
-            for (uint32_t e0 = fb + 32 / RPL; e0 < fe; e0 += 32 / RPL) {    // more than 16 entries (rare)
-                my_col = 0;
-                if (e0 + lane / RPL < fe) {
-                    my_ent = st.q.fix[e0 + lane / RPL];
-                    my_col = __ldg(reinterpret_cast<const uint32_t*>(gl0 + (lane % RPL) * (W4 * UNIT2_MASKS) + (my_ent & 0xffffu)));
-                }
-                resolve(my_ent, my_col);
-            }
-        }
-        // release the stage.  Refill: the stage consumed REFILL_LAG chunks ago gets the chunk STAGES2 further on.  The warps take
-        // turns (chunk c: warp c % 16), so that no warp carries the producer's instructions on top of its counting work -- with
-        // one fixed producer warp that warp sets the pace of the block and the other fifteen wait for it at the head of the ring.
+        // release the stage; the elected thread refills the stage consumed REFILL_LAG chunks ago (everybody is done with it
+        // by now, or will be within a few hundred cycles)
         __syncwarp();
         if (lane == 0) {
             mbar_arrive_a(empty_a + (uint32_t)s * 8u);
-#if PIVOT_ROTATE
-            if (warp == (c % PIVOT_WARPS)) {
-#else
             if (warp == 0) {
-#endif
                 const int cr = c - REFILL_LAG, cn = cr + STAGES2;
                 if (cr >= 0 && cn < p.n_chunks) {
-                    const int sr = cr % STAGES2;
-                    mbar_wait_a(empty_a + (uint32_t)sr * 8u, (uint32_t)((cr / STAGES2) & 1));
-                    issue(cn, sr);
+                    const int sr = s >= REFILL_LAG ? s - REFILL_LAG : s - REFILL_LAG + STAGES2;
+                    const uint32_t o1 = __ldg(qoff + cn + 1);                  // in flight while the stage drains
+                    mbar_wait_a(empty_a + (uint32_t)sr * 8u, s >= REFILL_LAG ? ph : ph ^ 1u);
+                    issue_at(cn, sr, o_next, o1);
+                    o_next = o1;
                 }
             }
         }
         __syncwarp();
+        if (++s == STAGES2) { s = 0; ph ^= 1u; }
     }
-    // p.work counts (pair, 4-word unit) iterations per lane.  The half-unit variant does not count in the kernel (no register
-    // to spare): the host knows the masks and adds halves x references per launch (engine.cu, run_round)
-#if !PIVOT_SKIP2
-    if (lane == 0 && p.work) atomicAdd(p.work, (unsigned long long)executed * RPL);
-#endif
+
+    // ---- fix entries: plain bases of the warp's slots that differ from the pivot.  A reference that holds the same base there
+    // is one more match.  Lane = entry for the loads of the column masks (32 independent loads per slot and group, L2 hits or
+    // the 8 KB mask part of the chunk records), then the non-zero masks are broadcast lane by lane. ----
+    const uint8_t* ws = p.wslot + ((size_t)qt * PIVOT_WARPS + warp) * QW2;
+    uint32_t fh[RPL][QW2];
+#pragma unroll
+    for (int j = 0; j < QW2; ++j) {
+#pragma unroll
+        for (int g = 0; g < RPL; ++g) fh[g][j] = 0;
+        const int slot = qt * QTILE + (int)ws[j];
+        if (slot >= p.n_slots) continue;
+        const uint32_t e1 = __ldg(p.snp_off + slot + 1);
+        for (uint32_t e0 = __ldg(p.snp_off + slot); e0 < e1; e0 += 32) {
+            const bool have = e0 + lane < e1;
+            const uint32_t ent = have ? __ldg(p.snp_ent + e0 + lane) : 0u;
+            const uint8_t* mrec = rsrc + (size_t)(ent >> 16) * CHUNK2_BYTES + CHUNK2_STAGED + ((ent >> 9) & 1u) * UNIT2_MASKS + (ent & 0x1ffu) * 4u;
+            uint32_t mk[RPL];
+#pragma unroll
+            for (int g = 0; g < RPL; ++g) mk[g] = have ? __ldg(reinterpret_cast<const uint32_t*>(mrec + g * (W4 * UNIT2_MASKS))) : 0u;
+#pragma unroll
+            for (int g = 0; g < RPL; ++g) {
+                uint32_t any = __ballot_sync(0xffffffffu, mk[g] != 0u);
+                while (any) {
+                    const int src = __ffs(any) - 1;
+                    any &= any - 1u;
+                    fh[g][j] += (__shfl_sync(0xffffffffu, mk[g], src) >> lane) & 1u;
+                }
+            }
+        }
+    }
 
     // ---- epilogue: plane counts -> exact counts -> score tile of the owner ----
     bool in_range[RPL];
@@ -295,16 +219,16 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     }
 #pragma unroll
     for (int j = 0; j < QW2; ++j) {
-        const int sjj = slot_of(j);
+        const int sjj = (int)ws[j];
         const int slot = qt * QTILE + sjj;
         if (slot >= p.n_slots) continue;
         const bool is_cons = slot == p.n_slots - 1;
 #pragma unroll
         for (int g = 0; g < RPL; ++g) {
             if (!in_range[g]) continue;
-            const int32_t M = p.mc_cnt[local[g]] - (int32_t)((acc[g][j] & 0xffffu) + __popc(oM[g][j])) + (int32_t)fixhit[sjj * (RPL * GROUP) + g * GROUP + lane];
+            const int32_t M = p.mc_cnt[local[g]] - (int32_t)((acc[g][j] & 0xffffu) + __popc(oM[g][j])) + (int32_t)fh[g][j];
             const int32_t V = p.rb_cnt[local[g]] - (int32_t)((acc[g][j] >> 16) + __popc(oV[g][j]));
-            const uint4 v = pair_epilogue_default(p, p.qfix_off, p.qfix_ent, slot, group0 + g, lane, local[g], M, V);
+            const uint4 v = pair_epilogue_default(p, p.qamb_off, p.qamb_ent, slot, group0 + g, lane, local[g], M, V);
             pair_store(p, owner, row0 + sjj, is_cons, local[g], v);
         }
     }
