@@ -613,6 +613,147 @@ static void usage(const char* prog, int full)
            "                         files (same size and mtime, same -A, same mode) reads it instead of parsing them\n");
 }
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * `uvaiaball` (src/ball.c:138-291) over uvg_ball_*: keeps the reference sequences within a radius of some query.
+ * Invoked as `uvaia_b200 ball ...` or through a program name that starts with "uvaiaball".
+ * ------------------------------------------------------------------------------------------------------------- */
+static void ball_usage(const char* prog, int full)
+{
+    printf("%s ball  [-h|--help] [-v|--version] [-x|--acgt] [-k|--keep_resolved] [-d|--distance=<int>] [--trim=<int>] [-A|--ref_ambiguity=<double>] "
+           "[-a|--query_ambiguity=<double>] [-p|--pool=<int>] -r|--reference=<ref.fa(.gz,.xz)> [-r ...]... <seqs.fa(.gz,.xz)> [-o|--output=<without suffix>]\n", prog);
+    if (!full) return;
+    printf("Finds all reference neighbours to query sequences within a ball radius (i.e. close to any query sequence), on a B200 GPU\n"
+           "  -x, --acgt             considers only ACGT sites (i.e. unambiguous SNP differences)\n"
+           "  -k, --keep_resolved    when excluding redundant query seqs, keep the more resolved (instead of default, less resolved)\n"
+           "  -d, --distance         ball radius, i.e. refs within this distance to any query seq are kept (default=5)\n"
+           "      --trim             number of sites to trim from both ends (default=0, suggested for sarscov2=230)\n"
+           "  -a, --query_ambiguity  maximum allowed ambiguity for QUERY sequence to be excluded (default=0.5)\n"
+           "  -A, --ref_ambiguity    maximum allowed ambiguity for REFERENCE sequence to be excluded (default=0.5)\n"
+           "  -p, --pool             accepted for compatibility\n"
+           "  -r, --reference        aligned reference sequences (can be several files)\n"
+           "  -o, --output           prefix of xzipped output alignment with subset of ref sequences (default ball_uvaia)\n"
+           "      --device           CUDA device ordinal (default 0);  --batch: reference rows per push (default 65536)\n");
+}
+
+static int ball_main(int argc, char** argv)
+{
+    int dist = 5, trim = 0, acgt = 0, hires = 0, device = 0;                    /* ball.c:63-66 */
+    long batch_rows = 65536;
+    double ambig_q = 0.5, ambig_r = 0.5;
+    const char* out_prefix = "ball_uvaia";
+    const char* ref_file[1024]; int n_ref_files = 0;
+    static struct option lo[] = {
+        {"help", 0, 0, 'h'}, {"version", 0, 0, 'v'}, {"acgt", 0, 0, 'x'}, {"keep_resolved", 0, 0, 'k'}, {"distance", 1, 0, 'd'}, {"trim", 1, 0, 1001},
+        {"query_ambiguity", 1, 0, 'a'}, {"ref_ambiguity", 1, 0, 'A'}, {"pool", 1, 0, 'p'}, {"reference", 1, 0, 'r'}, {"output", 1, 0, 'o'},
+        {"device", 1, 0, 1002}, {"batch", 1, 0, 1003}, {0, 0, 0, 0}};
+    int ch;
+    while ((ch = getopt_long(argc, argv, "hvxkd:a:A:p:r:o:", lo, NULL)) != -1) {
+        switch (ch) {
+        case 'h': ball_usage(argv[0], 1); return EXIT_SUCCESS;
+        case 'v': printf("%s\n", PROGRAM_VERSION); return EXIT_SUCCESS;
+        case 'x': acgt = 1; break;
+        case 'k': hires = 1; break;
+        case 'd': dist = atoi(optarg); break;
+        case 1001: trim = atoi(optarg); break;
+        case 'a': ambig_q = atof(optarg); break;
+        case 'A': ambig_r = atof(optarg); break;
+        case 'p': break;
+        case 'r': if (n_ref_files == 1024) die("at most 1024 reference files"); ref_file[n_ref_files++] = optarg; break;
+        case 'o': out_prefix = optarg; break;
+        case 1002: device = atoi(optarg); break;
+        case 1003: batch_rows = atol(optarg); break;
+        default: ball_usage(argv[0], 0); return EXIT_FAILURE;
+        }
+    }
+    if (n_ref_files < 1 || argc - optind != 1) { ball_usage(argv[0], 0); return EXIT_FAILURE; }
+    const char* query_file = argv[optind];
+    if (ambig_q < 0.001) ambig_q = 0.001;                                       /* ball.c:154-157 */
+    if (ambig_q > 1.) ambig_q = 1.;
+    if (ambig_r < 0.001) ambig_r = 0.001;
+    if (ambig_r > 1.) ambig_r = 1.;
+    if (batch_rows < 1) batch_rows = 1;
+    init_tables();
+    const double t0 = now_s();
+    fprintf(stderr, "Experimental program: uvaia_b200 ball package: %s\n", PROGRAM_VERSION);
+    int n_read = 0;
+    queries_t q = read_queries(query_file, ambig_q, trim, acgt, &n_read);
+    fprintf(stderr, "Finished reading %d query references in %lf secs;\n", n_read, now_s() - t0);
+    fprintf(stderr, "Query database composed of %d valid references, after excluding low quality.\n", q.n);
+    if (q.n < 1) die("No valid reference sequences found. Please check file %s.", query_file);
+    const int L = q.nchar;
+    fprintf(stderr, acgt ? "Only ACGT differences are taken into account. \n" : "Partial matches are taken into account (excluding only gaps and Ns).\n");
+    {   /* ball.c:190: redundant queries always go; -k keeps the more resolved one */
+        uint8_t* keep = xmalloc(q.n);
+        int n_kept = 0;
+        if (uvg_prune_queries(q.text, q.n, L, trim, acgt, hires, keep, &n_kept)) die("uvg_prune_queries failed");
+        int w = 0;
+        for (int i = 0; i < q.n; ++i) {
+            if (!keep[i]) { free(q.name[i]); continue; }
+            if (w != i) { memmove(q.text + (size_t)w * L, q.text + (size_t)i * L, L); q.name[w] = q.name[i]; }
+            ++w;
+        }
+        q.n = n_kept;
+        free(keep);
+        fprintf(stderr, "Query database now composed of %d valid references, after removing redundant (%s resolved) sequences.\n", q.n, hires ? "less" : "more");
+    }
+    uvg_ball_params prm;
+    memset(&prm, 0, sizeof prm);
+    prm.abi_version = UVG_ABI_VERSION; prm.nchar = L; prm.trim = trim; prm.dist = dist; prm.acgt_mode = acgt; prm.device = device;
+    uvg_ball* gpu = NULL;
+    uvg_query_info qi;
+    if (uvg_ball_create(&prm, &gpu)) die("%s", uvg_ball_last_error(NULL));
+    if (uvg_ball_set_queries(gpu, q.text, q.n, &qi)) die("%s", uvg_ball_last_error(gpu));
+    fprintf(stderr, "Query sequence alignment: %d segregating, %d non-segregating sites with indels, and %d constant sites (all are used in comparisons)\n",
+            qi.n_idx, qi.n_idx_m, qi.n_idx_c);
+    fprintf(stderr, "radius distance is %d (refs more distant than this are excluded)\n", (int)uvg_ball_radius(gpu));
+
+    const int min_non_n = (int)(L * ambig_r);                                   /* ball.c:201: A, not 1 - A */
+    if (batch_rows > ((long)1 << 30) / L) batch_rows = (((long)1 << 30) / L) > 0 ? ((long)1 << 30) / L : 1;
+    size_t plen = strlen(out_prefix);
+    char* outname = xmalloc(plen + 16);
+    sprintf(outname, "%s.aln.xz", out_prefix);
+    writer_t w = writer_open(outname);
+    stream_t sp;
+    memset(&sp, 0, sizeof sp);
+    sp.file = ref_file; sp.n_files = n_ref_files; sp.L = L; sp.min_non_n = min_non_n; sp.batch_rows = batch_rows; sp.qset = NULL; sp.t0 = t0;
+    for (int k = 0; k < 2; ++k) {
+        sp.batch[k].text = uvg_host_alloc_pinned((size_t)batch_rows * L);
+        if (!sp.batch[k].text) die("cannot allocate %zu bytes of pinned memory", (size_t)batch_rows * L);
+        sp.batch[k].name = xmalloc(batch_rows * sizeof(char*));
+    }
+    sem_init(&sp.free_slots, 0, 2);
+    sem_init(&sp.full_slots, 0, 0);
+    pthread_t reader;
+    if (pthread_create(&reader, NULL, stream_reader, &sp)) die("cannot start the reader thread");
+    uint8_t* keep = xmalloc(batch_rows);
+    long n_output = 0, n_invalid = 0;
+    for (int k = 0;; k ^= 1) {
+        sem_wait(&sp.full_slots);
+        batch_t* bt = &sp.batch[k];
+        if (bt->n > 0) {
+            if (uvg_ball_push_refs(gpu, bt->text, bt->n, min_non_n, keep, NULL)) die("%s", uvg_ball_last_error(gpu));
+            for (long i = 0; i < bt->n; ++i) {
+                if (keep[i] == 2) {                                             /* ball.c:246-252: within the radius, in file order */
+                    writer_put(&w, ">", 1); writer_put(&w, bt->name[i], strlen(bt->name[i])); writer_put(&w, "\n", 1);
+                    writer_put(&w, bt->text + (size_t)i * L, L); writer_put(&w, "\n", 1);
+                    ++n_output;
+                } else if (keep[i] == 0) ++n_invalid;
+                free(bt->name[i]);
+            }
+        }
+        const int last = bt->last;
+        sem_post(&sp.free_slots);
+        if (last) break;
+    }
+    pthread_join(reader, NULL);
+    n_invalid += sp.n_invalid;
+    writer_close(&w);
+    fprintf(stderr, "Total of %ld sequences read, %ld sequences within radius (kept), %ld too ambiguous (excluded)\n", sp.count, n_output, n_invalid);
+    fprintf(stderr, "Saved %ld sequences to file %s, %.3lf secs elapsed.\n", n_output, outname, now_s() - t0);
+    uvg_ball_destroy(gpu);
+    return EXIT_SUCCESS;
+}
+
 /* what omp_get_max_threads() answers in the reference program before -t is applied (nearest.c:81): OMP_NUM_THREADS when it
  * is set, else the processors this process may run on */
 static int omp_max_threads_like(void)
@@ -627,6 +768,12 @@ static int omp_max_threads_like(void)
 
 int main(int argc, char** argv)
 {
+    {   /* `uvaia_b200 ball ...` or a program name that starts with "uvaiaball": the radius search */
+        const char* base = strrchr(argv[0], '/');
+        base = base ? base + 1 : argv[0];
+        if (!strncmp(base, "uvaiaball", 9)) return ball_main(argc, argv);
+        if (argc > 1 && !strcmp(argv[1], "ball")) { argv[1] = argv[0]; return ball_main(argc - 1, argv + 1); }
+    }
     int nbest = 100, trim = 0, acgt = 0, xclude = 0, pool = 0, device = 0, hires = 0;
     long batch_rows = 65536, max_resident = 1 << 20;
     const char* cache_path = NULL;

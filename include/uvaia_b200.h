@@ -180,6 +180,33 @@ int uvg_nccl_init(uvg_ctx* ctx, const void* id128);            /* collective ove
 /* In sharded mode every rank declares how many accepted references exist in total before uvg_search. */
 int uvg_set_global_count(uvg_ctx* ctx, int64_t n_total);
 
+/* ---- radius search: the reference program `uvaiaball` (src/ball.c) ----
+ * Which reference sequences are within `dist` differences of SOME query: replaces seq_ball_against_query_structure
+ * (src/fastaseq.c:660-696) inside the OpenMP loop ball.c:240-244 and the reference filter ball.c:201,216-222.  The ball
+ * distance compares upper-cased BYTES over the site sets of create_query_indices (two usable bytes that differ count one;
+ * --acgt: only A, C, G, T are usable), so this path works on the sequence text, not on the packed planes, and has its own
+ * small context.  Host flow (ball.c:172-194): filter the queries (utils.c:10-48), order them (fastaseq.c:779-795), ALWAYS
+ * prune them with uvg_prune_queries (keep_more_resolved = the -k flag), then uvg_ball_set_queries. */
+typedef struct uvg_ball uvg_ball;
+typedef struct uvg_ball_params {
+    int32_t abi_version;    /* UVG_ABI_VERSION */
+    int32_t nchar;
+    int32_t trim;           /* --trim, clamped like fastaseq.c:708-712 */
+    int32_t dist;           /* -d / --distance (the program's default is 5); clamped to (nchar - 2 trim) / 10, fastaseq.c:713-715 */
+    int32_t acgt_mode;      /* -x / --acgt */
+    int32_t device;
+} uvg_ball_params;
+int  uvg_ball_create(const uvg_ball_params* p, uvg_ball** out);
+void uvg_ball_destroy(uvg_ball* b);
+const char* uvg_ball_last_error(const uvg_ball* b);   /* b may be NULL: error of the last failed uvg_ball_create */
+int32_t uvg_ball_radius(const uvg_ball* b);           /* dist after clamping */
+/* text = n_query rows of nchar bytes, filtered, ordered and pruned by the host; builds consensus / idx / idx_m / idx_c */
+int uvg_ball_set_queries(uvg_ball* b, const uint8_t* text, int32_t n_query, uvg_query_info* info);
+/* text = n reference rows of nchar bytes (host memory, any case).  keep[i] = 0: too ambiguous (valid_ref_sites < min_non_n;
+ * uvaiaball uses min_non_n = (int)(nchar * A), ball.c:201), 1: outside the ball, 2: within `dist` of some query (the rows
+ * uvaiaball writes to <prefix>.aln.xz, in file order).  non_n_out (may be NULL) = valid_ref_sites of every row. */
+int uvg_ball_push_refs(uvg_ball* b, const uint8_t* text, int64_t n, int32_t min_non_n, uint8_t* keep, int32_t* non_n_out);
+
 /* ---- bench / test utilities (not part of the reference seam) ---- */
 /* Device generator of SARS-CoV-2-shaped alignment rows (same model as uvaia_b200/synth.py; counter-based RNG keyed
  * by (seed, ordinal)).  clades = n_clades rows of nchar bytes (host).  Writes n rows for ordinals first.. into d_text. */

@@ -4,7 +4,7 @@
 REFS=$1; shift
 for v in "$@"; do
   if [ "$v" = "main" ]; then unset UVG_LIB; else export UVG_LIB=$PWD/uvaia_b200/lib_$v/libuvaia_b200.so; fi
-  python bench.py --refs $REFS --steps 3 --warmup 2 --no-e2e --no-cpu > gpurun_out/var_$v.json 2> gpurun_out/var_$v.err
+  timeout 180 python bench.py --refs $REFS --steps 3 --warmup 2 --no-e2e --no-cpu > gpurun_out/var_$v.json 2> gpurun_out/var_$v.err
   python - "$v" <<'PY'
 import json,sys
 v=sys.argv[1]

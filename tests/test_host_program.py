@@ -188,3 +188,31 @@ def test_host_program_parallel_parser_on_raw_files(name, tmp_path):
     assert lzma.open(prefix + ".csv.xz", "rb").read().decode() == c.expected_csv
     aln = read_fasta_text(lzma.open(prefix + ".aln.xz", "rb").read())
     assert [r[0].encode() for r in aln] == c.expected_aln_names
+
+
+# ---- `uvaia_b200 ball`: the radius search program (src/ball.c) ----
+from test_oracle_ball import BallCase, ball_case_names  # noqa: E402
+
+
+def test_ball_mode_usage():
+    p = run(["ball", "--help"])
+    assert p.returncode == 0 and b"--distance" in p.stdout
+    assert run(["ball"]).returncode == 1
+    assert run(["ball", "-r", "/nonexistent/r.fa", "/nonexistent/q.fa"]).returncode == 1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ball_case_names())
+def test_host_program_ball_mode_reproduces_uvaiaball(name, tmp_path):
+    c = BallCase(name)
+    args = ["ball"] + list(c.args)
+    for rf in c.ref_files:
+        args += ["-r", rf]
+    prefix = str(tmp_path / "ball")
+    p = run(args + ["-o", prefix, "--batch", "301", c.query_file])
+    assert p.returncode == 0, p.stderr.decode(errors="replace")[-2000:]
+    aln = read_fasta_text(lzma.open(prefix + ".aln.xz", "rb").read())
+    assert [r[0].encode() for r in aln] == c.expected
+    for ln in c.meta.get("reference_stderr", []):
+        if "Query database now composed" in ln:
+            assert ln.strip().encode() in p.stderr             # same query set after the pruning

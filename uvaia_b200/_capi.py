@@ -25,6 +25,11 @@ class uvg_params(C.Structure):
                 ("pair_kernel", C.c_int32), ("closed_form", C.c_int32), ("db_capacity", C.c_int64)]
 
 
+class uvg_ball_params(C.Structure):
+    _fields_ = [("abi_version", C.c_int32), ("nchar", C.c_int32), ("trim", C.c_int32), ("dist", C.c_int32),
+                ("acgt_mode", C.c_int32), ("device", C.c_int32)]
+
+
 class uvg_query_info(C.Structure):
     _fields_ = [("n_query", C.c_int32), ("nchar", C.c_int32), ("trim", C.c_int32),
                 ("n_idx", C.c_int32), ("n_idx_m", C.c_int32), ("n_idx_c", C.c_int32)]
@@ -69,6 +74,12 @@ SYMBOLS = {
     "uvg_nccl_unique_id": (C.c_int, [_P]),
     "uvg_nccl_init": (C.c_int, [_P, _P]),
     "uvg_set_global_count": (C.c_int, [_P, C.c_int64]),
+    "uvg_ball_create": (C.c_int, [C.POINTER(uvg_ball_params), C.POINTER(_P)]),
+    "uvg_ball_destroy": (None, [_P]),
+    "uvg_ball_last_error": (C.c_char_p, [_P]),
+    "uvg_ball_radius": (C.c_int32, [_P]),
+    "uvg_ball_set_queries": (C.c_int, [_P, _P, C.c_int32, C.POINTER(uvg_query_info)]),
+    "uvg_ball_push_refs": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P, _P]),
     "uvg_synth_rows_device": (C.c_int, [_P, _P, C.c_int32, C.c_uint64, C.c_int64, C.c_int64, C.c_double, C.c_double, _P]),
     "uvg_device_alloc": (_P, [_P, C.c_size_t]),
     "uvg_device_free": (None, [_P, _P]),

@@ -50,6 +50,12 @@ constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(ui
 #ifndef PIVOT_LAG
 #define PIVOT_LAG 3
 #endif
+#ifndef PIVOT_GRANULE
+#define PIVOT_GRANULE 0         // bytes per bulk copy of the reference side of a stage (0 = one copy of 4.5 KB)
+#endif
+#ifndef PIVOT_POLL
+#define PIVOT_POLL 0            // 1: the producer thread never blocks on a stage that is still in use: it tests, and retries after its next chunk
+#endif
 constexpr int REFILL_LAG = PIVOT_LAG;
 constexpr int QW2 = PIVOT_QW;                           // query slots per warp (register tile QW2 x RPL pairs per lane)
 constexpr int PIVOT_THREADS = PIVOT_WARPS * 32;
@@ -82,7 +88,14 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         const uint32_t bar = full_a + (uint32_t)s * 8u, dst = stage_a + (uint32_t)s * (uint32_t)sizeof(Stage2);
         mbar_expect_tx_a(bar, (o1 - o0) + (uint32_t)CHUNK2_STAGED);
         bulk_g2s_a(dst, p.qstream + o0, o1 - o0, bar);
+#if PIVOT_GRANULE == 0
         bulk_g2s_a(dst + (uint32_t)QREC_MAX, rsrc + (size_t)c * CHUNK2_BYTES, (uint32_t)CHUNK2_STAGED, bar);
+#else
+        static_assert(CHUNK2_STAGED % PIVOT_GRANULE == 0 && PIVOT_GRANULE % 16 == 0, "granule");
+#pragma unroll
+        for (int k = 0; k < CHUNK2_STAGED / PIVOT_GRANULE; ++k)
+            bulk_g2s_a(dst + (uint32_t)QREC_MAX + k * PIVOT_GRANULE, rsrc + (size_t)c * CHUNK2_BYTES + k * PIVOT_GRANULE, (uint32_t)PIVOT_GRANULE, bar);
+#endif
     };
     if (warp == 0) {
         // the offsets of the first records in one go (lane = record), then lane 0 fills the ring
@@ -103,6 +116,9 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
 #pragma unroll
         for (int j = 0; j < QW2; ++j) { oV[g][j] = 0; oM[g][j] = 0; acc[g][j] = 0; }
 
+#if PIVOT_POLL
+    int cn_poll = STAGES2;                                                   // producer thread: next chunk to issue
+#endif
     int s = 0;                                                               // stage of chunk c = c % STAGES2, ph = (c / STAGES2) & 1
     uint32_t ph = 0;
     for (int c = 0; c < p.n_chunks; ++c) {
@@ -164,6 +180,26 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         if (lane == 0) {
             mbar_arrive_a(empty_a + (uint32_t)s * 8u);
             if (warp == 0) {
+#if PIVOT_POLL
+                // refill every stage that all warps have released, in order, without ever blocking: what is still in use is
+                // retried after the next chunk (warp 0 is not tethered to the slowest warp of the block)
+                while (cn_poll < p.n_chunks && cn_poll - STAGES2 <= c) {
+                    const int cr = cn_poll - STAGES2, sr = cr % STAGES2;
+                    if (!mbar_test_a(empty_a + (uint32_t)sr * 8u, (uint32_t)((cr / STAGES2) & 1))) break;
+                    const uint32_t o1 = __ldg(qoff + cn_poll + 1);
+                    issue_at(cn_poll, sr, o_next, o1);
+                    o_next = o1;
+                    ++cn_poll;
+                }
+                if (cn_poll < p.n_chunks && cn_poll == c + 1) {               // this warp's own next chunk is not on its way: now it has to wait
+                    const int cr = cn_poll - STAGES2, sr = cr % STAGES2;
+                    const uint32_t o1 = __ldg(qoff + cn_poll + 1);
+                    mbar_wait_a(empty_a + (uint32_t)sr * 8u, (uint32_t)((cr / STAGES2) & 1));
+                    issue_at(cn_poll, sr, o_next, o1);
+                    o_next = o1;
+                    ++cn_poll;
+                }
+#else
                 const int cr = c - REFILL_LAG, cn = cr + STAGES2;
                 if (cr >= 0 && cn < p.n_chunks) {
                     const int sr = s >= REFILL_LAG ? s - REFILL_LAG : s - REFILL_LAG + STAGES2;
@@ -172,6 +208,7 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
                     issue_at(cn, sr, o_next, o1);
                     o_next = o1;
                 }
+#endif
             }
         }
         __syncwarp();

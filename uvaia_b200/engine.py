@@ -36,6 +36,59 @@ def prune_queries(text: np.ndarray, trim=0, acgt=False, keep_more_resolved=True)
     return keep.astype(bool)
 
 
+class Ball:
+    """uvaiaball on the GPU (uvg_ball_*, csrc/ball.cu): which reference rows are within `dist` differences of some query"""
+
+    def __init__(self, nchar, dist=5, trim=0, acgt=False, device=0):
+        self._lib = _capi.lib()
+        p = _capi.uvg_ball_params(_capi.UVG_ABI_VERSION, int(nchar), int(trim), int(dist), int(bool(acgt)), int(device))
+        h = C.c_void_p()
+        rc = self._lib.uvg_ball_create(C.byref(p), C.byref(h))
+        if rc != 0:
+            raise UvgError(f"uvg_ball_create failed ({rc}): {self._lib.uvg_ball_last_error(None).decode()}")
+        self._h = h
+        self.nchar = int(nchar)
+        self.dist = int(self._lib.uvg_ball_radius(h))
+
+    def _ck(self, rc, what):
+        if rc != 0:
+            raise UvgError(f"{what} failed ({rc}): {self._lib.uvg_ball_last_error(self._h).decode()}")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.uvg_ball_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_queries(self, text: np.ndarray):
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        assert text.ndim == 2 and text.shape[1] == self.nchar
+        info = _capi.uvg_query_info()
+        self._ck(self._lib.uvg_ball_set_queries(self._h, text.ctypes.data, text.shape[0], C.byref(info)), "uvg_ball_set_queries")
+        return info
+
+    def push_refs(self, text: np.ndarray, min_non_n=0):
+        """-> (keep uint8[n]: 0 too ambiguous / 1 outside / 2 inside the ball, non_n int32[n])"""
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        n = text.shape[0]
+        keep, nn = np.zeros(n, np.uint8), np.zeros(n, np.int32)
+        if n:
+            assert text.ndim == 2 and text.shape[1] == self.nchar
+            self._ck(self._lib.uvg_ball_push_refs(self._h, text.ctypes.data, n, int(min_non_n), keep.ctypes.data, nn.ctypes.data), "uvg_ball_push_refs")
+        return keep, nn
+
+
 class Engine:
     def __init__(self, nchar, nbest=100, trim=0, acgt=False, pool=512, device=0, first_round=0, max_round=0,
                  early_abort=False, rank=0, world=1, db_capacity=0, pair_kernel=None, closed_form=False):

@@ -125,6 +125,53 @@ class SearchOutput:
         return "\n".join(out) + "\n"
 
 
+def ball_files(query_file, ref_files, dist=5, trim=0, acgt=False, ambig_q=0.5, ambig_r=0.5, keep_more_resolved=False, batch_rows=4096, device=0):
+    """End-to-end `uvaiaball` run (ball.c:138-291) with the distances on the GPU.  -> (names of the references kept, in file
+    order; number too ambiguous)"""
+    from .engine import Ball
+    ambig_q = min(1.0, max(0.001, ambig_q))                     # ball.c:154-157
+    ambig_r = min(1.0, max(0.001, ambig_r))
+    recs = list(iter_fasta(query_file))
+    qn, qs = [r[0] for r in recs], [r[1] for r in recs]
+    keep = filter_queries(qs, ambig_q)
+    if not keep:
+        raise ValueError("no valid query sequences")
+    Q = np.frombuffer(b"".join(qs[i] for i in keep), np.uint8).reshape(len(keep), -1)
+    L = Q.shape[1]
+    t = clamp_trim(trim, L)
+    Q = np.ascontiguousarray(Q[query_order(Q, t, acgt)])
+    Q = np.ascontiguousarray(Q[prune_queries(Q, trim, acgt, keep_more_resolved)])       # ball.c:190: always, -k picks the side
+    min_non_n = int(L * ambig_r)                                # ball.c:201 (A, not 1 - A)
+    kept, n_invalid = [], 0
+    with Ball(L, dist=dist, trim=trim, acgt=acgt, device=device) as ball:
+        ball.set_queries(Q)
+        for rf in ref_files:
+            names, rows = [], []
+
+            def flush():
+                nonlocal n_invalid
+                if not rows:
+                    return
+                text = np.frombuffer(b"".join(rows), np.uint8).reshape(len(rows), L)
+                k, _ = ball.push_refs(text, min_non_n)
+                kept.extend(nm for nm, x in zip(names, k) if x == 2)
+                n_invalid += int((k == 0).sum())
+                names.clear(); rows.clear()
+
+            for nm, sq in iter_fasta(rf):
+                if len(sq) != L:
+                    # ball.c:216-231: a poor-quality reference of the wrong length is skipped, a good one is fatal
+                    if int(_VALIDTXT[np.frombuffer(sq, np.uint8)].sum()) < min_non_n:
+                        n_invalid += 1
+                        continue
+                    raise ValueError("all sequences must be aligned")
+                names.append(nm); rows.append(sq)
+                if len(rows) >= batch_rows:
+                    flush()
+            flush()
+    return kept, n_invalid
+
+
 def search_files(query_file, ref_files, nbest=100, trim=0, acgt=False, ambig_q=0.5, ambig_r=0.5, pool=512, exclude_self=False,
                  keep_resolved=False, batch_rows=4096, device=0, **engine_kw):
     """End-to-end `uvaia` run (nearest.c:159-353) with scoring and heaps on the GPU.  Returns a SearchOutput."""
