@@ -67,9 +67,11 @@ constexpr int CHUNK2_PLANES = RPL * W4 * UNIT2_PLANES;               // 4 KB
 constexpr int CHUNK2_COUNTS = RPL * W4 * GROUP * 4;                  // 512 B
 constexpr int CHUNK2_STAGED = CHUNK2_PLANES + CHUNK2_COUNTS;         // what a ring stage holds of a chunk record
 constexpr int CHUNK2_BYTES = CHUNK2_STAGED + RPL * W4 * UNIT2_MASKS; // 12.5 KB per (pair of groups, chunk)
-constexpr int PIVOT_QW = 4;                                          // query slots per warp of k_pairpivot
-constexpr int PIVOT_WARPS = QTILE / PIVOT_QW;
-// Query side of the pivot form: per (query tile, chunk) one variable-length record of a byte stream (PairParams::qstream,
+constexpr int PIVOT_QW = 4;                                          // query slots per counting warp of k_pairpivot
+constexpr int PIVOT_WARPS = 16;                                      // warp 0 only fills the staging ring, warps 1..15 count
+constexpr int PIVOT_SLOTS = (PIVOT_WARPS - 1) * PIVOT_QW;            // 60 query slots per thread block ("pivot tile"): consecutive slots,
+                                                                     // independent of the 64-slot tiles that own the score rows
+// Query side of the pivot form: per (pivot tile of 60 slots, chunk) one variable-length record of a byte stream (PairParams::qstream,
 // offsets in PairParams::qoff), staged by one TMA bulk copy of exactly its size:
 //     QWarpHead head[16 warps]                          what each warp has to do in the chunk
 //     uint4     item[n]                                 per half (64 sites) that is counted from the planes: words 2h, 2h+1 of the
@@ -92,7 +94,7 @@ constexpr int QREC_MAX = QHEAD_BYTES + QITEMS_MAX * 16;              // 4224: wh
 // the same base there is one more match.  These "fix" entries (~the SNPs of the query, a few dozen per genome) are resolved
 // after the main loop against the column masks of the derived database: entry = chunk << 16 | unit << 9 | word << 7 |
 // base (A,C,G,T) << 5 | site in word; per slot a range of PairParams::snp_ent.
-static_assert(W4 == 2 && PIVOT_WARPS == 16 && sizeof(QWarpHead) == 8, "QWarpHead bit layout");
+static_assert(W4 == 2 && PIVOT_WARPS == 16 && sizeof(QWarpHead) == 8 && PIVOT_SLOTS <= QTILE, "QWarpHead bit layout");
 __host__ __device__ inline size_t db2_chunk_bytes(int64_t group, int unit, int Wp)        // record of the chunk that holds (group, unit)
 {
     return ((size_t)(group / RPL) * (size_t)(Wp / WC) + (size_t)(unit / W4)) * CHUNK2_BYTES;
@@ -142,8 +144,8 @@ struct PairParams {
     const int32_t*   rb_cnt;      // per local reference: popcount of its base plane (all words)
     const int32_t*   mc_cnt;      //                      popcount of its mc plane
     const uint8_t*   qstream;     // records of every (query tile, chunk), see QWarpHead
-    const uint32_t*  qoff;        // [n_qtiles][n_chunks + 1] byte offsets of the records (multiples of 16)
-    const uint8_t*   wslot;       // [n_qtiles][PIVOT_WARPS][PIVOT_QW]: which slots of the tile each warp counts (balanced by work)
+    const uint32_t*  qoff;        // [n_ptiles][n_chunks + 1] byte offsets of the records (multiples of 16)
+    const uint8_t*   wslot;       // [n_ptiles][PIVOT_WARPS][PIVOT_QW]: which slots of the pivot tile each warp counts (balanced by work; 0xff: none)
     const uint32_t*  snp_off;     // [n_slots + 1] fix entries of every slot: plain bases that differ from the pivot
     const uint32_t*  snp_ent;
     const uint32_t*  ramb_off;    // [local refs + 1] ambiguity entries of the references
@@ -151,6 +153,7 @@ struct PairParams {
     const int32_t*   non_n;       // per local reference
     int32_t qnib_stride;
     int32_t Wp, n_chunks, n_qtiles;
+    int32_t n_ptiles;             // pivot tiles: ceil(n_slots / PIVOT_SLOTS)
     int32_t n_slots;              // real queries + 1: the last slot is the consensus pseudo-query (nearest.c:428-433)
     int64_t local_begin, local_end;   // local reference range of this launch
     // dense score tile(s): slot q of query tile qt goes to rank (qt % world), row (qt / world) * QTILE + q % QTILE; the

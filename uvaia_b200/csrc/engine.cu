@@ -78,6 +78,7 @@ struct uvg_ctx {
     cudaEvent_t ev_pair[NBUF]{}, ev_replay[NBUF]{}, ev_ag[NBUF]{};
     // queries
     int n_query = 0, n_slots = 0, n_qtiles = 0, rows_cap = 0, qnib_stride = 0;
+    int n_ptiles = 0;                                 // pivot form: thread-block tiles of PIVOT_SLOTS = 60 slots
     uvg_query_info qinfo{};
     int64_t qinfo_pivot_fix = -1;
     double set_queries_host_ms = 0, set_queries_device_ms = 0;                     // fix entries of the pivot form (-1: general kernel)
@@ -595,35 +596,37 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
                         }
                 }
         });
-        // Which 4 slots of a tile a warp counts: the warps of a block share one staging ring, so the block runs at the pace
-        // of the warp with the most work.  Longest-processing-time first: slots by decreasing work, each to the least
-        // loaded warp that still has room.
-        wslot.assign((size_t)c->n_qtiles * QTILE, 0);
-        for (int qt = 0; qt < c->n_qtiles; ++qt) {
-            int order[QTILE];
-            for (int i = 0; i < QTILE; ++i) order[i] = i;
-            const uint32_t* wk = &work[(size_t)qt * QTILE];
-            std::stable_sort(order, order + QTILE, [&](int x, int y) { return wk[x] > wk[y]; });
+        // Pivot tiles: a thread block takes PIVOT_SLOTS = 60 consecutive slots; warp 0 only fills the staging ring (measured: a
+        // warp that issues the TMA copies on top of its counting work sets the pace of the block and the others wait for it),
+        // warps 1..15 count 4 slots each.  Which 4: the warps share one ring, so the block runs at the pace of the warp with the
+        // most work -- longest-processing-time first: slots by decreasing work, each to the least loaded warp that has room.
+        const int n_ptiles = (c->n_slots + PIVOT_SLOTS - 1) / PIVOT_SLOTS;
+        c->n_ptiles = n_ptiles;
+        wslot.assign((size_t)n_ptiles * PIVOT_WARPS * PIVOT_QW, 0xff);
+        for (int pt = 0; pt < n_ptiles; ++pt) {
+            int order[PIVOT_SLOTS], n_here = std::min(PIVOT_SLOTS, c->n_slots - pt * PIVOT_SLOTS);
+            for (int i = 0; i < n_here; ++i) order[i] = i;
+            const uint32_t* wk = &work[(size_t)pt * PIVOT_SLOTS];
+            std::stable_sort(order, order + n_here, [&](int x, int y) { return wk[x] > wk[y]; });
             uint64_t load[PIVOT_WARPS] = {0}; int cnt[PIVOT_WARPS] = {0};
-            for (int i = 0; i < QTILE; ++i) {
+            for (int i = 0; i < n_here; ++i) {
                 int best = -1;
-                for (int w = 0; w < PIVOT_WARPS; ++w) if (cnt[w] < PIVOT_QW && (best < 0 || load[w] < load[best])) best = w;
-                wslot[(size_t)qt * QTILE + best * PIVOT_QW + cnt[best]++] = (uint8_t)order[i];
+                for (int w = 1; w < PIVOT_WARPS; ++w) if (cnt[w] < PIVOT_QW && (best < 0 || load[w] < load[best])) best = w;
+                wslot[((size_t)pt * PIVOT_WARPS + best) * PIVOT_QW + cnt[best]++] = (uint8_t)order[i];
                 load[best] += wk[order[i]];
             }
         }
-        // the stream: per (tile, chunk) the 16 warp heads, then the items of warp 0, warp 1, ... in the order the kernel walks
-        // them (unit, slot of the warp, half).  Tiles are built in parallel, then concatenated.
-        std::vector<std::vector<uint8_t>> tile_rec(c->n_qtiles);
-        std::vector<std::vector<uint32_t>> tile_off(c->n_qtiles);
-        std::vector<int64_t> tile_halves(c->n_qtiles, 0);
-        parallel_ranges(c->n_qtiles, host_threads(c->n_qtiles), [&](int, int ta, int tb) {
-            for (int qt = ta; qt < tb; ++qt) {
-                std::vector<uint8_t>& rec = tile_rec[qt];
-                std::vector<uint32_t>& off = tile_off[qt];
+        // the stream: per (pivot tile, chunk) the 16 warp heads, then the items of warp 1, warp 2, ... in the order the kernel
+        // walks them (unit, slot of the warp, half).  Tiles are built in parallel, then concatenated.
+        std::vector<std::vector<uint8_t>> tile_rec(n_ptiles);
+        std::vector<std::vector<uint32_t>> tile_off(n_ptiles);
+        std::vector<int64_t> tile_halves(n_ptiles, 0);
+        parallel_ranges(n_ptiles, host_threads(n_ptiles), [&](int, int ta, int tb) {
+            for (int pt = ta; pt < tb; ++pt) {
+                std::vector<uint8_t>& rec = tile_rec[pt];
+                std::vector<uint32_t>& off = tile_off[pt];
                 off.reserve(c->n_chunks + 1);
                 for (int ch = 0; ch < c->n_chunks; ++ch) {
-                    const HostPlanes2& blk = qd2[(size_t)qt * c->n_chunks + ch];
                     off.push_back((uint32_t)rec.size());
                     const size_t h0 = rec.size();
                     rec.resize(h0 + QHEAD_BYTES, 0);
@@ -633,10 +636,12 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
                         hd.item0 = (uint16_t)n_items;
                         for (int u = 0; u < W4; ++u)
                             for (int j = 0; j < PIVOT_QW; ++j) {
-                                const int qi = wslot[(size_t)qt * QTILE + wp * PIVOT_QW + j];
-                                if (qt * QTILE + qi >= c->n_slots) continue;
-                                const uint4& e = blk.pl[u][qi][1];
-                                const uint4& b = blk.pl[u][qi][0];
+                                const int sl = wslot[((size_t)pt * PIVOT_WARPS + wp) * PIVOT_QW + j];
+                                if (sl == 0xff) continue;
+                                const int q = pt * PIVOT_SLOTS + sl;                         // global slot; its planes live in the 64-slot tile q / QTILE
+                                const HostPlanes2& blk = qd2[(size_t)(q / QTILE) * c->n_chunks + ch];
+                                const uint4& e = blk.pl[u][q % QTILE][1];
+                                const uint4& b = blk.pl[u][q % QTILE][0];
                                 if ((b.x & b.y & b.z & b.w) == 0xffffffffu) { hd.fulln |= (uint8_t)(1u << (u * 4 + j)); continue; }
                                 const uint32_t bw[4] = {b.x, b.y, b.z, b.w}, ew[4] = {e.x, e.y, e.z, e.w};
                                 for (int h = 0; h < 2; ++h) {
@@ -650,18 +655,18 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
                             }
                         memcpy(&rec[h0 + (size_t)wp * sizeof(QWarpHead)], &hd, sizeof hd);
                     }
-                    tile_halves[qt] += n_items;
+                    tile_halves[pt] += n_items;
                 }
                 off.push_back((uint32_t)rec.size());
             }
         });
         int64_t halves_total = 0;
         size_t total = 0;
-        for (int qt = 0; qt < c->n_qtiles; ++qt) { total += tile_rec[qt].size(); halves_total += tile_halves[qt]; }
-        if (total > 0xfffffff0ull) pivot_ok = false;                        // offsets are 32 bits (never reached: 16 tiles ~ 1.5 MB)
+        for (int qt = 0; qt < n_ptiles; ++qt) { total += tile_rec[qt].size(); halves_total += tile_halves[qt]; }
+        if (total > 0xfffffff0ull) pivot_ok = false;                        // offsets are 32 bits (never reached: 17 tiles ~ 1.5 MB)
         qstream.reserve(total);
-        qoff.reserve((size_t)c->n_qtiles * (c->n_chunks + 1));
-        for (int qt = 0; qt < c->n_qtiles && pivot_ok; ++qt) {
+        qoff.reserve((size_t)n_ptiles * (c->n_chunks + 1));
+        for (int qt = 0; qt < n_ptiles && pivot_ok; ++qt) {
             const uint32_t base = (uint32_t)qstream.size();
             for (uint32_t o : tile_off[qt]) qoff.push_back(base + o);
             qstream.insert(qstream.end(), tile_rec[qt].begin(), tile_rec[qt].end());
@@ -704,9 +709,10 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
                 snp_ent.assign((size_t)(hdr[5] & 0xffffffffLL), 0u);
                 snp_off.assign(c->n_slots + 1, 0u);
                 qstream.assign((size_t)(hdr[5] >> 32), 0);
-                qoff.assign((size_t)c->n_qtiles * (c->n_chunks + 1), 0u);
+                c->n_ptiles = (c->n_slots + PIVOT_SLOTS - 1) / PIVOT_SLOTS;
+                qoff.assign((size_t)c->n_ptiles * (c->n_chunks + 1), 0u);
                 pivot_words.assign((size_t)(c->Wp / 4) * 8, 0u);
-                wslot.assign((size_t)c->n_qtiles * QTILE, 0);
+                wslot.assign((size_t)((c->n_slots + PIVOT_SLOTS - 1) / PIVOT_SLOTS) * PIVOT_WARPS * PIVOT_QW, 0);
             }
         }
     }
@@ -1341,7 +1347,7 @@ static void fill_pair_params(uvg_ctx* c, PairParams& pp, int64_t lb, int64_t le,
     pp.db2 = c->d_db2; pp.qstream = c->d_qstream; pp.qoff = c->d_qoff; pp.snp_off = c->d_snp_off; pp.snp_ent = c->d_snp_ent;
     pp.ramb_off = c->d_ramb_off; pp.ramb_ent = c->d_ramb_ent; pp.non_n = c->d_non_n;
     pp.qnib_stride = c->qnib_stride;
-    pp.Wp = c->Wp; pp.n_chunks = c->n_chunks; pp.n_qtiles = c->n_qtiles; pp.n_slots = c->n_slots;
+    pp.Wp = c->Wp; pp.n_chunks = c->n_chunks; pp.n_qtiles = c->n_qtiles; pp.n_slots = c->n_slots; pp.n_ptiles = c->n_ptiles;
     pp.local_begin = lb; pp.local_end = le;
     for (int r = 0; r < c->world; ++r) pp.out[r] = c->peer_tiles[r] + (size_t)buf * c->tile_elems;
     pp.row_stride = (int64_t)c->world * c->seg_cap; pp.col0 = col0;

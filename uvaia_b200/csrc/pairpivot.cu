@@ -22,11 +22,14 @@
 // every warp resolves the fix entries of its four slots against the column masks of the derived database (per site and base
 // one word: bit l = reference l of the group holds that base): loads for 32 entries at a time, all independent.  Ambiguity
 // codes go through the shared epilogue (pair_epilogue.cuh).
-// Shape: block = 64 query slots x 64 references, 16 warps x 4 slots, lane = 2 references, 64 registers, 2 blocks per
-// SM (32 warps per SM).  Staging: a ring of STAGES2 stages, each filled by two TMA bulk copies -- the (tile, chunk) record of
-// the query stream (variable length: 128-byte head + 16 bytes per counted half, ~0.8 KB on average) and the planes + counts
-// of the pair's chunk record (4.5 KB) -- with full/empty mbarriers (no __syncthreads in the loop: warps drift up to the ring
-// depth apart); one elected thread refills a stage PIVOT_LAG chunks after it was consumed.
+// Shape: block = 60 query slots ("pivot tile") x 64 references, 16 warps: warp 0 is the PRODUCER (it keeps the staging ring
+// full and counts nothing), warps 1..15 count 4 slots each, lane = 2 references; 64 registers, 2 blocks per SM.  Staging: a
+// ring of STAGES2 stages, each filled by two TMA bulk copies -- the (pivot tile, chunk) record of the query stream (variable
+// length: 128-byte head + 16 bytes per counted half, ~0.8 KB on average) and the planes + counts of the pair's chunk record
+// (4.5 KB) -- with full/empty mbarriers (no __syncthreads in the loop: warps drift up to the ring depth apart).  Why a warp
+// that only produces: a bulk copy costs its issuing warp ~200 cycles; a warp that issued the copies on top of an equal share
+// of the counting set the pace of the block, and the other fifteen waited for it at the head of the ring (r02 profile: 20 %
+// of all warp time in the full-barrier wait; rotating the duty among the warps was 1.6x slower still).
 #include "common.cuh"
 #include "kernels.h"
 #include "pair_epilogue.cuh"
@@ -46,20 +49,13 @@ struct __align__(16) Stage2 {
     uint32_t   cnt[RPL][W4][GROUP];      // unit totals of every reference: popc(mc) | popc(base) << 16
 };
 static_assert(sizeof(RefPlanes2) * RPL * W4 == CHUNK2_PLANES && sizeof(Stage2) == QREC_MAX + CHUNK2_STAGED, "ring stage");
-constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(uint64_t);
-#ifndef PIVOT_LAG
-#define PIVOT_LAG 3
-#endif
+constexpr int PIVOT_MAX_CHUNKS = 256;                                  // < 65,536 columns
+constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(uint64_t) + (PIVOT_MAX_CHUNKS + 4) * sizeof(uint32_t);
 #ifndef PIVOT_GRANULE
-#define PIVOT_GRANULE 0         // bytes per bulk copy of the reference side of a stage (0 = one copy of 4.5 KB)
+#define PIVOT_GRANULE 0         // bytes per bulk copy of the reference side of a stage (0 = one copy of 4.5 KB; smaller copies measured slower)
 #endif
-#ifndef PIVOT_POLL
-#define PIVOT_POLL 0            // 1: the producer thread never blocks on a stage that is still in use: it tests, and retries after its next chunk
-#endif
-constexpr int REFILL_LAG = PIVOT_LAG;
 constexpr int QW2 = PIVOT_QW;                           // query slots per warp (register tile QW2 x RPL pairs per lane)
 constexpr int PIVOT_THREADS = PIVOT_WARPS * 32;
-static_assert(REFILL_LAG >= 0 && REFILL_LAG < STAGES2, "refill lag");
 
 __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams p, const uint32_t k2, const uint32_t k128k)
 {
@@ -67,23 +63,24 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     Stage2* stage = reinterpret_cast<Stage2*>(smem);
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int qt = blockIdx.x % p.n_qtiles;
-    const int64_t group0 = (p.local_begin / (GROUP * RPL) + blockIdx.x / p.n_qtiles) * RPL;
-    const uint32_t* qoff = p.qoff + (size_t)qt * (p.n_chunks + 1);
+    const int pt = blockIdx.x % p.n_ptiles;                                  // pivot tile: slots [pt * 60, pt * 60 + 60)
+    const int64_t group0 = (p.local_begin / (GROUP * RPL) + blockIdx.x / p.n_ptiles) * RPL;
+    const uint32_t* qoff = p.qoff + (size_t)pt * (p.n_chunks + 1);
     const uint8_t* rsrc = p.db2 + (size_t)(group0 / RPL) * (size_t)p.n_chunks * CHUNK2_BYTES;      // chunk records of this block's pair of groups
-    const int owner = qt % p.world, row0 = (qt / p.world) * QTILE;
     // shared-memory addresses as plain integers: nothing in the loop goes through a generic -> shared conversion
     uint32_t stage_a = smem_u32(stage);
     asm volatile("mov.u32 %0, %0;" : "+r"(stage_a));                         // opaque: kept in a register instead of being re-derived (S2R + LEA) per use
     const uint32_t full_a = stage_a + (uint32_t)(STAGES2 * sizeof(Stage2)), empty_a = full_a + STAGES2 * 8u;
+    // offsets of the tile's records in shared memory: the producer thread must not wait for a global load per chunk
+    uint32_t* s_qoff = reinterpret_cast<uint32_t*>(smem + STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(uint64_t));
+    for (int i = threadIdx.x; i <= p.n_chunks; i += PIVOT_THREADS) s_qoff[i] = __ldg(qoff + i);
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES2; ++s) { mbar_init_a(full_a + s * 8u, 1); mbar_init_a(empty_a + s * 8u, PIVOT_THREADS / 32); }
+        for (int s = 0; s < STAGES2; ++s) { mbar_init_a(full_a + s * 8u, 1); mbar_init_a(empty_a + s * 8u, PIVOT_WARPS - 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
     // one stage = the query record of the chunk (exactly its bytes) + planes and counts of the pair's chunk record
-    uint32_t o_next = 0;                                                     // producer thread: offset of the record to issue next
     auto issue_at = [&](int c, int s, uint32_t o0, uint32_t o1) {
         const uint32_t bar = full_a + (uint32_t)s * 8u, dst = stage_a + (uint32_t)s * (uint32_t)sizeof(Stage2);
         mbar_expect_tx_a(bar, (o1 - o0) + (uint32_t)CHUNK2_STAGED);
@@ -97,15 +94,8 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
             bulk_g2s_a(dst + (uint32_t)QREC_MAX + k * PIVOT_GRANULE, rsrc + (size_t)c * CHUNK2_BYTES + k * PIVOT_GRANULE, (uint32_t)PIVOT_GRANULE, bar);
 #endif
     };
-    if (warp == 0) {
-        // the offsets of the first records in one go (lane = record), then lane 0 fills the ring
-        static_assert(STAGES2 < 32, "one lane per prologue offset");
-        const uint32_t mine = lane <= min(STAGES2, p.n_chunks) ? __ldg(qoff + lane) : 0u;
-#pragma unroll
-        for (int s = 0; s < STAGES2; ++s) {
-            const uint32_t o0 = __shfl_sync(0xffffffffu, mine, s), o1 = __shfl_sync(0xffffffffu, mine, s + 1);
-            if (lane == 0 && s < p.n_chunks) { issue_at(s, s, o0, o1); o_next = o1; }
-        }
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES2 && s < p.n_chunks; ++s) issue_at(s, s, s_qoff[s], s_qoff[s + 1]);
     }
 
     // per pair: carry-save "ones" registers of the two complement streams and one packed counter
@@ -116,9 +106,19 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
 #pragma unroll
         for (int j = 0; j < QW2; ++j) { oV[g][j] = 0; oM[g][j] = 0; acc[g][j] = 0; }
 
-#if PIVOT_POLL
-    int cn_poll = STAGES2;                                                   // producer thread: next chunk to issue
-#endif
+    if (warp == 0) {
+        // ---- producer warp: keeps the ring full.  Chunk c goes into stage c % STAGES2 as soon as the fifteen counting warps
+        // have released what the stage held before; it has no slots of its own, so nobody ever waits for its counting work ----
+        if (lane == 0) {
+            int s = 0; uint32_t ph = 0;                                      // stage / phase of the chunk being issued
+            for (int c = STAGES2; c < p.n_chunks; ++c) {
+                mbar_wait_a(empty_a + (uint32_t)s * 8u, ph);                 // use c / STAGES2 - 1 of the stage is over
+                issue_at(c, s, s_qoff[c], s_qoff[c + 1]);
+                if (++s == STAGES2) { s = 0; ph ^= 1u; }
+            }
+        }
+        return;
+    }
     int s = 0;                                                               // stage of chunk c = c % STAGES2, ph = (c / STAGES2) & 1
     uint32_t ph = 0;
     for (int c = 0; c < p.n_chunks; ++c) {
@@ -174,58 +174,23 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
                 }
             }
         }
-        // release the stage; the elected thread refills the stage consumed REFILL_LAG chunks ago (everybody is done with it
-        // by now, or will be within a few hundred cycles)
+        // release the stage to the producer warp
         __syncwarp();
-        if (lane == 0) {
-            mbar_arrive_a(empty_a + (uint32_t)s * 8u);
-            if (warp == 0) {
-#if PIVOT_POLL
-                // refill every stage that all warps have released, in order, without ever blocking: what is still in use is
-                // retried after the next chunk (warp 0 is not tethered to the slowest warp of the block)
-                while (cn_poll < p.n_chunks && cn_poll - STAGES2 <= c) {
-                    const int cr = cn_poll - STAGES2, sr = cr % STAGES2;
-                    if (!mbar_test_a(empty_a + (uint32_t)sr * 8u, (uint32_t)((cr / STAGES2) & 1))) break;
-                    const uint32_t o1 = __ldg(qoff + cn_poll + 1);
-                    issue_at(cn_poll, sr, o_next, o1);
-                    o_next = o1;
-                    ++cn_poll;
-                }
-                if (cn_poll < p.n_chunks && cn_poll == c + 1) {               // this warp's own next chunk is not on its way: now it has to wait
-                    const int cr = cn_poll - STAGES2, sr = cr % STAGES2;
-                    const uint32_t o1 = __ldg(qoff + cn_poll + 1);
-                    mbar_wait_a(empty_a + (uint32_t)sr * 8u, (uint32_t)((cr / STAGES2) & 1));
-                    issue_at(cn_poll, sr, o_next, o1);
-                    o_next = o1;
-                    ++cn_poll;
-                }
-#else
-                const int cr = c - REFILL_LAG, cn = cr + STAGES2;
-                if (cr >= 0 && cn < p.n_chunks) {
-                    const int sr = s >= REFILL_LAG ? s - REFILL_LAG : s - REFILL_LAG + STAGES2;
-                    const uint32_t o1 = __ldg(qoff + cn + 1);                  // in flight while the stage drains
-                    mbar_wait_a(empty_a + (uint32_t)sr * 8u, s >= REFILL_LAG ? ph : ph ^ 1u);
-                    issue_at(cn, sr, o_next, o1);
-                    o_next = o1;
-                }
-#endif
-            }
-        }
-        __syncwarp();
+        if (lane == 0) mbar_arrive_a(empty_a + (uint32_t)s * 8u);
         if (++s == STAGES2) { s = 0; ph ^= 1u; }
     }
 
     // ---- fix entries: plain bases of the warp's slots that differ from the pivot.  A reference that holds the same base there
     // is one more match.  Lane = entry for the loads of the column masks (32 independent loads per slot and group, L2 hits or
     // the 8 KB mask part of the chunk records), then the non-zero masks are broadcast lane by lane. ----
-    const uint8_t* ws = p.wslot + ((size_t)qt * PIVOT_WARPS + warp) * QW2;
+    const uint8_t* ws = p.wslot + ((size_t)pt * PIVOT_WARPS + warp) * QW2;      // slots of the pivot tile this warp counted (0xff: none)
     uint32_t fh[RPL][QW2];
 #pragma unroll
     for (int j = 0; j < QW2; ++j) {
 #pragma unroll
         for (int g = 0; g < RPL; ++g) fh[g][j] = 0;
-        const int slot = qt * QTILE + (int)ws[j];
-        if (slot >= p.n_slots) continue;
+        const int slot = pt * PIVOT_SLOTS + (int)ws[j];
+        if (ws[j] == 0xff || slot >= p.n_slots) continue;
         const uint32_t e1 = __ldg(p.snp_off + slot + 1);
         for (uint32_t e0 = __ldg(p.snp_off + slot); e0 < e1; e0 += 32) {
             const bool have = e0 + lane < e1;
@@ -256,17 +221,18 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     }
 #pragma unroll
     for (int j = 0; j < QW2; ++j) {
-        const int sjj = (int)ws[j];
-        const int slot = qt * QTILE + sjj;
-        if (slot >= p.n_slots) continue;
+        const int slot = pt * PIVOT_SLOTS + (int)ws[j];
+        if (ws[j] == 0xff || slot >= p.n_slots) continue;
         const bool is_cons = slot == p.n_slots - 1;
+        // the score rows belong to the 64-slot tiles of the search (owner rank, row inside the owner's score tile)
+        const int qt = slot / QTILE, owner = qt % p.world, row = (qt / p.world) * QTILE + slot % QTILE;
 #pragma unroll
         for (int g = 0; g < RPL; ++g) {
             if (!in_range[g]) continue;
             const int32_t M = p.mc_cnt[local[g]] - (int32_t)((acc[g][j] & 0xffffu) + __popc(oM[g][j])) + (int32_t)fh[g][j];
             const int32_t V = p.rb_cnt[local[g]] - (int32_t)((acc[g][j] >> 16) + __popc(oV[g][j]));
             const uint4 v = pair_epilogue_default(p, p.qamb_off, p.qamb_ent, slot, group0 + g, lane, local[g], M, V);
-            pair_store(p, owner, row0 + sjj, is_cons, local[g], v);
+            pair_store(p, owner, row, is_cons, local[g], v);
         }
     }
 }
@@ -338,8 +304,8 @@ cudaError_t launch_pairpivot(const PairParams& p, cudaStream_t st)
     if (p.local_end <= p.local_begin) return cudaSuccess;
     const int64_t per = GROUP * RPL;
     const int64_t g0 = p.local_begin / per, g1 = (p.local_end + per - 1) / per;
-    const int64_t blocks = (g1 - g0) * p.n_qtiles;
-    if (blocks > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
+    const int64_t blocks = (g1 - g0) * p.n_ptiles;
+    if (blocks > 0x7fffffffLL || p.n_chunks > PIVOT_MAX_CHUNKS) return cudaErrorInvalidConfiguration;
     // multipliers passed at run time so that the compiler keeps IMAD on the FMA pipe (no shift/add on the ALU pipe);
     // a carry word has weight 2: matches count 2 per set bit, valid sites 2 << 16
     k_pairpivot<<<(unsigned)blocks, PIVOT_THREADS, PIVOT_SMEM, st>>>(p, 2u, 2u << 16);

@@ -240,7 +240,8 @@ class Engine:
         buf = np.empty((self.n_query, self.K), dt)
         n = np.empty(self.n_query, np.int32)
         self._ck(self._lib.uvg_get_all_heaps(self._h, buf.ctypes.data, n.ctypes.data), "uvg_get_all_heaps")
-        return [(buf["score"][q, :n[q]].copy(), buf["ref"][q, :n[q]].copy()) for q in range(self.n_query)]
+        sc, rf = buf["score"], buf["ref"]                        # views into one buffer (no per-query copies)
+        return [(sc[q, :k], rf[q, :k]) for q, k in enumerate(n.tolist())]
 
     def ever_best(self, first, n):
         flags = np.zeros(int(n), np.uint8)
