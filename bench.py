@@ -70,6 +70,7 @@ def parse_args():
     ap.add_argument("--config", type=int, default=2, choices=[2, 3, 4, 5],
                     help="BASELINE.json configs[N-1] at its stated shape (default 2 = the metric's configuration; 1 = bundled data is a golden test, tests/golden/cases/real_c1_full)")
     ap.add_argument("--clades", type=int, default=200)
+    ap.add_argument("--closed-form", action="store_true", help="single GPU: pool-independent closed form + H1 flags instead of the literal --pool batches")
     a = ap.parse_args()
     given = {x.split("=")[0] for x in sys.argv[1:] if x.startswith("--")}
     preset = {2: {}, 3: {"queries": 10000, "refs": 5_000_000}, 4: {"ambiguous": 0.2},
@@ -333,7 +334,7 @@ def main():
     # --pool of the reference program on this box: 64 x omp_get_max_threads() (nearest.c:81); single GPU: the search emulates
     # those batches literally (hazard H1), sharded contexts run the pool-independent closed form and count the flags
     pool = 64 * (os.cpu_count() or 1)
-    eng = Engine(L, nbest=args.nbest, device=dev, first_round=first_round, max_round=max_round, early_abort=bool(args.early_abort), pool=pool,
+    eng = Engine(L, nbest=args.nbest, device=dev, first_round=first_round, max_round=max_round, early_abort=bool(args.early_abort), pool=pool, closed_form=bool(args.closed_form),
                  rank=rank, world=world, db_capacity=n_local,
                  pair_kernel={"auto": 0, "general": 1, "pivot": 2}[args.pair_kernel])
     qtext, qnames = make_queries(eng, clades, args.queries, L, args.ambiguous)
@@ -342,7 +343,7 @@ def main():
     base = {"metric": "queries_per_s_vs_%dk_db" % (R // 1000), "unit": "queries/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32 bit-planes / int32 counts",
             "data": "synthetic (device generator, seeds 1/1001/2002)",
-            "config": {"workload": workload, "nbest": args.nbest, "pool": pool, "h1": "literal --pool batches" if world == 1 else "closed form + flags", "early_abort": bool(args.early_abort), "sharding": "rows x%d" % world,
+            "config": {"workload": workload, "nbest": args.nbest, "pool": pool, "h1": "literal --pool batches" if world == 1 and not args.closed_form else "closed form + flags", "early_abort": bool(args.early_abort), "sharding": "rows x%d" % world,
                        "l2": "inputs larger than L2 (packed DB %.1f GB; the pivot form streams its derived planes, %.1f GB, once per pass)"
                              % (R * ((L + 255) // 256 * 256) * 3 / 8 / 1e9, R * ((L + 255) // 256 * 256) * 6 / 8 / 1e9)}}
 

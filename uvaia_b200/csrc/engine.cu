@@ -127,6 +127,9 @@ struct uvg_ctx {
     int64_t replay_seq = 0;                           // replay launches since the heaps were emptied
     std::vector<int64_t> file_starts{0};              // global ordinals at which a reference file starts (a batch ends with its file)
     uint32_t cons_amb_begin = 0, cons_amb_n = 0;      // ambiguity codes of the consensus slot inside d_qamb_ent
+    int64_t* d_bounds = nullptr; int64_t* h_bounds = nullptr; size_t bounds_cap = 0, bounds_used = 0;   // batch boundaries of the rounds enqueued since the heaps were emptied
+    uint8_t* d_snap_own = nullptr; int32_t* d_snap_batch = nullptr;         // speculation of a literal round: state at its start
+    uint8_t* d_ever_round = nullptr; unsigned long long* d_spec = nullptr;  //     admissions and counters (admitted, flags) of the speculative pass
     // round schedule
     int64_t rounds_done = 0, round_local_start = 0, round_global_start = 0;
     int32_t next_round = 0;
@@ -228,7 +231,7 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
     CK_(paircount_setup());
     CK_(pairpivot_setup());
     CK_(replay_setup(c->K));
-    CK_(cudaMalloc(&c->d_bstate, 32));
+    CK_(cudaMalloc(&c->d_bstate, 32)); CK_(cudaMalloc(&c->d_spec, 16));
     CK_(cudaMalloc(&c->d_counters, 64)); CK_(cudaMalloc(&c->d_nacc, 64)); CK_(cudaMalloc(&c->d_ipc, 64 * MAX_RANKS + 64));
     CK_(cudaMemset(c->d_counters, 0, 64));
     CK_(cudaMallocHost(&c->h_pinned, 2048));
@@ -271,6 +274,7 @@ static void free_queries(uvg_ctx* c, bool final = false)
     c->d_qstream = nullptr; c->d_qoff = c->d_snp_off = c->d_snp_ent = nullptr; c->d_pivot = nullptr;
     cudaFree(c->d_thr_local); for (int b = 0; b < NBUF; ++b) { cudaFree(c->d_thr_all[b]); c->d_thr_all[b] = nullptr; }
     cudaFree(c->d_own); cudaFree(c->d_all); c->d_own = c->d_all = nullptr;
+    cudaFree(c->d_snap_own); cudaFree(c->d_snap_batch); cudaFree(c->d_ever_round); c->d_snap_own = nullptr; c->d_snap_batch = nullptr; c->d_ever_round = nullptr;
     cudaFree(c->d_batch_id); cudaFree(c->d_max_inc_batch);
     cudaFree(c->d_tiles); c->d_tiles = nullptr; c->tiles_alloc = 0;
     c->d_qdata = nullptr; c->d_qnib = c->d_qamb_off = c->d_qamb_ent = nullptr; c->d_thr_local = nullptr;
@@ -290,7 +294,8 @@ extern "C" void uvg_destroy(uvg_ctx* c)
     free_queries(c, true);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->d_db); cudaFree(c->d_db2); cudaFree(c->d_ref_cnt); cudaFree(c->d_non_n); cudaFree(c->d_ramb_off); cudaFree(c->d_ramb_ent); cudaFree(c->d_ever);
-    cudaFree(c->d_counters); cudaFree(c->d_nacc); cudaFree(c->d_ipc); cudaFree(c->d_bstate);
+    cudaFree(c->d_counters); cudaFree(c->d_nacc); cudaFree(c->d_ipc); cudaFree(c->d_bstate); cudaFree(c->d_spec);
+    cudaFree(c->d_bounds); if (c->h_bounds) cudaFreeHost(c->h_bounds);
     cudaFree(c->d_stage_text[0]); cudaFree(c->d_stage_text[1]); cudaFree(c->d_stage_nn); cudaFree(c->d_stage_namb); cudaFree(c->d_stage_acc); cudaFree(c->d_stage_dst);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (auto& pr : c->pair_events) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
@@ -383,6 +388,7 @@ static int reset_heaps(uvg_ctx* c)
         const int32_t b0[8] = {0, 0, c->nchar, 0, c->nchar, c->nchar, 0, 0};
         UVG_CUDA(c, cudaMemcpyAsync(c->d_bstate, b0, sizeof b0, cudaMemcpyHostToDevice, c->st));
         c->replay_seq = 0;
+        c->bounds_used = 0;                                                 // everything is idle here (sync_all above)
     }
     if (c->d_ever && c->ever_cap) UVG_CUDA(c, cudaMemsetAsync(c->d_ever, 0, c->ever_cap, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));                              // `init` goes out of scope
@@ -734,6 +740,10 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     c->d_heap_n = reinterpret_cast<int32_t*>(c->d_own + c->own_off_n); c->d_max_inc = reinterpret_cast<int32_t*>(c->d_own + c->own_off_mi);
     UVG_CUDA(c, pooled_alloc(c, 10, &c->d_batch_id, (size_t)rows * 4)); UVG_CUDA(c, pooled_alloc(c, 11, &c->d_max_inc_batch, (size_t)rows * 4));
     if (c->world > 1) UVG_CUDA(c, pooled_alloc(c, 12, &c->d_all, (size_t)c->world * c->own_bytes));
+    if (c->literal) {
+        UVG_CUDA(c, pooled_alloc(c, 13, &c->d_snap_own, c->own_bytes));
+        UVG_CUDA(c, pooled_alloc(c, 14, &c->d_snap_batch, (size_t)rows * 8));
+    }
     // dense score tiles: rounds are capped so that one buffer stays within ~3 GiB
     {
         int64_t cap = round_size_max(c->prm);
@@ -744,6 +754,7 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
         // depend on the query set, so the tiles take what max_round asks for (or the allocation fails loudly below).
         if (c->world == 1) cap = std::max<int64_t>(GROUP * RPL, std::min(cap, fit));
         c->seg_cap = cap;
+        if (c->literal) UVG_CUDA(c, pooled_alloc(c, 21, &c->d_ever_round, (size_t)cap));
         c->tile_elems = (size_t)(rows + 2) * c->world * cap;
         if (NBUF * c->tile_elems > c->tiles_alloc) {                       // the multi-GiB buffer is kept when the next query set fits
             if (c->world > 1) close_peers(c);                                // (every rank takes this branch alike: the size depends on shared parameters only);
@@ -1409,17 +1420,12 @@ static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t
     if (rc) return rc;
     UVG_CUDA(c, cudaEventRecord(ra, c->st_rp));
     rp.ord_begin = round_first; rp.ord_end = round_first + round_count;
-    if (!c->literal) {
-        UVG_CUDA(c, launch_replay(rp, c->st_rp));
-        c->stats.other_kernel_launches += 1;
-    } else {
-        // the reference's batches: --pool accepted references, restarting with every file (nearest.c:245-286).  One launch per
-        // piece of a batch inside this round; the batch-wide limit travels through d_bstate (see ReplayParams).
-        rp.literal = 1; rp.local_ord0 = c->global_base;
-        rp.db = c->d_db; rp.qcons = c->d_qdata + (size_t)(c->n_query / QTILE) * c->n_chunks; rp.cons_qi = c->n_query % QTILE;
-        rp.cons_nib = c->d_qnib + (size_t)c->n_query * c->qnib_stride;
-        rp.camb = c->d_qamb_ent + c->cons_amb_begin; rp.n_camb = (int32_t)c->cons_amb_n;
-        rp.ramb_off = c->d_ramb_off; rp.ramb_ent = c->d_ramb_ent; rp.Wp = c->Wp;
+    // the reference's batches that touch this round: --pool accepted references, restarting with every file
+    // (nearest.c:245-286).  pieces = the round cut at the batch boundaries; bounds = first ordinals of those batches
+    struct Piece { int64_t o, e; bool start; };
+    std::vector<Piece> pieces;
+    std::vector<int64_t> bounds;
+    {
         const int64_t pool = c->prm.pool, end = round_first + round_count;
         size_t k = std::upper_bound(c->file_starts.begin(), c->file_starts.end(), round_first) - c->file_starts.begin() - 1;
         for (int64_t o = round_first; o < end;) {
@@ -1427,15 +1433,74 @@ static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t
             const int64_t fs = c->file_starts[k];
             int64_t nb = fs + ((o - fs) / pool + 1) * pool;
             if (k + 1 < c->file_starts.size()) nb = std::min(nb, c->file_starts[k + 1]);
-            const int64_t e = std::min(end, nb);
+            pieces.push_back({o, std::min(end, nb), (o - fs) % pool == 0});
+            bounds.push_back(fs + (o - fs) / pool * pool);                    // first ordinal of the batch that holds o
+            if (nb >= end) bounds.push_back(nb);
+            o = std::min(end, nb);
+        }
+    }
+    if (!bounds.empty()) {
+        // device copy of the bounds: appended to a buffer that lives until the heaps are emptied (rounds in flight read it)
+        const size_t need = c->bounds_used + bounds.size();
+        if (need > c->bounds_cap) {
+            int rc2 = sync_all(c);
+            if (rc2) return rc2;
+            const size_t cap = std::max<size_t>(need * 2, 1 << 16);
+            int64_t* nd = nullptr; int64_t* nh = nullptr;
+            UVG_CUDA(c, cudaMalloc(&nd, cap * 8));
+            UVG_CUDA(c, cudaMallocHost(&nh, cap * 8));
+            cudaFree(c->d_bounds); if (c->h_bounds) cudaFreeHost(c->h_bounds);
+            c->d_bounds = nd; c->h_bounds = nh; c->bounds_cap = cap; c->bounds_used = 0;
+        }
+        memcpy(c->h_bounds + c->bounds_used, bounds.data(), bounds.size() * 8);
+        UVG_CUDA(c, cudaMemcpyAsync(c->d_bounds + c->bounds_used, c->h_bounds + c->bounds_used, bounds.size() * 8, cudaMemcpyHostToDevice, c->st_rp));
+        rp.bounds = c->d_bounds + c->bounds_used; rp.n_bounds = (int32_t)bounds.size();
+        c->bounds_used += bounds.size();
+    }
+    if (!c->literal) {
+        UVG_CUDA(c, launch_replay(rp, c->st_rp));
+        c->stats.other_kernel_launches += 1;
+    } else if (round_count > 0) {
+        // Literal emulation of the reference's batches (hazard H1), speculatively.  The reference's result can differ from the
+        // pool-independent closed form only for pairs the closed-form pass FLAGS (a superset, replay.cu); rounds without a flag
+        // -- all of them for ordinary query sets -- are settled by ONE closed-form launch.  So: (1) keep the state of the
+        // round's start, (2) closed-form pass over the whole round with its admissions marked in a scratch array, (3) commit if it
+        // raised no flag, else (4) put the state back and replay the round literally, one launch per piece of a batch, the
+        // batch-wide limit travelling through d_bstate.  Everything is decided on the device: the launches of (4) return at once
+        // when the round is settled, no host synchronisation.
+        const size_t rows = (size_t)c->rows_cap;
+        UVG_CUDA(c, cudaMemcpyAsync(c->d_snap_own, c->d_own, c->own_bytes, cudaMemcpyDeviceToDevice, c->st_rp));
+        UVG_CUDA(c, cudaMemcpyAsync(c->d_snap_batch, c->d_batch_id, rows * 4, cudaMemcpyDeviceToDevice, c->st_rp));
+        UVG_CUDA(c, cudaMemcpyAsync(c->d_snap_batch + rows, c->d_max_inc_batch, rows * 4, cudaMemcpyDeviceToDevice, c->st_rp));
+        UVG_CUDA(c, cudaMemsetAsync(c->d_spec, 0, 16, c->st_rp));
+        UVG_CUDA(c, cudaMemsetAsync(c->d_ever_round, 0, (size_t)round_count, c->st_rp));
+        ReplayParams sp = rp;
+        sp.counters = c->d_spec; sp.ever_round = c->d_ever_round; sp.ord_round0 = round_first;
+        UVG_CUDA(c, launch_replay(sp, c->st_rp));
+        UVG_CUDA(c, launch_spec_commit(c->d_spec, c->d_ever_round, round_count, round_first, c->d_ever, c->d_counters, c->st_rp));
+        const int64_t i0 = c->replay_seq;
+        SpecRestore sr{};
+        sr.spec = c->d_spec; sr.snap_own = reinterpret_cast<const uint4*>(c->d_snap_own); sr.own = reinterpret_cast<uint4*>(c->d_own);
+        sr.own_vec = (int64_t)(c->own_bytes / 16);
+        sr.snap_batch_id = c->d_snap_batch; sr.batch_id = c->d_batch_id; sr.snap_mib = c->d_snap_batch + rows; sr.mib = c->d_max_inc_batch; sr.rows = (int32_t)rows;
+        sr.snap_max_inc = reinterpret_cast<const int32_t*>(c->d_snap_own + c->own_off_mi);
+        sr.n_query = c->n_query;
+        sr.open_batch = pieces[0].start ? -1 : (int32_t)bounds[0];
+        sr.b_prev = c->d_bstate + (i0 + 2) % 3; sr.b_carry = c->d_bstate + 4 + (i0 + 1) % 2; sr.b_acc = c->d_bstate + i0 % 3;
+        UVG_CUDA(c, launch_spec_restore(sr, c->st_rp));
+        rp.literal = 1; rp.local_ord0 = c->global_base; rp.spec_flags = c->d_spec + 1;
+        rp.db = c->d_db; rp.qcons = c->d_qdata + (size_t)(c->n_query / QTILE) * c->n_chunks; rp.cons_qi = c->n_query % QTILE;
+        rp.cons_nib = c->d_qnib + (size_t)c->n_query * c->qnib_stride;
+        rp.camb = c->d_qamb_ent + c->cons_amb_begin; rp.n_camb = (int32_t)c->cons_amb_n;
+        rp.ramb_off = c->d_ramb_off; rp.ramb_ent = c->d_ramb_ent; rp.Wp = c->Wp;
+        for (const Piece& pc : pieces) {
             const int64_t i = c->replay_seq++;
-            rp.ord_begin = o; rp.ord_end = e; rp.batch_start = (o - fs) % pool == 0;
+            rp.ord_begin = pc.o; rp.ord_end = pc.e; rp.batch_start = pc.start;
             rp.b_prev = c->d_bstate + (i + 2) % 3; rp.b_acc = c->d_bstate + i % 3; rp.b_zero = c->d_bstate + (i + 1) % 3;
             rp.b_carry_in = c->d_bstate + 4 + (i + 1) % 2; rp.b_carry_out = c->d_bstate + 4 + i % 2;
             UVG_CUDA(c, launch_replay(rp, c->st_rp));
-            c->stats.other_kernel_launches += 1;
-            o = e;
         }
+        c->stats.other_kernel_launches += 3 + (int64_t)pieces.size();
     }
     UVG_CUDA(c, cudaEventRecord(rb, c->st_rp));
     ++*n_ev;

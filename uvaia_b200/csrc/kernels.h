@@ -42,13 +42,21 @@ struct ReplayParams {
     int64_t seg_global[MAX_RANKS];
     int32_t rows_cap;             // row rows_cap = consensus counts, row rows_cap + 1 = per-reference record (non_n)
     HeapItem* heaps; int32_t* heap_n; int32_t* max_inc;               // per owned row: [rows_cap][K+1], [rows_cap], [rows_cap]
-    int32_t* batch_id; int32_t* max_inc_batch;                        // H1 bookkeeping per owned row
+    int32_t* batch_id; int32_t* max_inc_batch;                        // H1 bookkeeping per owned row: first ordinal of the reference's batch of the
+                                                                      //     row's last candidate (-1: none), max_incompatible at the start of that batch
     Threshold* thr;                                                   // [rows_cap] thresholds of the owned rows (output)
     uint8_t* ever_best;                                               // per GLOBAL ordinal
     unsigned long long* counters;                                     // [0]=admitted, [1]=H1 flags
     int32_t n_query;                                                  // real queries (all ranks)
     int32_t world, rank;                                              // row -> query: ((row / QTILE) * world + rank) * QTILE + row % QTILE
     int32_t K, acgt_mode, pool;
+    // the reference's batches that touch this launch: sorted first ordinals, bounds[0] <= first ordinal of the launch, the last
+    // entry >= its end (--pool accepted references per batch, a batch also ends with its file: nearest.c:245-286)
+    const int64_t* bounds; int32_t n_bounds;
+    // speculative pass of a literal round (see engine.cu run_round): admissions are marked in ever_round[ordinal - ord_round0]
+    // instead of ever_best; literal launches return at once when *spec_flags == 0
+    uint8_t* ever_round; int64_t ord_round0;
+    const unsigned long long* spec_flags;
     // the launch replays the global ordinals [ord_begin, ord_end) of the round (literal mode: one launch per batch piece)
     int64_t ord_begin, ord_end;
     // ---- literal emulation of the reference's batch-wide consensus limit (hazard H1; single GPU) ----
@@ -66,6 +74,20 @@ struct ReplayParams {
     int32_t Wp;
 };
 cudaError_t launch_replay(const ReplayParams& p, cudaStream_t st);
+// speculation of a literal round: commit the speculative pass if it raised no flag (spec[1] == 0) ...
+cudaError_t launch_spec_commit(const unsigned long long* spec, const uint8_t* ever_round, int64_t n, int64_t ord_round0, uint8_t* ever_best,
+                               unsigned long long* counters, cudaStream_t st);
+// ... else put the state of the round's start back and prepare the batch-wide limits of the first literal launch
+struct SpecRestore {
+    const unsigned long long* spec;
+    const uint4* snap_own; uint4* own; int64_t own_vec;               // heaps | heap_n | max_inc block, in 16-byte units
+    const int32_t* snap_batch_id; int32_t* batch_id; const int32_t* snap_mib; int32_t* mib; int32_t rows;
+    const int32_t* snap_max_inc;                                      // inside snap_own
+    int32_t n_query;                                                  // rows of real queries (single GPU: row = query)
+    int32_t open_batch;                                               // first ordinal of the batch in progress at the round's start (-1: a batch starts there)
+    int32_t* b_prev; int32_t* b_carry; int32_t* b_acc;                // what the first literal launch reads / accumulates into
+};
+cudaError_t launch_spec_restore(const SpecRestore& r, cudaStream_t st);
 cudaError_t replay_setup(int K);
 
 }  // namespace uvg

@@ -57,11 +57,13 @@ __device__ __forceinline__ int item_mismatch(const HeapItem& it, int acgt_mode)
 struct RpState {
     int n, max_inc;
     int root[4];          // first keys of the heap root (valid when n == K)
-    int cur_batch, mib;   // batch (of --pool accepted references) of the last candidate and max_incompatible at its start
+    int cb_begin, cb_end, bk;   // closed form: the reference's batch of the last candidate [cb_begin, cb_end) (global ordinals), its index in p.bounds
+    int mib;                    //              max_incompatible of THIS query at the start of that batch
     int restart;          // first position to re-test after an admission, or -1
     int pend;             // literal mode: window position of a pair whose consensus stage the reference truncated, or -1
     int t[4];             // literal mode: the truncated consensus counts of that pair (cons_prefix)
 };
+static_assert(sizeof(RpState) <= 16 * 4, "RpState lives in the first 16 ints of s_misc");
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Literal emulation of hazard H1 (nearest.c:289-294, 428-433, 485-501).  The reference scores the
@@ -218,6 +220,9 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
     const int row = blockIdx.x;
     const int q = ((row / QTILE) * p.world + p.rank) * QTILE + row % QTILE;        // query this row belongs to
     if (q >= p.n_query) return;
+    // literal launches of a round that the speculative closed-form pass has already settled (no pair could have been
+    // scored differently by the reference: 0 flags) have nothing to do
+    if (p.spec_flags && *p.spec_flags == 0ull) return;
     const int K = p.K, acgt = p.acgt_mode;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     HeapItem* gheap = p.heaps + (size_t)row * (K + 1);
@@ -232,7 +237,18 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
         if (threadIdx.x == 0) {
             st->n = n0; st->max_inc = p.max_inc[row];
             for (int k = 0; k < 4; ++k) st->root[k] = n0 == K ? a[1].s[k] : 0;
-            st->cur_batch = p.batch_id[row]; st->mib = p.max_inc_batch[row];
+            st->mib = p.max_inc_batch[row];
+            // the batch of the last candidate of an earlier launch: still open if it reaches into this launch
+            const int b0 = p.batch_id[row];
+            int k = 0, e = b0;
+            if (p.n_bounds > 0 && b0 >= (int)p.bounds[0]) {
+                while (k + 1 < p.n_bounds && (int)p.bounds[k + 1] <= b0) ++k;
+                e = k + 1 < p.n_bounds ? (int)p.bounds[k + 1] : b0;
+            }
+            st->cb_begin = b0; st->cb_end = e; st->bk = k;
+            // literal launches never straddle a batch boundary: the first launch of a batch notes where it starts and the
+            // query's limit there (what the speculative pass of a later round compares with, k_spec_restore)
+            if (p.literal && p.batch_start) { st->cb_begin = (int)p.ord_begin; st->mib = st->max_inc; }
             st->restart = -1; st->pend = -1;
         }
     }
@@ -266,7 +282,7 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
             for (;;) {
                 __syncthreads();
                 // ---- all threads: test the window against the current state ----
-                const int n = st->n, max_inc = st->max_inc, mib = st->mib, cur_batch = st->cur_batch;
+                const int n = st->n, max_inc = st->max_inc, mib = st->mib, cb_begin = st->cb_begin, cb_end = st->cb_end;
                 const int r0 = st->root[0], r1 = st->root[1], r2 = st->root[2], r3 = st->root[3];
 #pragma unroll
                 for (int k = 0; k < RP_PER; ++k) {
@@ -301,7 +317,7 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
                             // have scored this pair with consensus counts truncated at the batch-start limit.  Necessary
                             // condition for its result to differ from the closed form:
                             const int64_t ord = seg_global + w0 + i;
-                            if ((int)(ord / p.pool) == cur_batch) {
+                            if (ord >= cb_begin && ord < cb_end) {
                                 const uint4 cc = tcons[seg_col + w0 + i];
                                 const int ci = acgt ? (int)(cc.y - cc.x) : (int)(cc.w - cc.x);
                                 flag = ci >= mib && D - ci + mib < max_inc;
@@ -314,7 +330,7 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
                 __syncthreads();
                 // ---- thread 0: admit in file order until the state changes ----
                 if (threadIdx.x == 0) {
-                    int nn = n, mi = max_inc, restart = -1, cb = cur_batch, mb = mib, pend = -1;
+                    int nn = n, mi = max_inc, restart = -1, cbb = cb_begin, cbe = cb_end, bk = st->bk, mb = mib, pend = -1;
                     // heap_insert (min_heap.c:93-117) + the max_incompatible update (nearest.c:475 / :508); true = the state changed
                     auto admit = [&](const HeapItem& it) -> bool {
                         if (nn == K) {
@@ -327,7 +343,8 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
                             heap_up(a, nn);
                         }
                         ++admitted;
-                        p.ever_best[it.r] = 1;                                              // is_best, nearest.c:505
+                        if (p.ever_round) p.ever_round[it.r - p.ord_round0] = 1;           // speculative pass: committed by k_spec_commit
+                        else p.ever_best[it.r] = 1;                                         // is_best, nearest.c:505
                         if (nn == K) {
                             mi = item_mismatch(a[1], acgt) + 1;
                             for (int k = 0; k < 4; ++k) st->root[k] = a[1].s[k];
@@ -346,9 +363,11 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
                             const uint4 sc = s_sc[i];
                             const int64_t col = seg_col + w0 + i;
                             const int r = (int)(seg_global + w0 + i);
-                            if (!lit) {
-                                const int bt = r / p.pool;
-                                if (bt != cb) { cb = bt; mb = mi; }
+                            if (!lit && (r < cbb || r >= cbe)) {
+                                // a new batch of the reference program starts for this query: its limit at the start of that batch
+                                while (bk + 1 < p.n_bounds && (int)p.bounds[bk + 1] <= r) ++bk;
+                                cbb = (int)p.bounds[bk]; cbe = bk + 1 < p.n_bounds ? (int)p.bounds[bk + 1] : 0x7fffffff;
+                                mb = mi;
                             }
                             const uint4 cc = tcons[col];
                             const int c0 = (int)cc.x, nonn = (int)tmeta[col].x;
@@ -374,7 +393,7 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
                             h1 += __popc(f);
                         }
                     }
-                    st->n = nn; st->max_inc = mi; st->cur_batch = cb; st->mib = mb; st->restart = restart; st->pend = pend;
+                    st->n = nn; st->max_inc = mi; st->cb_begin = cbb; st->cb_end = cbe; st->bk = bk; st->mib = mb; st->restart = restart; st->pend = pend;
                 }
                 __syncthreads();
                 const int pend = st->pend;
@@ -428,7 +447,7 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
 
     const int n = st->n;
     if (threadIdx.x == 0) {
-        p.heap_n[row] = n; p.max_inc[row] = st->max_inc; p.batch_id[row] = st->cur_batch; p.max_inc_batch[row] = st->mib;
+        p.heap_n[row] = n; p.max_inc[row] = st->max_inc; p.batch_id[row] = st->cb_begin; p.max_inc_batch[row] = st->mib;
         if (lit) atomicMax(p.b_acc, st->max_inc);                                  // batch-wide limit of the next batch = max over the queries
         if (admitted) atomicAdd(p.counters + 0, (unsigned long long)admitted);
         if (h1) atomicAdd(p.counters + 1, (unsigned long long)h1);
@@ -449,6 +468,55 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
         }
     }
     if (heap_in_smem) for (int i = 1 + threadIdx.x; i <= n; i += blockDim.x) gheap[i] = a[i];
+}
+
+// ---- speculation of a literal round (engine.cu run_round) ----
+__global__ void k_spec_commit(const unsigned long long* __restrict__ spec, const uint8_t* __restrict__ ever_round, int64_t n, int64_t ord_round0,
+                              uint8_t* __restrict__ ever_best, unsigned long long* __restrict__ counters)
+{
+    if (spec[1] != 0ull) return;                                                   // flagged: the literal launches redo the round
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        if (ever_round[i]) ever_best[ord_round0 + i] = 1;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && spec[0]) atomicAdd(counters, spec[0]);
+}
+
+__global__ void __launch_bounds__(256) k_spec_restore(const SpecRestore r)
+{
+    if (r.spec[1] == 0ull) return;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < r.own_vec; i += (int64_t)gridDim.x * blockDim.x) r.own[i] = r.snap_own[i];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < r.rows; i += gridDim.x * blockDim.x) { r.batch_id[i] = r.snap_batch_id[i]; r.mib[i] = r.snap_mib[i]; }
+    if (blockIdx.x != 0) return;
+    // batch-wide limits of the consensus stage as the reference had them at the start of the round: for a batch that starts
+    // there the maximum of the queries' limits now; for a batch in progress the maximum of the limits at ITS start (a query
+    // whose last candidate is older than that batch has not changed since)
+    __shared__ int s_max[2][8];
+    int now = 0, open = 0;
+    for (int i = threadIdx.x; i < r.n_query; i += blockDim.x) {
+        const int m = r.snap_max_inc[i];
+        now = max(now, m);
+        open = max(open, r.snap_batch_id[i] == r.open_batch ? r.snap_mib[i] : m);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { now = max(now, __shfl_xor_sync(0xffffffffu, now, o)); open = max(open, __shfl_xor_sync(0xffffffffu, open, o)); }
+    if ((threadIdx.x & 31) == 0) { s_max[0][threadIdx.x >> 5] = now; s_max[1][threadIdx.x >> 5] = open; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 0; k < 8; ++k) { now = max(now, s_max[0][k]); open = max(open, s_max[1][k]); }
+        *r.b_prev = now; *r.b_carry = open; *r.b_acc = 0;
+    }
+}
+
+cudaError_t launch_spec_commit(const unsigned long long* spec, const uint8_t* ever_round, int64_t n, int64_t ord_round0, uint8_t* ever_best,
+                               unsigned long long* counters, cudaStream_t st)
+{
+    k_spec_commit<<<(unsigned)std::max<int64_t>(1, std::min<int64_t>(64, (n + 255) / 256)), 256, 0, st>>>(spec, ever_round, n, ord_round0, ever_best, counters);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_spec_restore(const SpecRestore& r, cudaStream_t st)
+{
+    k_spec_restore<<<64, 256, 0, st>>>(r);
+    return cudaGetLastError();
 }
 
 static size_t replay_smem_bytes(int K, int* in_smem)
