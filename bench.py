@@ -30,8 +30,9 @@ NCHAR = 29903
 # result checksums (sum over every table of the six counts and the reference ordinals) of single-GPU runs, asserted at any N
 KNOWN_CHECKSUMS = {(1000, 1_000_000, 29903, 100, 0.0, 200): 31652904200}
 # algorithmic instruction counts per (pair, 32-site word) of the two pair-count kernels
-OPS = {"pivot": {"kernel": "k_pairpivot", "lop3": 4.0, "popc": 1.0, "db_bytes_per_word": 24,     # 2 AND + 2 x (one 3:2 compressor per two words); 2 x 0.5 POPC
-                 "ncu": "ncu_pairpivot_r01k_sparse.json"},
+OPS = {"pivot": {"kernel": "k_pairpivot", "lop3": 4.0, "popc": 1.0, "db_bytes_per_word": 9,      # 2 AND + 2 x (one 3:2 compressor per two words); 2 x 0.5 POPC;
+                                                                                                  # staged: planes + counts, 4.5 KB per 64 references x 8 words
+                 "ncu": "ncu_pairpivot_r02k_producer_warp.json"},
        "general": {"kernel": "k_paircount", "lop3": 4.5, "popc": 1.25, "db_bytes_per_word": 12,  # 3 for valid+match, 1.5 carry-save tree; 1 + 0.25 POPC
                    "ncu": "ncu_paircount_r01e_csa.json"}}
 
@@ -344,8 +345,8 @@ def main():
             "warmup": args.warmup, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32 bit-planes / int32 counts",
             "data": "synthetic (device generator, seeds 1/1001/2002)",
             "config": {"workload": workload, "nbest": args.nbest, "pool": pool, "h1": "literal --pool batches" if world == 1 and not args.closed_form else "closed form + flags", "early_abort": bool(args.early_abort), "sharding": "rows x%d" % world,
-                       "l2": "inputs larger than L2 (packed DB %.1f GB; the pivot form streams its derived planes, %.1f GB, once per pass)"
-                             % (R * ((L + 255) // 256 * 256) * 3 / 8 / 1e9, R * ((L + 255) // 256 * 256) * 6 / 8 / 1e9)}}
+                       "l2": "inputs larger than L2 (packed DB %.1f GB; the pivot form streams planes + counts of its derived database, %.1f GB of %.1f GB, once per pivot tile)"
+                             % (R * ((L + 255) // 256 * 256) * 3 / 8 / 1e9, R * ((L + 255) // 256 * 256) / 32 * 9 / 1e9, R * ((L + 255) // 256 * 256) / 32 * 25 / 1e9)}}
 
     # ---- build the device-resident database (K1), optionally keeping the text on the host for the e2e leg ----
     want_e2e = not args.no_e2e
@@ -521,7 +522,8 @@ def main():
     db_bytes = n_local * ((W + 7) // 8 * 8) * ops["db_bytes_per_word"]        # streamed database bytes per 32-site word and reference
     tr = ncu_traffic(ops["ncu"])
     if tr:   # algorithmic bytes of the captured launch: its slice of the streamed database once + one 16-byte record per pair
-        refs = tr["launch_grid_blocks"] // n_qtiles * 64
+        tiles_k = (Q + 1 + 59) // 60 if st["pivot_fix_entries"] >= 0 else n_qtiles      # the pivot kernel's blocks take 60 slots (pivot tiles)
+        refs = tr["launch_grid_blocks"] // tiles_k * 64
         tr["algorithmic_bytes"] = refs * ((W + 7) // 8 * 8) * ops["db_bytes_per_word"] + refs * (Q + 1) * 16
         tr["launch_refs"] = refs
     roofline = {"kernel": ops["kernel"], "bound": bound, "achieved": popc if bound == "int-popc" else lop3,
@@ -539,6 +541,11 @@ def main():
                 # the pivot form skips (query, 128-site unit) pairs where the query is complete and equal to the pivot: the same
                 # search priced with the DENSE op count of its formulation (what a kernel that does not skip would have to issue)
                 "frac_if_priced_dense": max(f_l, f_p) * pairwords_dense / max(1.0, pairwords_rank),
+                # continuity with round 1, whose kernel executed 0.3588 of the dense pair-words of this workload (whole 128-site
+                # units): the same search priced on THAT work.  The r02 kernel gives the same tables executing 0.160 (all-N units come
+                # from a counts table, the rest is counted in 64-site halves), so `frac` per executed pair-word fell while the search
+                # got faster; this key is an explanation, not the roofline claim
+                "frac_at_r01_work": (ops["lop3"] * 0.3588 * pairwords_dense / (k_ms * 1e-3) / 1e9 / peaks["lop3_gips"]) if st["pivot_fix_entries"] >= 0 else None,
                 "pivot_fix_entries_per_query": (st["pivot_fix_entries"] / max(1, Q + 1)) if st["pivot_fix_entries"] >= 0 else None}
 
     cb = None

@@ -17,7 +17,8 @@
 namespace uvg {
 
 __device__ __forceinline__ uint4 pair_epilogue_default(const PairParams& p, const uint32_t* __restrict__ fix_off, const uint32_t* __restrict__ fix_ent,
-                                                       int slot, int64_t group, int lane, int64_t local, int32_t M, int32_t V)
+                                                       int slot, int64_t group, int lane, int64_t local, int32_t M, int32_t V,
+                                                       const bool query_list = true)
 {
     const uint32_t* dbw = reinterpret_cast<const uint32_t*>(p.db);
     int32_t dm = 0, dv = 0, dp = 0, dt = 0;
@@ -27,7 +28,7 @@ __device__ __forceinline__ uint4 pair_epilogue_default(const PairParams& p, cons
         const uint32_t qc = (__ldg(p.qnib + (size_t)slot * p.qnib_stride + (site >> 3)) >> ((site & 7u) * 4u)) & 15u;
         dv += qc != 0u; dp += (qc & rc) != 0u; dt += qc == rc;
     }
-    const uint32_t qe0 = fix_off[slot], qe1 = fix_off[slot + 1];
+    const uint32_t qe0 = query_list ? fix_off[slot] : 0u, qe1 = query_list ? fix_off[slot + 1] : 0u;   // the pivot kernel resolves (c) itself
     const size_t lane_base = db_unit_index(group, 0, 0, lane, p.Wp) * 4;
 #pragma unroll 4
     for (uint32_t e = qe0; e < qe1; ++e) {

@@ -180,18 +180,37 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         if (++s == STAGES2) { s = 0; ph ^= 1u; }
     }
 
-    // ---- fix entries: plain bases of the warp's slots that differ from the pivot.  A reference that holds the same base there
-    // is one more match.  Lane = entry for the loads of the column masks (32 independent loads per slot and group, L2 hits or
-    // the 8 KB mask part of the chunk records), then the non-zero masks are broadcast lane by lane. ----
+    // ---- sparse corrections from the column masks of the derived database (per site and base one word: bit l = reference l of
+    // the group holds that base there), per slot of the warp:
+    //   fix entries    -- plain bases that differ from the pivot: a reference that holds the same base is one more match;
+    //   ambiguity codes -- the site is outside the query planes: a reference with a plain base there makes the pair valid, and
+    //                      partial when the code contains that base (alignment.c:871-877; never acgt / text: the codes differ).
+    // Lane = entry for the loads (32 entries x 1..4 independent 4-byte loads in flight, L2 hits or the 8 KB mask part of the
+    // chunk records), then the 32 x 32 bit matrix (entry x reference) is transposed across the warp (5 butterfly steps), so
+    // that every lane holds the 32 entries' bits of ITS reference and one POPC counts them: ~2 instructions per entry and
+    // group instead of a serial bit test per entry (r01: ~18 per entry in the epilogue, 12x the main loop on config 4). ----
     const uint8_t* ws = p.wslot + ((size_t)pt * PIVOT_WARPS + warp) * QW2;      // slots of the pivot tile this warp counted (0xff: none)
-    uint32_t fh[RPL][QW2];
+    uint32_t fh[RPL][QW2], fv[RPL][QW2], fp[RPL][QW2];                           // matches by fix entries; valid / partial by ambiguity codes
+    auto transpose32 = [&](uint32_t x) -> uint32_t {
+#pragma unroll
+        for (int j = 16; j >= 1; j >>= 1) {
+            const uint32_t m = j == 16 ? 0x0000ffffu : j == 8 ? 0x00ff00ffu : j == 4 ? 0x0f0f0f0fu : j == 2 ? 0x33333333u : 0x55555555u;
+            const uint32_t y = __shfl_xor_sync(0xffffffffu, x, j);
+            x = (lane & j) ? ((x & ~m) | ((y >> j) & m)) : ((x & m) | ((y << j) & ~m));
+        }
+        return x;
+    };
+    auto mask_words = [&](uint32_t site) -> const uint8_t* {                     // column masks [base A,C,G,T][site in word] of the site's word, first group
+        const uint32_t w = site >> 5;
+        return rsrc + (size_t)(w / WC) * CHUNK2_BYTES + CHUNK2_STAGED + ((w % WC) / 4) * UNIT2_MASKS + (((w & 3u) * 4u) * 32u + (site & 31u)) * 4u;
+    };
 #pragma unroll
     for (int j = 0; j < QW2; ++j) {
 #pragma unroll
-        for (int g = 0; g < RPL; ++g) fh[g][j] = 0;
+        for (int g = 0; g < RPL; ++g) { fh[g][j] = 0; fv[g][j] = 0; fp[g][j] = 0; }
         const int slot = pt * PIVOT_SLOTS + (int)ws[j];
         if (ws[j] == 0xff || slot >= p.n_slots) continue;
-        const uint32_t e1 = __ldg(p.snp_off + slot + 1);
+        uint32_t e1 = __ldg(p.snp_off + slot + 1);
         for (uint32_t e0 = __ldg(p.snp_off + slot); e0 < e1; e0 += 32) {
             const bool have = e0 + lane < e1;
             const uint32_t ent = have ? __ldg(p.snp_ent + e0 + lane) : 0u;
@@ -200,13 +219,27 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
 #pragma unroll
             for (int g = 0; g < RPL; ++g) mk[g] = have ? __ldg(reinterpret_cast<const uint32_t*>(mrec + g * (W4 * UNIT2_MASKS))) : 0u;
 #pragma unroll
+            for (int g = 0; g < RPL; ++g)
+                if (__ballot_sync(0xffffffffu, mk[g] != 0u)) fh[g][j] += __popc(transpose32(mk[g]));
+        }
+        e1 = __ldg(p.qamb_off + slot + 1);
+        for (uint32_t e0 = __ldg(p.qamb_off + slot); e0 < e1; e0 += 32) {
+            const bool have = e0 + lane < e1;
+            const uint32_t ent = have ? __ldg(p.qamb_ent + e0 + lane) : 0u, code = ent >> 28;
+            const uint8_t* mrec = mask_words(ent & AMB_SITE_MASK);
+#pragma unroll
             for (int g = 0; g < RPL; ++g) {
-                uint32_t any = __ballot_sync(0xffffffffu, mk[g] != 0u);
-                while (any) {
-                    const int src = __ffs(any) - 1;
-                    any &= any - 1u;
-                    fh[g][j] += (__shfl_sync(0xffffffffu, mk[g], src) >> lane) & 1u;
+                uint32_t vm = 0, pm = 0;
+                if (have) {
+#pragma unroll
+                    for (int a = 0; a < 4; ++a) {
+                        const uint32_t m = __ldg(reinterpret_cast<const uint32_t*>(mrec + g * (W4 * UNIT2_MASKS) + a * 128));
+                        vm |= m;
+                        pm |= (code >> a) & 1u ? m : 0u;
+                    }
                 }
+                fv[g][j] += __popc(transpose32(vm));
+                fp[g][j] += __popc(transpose32(pm));
             }
         }
     }
@@ -231,7 +264,8 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
             if (!in_range[g]) continue;
             const int32_t M = p.mc_cnt[local[g]] - (int32_t)((acc[g][j] & 0xffffu) + __popc(oM[g][j])) + (int32_t)fh[g][j];
             const int32_t V = p.rb_cnt[local[g]] - (int32_t)((acc[g][j] >> 16) + __popc(oV[g][j]));
-            const uint4 v = pair_epilogue_default(p, p.qamb_off, p.qamb_ent, slot, group0 + g, lane, local[g], M, V);
+            uint4 v = pair_epilogue_default(p, p.qamb_off, p.qamb_ent, slot, group0 + g, lane, local[g], M, V, false);
+            v.z += fp[g][j]; v.w += fv[g][j];                                  // the query's ambiguity codes: partial, valid
             pair_store(p, owner, row, is_cons, local[g], v);
         }
     }
