@@ -144,6 +144,7 @@ struct uvg_ctx {
     int64_t work_host = 0;                            // executed work the host derives from the masks (pairpivot.cu does not count in the kernel)
     bool heaps_cached = false;
     std::vector<HeapItem> h_heaps; std::vector<int32_t> h_heap_n, h_max_inc;
+    uint8_t* h_all = nullptr; size_t h_all_bytes = 0;      // pinned landing area of the result blocks
 };
 
 #define UVG_FAIL(ctx, code, ...) do { char b_[512]; snprintf(b_, sizeof b_, __VA_ARGS__); (ctx)->err = b_; return (code); } while (0)
@@ -298,6 +299,7 @@ extern "C" void uvg_destroy(uvg_ctx* c)
     cudaFree(c->d_bounds); if (c->h_bounds) cudaFreeHost(c->h_bounds);
     cudaFree(c->d_stage_text[0]); cudaFree(c->d_stage_text[1]); cudaFree(c->d_stage_nn); cudaFree(c->d_stage_namb); cudaFree(c->d_stage_acc); cudaFree(c->d_stage_dst);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    if (c->h_all) cudaFreeHost(c->h_all);
     for (auto& pr : c->pair_events) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
     if (c->ev_a) { cudaEventDestroy(c->ev_a); cudaEventDestroy(c->ev_b); cudaEventDestroy(c->ev_c); cudaEventDestroy(c->ev_d); }
     for (int b = 0; b < NBUF; ++b) {
@@ -1633,14 +1635,22 @@ static int cache_heaps(uvg_ctx* c)
     if (c->heaps_cached) return UVG_OK;
     const size_t rows_r = (size_t)c->rows_cap, rows = (size_t)c->world * rows_r, stride = c->K + 1;
     c->h_heaps.resize(rows * stride); c->h_heap_n.resize(rows); c->h_max_inc.resize(rows);
-    const uint8_t* src = c->world > 1 ? c->d_all : c->d_own;
-    for (int r = 0; r < c->world; ++r) {
-        const uint8_t* blk = src + (size_t)r * c->own_bytes;
-        UVG_CUDA(c, cudaMemcpyAsync(c->h_heaps.data() + (size_t)r * rows_r * stride, blk, rows_r * stride * sizeof(HeapItem), cudaMemcpyDeviceToHost, c->st));
-        UVG_CUDA(c, cudaMemcpyAsync(c->h_heap_n.data() + (size_t)r * rows_r, blk + c->own_off_n, rows_r * 4, cudaMemcpyDeviceToHost, c->st));
-        UVG_CUDA(c, cudaMemcpyAsync(c->h_max_inc.data() + (size_t)r * rows_r, blk + c->own_off_mi, rows_r * 4, cudaMemcpyDeviceToHost, c->st));
+    // one device -> host copy of the packed result blocks (pinned), then the three arrays are sliced out on the host
+    const size_t total = (size_t)c->world * c->own_bytes;
+    if (total > c->h_all_bytes) {
+        if (c->h_all) cudaFreeHost(c->h_all);
+        c->h_all = nullptr; c->h_all_bytes = 0;
+        UVG_CUDA(c, cudaMallocHost(&c->h_all, total));
+        c->h_all_bytes = total;
     }
+    UVG_CUDA(c, cudaMemcpyAsync(c->h_all, c->world > 1 ? c->d_all : c->d_own, total, cudaMemcpyDeviceToHost, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
+    for (int r = 0; r < c->world; ++r) {
+        const uint8_t* blk = c->h_all + (size_t)r * c->own_bytes;
+        memcpy(c->h_heaps.data() + (size_t)r * rows_r * stride, blk, rows_r * stride * sizeof(HeapItem));
+        memcpy(c->h_heap_n.data() + (size_t)r * rows_r, blk + c->own_off_n, rows_r * 4);
+        memcpy(c->h_max_inc.data() + (size_t)r * rows_r, blk + c->own_off_mi, rows_r * 4);
+    }
     c->heaps_cached = true;
     return UVG_OK;
 }

@@ -16,10 +16,12 @@
 
 namespace uvg {
 
-constexpr int RP_THREADS = 128;
-constexpr int RP_WIN = 1024;                 // references per window
-constexpr int RP_PER = RP_WIN / RP_THREADS;
+// Block size NT (template): 128 threads x windows of 1,024 references when there are many rows (one GPU: a block per query
+// fills the machine), 512 threads x windows of 4,096 when a rank owns few rows (8 GPUs: 128 rows) -- a row is streamed by ONE
+// block, so its memory-level parallelism is what the last, un-overlapped replay of a sharded search costs.
+constexpr int RP_PER = 8;                    // references per thread and window
 constexpr int RP_HEAP_SMEM_ITEMS = 1024;     // heaps up to this many slots live in shared memory
+#define RP_CONSTS(NT) constexpr int RP_THREADS = (NT); constexpr int RP_WIN = (NT) * RP_PER; (void)RP_WIN;
 
 __device__ __forceinline__ bool item_less(const HeapItem& x, const HeapItem& y)
 {   // x is worse than y in the order of compare_q_item_score (src/min_heap.c:41-47)
@@ -86,8 +88,10 @@ struct ConsSrc {            // what cons_prefix reads (all device pointers)
     int Wp, acgt;
 };
 
+template <int NT>
 __device__ __forceinline__ int block_sum(int v, int* s_red)
 {   // sum over the block; s_red holds RP_THREADS / 32 + 1 ints
+    RP_CONSTS(NT)
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     __syncthreads();
@@ -154,8 +158,10 @@ __device__ __forceinline__ void cons_events(const ConsSrc& c, int64_t lr, int64_
 
 // block-wide; returns (through st->t) the counts the reference's truncated consensus stage holds for reference `lr` at limit B:
 // default mode [acgt, text, partial, valid], --acgt [mismatches, valid, -, -]
+template <int NT>
 __device__ void cons_prefix(const ConsSrc& c, int64_t lr, int B, RpState* st, int* s_red, int* s_scan)
 {
+    RP_CONSTS(NT)
     const int tid = threadIdx.x;
     const int nU = c.Wp / 4, per = (nU + RP_THREADS - 1) / RP_THREADS;
     const int ua = min(nU, tid * per), ub = min(nU, ua + per);
@@ -188,7 +194,7 @@ __device__ void cons_prefix(const ConsSrc& c, int64_t lr, int B, RpState* st, in
             int mm = 0, vv = 0, a = 0, b2 = 0, e = 0;
             if (tid < wb - wa) cons_units(c, lr, wa + tid, wa + tid + 1, mid, mm, vv);
             cons_events(c, lr, (int64_t)wa * 128, mid, tid, RP_THREADS, a, b2, e);
-            const int cnt = block_sum((vv - mm) + e, s_red);
+            const int cnt = block_sum<NT>((vv - mm) + e, s_red);
             if (cnt >= need) hi = mid; else lo = mid + 1;
         }
         pstar = lo;
@@ -197,7 +203,7 @@ __device__ void cons_prefix(const ConsSrc& c, int64_t lr, int B, RpState* st, in
     cons_units(c, lr, ua, ub, pstar, m, v);
     et = ep = ev = 0;
     cons_events(c, lr, 0, pstar, tid, RP_THREADS, et, ep, ev);
-    const int tm = block_sum(m, s_red), tv = block_sum(v, s_red), tt = block_sum(et, s_red), tp = block_sum(ep, s_red), te = block_sum(ev, s_red);
+    const int tm = block_sum<NT>(m, s_red), tv = block_sum<NT>(v, s_red), tt = block_sum<NT>(et, s_red), tp = block_sum<NT>(ep, s_red), te = block_sum<NT>(ev, s_red);
     if (tid == 0) {
         if (c.acgt) { st->t[0] = tv - tm; st->t[1] = tv; st->t[2] = 0; st->t[3] = 0; }
         else { st->t[0] = tm; st->t[1] = tm + tt; st->t[2] = tm + tp; st->t[3] = tv + te; }
@@ -205,17 +211,20 @@ __device__ void cons_prefix(const ConsSrc& c, int64_t lr, int B, RpState* st, in
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int heap_in_smem)
+template <int NT>
+__global__ void __launch_bounds__(NT) k_replay(const ReplayParams p, int heap_in_smem)
 {
+    RP_CONSTS(NT)
     extern __shared__ __align__(16) uint8_t smem[];
     uint4* s_sc = reinterpret_cast<uint4*>(smem);                                  // RP_WIN raw counts
     uint32_t* s_mask = reinterpret_cast<uint32_t*>(smem + RP_WIN * sizeof(uint4)); // candidate bits
     uint32_t* s_fmask = s_mask + RP_WIN / 32;                                      // hazard-H1 bits (closed form: flags; literal: truncated pairs)
-    int32_t* s_misc = reinterpret_cast<int32_t*>(s_fmask + RP_WIN / 32);           // 32 ints
-    int32_t* s_scan = s_misc + 32;                                                 // RP_THREADS + 2 ints (cons_prefix)
+    int32_t* s_misc = reinterpret_cast<int32_t*>(s_fmask + RP_WIN / 32);           // 64 ints: state | 16 per-warp maxima | 16 per-warp sums
+    int32_t* s_scan = s_misc + 64;                                                 // RP_THREADS + 2 ints (cons_prefix)
     HeapItem* s_heap = reinterpret_cast<HeapItem*>(s_scan + RP_THREADS + 32);
     RpState* st = reinterpret_cast<RpState*>(s_misc);
-    int* s_red = s_misc + 24;                                                      // RP_THREADS / 32 ints (block_sum)
+    int* s_red = s_misc + 32;                                                      // RP_THREADS / 32 ints (block_sum)
+    static_assert(NT / 32 <= 16, "per-warp scratch");
 
     const int row = blockIdx.x;
     const int q = ((row / QTILE) * p.world + p.rank) * QTILE + row % QTILE;        // query this row belongs to
@@ -400,7 +409,7 @@ __global__ void __launch_bounds__(RP_THREADS) k_replay(const ReplayParams p, int
                 if (pend >= 0) {
                     // literal mode: the pair at `pend` reaches the heap with the TRUNCATED consensus counts (block-wide recount)
                     const int64_t ord = seg_global + w0 + pend;
-                    cons_prefix(csrc, ord - p.local_ord0, B, st, s_red, s_scan);
+                    cons_prefix<NT>(csrc, ord - p.local_ord0, B, st, s_red, s_scan);
                     if (threadIdx.x == 0) {
                         const uint4 sc = s_sc[pend];
                         const int64_t col = seg_col + w0 + pend;
@@ -519,9 +528,10 @@ cudaError_t launch_spec_restore(const SpecRestore& r, cudaStream_t st)
     return cudaGetLastError();
 }
 
-static size_t replay_smem_bytes(int K, int* in_smem)
+static size_t replay_smem_bytes(int K, int NT, int* in_smem)
 {
-    size_t fixed = RP_WIN * sizeof(uint4) + 2 * (RP_WIN / 32) * 4 + 32 * 4 + (RP_THREADS + 32) * 4;
+    const size_t RP_WIN = (size_t)NT * RP_PER;
+    size_t fixed = RP_WIN * sizeof(uint4) + 2 * (RP_WIN / 32) * 4 + 64 * 4 + ((size_t)NT + 32) * 4;
     *in_smem = (K + 1) <= RP_HEAP_SMEM_ITEMS;
     return fixed + (*in_smem ? (size_t)(K + 1) * sizeof(HeapItem) : 0);
 }
@@ -529,16 +539,22 @@ static size_t replay_smem_bytes(int K, int* in_smem)
 cudaError_t replay_setup(int K)
 {
     int in_smem;
-    size_t bytes = replay_smem_bytes(K, &in_smem);
-    return cudaFuncSetAttribute(k_replay, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    cudaError_t e = cudaFuncSetAttribute(k_replay<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)replay_smem_bytes(K, 128, &in_smem));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_replay<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)replay_smem_bytes(K, 512, &in_smem));
+    return e;
 }
 
 cudaError_t launch_replay(const ReplayParams& p, cudaStream_t st)
 {
     if (p.rows_cap <= 0) return cudaSuccess;
     int in_smem;
-    size_t bytes = replay_smem_bytes(p.K, &in_smem);
-    k_replay<<<p.rows_cap, RP_THREADS, bytes, st>>>(p, in_smem);
+    if (p.rows_cap <= 320) {                                                       // few rows (sharded): wide blocks
+        const size_t bytes = replay_smem_bytes(p.K, 512, &in_smem);
+        k_replay<512><<<p.rows_cap, 512, bytes, st>>>(p, in_smem);
+    } else {
+        const size_t bytes = replay_smem_bytes(p.K, 128, &in_smem);
+        k_replay<128><<<p.rows_cap, 128, bytes, st>>>(p, in_smem);
+    }
     return cudaGetLastError();
 }
 
