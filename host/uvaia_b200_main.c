@@ -75,7 +75,7 @@ static void reader_open(reader_t* r, const char* path)
     size_t got = fread(magic, 1, 6, f);
     fclose(f);
     const char* tool = NULL;
-    if (got >= 6 && !memcmp(magic, "\xfd" "7zXZ\0", 6)) tool = "xz -dc -- ";
+    if (got >= 6 && !memcmp(magic, "\xfd" "7zXZ\0", 6)) tool = "xz -dc -T0 -- ";          /* xz >= 5.4 decodes the blocks of a multi-block file (what `xz -T0` writes) on all cores */
     else if (got >= 3 && !memcmp(magic, "BZh", 3)) tool = "bzip2 -dc -- ";
     if (tool) {
         char* q = shell_quote(path);

@@ -234,7 +234,7 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
     CK_(replay_setup(c->K));
     CK_(cudaMalloc(&c->d_bstate, 32)); CK_(cudaMalloc(&c->d_spec, 16));
     CK_(cudaMalloc(&c->d_counters, 64)); CK_(cudaMalloc(&c->d_nacc, 64)); CK_(cudaMalloc(&c->d_ipc, 64 * MAX_RANKS + 64));
-    CK_(cudaMemset(c->d_counters, 0, 64));
+    CK_(cudaMemsetAsync(c->d_counters, 0, 64, c->st)); CK_(cudaStreamSynchronize(c->st));
     CK_(cudaMallocHost(&c->h_pinned, 2048));
 #undef CK_
     *out = c;
@@ -337,17 +337,20 @@ static int ensure_db2(uvg_ctx* c)
     const size_t pairs_old = (size_t)(c->db2_cap / (GROUP * RPL)), pairs_new = (size_t)(c->db_cap / (GROUP * RPL));
     uint8_t* n = nullptr;
     UVG_CUDA(c, cudaMalloc(&n, pairs_new * per_pair));
-    if (c->d_db2 && c->db2_cap) UVG_CUDA(c, cudaMemcpy(n, c->d_db2, pairs_old * per_pair, cudaMemcpyDeviceToDevice));
-    UVG_CUDA(c, cudaMemset(n + pairs_old * per_pair, 0, (pairs_new - pairs_old) * per_pair));
+    // stream-ordered on c->st and waited for: the context's streams are non-blocking, a memset on the NULL stream is NOT ordered
+    // before the derive kernel that follows (r02: a late memset zeroed freshly derived planes, one test in 357, timing dependent)
+    if (c->d_db2 && c->db2_cap) UVG_CUDA(c, cudaMemcpyAsync(n, c->d_db2, pairs_old * per_pair, cudaMemcpyDeviceToDevice, c->st));
+    UVG_CUDA(c, cudaMemsetAsync(n + pairs_old * per_pair, 0, (pairs_new - pairs_old) * per_pair, c->st));
     // the per-reference plane totals are re-derived with the planes: new array, the resident range is filled by the caller
     // (uvg_set_queries) or was filled by earlier pushes and is copied
     int32_t* cn = nullptr;
     UVG_CUDA(c, cudaMalloc(&cn, (size_t)c->db_cap * 2 * sizeof(int32_t)));
-    UVG_CUDA(c, cudaMemset(cn, 0, (size_t)c->db_cap * 2 * sizeof(int32_t)));
+    UVG_CUDA(c, cudaMemsetAsync(cn, 0, (size_t)c->db_cap * 2 * sizeof(int32_t), c->st));
     if (c->d_ref_cnt && c->db2_cap) {
-        UVG_CUDA(c, cudaMemcpy(cn, c->d_ref_cnt, (size_t)c->db2_cap * 4, cudaMemcpyDeviceToDevice));
-        UVG_CUDA(c, cudaMemcpy(cn + c->db_cap, c->d_ref_cnt + c->db2_cap, (size_t)c->db2_cap * 4, cudaMemcpyDeviceToDevice));
+        UVG_CUDA(c, cudaMemcpyAsync(cn, c->d_ref_cnt, (size_t)c->db2_cap * 4, cudaMemcpyDeviceToDevice, c->st));
+        UVG_CUDA(c, cudaMemcpyAsync(cn + c->db_cap, c->d_ref_cnt + c->db2_cap, (size_t)c->db2_cap * 4, cudaMemcpyDeviceToDevice, c->st));
     }
+    UVG_CUDA(c, cudaStreamSynchronize(c->st));
     cudaFree(c->d_db2); cudaFree(c->d_ref_cnt);
     c->d_db2 = n; c->d_ref_cnt = cn; c->db2_cap = c->db_cap;
     return UVG_OK;
