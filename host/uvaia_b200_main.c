@@ -609,6 +609,8 @@ static void usage(const char* prog, int full)
            "  -t, --nthreads         accepted for compatibility (scoring runs on the GPU)\n"
            "  -o, --output           prefix of xzipped output alignment and table with nearest neighbour sequences\n"
            "      --device           CUDA device ordinal (default 0);  --batch: reference rows per push (default 65536)\n"
+           "      --devices          several GPUs of the box, e.g. 0-7 or 0,2,5: the references are row-sharded over them (the\n"
+           "                         tables do not depend on it; --cache and --max_resident do not apply)\n"
            "      --cache            file that keeps the packed references of this run; a later run over the same reference\n"
            "                         files (same size and mtime, same -A, same mode) reads it instead of parsing them\n");
 }
@@ -754,6 +756,83 @@ static int ball_main(int argc, char** argv)
     return EXIT_SUCCESS;
 }
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * --devices: the database row-sharded over several GPUs of the box inside ONE process -- one host thread and one
+ * uvg_ctx per GPU.  The main thread cuts every batch of the reader into runs of rows that belong to one
+ * rank (uniform rounds of MG_ROUND accepted references per rank, dealt in file order: uvg_shard_of with n_total = -1)
+ * and hands them to the rank threads, which copy, filter and encode them concurrently; the search runs when the
+ * last file has been read (the contexts run the pool-independent closed form and count hazard-H1 flags).
+ * ------------------------------------------------------------------------------------------------------------- */
+static long MG_ROUND = 16384;             /* accepted references per GPU and round; UVG_MG_ROUND overrides (multiple of 64: the tests use small rounds) */
+enum { MG_QUIT = 0, MG_PUSH, MG_MARK, MG_SEARCH, MG_EVER };
+typedef struct {
+    int rank, world;
+    uvg_params prm;
+    const unsigned char* qtext; int nq;
+    unsigned char nccl_id[128];
+    uvg_ctx* ctx; uvg_query_info qi;
+    pthread_t th; sem_t go, done;
+    int job, busy;
+    const unsigned char* text; long n; int min_non_n; int64_t count, n_acc; uint8_t* flags;
+    char err[600]; int failed;
+} mg_rank_t;
+
+static void mg_fail(mg_rank_t* r, const char* what) { snprintf(r->err, sizeof r->err, "GPU %d (rank %d): %s: %s", r->prm.device, r->rank, what, uvg_last_error(r->ctx)); r->failed = 1; }
+static void* mg_thread(void* arg)
+{
+    mg_rank_t* r = arg;
+    if (uvg_create(&r->prm, &r->ctx)) { snprintf(r->err, sizeof r->err, "GPU %d: %s", r->prm.device, uvg_last_error(NULL)); r->failed = 1; }
+    else if (uvg_nccl_init(r->ctx, r->nccl_id)) mg_fail(r, "uvg_nccl_init");
+    else if (uvg_set_queries(r->ctx, r->qtext, r->nq, &r->qi)) mg_fail(r, "uvg_set_queries");      /* rank 0 prepares, the others receive by broadcast */
+    sem_post(&r->done);
+    for (;;) {
+        sem_wait(&r->go);
+        if (r->job == MG_QUIT) break;
+        if (!r->failed) {
+            if (r->job == MG_PUSH) { r->n_acc = 0; if (uvg_push_refs(r->ctx, r->text, r->n, r->min_non_n, NULL, NULL, &r->n_acc)) mg_fail(r, "uvg_push_refs"); }
+            else if (r->job == MG_MARK) { if (uvg_mark_file_end(r->ctx, r->count)) mg_fail(r, "uvg_mark_file_end"); }
+            else if (r->job == MG_SEARCH) { if (uvg_set_global_count(r->ctx, r->count) || uvg_search(r->ctx)) mg_fail(r, "uvg_search"); }
+            else if (r->job == MG_EVER) { if (r->count && uvg_get_ever_best(r->ctx, 0, r->count, r->flags)) mg_fail(r, "uvg_get_ever_best"); }
+        }
+        sem_post(&r->done);
+    }
+    return NULL;
+}
+static void mg_wait(mg_rank_t* r) { if (r->busy) { sem_wait(&r->done); r->busy = 0; if (r->failed) die("%s", r->err); } }
+static void mg_submit(mg_rank_t* r, int job) { mg_wait(r); r->job = job; r->busy = 1; sem_post(&r->go); }
+static void mg_all(mg_rank_t* rk, int G, int job, int64_t count)
+{
+    for (int g = 0; g < G; ++g) { mg_wait(&rk[g]); rk[g].count = count; mg_submit(&rk[g], job); }
+    for (int g = 0; g < G; ++g) mg_wait(&rk[g]);
+}
+/* valid_ref_sites of the rows of a batch on host threads (quick_count_sequence_non_N, fastaseq.c:642-648): the host has to
+ * know which rows the filter accepts before it can deal them out by accepted ordinal */
+typedef struct { const unsigned char* text; long a, b; int L; int* out; } nn_job_t;
+static void* nn_worker(void* arg)
+{
+    nn_job_t* j = arg;
+    for (long i = j->a; i < j->b; ++i) {
+        const unsigned char* row = j->text + (size_t)i * j->L;
+        int c = 0;
+        for (int k = 0; k < j->L; ++k) c += g_validtxt[row[k]];
+        j->out[i] = c;
+    }
+    return NULL;
+}
+static void batch_non_n(const unsigned char* text, long n, int L, int* out)
+{
+    long T = sysconf(_SC_NPROCESSORS_ONLN) - 1;
+    if (T > 32) T = 32;
+    if (T > n / 64) T = n / 64;
+    if (T < 2) { nn_job_t j = {text, 0, n, L, out}; nn_worker(&j); return; }
+    pthread_t th[32]; nn_job_t job[32];
+    for (long t = 0; t < T; ++t) {
+        job[t] = (nn_job_t){text, n * t / T, n * (t + 1) / T, L, out};
+        if (pthread_create(&th[t], NULL, nn_worker, &job[t])) die("cannot start a worker thread");
+    }
+    for (long t = 0; t < T; ++t) pthread_join(th[t], NULL);
+}
+
 /* what omp_get_max_threads() answers in the reference program before -t is applied (nearest.c:81): OMP_NUM_THREADS when it
  * is set, else the processors this process may run on */
 static int omp_max_threads_like(void)
@@ -775,6 +854,7 @@ int main(int argc, char** argv)
         if (argc > 1 && !strcmp(argv[1], "ball")) { argv[1] = argv[0]; return ball_main(argc - 1, argv + 1); }
     }
     int nbest = 100, trim = 0, acgt = 0, xclude = 0, pool = 0, device = 0, hires = 0;
+    int devs[8], n_dev = 0;                                                     /* --devices: row sharding over several GPUs */
     long batch_rows = 65536, max_resident = 1 << 20;
     const char* cache_path = NULL;
     int parse_only = 0;
@@ -785,7 +865,7 @@ int main(int argc, char** argv)
         {"help", 0, 0, 'h'}, {"version", 0, 0, 'v'}, {"acgt", 0, 0, 1000}, {"keep_resolved", 0, 0, 'k'}, {"exclude_self", 0, 0, 'x'},
         {"nbest", 1, 0, 'n'}, {"trim", 1, 0, 1001}, {"query_ambiguity", 1, 0, 'a'}, {"ref_ambiguity", 1, 0, 'A'}, {"pool", 1, 0, 'p'},
         {"reference", 1, 0, 'r'}, {"nthreads", 1, 0, 't'}, {"output", 1, 0, 'o'}, {"device", 1, 0, 1002}, {"batch", 1, 0, 1003},
-        {"max_resident", 1, 0, 1004}, {"cache", 1, 0, 1005}, {"parse_only", 0, 0, 1006}, {0, 0, 0, 0}};
+        {"max_resident", 1, 0, 1004}, {"cache", 1, 0, 1005}, {"parse_only", 0, 0, 1006}, {"devices", 1, 0, 1007}, {0, 0, 0, 0}};
     int ch;
     while ((ch = getopt_long(argc, argv, "hvkxn:a:A:p:r:t:o:", lo, NULL)) != -1) {
         switch (ch) {
@@ -807,6 +887,18 @@ int main(int argc, char** argv)
         case 1004: max_resident = atol(optarg); break;
         case 1005: cache_path = optarg; break;
         case 1006: parse_only = 1; break;
+        case 1007: {                                                            /* "0,1,2" or "0-7" */
+            n_dev = 0;
+            for (const char* c = optarg; *c && n_dev < 8;) {
+                const int a = atoi(c);
+                while (*c >= '0' && *c <= '9') ++c;
+                int b = a;
+                if (*c == '-') { b = atoi(++c); while (*c >= '0' && *c <= '9') ++c; }
+                for (int d = a; d <= b && n_dev < 8; ++d) devs[n_dev++] = d;
+                if (*c == ',') ++c; else if (*c) { usage(argv[0], 0); return EXIT_FAILURE; }
+            }
+            break;
+        }
         default: usage(argv[0], 0); return EXIT_FAILURE;
         }
     }
@@ -857,7 +949,11 @@ int main(int argc, char** argv)
     prm.abi_version = UVG_ABI_VERSION; prm.nchar = L; prm.trim = trim; prm.nbest = nbest; prm.acgt_mode = acgt; prm.pool = pool; prm.device = device;
     uvg_ctx* gpu = NULL;
     uvg_query_info qi;
-    if (uvg_create(&prm, &gpu)) die("%s", uvg_last_error(NULL));
+    const int multi = n_dev > 1;
+    if (multi && getenv("UVG_MG_ROUND") && atol(getenv("UVG_MG_ROUND")) >= 64) MG_ROUND = atol(getenv("UVG_MG_ROUND")) / 64 * 64;
+    if (n_dev == 1) prm.device = device = devs[0];
+    if (multi && cache_path) { fprintf(stderr, "Note: --cache is ignored with --devices.\n"); cache_path = NULL; }
+    if (!multi && uvg_create(&prm, &gpu)) die("%s", uvg_last_error(NULL));
     if (hires) {                                                                /* nearest.c:219-224 */
         uint8_t* keep = xmalloc(q.n);
         int n_kept = 0;
@@ -872,7 +968,25 @@ int main(int argc, char** argv)
         free(keep);
         fprintf(stderr, "Updated query database composed of %d valid references, after removing redundant (less resolved) sequences.\n", q.n);
     }
-    if (uvg_set_queries(gpu, q.text, q.n, &qi)) die("%s", uvg_last_error(gpu));
+    mg_rank_t rk[8];
+    memset(rk, 0, sizeof rk);
+    if (multi) {
+        /* one thread + one context per GPU; the query planes are prepared by rank 0 and broadcast over NVLink */
+        unsigned char id[128];
+        if (uvg_nccl_unique_id(id)) die("%s", uvg_last_error(NULL));
+        for (int g = 0; g < n_dev; ++g) {
+            rk[g].rank = g; rk[g].world = n_dev; rk[g].prm = prm;
+            rk[g].prm.device = devs[g]; rk[g].prm.rank = g; rk[g].prm.world = n_dev;
+            rk[g].prm.first_round = (int32_t)MG_ROUND; rk[g].prm.max_round = (int32_t)MG_ROUND; rk[g].prm.nominal_tail = 1;
+            rk[g].qtext = q.text; rk[g].nq = q.n; memcpy(rk[g].nccl_id, id, 128);
+            sem_init(&rk[g].go, 0, 0); sem_init(&rk[g].done, 0, 0);
+            rk[g].busy = 1;
+            if (pthread_create(&rk[g].th, NULL, mg_thread, &rk[g])) die("cannot start the thread of GPU %d", devs[g]);
+        }
+        for (int g = 0; g < n_dev; ++g) mg_wait(&rk[g]);
+        gpu = rk[0].ctx; qi = rk[0].qi;
+        fprintf(stderr, "The reference sequences are row-sharded over %d GPUs (rounds of %ld accepted references per GPU).\n", n_dev, MG_ROUND);
+    } else if (uvg_set_queries(gpu, q.text, q.n, &qi)) die("%s", uvg_last_error(gpu));
     fprintf(stderr, "Query sequence alignment: %d segregating, %d non-segregating sites with indels, and %d constant sites (all are used in comparisons)\n",
             qi.n_idx, qi.n_idx_m, qi.n_idx_c);                                  /* fastaseq.c:774 */
     fprintf(stderr, acgt ? "Considering ACGT differences only (excluding all other characters). \n"
@@ -893,6 +1007,7 @@ int main(int argc, char** argv)
     uint8_t* push_ok = NULL; int64_t n_pushed = 0, push_cap = 0;                /* per pushed row, in stream order: accepted by the filter */
     long n_invalid = 0, count = 0, same_name = 0;
     uint8_t* rec_ok = NULL; int64_t n_rec = 0;
+    int* mg_nonn = NULL; int64_t mg_mark[1100]; int mg_n_mark = 0;              /* --devices: valid_ref_sites of a batch; accepted counts at the file ends */
     void* pinned_text[2] = {NULL, NULL}; char** batch_names[2] = {NULL, NULL};
     FILE* cache_in = NULL;
     cache_writer_t cw;
@@ -973,10 +1088,47 @@ int main(int argc, char** argv)
         for (int k = 0;; k ^= 1) {
             sem_wait(&sp.full_slots);
             batch_t* bt = &sp.batch[k];
+            if (multi && bt->n > 0) {
+                /* which rows the filter accepts (host threads), then runs of rows per rank: accepted ordinal o belongs to rank
+                 * (o / MG_ROUND) % G (uniform rounds in file order); rows the filter drops travel with the run they fall into
+                 * and are dropped again by the rank's encoder (same rule) */
+                if (!mg_nonn) mg_nonn = xmalloc(batch_rows * sizeof *mg_nonn);
+                batch_non_n(bt->text, bt->n, L, mg_nonn);
+                if (n_acc_total + bt->n > rname_cap) { rname_cap = 2 * (n_acc_total + bt->n) + 1024; rname = xrealloc(rname, rname_cap * sizeof *rname); }
+                if (n_pushed + bt->n > push_cap) { push_cap = 2 * (n_pushed + bt->n) + 1024; push_ok = xrealloc(push_ok, push_cap); }
+                long run0 = 0; int run_rank = -1; int64_t run_acc = 0;
+                int fe = 0;
+                for (long i = 0; i <= bt->n; ++i) {
+                    while (fe < bt->n_fend && bt->fend[fe] == i) { mg_mark[mg_n_mark++] = n_acc_total; ++fe; }      /* a file ends before row i */
+                    const int ok = i < bt->n && mg_nonn[i] >= min_non_n;
+                    const int r = ok ? (int)((n_acc_total / MG_ROUND) % n_dev) : run_rank;
+                    if (i == bt->n || (ok && run_rank >= 0 && r != run_rank)) {
+                        if (run_rank >= 0 && i > run0) {                       /* close the run [run0, i) */
+                            mg_rank_t* t = &rk[run_rank];
+                            mg_wait(t);
+                            if (t->n_acc != t->count) die("GPU %d accepted %lld of a run of references, the host counted %lld", t->prm.device, (long long)t->n_acc, (long long)t->count);
+                            t->text = bt->text + (size_t)run0 * L; t->n = i - run0; t->min_non_n = min_non_n; t->count = run_acc;
+                            mg_submit(t, MG_PUSH);
+                        }
+                        run0 = i; run_acc = 0; run_rank = -1;
+                        if (i == bt->n) break;
+                    }
+                    if (i < bt->n) {
+                        push_ok[n_pushed++] = (uint8_t)ok;
+                        if (ok) { if (run_rank < 0) run_rank = r; rname[n_acc_total++] = bt->name[i]; ++run_acc; } else { free(bt->name[i]); ++n_invalid; }
+                    }
+                }
+                for (int g = 0; g < n_dev; ++g) {                              /* the batch buffer goes back to the reader: everything pushed */
+                    mg_wait(&rk[g]);
+                    if (rk[g].n_acc != rk[g].count) die("GPU %d accepted %lld of a run of references, the host counted %lld", rk[g].prm.device, (long long)rk[g].n_acc, (long long)rk[g].count);
+                    rk[g].n_acc = rk[g].count = 0;
+                }
+                bt->n = 0;
+            }
             /* the rows of a batch go to the device in pieces that end where a file ends: uvg_mark_file_end tells the library
              * where the reference's --pool batches restart (nearest.c:245-286) */
             long row0 = 0;
-            for (int fe = 0; fe <= bt->n_fend; ++fe) {
+            for (int fe = 0; !multi && fe <= bt->n_fend; ++fe) {
                 const long row1 = fe < bt->n_fend ? bt->fend[fe] : bt->n, m = row1 - row0;
                 if (m > 0) {
                     int64_t na = 0;
@@ -1022,14 +1174,23 @@ int main(int argc, char** argv)
     }
     fprintf(stderr, "Total of %ld sequences read; %ld too ambiguous (excluded). %.3lf secs elapsed. \n", count, n_invalid, now_s() - t0);
     if (xclude) fprintf(stderr, " %ld reference sequences already present in query alignment (based on name only).\n", same_name);
-    if (uvg_wait(gpu)) die("%s", uvg_last_error(gpu));
+    uint8_t* best = xmalloc((size_t)n_acc_total + 1);
+    long long mg_flags = 0;
+    if (multi) {
+        uint8_t* scratch = xmalloc((size_t)n_acc_total + 1);
+        for (int k = 0; k < mg_n_mark; ++k) mg_all(rk, n_dev, MG_MARK, mg_mark[k]);
+        mg_all(rk, n_dev, MG_SEARCH, n_acc_total);                              /* collective: rounds over all shards, tables to every rank */
+        for (int g = 0; g < n_dev; ++g) rk[g].flags = g ? scratch : best;       /* collective: the ranks' ever-best flags are combined */
+        mg_all(rk, n_dev, MG_EVER, n_acc_total);
+        for (int g = 0; g < n_dev; ++g) { uvg_stats sg; if (!uvg_get_stats(rk[g].ctx, &sg)) mg_flags += sg.n_h1_flags; }
+        free(scratch);
+    } else if (uvg_wait(gpu)) die("%s", uvg_last_error(gpu));
 
     /* 3. <prefix>.aln.xz: every reference that ever entered a heap, in file order (nearest.c:303-314).  The text is not
      * kept on the host: the reference files are streamed a second time and the flagged records are written. */
     uvg_stats st;
     if (uvg_get_stats(gpu, &st)) die("%s", uvg_last_error(gpu));
-    uint8_t* best = xmalloc((size_t)n_acc_total + 1);
-    if (n_acc_total && uvg_get_ever_best(gpu, 0, n_acc_total, best)) die("%s", uvg_last_error(gpu));
+    if (!multi && n_acc_total && uvg_get_ever_best(gpu, 0, n_acc_total, best)) die("%s", uvg_last_error(gpu));
     size_t plen = strlen(out_prefix);
     char* outname = xmalloc(plen + 16);
     sprintf(outname, "%s.aln.xz", out_prefix);
@@ -1052,7 +1213,10 @@ int main(int argc, char** argv)
     fprintf(stderr, "Total of %ld sequences read; %ld saved sequences include closest neighbours and intermediate, %ld too ambiguous (excluded). "
                     "Highest number of ACGT mismatches = %lld in current neighbourhood.\n", count, n_output, n_invalid, (long long)st.max_mismatch);
     fprintf(stderr, "Saved %ld sequences to file %s , %.3lf secs elapsed.\n", n_output, outname, now_s() - t0);
-    if (st.n_h1_flags)
+    if (multi && mg_flags)
+        fprintf(stderr, "Note: %lld admissions may depend on --pool in the reference program (its consensus stage truncates per batch); sharded searches give "
+                        "the pool-independent table (= --pool 1).  Run on one GPU for the table of --pool %d.\n", mg_flags, pool);
+    if (!multi && st.n_h1_flags)
         fprintf(stderr, "Note: %lld pairs were scored with consensus counts truncated at the batch-wide limit, as the reference program does "
                         "with --pool %d (its table depends on the pool size for this input).\n", (long long)st.n_h1_flags, pool);
 
@@ -1082,7 +1246,11 @@ int main(int argc, char** argv)
     }
     fprintf(stderr, "Saved distance table to file %s , %.3lf secs elapsed.\n", outname, now_s() - t0);
 
-    uvg_destroy(gpu);
+    if (multi) {
+        for (int g = 0; g < n_dev; ++g) { mg_submit(&rk[g], MG_QUIT); pthread_join(rk[g].th, NULL); }
+        for (int g = 0; g < n_dev; ++g) uvg_destroy(rk[g].ctx);
+    } else uvg_destroy(gpu);
+    free(mg_nonn);
     for (int k = 0; k < 2; ++k) { uvg_host_free_pinned(pinned_text[k]); free(batch_names[k]); }
     for (int64_t i = 0; i < n_acc_total; ++i) free(rname[i]);
     for (int i = 0; i < q.n; ++i) free(q.name[i]);

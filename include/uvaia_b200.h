@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define UVG_ABI_VERSION 2
+#define UVG_ABI_VERSION 3
 
 enum { UVG_OK = 0, UVG_EINVAL = -1, UVG_ENODEV = -2, UVG_ENOMEM = -3, UVG_ECUDA = -4, UVG_ESTATE = -5, UVG_ENCCL = -6 };
 
@@ -67,6 +67,10 @@ typedef struct uvg_params {
                                uvg_stats.n_h1_flags counts the pairs the reference might have scored differently (0 => the
                                table is the reference's for every --pool).  Sharded contexts (world > 1) always run this form. */
     int64_t db_capacity;    /* references to reserve HBM for (0 = grow on demand) */
+    int32_t nominal_tail;   /* sharded: 1 = the last round keeps its nominal size (the first ranks take what is left), for hosts that
+                               deal the rows out while they stream the files and do not know the total: uvg_shard_of with
+                               n_total = -1 is their distribution.  0 = the last round is cut evenly (needs the total up front) */
+    int32_t reserved2;      /* must be 0 */
 } uvg_params;
 
 typedef struct uvg_query_info {

@@ -17,8 +17,8 @@ BIN = os.path.join(ROOT, "uvaia_b200", "bin", "uvaia_b200")
 NON_H1 = [n for n in case_names() if not Case(n).h1]
 
 
-def run(args, cwd=None):
-    return subprocess.run([BIN] + args, stdout=subprocess.PIPE, stderr=subprocess.PIPE, cwd=cwd, timeout=600)
+def run(args, cwd=None, env=None):
+    return subprocess.run([BIN] + args, stdout=subprocess.PIPE, stderr=subprocess.PIPE, cwd=cwd, timeout=600, env=env)
 
 
 def test_binary_is_built():
@@ -216,3 +216,24 @@ def test_host_program_ball_mode_reproduces_uvaiaball(name, tmp_path):
     for ln in c.meta.get("reference_stderr", []):
         if "Query database now composed" in ln:
             assert ln.strip().encode() in p.stderr             # same query set after the pruning
+
+
+# ---- --devices: the same program with the references row-sharded over several GPUs inside one process ----
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", [n for n in NON_H1 if n not in ("real_c1_full_reversed",)])
+def test_host_program_on_two_gpus(name, tmp_path):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least 2 GPUs")
+    c = Case(name)
+    args = list(c.args)
+    for rf in c.ref_files:
+        args += ["-r", rf]
+    prefix = str(tmp_path / "out")
+    p = run(args + ["-o", prefix, "--batch", "257", "--devices", "0,1", c.query_file], env=dict(os.environ, UVG_MG_ROUND="64"))   # small rounds: both GPUs get rows
+    assert p.returncode == 0, p.stderr.decode(errors="replace")[-2000:]
+    assert b"row-sharded over 2 GPUs" in p.stderr
+    csv = lzma.open(prefix + ".csv.xz", "rb").read().decode()
+    assert csv == c.expected_csv
+    aln = read_fasta_text(lzma.open(prefix + ".aln.xz", "rb").read())
+    assert [r[0].encode() for r in aln] == c.expected_aln_names

@@ -11,7 +11,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("UVG_LIB") or os.path.join(_HERE, "lib", "libuvaia_b200.so")     # UVG_LIB: kernel-variant experiments
 
-UVG_ABI_VERSION = 2
+UVG_ABI_VERSION = 3
 
 
 class uvg_item(C.Structure):
@@ -22,7 +22,8 @@ class uvg_params(C.Structure):
     _fields_ = [("abi_version", C.c_int32), ("nchar", C.c_int32), ("trim", C.c_int32), ("nbest", C.c_int32),
                 ("acgt_mode", C.c_int32), ("pool", C.c_int32), ("device", C.c_int32), ("first_round", C.c_int32),
                 ("max_round", C.c_int32), ("early_abort", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
-                ("pair_kernel", C.c_int32), ("closed_form", C.c_int32), ("db_capacity", C.c_int64)]
+                ("pair_kernel", C.c_int32), ("closed_form", C.c_int32), ("db_capacity", C.c_int64),
+                ("nominal_tail", C.c_int32), ("reserved2", C.c_int32)]
 
 
 class uvg_ball_params(C.Structure):

@@ -23,6 +23,7 @@
 #include <thread>
 #include <vector>
 #include <dlfcn.h>
+#include <unistd.h>
 
 using namespace uvg;
 
@@ -113,6 +114,7 @@ struct uvg_ctx {
     uint4* d_tiles = nullptr; size_t tile_elems = 0;  // one buffer = tile_elems uint4
     size_t tiles_alloc = 0;                           // uint4 elements allocated (single GPU: kept across query sets)
     uint4* peer_tiles[MAX_RANKS]{};                   // base of d_tiles on every rank (peer-mapped)
+    bool peer_ipc[MAX_RANKS]{};                       // mapped through a CUDA IPC handle (another process): closed with cudaIpcCloseMemHandle
     bool peers_ready = false;
     unsigned long long* d_counters = nullptr;
     unsigned long long* h_pinned = nullptr;           // small pinned read-back area
@@ -167,7 +169,7 @@ static int32_t round_size_next(int32_t cur, int32_t mx) { int64_t n = (int64_t)c
 // of the tail (ceil(remaining / world) rounded up to a block's 64 references); total < 0 = unknown: nominal size
 static int64_t round_size_at(int64_t S, int64_t T, int64_t total, int world)
 {
-    if (total < 0 || S + (int64_t)world * T <= total) return T;
+    if (total < 0 || world < 0 || S + (int64_t)world * T <= total) return T;
     const int64_t rem = total - S, per = GROUP * RPL;
     return std::min<int64_t>(T, std::max<int64_t>(per, ((rem + world - 1) / world + per - 1) / per * per));
 }
@@ -233,7 +235,7 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
     CK_(pairpivot_setup());
     CK_(replay_setup(c->K));
     CK_(cudaMalloc(&c->d_bstate, 32)); CK_(cudaMalloc(&c->d_spec, 16));
-    CK_(cudaMalloc(&c->d_counters, 64)); CK_(cudaMalloc(&c->d_nacc, 64)); CK_(cudaMalloc(&c->d_ipc, 64 * MAX_RANKS + 64));
+    CK_(cudaMalloc(&c->d_counters, 64)); CK_(cudaMalloc(&c->d_nacc, 64)); CK_(cudaMalloc(&c->d_ipc, 96 * MAX_RANKS + 96));
     CK_(cudaMemsetAsync(c->d_counters, 0, 64, c->st)); CK_(cudaStreamSynchronize(c->st));
     CK_(cudaMallocHost(&c->h_pinned, 2048));
 #undef CK_
@@ -244,8 +246,8 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
 static void close_peers(uvg_ctx* c)
 {
     for (int r = 0; r < MAX_RANKS; ++r) {
-        if (c->peer_tiles[r] && r != c->rank && c->world > 1) cudaIpcCloseMemHandle(c->peer_tiles[r]);
-        c->peer_tiles[r] = nullptr;
+        if (c->peer_tiles[r] && r != c->rank && c->world > 1 && c->peer_ipc[r]) cudaIpcCloseMemHandle(c->peer_tiles[r]);
+        c->peer_tiles[r] = nullptr; c->peer_ipc[r] = false;
     }
     c->peers_ready = false;
 }
@@ -1335,20 +1337,34 @@ static int event_pair(uvg_ctx* c, size_t idx, cudaEvent_t* a, cudaEvent_t* b)
 static int ensure_peers(uvg_ctx* c)
 {
     if (c->peers_ready) return UVG_OK;
-    cudaIpcMemHandle_t mine;
-    UVG_CUDA(c, cudaIpcGetMemHandle(&mine, c->d_tiles));
-    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    // what every rank publishes: the IPC handle of its score tiles (ranks in other processes map it), and process id, device
+    // and plain pointer (ranks of the SAME process -- one host thread and one context per GPU -- cannot open their own
+    // process's IPC handles: they enable peer access and use the pointer)
+    struct PeerInfo { cudaIpcMemHandle_t handle; int64_t pid; uint64_t ptr; int32_t device; int32_t pad[3]; };
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64 && sizeof(PeerInfo) == 96, "peer record");
+    PeerInfo mine{};
+    UVG_CUDA(c, cudaIpcGetMemHandle(&mine.handle, c->d_tiles));
+    mine.pid = (int64_t)getpid(); mine.ptr = (uint64_t)(uintptr_t)c->d_tiles; mine.device = c->prm.device;
     uint8_t* stage = static_cast<uint8_t*>(c->d_ipc);
-    UVG_CUDA(c, cudaMemcpyAsync(stage, &mine, 64, cudaMemcpyHostToDevice, c->st));
-    UVG_NCCL(c, g_nccl.AllGather(stage, stage + 64, 64, ncclUint8, c->comm, c->st));
-    std::vector<cudaIpcMemHandle_t> all(c->world);
-    UVG_CUDA(c, cudaMemcpyAsync(all.data(), stage + 64, 64 * (size_t)c->world, cudaMemcpyDeviceToHost, c->st));
+    UVG_CUDA(c, cudaMemcpyAsync(stage, &mine, sizeof mine, cudaMemcpyHostToDevice, c->st));
+    UVG_NCCL(c, g_nccl.AllGather(stage, stage + sizeof mine, sizeof mine, ncclUint8, c->comm, c->st));
+    std::vector<PeerInfo> all(c->world);
+    UVG_CUDA(c, cudaMemcpyAsync(all.data(), stage + sizeof mine, sizeof(PeerInfo) * (size_t)c->world, cudaMemcpyDeviceToHost, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
     for (int r = 0; r < c->world; ++r) {
-        if (r == c->rank) { c->peer_tiles[r] = c->d_tiles; continue; }
+        if (r == c->rank) { c->peer_tiles[r] = c->d_tiles; c->peer_ipc[r] = false; continue; }
+        if (all[r].pid == mine.pid) {
+            const cudaError_t e = cudaDeviceEnablePeerAccess(all[r].device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) UVG_CUDA(c, e);
+            cudaGetLastError();
+            c->peer_tiles[r] = reinterpret_cast<uint4*>((uintptr_t)all[r].ptr);
+            c->peer_ipc[r] = false;
+            continue;
+        }
         void* p = nullptr;
-        UVG_CUDA(c, cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess));
+        UVG_CUDA(c, cudaIpcOpenMemHandle(&p, all[r].handle, cudaIpcMemLazyEnablePeerAccess));
         c->peer_tiles[r] = static_cast<uint4*>(p);
+        c->peer_ipc[r] = true;
     }
     c->peers_ready = true;
     return UVG_OK;
@@ -1537,7 +1553,7 @@ static int search_enqueue(uvg_ctx* c)
         UVG_CUDA(c, cudaEventRecord(c->ev_a, c->st));
     }
     for (;;) {
-        const int64_t T = c->world == 1 ? (int64_t)c->next_round : round_size_at(c->round_global_start, c->next_round, c->global_total, c->world);
+        const int64_t T = c->world == 1 ? (int64_t)c->next_round : round_size_at(c->round_global_start, c->next_round, c->prm.nominal_tail ? -1 : c->global_total, c->world);
         int64_t lstart, cnt, rfirst, rcount;
         if (c->world == 1) {
             cnt = std::min<int64_t>(T, c->db_n - c->db_scored);

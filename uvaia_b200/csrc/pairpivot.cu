@@ -51,6 +51,12 @@ struct __align__(16) Stage2 {
 static_assert(sizeof(RefPlanes2) * RPL * W4 == CHUNK2_PLANES && sizeof(Stage2) == QREC_MAX + CHUNK2_STAGED, "ring stage");
 constexpr int PIVOT_MAX_CHUNKS = 256;                                  // < 65,536 columns
 constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(uint64_t) + (PIVOT_MAX_CHUNKS + 4) * sizeof(uint32_t);
+#ifndef PIVOT_UNROLL_UNITS
+#define PIVOT_UNROLL_UNITS 1
+#endif
+#ifndef PIVOT_PRODUCER_SLEEP
+#define PIVOT_PRODUCER_SLEEP 0   // ns the producer thread sleeps between two tests of a stage that is still in use
+#endif
 #ifndef PIVOT_GRANULE
 #define PIVOT_GRANULE 0         // bytes per bulk copy of the reference side of a stage (0 = one copy of 4.5 KB; smaller copies measured slower)
 #endif
@@ -112,7 +118,11 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         if (lane == 0) {
             int s = 0; uint32_t ph = 0;                                      // stage / phase of the chunk being issued
             for (int c = STAGES2; c < p.n_chunks; ++c) {
+#if PIVOT_PRODUCER_SLEEP
+                while (!mbar_test_a(empty_a + (uint32_t)s * 8u, ph)) __nanosleep(PIVOT_PRODUCER_SLEEP);
+#else
                 mbar_wait_a(empty_a + (uint32_t)s * 8u, ph);                 // use c / STAGES2 - 1 of the stage is over
+#endif
                 issue_at(c, s, s_qoff[c], s_qoff[c + 1]);
                 if (++s == STAGES2) { s = 0; ph ^= 1u; }
             }
@@ -128,7 +138,11 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         const uint2 hd = reinterpret_cast<const uint2*>(st.q)[warp];
         const uint32_t hmask = hd.x & 0xffffu, nmask = (hd.x >> 16) & 0xffu;
         const uint4* item = reinterpret_cast<const uint4*>(st.q + QHEAD_BYTES) + (hd.y & 0xffffu);
+#if PIVOT_UNROLL_UNITS
 #pragma unroll
+#else
+#pragma unroll 1                                                             // one copy of the unit body: half the loop's instruction footprint
+#endif
         for (int u = 0; u < W4; ++u) {
             const uint32_t nu = (nmask >> (u * 4)) & 15u;
             if (nu) {                                                        // all-N units: the reference's own unit totals

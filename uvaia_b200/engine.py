@@ -91,13 +91,13 @@ class Ball:
 
 class Engine:
     def __init__(self, nchar, nbest=100, trim=0, acgt=False, pool=512, device=0, first_round=0, max_round=0,
-                 early_abort=False, rank=0, world=1, db_capacity=0, pair_kernel=None, closed_form=False):
+                 early_abort=False, rank=0, world=1, db_capacity=0, pair_kernel=None, closed_form=False, nominal_tail=False):
         if pair_kernel is None:      # test / debug knob: UVG_PAIR_KERNEL=auto|general|pivot (include/uvaia_b200.h, uvg_params.pair_kernel)
             pair_kernel = PAIR_KERNELS[os.environ.get("UVG_PAIR_KERNEL", "auto")]
         self._lib = _capi.lib()
         p = _capi.uvg_params(_capi.UVG_ABI_VERSION, int(nchar), int(trim), int(nbest), int(bool(acgt)), int(pool),
                              int(device), int(first_round), int(max_round), int(bool(early_abort)), int(rank), int(world),
-                             int(pair_kernel), int(bool(closed_form)), int(db_capacity))
+                             int(pair_kernel), int(bool(closed_form)), int(db_capacity), int(bool(nominal_tail)), 0)
         h = C.c_void_p()
         rc = self._lib.uvg_create(C.byref(p), C.byref(h))
         if rc != 0:
