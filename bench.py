@@ -157,7 +157,7 @@ def make_queries(eng, clades, nq, nchar, ambiguous):
     return np.ascontiguousarray(text[order]), [b"Q%06d" % keep[i] for i in order]
 
 
-from uvaia_b200.shard import rank_tiles  # noqa: E402  (round schedule of the row sharding, twin of uvg_shard_of)
+from uvaia_b200.shard import rank_tiles, rounds as shard_rounds  # noqa: E402  (round schedule of the row sharding, twin of uvg_shard_of)
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -441,11 +441,20 @@ def main():
                     eng.search_async()
                 eng.wait()
             else:
-                for gb, cnt in tiles:
-                    eng.push_refs_ptr(host_buf + o * L, cnt, 0)
-                    o += cnt
+                # pipelined sharded host: every rank pushes its tile of round j (copy + encoder) and enqueues the round; the
+                # pair-count launches of round j run under the copies of round j+1.  uvg_set_search_limit keeps a rank from
+                # searching a round whose rows have not arrived everywhere it matters: its own.
                 eng.set_global_count(R)
-                eng.search()
+                for S, T in shard_rounds(R, world, first_round, max_round):
+                    gb = S + rank * T
+                    cnt = max(0, min(gb + T, R) - gb)
+                    if cnt:
+                        eng.push_refs_ptr(host_buf + o * L, cnt, 0)
+                        o += cnt
+                    eng.set_search_limit(min(S + world * T, R))
+                    eng.search_async()
+                eng.set_search_limit(-1)
+                eng.wait()
             t_ps = time.perf_counter() - t1 - t_sq
             heaps = eng.heaps()
             barrier()

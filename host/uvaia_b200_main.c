@@ -1183,6 +1183,7 @@ int main(int argc, char** argv)
         for (int g = 0; g < n_dev; ++g) rk[g].flags = g ? scratch : best;       /* collective: the ranks' ever-best flags are combined */
         mg_all(rk, n_dev, MG_EVER, n_acc_total);
         for (int g = 0; g < n_dev; ++g) { uvg_stats sg; if (!uvg_get_stats(rk[g].ctx, &sg)) mg_flags += sg.n_h1_flags; }
+        fprintf(stderr, "Search over %d GPUs finished, %.3lf secs elapsed.\n", n_dev, now_s() - t0);
         free(scratch);
     } else if (uvg_wait(gpu)) die("%s", uvg_last_error(gpu));
 

@@ -183,6 +183,11 @@ int uvg_nccl_unique_id(void* out128);                          /* 128 bytes, mad
 int uvg_nccl_init(uvg_ctx* ctx, const void* id128);            /* collective over all `world` contexts */
 /* In sharded mode every rank declares how many accepted references exist in total before uvg_search. */
 int uvg_set_global_count(uvg_ctx* ctx, int64_t n_total);
+/* Pipelined sharded hosts: every rank pushes its rows round by round and calls uvg_search_async after each round; only
+ * rounds that end at or below `n_resident` (accepted references, counted over all ranks in file order) are searched by
+ * that call -- the next round's rows may still be crossing PCIe on some rank.  -1 = no limit (the default).  Every rank
+ * passes the same values in the same order (the rounds are collective). */
+int uvg_set_search_limit(uvg_ctx* ctx, int64_t n_resident);
 
 /* ---- radius search: the reference program `uvaiaball` (src/ball.c) ----
  * Which reference sequences are within `dist` differences of SOME query: replaces seq_ball_against_query_structure

@@ -13,6 +13,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--refs", type=int, default=200000)
 ap.add_argument("--queries", type=int, default=1000)
 ap.add_argument("--dir", default=None)
+ap.add_argument("--devices", default=None, help="also run with the references row-sharded over these GPUs, e.g. 0-3")
 a = ap.parse_args()
 L = 29903
 clades = bench.make_model(L)
@@ -38,7 +39,10 @@ import lzma
 import re
 BIN = os.path.join(ROOT, "uvaia_b200", "bin", "uvaia_b200")
 runs = {}
-for label, extra in (("text_serial_parser", ["--serial"]), ("text", []), ("cache_write", ["--cache", os.path.join(wd, "refs.uvg")]), ("cache_read", ["--cache", os.path.join(wd, "refs.uvg")])):
+variants = [("text_serial_parser", ["--serial"]), ("text", []), ("cache_write", ["--cache", os.path.join(wd, "refs.uvg")]), ("cache_read", ["--cache", os.path.join(wd, "refs.uvg")])]
+if a.devices:
+    variants.append(("text_devices_" + a.devices.replace(",", "_"), ["--devices", a.devices]))
+for label, extra in variants:
     t0 = time.perf_counter()
     env = dict(os.environ, UVG_PARSE_TIMING="1")
     if extra == ["--serial"]:
@@ -48,7 +52,7 @@ for label, extra in (("text_serial_parser", ["--serial"]), ("text", []), ("cache
     dt = time.perf_counter() - t0
     err = p.stderr.decode(errors="replace")
     marks = {}
-    for key, pat in (("search_done_s", r"too ambiguous \(excluded\)\. ([0-9.]+) secs elapsed"), ("aln_done_s", r"Saved \d+ sequences to file .* ([0-9.]+) secs elapsed"),
+    for key, pat in (("search_done_s", r"too ambiguous \(excluded\)\. ([0-9.]+) secs elapsed"), ("sharded_search_done_s", r"Search over \d+ GPUs finished, ([0-9.]+) secs elapsed"), ("aln_done_s", r"Saved \d+ sequences to file .* ([0-9.]+) secs elapsed"),
                      ("csv_done_s", r"Saved distance table to file .* ([0-9.]+) secs elapsed")):
         m = re.search(pat, err)
         marks[key] = float(m.group(1)) if m else None

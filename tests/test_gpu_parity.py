@@ -247,6 +247,12 @@ def test_long_alignment_counters_do_not_wrap():
     run_vs_oracle(L=70001, nq=6, nr=96, nbest=4, amb=0.02, seed=77)
 
 
+def test_five_megabase_alignment_vs_oracle():
+    """BASELINE config 5's column count (5 Mb core-genome alignment) with a few queries and references: 19,532 chunks per row,
+    32-bit totals in the pair-count kernel, the literal replay's prefix recount over 39,063 units"""
+    run_vs_oracle(L=5_000_001, nq=3, nr=40, nbest=5, amb=0.001, seed=123)
+
+
 def test_streaming_push_search_drop_equals_resident_search():
     L = 1200
     qn, Q, rn, R = make_inputs(L, 20, 4000, 41, 0.05, 0.02)

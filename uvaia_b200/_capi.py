@@ -75,6 +75,7 @@ SYMBOLS = {
     "uvg_nccl_unique_id": (C.c_int, [_P]),
     "uvg_nccl_init": (C.c_int, [_P, _P]),
     "uvg_set_global_count": (C.c_int, [_P, C.c_int64]),
+    "uvg_set_search_limit": (C.c_int, [_P, C.c_int64]),
     "uvg_ball_create": (C.c_int, [C.POINTER(uvg_ball_params), C.POINTER(_P)]),
     "uvg_ball_destroy": (None, [_P]),
     "uvg_ball_last_error": (C.c_char_p, [_P]),

@@ -105,6 +105,7 @@ struct uvg_ctx {
     bool ever_reduced = true;                         // sharded: the ever-best flags of all ranks have been combined (lazily, uvg_get_ever_best)
     // database (local shard)
     int64_t db_cap = 0, db_n = 0, db_scored = 0, global_base = 0, global_total = -1;
+    int64_t search_limit = -1;                        // sharded, pipelined hosts: only rounds that end at or below this ordinal are searched yet
     uint4* d_db = nullptr;
     int32_t* d_non_n = nullptr;
     uint32_t* d_ramb_off = nullptr; uint32_t* d_ramb_ent = nullptr; int64_t amb_cap = 0, amb_n = 0;
@@ -1159,7 +1160,7 @@ extern "C" int uvg_clear_refs(uvg_ctx* c)
     int rc = sync_all(c);
     if (rc) return rc;
     c->search_open = false; c->n_ev = 0;
-    c->global_base = 0; c->db_n = 0; c->db_scored = 0; c->round_local_start = 0; c->global_total = -1; c->amb_n = 0;
+    c->global_base = 0; c->db_n = 0; c->db_scored = 0; c->round_local_start = 0; c->global_total = -1; c->amb_n = 0; c->search_limit = -1;
     c->file_starts.assign(1, 0);
     return c->n_query ? reset_heaps(c) : UVG_OK;
 }
@@ -1562,6 +1563,7 @@ static int search_enqueue(uvg_ctx* c)
         } else {
             const int64_t S = c->round_global_start;
             if (S >= c->global_total) break;
+            if (c->search_limit >= 0 && std::min(S + (int64_t)c->world * T, c->global_total) > c->search_limit) break;   // its rows are still on their way
             const int64_t gb = S + (int64_t)c->rank * T, ge = std::min(gb + T, c->global_total);
             cnt = std::max<int64_t>(0, ge - gb);
             lstart = c->round_local_start; rfirst = S; rcount = std::min<int64_t>((int64_t)c->world * T, c->global_total - S);
@@ -1810,6 +1812,13 @@ extern "C" int uvg_set_global_count(uvg_ctx* c, int64_t n_total)
 {
     if (!c || n_total < 0) return UVG_EINVAL;
     c->global_total = n_total;
+    return UVG_OK;
+}
+
+extern "C" int uvg_set_search_limit(uvg_ctx* c, int64_t n_resident)
+{
+    if (!c) return UVG_EINVAL;
+    c->search_limit = n_resident < 0 ? -1 : n_resident;
     return UVG_OK;
 }
 

@@ -279,6 +279,10 @@ class Engine:
     def set_global_count(self, n):
         self._ck(self._lib.uvg_set_global_count(self._h, int(n)), "uvg_set_global_count")
 
+    def set_search_limit(self, n):
+        """pipelined sharded hosts: search only the rounds that end at or below accepted ordinal n (-1: no limit)"""
+        self._ck(self._lib.uvg_set_search_limit(self._h, int(n)), "uvg_set_search_limit")
+
     # ---- utilities ----
     def device_alloc(self, nbytes):
         p = self._lib.uvg_device_alloc(self._h, int(nbytes))
