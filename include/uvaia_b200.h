@@ -65,11 +65,14 @@ typedef struct uvg_params {
                                --pool and these file boundaries (uvg_mark_file_end); costs one replay launch per batch.
                                1: pool-independent closed form (= the reference at --pool 1) in one replay launch per round;
                                uvg_stats.n_h1_flags counts the pairs the reference might have scored differently (0 => the
-                               table is the reference's for every --pool).  Sharded contexts (world > 1) always run this form. */
+                               table is the reference's for every --pool).  Sharded contexts (world > 1) emulate the batches
+                               literally for query sets of one tile (at most 63 queries: rank 0 owns them all, truncated
+                               references are read from the rank that holds them over peer memory) and run this form for
+                               larger query sets. */
     int64_t db_capacity;    /* references to reserve HBM for (0 = grow on demand) */
     int32_t nominal_tail;   /* sharded: 1 = the last round keeps its nominal size (the first ranks take what is left), for hosts that
                                deal the rows out while they stream the files and do not know the total: uvg_shard_of with
-                               n_total = -1 is their distribution.  0 = the last round is cut evenly (needs the total up front) */
+                               n_total = -1 is their distribution.  0 = the rounds taper off towards the end of the database and share it evenly (needs the total up front) */
     int32_t reserved2;      /* must be 0 */
 } uvg_params;
 
@@ -163,9 +166,11 @@ int uvg_reset_search(uvg_ctx* ctx);
 
 /* ---- results: replaces heap_finalise_heap_qsort + the reads in save_distance_table (nearest.c:513-547) ----
  * out must hold max(2,nbest) items; rows come in the reference's output order (heap array after the slot0<->slot n
- * swap, then libc qsort with compare_q_item); *n = rows (hazard H2: never the NULL-name rows). */
+ * swap, then qsort with compare_q_item: glibc's qsort is a stable merge sort, so rows that compare equal keep their heap
+ * order -- heaps of up to 2,048 slots are rank-sorted on the device at the end of the search, larger ones by libc qsort on
+ * the host); *n = rows (hazard H2: never the NULL-name rows). */
 int uvg_get_heap(uvg_ctx* ctx, int32_t iq, uvg_item* out, int32_t* n);
-/* Every query's table in one call (one device->host copy, the qsorts on host threads): out holds n_query x max(2,nbest)
+/* Every query's table in one call (one device->host copy of the sorted tables): out holds n_query x max(2,nbest)
  * items, the rows of query iq start at out + iq * max(2,nbest); n[iq] = rows of query iq. */
 int uvg_get_all_heaps(uvg_ctx* ctx, uvg_item* out, int32_t* n);
 /* flags[i] = 1 if accepted reference ordinal first+i ever entered any heap (is_best, nearest.c:303-314).  Sharded contexts:
@@ -175,8 +180,9 @@ int uvg_get_stats(uvg_ctx* ctx, uvg_stats* out);
 
 /* ---- row sharding over several GPUs (one context per GPU / process) ----
  * Round j covers global ordinals [S_j, S_j + world*T_j) and rank g holds [S_j + g*T_j, S_j + (g+1)*T_j), with
- * T_1 = first_round, T_{j+1} = min(4*T_j, max_round); the last round, which the remaining references cannot fill, is cut
- * to ceil(remaining / world) rounded up to 64 so that the tail is shared evenly.  uvg_shard_of maps a global ordinal to
+ * T_1 = first_round, T_{j+1} = min(4*T_j, max_round); once every rank has less than two nominal rounds left, a round takes
+ * half of what is left per rank (rounded up to 64, not below 4,096; the rest when that is at most 4,096), so that the tail
+ * is shared evenly and the last replay, which no pair counting hides, is short.  uvg_shard_of maps a global ordinal to
  * (rank, local index); n_total = accepted references in all (the value given to uvg_set_global_count). */
 int uvg_shard_of(int64_t ordinal, int64_t n_total, int32_t world, int32_t first_round, int32_t max_round, int32_t* rank, int64_t* local);
 int uvg_nccl_unique_id(void* out128);                          /* 128 bytes, made by rank 0, sent to all by the host */

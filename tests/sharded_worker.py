@@ -65,27 +65,26 @@ def run_case(rank, world, L, nq, nr, nbest, acgt=False, amb=0.0, first_round=64,
         if not np.array_equal(np.nonzero(eb)[0], np.array(ref.ever_best, np.int64)):
             bad += 1000
     if rank == 0:
-        # sharded contexts run the pool-independent closed form (uvg_params.closed_form): compare like with like
-        with Engine(L, nbest=nbest, acgt=acgt, pool=64, device=dev, first_round=first_round, max_round=max_round, closed_form=True) as one:
-            one.set_queries(Qo)
-            one.push_refs(Racc, min_non_n)
-            one.search()
-            for iq in range(len(names)):
-                sc, rf = one.heap(iq)
-                if not (np.array_equal(got[iq][0], sc) and np.array_equal(got[iq][1], rf)):
-                    bad += 1
-            if not np.array_equal(eb, one.ever_best(0, total)):
-                bad += 1000
-            i2 = one.set_queries(Qo2)
-            one.search()
-            for iq in range(len(names2)):
-                sc, rf = one.heap(iq)
-                if not (np.array_equal(got2[iq][0], sc) and np.array_equal(got2[iq][1], rf)):
-                    bad += 1
-            if not np.array_equal(eb2, one.ever_best(0, total)):
-                bad += 1000
-            if idx2 != (i2.n_idx, i2.n_idx_m, i2.n_idx_c):
-                bad += 100000
+        # sharded contexts run the pool-independent closed form (uvg_params.closed_form) unless the query set fits one tile
+        # of 64 slots, where they emulate the reference's batches literally like a single GPU does: compare like with like
+        def single_gpu(Qset, want, want_eb):
+            bad = 0
+            with Engine(L, nbest=nbest, acgt=acgt, pool=64, device=dev, first_round=first_round, max_round=max_round, closed_form=len(Qset) >= 64) as one:
+                info = one.set_queries(Qset)
+                one.push_refs(Racc, min_non_n)
+                one.search()
+                for iq in range(len(Qset)):
+                    sc, rf = one.heap(iq)
+                    if not (np.array_equal(want[iq][0], sc) and np.array_equal(want[iq][1], rf)):
+                        bad += 1
+                if not np.array_equal(want_eb, one.ever_best(0, total)):
+                    bad += 1000
+            return bad, (info.n_idx, info.n_idx_m, info.n_idx_c)
+        bad += single_gpu(Qo, got, eb)[0]
+        b2, i2 = single_gpu(Qo2, got2, eb2)
+        bad += b2
+        if idx2 != i2:
+            bad += 100000
     if check_oracle:                                                    # every rank got the same site-set sizes through the broadcast
         c2, x2, xm2, xc2 = orc.partition(Qo2, 0, acgt)
         if idx2 != (len(x2), len(xm2), len(xc2)):
@@ -95,6 +94,69 @@ def run_case(rank, world, L, nq, nr, nbest, acgt=False, amb=0.0, first_round=64,
     if rank == 0:
         print(f"sharded x{world}: L={L} nq={nq} nr={nr} K={nbest} acgt={acgt} amb={amb} rounds {first_round}..{max_round} ea={early_abort}: "
               f"{'OK' if int(t.item()) == 0 else 'FAIL ' + str(int(t.item()))}  rounds={st['n_rounds']} admitted(rank0)={st['n_admitted']}", flush=True)
+    return int(t.item()) == 0
+
+
+def run_literal_case(rank, world, nq, pool, acgt=False, seed=301, first_round=64, max_round=256):
+    """hazard H1 on shards: a query set of one tile (<= 63 queries) runs the literal emulation of the reference's --pool
+    batches on rank 0, with the packed planes of truncated references read from the rank that holds them; results = the
+    oracle's literal mode = a single-GPU context in its default (literal) mode"""
+    L, nbest = 1500, 12
+    m = SynthModel(nsites=L, n_clades=6, seed=seed, clade_subs=12)
+    qn, Q = m.sample(nq, seed + 1, ambiguous_frac=0.0 if seed != 306 else 0.02, prefix="Q")
+    rn, R = m.sample(1300, seed + 2, ambiguous_frac=0.01, prefix="R")
+    rng = np.random.default_rng(seed)
+    for r in R:                                  # N runs anywhere: the consensus-stage mismatches move around
+        for _ in range(int(rng.integers(0, 4))):
+            a = int(rng.integers(0, L - 50))
+            r[a:a + int(rng.integers(5, 200))] = ord("N")
+    qs = [q.tobytes() for q in Q]
+    names, Qo, *_ = orc.prepare_queries(qn, qs, 0, acgt, 0.5)
+    min_non_n = int(L * 0.5)
+    keep = np.nonzero((~orc.INDEL[R]).sum(1) >= min_non_n)[0]
+    Racc = np.ascontiguousarray(R[keep])
+    total = len(Racc)
+    file_end = int((keep < 801).sum())                                   # two -r files: a batch ends with the first file
+    dev = int(os.environ.get("LOCAL_RANK", rank))
+    with Engine(L, nbest=nbest, acgt=acgt, pool=pool, device=dev, first_round=first_round, max_round=max_round, rank=rank, world=world) as eng:
+        eng.set_queries(Qo)
+        for gb, cnt in rank_tiles(total, rank, world, first_round, max_round):
+            nn, acc, na = eng.push_refs(Racc[gb:gb + cnt], min_non_n)
+            assert na == cnt
+        eng.mark_file_end(file_end)
+        uid = [Engine.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        eng.nccl_init(uid[0])
+        eng.set_global_count(total)
+        eng.search()
+        got = [eng.heap(iq) for iq in range(len(names))]
+        eb = eng.ever_best(0, total)
+        st = eng.stats()
+    ref = orc.search(qn, qs, None, nbest=nbest, acgt=acgt, refs=[(rn[:801], [r.tobytes() for r in R[:801]]), (rn[801:], [r.tobytes() for r in R[801:]])],
+                     pool=pool, literal=True)
+    bad = 0
+    for iq in range(len(names)):
+        ws = np.array([w[0] for w in ref.rows[iq]], np.int32).reshape(-1, 6)
+        wr = np.array([w[2] for w in ref.rows[iq]], np.int64)
+        if not (np.array_equal(got[iq][0], ws) and np.array_equal(got[iq][1], wr)):
+            bad += 1
+    if not np.array_equal(np.nonzero(eb)[0], np.array(ref.ever_best, np.int64)):
+        bad += 1000
+    if rank == 0:
+        with Engine(L, nbest=nbest, acgt=acgt, pool=pool, device=dev, first_round=first_round, max_round=max_round) as one:
+            one.set_queries(Qo)
+            one.push_refs(Racc, min_non_n)
+            one.mark_file_end(file_end)
+            one.search()
+            for iq in range(len(names)):
+                sc, rf = one.heap(iq)
+                if not (np.array_equal(got[iq][0], sc) and np.array_equal(got[iq][1], rf)):
+                    bad += 1
+    t = torch.tensor([bad], device=f"cuda:{dev}")
+    dist.all_reduce(t)
+    if rank == 0:
+        print(f"sharded x{world} literal: nq={nq} pool={pool} acgt={acgt} seed={seed}: {'OK' if int(t.item()) == 0 else 'FAIL ' + str(int(t.item()))}"
+              f"  oracle h1 events={ref.h1_events} flags(rank0)={st['n_h1_flags']}", flush=True)
     return int(t.item()) == 0
 
 
@@ -112,6 +174,9 @@ def main():
     # many queries and full-size rounds: the score tiles exceed the 3 GiB a single-GPU context caps them at, and the round
     # schedule of the shards must still be the one uvg_shard_of deals the rows with (first_round, max_round only)
     ok &= run_case(rank, world, 400, 4200, 140000, 10, first_round=16384, max_round=65536, check_oracle=False, seed=11)
+    for nq, pool, acgt, seed in ((1, 1, False, 301), (1, 7, False, 302), (1, 64, True, 303), (2, 7, False, 304), (3, 5, True, 305), (3, 64, False, 306),
+                                 (1, 512, False, 307), (2, 1, True, 308)):
+        ok &= run_literal_case(rank, world, nq, pool, acgt=acgt, seed=seed)
     dist.barrier()
     dist.destroy_process_group()
     if rank == 0:

@@ -402,6 +402,31 @@ def test_pool_dependence_vs_live_reference_binary(nq, acgt, seed, pool):
     assert out.csv(acgt) == want
 
 
+@pytest.mark.parametrize("nbest", [2048, 2500])
+def test_final_tables_sorted_on_device_and_on_host(nbest):
+    """the final order of a table = heap array after the slot swap + a STABLE descending sort (glibc's qsort is a merge
+    sort): up to 2,048 slots k_finalise ranks the rows on the device, larger heaps go through libc qsort on the host.
+    Many identical references (ties in all six keys) on both sides of the limit, uvg_get_heap and uvg_get_all_heaps."""
+    L, nq, nr = 600, 5, 3000
+    qn, Q, rn, R = make_inputs(L, nq, nr, 31, 0.0, 0.0)
+    R[100:900] = R[100]                                  # 800 identical rows
+    R[1500:1800] = R[7]
+    qs = [q.tobytes() for q in Q]
+    ref = orc.search(qn, qs, None, nbest=nbest, refs=[(rn, [r.tobytes() for r in R])], pool=64)
+    names, Qo, *_ = orc.prepare_queries(qn, qs, 0, False, 0.5)
+    with Engine(L, nbest=nbest, pool=64, closed_form=True, first_round=256, max_round=1024) as eng:
+        eng.set_queries(Qo)
+        eng.push_refs(R, 0)
+        eng.search()
+        tables = eng.heaps()
+        for iq in range(len(names)):
+            want = ref.rows[iq]
+            ws = np.array([w[0] for w in want], np.int32).reshape(-1, 6)
+            wr = np.array([w[2] for w in want], np.int64)
+            for sc, rf in (eng.heap(iq), tables[iq]):
+                assert np.array_equal(sc, ws) and np.array_equal(rf, wr), f"query {iq}"
+
+
 def test_pivot_form_resident_db_requery_and_divergent_queries(pair_kernel):
     """pivot form of the pair-count kernel: (1) references pushed BEFORE the queries get their derived planes in
     uvg_set_queries, (2) a second query set on the same resident database re-derives them, (3) queries far from any

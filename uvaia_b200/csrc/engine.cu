@@ -30,6 +30,7 @@ using namespace uvg;
 namespace {
 std::string g_create_error;
 constexpr int NBUF = 2;
+constexpr int FIN_DEVICE_MAX_K = 2048;            // heaps up to this many slots get their final sort on the device (k_finalise), larger ones on the host
 
 // ---- NCCL through dlopen (the library loads without NCCL for single-GPU use) ------------------------------------
 typedef struct ncclComm* ncclComm_t;
@@ -99,6 +100,9 @@ struct uvg_ctx {
     // results of the owned rows in ONE block: heaps [rows_cap][K+1] | heap_n [rows_cap] | max_inc [rows_cap] (own_bytes), so
     // that a sharded search ends with a single all-gather into d_all [world][own_bytes]
     uint8_t* d_own = nullptr; uint8_t* d_all = nullptr; size_t own_bytes = 0, own_off_n = 0, own_off_mi = 0;
+    // final tables of the owned rows (k_finalise), the block that travels: uvg_item [rows_cap][K] | heap_n | max_inc (fin_bytes).
+    // Heaps beyond FIN_DEVICE_MAX_K slots are sorted on the host instead (fin_device false: the raw block travels).
+    uint8_t* d_fin = nullptr; size_t fin_bytes = 0, fin_off_n = 0, fin_off_mi = 0; bool fin_device = false;
     HeapItem* d_heaps = nullptr;                      // = d_own
     int32_t *d_heap_n = nullptr, *d_max_inc = nullptr;    // inside d_own
     int32_t *d_batch_id = nullptr, *d_max_inc_batch = nullptr;
@@ -115,7 +119,12 @@ struct uvg_ctx {
     uint4* d_tiles = nullptr; size_t tile_elems = 0;  // one buffer = tile_elems uint4
     size_t tiles_alloc = 0;                           // uint4 elements allocated (single GPU: kept across query sets)
     uint4* peer_tiles[MAX_RANKS]{};                   // base of d_tiles on every rank (peer-mapped)
-    bool peer_ipc[MAX_RANKS]{};                       // mapped through a CUDA IPC handle (another process): closed with cudaIpcCloseMemHandle
+    bool peer_ipc[MAX_RANKS]{};
+    // sharded literal replay: packed planes and ambiguity lists of every rank (peer-mapped anew by every uvg_search: they move when they grow)
+    const uint4* peer_db[MAX_RANKS]{}; const uint32_t* peer_ramb_off[MAX_RANKS]{}; const uint32_t* peer_ramb_ent[MAX_RANKS]{};
+    bool peer_db_ipc[MAX_RANKS][3]{};
+    bool peer_db_live = false;                        // other ranks hold mappings of d_db / d_ramb_*: growing them defers the free
+    std::vector<void*> deferred_free;                       // mapped through a CUDA IPC handle (another process): closed with cudaIpcCloseMemHandle
     bool peers_ready = false;
     unsigned long long* d_counters = nullptr;
     unsigned long long* h_pinned = nullptr;           // small pinned read-back area
@@ -166,13 +175,19 @@ static int32_t round_size_max(const uvg_params& p)
     return std::max(v, round_size_first(p));
 }
 static int32_t round_size_next(int32_t cur, int32_t mx) { int64_t n = (int64_t)cur * 4; return (int32_t)std::min<int64_t>(n, mx); }
-// sharded mode: the last round, which the remaining references cannot fill, is cut so that every rank gets the same share
-// of the tail (ceil(remaining / world) rounded up to a block's 64 references); total < 0 = unknown: nominal size
+// The rounds taper off towards the end of the database: the replay of a round runs under the pair counting of the next one,
+// except the last replay, which nothing hides -- so once less than two nominal rounds remain, every round takes half of what
+// is left (per rank, rounded up to a block's 64 references, not below ROUND_TAPER_MIN) and the last one is small.  In
+// sharded mode this also shares the tail evenly between the ranks.  total < 0 = unknown (streaming hosts): nominal size.
+constexpr int64_t ROUND_TAPER_MIN = 4096;
 static int64_t round_size_at(int64_t S, int64_t T, int64_t total, int world)
 {
-    if (total < 0 || world < 0 || S + (int64_t)world * T <= total) return T;
-    const int64_t rem = total - S, per = GROUP * RPL;
-    return std::min<int64_t>(T, std::max<int64_t>(per, ((rem + world - 1) / world + per - 1) / per * per));
+    if (total < 0 || world < 1) return T;
+    const int64_t rem = std::max<int64_t>(0, total - S), per = GROUP * RPL;
+    const int64_t share = (rem + world - 1) / world;                          // what every rank still has to score
+    if (share >= 2 * T) return T;
+    const int64_t up = [&](int64_t v) { return std::max<int64_t>(per, (v + per - 1) / per * per); }(share <= ROUND_TAPER_MIN ? share : std::max<int64_t>(ROUND_TAPER_MIN, (share + 1) / 2));
+    return std::min<int64_t>(T, up);
 }
 
 extern "C" int uvg_abi_version(void) { return UVG_ABI_VERSION; }
@@ -209,7 +224,7 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
     c->world = p->world > 1 ? p->world : 1;
     c->next_round = round_size_first(*p);
     if (c->prm.pool < 1) c->prm.pool = 1;
-    c->literal = c->world == 1 && p->closed_form == 0;
+    c->literal = c->world == 1 && p->closed_form == 0;      // sharded: decided per query set (uvg_set_queries)
 #define CK_(call) do { cudaError_t e2_ = (call); if (e2_ != cudaSuccess) { g_create_error = std::string("CUDA: ") + cudaGetErrorString(e2_); delete c; return UVG_ECUDA; } } while (0)
     CK_(cudaSetDevice(p->device));
     cudaDeviceProp prop;
@@ -236,7 +251,7 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
     CK_(pairpivot_setup());
     CK_(replay_setup(c->K));
     CK_(cudaMalloc(&c->d_bstate, 32)); CK_(cudaMalloc(&c->d_spec, 16));
-    CK_(cudaMalloc(&c->d_counters, 64)); CK_(cudaMalloc(&c->d_nacc, 64)); CK_(cudaMalloc(&c->d_ipc, 96 * MAX_RANKS + 96));
+    CK_(cudaMalloc(&c->d_counters, 64)); CK_(cudaMalloc(&c->d_nacc, 64)); CK_(cudaMalloc(&c->d_ipc, 256 * MAX_RANKS + 256));
     CK_(cudaMemsetAsync(c->d_counters, 0, 64, c->st)); CK_(cudaStreamSynchronize(c->st));
     CK_(cudaMallocHost(&c->h_pinned, 2048));
 #undef CK_
@@ -244,8 +259,10 @@ extern "C" int uvg_create(const uvg_params* p, uvg_ctx** out)
     return UVG_OK;
 }
 
+static void close_peer_db(uvg_ctx* c);
 static void close_peers(uvg_ctx* c)
 {
+    close_peer_db(c);
     for (int r = 0; r < MAX_RANKS; ++r) {
         if (c->peer_tiles[r] && r != c->rank && c->world > 1 && c->peer_ipc[r]) cudaIpcCloseMemHandle(c->peer_tiles[r]);
         c->peer_tiles[r] = nullptr; c->peer_ipc[r] = false;
@@ -277,7 +294,7 @@ static void free_queries(uvg_ctx* c, bool final = false)
     cudaFree(c->d_qstream); cudaFree(c->d_qoff); cudaFree(c->d_snp_off); cudaFree(c->d_snp_ent); cudaFree(c->d_pivot); cudaFree(c->d_wslot); c->d_wslot = nullptr;
     c->d_qstream = nullptr; c->d_qoff = c->d_snp_off = c->d_snp_ent = nullptr; c->d_pivot = nullptr;
     cudaFree(c->d_thr_local); for (int b = 0; b < NBUF; ++b) { cudaFree(c->d_thr_all[b]); c->d_thr_all[b] = nullptr; }
-    cudaFree(c->d_own); cudaFree(c->d_all); c->d_own = c->d_all = nullptr;
+    cudaFree(c->d_own); cudaFree(c->d_all); cudaFree(c->d_fin); c->d_own = c->d_all = c->d_fin = nullptr;
     cudaFree(c->d_snap_own); cudaFree(c->d_snap_batch); cudaFree(c->d_ever_round); c->d_snap_own = nullptr; c->d_snap_batch = nullptr; c->d_ever_round = nullptr;
     cudaFree(c->d_batch_id); cudaFree(c->d_max_inc_batch);
     cudaFree(c->d_tiles); c->d_tiles = nullptr; c->tiles_alloc = 0;
@@ -296,6 +313,8 @@ extern "C" void uvg_destroy(uvg_ctx* c)
     if (c->st_push) cudaStreamSynchronize(c->st_push);
     if (c->st_copy) cudaStreamSynchronize(c->st_copy);
     free_queries(c, true);
+    for (void* p : c->deferred_free) cudaFree(p);
+    c->deferred_free.clear();
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->d_db); cudaFree(c->d_db2); cudaFree(c->d_ref_cnt); cudaFree(c->d_non_n); cudaFree(c->d_ramb_off); cudaFree(c->d_ramb_ent); cudaFree(c->d_ever);
     cudaFree(c->d_counters); cudaFree(c->d_nacc); cudaFree(c->d_ipc); cudaFree(c->d_bstate); cudaFree(c->d_spec);
@@ -503,6 +522,12 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     c->n_slots = Q + 1;                                                     // + the consensus pseudo-query (nearest.c:428-433)
     c->n_qtiles = (c->n_slots + QTILE - 1) / QTILE;
     c->rows_cap = (c->n_qtiles + c->world - 1) / c->world * QTILE;
+    // Literal emulation of the reference's --pool batches (hazard H1): on one GPU always (unless closed_form); sharded when all
+    // queries fit one tile of 64 slots -- the searches in which the hazard actually fires (one or a few queries: every site is
+    // a consensus site).  Then rank 0 owns every query, the batch-wide limit is the maximum over ITS rows and nothing has to
+    // cross ranks but the packed planes of a truncated reference (peer-mapped, ensure_peer_db).  Larger sharded query sets
+    // run the closed form and count the flags.
+    c->literal = c->prm.closed_form == 0 && (c->world == 1 || c->n_qtiles == 1);
     c->qnib_stride = (L + 7) / 8;
     c->qinfo.n_query = Q; c->qinfo.nchar = L; c->qinfo.trim = trim;
 
@@ -747,7 +772,12 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
     c->d_heaps = reinterpret_cast<HeapItem*>(c->d_own);
     c->d_heap_n = reinterpret_cast<int32_t*>(c->d_own + c->own_off_n); c->d_max_inc = reinterpret_cast<int32_t*>(c->d_own + c->own_off_mi);
     UVG_CUDA(c, pooled_alloc(c, 10, &c->d_batch_id, (size_t)rows * 4)); UVG_CUDA(c, pooled_alloc(c, 11, &c->d_max_inc_batch, (size_t)rows * 4));
-    if (c->world > 1) UVG_CUDA(c, pooled_alloc(c, 12, &c->d_all, (size_t)c->world * c->own_bytes));
+    c->fin_device = c->K <= FIN_DEVICE_MAX_K;
+    c->fin_off_n = (size_t)rows * c->K * sizeof(uvg_item);
+    c->fin_off_mi = c->fin_off_n + (size_t)rows * 4;
+    c->fin_bytes = (c->fin_off_mi + (size_t)rows * 4 + 15) / 16 * 16;
+    if (c->fin_device) UVG_CUDA(c, pooled_alloc(c, 22, &c->d_fin, c->fin_bytes));
+    if (c->world > 1) UVG_CUDA(c, pooled_alloc(c, 12, &c->d_all, (size_t)c->world * (c->fin_device ? c->fin_bytes : c->own_bytes)));
     if (c->literal) {
         UVG_CUDA(c, pooled_alloc(c, 13, &c->d_snap_own, c->own_bytes));
         UVG_CUDA(c, pooled_alloc(c, 14, &c->d_snap_batch, (size_t)rows * 8));
@@ -762,7 +792,7 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
         // depend on the query set, so the tiles take what max_round asks for (or the allocation fails loudly below).
         if (c->world == 1) cap = std::max<int64_t>(GROUP * RPL, std::min(cap, fit));
         c->seg_cap = cap;
-        if (c->literal) UVG_CUDA(c, pooled_alloc(c, 21, &c->d_ever_round, (size_t)cap));
+        if (c->literal) UVG_CUDA(c, pooled_alloc(c, 21, &c->d_ever_round, (size_t)cap * c->world));      // admissions of one round (all segments)
         c->tile_elems = (size_t)(rows + 2) * c->world * cap;
         if (NBUF * c->tile_elems > c->tiles_alloc) {                       // the multi-GiB buffer is kept when the next query set fits
             if (c->world > 1) close_peers(c);                                // (every rank takes this branch alike: the size depends on shared parameters only);
@@ -957,7 +987,7 @@ extern "C" int uvg_reset_search(uvg_ctx* c)
 // database residency (K1)
 // =====================================================================================================================
 template <typename T>
-static cudaError_t grow_array(T** ptr, size_t old_count, size_t new_count, bool zero_new, cudaStream_t st)
+static cudaError_t grow_array(T** ptr, size_t old_count, size_t new_count, bool zero_new, cudaStream_t st, std::vector<void*>* defer = nullptr)
 {
     T* n = nullptr;
     cudaError_t e = cudaMalloc(&n, new_count * sizeof(T));
@@ -972,7 +1002,8 @@ static cudaError_t grow_array(T** ptr, size_t old_count, size_t new_count, bool 
     }
     e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) return e;
-    cudaFree(*ptr);
+    if (defer && *ptr) defer->push_back(*ptr);      // another rank may still read the old array (ensure_peer_db releases it)
+    else cudaFree(*ptr);
     *ptr = n;
     return cudaSuccess;
 }
@@ -989,9 +1020,10 @@ static int ensure_db_capacity(uvg_ctx* c, int64_t need_refs)
     cap = (cap + GROUP * RPL - 1) / (GROUP * RPL) * (GROUP * RPL);
     const size_t per_group = (size_t)(c->Wp / 4) * NPLANE * GROUP;            // uint4 per group
     const size_t og = (size_t)(c->db_cap / GROUP), ng = (size_t)(cap / GROUP);
-    UVG_CUDA(c, grow_array(&c->d_db, og * per_group, ng * per_group, true, c->st_push));
+    std::vector<void*>* defer = c->peer_db_live ? &c->deferred_free : nullptr;
+    UVG_CUDA(c, grow_array(&c->d_db, og * per_group, ng * per_group, true, c->st_push, defer));
     UVG_CUDA(c, grow_array(&c->d_non_n, (size_t)c->db_cap, (size_t)cap, true, c->st_push));
-    UVG_CUDA(c, grow_array(&c->d_ramb_off, c->db_cap ? (size_t)c->db_cap + 1 : 0, (size_t)cap + 1, true, c->st_push));
+    UVG_CUDA(c, grow_array(&c->d_ramb_off, c->db_cap ? (size_t)c->db_cap + 1 : 0, (size_t)cap + 1, true, c->st_push, defer));
     c->db_cap = cap;
     return ensure_db2(c);
 }
@@ -1004,7 +1036,7 @@ static int ensure_amb_capacity(uvg_ctx* c, int64_t need)
     if (rc) return rc;
     int64_t cap = std::max<int64_t>(need, c->amb_cap * 2);
     cap = std::max<int64_t>(cap, std::max<int64_t>(1 << 16, c->prm.db_capacity * 4));   // ~1.7 codes per SARS-CoV-2 genome
-    UVG_CUDA(c, grow_array(&c->d_ramb_ent, (size_t)c->amb_cap, (size_t)cap, false, c->st_push));
+    UVG_CUDA(c, grow_array(&c->d_ramb_ent, (size_t)c->amb_cap, (size_t)cap, false, c->st_push, c->peer_db_live ? &c->deferred_free : nullptr));
     c->amb_cap = cap;
     return UVG_OK;
 }
@@ -1371,6 +1403,61 @@ static int ensure_peers(uvg_ctx* c)
     return UVG_OK;
 }
 
+// sharded literal replay: every rank maps the packed database of every rank (planes, ambiguity offsets and entries)
+static void close_peer_db(uvg_ctx* c)
+{
+    for (int r = 0; r < MAX_RANKS; ++r) {
+        const void* ptr[3] = {c->peer_db[r], c->peer_ramb_off[r], c->peer_ramb_ent[r]};
+        for (int k = 0; k < 3; ++k) if (ptr[k] && c->peer_db_ipc[r][k]) cudaIpcCloseMemHandle(const_cast<void*>(ptr[k]));
+        c->peer_db[r] = nullptr; c->peer_ramb_off[r] = c->peer_ramb_ent[r] = nullptr;
+        for (int k = 0; k < 3; ++k) c->peer_db_ipc[r][k] = false;
+    }
+}
+static int ensure_peer_db(uvg_ctx* c)
+{
+    struct DbInfo { cudaIpcMemHandle_t handle[3]; uint64_t ptr[3]; int64_t pid; int32_t device; int32_t pad; };
+    static_assert(sizeof(DbInfo) == 232, "peer database record");
+    int rc = sync_all(c);                                                    // nothing of an earlier search reads the old mappings
+    if (rc) return rc;
+    close_peer_db(c);
+    DbInfo mine{};
+    void* own[3] = {c->d_db, c->d_ramb_off, c->d_ramb_ent};
+    for (int k = 0; k < 3; ++k) {
+        mine.ptr[k] = (uint64_t)(uintptr_t)own[k];
+        if (own[k]) UVG_CUDA(c, cudaIpcGetMemHandle(&mine.handle[k], own[k]));
+    }
+    mine.pid = (int64_t)getpid(); mine.device = c->prm.device;
+    uint8_t* stage = static_cast<uint8_t*>(c->d_ipc);
+    UVG_CUDA(c, cudaMemcpyAsync(stage, &mine, sizeof mine, cudaMemcpyHostToDevice, c->st));
+    UVG_NCCL(c, g_nccl.AllGather(stage, stage + sizeof mine, sizeof mine, ncclUint8, c->comm, c->st));
+    std::vector<DbInfo> all(c->world);
+    UVG_CUDA(c, cudaMemcpyAsync(all.data(), stage + sizeof mine, sizeof(DbInfo) * (size_t)c->world, cudaMemcpyDeviceToHost, c->st));
+    UVG_CUDA(c, cudaStreamSynchronize(c->st));
+    // every rank has passed its sync_all: nobody reads an array that was replaced since the last exchange
+    for (void* p : c->deferred_free) cudaFree(p);
+    c->deferred_free.clear();
+    c->peer_db_live = true;
+    for (int r = 0; r < c->world; ++r) {
+        void* got[3] = {nullptr, nullptr, nullptr};
+        for (int k = 0; k < 3; ++k) {
+            if (!all[r].ptr[k]) continue;                                    // that rank holds no references (or no ambiguity entries)
+            if (r == c->rank) got[k] = own[k];
+            else if (all[r].pid == mine.pid) {
+                const cudaError_t e = cudaDeviceEnablePeerAccess(all[r].device, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) UVG_CUDA(c, e);
+                cudaGetLastError();
+                got[k] = reinterpret_cast<void*>((uintptr_t)all[r].ptr[k]);
+            } else {
+                UVG_CUDA(c, cudaIpcOpenMemHandle(&got[k], all[r].handle[k], cudaIpcMemLazyEnablePeerAccess));
+                c->peer_db_ipc[r][k] = true;
+            }
+        }
+        c->peer_db[r] = static_cast<const uint4*>(got[0]);
+        c->peer_ramb_off[r] = static_cast<const uint32_t*>(got[1]); c->peer_ramb_ent[r] = static_cast<const uint32_t*>(got[2]);
+    }
+    return UVG_OK;
+}
+
 static void fill_pair_params(uvg_ctx* c, PairParams& pp, int64_t lb, int64_t le, int buf, int64_t col0)
 {
     pp.db = c->d_db; pp.qdata = c->d_qdata; pp.thr = c->d_thr_all[buf];
@@ -1510,11 +1597,17 @@ static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t
         sr.open_batch = pieces[0].start ? -1 : (int32_t)bounds[0];
         sr.b_prev = c->d_bstate + (i0 + 2) % 3; sr.b_carry = c->d_bstate + 4 + (i0 + 1) % 2; sr.b_acc = c->d_bstate + i0 % 3;
         UVG_CUDA(c, launch_spec_restore(sr, c->st_rp));
-        rp.literal = 1; rp.local_ord0 = c->global_base; rp.spec_flags = c->d_spec + 1;
-        rp.db = c->d_db; rp.qcons = c->d_qdata + (size_t)(c->n_query / QTILE) * c->n_chunks; rp.cons_qi = c->n_query % QTILE;
+        rp.literal = 1; rp.spec_flags = c->d_spec + 1;
+        rp.seg_local0 = lstart;
+        for (int g = 0; g < c->world; ++g) {
+            rp.seg_db[g] = c->world > 1 ? c->peer_db[g] : c->d_db;
+            rp.seg_ramb_off[g] = c->world > 1 ? c->peer_ramb_off[g] : c->d_ramb_off;
+            rp.seg_ramb_ent[g] = c->world > 1 ? c->peer_ramb_ent[g] : c->d_ramb_ent;
+        }
+        rp.qcons = c->d_qdata + (size_t)(c->n_query / QTILE) * c->n_chunks; rp.cons_qi = c->n_query % QTILE;
         rp.cons_nib = c->d_qnib + (size_t)c->n_query * c->qnib_stride;
         rp.camb = c->d_qamb_ent + c->cons_amb_begin; rp.n_camb = (int32_t)c->cons_amb_n;
-        rp.ramb_off = c->d_ramb_off; rp.ramb_ent = c->d_ramb_ent; rp.Wp = c->Wp;
+        rp.Wp = c->Wp;
         for (const Piece& pc : pieces) {
             const int64_t i = c->replay_seq++;
             rp.ord_begin = pc.o; rp.ord_end = pc.e; rp.batch_start = pc.start;
@@ -1531,13 +1624,14 @@ static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t
 }
 
 // enqueue the rounds that cover every resident reference not scored yet; returns without waiting
-static int search_enqueue(uvg_ctx* c)
+static int search_enqueue(uvg_ctx* c, bool taper)
 {
     if (c->n_query == 0) UVG_FAIL(c, UVG_ESTATE, "uvg_search: no queries set");
     if (c->world > 1 && !c->comm) UVG_FAIL(c, UVG_ESTATE, "uvg_search: sharded context without uvg_nccl_init");
     if (c->world > 1 && c->global_total < 0) UVG_FAIL(c, UVG_ESTATE, "uvg_search: sharded context without uvg_set_global_count");
     int rc;
     if (c->world > 1) { rc = ensure_peers(c); if (rc) return rc; }
+    if (c->world > 1 && c->literal) { rc = ensure_peer_db(c); if (rc) return rc; }       // collective: the arrays move when they grow
     const int32_t mx = (int32_t)std::min<int64_t>(round_size_max(c->prm), c->seg_cap);
     if (c->next_round > mx) c->next_round = mx;
     c->heaps_cached = false;
@@ -1554,7 +1648,9 @@ static int search_enqueue(uvg_ctx* c)
         UVG_CUDA(c, cudaEventRecord(c->ev_a, c->st));
     }
     for (;;) {
-        const int64_t T = c->world == 1 ? (int64_t)c->next_round : round_size_at(c->round_global_start, c->next_round, c->prm.nominal_tail ? -1 : c->global_total, c->world);
+        // single GPU: uvg_search knows that the resident rows are all there is and tapers the rounds towards their end;
+        // uvg_search_async (more rows follow) keeps the nominal sizes
+        const int64_t T = c->world == 1 ? (taper ? round_size_at(c->db_scored, c->next_round, c->db_n, 1) : (int64_t)c->next_round) : round_size_at(c->round_global_start, c->next_round, c->prm.nominal_tail ? -1 : c->global_total, c->world);
         int64_t lstart, cnt, rfirst, rcount;
         if (c->world == 1) {
             cnt = std::min<int64_t>(T, c->db_n - c->db_scored);
@@ -1588,7 +1684,7 @@ extern "C" int uvg_search_async(uvg_ctx* c)
 {
     if (!c) return UVG_EINVAL;
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
-    return search_enqueue(c);
+    return search_enqueue(c, false);
 }
 
 extern "C" int uvg_wait(uvg_ctx* c)
@@ -1599,11 +1695,17 @@ extern "C" int uvg_wait(uvg_ctx* c)
     // the search ends when the last replay has finished: join stream B into stream A
     UVG_CUDA(c, cudaEventRecord(c->ev_d, c->st_rp));
     UVG_CUDA(c, cudaStreamWaitEvent(c->st, c->ev_d, 0));
+    if (c->fin_device && c->n_query > 0) {
+        // the final tables are made where the heaps are: slot swap + stable descending sort per row, sizes and limits behind them
+        UVG_CUDA(c, launch_finalise(c->d_heaps, c->d_heap_n, c->K, c->rows_cap, c->d_fin, c->st));
+        UVG_CUDA(c, cudaMemcpyAsync(c->d_fin + c->fin_off_n, c->d_heap_n, (size_t)c->rows_cap * 4, cudaMemcpyDeviceToDevice, c->st));
+        UVG_CUDA(c, cudaMemcpyAsync(c->d_fin + c->fin_off_mi, c->d_max_inc, (size_t)c->rows_cap * 4, cudaMemcpyDeviceToDevice, c->st));
+        c->stats.other_kernel_launches += 1;
+    }
     if (c->world > 1) {
-        // the tables of all queries to every rank (small all-gathers over NVLink), OR of the ever-best flags
         // the tables of all queries to every rank: ONE all-gather over NVLink (heaps, sizes and limits are one block).  The
         // ever-best flags are combined lazily by uvg_get_ever_best (nobody needs them inside the search).
-        UVG_NCCL(c, g_nccl.AllGather(c->d_own, c->d_all, c->own_bytes, ncclUint8, c->comm, c->st));
+        UVG_NCCL(c, g_nccl.AllGather(c->fin_device ? c->d_fin : c->d_own, c->d_all, c->fin_device ? c->fin_bytes : c->own_bytes, ncclUint8, c->comm, c->st));
         c->ever_reduced = false;
     }
     UVG_CUDA(c, cudaEventRecord(c->ev_b, c->st));
@@ -1612,6 +1714,9 @@ extern "C" int uvg_wait(uvg_ctx* c)
     int rc = sync_all(c);
     if (rc) return rc;
     c->search_open = false;
+    // the final all-gather came after every rank's last replay: nobody reads an array that grew (and moved) during the search
+    for (void* p : c->deferred_free) cudaFree(p);
+    c->deferred_free.clear();
     {   // executed (pair, 4-word unit) iterations per lane: whole units + halves / 2 (pairpivot.cu counts halves of two words)
         const int64_t total = (int64_t)c->h_pinned[20] + c->work_host;
         c->work_last = total - c->work_seen;
@@ -1631,7 +1736,7 @@ extern "C" int uvg_search(uvg_ctx* c)
 {
     if (!c) return UVG_EINVAL;
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
-    int rc = search_enqueue(c);
+    int rc = search_enqueue(c, true);
     if (rc) return rc;
     return uvg_wait(c);
 }
@@ -1639,6 +1744,7 @@ extern "C" int uvg_search(uvg_ctx* c)
 // =====================================================================================================================
 // results
 // =====================================================================================================================
+static_assert(sizeof(uvg_item) == 32, "k_finalise writes uvg_item rows");
 static int compare_items_desc(const void* pa, const void* pb)
 {   // compare_q_item_score (src/min_heap.c:41-47): first non-zero b[i]-a[i]
     const HeapItem* a = static_cast<const HeapItem*>(pa);
@@ -1655,22 +1761,26 @@ static int cache_heaps(uvg_ctx* c)
     if (c->search_open) { int rc = uvg_wait(c); if (rc) return rc; }
     if (c->heaps_cached) return UVG_OK;
     const size_t rows_r = (size_t)c->rows_cap, rows = (size_t)c->world * rows_r, stride = c->K + 1;
-    c->h_heaps.resize(rows * stride); c->h_heap_n.resize(rows); c->h_max_inc.resize(rows);
-    // one device -> host copy of the packed result blocks (pinned), then the three arrays are sliced out on the host
-    const size_t total = (size_t)c->world * c->own_bytes;
+    c->h_heap_n.resize(rows); c->h_max_inc.resize(rows);
+    // one device -> host copy of the result blocks of all ranks (pinned); sizes and limits are sliced out on the host
+    const size_t blk_bytes = c->fin_device ? c->fin_bytes : c->own_bytes, off_n = c->fin_device ? c->fin_off_n : c->own_off_n,
+                 off_mi = c->fin_device ? c->fin_off_mi : c->own_off_mi;
+    const size_t total = (size_t)c->world * blk_bytes;
     if (total > c->h_all_bytes) {
         if (c->h_all) cudaFreeHost(c->h_all);
         c->h_all = nullptr; c->h_all_bytes = 0;
         UVG_CUDA(c, cudaMallocHost(&c->h_all, total));
         c->h_all_bytes = total;
     }
-    UVG_CUDA(c, cudaMemcpyAsync(c->h_all, c->world > 1 ? c->d_all : c->d_own, total, cudaMemcpyDeviceToHost, c->st));
+    const uint8_t* src = c->world > 1 ? c->d_all : (c->fin_device ? c->d_fin : c->d_own);
+    UVG_CUDA(c, cudaMemcpyAsync(c->h_all, src, total, cudaMemcpyDeviceToHost, c->st));
     UVG_CUDA(c, cudaStreamSynchronize(c->st));
+    if (!c->fin_device) c->h_heaps.resize(rows * stride);
     for (int r = 0; r < c->world; ++r) {
-        const uint8_t* blk = c->h_all + (size_t)r * c->own_bytes;
-        memcpy(c->h_heaps.data() + (size_t)r * rows_r * stride, blk, rows_r * stride * sizeof(HeapItem));
-        memcpy(c->h_heap_n.data() + (size_t)r * rows_r, blk + c->own_off_n, rows_r * 4);
-        memcpy(c->h_max_inc.data() + (size_t)r * rows_r, blk + c->own_off_mi, rows_r * 4);
+        const uint8_t* blk = c->h_all + (size_t)r * blk_bytes;
+        if (!c->fin_device) memcpy(c->h_heaps.data() + (size_t)r * rows_r * stride, blk, rows_r * stride * sizeof(HeapItem));
+        memcpy(c->h_heap_n.data() + (size_t)r * rows_r, blk + off_n, rows_r * 4);
+        memcpy(c->h_max_inc.data() + (size_t)r * rows_r, blk + off_mi, rows_r * 4);
     }
     c->heaps_cached = true;
     return UVG_OK;
@@ -1688,6 +1798,11 @@ static int finalise_row(const uvg_ctx* c, int iq, uvg_item* out)
     const size_t row = row_of_query(c, iq);
     const int n = c->h_heap_n[row];
     if (n == 0) return 0;
+    if (c->fin_device) {                                                      // sorted on the device (k_finalise): rows of rank r start at block r
+        const size_t r = row / c->rows_cap, lrow = row % c->rows_cap;
+        memcpy(out, c->h_all + r * c->fin_bytes + lrow * c->K * sizeof(uvg_item), (size_t)n * sizeof(uvg_item));
+        return n;
+    }
     const HeapItem* a = c->h_heaps.data() + row * (c->K + 1);
     std::vector<HeapItem> arr(n);
     arr[0] = a[n];
@@ -1718,6 +1833,16 @@ extern "C" int uvg_get_all_heaps(uvg_ctx* c, uvg_item* out, int32_t* n_out)
     UVG_CUDA(c, cudaSetDevice(c->prm.device));
     int rc = cache_heaps(c);
     if (rc) return rc;
+    if (c->fin_device) {                                                      // whole query tiles are contiguous on both sides
+        for (int qt = 0; qt < c->n_qtiles; ++qt) {
+            const int q0 = qt * QTILE, nq = std::min(QTILE, c->n_query - q0);
+            if (nq <= 0) break;
+            const size_t row = row_of_query(c, q0), r = row / c->rows_cap, lrow = row % c->rows_cap;
+            memcpy(out + (size_t)q0 * c->K, c->h_all + r * c->fin_bytes + lrow * c->K * sizeof(uvg_item), (size_t)nq * c->K * sizeof(uvg_item));
+            for (int i = 0; i < nq; ++i) n_out[q0 + i] = c->h_heap_n[row + i];
+        }
+        return UVG_OK;
+    }
     parallel_ranges(c->n_query, host_threads(c->n_query / 64), [&](int, int qa, int qb) {
         for (int iq = qa; iq < qb; ++iq) n_out[iq] = finalise_row(c, iq, out + (size_t)iq * c->K);
     });

@@ -67,10 +67,12 @@ struct ReplayParams {
     int32_t* b_carry_out;         // ... for the next launch
     int32_t* b_acc;               // this launch's accumulator (atomicMax of every query's final max_incompatible)
     int32_t* b_zero;              // the accumulator of the NEXT launch (zeroed here)
-    int64_t local_ord0;           // global ordinal of local reference 0 (local index = ordinal - local_ord0)
-    const uint4* db; const QChunk* qcons; int32_t cons_qi; const uint32_t* cons_nib;
+    // packed references of every segment's rank (peer-mapped when sharded), for the prefix recount of truncated pairs:
+    // the reference at position i of segment g is row seg_local0 + i of that rank's database
+    const uint4* seg_db[MAX_RANKS]; const uint32_t* seg_ramb_off[MAX_RANKS]; const uint32_t* seg_ramb_ent[MAX_RANKS];
+    int64_t seg_local0;
+    const QChunk* qcons; int32_t cons_qi; const uint32_t* cons_nib;
     const uint32_t* camb; int32_t n_camb;
-    const uint32_t* ramb_off; const uint32_t* ramb_ent;
     int32_t Wp;
 };
 cudaError_t launch_replay(const ReplayParams& p, cudaStream_t st);
@@ -88,6 +90,8 @@ struct SpecRestore {
     int32_t* b_prev; int32_t* b_carry; int32_t* b_acc;                // what the first literal launch reads / accumulates into
 };
 cudaError_t launch_spec_restore(const SpecRestore& r, cudaStream_t st);
+// final tables of `rows` heaps (slot swap + stable descending sort), as uvg_item rows [rows][K]
+cudaError_t launch_finalise(const HeapItem* heaps, const int32_t* heap_n, int K, int rows, void* out, cudaStream_t st);
 cudaError_t replay_setup(int K);
 
 }  // namespace uvg

@@ -268,8 +268,8 @@ __global__ void __launch_bounds__(NT) k_replay(const ReplayParams p, int heap_in
     if (lit && row == 0 && threadIdx.x == 0) { *p.b_carry_out = B; *p.b_zero = 0; }
     ConsSrc csrc;
     if (lit) {
-        csrc.db = p.db; csrc.qcons = p.qcons; csrc.cons_qi = p.cons_qi; csrc.cons_nib = p.cons_nib; csrc.camb = p.camb; csrc.n_camb = p.n_camb;
-        csrc.ramb_off = p.ramb_off; csrc.ramb_ent = p.ramb_ent; csrc.Wp = p.Wp; csrc.acgt = acgt;
+        csrc.db = nullptr; csrc.qcons = p.qcons; csrc.cons_qi = p.cons_qi; csrc.cons_nib = p.cons_nib; csrc.camb = p.camb; csrc.n_camb = p.n_camb;
+        csrc.ramb_off = nullptr; csrc.ramb_ent = nullptr; csrc.Wp = p.Wp; csrc.acgt = acgt;
     }
     int admitted = 0, h1 = 0;                                                      // thread 0 only
     __syncthreads();
@@ -409,7 +409,8 @@ __global__ void __launch_bounds__(NT) k_replay(const ReplayParams p, int heap_in
                 if (pend >= 0) {
                     // literal mode: the pair at `pend` reaches the heap with the TRUNCATED consensus counts (block-wide recount)
                     const int64_t ord = seg_global + w0 + pend;
-                    cons_prefix<NT>(csrc, ord - p.local_ord0, B, st, s_red, s_scan);
+                    csrc.db = p.seg_db[g]; csrc.ramb_off = p.seg_ramb_off[g]; csrc.ramb_ent = p.seg_ramb_ent[g];     // the rank that holds the reference
+                    cons_prefix<NT>(csrc, p.seg_local0 + w0 + pend, B, st, s_red, s_scan);
                     if (threadIdx.x == 0) {
                         const uint4 sc = s_sc[pend];
                         const int64_t col = seg_col + w0 + pend;
@@ -525,6 +526,56 @@ cudaError_t launch_spec_commit(const unsigned long long* spec, const uint8_t* ev
 cudaError_t launch_spec_restore(const SpecRestore& r, cudaStream_t st)
 {
     k_spec_restore<<<64, 256, 0, st>>>(r);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Final tables on the device: heap_finalise_heap_qsort (src/min_heap.c:149-153) of every owned row -- slot 0 <-> slot n,
+// then the descending sort of slots [0, n) by compare_q_item_score (:41-47).  glibc's qsort is a stable merge sort for
+// arrays this small, so rows that compare equal keep their order in the heap array; a rank sort (position = number of rows
+// that go before) gives exactly that order.  One block per row; rows leave as uvg_item (six scores + 64-bit ordinal).
+// ---------------------------------------------------------------------------------------------------------------------
+struct FinalItem { int32_t s[6]; long long ref; };
+static_assert(sizeof(FinalItem) == 32, "uvg_item layout");
+
+__global__ void __launch_bounds__(128) k_finalise(const HeapItem* __restrict__ heaps, const int32_t* __restrict__ heap_n, int K, int rows, FinalItem* __restrict__ out)
+{
+    extern __shared__ uint4 s_fin[];
+    HeapItem* a = reinterpret_cast<HeapItem*>(s_fin);
+    for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+        const int n = heap_n[row];
+        const HeapItem* h = heaps + (size_t)row * (K + 1);
+        __syncthreads();
+        for (int i = threadIdx.x; i < n; i += blockDim.x) a[i] = h[i == 0 ? n : i];
+        __syncthreads();
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            const HeapItem me = a[i];
+            int pos = 0;
+            for (int j = 0; j < n; ++j) {
+                const HeapItem o = a[j];
+                int c = 0;                                                   // > 0: o sorts before me
+#pragma unroll
+                for (int k = 5; k >= 0; --k) { const int d = o.s[k] - me.s[k]; c = d ? d : c; }
+                pos += (c > 0) | ((c == 0) & (j < i));
+            }
+            FinalItem f;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) f.s[k] = me.s[k];
+            f.ref = me.r;
+            out[(size_t)row * K + pos] = f;
+        }
+    }
+}
+
+cudaError_t launch_finalise(const HeapItem* heaps, const int32_t* heap_n, int K, int rows, void* out, cudaStream_t st)
+{
+    if (rows <= 0) return cudaSuccess;
+    const size_t smem = (size_t)(K + 1) * sizeof(HeapItem);
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k_finalise, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    k_finalise<<<(unsigned)std::min(rows, 148 * 8), 128, smem, st>>>(heaps, heap_n, K, rows, static_cast<FinalItem*>(out));
     return cudaGetLastError();
 }
 

@@ -3,8 +3,9 @@
 The reference is a single process; the partition is ours.  The per-query admission of the reference is
 order dependent, so shards are NOT independent top-k problems: references are dealt to ranks in rounds of contiguous
 tiles in file order -- round j covers global ordinals [S_j, S_j + world*T_j), rank g scores [S_j + g*T_j, S_j + (g+1)*T_j),
-T_1 = first_round, T_{j+1} = min(4*T_j, max_round); the LAST round, which the remaining references cannot fill, is cut
-to ceil(remaining / world) rounded up to 64 so that every rank gets the same share of the tail -- and the scores of every round are handed to the rank that owns
+T_1 = first_round, T_{j+1} = min(4*T_j, max_round); towards the end of the database the rounds taper off (round_size_at:
+half of what is left per rank, never below 4,096, rounded up to 64), so that every rank gets the same share of the tail
+and the last replay is short -- and the scores of every round are handed to the rank that owns
 the query (query tile qt belongs to rank qt % world), which replays them in global file order.
 """
 from __future__ import annotations
@@ -22,12 +23,21 @@ def round_sizes(first_round=0, max_round=0):
     return first, max(mx, first)
 
 
+ROUND_TAPER_MIN = 4096
+
+
 def round_size_at(S, T, total, world):
-    """size per rank of the round that starts at global ordinal S with nominal size T (twin of round_size_at, engine.cu)"""
-    if total is None or total < 0 or S + world * T <= total:
+    """size per rank of the round that starts at global ordinal S with nominal size T (twin of round_size_at, engine.cu):
+    once less than two nominal rounds remain per rank, every round takes half of what is left (the last replay, which no
+    pair counting hides, becomes short; the ranks share the tail evenly)"""
+    if total is None or total < 0:
         return T
-    rem = total - S
-    return min(T, max(64, ((rem + world - 1) // world + 63) // 64 * 64))
+    rem = max(0, total - S)
+    share = (rem + world - 1) // world
+    if share >= 2 * T:
+        return T
+    v = share if share <= ROUND_TAPER_MIN else max(ROUND_TAPER_MIN, (share + 1) // 2)
+    return min(T, max(64, (v + 63) // 64 * 64))
 
 
 def rounds(total, world, first_round=0, max_round=0):
