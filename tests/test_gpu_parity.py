@@ -416,7 +416,7 @@ def test_final_tables_sorted_on_device_and_on_host(nbest):
     names, Qo, *_ = orc.prepare_queries(qn, qs, 0, False, 0.5)
     with Engine(L, nbest=nbest, pool=64, closed_form=True, first_round=256, max_round=1024) as eng:
         eng.set_queries(Qo)
-        eng.push_refs(R, 0)
+        eng.push_refs(R, int(L * 0.5))
         eng.search()
         tables = eng.heaps()
         for iq in range(len(names)):

@@ -567,8 +567,11 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
                     n_plain += plain;
                     if (code & (code - 1u)) { amb[q].push_back((uint32_t)s | (code << 28)); continue; }
                     if (pivot_ok && plain) {
-                        if (code == pv[s]) me |= bit;
-                        else snp[q].push_back((uint32_t)s | (code << 28));
+                        // the planes treat EVERY plain base as the pivot's; a base that differs is settled by its fix entry
+                        // (one reference that holds the pivot's base less, one that holds the query's base more), so a
+                        // SNP alone does not make the kernel count its half from the planes
+                        me |= bit;
+                        if (code != pv[s]) snp[q].push_back((uint32_t)s | (code << 28));
                     }
                 }
                 const int k = w & 3;
@@ -711,14 +714,15 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
             qstream.insert(qstream.end(), tile_rec[qt].begin(), tile_rec[qt].end());
         }
         c->pivot_halves = halves_total;
-        // fix entries per slot: chunk << 16 | unit << 9 | word << 7 | base (A,C,G,T) << 5 | site in word (common.cuh)
+        // fix entries per slot: chunk << 16 | pivot's base << 10 | unit << 9 | word << 7 | query's base (A,C,G,T) << 5 | site in word
         snp_off.assign(c->n_slots + 1, 0);
         for (int q = 0; q < c->n_slots; ++q) {
             snp_off[q] = (uint32_t)snp_ent.size();
             for (uint32_t ent : snp[q]) {
                 const uint32_t site = ent & AMB_SITE_MASK, code = ent >> 28, w = site >> 5;
                 const uint32_t a = code == 1 ? 0 : code == 2 ? 1 : code == 4 ? 2 : 3;
-                snp_ent.push_back((w / WC) << 16 | ((w % WC) / 4) << 9 | (w & 3u) << 7 | a << 5 | (site & 31u));
+                const uint32_t pc = pv[site], pa = pc == 1 ? 0 : pc == 2 ? 1 : pc == 4 ? 2 : 3;
+                snp_ent.push_back((w / WC) << 16 | pa << 10 | ((w % WC) / 4) << 9 | (w & 3u) << 7 | a << 5 | (site & 31u));
             }
         }
         snp_off[c->n_slots] = (uint32_t)snp_ent.size();

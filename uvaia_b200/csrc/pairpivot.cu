@@ -203,6 +203,11 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     // chunk records), then the 32 x 32 bit matrix (entry x reference) is transposed across the warp (5 butterfly steps), so
     // that every lane holds the 32 entries' bits of ITS reference and one POPC counts them: ~2 instructions per entry and
     // group instead of a serial bit test per entry (r01: ~18 per entry in the epilogue, 12x the main loop on config 4). ----
+    // the carry-save "ones" registers are folded into the packed counters: the corrections below need the registers
+#pragma unroll
+    for (int g = 0; g < RPL; ++g)
+#pragma unroll
+        for (int j = 0; j < QW2; ++j) acc[g][j] += (uint32_t)__popc(oM[g][j]) + ((uint32_t)__popc(oV[g][j]) << 16);
     const uint8_t* ws = p.wslot + ((size_t)pt * PIVOT_WARPS + warp) * QW2;      // slots of the pivot tile this warp counted (0xff: none)
     uint32_t fh[RPL][QW2], fv[RPL][QW2], fp[RPL][QW2];                           // matches by fix entries; valid / partial by ambiguity codes
     auto transpose32 = [&](uint32_t x) -> uint32_t {
@@ -228,13 +233,21 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         for (uint32_t e0 = __ldg(p.snp_off + slot); e0 < e1; e0 += 32) {
             const bool have = e0 + lane < e1;
             const uint32_t ent = have ? __ldg(p.snp_ent + e0 + lane) : 0u;
-            const uint8_t* mrec = rsrc + (size_t)(ent >> 16) * CHUNK2_BYTES + CHUNK2_STAGED + ((ent >> 9) & 1u) * UNIT2_MASKS + (ent & 0x1ffu) * 4u;
-            uint32_t mk[RPL];
+            const uint8_t* mrec = rsrc + (size_t)(ent >> 16) * CHUNK2_BYTES + CHUNK2_STAGED + ((ent >> 9) & 1u) * UNIT2_MASKS;
+            const uint32_t oq = (ent & 0x1ffu) * 4u, op = ((ent & 0x19fu) | ((ent >> 5) & 0x60u)) * 4u;       // same word and site, the query's / the pivot's base
+            uint32_t mq[RPL], mp[RPL];
 #pragma unroll
-            for (int g = 0; g < RPL; ++g) mk[g] = have ? __ldg(reinterpret_cast<const uint32_t*>(mrec + g * (W4 * UNIT2_MASKS))) : 0u;
+            for (int g = 0; g < RPL; ++g) {
+                mq[g] = have ? __ldg(reinterpret_cast<const uint32_t*>(mrec + g * (W4 * UNIT2_MASKS) + oq)) : 0u;
+                mp[g] = have ? __ldg(reinterpret_cast<const uint32_t*>(mrec + g * (W4 * UNIT2_MASKS) + op)) : 0u;
+            }
 #pragma unroll
-            for (int g = 0; g < RPL; ++g)
-                if (__ballot_sync(0xffffffffu, mk[g] != 0u)) fh[g][j] += __popc(transpose32(mk[g]));
+            for (int g = 0; g < RPL; ++g) {
+                // the planes counted the site as "query holds the pivot's base": take back the references that hold it, add those
+                // that hold the query's base
+                if (__ballot_sync(0xffffffffu, mq[g] != 0u)) fh[g][j] += __popc(transpose32(mq[g]));
+                fh[g][j] -= __popc(transpose32(mp[g]));
+            }
         }
         e1 = __ldg(p.qamb_off + slot + 1);
         for (uint32_t e0 = __ldg(p.qamb_off + slot); e0 < e1; e0 += 32) {
@@ -276,8 +289,8 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
 #pragma unroll
         for (int g = 0; g < RPL; ++g) {
             if (!in_range[g]) continue;
-            const int32_t M = p.mc_cnt[local[g]] - (int32_t)((acc[g][j] & 0xffffu) + __popc(oM[g][j])) + (int32_t)fh[g][j];
-            const int32_t V = p.rb_cnt[local[g]] - (int32_t)((acc[g][j] >> 16) + __popc(oV[g][j]));
+            const int32_t M = p.mc_cnt[local[g]] - (int32_t)(acc[g][j] & 0xffffu) + (int32_t)fh[g][j];
+            const int32_t V = p.rb_cnt[local[g]] - (int32_t)(acc[g][j] >> 16);
             uint4 v = pair_epilogue_default(p, p.qamb_off, p.qamb_ent, slot, group0 + g, lane, local[g], M, V, false);
             v.z += fp[g][j]; v.w += fv[g][j];                                  // the query's ambiguity codes: partial, valid
             pair_store(p, owner, row, is_cons, local[g], v);

@@ -234,12 +234,24 @@ class Engine:
         arr = np.frombuffer(buf, dtype=np.dtype([("score", np.int32, 6), ("ref", np.int64)]), count=n.value)
         return arr["score"].copy(), arr["ref"].copy()
 
+    ITEM_DTYPE = np.dtype([("score", np.int32, 6), ("ref", np.int64)])          # uvg_item
+
+    def heaps_raw(self, out=None, n_out=None):
+        """every query's table in one call (uvg_get_all_heaps): (items [n_query, max(2, nbest)] of ITEM_DTYPE, rows per
+        query int32 [n_query]); rows beyond a query's count are unspecified.  `out` / `n_out`: buffers of that shape to fill
+        (a serving loop that keeps its result buffers pays no page faults for fresh ones)"""
+        if out is None:
+            out = np.empty((self.n_query, self.K), self.ITEM_DTYPE)
+        if n_out is None:
+            n_out = np.empty(self.n_query, np.int32)
+        assert out.dtype == self.ITEM_DTYPE and out.shape == (self.n_query, self.K) and out.flags.c_contiguous
+        assert n_out.dtype == np.int32 and n_out.shape == (self.n_query,) and n_out.flags.c_contiguous
+        self._ck(self._lib.uvg_get_all_heaps(self._h, out.ctypes.data, n_out.ctypes.data), "uvg_get_all_heaps")
+        return out, n_out
+
     def heaps(self):
-        """every query's table: [(scores int32[n,6], refs int64[n])] (one call: uvg_get_all_heaps)"""
-        dt = np.dtype([("score", np.int32, 6), ("ref", np.int64)])
-        buf = np.empty((self.n_query, self.K), dt)
-        n = np.empty(self.n_query, np.int32)
-        self._ck(self._lib.uvg_get_all_heaps(self._h, buf.ctypes.data, n.ctypes.data), "uvg_get_all_heaps")
+        """every query's table: [(scores int32[n,6], refs int64[n])] (views into the one buffer of heaps_raw)"""
+        buf, n = self.heaps_raw()
         sc, rf = buf["score"], buf["ref"]                        # views into one buffer (no per-query copies)
         return [(sc[q, :k], rf[q, :k]) for q, k in enumerate(n.tolist())]
 
