@@ -387,13 +387,13 @@ def main():
         torch.cuda.synchronize()
 
     # ---- timed: device-resident search ----
-    for _ in range(args.warmup):
-        eng.reset_search(); eng.search()
+    tab_items, tab_rows = np.zeros((eng.n_query, eng.K), Engine.ITEM_DTYPE), np.zeros(eng.n_query, np.int32)      # result buffers of the serving loop
+    for _ in range(args.warmup):                               # whole steps: the first table read allocates the library's pinned result buffer
+        eng.reset_search(); eng.search(); eng.heaps_raw(tab_items, tab_rows)
     sampler = ClockSampler(dev)
     barrier()
     sampler.start()
     ev_ms, pair_ms, replay_ms, launches, chunks, tables_ms = 0.0, 0.0, 0.0, 0, 0, 0.0
-    tab_items, tab_rows = np.zeros((eng.n_query, eng.K), Engine.ITEM_DTYPE), np.zeros(eng.n_query, np.int32)      # result buffers of the serving loop
     t0 = time.perf_counter()
     for _ in range(args.steps):
         eng.reset_search(); eng.search()

@@ -49,17 +49,33 @@ struct __align__(16) Stage2 {
     uint32_t   cnt[RPL][W4][GROUP];      // unit totals of every reference: popc(mc) | popc(base) << 16
 };
 static_assert(sizeof(RefPlanes2) * RPL * W4 == CHUNK2_PLANES && sizeof(Stage2) == QREC_MAX + CHUNK2_STAGED, "ring stage");
+#ifndef PIVOT_CPS
+#define PIVOT_CPS 1             // chunks per ring stage: one full / empty barrier round trip per PIVOT_CPS chunks
+#endif
+constexpr int PIVOT_CPS_ = PIVOT_CPS;
 constexpr int PIVOT_MAX_CHUNKS = 256;                                  // < 65,536 columns
-constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(uint64_t) + (PIVOT_MAX_CHUNKS + 4) * sizeof(uint32_t);
+constexpr size_t PIVOT_RING_BYTES = (size_t)((STAGES2 + PIVOT_CPS_ - 1) / PIVOT_CPS_) * PIVOT_CPS_ * sizeof(Stage2);
+constexpr size_t PIVOT_SMEM = PIVOT_RING_BYTES + 2 * STAGES2 * sizeof(uint64_t) + (PIVOT_MAX_CHUNKS + 4) * sizeof(uint32_t);
 #ifndef PIVOT_UNROLL_UNITS
 #define PIVOT_UNROLL_UNITS 1
 #endif
 #ifndef PIVOT_PRODUCER_SLEEP
 #define PIVOT_PRODUCER_SLEEP 0   // ns the producer thread sleeps between two tests of a stage that is still in use
 #endif
+#ifndef PIVOT_UNIFORM_HEAD
+#define PIVOT_UNIFORM_HEAD 1
+#endif
+#ifndef PIVOT_CONSUMER_SLEEP
+#define PIVOT_CONSUMER_SLEEP 0  // ns a counting warp sleeps between two tests of a stage that has not arrived yet (0 = try_wait)
+#endif
+#ifndef PIVOT_WAIT_HINT
+#define PIVOT_WAIT_HINT 0       // ns a counting warp may sleep inside the try_wait for its stage (0 = the default time limit)
+#endif
 #ifndef PIVOT_GRANULE
 #define PIVOT_GRANULE 0         // bytes per bulk copy of the reference side of a stage (0 = one copy of 4.5 KB; smaller copies measured slower)
 #endif
+constexpr int CPS = PIVOT_CPS;
+constexpr int RING = (STAGES2 + CPS - 1) / CPS;         // ring stages of CPS chunk slots each
 constexpr int QW2 = PIVOT_QW;                           // query slots per warp (register tile QW2 x RPL pairs per lane)
 constexpr int PIVOT_THREADS = PIVOT_WARPS * 32;
 
@@ -76,32 +92,41 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     // shared-memory addresses as plain integers: nothing in the loop goes through a generic -> shared conversion
     uint32_t stage_a = smem_u32(stage);
     asm volatile("mov.u32 %0, %0;" : "+r"(stage_a));                         // opaque: kept in a register instead of being re-derived (S2R + LEA) per use
-    const uint32_t full_a = stage_a + (uint32_t)(STAGES2 * sizeof(Stage2)), empty_a = full_a + STAGES2 * 8u;
+    const uint32_t full_a = stage_a + (uint32_t)PIVOT_RING_BYTES, empty_a = full_a + STAGES2 * 8u;
     // offsets of the tile's records in shared memory: the producer thread must not wait for a global load per chunk
-    uint32_t* s_qoff = reinterpret_cast<uint32_t*>(smem + STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(uint64_t));
+    uint32_t* s_qoff = reinterpret_cast<uint32_t*>(smem + PIVOT_RING_BYTES + 2 * STAGES2 * sizeof(uint64_t));
     for (int i = threadIdx.x; i <= p.n_chunks; i += PIVOT_THREADS) s_qoff[i] = __ldg(qoff + i);
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES2; ++s) { mbar_init_a(full_a + s * 8u, 1); mbar_init_a(empty_a + s * 8u, PIVOT_WARPS - 1); }
+        for (int s = 0; s < RING; ++s) { mbar_init_a(full_a + s * 8u, 1); mbar_init_a(empty_a + s * 8u, PIVOT_WARPS - 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    // one stage = the query record of the chunk (exactly its bytes) + planes and counts of the pair's chunk record
-    auto issue_at = [&](int c, int s, uint32_t o0, uint32_t o1) {
-        const uint32_t bar = full_a + (uint32_t)s * 8u, dst = stage_a + (uint32_t)s * (uint32_t)sizeof(Stage2);
-        mbar_expect_tx_a(bar, (o1 - o0) + (uint32_t)CHUNK2_STAGED);
-        bulk_g2s_a(dst, p.qstream + o0, o1 - o0, bar);
-#if PIVOT_GRANULE == 0
-        bulk_g2s_a(dst + (uint32_t)QREC_MAX, rsrc + (size_t)c * CHUNK2_BYTES, (uint32_t)CHUNK2_STAGED, bar);
-#else
-        static_assert(CHUNK2_STAGED % PIVOT_GRANULE == 0 && PIVOT_GRANULE % 16 == 0, "granule");
+    // one chunk slot of a stage = the query record of the chunk (exactly its bytes) + planes and counts of the pair's chunk
+    // record; stage k of the search holds the chunks [k * CPS, k * CPS + CPS) and one barrier covers them all
+    const int n_stages = (p.n_chunks + CPS - 1) / CPS;
+    auto issue_at = [&](int k, int s) {
+        const uint32_t bar = full_a + (uint32_t)s * 8u, dst = stage_a + (uint32_t)s * (uint32_t)(CPS * sizeof(Stage2));
+        const int c0 = k * CPS, c1 = min(c0 + CPS, p.n_chunks);
+        mbar_expect_tx_a(bar, (s_qoff[c1] - s_qoff[c0]) + (uint32_t)((c1 - c0) * CHUNK2_STAGED));
 #pragma unroll
-        for (int k = 0; k < CHUNK2_STAGED / PIVOT_GRANULE; ++k)
-            bulk_g2s_a(dst + (uint32_t)QREC_MAX + k * PIVOT_GRANULE, rsrc + (size_t)c * CHUNK2_BYTES + k * PIVOT_GRANULE, (uint32_t)PIVOT_GRANULE, bar);
+        for (int i = 0; i < CPS; ++i) {
+            const int c = c0 + i;
+            if (c >= c1) break;
+            const uint32_t o0 = s_qoff[c], o1 = s_qoff[c + 1], d = dst + (uint32_t)(i * sizeof(Stage2));
+            bulk_g2s_a(d, p.qstream + o0, o1 - o0, bar);
+#if PIVOT_GRANULE == 0
+            bulk_g2s_a(d + (uint32_t)QREC_MAX, rsrc + (size_t)c * CHUNK2_BYTES, (uint32_t)CHUNK2_STAGED, bar);
+#else
+            static_assert(CHUNK2_STAGED % PIVOT_GRANULE == 0 && PIVOT_GRANULE % 16 == 0, "granule");
+#pragma unroll
+            for (int k2_ = 0; k2_ < CHUNK2_STAGED / PIVOT_GRANULE; ++k2_)
+                bulk_g2s_a(d + (uint32_t)QREC_MAX + k2_ * PIVOT_GRANULE, rsrc + (size_t)c * CHUNK2_BYTES + k2_ * PIVOT_GRANULE, (uint32_t)PIVOT_GRANULE, bar);
 #endif
+        }
     };
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES2 && s < p.n_chunks; ++s) issue_at(s, s, s_qoff[s], s_qoff[s + 1]);
+        for (int s = 0; s < RING && s < n_stages; ++s) issue_at(s, s);
     }
 
     // per pair: carry-save "ones" registers of the two complement streams and one packed counter
@@ -116,26 +141,42 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         // ---- producer warp: keeps the ring full.  Chunk c goes into stage c % STAGES2 as soon as the fifteen counting warps
         // have released what the stage held before; it has no slots of its own, so nobody ever waits for its counting work ----
         if (lane == 0) {
-            int s = 0; uint32_t ph = 0;                                      // stage / phase of the chunk being issued
-            for (int c = STAGES2; c < p.n_chunks; ++c) {
+            int s = 0; uint32_t ph = 0;                                      // stage / phase of the chunks being issued
+            for (int k = RING; k < n_stages; ++k) {
 #if PIVOT_PRODUCER_SLEEP
                 while (!mbar_test_a(empty_a + (uint32_t)s * 8u, ph)) __nanosleep(PIVOT_PRODUCER_SLEEP);
 #else
-                mbar_wait_a(empty_a + (uint32_t)s * 8u, ph);                 // use c / STAGES2 - 1 of the stage is over
+                mbar_wait_a(empty_a + (uint32_t)s * 8u, ph);                 // use k / RING - 1 of the stage is over
 #endif
-                issue_at(c, s, s_qoff[c], s_qoff[c + 1]);
-                if (++s == STAGES2) { s = 0; ph ^= 1u; }
+                issue_at(k, s);
+                if (++s == RING) { s = 0; ph ^= 1u; }
             }
         }
         return;
     }
-    int s = 0;                                                               // stage of chunk c = c % STAGES2, ph = (c / STAGES2) & 1
+    int s = 0;                                                               // ring stage of search stage k = k % RING, ph = (k / RING) & 1
     uint32_t ph = 0;
-    for (int c = 0; c < p.n_chunks; ++c) {
+    for (int k = 0; k < n_stages; ++k) {
+#if PIVOT_CONSUMER_SLEEP
+        while (!mbar_test_a(full_a + (uint32_t)s * 8u, ph)) __nanosleep(PIVOT_CONSUMER_SLEEP);
+#elif PIVOT_WAIT_HINT
+        mbar_wait_hint_a(full_a + (uint32_t)s * 8u, ph, PIVOT_WAIT_HINT);
+#else
         mbar_wait_a(full_a + (uint32_t)s * 8u, ph);
-        const Stage2& st = stage[s];
+#endif
+#if PIVOT_CPS > 1
+#pragma unroll 1
+#endif
+      for (int sub = 0; sub < CPS; ++sub) {
+        if (CPS > 1 && k * CPS + sub >= p.n_chunks) break;
+        const Stage2& st = stage[s * CPS + sub];
         // what this warp has to do in the chunk, and where its items start
-        const uint2 hd = reinterpret_cast<const uint2*>(st.q)[warp];
+        uint2 hd = reinterpret_cast<const uint2*>(st.q)[warp];
+#if PIVOT_UNIFORM_HEAD
+        // the head is the same for all lanes; a broadcast from lane 0 lets the compiler KNOW it, so that the branches on its bits
+        // are uniform branches without convergence barriers (BSSY / BSYNC were ~10 % of the instructions of the loop)
+        hd.x = __shfl_sync(0xffffffffu, hd.x, 0); hd.y = __shfl_sync(0xffffffffu, hd.y, 0);
+#endif
         const uint32_t hmask = hd.x & 0xffffu, nmask = (hd.x >> 16) & 0xffu;
         const uint4* item = reinterpret_cast<const uint4*>(st.q + QHEAD_BYTES) + (hd.y & 0xffffu);
 #if PIVOT_UNROLL_UNITS
@@ -188,10 +229,11 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
                 }
             }
         }
+      }
         // release the stage to the producer warp
         __syncwarp();
         if (lane == 0) mbar_arrive_a(empty_a + (uint32_t)s * 8u);
-        if (++s == STAGES2) { s = 0; ph ^= 1u; }
+        if (++s == RING) { s = 0; ph ^= 1u; }
     }
 
     // ---- sparse corrections from the column masks of the derived database (per site and base one word: bit l = reference l of
@@ -208,8 +250,22 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     for (int g = 0; g < RPL; ++g)
 #pragma unroll
         for (int j = 0; j < QW2; ++j) acc[g][j] += (uint32_t)__popc(oM[g][j]) + ((uint32_t)__popc(oV[g][j]) << 16);
-    const uint8_t* ws = p.wslot + ((size_t)pt * PIVOT_WARPS + warp) * QW2;      // slots of the pivot tile this warp counted (0xff: none)
-    uint32_t fh[RPL][QW2], fv[RPL][QW2], fp[RPL][QW2];                           // matches by fix entries; valid / partial by ambiguity codes
+    // slots of the pivot tile this warp counted (-1: none), broadcast from lane 0 like everything below that is the same for
+    // all lanes (list bounds, owners): the compiler then keeps it in uniform registers and the loops need no convergence barriers
+    int slot_of[QW2];
+    {
+        static_assert(QW2 == 4, "four slot bytes in one word");
+        const uint32_t ws4 = __shfl_sync(0xffffffffu, __ldg(reinterpret_cast<const uint32_t*>(p.wslot) + (size_t)pt * PIVOT_WARPS + warp), 0);
+#pragma unroll
+        for (int j = 0; j < QW2; ++j) {
+            const uint32_t b = (ws4 >> (j * 8)) & 0xffu;
+            const int slot = pt * PIVOT_SLOTS + (int)b;
+            slot_of[j] = (b == 0xffu || slot >= p.n_slots) ? -1 : slot;
+        }
+    }
+    // matches by fix entries, partial by ambiguity codes; the valid sites the codes add are folded into the counter at once
+    // (it holds what is SUBTRACTED from the reference's total, modulo 2^16: alignments of the pivot form have < 65,536 columns)
+    uint32_t fh[RPL][QW2], fp[RPL][QW2];
     auto transpose32 = [&](uint32_t x) -> uint32_t {
 #pragma unroll
         for (int j = 16; j >= 1; j >>= 1) {
@@ -226,11 +282,11 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
 #pragma unroll
     for (int j = 0; j < QW2; ++j) {
 #pragma unroll
-        for (int g = 0; g < RPL; ++g) { fh[g][j] = 0; fv[g][j] = 0; fp[g][j] = 0; }
-        const int slot = pt * PIVOT_SLOTS + (int)ws[j];
-        if (ws[j] == 0xff || slot >= p.n_slots) continue;
-        uint32_t e1 = __ldg(p.snp_off + slot + 1);
-        for (uint32_t e0 = __ldg(p.snp_off + slot); e0 < e1; e0 += 32) {
+        for (int g = 0; g < RPL; ++g) { fh[g][j] = 0; fp[g][j] = 0; }
+        const int slot = slot_of[j];
+        if (slot < 0) continue;
+        uint32_t e1 = __shfl_sync(0xffffffffu, __ldg(p.snp_off + slot + 1), 0);
+        for (uint32_t e0 = __shfl_sync(0xffffffffu, __ldg(p.snp_off + slot), 0); e0 < e1; e0 += 32) {
             const bool have = e0 + lane < e1;
             const uint32_t ent = have ? __ldg(p.snp_ent + e0 + lane) : 0u;
             const uint8_t* mrec = rsrc + (size_t)(ent >> 16) * CHUNK2_BYTES + CHUNK2_STAGED + ((ent >> 9) & 1u) * UNIT2_MASKS;
@@ -249,8 +305,8 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
                 fh[g][j] -= __popc(transpose32(mp[g]));
             }
         }
-        e1 = __ldg(p.qamb_off + slot + 1);
-        for (uint32_t e0 = __ldg(p.qamb_off + slot); e0 < e1; e0 += 32) {
+        e1 = __shfl_sync(0xffffffffu, __ldg(p.qamb_off + slot + 1), 0);
+        for (uint32_t e0 = __shfl_sync(0xffffffffu, __ldg(p.qamb_off + slot), 0); e0 < e1; e0 += 32) {
             const bool have = e0 + lane < e1;
             const uint32_t ent = have ? __ldg(p.qamb_ent + e0 + lane) : 0u, code = ent >> 28;
             const uint8_t* mrec = mask_words(ent & AMB_SITE_MASK);
@@ -265,35 +321,44 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
                         pm |= (code >> a) & 1u ? m : 0u;
                     }
                 }
-                fv[g][j] += __popc(transpose32(vm));
+                acc[g][j] -= (uint32_t)__popc(transpose32(vm)) << 16;
                 fp[g][j] += __popc(transpose32(pm));
             }
         }
     }
 
-    // ---- epilogue: plane counts -> exact counts -> score tile of the owner ----
-    bool in_range[RPL];
-    int64_t local[RPL];
+    // ---- epilogue: plane counts -> exact counts -> score tile of the owner (the four counts of alignment.c:866-879).  The sites
+    // where the REFERENCE holds an ambiguity code are outside its planes: its (short) list is walked once per reference and
+    // every entry is looked up in the 4-bit codes of the warp's four slots (pair_epilogue.cuh does the same per pair). ----
+    // the score rows belong to the 64-slot tiles of the search: owner rank and row inside the owner's score tile
 #pragma unroll
     for (int g = 0; g < RPL; ++g) {
-        local[g] = (group0 + g) * GROUP + lane;
-        in_range[g] = local[g] >= p.local_begin && local[g] < p.local_end;
-    }
+        const int64_t local = (group0 + g) * GROUP + lane;
+        if (local < p.local_begin || local >= p.local_end) continue;
+        int32_t dv[QW2], dp[QW2], dt[QW2];
 #pragma unroll
-    for (int j = 0; j < QW2; ++j) {
-        const int slot = pt * PIVOT_SLOTS + (int)ws[j];
-        if (ws[j] == 0xff || slot >= p.n_slots) continue;
-        const bool is_cons = slot == p.n_slots - 1;
-        // the score rows belong to the 64-slot tiles of the search (owner rank, row inside the owner's score tile)
-        const int qt = slot / QTILE, owner = qt % p.world, row = (qt / p.world) * QTILE + slot % QTILE;
+        for (int j = 0; j < QW2; ++j) { dv[j] = 0; dp[j] = 0; dt[j] = 0; }
+        const uint32_t re1 = p.ramb_off[local + 1];
+        for (uint32_t e = p.ramb_off[local]; e < re1; ++e) {
+            const uint32_t ent = __ldg(p.ramb_ent + e), site = ent & AMB_SITE_MASK, rc = ent >> 28;
 #pragma unroll
-        for (int g = 0; g < RPL; ++g) {
-            if (!in_range[g]) continue;
-            const int32_t M = p.mc_cnt[local[g]] - (int32_t)(acc[g][j] & 0xffffu) + (int32_t)fh[g][j];
-            const int32_t V = p.rb_cnt[local[g]] - (int32_t)(acc[g][j] >> 16);
-            uint4 v = pair_epilogue_default(p, p.qamb_off, p.qamb_ent, slot, group0 + g, lane, local[g], M, V, false);
-            v.z += fp[g][j]; v.w += fv[g][j];                                  // the query's ambiguity codes: partial, valid
-            pair_store(p, owner, row, is_cons, local[g], v);
+            for (int j = 0; j < QW2; ++j) {
+                if (slot_of[j] < 0) continue;
+                const uint32_t qc = (__ldg(p.qnib + (size_t)slot_of[j] * p.qnib_stride + (site >> 3)) >> ((site & 7u) * 4u)) & 15u;
+                dv[j] += qc != 0u; dp[j] += (qc & rc) != 0u; dt[j] += qc == rc;
+            }
+        }
+        const int32_t mc_total = p.mc_cnt[local], rb_total = p.rb_cnt[local];
+#pragma unroll
+        for (int j = 0; j < QW2; ++j) {
+            const int slot = slot_of[j];
+            if (slot < 0) continue;
+            const int32_t M = mc_total - (int32_t)(acc[g][j] & 0xffffu) + (int32_t)fh[g][j];
+            const int32_t V = (int32_t)(((uint32_t)rb_total - (acc[g][j] >> 16)) & 0xffffu);
+            // acgt, text, partial (+ the query's ambiguity codes), valid
+            const uint4 v = make_uint4((uint32_t)M, (uint32_t)(M + dt[j]), (uint32_t)(M + dp[j]) + fp[g][j], (uint32_t)(V + dv[j]));
+            const int qt = slot / QTILE;                                     // uniform: one division per slot and reference group
+            pair_store(p, qt % p.world, (qt / p.world) * QTILE + slot % QTILE, slot == p.n_slots - 1, local, v);
         }
     }
 }

@@ -45,6 +45,15 @@ __device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity)
                      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
     } while (!ok);
 }
+// the same with a suspend-time hint (ns): the waiting warp may sleep that long inside the instruction instead of re-issuing it
+__device__ __forceinline__ void mbar_wait_hint_a(uint32_t bar, uint32_t parity, uint32_t ns)
+{
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity), "r"(ns) : "memory");
+    } while (!ok);
+}
 __device__ __forceinline__ bool mbar_test_a(uint32_t bar, uint32_t parity)          // non-blocking
 {
     uint32_t ok;
