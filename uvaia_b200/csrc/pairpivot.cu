@@ -49,13 +49,8 @@ struct __align__(16) Stage2 {
     uint32_t   cnt[RPL][W4][GROUP];      // unit totals of every reference: popc(mc) | popc(base) << 16
 };
 static_assert(sizeof(RefPlanes2) * RPL * W4 == CHUNK2_PLANES && sizeof(Stage2) == QREC_MAX + CHUNK2_STAGED, "ring stage");
-#ifndef PIVOT_CPS
-#define PIVOT_CPS 1             // chunks per ring stage: one full / empty barrier round trip per PIVOT_CPS chunks
-#endif
-constexpr int PIVOT_CPS_ = PIVOT_CPS;
 constexpr int PIVOT_MAX_CHUNKS = 256;                                  // < 65,536 columns
-constexpr size_t PIVOT_RING_BYTES = (size_t)((STAGES2 + PIVOT_CPS_ - 1) / PIVOT_CPS_) * PIVOT_CPS_ * sizeof(Stage2);
-constexpr size_t PIVOT_SMEM = PIVOT_RING_BYTES + 2 * STAGES2 * sizeof(uint64_t) + (PIVOT_MAX_CHUNKS + 4) * sizeof(uint32_t);
+constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(uint64_t) + (PIVOT_MAX_CHUNKS + 4) * sizeof(uint32_t);
 #ifndef PIVOT_UNROLL_UNITS
 #define PIVOT_UNROLL_UNITS 1
 #endif
@@ -74,8 +69,6 @@ constexpr size_t PIVOT_SMEM = PIVOT_RING_BYTES + 2 * STAGES2 * sizeof(uint64_t) 
 #ifndef PIVOT_GRANULE
 #define PIVOT_GRANULE 0         // bytes per bulk copy of the reference side of a stage (0 = one copy of 4.5 KB; smaller copies measured slower)
 #endif
-constexpr int CPS = PIVOT_CPS;
-constexpr int RING = (STAGES2 + CPS - 1) / CPS;         // ring stages of CPS chunk slots each
 constexpr int QW2 = PIVOT_QW;                           // query slots per warp (register tile QW2 x RPL pairs per lane)
 constexpr int PIVOT_THREADS = PIVOT_WARPS * 32;
 
@@ -92,41 +85,33 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     // shared-memory addresses as plain integers: nothing in the loop goes through a generic -> shared conversion
     uint32_t stage_a = smem_u32(stage);
     asm volatile("mov.u32 %0, %0;" : "+r"(stage_a));                         // opaque: kept in a register instead of being re-derived (S2R + LEA) per use
-    const uint32_t full_a = stage_a + (uint32_t)PIVOT_RING_BYTES, empty_a = full_a + STAGES2 * 8u;
+    const uint32_t full_a = stage_a + (uint32_t)(STAGES2 * sizeof(Stage2)), empty_a = full_a + STAGES2 * 8u;
     // offsets of the tile's records in shared memory: the producer thread must not wait for a global load per chunk
-    uint32_t* s_qoff = reinterpret_cast<uint32_t*>(smem + PIVOT_RING_BYTES + 2 * STAGES2 * sizeof(uint64_t));
+    uint32_t* s_qoff = reinterpret_cast<uint32_t*>(smem + STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(uint64_t));
     for (int i = threadIdx.x; i <= p.n_chunks; i += PIVOT_THREADS) s_qoff[i] = __ldg(qoff + i);
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < RING; ++s) { mbar_init_a(full_a + s * 8u, 1); mbar_init_a(empty_a + s * 8u, PIVOT_WARPS - 1); }
+        for (int s = 0; s < STAGES2; ++s) { mbar_init_a(full_a + s * 8u, 1); mbar_init_a(empty_a + s * 8u, PIVOT_WARPS - 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    // one chunk slot of a stage = the query record of the chunk (exactly its bytes) + planes and counts of the pair's chunk
-    // record; stage k of the search holds the chunks [k * CPS, k * CPS + CPS) and one barrier covers them all
-    const int n_stages = (p.n_chunks + CPS - 1) / CPS;
-    auto issue_at = [&](int k, int s) {
-        const uint32_t bar = full_a + (uint32_t)s * 8u, dst = stage_a + (uint32_t)s * (uint32_t)(CPS * sizeof(Stage2));
-        const int c0 = k * CPS, c1 = min(c0 + CPS, p.n_chunks);
-        mbar_expect_tx_a(bar, (s_qoff[c1] - s_qoff[c0]) + (uint32_t)((c1 - c0) * CHUNK2_STAGED));
-#pragma unroll
-        for (int i = 0; i < CPS; ++i) {
-            const int c = c0 + i;
-            if (c >= c1) break;
-            const uint32_t o0 = s_qoff[c], o1 = s_qoff[c + 1], d = dst + (uint32_t)(i * sizeof(Stage2));
-            bulk_g2s_a(d, p.qstream + o0, o1 - o0, bar);
+    // one stage = the query record of the chunk (exactly its bytes) + planes and counts of the pair's chunk record.  (Two
+    // chunks per stage and barrier round trip were measured 4 % slower: the stages get coarser, the warps drift less freely.)
+    auto issue_at = [&](int c, int s, uint32_t o0, uint32_t o1) {
+        const uint32_t bar = full_a + (uint32_t)s * 8u, dst = stage_a + (uint32_t)s * (uint32_t)sizeof(Stage2);
+        mbar_expect_tx_a(bar, (o1 - o0) + (uint32_t)CHUNK2_STAGED);
+        bulk_g2s_a(dst, p.qstream + o0, o1 - o0, bar);
 #if PIVOT_GRANULE == 0
-            bulk_g2s_a(d + (uint32_t)QREC_MAX, rsrc + (size_t)c * CHUNK2_BYTES, (uint32_t)CHUNK2_STAGED, bar);
+        bulk_g2s_a(dst + (uint32_t)QREC_MAX, rsrc + (size_t)c * CHUNK2_BYTES, (uint32_t)CHUNK2_STAGED, bar);
 #else
-            static_assert(CHUNK2_STAGED % PIVOT_GRANULE == 0 && PIVOT_GRANULE % 16 == 0, "granule");
+        static_assert(CHUNK2_STAGED % PIVOT_GRANULE == 0 && PIVOT_GRANULE % 16 == 0, "granule");
 #pragma unroll
-            for (int k2_ = 0; k2_ < CHUNK2_STAGED / PIVOT_GRANULE; ++k2_)
-                bulk_g2s_a(d + (uint32_t)QREC_MAX + k2_ * PIVOT_GRANULE, rsrc + (size_t)c * CHUNK2_BYTES + k2_ * PIVOT_GRANULE, (uint32_t)PIVOT_GRANULE, bar);
+        for (int k = 0; k < CHUNK2_STAGED / PIVOT_GRANULE; ++k)
+            bulk_g2s_a(dst + (uint32_t)QREC_MAX + k * PIVOT_GRANULE, rsrc + (size_t)c * CHUNK2_BYTES + k * PIVOT_GRANULE, (uint32_t)PIVOT_GRANULE, bar);
 #endif
-        }
     };
     if (threadIdx.x == 0) {
-        for (int s = 0; s < RING && s < n_stages; ++s) issue_at(s, s);
+        for (int s = 0; s < STAGES2 && s < p.n_chunks; ++s) issue_at(s, s, s_qoff[s], s_qoff[s + 1]);
     }
 
     // per pair: carry-save "ones" registers of the two complement streams and one packed counter
@@ -141,22 +126,22 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         // ---- producer warp: keeps the ring full.  Chunk c goes into stage c % STAGES2 as soon as the fifteen counting warps
         // have released what the stage held before; it has no slots of its own, so nobody ever waits for its counting work ----
         if (lane == 0) {
-            int s = 0; uint32_t ph = 0;                                      // stage / phase of the chunks being issued
-            for (int k = RING; k < n_stages; ++k) {
+            int s = 0; uint32_t ph = 0;                                      // stage / phase of the chunk being issued
+            for (int c = STAGES2; c < p.n_chunks; ++c) {
 #if PIVOT_PRODUCER_SLEEP
                 while (!mbar_test_a(empty_a + (uint32_t)s * 8u, ph)) __nanosleep(PIVOT_PRODUCER_SLEEP);
 #else
-                mbar_wait_a(empty_a + (uint32_t)s * 8u, ph);                 // use k / RING - 1 of the stage is over
+                mbar_wait_a(empty_a + (uint32_t)s * 8u, ph);                 // use c / STAGES2 - 1 of the stage is over
 #endif
-                issue_at(k, s);
-                if (++s == RING) { s = 0; ph ^= 1u; }
+                issue_at(c, s, s_qoff[c], s_qoff[c + 1]);
+                if (++s == STAGES2) { s = 0; ph ^= 1u; }
             }
         }
         return;
     }
-    int s = 0;                                                               // ring stage of search stage k = k % RING, ph = (k / RING) & 1
+    int s = 0;                                                               // stage of chunk c = c % STAGES2, ph = (c / STAGES2) & 1
     uint32_t ph = 0;
-    for (int k = 0; k < n_stages; ++k) {
+    for (int c = 0; c < p.n_chunks; ++c) {
 #if PIVOT_CONSUMER_SLEEP
         while (!mbar_test_a(full_a + (uint32_t)s * 8u, ph)) __nanosleep(PIVOT_CONSUMER_SLEEP);
 #elif PIVOT_WAIT_HINT
@@ -164,12 +149,7 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
 #else
         mbar_wait_a(full_a + (uint32_t)s * 8u, ph);
 #endif
-#if PIVOT_CPS > 1
-#pragma unroll 1
-#endif
-      for (int sub = 0; sub < CPS; ++sub) {
-        if (CPS > 1 && k * CPS + sub >= p.n_chunks) break;
-        const Stage2& st = stage[s * CPS + sub];
+        const Stage2& st = stage[s];
         // what this warp has to do in the chunk, and where its items start
         uint2 hd = reinterpret_cast<const uint2*>(st.q)[warp];
 #if PIVOT_UNIFORM_HEAD
@@ -229,11 +209,10 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
                 }
             }
         }
-      }
         // release the stage to the producer warp
         __syncwarp();
         if (lane == 0) mbar_arrive_a(empty_a + (uint32_t)s * 8u);
-        if (++s == RING) { s = 0; ph ^= 1u; }
+        if (++s == STAGES2) { s = 0; ph ^= 1u; }
     }
 
     // ---- sparse corrections from the column masks of the derived database (per site and base one word: bit l = reference l of
