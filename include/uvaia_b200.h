@@ -221,6 +221,16 @@ int uvg_ball_set_queries(uvg_ball* b, const uint8_t* text, int32_t n_query, uvg_
  * uvaiaball uses min_non_n = (int)(nchar * A), ball.c:201), 1: outside the ball, 2: within `dist` of some query (the rows
  * uvaiaball writes to <prefix>.aln.xz, in file order).  non_n_out (may be NULL) = valid_ref_sites of every row. */
 int uvg_ball_push_refs(uvg_ball* b, const uint8_t* text, int64_t n, int32_t min_non_n, uint8_t* keep, int32_t* non_n_out);
+/* The same classification for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO counterpart in the reference.  d_text: n rows of nchar
+ * bytes in DEVICE memory; d_keep [n] and d_non_n [n] (may be NULL) are DEVICE buffers of the caller and receive what
+ * uvg_ball_push_refs returns in keep / non_n_out.  The call allocates nothing (no cudaMalloc / cudaFree): the scratch between its
+ * two kernels is a file-scope device array of 8 bytes x UVG_BALL_NOALLOC_MAX_ROWS = 512 KiB that every GPU which loads the library
+ * holds until the process exits.  n > UVG_BALL_NOALLOC_MAX_ROWS is rejected (UVG_EINVAL, message in uvg_ball_last_error): split the
+ * rows over several calls.  All calls on a device share the array: calls that overlap on the GPU (contexts of the same device used
+ * from several threads) race; a call returns when its kernels have finished.  uvg_ball_set_queries (which does allocate) comes first. */
+#define UVG_BALL_NOALLOC_MAX_ROWS 65536
+int uvg_ball_classify_device_noalloc(uvg_ball* b, const uint8_t* d_text, int64_t n, int32_t min_non_n, uint8_t* d_keep, int32_t* d_non_n);
 
 /* ---- bench / test utilities (not part of the reference seam) ---- */
 /* Device generator of SARS-CoV-2-shaped alignment rows (same model as uvaia_b200/synth.py; counter-based RNG keyed

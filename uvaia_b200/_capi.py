@@ -82,6 +82,7 @@ SYMBOLS = {
     "uvg_ball_radius": (C.c_int32, [_P]),
     "uvg_ball_set_queries": (C.c_int, [_P, _P, C.c_int32, C.POINTER(uvg_query_info)]),
     "uvg_ball_push_refs": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P, _P]),
+    "uvg_ball_classify_device_noalloc": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P, _P]),
     "uvg_synth_rows_device": (C.c_int, [_P, _P, C.c_int32, C.c_uint64, C.c_int64, C.c_int64, C.c_double, C.c_double, _P]),
     "uvg_device_alloc": (_P, [_P, C.c_size_t]),
     "uvg_device_free": (None, [_P, _P]),

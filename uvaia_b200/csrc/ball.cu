@@ -21,6 +21,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -31,6 +32,16 @@ __constant__ uint8_t c_usable[256];    // of an UPPER-CASE byte: default mode va
 __constant__ uint8_t c_validtxt[256];  // of an upper-case byte: not in NnXx-?Oo. (quick_count_sequence_non_N counts these over the whole row)
 
 constexpr int BALL_THREADS = 256;
+
+// Scratch of uvg_ball_classify_device_noalloc (the entry point that allocates nothing): what k_ball_cons hands to k_ball_query
+// -- per row the consensus-stage differences c, and valid_ref_sites when the caller does not want them.  File-scope device
+// memory: every GPU that loads the library holds these 512 KiB until the process exits.  In HOST code the name below is only a
+// stand-in for the symbol, not a device address: the address comes from cudaGetSymbolAddress (noalloc_scratch_of), per device.
+struct BallScratch {
+    int32_t c[UVG_BALL_NOALLOC_MAX_ROWS];
+    int32_t non_n[UVG_BALL_NOALLOC_MAX_ROWS];
+};
+static __device__ __align__(256) BallScratch g_ball_scratch;
 
 // keep codes: 0 = too ambiguous (filtered), 1 = outside the ball, 2 = inside, 3 = undecided after the consensus stages
 __global__ void __launch_bounds__(BALL_THREADS) k_ball_cons(const uint8_t* __restrict__ text, int64_t n, int L, const uint8_t* __restrict__ cc,
@@ -280,6 +291,59 @@ extern "C" int uvg_ball_push_refs(uvg_ball* b, const uint8_t* text, int64_t n, i
         BALL_CUDA(b, cudaMemcpyAsync(keep_out + i, d_keep, (size_t)m, cudaMemcpyDeviceToHost, b->st));
         if (non_n_out) BALL_CUDA(b, cudaMemcpyAsync(non_n_out + i, d_nn, (size_t)m * 4, cudaMemcpyDeviceToHost, b->st));
     }
+    BALL_CUDA(b, cudaStreamSynchronize(b->st));
+    return UVG_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// uvg_ball_classify_device_noalloc: the two kernels of uvg_ball_push_refs for callers that must not allocate (code under CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Rows and results are the caller's DEVICE buffers; the scratch between the kernels is the file-scope
+// array g_ball_scratch.  No cudaMalloc / cudaFree / allocating library routine is called here.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr int BALL_MAX_DEVICES = 64;
+std::mutex g_scratch_mutex;
+BallScratch* g_scratch_ptr[BALL_MAX_DEVICES] = {};       // device address of g_ball_scratch on every device that asked for it
+
+// once per device, with that device current: the device address of the symbol (the host-side name is NOT one)
+cudaError_t noalloc_scratch_of(int device, BallScratch** out)
+{
+    std::lock_guard<std::mutex> lock(g_scratch_mutex);
+    if (!g_scratch_ptr[device]) {
+        void* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_ball_scratch);
+        if (e != cudaSuccess) return e;
+        g_scratch_ptr[device] = static_cast<BallScratch*>(ptr);
+    }
+    *out = g_scratch_ptr[device];
+    return cudaSuccess;
+}
+}  // namespace
+
+extern "C" int uvg_ball_classify_device_noalloc(uvg_ball* b, const uint8_t* d_text, int64_t n, int32_t min_non_n, uint8_t* d_keep, int32_t* d_non_n)
+{
+    if (!b || (!d_text && n > 0) || n < 0 || (!d_keep && n > 0)) { if (b) b->err = "uvg_ball_classify_device_noalloc: bad arguments"; return UVG_EINVAL; }
+    if (b->n_query == 0) BALL_FAIL(b, UVG_ESTATE, "uvg_ball_classify_device_noalloc: no queries set");
+    if (n > (int64_t)UVG_BALL_NOALLOC_MAX_ROWS)
+        BALL_FAIL(b, UVG_EINVAL, "uvg_ball_classify_device_noalloc: %lld rows exceed the %d rows the static scratch array holds "
+                  "(UVG_BALL_NOALLOC_MAX_ROWS); split the call or use uvg_ball_push_refs", (long long)n, (int)UVG_BALL_NOALLOC_MAX_ROWS);
+    if (b->prm.device >= BALL_MAX_DEVICES) BALL_FAIL(b, UVG_EINVAL, "uvg_ball_classify_device_noalloc: device ordinal %d beyond %d", b->prm.device, BALL_MAX_DEVICES);
+    BALL_CUDA(b, cudaSetDevice(b->prm.device));
+    if (n == 0) return UVG_OK;
+    BallScratch* scratch = nullptr;
+    BALL_CUDA(b, noalloc_scratch_of(b->prm.device, &scratch));
+    const int L = b->nchar, R = b->dist + 1;
+    // nothing in the scratch has to start at zero: k_ball_cons writes c / non_n of every row < n before k_ball_query reads them
+    // (same stream).  It keeps the last call's contents; two calls that overlap on the GPU (other streams, other contexts of the
+    // same device, other threads) would race on it -- every call runs on the context's stream and is waited for here.
+    int32_t* d_c = scratch->c;
+    int32_t* d_nn = d_non_n ? d_non_n : scratch->non_n;
+    k_ball_cons<<<(unsigned)n, BALL_THREADS, 0, b->st>>>(d_text, n, L, b->d_cc, min_non_n, R, d_c, d_nn, d_keep);
+    BALL_CUDA(b, cudaGetLastError());
+    k_ball_query<<<(unsigned)n, BALL_THREADS, (size_t)std::max(1, b->n_words) * 4, b->st>>>(d_text, n, L, b->d_idx, b->n_idx, b->n_words, b->d_qxT,
+                                                                                         b->n_query, b->q_stride, R, d_c, d_keep);
+    BALL_CUDA(b, cudaGetLastError());
     BALL_CUDA(b, cudaStreamSynchronize(b->st));
     return UVG_OK;
 }

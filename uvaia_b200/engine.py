@@ -89,6 +89,15 @@ class Ball:
         return keep, nn
 
 
+    NOALLOC_MAX_ROWS = 65536                                  # UVG_BALL_NOALLOC_MAX_ROWS (include/uvaia_b200.h)
+
+    def classify_device_noalloc(self, d_text, n, min_non_n, d_keep, d_non_n=0):
+        """uvg_ball_classify_device_noalloc: rows and results are DEVICE addresses of the caller (ints); the call allocates
+        nothing (static device scratch, at most NOALLOC_MAX_ROWS rows per call)"""
+        self._ck(self._lib.uvg_ball_classify_device_noalloc(self._h, int(d_text), int(n), int(min_non_n), int(d_keep), int(d_non_n) or None),
+                 "uvg_ball_classify_device_noalloc")
+
+
 class Engine:
     def __init__(self, nchar, nbest=100, trim=0, acgt=False, pool=512, device=0, first_round=0, max_round=0,
                  early_abort=False, rank=0, world=1, db_capacity=0, pair_kernel=None, closed_form=False, nominal_tail=False):
