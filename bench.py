@@ -32,7 +32,7 @@ KNOWN_CHECKSUMS = {(1000, 1_000_000, 29903, 100, 0.0, 200): 31652904200}
 # algorithmic instruction counts per (pair, 32-site word) of the two pair-count kernels
 OPS = {"pivot": {"kernel": "k_pairpivot", "lop3": 4.0, "popc": 1.0, "db_bytes_per_word": 9,      # 2 AND + 2 x (one 3:2 compressor per two words); 2 x 0.5 POPC;
                                                                                                   # staged: planes + counts, 4.5 KB per 64 references x 8 words
-                 "ncu": "ncu_pairpivot_r02k_producer_warp.json"},
+                 "ncu": "ncu_pairpivot_r02ak_uniform_heads.json"},
        "general": {"kernel": "k_paircount", "lop3": 4.5, "popc": 1.25, "db_bytes_per_word": 12,  # 3 for valid+match, 1.5 carry-save tree; 1 + 0.25 POPC
                    "ncu": "ncu_paircount_r01e_csa.json"}}
 

@@ -1487,6 +1487,10 @@ static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t
     // buffer b was last read by the replay of round j-2: single GPU -> our own replay; sharded -> every rank's replay,
     // which the all-gather of round j-1 (issued after it on each rank's stream B) has already waited for
     UVG_CUDA(c, cudaStreamWaitEvent(c->st, c->world > 1 ? c->ev_ag[(b + 1) % NBUF] : c->ev_replay[b], 0));
+    // diagnostic (UVG_DEBUG_NO_OVERLAP=1): the pair counting of round j also waits for the replay of round j-1, so that its
+    // kernel times are those of an undisturbed GPU (how much the replay running beside it costs; profiles/)
+    static const bool no_overlap = getenv("UVG_DEBUG_NO_OVERLAP") && atoi(getenv("UVG_DEBUG_NO_OVERLAP")) != 0;
+    if (no_overlap && c->rounds_done > 0) UVG_CUDA(c, cudaStreamWaitEvent(c->st, c->ev_replay[(b + 1) % NBUF], 0));
     cudaEvent_t ea, eb;
     int rc = event_pair(c, *n_ev, &ea, &eb);
     if (rc) return rc;

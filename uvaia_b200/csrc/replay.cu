@@ -10,6 +10,7 @@
 // (~K ln(R/K) times per query), so all threads test 1,024 references at a time against the CURRENT state -- an exact
 // test, not a bound -- one thread admits the first survivor, and the rest of the window is re-tested from shared
 // memory against the new state.
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
 #include <algorithm>
@@ -20,6 +21,7 @@ namespace uvg {
 // fills the machine), 512 threads x windows of 4,096 when a rank owns few rows (8 GPUs: 128 rows) -- a row is streamed by ONE
 // block, so its memory-level parallelism is what the last, un-overlapped replay of a sharded search costs.
 constexpr int RP_PER = 8;                    // references per thread and window
+constexpr int REPLAY_GRID_CAP = 0;           // most thread blocks of a replay launch (0 = one per row); see replay_row
 constexpr int RP_HEAP_SMEM_ITEMS = 1024;     // heaps up to this many slots live in shared memory
 #define RP_CONSTS(NT) constexpr int RP_THREADS = (NT); constexpr int RP_WIN = (NT) * RP_PER; (void)RP_WIN;
 
@@ -211,8 +213,12 @@ __device__ void cons_prefix(const ConsSrc& c, int64_t lr, int B, RpState* st, in
     __syncthreads();
 }
 
+// One row (= one owned query) of a round.  The thread blocks of k_replay are few and long-lived, and they sit beside the
+// pair-count kernel of the next round, whose two blocks per SM fill the register file: every resident replay block keeps a
+// pair-count block off its SM for as long as it lives.  So the replay runs with a capped grid (launch_replay) and each
+// block takes several rows in turn.
 template <int NT>
-__global__ void __launch_bounds__(NT) k_replay(const ReplayParams p, int heap_in_smem)
+__device__ __forceinline__ void replay_row(const ReplayParams& p, const int heap_in_smem, const int row)
 {
     RP_CONSTS(NT)
     extern __shared__ __align__(16) uint8_t smem[];
@@ -226,7 +232,6 @@ __global__ void __launch_bounds__(NT) k_replay(const ReplayParams p, int heap_in
     int* s_red = s_misc + 32;                                                      // RP_THREADS / 32 ints (block_sum)
     static_assert(NT / 32 <= 16, "per-warp scratch");
 
-    const int row = blockIdx.x;
     const int q = ((row / QTILE) * p.world + p.rank) * QTILE + row % QTILE;        // query this row belongs to
     if (q >= p.n_query) return;
     // literal launches of a round that the speculative closed-form pass has already settled (no pair could have been
@@ -280,19 +285,33 @@ __global__ void __launch_bounds__(NT) k_replay(const ReplayParams p, int heap_in
         // the launch covers the global ordinals [ord_begin, ord_end) of the round (the whole round unless a batch ends inside it)
         const int seg_lo = (int)max((int64_t)0, p.ord_begin - seg_global);
         const int seg_n = (int)min((int64_t)p.seg_cnt[g], p.ord_end - seg_global);
+        // the windows of a row are a serial chain (the state of one feeds the next), so what a window costs is latency: its
+        // records are fetched into registers one window ahead, and a window without a candidate -- almost all of them once the
+        // heap is full -- takes ONE barrier: every thread tests the records it staged itself, and __syncthreads_or tells
+        // whether anybody has to look closer
+        uint4 ahead[RP_PER];
+#pragma unroll
+        for (int k = 0; k < RP_PER; ++k) {
+            const int i = k * RP_THREADS + threadIdx.x;
+            ahead[k] = seg_lo + i < seg_n ? trow[seg_col + seg_lo + i] : make_uint4(0u, 0u, 0u, 0u);
+        }
         for (int w0 = seg_lo; w0 < seg_n; w0 += RP_WIN) {
             const int cntw = min(RP_WIN, seg_n - w0);
 #pragma unroll
+            for (int k = 0; k < RP_PER; ++k) s_sc[k * RP_THREADS + threadIdx.x] = ahead[k];
+#pragma unroll
             for (int k = 0; k < RP_PER; ++k) {
-                const int i = k * RP_THREADS + threadIdx.x;
-                if (i < cntw) s_sc[i] = trow[seg_col + w0 + i];
+                const int i = w0 + RP_WIN + k * RP_THREADS + threadIdx.x;
+                if (i < seg_n) ahead[k] = trow[seg_col + i];
             }
             int start = 0;
             for (;;) {
-                __syncthreads();
+                // no barrier here: a thread tests the records it wrote itself, and the state was published before the last
+                // barrier of the previous pass
                 // ---- all threads: test the window against the current state ----
                 const int n = st->n, max_inc = st->max_inc, mib = st->mib, cb_begin = st->cb_begin, cb_end = st->cb_end;
                 const int r0 = st->root[0], r1 = st->root[1], r2 = st->root[2], r3 = st->root[3];
+                uint32_t any = 0;
 #pragma unroll
                 for (int k = 0; k < RP_PER; ++k) {
                     const int i = k * RP_THREADS + threadIdx.x;
@@ -335,8 +354,9 @@ __global__ void __launch_bounds__(NT) k_replay(const ReplayParams p, int heap_in
                     }
                     const uint32_t m = __ballot_sync(0xffffffffu, cand), f = __ballot_sync(0xffffffffu, flag);
                     if (lane == 0) { s_mask[k * (RP_THREADS / 32) + warp] = m; s_fmask[k * (RP_THREADS / 32) + warp] = f; }
+                    any |= m | f;
                 }
-                __syncthreads();
+                if (!__syncthreads_or((int)(any != 0u))) break;                    // nothing to admit, nothing to flag
                 // ---- thread 0: admit in file order until the state changes ----
                 if (threadIdx.x == 0) {
                     int nn = n, mi = max_inc, restart = -1, cbb = cb_begin, cbe = cb_end, bk = st->bk, mb = mib, pend = -1;
@@ -451,7 +471,6 @@ __global__ void __launch_bounds__(NT) k_replay(const ReplayParams p, int heap_in
                 if (restart < 0 || restart >= cntw) break;
                 start = restart;
             }
-            __syncthreads();
         }
     }
 
@@ -478,6 +497,15 @@ __global__ void __launch_bounds__(NT) k_replay(const ReplayParams p, int heap_in
         }
     }
     if (heap_in_smem) for (int i = 1 + threadIdx.x; i <= n; i += blockDim.x) gheap[i] = a[i];
+}
+
+template <int NT>
+__global__ void __launch_bounds__(NT, NT == 128 ? 6 : 1) k_replay(const ReplayParams p, int heap_in_smem)
+{
+    for (int row = blockIdx.x; row < p.rows_cap; row += gridDim.x) {
+        replay_row<NT>(p, heap_in_smem, row);
+        __syncthreads();                                                           // the next row reuses the shared memory
+    }
 }
 
 // ---- speculation of a literal round (engine.cu run_round) ----
@@ -598,13 +626,17 @@ cudaError_t replay_setup(int K)
 cudaError_t launch_replay(const ReplayParams& p, cudaStream_t st)
 {
     if (p.rows_cap <= 0) return cudaSuccess;
+    // experiment knobs: UVG_REPLAY_GRID = most blocks of a launch (0: one per row), UVG_REPLAY_WIDE = 1: 512-thread blocks when rows are few
+    static const int grid_cap = getenv("UVG_REPLAY_GRID") ? atoi(getenv("UVG_REPLAY_GRID")) : REPLAY_GRID_CAP;
+    static const int wide = getenv("UVG_REPLAY_WIDE") ? atoi(getenv("UVG_REPLAY_WIDE")) : 0;
+    const int grid = grid_cap > 0 ? std::min(p.rows_cap, grid_cap) : p.rows_cap;
     int in_smem;
-    if (p.rows_cap <= 320) {                                                       // few rows (sharded): wide blocks
+    if (wide && p.rows_cap <= 320) {
         const size_t bytes = replay_smem_bytes(p.K, 512, &in_smem);
-        k_replay<512><<<p.rows_cap, 512, bytes, st>>>(p, in_smem);
+        k_replay<512><<<grid, 512, bytes, st>>>(p, in_smem);
     } else {
         const size_t bytes = replay_smem_bytes(p.K, 128, &in_smem);
-        k_replay<128><<<p.rows_cap, 128, bytes, st>>>(p, in_smem);
+        k_replay<128><<<grid, 128, bytes, st>>>(p, in_smem);
     }
     return cudaGetLastError();
 }
