@@ -18,8 +18,11 @@
 namespace uvg {
 
 // Block size NT (template): 128 threads x windows of 1,024 references when there are many rows (one GPU: a block per query
-// fills the machine), 512 threads x windows of 4,096 when a rank owns few rows (8 GPUs: 128 rows) -- a row is streamed by ONE
-// block, so its memory-level parallelism is what the last, un-overlapped replay of a sharded search costs.
+// fills the machine), 256 threads x windows of 2,048 when a rank owns few rows (8 GPUs: 128 rows) -- a row is streamed by ONE
+// block, so its memory-level parallelism is what the replays at the end of a sharded search cost.  Both at 78 registers: the
+// blocks live beside the pair-count kernel of the next round, whose two blocks per SM fill the register file, and every
+// register a replay block holds keeps pair-count blocks off its SM (512-thread blocks at 114 registers took whole SMs:
+// profiles/replay_interference_r02an.log).
 constexpr int RP_PER = 8;                    // references per thread and window
 constexpr int REPLAY_GRID_CAP = 0;           // most thread blocks of a replay launch (0 = one per row); see replay_row
 constexpr int RP_HEAP_SMEM_ITEMS = 1024;     // heaps up to this many slots live in shared memory
@@ -500,7 +503,7 @@ __device__ __forceinline__ void replay_row(const ReplayParams& p, const int heap
 }
 
 template <int NT>
-__global__ void __launch_bounds__(NT, NT == 128 ? 6 : 1) k_replay(const ReplayParams p, int heap_in_smem)
+__global__ void __launch_bounds__(NT, NT == 128 ? 6 : 3) k_replay(const ReplayParams p, int heap_in_smem)
 {
     for (int row = blockIdx.x; row < p.rows_cap; row += gridDim.x) {
         replay_row<NT>(p, heap_in_smem, row);
@@ -619,21 +622,21 @@ cudaError_t replay_setup(int K)
 {
     int in_smem;
     cudaError_t e = cudaFuncSetAttribute(k_replay<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)replay_smem_bytes(K, 128, &in_smem));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_replay<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)replay_smem_bytes(K, 512, &in_smem));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_replay<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)replay_smem_bytes(K, 256, &in_smem));
     return e;
 }
 
 cudaError_t launch_replay(const ReplayParams& p, cudaStream_t st)
 {
     if (p.rows_cap <= 0) return cudaSuccess;
-    // experiment knobs: UVG_REPLAY_GRID = most blocks of a launch (0: one per row), UVG_REPLAY_WIDE = 1: 512-thread blocks when rows are few
+    // experiment knobs: UVG_REPLAY_GRID = most blocks of a launch (0: one per row), UVG_REPLAY_WIDE = 1: 256-thread blocks when rows are few
     static const int grid_cap = getenv("UVG_REPLAY_GRID") ? atoi(getenv("UVG_REPLAY_GRID")) : REPLAY_GRID_CAP;
-    static const int wide = getenv("UVG_REPLAY_WIDE") ? atoi(getenv("UVG_REPLAY_WIDE")) : 0;
+    static const int wide = getenv("UVG_REPLAY_WIDE") ? atoi(getenv("UVG_REPLAY_WIDE")) : 1;
     const int grid = grid_cap > 0 ? std::min(p.rows_cap, grid_cap) : p.rows_cap;
     int in_smem;
     if (wide && p.rows_cap <= 320) {
-        const size_t bytes = replay_smem_bytes(p.K, 512, &in_smem);
-        k_replay<512><<<grid, 512, bytes, st>>>(p, in_smem);
+        const size_t bytes = replay_smem_bytes(p.K, 256, &in_smem);
+        k_replay<256><<<grid, 256, bytes, st>>>(p, in_smem);
     } else {
         const size_t bytes = replay_smem_bytes(p.K, 128, &in_smem);
         k_replay<128><<<grid, 128, bytes, st>>>(p, in_smem);
