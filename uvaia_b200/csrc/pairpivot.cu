@@ -63,6 +63,9 @@ constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(ui
 #ifndef PIVOT_CONSUMER_SLEEP
 #define PIVOT_CONSUMER_SLEEP 0  // ns a counting warp sleeps between two tests of a stage that has not arrived yet (0 = try_wait)
 #endif
+#ifndef PIVOT_WALK_FFS
+#define PIVOT_WALK_FFS 0        // 1: the counted halves of a unit are walked by find-first-set + switch instead of eight bit tests
+#endif
 #ifndef PIVOT_WAIT_HINT
 #define PIVOT_WAIT_HINT 0       // ns a counting warp may sleep inside the try_wait for its stage (0 = the default time limit)
 #endif
@@ -182,6 +185,35 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
             uint4 rb[RPL], rm[RPL];
 #pragma unroll
             for (int g = 0; g < RPL; ++g) { rb[g] = st.ref[g][u].base[lane]; rm[g] = st.ref[g][u].mc[lane]; }
+#if PIVOT_WALK_FFS
+            // walk the set bits only (1.6 of the 16 halves of a chunk are counted): find-first-set + a switch over the (slot, half)
+            // the bit names, whose cases are the same straight-line blocks -- instead of eight tests per unit
+            uint32_t todo = hu;
+            do {
+                const int b = __ffs((int)todo) - 1;
+                todo &= todo - 1u;
+                const uint4 q = *item++;                                     // nq words 2h, 2h+1 | ne words 2h, 2h+1
+#define PIVOT_HALF(J, W0, W1)                                                                       \
+                    _Pragma("unroll") for (int g = 0; g < RPL; ++g) {                               \
+                        uint32_t ov = oV[g][J], om = oM[g][J], cv, cm;                              \
+                        csa(ov, cv, ov, rb[g].W0 & q.x, rb[g].W1 & q.y);                            \
+                        csa(om, cm, om, rm[g].W0 & q.z, rm[g].W1 & q.w);                            \
+                        oV[g][J] = ov; oM[g][J] = om;                                               \
+                        acc[g][J] = imad(__popc(cm), k2, imad(__popc(cv), k128k, acc[g][J]));       \
+                    }
+                switch (b) {
+                    case 0: PIVOT_HALF(0, x, y) break;
+                    case 1: PIVOT_HALF(0, z, w) break;
+                    case 2: PIVOT_HALF(1, x, y) break;
+                    case 3: PIVOT_HALF(1, z, w) break;
+                    case 4: PIVOT_HALF(2, x, y) break;
+                    case 5: PIVOT_HALF(2, z, w) break;
+                    case 6: PIVOT_HALF(3, x, y) break;
+                    default: PIVOT_HALF(3, z, w) break;
+                }
+#undef PIVOT_HALF
+            } while (todo);
+#else
 #pragma unroll
             for (int j = 0; j < QW2; ++j) {
                 const uint32_t hj = (hu >> (j * 2)) & 3u;
@@ -208,6 +240,7 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
                     }
                 }
             }
+#endif
         }
         // release the stage to the producer warp
         __syncwarp();
