@@ -32,7 +32,7 @@ KNOWN_CHECKSUMS = {(1000, 1_000_000, 29903, 100, 0.0, 200): 31652904200}
 # algorithmic instruction counts per (pair, 32-site word) of the two pair-count kernels
 OPS = {"pivot": {"kernel": "k_pairpivot", "lop3": 4.0, "popc": 1.0, "db_bytes_per_word": 9,      # 2 AND + 2 x (one 3:2 compressor per two words); 2 x 0.5 POPC;
                                                                                                   # staged: planes + counts, 4.5 KB per 64 references x 8 words
-                 "ncu": "ncu_pairpivot_r02ak_uniform_heads.json"},
+                 "ncu": "ncu_pairpivot_r02bb_four_refs_per_lane.json"},
        "general": {"kernel": "k_paircount", "lop3": 4.5, "popc": 1.25, "db_bytes_per_word": 12,  # 3 for valid+match, 1.5 carry-save tree; 1 + 0.25 POPC
                    "ncu": "ncu_paircount_r01e_csa.json"}}
 
@@ -534,7 +534,7 @@ def main():
     tr = ncu_traffic(ops["ncu"])
     if tr:   # algorithmic bytes of the captured launch: its slice of the streamed database once + one 16-byte record per pair
         tiles_k = (Q + 1 + 59) // 60 if st["pivot_fix_entries"] >= 0 else n_qtiles      # the pivot kernel's blocks take 60 slots (pivot tiles)
-        refs = tr["launch_grid_blocks"] // tiles_k * 64
+        refs = tr["launch_grid_blocks"] // tiles_k * (128 if st["pivot_fix_entries"] >= 0 else 64)    # references per thread block: pivot form 4 x 32, general 2 x 32
         tr["algorithmic_bytes"] = refs * ((W + 7) // 8 * 8) * ops["db_bytes_per_word"] + refs * (Q + 1) * 16
         tr["launch_refs"] = refs
     roofline = {"kernel": ops["kernel"], "bound": bound, "achieved": popc if bound == "int-popc" else lop3,

@@ -58,15 +58,21 @@ static_assert(sizeof(QChunk) % 16 == 0, "bulk copy size must be a multiple of 16
 // The counts serve the units in which a query holds no plain base at all (inside an N run, trimmed away): there
 // popc(r.base & nq) and popc(r.mc & ne) are the reference's own unit totals -- one add instead of 16 LOP3 + 4 POPC.
 #ifndef PIVOT_STAGES
-#define PIVOT_STAGES 9
+#define PIVOT_STAGES 7
 #endif
 constexpr int STAGES2 = PIVOT_STAGES;
 constexpr int UNIT2_PLANES = 2 * GROUP * 16;                         // base + mc of one (group, unit): 1 KB
 constexpr int UNIT2_MASKS = 4 * 4 * GROUP * 4;                       // column masks of one (group, unit): 2 KB
-constexpr int CHUNK2_PLANES = RPL * W4 * UNIT2_PLANES;               // 4 KB
-constexpr int CHUNK2_COUNTS = RPL * W4 * GROUP * 4;                  // 512 B
+#ifndef PIVOT_RPL
+#define PIVOT_RPL 4
+#endif
+constexpr int PRPL = PIVOT_RPL;                                      // reference groups per thread block of the pivot form = references per lane:
+                                                                     // what a warp does per chunk besides counting (wait, head, walk, release) is
+                                                                     // paid once per PRPL x 32 references
+constexpr int CHUNK2_PLANES = PRPL * W4 * UNIT2_PLANES;              // 8 KB
+constexpr int CHUNK2_COUNTS = PRPL * W4 * GROUP * 4;                 // 1 KB
 constexpr int CHUNK2_STAGED = CHUNK2_PLANES + CHUNK2_COUNTS;         // what a ring stage holds of a chunk record
-constexpr int CHUNK2_BYTES = CHUNK2_STAGED + RPL * W4 * UNIT2_MASKS; // 12.5 KB per (pair of groups, chunk)
+constexpr int CHUNK2_BYTES = CHUNK2_STAGED + PRPL * W4 * UNIT2_MASKS; // 25 KB per (PRPL groups, chunk)
 constexpr int PIVOT_QW = 4;                                          // query slots per counting warp of k_pairpivot
 constexpr int PIVOT_WARPS = 16;                                      // warp 0 only fills the staging ring, warps 1..15 count
 constexpr int PIVOT_SLOTS = (PIVOT_WARPS - 1) * PIVOT_QW;            // 60 query slots per thread block ("pivot tile"): consecutive slots,
@@ -74,10 +80,12 @@ constexpr int PIVOT_SLOTS = (PIVOT_WARPS - 1) * PIVOT_QW;            // 60 query
 // Query side of the pivot form: per (pivot tile of 60 slots, chunk) one variable-length record of a byte stream (PairParams::qstream,
 // offsets in PairParams::qoff), staged by one TMA bulk copy of exactly its size:
 //     QWarpHead head[16 warps]                          what each warp has to do in the chunk
-//     uint4     item[n]                                 per half (64 sites) that is counted from the planes: words 2h, 2h+1 of the
-//                                                       two COMPLEMENT planes of the slot -- nq (no plain base here, or trimmed /
-//                                                       padding) in .x .y, ne (not the pivot's base) in .z .w; the items of a warp
-//                                                       are contiguous, in the order the kernel walks them (unit, slot, half)
+//     uint2     item[n]                                 per half (64 sites) that is counted from the planes: words 2h, 2h+1 of the
+//                                                       COMPLEMENT plane of the slot -- nq: no plain base here, or trimmed /
+//                                                       padding.  (A plain base that differs from the pivot's is settled by its
+//                                                       fix entry, so "not the pivot's base" is the same plane.)  The items of a
+//                                                       warp are contiguous, in the order the kernel walks them (unit, slot, half);
+//                                                       a record is padded to a multiple of 16 bytes (bulk copy)
 // Only ~16 % of the (slot, half) pairs of a SARS-CoV-2 query set need an item: the record averages ~0.8 KB where the dense
 // planes of the tile took 4 KB of every ring stage.
 struct __align__(8) QWarpHead {
@@ -89,7 +97,8 @@ struct __align__(8) QWarpHead {
 };
 constexpr int QHEAD_BYTES = PIVOT_WARPS * (int)sizeof(QWarpHead);    // 128
 constexpr int QITEMS_MAX = QTILE * W4 * 2;                           // every half of every slot: 256
-constexpr int QREC_MAX = QHEAD_BYTES + QITEMS_MAX * 16;              // 4224: what a ring stage reserves
+constexpr int QITEM_BYTES = 8;                                       // words 2h, 2h+1 of the slot's complement plane
+constexpr int QREC_MAX = QHEAD_BYTES + QITEMS_MAX * QITEM_BYTES;     // 2176: what a ring stage reserves
 // A query site holding a plain base that differs from the pivot is outside the planes' match count; a reference holding
 // the same base there is one more match.  These "fix" entries (~the SNPs of the query, a few dozen per genome) are resolved
 // after the main loop against the column masks of the derived database: entry = chunk << 16 | unit << 9 | word << 7 |
@@ -97,19 +106,19 @@ constexpr int QREC_MAX = QHEAD_BYTES + QITEMS_MAX * 16;              // 4224: wh
 static_assert(W4 == 2 && PIVOT_WARPS == 16 && sizeof(QWarpHead) == 8 && PIVOT_SLOTS <= QTILE, "QWarpHead bit layout");
 __host__ __device__ inline size_t db2_chunk_bytes(int64_t group, int unit, int Wp)        // record of the chunk that holds (group, unit)
 {
-    return ((size_t)(group / RPL) * (size_t)(Wp / WC) + (size_t)(unit / W4)) * CHUNK2_BYTES;
+    return ((size_t)(group / PRPL) * (size_t)(Wp / WC) + (size_t)(unit / W4)) * CHUNK2_BYTES;
 }
 __host__ __device__ inline size_t db2_planes_bytes(int64_t group, int unit, int Wp)       // base plane of (group, unit); mc follows at + GROUP * 16
 {
-    return db2_chunk_bytes(group, unit, Wp) + (size_t)((group % RPL) * W4 + unit % W4) * UNIT2_PLANES;
+    return db2_chunk_bytes(group, unit, Wp) + (size_t)((group % PRPL) * W4 + unit % W4) * UNIT2_PLANES;
 }
 __host__ __device__ inline size_t db2_masks_bytes(int64_t group, int unit, int Wp)        // column masks of (group, unit)
 {
-    return db2_chunk_bytes(group, unit, Wp) + CHUNK2_STAGED + (size_t)((group % RPL) * W4 + unit % W4) * UNIT2_MASKS;
+    return db2_chunk_bytes(group, unit, Wp) + CHUNK2_STAGED + (size_t)((group % PRPL) * W4 + unit % W4) * UNIT2_MASKS;
 }
 __host__ __device__ inline size_t db2_counts_bytes(int64_t group, int unit, int Wp)       // unit totals of the 32 references of (group, unit)
 {
-    return db2_chunk_bytes(group, unit, Wp) + CHUNK2_PLANES + (size_t)((group % RPL) * W4 + unit % W4) * GROUP * 4;
+    return db2_chunk_bytes(group, unit, Wp) + CHUNK2_PLANES + (size_t)((group % PRPL) * W4 + unit % W4) * GROUP * 4;
 }
 
 // Heap slot (32 B): the reference's q_item (src/min_heap.h:14-18) with name -> ordinal.

@@ -355,8 +355,8 @@ static int ensure_db2(uvg_ctx* c)
     if (!c->pivot_on || c->db2_cap >= c->db_cap) return UVG_OK;
     int rc = sync_all(c);
     if (rc) return rc;
-    const size_t per_pair = (size_t)c->n_chunks * CHUNK2_BYTES;             // bytes per pair of groups (capacities are multiples of a pair)
-    const size_t pairs_old = (size_t)(c->db2_cap / (GROUP * RPL)), pairs_new = (size_t)(c->db_cap / (GROUP * RPL));
+    const size_t per_pair = (size_t)c->n_chunks * CHUNK2_BYTES;             // bytes per record set of PRPL groups (capacities are multiples of it)
+    const size_t pairs_old = (size_t)(c->db2_cap / (GROUP * PRPL)), pairs_new = (size_t)(c->db_cap / (GROUP * PRPL));
     uint8_t* n = nullptr;
     UVG_CUDA(c, cudaMalloc(&n, pairs_new * per_pair));
     // stream-ordered on c->st and waited for: the context's streams are non-blocking, a memset on the NULL stream is NOT ordered
@@ -689,14 +689,15 @@ extern "C" int uvg_set_queries(uvg_ctx* c, const uint8_t* text, int32_t n_query,
                                 for (int h = 0; h < 2; ++h) {
                                     if (!(ew[2 * h] | ew[2 * h + 1])) continue;
                                     hd.half |= (uint16_t)(1u << (u * 8 + j * 2 + h));
-                                    const uint32_t it[4] = {bw[2 * h], bw[2 * h + 1], ew[2 * h], ew[2 * h + 1]};
+                                    const uint32_t it[2] = {bw[2 * h], bw[2 * h + 1]};                  // ne == nq: one plane (pairpivot.cu)
                                     const uint8_t* ib = reinterpret_cast<const uint8_t*>(it);
-                                    rec.insert(rec.end(), ib, ib + 16);
+                                    rec.insert(rec.end(), ib, ib + QITEM_BYTES);
                                     ++n_items; ++hd.n_items;
                                 }
                             }
                         memcpy(&rec[h0 + (size_t)wp * sizeof(QWarpHead)], &hd, sizeof hd);
                     }
+                    if (rec.size() % 16) rec.resize(rec.size() + 16 - rec.size() % 16, 0);      // bulk copies move multiples of 16 bytes
                     tile_halves[pt] += n_items;
                 }
                 off.push_back((uint32_t)rec.size());
@@ -1021,7 +1022,7 @@ static int ensure_db_capacity(uvg_ctx* c, int64_t need_refs)
     int64_t cap = std::max<int64_t>(need_refs, c->db_cap * 2);
     cap = std::max<int64_t>(cap, c->prm.db_capacity);
     cap = std::max<int64_t>(cap, 4096);
-    cap = (cap + GROUP * RPL - 1) / (GROUP * RPL) * (GROUP * RPL);
+    cap = (cap + GROUP * PRPL - 1) / (GROUP * PRPL) * (GROUP * PRPL);     // whole records of the derived database (PRPL >= RPL groups)
     const size_t per_group = (size_t)(c->Wp / 4) * NPLANE * GROUP;            // uint4 per group
     const size_t og = (size_t)(c->db_cap / GROUP), ng = (size_t)(cap / GROUP);
     std::vector<void*>* defer = c->peer_db_live ? &c->deferred_free : nullptr;
@@ -1501,8 +1502,8 @@ static int run_round(uvg_ctx* c, int64_t lstart, int64_t cnt, int64_t T, int64_t
         UVG_CUDA(c, c->pivot_on ? launch_pairpivot(pp, c->st) : launch_paircount(pp, c->prm.acgt_mode, c->st));
         c->stats.pair_kernel_launches += 1;
         if (c->pivot_on) {   // executed (pair, 4-word unit) iterations per lane of this launch: blocks per tile x halves / 2 x references per lane
-            const int64_t per = GROUP * RPL, pairs = (lstart + cnt + per - 1) / per - lstart / per;
-            c->work_host += pairs * c->pivot_halves * RPL / 2;
+            const int64_t per = GROUP * PRPL, pairs = (lstart + cnt + per - 1) / per - lstart / per;
+            c->work_host += pairs * c->pivot_halves * PRPL / 2;
         }
     }
     UVG_CUDA(c, cudaEventRecord(eb, c->st));

@@ -38,21 +38,21 @@
 namespace uvg {
 
 // staged part of a chunk record of the derived database
-struct __align__(16) RefPlanes2 {
-    uint4 base[GROUP];
-    uint4 mc[GROUP];
+struct __align__(16) RefPlanes2 {           // half-major: a warp's 8-byte loads of one half are consecutive (no bank conflicts)
+    uint2 base[2][GROUP];                   // [half: words 0,1 | words 2,3][reference of the group]
+    uint2 mc[2][GROUP];
 };
 static_assert(sizeof(RefPlanes2) == UNIT2_PLANES, "planes of one (group, unit) of the derived database");
 struct __align__(16) Stage2 {
     uint8_t    q[QREC_MAX];              // QWarpHead[16] | items
-    RefPlanes2 ref[RPL][W4];
-    uint32_t   cnt[RPL][W4][GROUP];      // unit totals of every reference: popc(mc) | popc(base) << 16
+    RefPlanes2 ref[PRPL][W4];
+    uint32_t   cnt[PRPL][W4][GROUP];     // unit totals of every reference: popc(mc) | popc(base) << 16
 };
-static_assert(sizeof(RefPlanes2) * RPL * W4 == CHUNK2_PLANES && sizeof(Stage2) == QREC_MAX + CHUNK2_STAGED, "ring stage");
+static_assert(sizeof(RefPlanes2) * PRPL * W4 == CHUNK2_PLANES && sizeof(Stage2) == QREC_MAX + CHUNK2_STAGED, "ring stage");
 constexpr int PIVOT_MAX_CHUNKS = 256;                                  // < 65,536 columns
 constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(uint64_t) + (PIVOT_MAX_CHUNKS + 4) * sizeof(uint32_t);
 #ifndef PIVOT_UNROLL_UNITS
-#define PIVOT_UNROLL_UNITS 1
+#define PIVOT_UNROLL_UNITS 0
 #endif
 #ifndef PIVOT_PRODUCER_SLEEP
 #define PIVOT_PRODUCER_SLEEP 0   // ns the producer thread sleeps between two tests of a stage that is still in use
@@ -66,6 +66,9 @@ constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(ui
 #ifndef PIVOT_WALK_FFS
 #define PIVOT_WALK_FFS 0        // 1: the counted halves of a unit are walked by find-first-set + switch instead of eight bit tests
 #endif
+#ifndef PIVOT_DIRECT
+#define PIVOT_DIRECT 0          // 1: every counted word gets its own POPC (4 AND + 4 POPC + 4 IMAD per pair and half: ALU 4, XU 4, FMA 4)
+#endif                          //    instead of the carry-save step (8 LOP3 + 2 POPC + 2 IMAD: ALU 8) -- the walk keeps the ALU pipe busy
 #ifndef PIVOT_WAIT_HINT
 #define PIVOT_WAIT_HINT 0       // ns a counting warp may sleep inside the try_wait for its stage (0 = the default time limit)
 #endif
@@ -82,9 +85,9 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int pt = blockIdx.x % p.n_ptiles;                                  // pivot tile: slots [pt * 60, pt * 60 + 60)
-    const int64_t group0 = (p.local_begin / (GROUP * RPL) + blockIdx.x / p.n_ptiles) * RPL;
+    const int64_t group0 = (p.local_begin / (GROUP * PRPL) + blockIdx.x / p.n_ptiles) * PRPL;
     const uint32_t* qoff = p.qoff + (size_t)pt * (p.n_chunks + 1);
-    const uint8_t* rsrc = p.db2 + (size_t)(group0 / RPL) * (size_t)p.n_chunks * CHUNK2_BYTES;      // chunk records of this block's pair of groups
+    const uint8_t* rsrc = p.db2 + (size_t)(group0 / PRPL) * (size_t)p.n_chunks * CHUNK2_BYTES;      // chunk records of this block's pair of groups
     // shared-memory addresses as plain integers: nothing in the loop goes through a generic -> shared conversion
     uint32_t stage_a = smem_u32(stage);
     asm volatile("mov.u32 %0, %0;" : "+r"(stage_a));                         // opaque: kept in a register instead of being re-derived (S2R + LEA) per use
@@ -117,14 +120,18 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         for (int s = 0; s < STAGES2 && s < p.n_chunks; ++s) issue_at(s, s, s_qoff[s], s_qoff[s + 1]);
     }
 
-    // per pair: carry-save "ones" registers of the two complement streams and one packed counter
-    //     acc = (#weight-2 carries of r.mc & ne) * 2 | (#weight-2 carries of r.base & nq) * 2 << 16     (+ the unit totals of all-N units)
-    uint32_t oV[RPL][QW2], oM[RPL][QW2], acc[RPL][QW2];
+    // per pair one packed counter: what has to be SUBTRACTED from the reference's totals,
+    //     acc = sum popc(r.mc & ne) | sum popc(r.base & nq) << 16           (+ the unit totals of all-N units)
+    // Every counted word gets its own POPC (per pair and half 4 AND + 4 POPC + 4 IMAD: ALU 4, XU 4, FMA 4).  The carry-save
+    // step of the first half of the round (8 LOP3 + 2 POPC + 2 IMAD) suited a dense loop; this loop is mostly the walk, which
+    // keeps the ALU pipe busy while the XU pipe idles -- and without the "ones" registers a lane holds PRPL = 4 references.
+    uint32_t acc[PRPL][QW2];
 #pragma unroll
-    for (int g = 0; g < RPL; ++g)
+    for (int g = 0; g < PRPL; ++g)
 #pragma unroll
-        for (int j = 0; j < QW2; ++j) { oV[g][j] = 0; oM[g][j] = 0; acc[g][j] = 0; }
+        for (int j = 0; j < QW2; ++j) acc[g][j] = 0;
 
+    const uint32_t k1 = k2 >> 1, k64k = k128k >> 1;                          // run-time multipliers 1 and 1 << 16: IMAD stays on the FMA pipe
     if (warp == 0) {
         // ---- producer warp: keeps the ring full.  Chunk c goes into stage c % STAGES2 as soon as the fifteen counting warps
         // have released what the stage held before; it has no slots of its own, so nobody ever waits for its counting work ----
@@ -161,7 +168,7 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         hd.x = __shfl_sync(0xffffffffu, hd.x, 0); hd.y = __shfl_sync(0xffffffffu, hd.y, 0);
 #endif
         const uint32_t hmask = hd.x & 0xffffu, nmask = (hd.x >> 16) & 0xffu;
-        const uint4* item = reinterpret_cast<const uint4*>(st.q + QHEAD_BYTES) + (hd.y & 0xffffu);
+        const uint2* item = reinterpret_cast<const uint2*>(st.q + QHEAD_BYTES) + (hd.y & 0xffffu);
 #if PIVOT_UNROLL_UNITS
 #pragma unroll
 #else
@@ -170,77 +177,39 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         for (int u = 0; u < W4; ++u) {
             const uint32_t nu = (nmask >> (u * 4)) & 15u;
             if (nu) {                                                        // all-N units: the reference's own unit totals
-                uint32_t ct[RPL];
+                uint32_t ct[PRPL];
 #pragma unroll
-                for (int g = 0; g < RPL; ++g) ct[g] = st.cnt[g][u][lane];
+                for (int g = 0; g < PRPL; ++g) ct[g] = st.cnt[g][u][lane];
 #pragma unroll
                 for (int j = 0; j < QW2; ++j)
                     if ((nu >> j) & 1u) {
 #pragma unroll
-                        for (int g = 0; g < RPL; ++g) acc[g][j] += ct[g];
+                        for (int g = 0; g < PRPL; ++g) acc[g][j] += ct[g];
                     }
             }
             const uint32_t hu = (hmask >> (u * 8)) & 255u;
             if (hu == 0u) continue;
-            uint4 rb[RPL], rm[RPL];
-#pragma unroll
-            for (int g = 0; g < RPL; ++g) { rb[g] = st.ref[g][u].base[lane]; rm[g] = st.ref[g][u].mc[lane]; }
-#if PIVOT_WALK_FFS
-            // walk the set bits only (1.6 of the 16 halves of a chunk are counted): find-first-set + a switch over the (slot, half)
-            // the bit names, whose cases are the same straight-line blocks -- instead of eight tests per unit
-            uint32_t todo = hu;
-            do {
-                const int b = __ffs((int)todo) - 1;
-                todo &= todo - 1u;
-                const uint4 q = *item++;                                     // nq words 2h, 2h+1 | ne words 2h, 2h+1
-#define PIVOT_HALF(J, W0, W1)                                                                       \
-                    _Pragma("unroll") for (int g = 0; g < RPL; ++g) {                               \
-                        uint32_t ov = oV[g][J], om = oM[g][J], cv, cm;                              \
-                        csa(ov, cv, ov, rb[g].W0 & q.x, rb[g].W1 & q.y);                            \
-                        csa(om, cm, om, rm[g].W0 & q.z, rm[g].W1 & q.w);                            \
-                        oV[g][J] = ov; oM[g][J] = om;                                               \
-                        acc[g][J] = imad(__popc(cm), k2, imad(__popc(cv), k128k, acc[g][J]));       \
-                    }
-                switch (b) {
-                    case 0: PIVOT_HALF(0, x, y) break;
-                    case 1: PIVOT_HALF(0, z, w) break;
-                    case 2: PIVOT_HALF(1, x, y) break;
-                    case 3: PIVOT_HALF(1, z, w) break;
-                    case 4: PIVOT_HALF(2, x, y) break;
-                    case 5: PIVOT_HALF(2, z, w) break;
-                    case 6: PIVOT_HALF(3, x, y) break;
-                    default: PIVOT_HALF(3, z, w) break;
-                }
-#undef PIVOT_HALF
-            } while (todo);
-#else
+            // the loop over the slots is unrolled (a slot's counters are registers), the loops over units and halves are not: with
+            // four references per lane the fully unrolled walk was 16.6 KB of SASS and half of all warp samples waited for
+            // instructions (profiles/ncu_pairpivot_r02av_*); a unit or half only moves the shared-memory address
 #pragma unroll
             for (int j = 0; j < QW2; ++j) {
                 const uint32_t hj = (hu >> (j * 2)) & 3u;
-                if (hj & 1u) {
-                    const uint4 q = *item++;                                 // nq words 0, 1 | ne words 0, 1
+                if (hj == 0u) continue;
+#pragma unroll 1
+                for (int h = 0; h < 2; ++h) {
+                    if (!((hj >> h) & 1u)) continue;
+                    const uint2 q = *item++;                                 // nq words 2h, 2h+1
 #pragma unroll
-                    for (int g = 0; g < RPL; ++g) {
-                        uint32_t ov = oV[g][j], om = oM[g][j], cv, cm;
-                        csa(ov, cv, ov, rb[g].x & q.x, rb[g].y & q.y);
-                        csa(om, cm, om, rm[g].x & q.z, rm[g].y & q.w);
-                        oV[g][j] = ov; oM[g][j] = om;
-                        acc[g][j] = imad(__popc(cm), k2, imad(__popc(cv), k128k, acc[g][j]));
-                    }
-                }
-                if (hj & 2u) {
-                    const uint4 q = *item++;                                 // words 2, 3
-#pragma unroll
-                    for (int g = 0; g < RPL; ++g) {
-                        uint32_t ov = oV[g][j], om = oM[g][j], cv, cm;
-                        csa(ov, cv, ov, rb[g].z & q.x, rb[g].w & q.y);
-                        csa(om, cm, om, rm[g].z & q.z, rm[g].w & q.w);
-                        oV[g][j] = ov; oM[g][j] = om;
-                        acc[g][j] = imad(__popc(cm), k2, imad(__popc(cv), k128k, acc[g][j]));
+                    for (int g = 0; g < PRPL; ++g) {
+                        // words 2h, 2h+1 of the reference's two planes: 8 bytes each, transient registers
+                        const uint2 rb = st.ref[g][u].base[h][lane];
+                        const uint2 rm = st.ref[g][u].mc[h][lane];
+                        acc[g][j] = imad(__popc(rm.x & q.x), k1, imad(__popc(rm.y & q.y), k1,
+                                    imad(__popc(rb.x & q.x), k64k, imad(__popc(rb.y & q.y), k64k, acc[g][j]))));
                     }
                 }
             }
-#endif
         }
         // release the stage to the producer warp
         __syncwarp();
@@ -257,11 +226,6 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
     // chunk records), then the 32 x 32 bit matrix (entry x reference) is transposed across the warp (5 butterfly steps), so
     // that every lane holds the 32 entries' bits of ITS reference and one POPC counts them: ~2 instructions per entry and
     // group instead of a serial bit test per entry (r01: ~18 per entry in the epilogue, 12x the main loop on config 4). ----
-    // the carry-save "ones" registers are folded into the packed counters: the corrections below need the registers
-#pragma unroll
-    for (int g = 0; g < RPL; ++g)
-#pragma unroll
-        for (int j = 0; j < QW2; ++j) acc[g][j] += (uint32_t)__popc(oM[g][j]) + ((uint32_t)__popc(oV[g][j]) << 16);
     // slots of the pivot tile this warp counted (-1: none), broadcast from lane 0 like everything below that is the same for
     // all lanes (list bounds, owners): the compiler then keeps it in uniform registers and the loops need no convergence barriers
     int slot_of[QW2];
@@ -276,8 +240,10 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         }
     }
     // matches by fix entries, partial by ambiguity codes; the valid sites the codes add are folded into the counter at once
-    // (it holds what is SUBTRACTED from the reference's total, modulo 2^16: alignments of the pivot form have < 65,536 columns)
-    uint32_t fh[RPL][QW2], fp[RPL][QW2];
+    // (it holds what is SUBTRACTED from the reference's total, modulo 2^16: alignments of the pivot form have < 65,536 columns).
+    // Corrections and epilogue run in passes of TG = 2 reference groups, so that the per-pair correction registers stay few.
+    constexpr int TG = 2;
+    static_assert(PRPL % TG == 0, "passes of the tail");
     auto transpose32 = [&](uint32_t x) -> uint32_t {
 #pragma unroll
         for (int j = 16; j >= 1; j >>= 1) {
@@ -292,85 +258,88 @@ __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams
         return rsrc + (size_t)(w / WC) * CHUNK2_BYTES + CHUNK2_STAGED + ((w % WC) / 4) * UNIT2_MASKS + (((w & 3u) * 4u) * 32u + (site & 31u)) * 4u;
     };
 #pragma unroll
-    for (int j = 0; j < QW2; ++j) {
-#pragma unroll
-        for (int g = 0; g < RPL; ++g) { fh[g][j] = 0; fp[g][j] = 0; }
-        const int slot = slot_of[j];
-        if (slot < 0) continue;
-        uint32_t e1 = __shfl_sync(0xffffffffu, __ldg(p.snp_off + slot + 1), 0);
-        for (uint32_t e0 = __shfl_sync(0xffffffffu, __ldg(p.snp_off + slot), 0); e0 < e1; e0 += 32) {
-            const bool have = e0 + lane < e1;
-            const uint32_t ent = have ? __ldg(p.snp_ent + e0 + lane) : 0u;
-            const uint8_t* mrec = rsrc + (size_t)(ent >> 16) * CHUNK2_BYTES + CHUNK2_STAGED + ((ent >> 9) & 1u) * UNIT2_MASKS;
-            const uint32_t oq = (ent & 0x1ffu) * 4u, op = ((ent & 0x19fu) | ((ent >> 5) & 0x60u)) * 4u;       // same word and site, the query's / the pivot's base
-            uint32_t mq[RPL], mp[RPL];
-#pragma unroll
-            for (int g = 0; g < RPL; ++g) {
-                mq[g] = have ? __ldg(reinterpret_cast<const uint32_t*>(mrec + g * (W4 * UNIT2_MASKS) + oq)) : 0u;
-                mp[g] = have ? __ldg(reinterpret_cast<const uint32_t*>(mrec + g * (W4 * UNIT2_MASKS) + op)) : 0u;
-            }
-#pragma unroll
-            for (int g = 0; g < RPL; ++g) {
-                // the planes counted the site as "query holds the pivot's base": take back the references that hold it, add those
-                // that hold the query's base
-                if (__ballot_sync(0xffffffffu, mq[g] != 0u)) fh[g][j] += __popc(transpose32(mq[g]));
-                fh[g][j] -= __popc(transpose32(mp[g]));
-            }
-        }
-        e1 = __shfl_sync(0xffffffffu, __ldg(p.qamb_off + slot + 1), 0);
-        for (uint32_t e0 = __shfl_sync(0xffffffffu, __ldg(p.qamb_off + slot), 0); e0 < e1; e0 += 32) {
-            const bool have = e0 + lane < e1;
-            const uint32_t ent = have ? __ldg(p.qamb_ent + e0 + lane) : 0u, code = ent >> 28;
-            const uint8_t* mrec = mask_words(ent & AMB_SITE_MASK);
-#pragma unroll
-            for (int g = 0; g < RPL; ++g) {
-                uint32_t vm = 0, pm = 0;
-                if (have) {
-#pragma unroll
-                    for (int a = 0; a < 4; ++a) {
-                        const uint32_t m = __ldg(reinterpret_cast<const uint32_t*>(mrec + g * (W4 * UNIT2_MASKS) + a * 128));
-                        vm |= m;
-                        pm |= (code >> a) & 1u ? m : 0u;
-                    }
-                }
-                acc[g][j] -= (uint32_t)__popc(transpose32(vm)) << 16;
-                fp[g][j] += __popc(transpose32(pm));
-            }
-        }
-    }
-
-    // ---- epilogue: plane counts -> exact counts -> score tile of the owner (the four counts of alignment.c:866-879).  The sites
-    // where the REFERENCE holds an ambiguity code are outside its planes: its (short) list is walked once per reference and
-    // every entry is looked up in the 4-bit codes of the warp's four slots (pair_epilogue.cuh does the same per pair). ----
-    // the score rows belong to the 64-slot tiles of the search: owner rank and row inside the owner's score tile
-#pragma unroll
-    for (int g = 0; g < RPL; ++g) {
-        const int64_t local = (group0 + g) * GROUP + lane;
-        if (local < p.local_begin || local >= p.local_end) continue;
-        int32_t dv[QW2], dp[QW2], dt[QW2];
-#pragma unroll
-        for (int j = 0; j < QW2; ++j) { dv[j] = 0; dp[j] = 0; dt[j] = 0; }
-        const uint32_t re1 = p.ramb_off[local + 1];
-        for (uint32_t e = p.ramb_off[local]; e < re1; ++e) {
-            const uint32_t ent = __ldg(p.ramb_ent + e), site = ent & AMB_SITE_MASK, rc = ent >> 28;
-#pragma unroll
-            for (int j = 0; j < QW2; ++j) {
-                if (slot_of[j] < 0) continue;
-                const uint32_t qc = (__ldg(p.qnib + (size_t)slot_of[j] * p.qnib_stride + (site >> 3)) >> ((site & 7u) * 4u)) & 15u;
-                dv[j] += qc != 0u; dp[j] += (qc & rc) != 0u; dt[j] += qc == rc;
-            }
-        }
-        const int32_t mc_total = p.mc_cnt[local], rb_total = p.rb_cnt[local];
+    for (int gp = 0; gp < PRPL; gp += TG) {
+        uint32_t fh[TG][QW2], fp[TG][QW2];
 #pragma unroll
         for (int j = 0; j < QW2; ++j) {
+#pragma unroll
+            for (int g = 0; g < TG; ++g) { fh[g][j] = 0; fp[g][j] = 0; }
             const int slot = slot_of[j];
             if (slot < 0) continue;
-            const int32_t M = mc_total - (int32_t)(acc[g][j] & 0xffffu) + (int32_t)fh[g][j];
-            const int32_t V = (int32_t)(((uint32_t)rb_total - (acc[g][j] >> 16)) & 0xffffu);
-            // acgt, text, partial (+ the query's ambiguity codes), valid
-            const uint4 v = make_uint4((uint32_t)M, (uint32_t)(M + dt[j]), (uint32_t)(M + dp[j]) + fp[g][j], (uint32_t)(V + dv[j]));
-            const int qt = slot / QTILE;                                     // uniform: one division per slot and reference group
-            pair_store(p, qt % p.world, (qt / p.world) * QTILE + slot % QTILE, slot == p.n_slots - 1, local, v);
+            uint32_t e1 = __shfl_sync(0xffffffffu, __ldg(p.snp_off + slot + 1), 0);
+            for (uint32_t e0 = __shfl_sync(0xffffffffu, __ldg(p.snp_off + slot), 0); e0 < e1; e0 += 32) {
+                const bool have = e0 + lane < e1;
+                const uint32_t ent = have ? __ldg(p.snp_ent + e0 + lane) : 0u;
+                const uint8_t* mrec = rsrc + (size_t)(ent >> 16) * CHUNK2_BYTES + CHUNK2_STAGED + ((ent >> 9) & 1u) * UNIT2_MASKS + gp * (W4 * UNIT2_MASKS);
+                const uint32_t oq = (ent & 0x1ffu) * 4u, op = ((ent & 0x19fu) | ((ent >> 5) & 0x60u)) * 4u;       // same word and site, the query's / the pivot's base
+                uint32_t mq[TG], mp[TG];
+#pragma unroll
+                for (int g = 0; g < TG; ++g) {
+                    mq[g] = have ? __ldg(reinterpret_cast<const uint32_t*>(mrec + g * (W4 * UNIT2_MASKS) + oq)) : 0u;
+                    mp[g] = have ? __ldg(reinterpret_cast<const uint32_t*>(mrec + g * (W4 * UNIT2_MASKS) + op)) : 0u;
+                }
+#pragma unroll
+                for (int g = 0; g < TG; ++g) {
+                    // the planes counted the site as "query holds the pivot's base": take back the references that hold it, add those
+                    // that hold the query's base
+                    if (__ballot_sync(0xffffffffu, mq[g] != 0u)) fh[g][j] += __popc(transpose32(mq[g]));
+                    fh[g][j] -= __popc(transpose32(mp[g]));
+                }
+            }
+            e1 = __shfl_sync(0xffffffffu, __ldg(p.qamb_off + slot + 1), 0);
+            for (uint32_t e0 = __shfl_sync(0xffffffffu, __ldg(p.qamb_off + slot), 0); e0 < e1; e0 += 32) {
+                const bool have = e0 + lane < e1;
+                const uint32_t ent = have ? __ldg(p.qamb_ent + e0 + lane) : 0u, code = ent >> 28;
+                const uint8_t* mrec = mask_words(ent & AMB_SITE_MASK) + gp * (W4 * UNIT2_MASKS);
+#pragma unroll
+                for (int g = 0; g < TG; ++g) {
+                    uint32_t vm = 0, pm = 0;
+                    if (have) {
+#pragma unroll
+                        for (int a = 0; a < 4; ++a) {
+                            const uint32_t m = __ldg(reinterpret_cast<const uint32_t*>(mrec + g * (W4 * UNIT2_MASKS) + a * 128));
+                            vm |= m;
+                            pm |= (code >> a) & 1u ? m : 0u;
+                        }
+                    }
+                    acc[gp + g][j] -= (uint32_t)__popc(transpose32(vm)) << 16;
+                    fp[g][j] += __popc(transpose32(pm));
+                }
+            }
+        }
+
+        // ---- epilogue: plane counts -> exact counts -> score tile of the owner (the four counts of alignment.c:866-879).  The
+        // sites where the REFERENCE holds an ambiguity code are outside its planes: its (short) list is walked once per reference
+        // and every entry is looked up in the 4-bit codes of the warp's four slots (pair_epilogue.cuh does the same per pair). ----
+#pragma unroll
+        for (int g = 0; g < TG; ++g) {
+            const int64_t local = (group0 + gp + g) * GROUP + lane;
+            if (local < p.local_begin || local >= p.local_end) continue;
+            int32_t dv[QW2], dp[QW2], dt[QW2];
+#pragma unroll
+            for (int j = 0; j < QW2; ++j) { dv[j] = 0; dp[j] = 0; dt[j] = 0; }
+            const uint32_t re1 = p.ramb_off[local + 1];
+            for (uint32_t e = p.ramb_off[local]; e < re1; ++e) {
+                const uint32_t ent = __ldg(p.ramb_ent + e), site = ent & AMB_SITE_MASK, rc = ent >> 28;
+#pragma unroll
+                for (int j = 0; j < QW2; ++j) {
+                    if (slot_of[j] < 0) continue;
+                    const uint32_t qc = (__ldg(p.qnib + (size_t)slot_of[j] * p.qnib_stride + (site >> 3)) >> ((site & 7u) * 4u)) & 15u;
+                    dv[j] += qc != 0u; dp[j] += (qc & rc) != 0u; dt[j] += qc == rc;
+                }
+            }
+            const int32_t mc_total = p.mc_cnt[local], rb_total = p.rb_cnt[local];
+#pragma unroll
+            for (int j = 0; j < QW2; ++j) {
+                const int slot = slot_of[j];
+                if (slot < 0) continue;
+                const int32_t M = mc_total - (int32_t)(acc[gp + g][j] & 0xffffu) + (int32_t)fh[g][j];
+                const int32_t V = (int32_t)(((uint32_t)rb_total - (acc[gp + g][j] >> 16)) & 0xffffu);
+                // acgt, text, partial (+ the query's ambiguity codes), valid
+                const uint4 v = make_uint4((uint32_t)M, (uint32_t)(M + dt[j]), (uint32_t)(M + dp[j]) + fp[g][j], (uint32_t)(V + dv[j]));
+                const int qt = slot / QTILE;                                 // uniform: one division per slot and reference group
+                pair_store(p, qt % p.world, (qt / p.world) * QTILE + slot % QTILE, slot == p.n_slots - 1, local, v);
+            }
         }
     }
 }
@@ -406,8 +375,8 @@ __global__ void __launch_bounds__(256) k_derive_pivot(const uint4* __restrict__ 
     RefPlanes2* rec = reinterpret_cast<RefPlanes2*>(db2 + db2_planes_bytes(group, unit, Wp));
     uint32_t* colmask = reinterpret_cast<uint32_t*>(db2 + db2_masks_bytes(group, unit, Wp));     // [word][base A,C,G,T][site in word]
     if (fresh) {
-        rec->base[lane] = rb;
-        rec->mc[lane] = mc;
+        rec->base[0][lane] = make_uint2(rb.x, rb.y); rec->base[1][lane] = make_uint2(rb.z, rb.w);
+        rec->mc[0][lane] = make_uint2(mc.x, mc.y); rec->mc[1][lane] = make_uint2(mc.z, mc.w);
         reinterpret_cast<uint32_t*>(db2 + db2_counts_bytes(group, unit, Wp))[lane] =
             (uint32_t)(__popc(mc.x) + __popc(mc.y) + __popc(mc.z) + __popc(mc.w)) | (uint32_t)(__popc(rb.x) + __popc(rb.y) + __popc(rb.z) + __popc(rb.w)) << 16;
         atomicAdd(rb_cnt + ordinal, __popc(rb.x) + __popc(rb.y) + __popc(rb.z) + __popc(rb.w));
@@ -440,7 +409,7 @@ cudaError_t pairpivot_setup()
 cudaError_t launch_pairpivot(const PairParams& p, cudaStream_t st)
 {
     if (p.local_end <= p.local_begin) return cudaSuccess;
-    const int64_t per = GROUP * RPL;
+    const int64_t per = GROUP * PRPL;
     const int64_t g0 = p.local_begin / per, g1 = (p.local_end + per - 1) / per;
     const int64_t blocks = (g1 - g0) * p.n_ptiles;
     if (blocks > 0x7fffffffLL || p.n_chunks > PIVOT_MAX_CHUNKS) return cudaErrorInvalidConfiguration;
