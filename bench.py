@@ -30,8 +30,9 @@ NCHAR = 29903
 # result checksums (sum over every table of the six counts and the reference ordinals) of single-GPU runs, asserted at any N
 KNOWN_CHECKSUMS = {(1000, 1_000_000, 29903, 100, 0.0, 200): 31652904200}
 # algorithmic instruction counts per (pair, 32-site word) of the two pair-count kernels
-OPS = {"pivot": {"kernel": "k_pairpivot", "lop3": 4.0, "popc": 1.0, "db_bytes_per_word": 9,      # 2 AND + 2 x (one 3:2 compressor per two words); 2 x 0.5 POPC;
-                                                                                                  # staged: planes + counts, 4.5 KB per 64 references x 8 words
+OPS = {"pivot": {"kernel": "k_pairpivot", "lop3": 2.0, "popc": 2.0, "db_bytes_per_word": 9,      # per pair-word 2 AND + 2 POPC (+ 2 IMAD on the FMA pipe): every counted word
+                                                                                                  # gets its own POPC (the first half of the round used a carry-save step:
+                                                                                                  # 4 LOP3 + 1 POPC); staged: planes + counts, 9 KB per 128 references x 8 words
                  "ncu": "ncu_pairpivot_r02bb_four_refs_per_lane.json"},
        "general": {"kernel": "k_paircount", "lop3": 4.5, "popc": 1.25, "db_bytes_per_word": 12,  # 3 for valid+match, 1.5 carry-save tree; 1 + 0.25 POPC
                    "ncu": "ncu_paircount_r01e_csa.json"}}
@@ -550,13 +551,15 @@ def main():
                 "executed_pairwords_per_step": pairwords_rank, "dense_pairwords_per_step": pairwords_dense,
                 "executed_fraction_of_dense": pairwords_rank / max(1, pairwords_dense),
                 # the pivot form skips (query, 128-site unit) pairs where the query is complete and equal to the pivot: the same
-                # search priced with the DENSE op count of its formulation (what a kernel that does not skip would have to issue)
-                "frac_if_priced_dense": max(f_l, f_p) * pairwords_dense / max(1.0, pairwords_rank),
+                # search priced with the DENSE op count of the dense pivot formulation (4 LOP3 per pair-word on the LOP3 peak: what a
+                # kernel that does not skip would have to issue)
+                "frac_if_priced_dense": 4.0 * pairwords_dense / (k_ms * 1e-3) / 1e9 / peaks["lop3_gips"],
                 # continuity with round 1, whose kernel executed 0.3588 of the dense pair-words of this workload (whole 128-site
-                # units): the same search priced on THAT work.  The r02 kernel gives the same tables executing 0.160 (all-N units come
-                # from a counts table, the rest is counted in 64-site halves), so `frac` per executed pair-word fell while the search
-                # got faster; this key is an explanation, not the roofline claim
-                "frac_at_r01_work": (ops["lop3"] * 0.3588 * pairwords_dense / (k_ms * 1e-3) / 1e9 / peaks["lop3_gips"]) if st["pivot_fix_entries"] >= 0 else None,
+                # units) at 4 LOP3 each: the same search priced on THAT work.  The r02 kernel gives the same tables executing 0.096 (all-N
+                # units come from a counts table, the rest is counted in 64-site halves, SNP-only halves are settled by fix entries) at
+                # 2 AND + 2 POPC each, so `frac` per executed pair-word is a different quantity; this key is an explanation, not the
+                # roofline claim
+                "frac_at_r01_work": (4.0 * 0.3588 * pairwords_dense / (k_ms * 1e-3) / 1e9 / peaks["lop3_gips"]) if st["pivot_fix_entries"] >= 0 else None,
                 "pivot_fix_entries_per_query": (st["pivot_fix_entries"] / max(1, Q + 1)) if st["pivot_fix_entries"] >= 0 else None}
 
     cb = None
