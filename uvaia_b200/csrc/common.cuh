@@ -46,17 +46,18 @@ static_assert(sizeof(QChunk) % 16 == 0, "bulk copy size must be a multiple of 16
 //     mc  = sites where the REFERENCE holds the pivot base         (derived database plane, one pass per query set)
 //     qeq = sites where the QUERY holds the pivot base
 // the match word of a pair is mc & qeq and the valid word r.base & q.base: two ANDs instead of three LOP3 with five
-// inputs.  The kernel works on the COMPLEMENTS (nq = no plain base here, ne = not the pivot's base): valid = popc(r.base) -
-// sum popc(r.base & nq), match' = popc(r.mc) - sum popc(r.mc & ne), with per-reference totals as first terms and sums
-// that only get contributions where the query has an N, a gap, a code or a SNP; both popcounts go through a 2-word
-// carry-save step (4 LOP3 + 1 POPC per counted pair-word, balanced for the measured 4:1 LOP3:POPC issue ratio).
-// Derived database: per (pair of groups = the 64 references of a thread block, chunk of WC column words) one contiguous
-// 12 KB record
-//     planes   [group of the pair][unit][ uint4 base[32] | uint4 mc[32] ]                    4 KB  \ staged by TMA bulk copies
-//     counts   [group of the pair][unit][32 references] uint32: popc(mc unit) | popc(base unit) << 16   512 B /
-//     colmasks [group of the pair][unit][4 words][4 bases A,C,G,T][32 sites] uint32         8 KB: read by fix entries only
+// inputs.  The kernel works on the COMPLEMENT nq = no plain base here (every plain base counts as the pivot's; one that
+// differs is settled by its fix entry): valid = popc(r.base) - sum popc(r.base & nq), match' = popc(r.mc) - sum popc(r.mc &
+// nq), with per-reference totals as first terms and sums that only get contributions where the query has an N, a gap or a
+// code; every counted word gets its own POPC (2 AND + 2 POPC + 2 IMAD per counted pair-word).
+// Derived database: per (PRPL = 4 groups = the 128 references of a thread block, chunk of WC column words) one contiguous
+// 25 KB record
+//     planes   [group of the block][unit][ uint2 base[half][32] | uint2 mc[half][32] ]       8 KB  \ staged by TMA bulk copies
+//     counts   [group of the block][unit][32 references] uint32: popc(mc unit) | popc(base unit) << 16   1 KB /
+//     colmasks [group of the block][unit][4 words][4 bases A,C,G,T][32 sites] uint32        16 KB: read by fix entries only
+// (planes half-major: words 0,1 of the 32 references, then words 2,3 -- a warp's 8-byte loads of one half are consecutive).
 // The counts serve the units in which a query holds no plain base at all (inside an N run, trimmed away): there
-// popc(r.base & nq) and popc(r.mc & ne) are the reference's own unit totals -- one add instead of 16 LOP3 + 4 POPC.
+// popc(r.base & nq) and popc(r.mc & nq) are the reference's own unit totals -- one add instead of 8 AND + 8 POPC.
 #ifndef PIVOT_STAGES
 #define PIVOT_STAGES 7
 #endif

@@ -6,30 +6,33 @@
 // All queries of one search are close to a pivot sequence P (per site the plain base most queries hold; uvg_set_queries).
 // For a site where the query holds P's base, "query == reference" is "reference == P", which does not depend on the query:
 //     mc (reference plane, derived once per query set by k_derive_pivot) = r.base & (r == P)
-// The query planes are used INVERTED: nq = no plain base here (or trimmed away / padding), ne = not P's base (nq is a
-// subset of ne), so that
-//     valid  = popc(r.base) - sum popc(r.base & nq)        match' = popc(r.mc) - sum popc(r.mc & ne)
+// The query plane is used INVERTED: nq = no plain base here (or trimmed away / padding), so that
+//     valid  = popc(r.base) - sum popc(r.base & nq)        match' = popc(r.mc) - sum popc(r.mc & nq)
 // with per-reference totals (k_derive_pivot) as first terms and sums that only get contributions from sites where the query
-// has an N, a gap, an ambiguity code or a SNP.  Per (slot, 128-site unit) a warp does one of three things (QWarpHead):
-//   * nothing: the query is complete and equal to the pivot over the unit (~62 % of the units of a SARS-CoV-2 query set);
+// has an N, a gap or an ambiguity code.  match' treats EVERY plain base of the query as the pivot's; a base that differs (a
+// SNP, a few dozen per genome) is settled by its fix entry after the loop.  Per (slot, 128-site unit) a warp does one of
+// three things (QWarpHead):
+//   * nothing: the query holds a plain base everywhere in the unit (~75 % of the units of a SARS-CoV-2 query set);
 //   * one add from the counts table of the derived database: the query holds no plain base in the unit (inside an N run,
 //     trimmed away), so both sums are the reference's own unit totals (~12 %);
-//   * count up to two halves of 64 sites from the planes (~26 % of the units, 1.26 halves each): per pair and half 4 AND,
-//     one 3:2 compressor per stream (ones register + one carry word of weight 2), 2 POPC, 2 IMAD
-//         = 4 LOP3 (ALU) + 1 POPC (XU) + 1 IMAD (FMA) per counted pair and 32-site word,
-//     which balances the ALU and XU pipes at the measured 4:1 LOP3:POPC rate of sm_100 (profiles/int_pipes_b200_r01.json).
-// Query sites with a plain base != P (the query's own SNPs, a few dozen per genome) are outside match'; after the main loop
-// every warp resolves the fix entries of its four slots against the column masks of the derived database (per site and base
-// one word: bit l = reference l of the group holds that base): loads for 32 entries at a time, all independent.  Ambiguity
-// codes go through the shared epilogue (pair_epilogue.cuh).
-// Shape: block = 60 query slots ("pivot tile") x 64 references, 16 warps: warp 0 is the PRODUCER (it keeps the staging ring
-// full and counts nothing), warps 1..15 count 4 slots each, lane = 2 references; 64 registers, 2 blocks per SM.  Staging: a
-// ring of STAGES2 stages, each filled by two TMA bulk copies -- the (pivot tile, chunk) record of the query stream (variable
-// length: 128-byte head + 16 bytes per counted half, ~0.8 KB on average) and the planes + counts of the pair's chunk record
-// (4.5 KB) -- with full/empty mbarriers (no __syncthreads in the loop: warps drift up to the ring depth apart).  Why a warp
-// that only produces: a bulk copy costs its issuing warp ~200 cycles; a warp that issued the copies on top of an equal share
-// of the counting set the pace of the block, and the other fifteen waited for it at the head of the ring (r02 profile: 20 %
-// of all warp time in the full-barrier wait; rotating the duty among the warps was 1.6x slower still).
+//   * count up to two halves of 64 sites from the planes (~14 % of the units): per pair and half 4 AND + 4 POPC + 4 IMAD
+//         = 2 AND (ALU) + 2 POPC (XU) + 2 IMAD (FMA) per counted pair and 32-site word.
+//     (The first half of round 2 used a carry-save step, 4 LOP3 + 1 POPC + 1 IMAD, balanced for a dense loop; this loop is
+//     mostly the walk, which keeps the ALU pipe busy, and without the "ones" registers a lane holds four references.)
+// After the main loop every warp resolves the fix entries of its four slots against the column masks of the derived database
+// (per site and base one word: bit l = reference l of the group holds that base): minus the references that hold the pivot's
+// base, plus those that hold the query's; loads for 32 entries at a time, all independent, then a 32 x 32 bit transpose across
+// the warp.  The query's ambiguity codes go the same way; the references' codes are looked up per reference in the epilogue.
+// Shape: block = 60 query slots ("pivot tile") x 128 references, 16 warps: warp 0 is the PRODUCER (it keeps the staging ring
+// full and counts nothing), warps 1..15 count 4 slots each, lane = PRPL = 4 references (what a warp does per chunk besides
+// counting -- wait, head, walk, release -- is paid once per 128 references); 64 registers, 2 blocks per SM.  Staging: a ring
+// of STAGES2 stages, each filled by two TMA bulk copies -- the (pivot tile, chunk) record of the query stream (variable
+// length: 128-byte head + 8 bytes per counted half) and the planes + counts of the block's chunk record (9 KB) -- with
+// full/empty mbarriers (no __syncthreads in the loop: warps drift up to the ring depth apart).  7 stages = 80 KB per block: the
+// shared memory of the two blocks of an SM is carved out of the L1, and a deeper ring (205 KB per SM) measured 15 % slower.
+// Why a warp that only produces: a bulk copy costs its issuing warp ~200 cycles; a warp that issued the copies on top of an
+// equal share of the counting set the pace of the block, and the other fifteen waited for it at the head of the ring (r02
+// profile: 20 % of all warp time in the full-barrier wait; rotating the duty among the warps was 1.6x slower still).
 #include "common.cuh"
 #include "kernels.h"
 #include "pair_epilogue.cuh"
@@ -75,7 +78,7 @@ constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(ui
 #ifndef PIVOT_GRANULE
 #define PIVOT_GRANULE 0         // bytes per bulk copy of the reference side of a stage (0 = one copy of 4.5 KB; smaller copies measured slower)
 #endif
-constexpr int QW2 = PIVOT_QW;                           // query slots per warp (register tile QW2 x RPL pairs per lane)
+constexpr int QW2 = PIVOT_QW;                           // query slots per warp (register tile QW2 x PRPL pairs per lane)
 constexpr int PIVOT_THREADS = PIVOT_WARPS * 32;
 
 __global__ void __launch_bounds__(PIVOT_THREADS, 2) k_pairpivot(const PairParams p, const uint32_t k2, const uint32_t k128k)
