@@ -55,7 +55,7 @@ static_assert(sizeof(RefPlanes2) * PRPL * W4 == CHUNK2_PLANES && sizeof(Stage2) 
 constexpr int PIVOT_MAX_CHUNKS = 256;                                  // < 65,536 columns
 constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(uint64_t) + (PIVOT_MAX_CHUNKS + 4) * sizeof(uint32_t);
 #ifndef PIVOT_UNROLL_UNITS
-#define PIVOT_UNROLL_UNITS 0
+#define PIVOT_UNROLL_UNITS 0    // 1: the loop over the two units of a chunk is unrolled (twice the loop's instruction footprint: measured slower)
 #endif
 #ifndef PIVOT_PRODUCER_SLEEP
 #define PIVOT_PRODUCER_SLEEP 0   // ns the producer thread sleeps between two tests of a stage that is still in use
@@ -66,12 +66,6 @@ constexpr size_t PIVOT_SMEM = STAGES2 * sizeof(Stage2) + 2 * STAGES2 * sizeof(ui
 #ifndef PIVOT_CONSUMER_SLEEP
 #define PIVOT_CONSUMER_SLEEP 0  // ns a counting warp sleeps between two tests of a stage that has not arrived yet (0 = try_wait)
 #endif
-#ifndef PIVOT_WALK_FFS
-#define PIVOT_WALK_FFS 0        // 1: the counted halves of a unit are walked by find-first-set + switch instead of eight bit tests
-#endif
-#ifndef PIVOT_DIRECT
-#define PIVOT_DIRECT 0          // 1: every counted word gets its own POPC (4 AND + 4 POPC + 4 IMAD per pair and half: ALU 4, XU 4, FMA 4)
-#endif                          //    instead of the carry-save step (8 LOP3 + 2 POPC + 2 IMAD: ALU 8) -- the walk keeps the ALU pipe busy
 #ifndef PIVOT_WAIT_HINT
 #define PIVOT_WAIT_HINT 0       // ns a counting warp may sleep inside the try_wait for its stage (0 = the default time limit)
 #endif
