@@ -66,7 +66,10 @@ def test_create_rejects_bad_arguments_and_missing_device():
 def test_shard_schedule_partitions_ordinals_in_file_order():
     from uvaia_b200.engine import Engine
     from uvaia_b200.shard import rank_tiles
-    for world, first, mx, total in [(1, 32, 128, 1000), (2, 32, 128, 1000), (4, 64, 256, 5000), (8, 1024, 65536, 300000), (3, 32, 32, 333)]:
+    # incl. totals below one round, below the taper's floor of 4,096 per rank, and totals that end exactly on a round boundary
+    for world, first, mx, total in [(1, 32, 128, 1000), (2, 32, 128, 1000), (4, 64, 256, 5000), (8, 1024, 65536, 300000), (3, 32, 32, 333),
+                                    (2, 1024, 65536, 1), (8, 1024, 65536, 63), (2, 1024, 65536, 2 * (1024 + 4096 + 16384)), (4, 1024, 65536, 1_000_000),
+                                    (8, 1024, 65536, 1_000_000), (2, 16384, 65536, 140_000), (5, 64, 64, 64 * 5 * 7)]:
         seen = {}
         for rank in range(world):
             local = 0
